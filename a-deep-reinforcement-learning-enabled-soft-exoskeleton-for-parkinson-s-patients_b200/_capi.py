@@ -1,0 +1,89 @@
+"""ctypes binding of libexo_env.so (include/exo_env.h). Loading fails loudly: there is no CPU path."""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libexo_env.so")
+
+OBS_DIM, ACT_DIM, NLINKS, N_STATS = 80, 7, 19, 16
+F32, F64 = 0, 1
+ODE_PROPAGATOR, ODE_RK45 = 0, 1
+
+
+class ExoConfig(C.Structure):
+    _fields_ = [("tremor_amplitude_range", C.c_double * 2), ("first_harmonics_interval", C.c_double * 2),
+                ("second_harmonics_interval", C.c_double * 2),
+                ("max_force_shoulder", C.c_double), ("max_force_elbow", C.c_double),
+                ("dr_actuator_end_pos_shift", C.c_double), ("dr_actuator_range", C.c_double),
+                ("matrix_noise_fraction", C.c_double),
+                ("humerus_length", C.c_double), ("forearm_length", C.c_double), ("hand_length", C.c_double),
+                ("link_state_lag", C.c_int32), ("joint_limits", C.c_int32), ("precision", C.c_int32),
+                ("ode", C.c_int32), ("auto_reset", C.c_int32), ("reference_ctor", C.c_int32),
+                ("metrics", C.c_int32), ("reserved", C.c_int32)]
+
+
+class ExoGeometry(C.Structure):
+    _fields_ = [("parent", C.c_int32 * NLINKS), ("joint_type", C.c_int32 * NLINKS),
+                ("origin_xyz", (C.c_double * 3) * NLINKS), ("origin_R", (C.c_double * 9) * NLINKS),
+                ("axis", (C.c_double * 3) * NLINKS), ("com_xyz", (C.c_double * 3) * NLINKS),
+                ("lower", C.c_double * NLINKS), ("upper", C.c_double * NLINKS), ("base_pos", C.c_double * 3),
+                ("act_link", C.c_int32 * 14), ("shoulder_link", C.c_int32), ("elbow_link", C.c_int32)]
+
+
+class ExoInfo(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in ("actuator_torques", "torque_val", "ampl_val", "tremor_torque_val",
+                                          "tremor_ampl_val", "reward_parts", "amp_metric")]
+
+
+class ExoStateView(C.Structure):
+    _fields_ = [("n_envs", C.c_int32), ("stride", C.c_int32), ("precision", C.c_int32), ("table_len", C.c_int32),
+                ("table_axes", C.c_int32)] + \
+               [(k, C.c_void_p) for k in ("q", "q_lag", "pos_vec", "elbow_ref", "prev_action", "prev_action2", "force_max",
+                                          "shift", "G", "IDS", "tremor_table", "tremor_mag", "counts", "meta", "mt_state",
+                                          "ep_return")]
+
+
+# name -> (restype, argtypes); also the list tests check against include/exo_env.h
+SIGNATURES = {
+    "exo_last_error": (C.c_char_p, []),
+    "exo_abi_version": (C.c_int, []),
+    "exo_create": (C.c_int, [C.POINTER(ExoConfig), C.POINTER(ExoGeometry), C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
+    "exo_destroy": (C.c_int, [C.c_void_p]),
+    "exo_load_motions": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int32), C.c_int32, C.c_int32]),
+    "exo_set_env_types": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint8), C.POINTER(C.c_int32)]),
+    "exo_seed": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p]),
+    "exo_reset": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "exo_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(ExoInfo), C.c_void_p]),
+    "exo_step_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "exo_reset_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "exo_get_state": (C.c_int, [C.c_void_p, C.POINTER(ExoStateView)]),
+    "exo_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
+    "exo_launch_count": (C.c_int64, [C.c_void_p]),
+    "exo_forward_kinematics": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_void_p]),
+}
+
+_lib = None
+
+
+class ExoError(RuntimeError):
+    pass
+
+
+def load():
+    """dlopen libexo_env.so and bind every entry point. Raises if the library has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ExoError("%s is missing: run `python __graft_entry__.py build` (nvcc, sm_100a). "
+                           "There is no CPU implementation to fall back to." % LIB_PATH)
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise ExoError("libexo_env: %s (status %d)" % (load().exo_last_error().decode(), rc))

@@ -1,0 +1,396 @@
+// exo_api.cu — host side of libexo_env.so: the C-ABI declared in include/exo_env.h.
+// Owns the resident SoA state in HBM, flattens the URDF tree into the 5-joint chain constants and launches
+// the kernels of exo_step.cuh / exo_reset.cuh on the caller's stream. No CPU compute path exists here.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <vector>
+
+#include "../../include/exo_env.h"
+#include "exo_launch.h"
+
+using namespace exo;
+
+static thread_local char g_err[512] = "";
+static int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CK(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t _e = (call);                                                                         \
+        if (_e != cudaSuccess) return fail(EXO_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); \
+    } while (0)
+
+extern "C" const char* exo_last_error(void) { return g_err; }
+extern "C" int exo_abi_version(void) { return 1; }
+
+struct ExoHandle {
+    ExoConfig cfg;
+    ExoGeometry geo;
+    int n, stride, device, nax, max_len, n_motions;
+    bool have_motions, have_types, seeded;
+    int64_t launches;
+    std::vector<void*> allocs;
+    EnvArrays<float> Af;
+    EnvArrays<double> Ad;
+    ChainConst<float> Cf;
+    ChainConst<double> Cd;
+    // staging for the host-buffer entry points
+    float* d_act; float* d_obs; void* d_rew; uint8_t* d_done; uint8_t* d_mask;
+    uint32_t* d_seeds;
+    std::vector<int> motion_len;
+};
+
+static int dev_alloc(ExoHandle* h, void** p, size_t bytes, bool zero = true) {
+    CK(cudaMalloc(p, bytes ? bytes : 16));
+    h->allocs.push_back(*p);
+    if (zero) CK(cudaMemset(*p, 0, bytes ? bytes : 16));
+    return 0;
+}
+
+static void mat3mul(const double* A, const double* B, double* C) {
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) C[i * 3 + j] = A[i * 3] * B[j] + A[i * 3 + 1] * B[3 + j] + A[i * 3 + 2] * B[6 + j];
+}
+
+// Walk from a link up through prismatic joints (held at 0 by Bullet's default velocity motors) to the revolute
+// link (or base) that carries it; returns the carrier index and the point in the carrier's frame.
+static int carrier_of(const ExoGeometry* g, int link, double* off) {
+    double p[3] = {g->com_xyz[link][0], g->com_xyz[link][1], g->com_xyz[link][2]};
+    int l = link;
+    while (l >= 0 && g->joint_type[l] == 1) {
+        double q[3];
+        for (int i = 0; i < 3; i++)
+            q[i] = g->origin_xyz[l][i] + g->origin_R[l][i * 3] * p[0] + g->origin_R[l][i * 3 + 1] * p[1] + g->origin_R[l][i * 3 + 2] * p[2];
+        memcpy(p, q, sizeof(p));
+        l = g->parent[l];
+    }
+    memcpy(off, p, sizeof(p));
+    return l;
+}
+
+template <typename R>
+static void cast_chain(const ChainConst<double>& s, ChainConst<R>& d) {
+    const double* sp = reinterpret_cast<const double*>(&s);
+    R* dp = reinterpret_cast<R*>(&d);
+    for (size_t i = 0; i < sizeof(ChainConst<double>) / sizeof(double); i++) dp[i] = (R)sp[i];
+}
+
+static int build_chain(ExoHandle* h) {
+    const ExoGeometry* g = &h->geo;
+    ChainConst<double>& C = h->Cd;
+    memset(&C, 0, sizeof(C));
+    for (int i = 0; i < 5; i++) {
+        if (g->joint_type[i] != 0 || g->parent[i] != i - 1)
+            return fail(EXO_ERR_TOPOLOGY, "links 0..4 must be a serial chain of revolute joints (link %d)", i);
+        if (fabs(g->axis[i][0]) > 1e-12 || fabs(g->axis[i][1]) > 1e-12 || fabs(g->axis[i][2] - 1.0) > 1e-12)
+            return fail(EXO_ERR_TOPOLOGY, "revolute joint %d: axis must be local z", i);
+        memcpy(C.Rorg[i], g->origin_R[i], 9 * sizeof(double));
+        memcpy(C.porg[i], g->origin_xyz[i], 3 * sizeof(double));
+        C.lower[i] = g->lower[i];
+        C.upper[i] = g->upper[i];
+    }
+    for (int k = 0; k < 3; k++) C.p0[k] = g->base_pos[k] + g->origin_xyz[0][k];
+    // expected carriers, in the order act11,act12,act21,...,act72 : humerus=2, forearm=4, base=-1
+    static const int want[14] = {2, 4, 2, 4, -1, 2, -1, 2, -1, 2, -1, 2, -1, 2};
+    int hum = 0, alk = 0, fix = 0;
+    // slot order inside off_hum: act11, act21, act32, act42, act52, act62, act72
+    static const int hum_slot[14] = {0, -1, 1, -1, -1, 2, -1, 3, -1, 4, -1, 5, -1, 6};
+    for (int a = 0; a < 14; a++) {
+        double off[3];
+        const int c = carrier_of(g, g->act_link[a], off);
+        if (c != want[a]) return fail(EXO_ERR_TOPOLOGY, "actuator endpoint %d rides on link %d, kernel expects %d", a, c, want[a]);
+        if (c == 2) { memcpy(C.off_hum[hum_slot[a]], off, sizeof(off)); hum++; }
+        else if (c == 4) { memcpy(C.off_alk[alk++], off, sizeof(off)); }
+        else { for (int k = 0; k < 3; k++) C.fixed[fix][k] = g->base_pos[k] + off[k]; fix++; }
+    }
+    double off[3];
+    if (carrier_of(g, g->shoulder_link, off) != 0 || fabs(off[0]) + fabs(off[1]) + fabs(off[2]) > 0)
+        return fail(EXO_ERR_TOPOLOGY, "shoulder reference must be the origin of link 0");
+    memcpy(C.sh_ref, C.p0, sizeof(C.p0));
+    if (carrier_of(g, g->elbow_link, off) != 3) return fail(EXO_ERR_TOPOLOGY, "elbow reference must ride on link 3");
+    memcpy(C.off_elbow, off, sizeof(off));
+    (void)mat3mul;
+    cast_chain(C, h->Cf);
+    return 0;
+}
+
+template <typename R>
+static int alloc_arrays(ExoHandle* h, EnvArrays<R>& A) {
+    const size_t st = h->stride;
+    memset(&A, 0, sizeof(A));
+    A.n = h->n; A.stride = h->stride;
+#define AL(field, T, k) if (int rc = dev_alloc(h, (void**)&A.field, sizeof(T) * (size_t)(k) * st)) return rc
+    AL(q, R, 5); AL(qlag, R, 5); AL(posvec, R, 21); AL(elref, R, 3); AL(fprev, R, 7); AL(fprev2, R, 7); AL(ret, R, 1);
+    AL(counts, int, 1); AL(fmax, R, 2); AL(shift, R, 42); AL(G, R, 49); AL(IDS, double, 147); AL(mag, double, 1);
+    AL(meta, int, 1); AL(mt, uint32_t, 625);
+#undef AL
+    if (int rc = dev_alloc(h, (void**)&A.stats, sizeof(double) * EXO_N_STATS)) return rc;
+    return 0;
+}
+
+extern "C" int exo_create(const ExoConfig* cfg, const ExoGeometry* geo, int32_t n_envs, int32_t device, ExoHandle** out) {
+    if (!cfg || !geo || !out || n_envs <= 0) return fail(EXO_ERR_ARG, "exo_create: bad arguments");
+    if (cfg->precision != EXO_F32 && cfg->precision != EXO_F64) return fail(EXO_ERR_ARG, "precision must be EXO_F32 or EXO_F64");
+    if (cfg->ode != EXO_ODE_PROPAGATOR) return fail(EXO_ERR_ARG, "ode mode %d is not built in this version", cfg->ode);
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(EXO_ERR_CUDA, "device %d not present (%d CUDA devices): this library has no CPU path", device, ndev);
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return fail(EXO_ERR_CUDA, "device %d is sm_%d%d; libexo_env.so carries sm_100a code only", device, prop.major, prop.minor);
+    CK(cudaSetDevice(device));
+    ExoHandle* h = new ExoHandle();
+    h->cfg = *cfg; h->geo = *geo; h->n = n_envs; h->stride = (n_envs + 31) & ~31; h->device = device;
+    h->nax = 4; h->max_len = 0; h->n_motions = 0; h->have_motions = h->have_types = h->seeded = false; h->launches = 0;
+    h->d_act = nullptr; h->d_obs = nullptr; h->d_rew = nullptr; h->d_done = nullptr; h->d_mask = nullptr; h->d_seeds = nullptr;
+    if (int rc = build_chain(h)) { delete h; return rc; }
+    int rc = (cfg->precision == EXO_F32) ? alloc_arrays(h, h->Af) : alloc_arrays(h, h->Ad);
+    if (!rc) rc = dev_alloc(h, (void**)&h->d_act, sizeof(float) * 7 * (size_t)n_envs);
+    if (!rc) rc = dev_alloc(h, (void**)&h->d_obs, sizeof(float) * 80 * (size_t)n_envs);
+    if (!rc) rc = dev_alloc(h, (void**)&h->d_rew, sizeof(double) * (size_t)n_envs);
+    if (!rc) rc = dev_alloc(h, (void**)&h->d_done, (size_t)n_envs);
+    if (!rc) rc = dev_alloc(h, (void**)&h->d_mask, (size_t)n_envs);
+    if (!rc) rc = dev_alloc(h, (void**)&h->d_seeds, sizeof(uint32_t) * (size_t)n_envs);
+    if (rc) { exo_destroy(h); return rc; }
+    *out = h;
+    return 0;
+}
+
+extern "C" int exo_destroy(ExoHandle* h) {
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    for (void* p : h->allocs) cudaFree(p);
+    delete h;
+    return 0;
+}
+
+template <typename R>
+static int load_motions_t(ExoHandle* h, EnvArrays<R>& A, const double* tables, const int32_t* lengths, int nm, int max_len) {
+    std::vector<R> host((size_t)nm * 5 * max_len);
+    for (size_t i = 0; i < host.size(); i++) host[i] = (R)tables[i];
+    R* d; int* dl;
+    if (int rc = dev_alloc(h, (void**)&d, sizeof(R) * host.size(), false)) return rc;
+    if (int rc = dev_alloc(h, (void**)&dl, sizeof(int) * nm, false)) return rc;
+    CK(cudaMemcpy(d, host.data(), sizeof(R) * host.size(), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dl, lengths, sizeof(int) * nm, cudaMemcpyHostToDevice));
+    A.motion = d; A.motion_len = dl; A.max_len = max_len; A.n_motions = nm;
+    return 0;
+}
+
+extern "C" int exo_load_motions(ExoHandle* h, const double* tables, const int32_t* lengths, int32_t n_motions, int32_t max_len) {
+    if (!h || !tables || !lengths || n_motions <= 0 || n_motions > 255) return fail(EXO_ERR_ARG, "exo_load_motions: bad arguments");
+    if (h->have_motions) return fail(EXO_ERR_STATE, "motions already loaded");
+    for (int m = 0; m < n_motions; m++)
+        if (lengths[m] < 5 || lengths[m] > max_len || lengths[m] > EXO_MAX_LEN) return fail(EXO_ERR_ARG, "motion %d: length %d out of range", m, lengths[m]);
+    CK(cudaSetDevice(h->device));
+    int rc = h->cfg.precision == EXO_F32 ? load_motions_t(h, h->Af, tables, lengths, n_motions, max_len)
+                                         : load_motions_t(h, h->Ad, tables, lengths, n_motions, max_len);
+    if (rc) return rc;
+    h->motion_len.assign(lengths, lengths + n_motions);
+    h->max_len = max_len; h->n_motions = n_motions; h->have_motions = true;
+    return 0;
+}
+
+template <typename R>
+static int alloc_tables(ExoHandle* h, EnvArrays<R>& A) {
+    int tl = 0;
+    for (int l : h->motion_len) tl = l > tl ? l : tl;
+    A.table_len = tl;
+    const size_t st = h->stride;
+    if (int rc = dev_alloc(h, (void**)&A.tt, sizeof(R) * (size_t)tl * h->nax * st)) return rc;
+    if (int rc = dev_alloc(h, (void**)&A.sc_noise, sizeof(double) * (size_t)tl * st, false)) return rc;
+    if (int rc = dev_alloc(h, (void**)&A.sc_w1, sizeof(double) * (size_t)tl * st, false)) return rc;
+    if (int rc = dev_alloc(h, (void**)&A.sc_w2, sizeof(double) * (size_t)tl * st, false)) return rc;
+    if (int rc = dev_alloc(h, (void**)&A.sc_sign, sizeof(uint32_t) * 7 * EXO_SIGN_WORDS * st, false)) return rc;
+    return 0;
+}
+
+extern "C" int exo_set_env_types(ExoHandle* h, const uint8_t* seq, const int32_t* motion_id) {
+    if (!h || !seq || !motion_id) return fail(EXO_ERR_ARG, "exo_set_env_types: bad arguments");
+    if (!h->have_motions) return fail(EXO_ERR_STATE, "call exo_load_motions first");
+    if (h->have_types) return fail(EXO_ERR_STATE, "env types already set");
+    CK(cudaSetDevice(h->device));
+    std::vector<int> meta(h->stride, 0);
+    int nax = 4;
+    for (int e = 0; e < h->n; e++) {
+        int bits = 0;
+        for (int j = 0; j < 7; j++) {
+            if (seq[(size_t)e * 7 + j] > 1) return fail(EXO_ERR_ARG, "tremor_sequence entries must be 0 or 1 (env %d)", e);
+            bits |= (seq[(size_t)e * 7 + j] & 1) << j;
+        }
+        if (bits >> 4) nax = 7;
+        if (motion_id[e] < 0 || motion_id[e] >= h->n_motions) return fail(EXO_ERR_ARG, "env %d: motion id %d out of range", e, motion_id[e]);
+        meta[e] = bits | (motion_id[e] << 8);
+    }
+    h->nax = nax;
+    int* dmeta = h->cfg.precision == EXO_F32 ? h->Af.meta : h->Ad.meta;
+    CK(cudaMemcpy(dmeta, meta.data(), sizeof(int) * h->stride, cudaMemcpyHostToDevice));
+    int rc = h->cfg.precision == EXO_F32 ? alloc_tables(h, h->Af) : alloc_tables(h, h->Ad);
+    if (rc) return rc;
+    h->have_types = true;
+    return 0;
+}
+
+template <typename R>
+static StepConst<R> step_const(const ExoHandle* h) {
+    StepConst<R> K;
+    K.fmax_sh0 = (R)h->cfg.max_force_shoulder; K.fmax_el0 = (R)h->cfg.max_force_elbow;
+    K.L1 = (R)h->cfg.humerus_length; K.L2 = (R)h->cfg.forearm_length;
+    K.lag = h->cfg.link_state_lag; K.limits = h->cfg.joint_limits; K.auto_reset = h->cfg.auto_reset; K.metrics = h->cfg.metrics;
+    return K;
+}
+
+static ResetConst reset_const(const ExoHandle* h) {
+    ResetConst K;
+    K.amp_lo = h->cfg.tremor_amplitude_range[0]; K.amp_hi = h->cfg.tremor_amplitude_range[1];
+    K.f1_lo = h->cfg.first_harmonics_interval[0]; K.f1_hi = h->cfg.first_harmonics_interval[1];
+    K.f2_lo = h->cfg.second_harmonics_interval[0]; K.f2_hi = h->cfg.second_harmonics_interval[1];
+    K.shift_range = h->cfg.dr_actuator_end_pos_shift; K.act_range = h->cfg.dr_actuator_range; K.noise_frac = h->cfg.matrix_noise_fraction;
+    K.fmax_sh0 = h->cfg.max_force_shoulder; K.fmax_el0 = h->cfg.max_force_elbow;
+    K.dt = 1.0 / 40.0;                       // Exoskeleton_env.py:59
+    K.lag = h->cfg.link_state_lag;
+    return K;
+}
+
+template <typename R>
+static int reset_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const uint8_t* mask, float* obs, cudaStream_t s) {
+    const ResetConst K = reset_const(h);
+    const StepConst<R> SK = step_const<R>(h);
+    launch_reset<R>(A, C, K, SK, h->nax, mask, obs, s);
+    h->launches += 2;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+static int check_ready(ExoHandle* h, const char* who) {
+    if (!h) return fail(EXO_ERR_ARG, "%s: null handle", who);
+    if (!h->seeded) return fail(EXO_ERR_STATE, "%s: call exo_load_motions, exo_set_env_types and exo_seed first", who);
+    CK(cudaSetDevice(h->device));
+    return 0;
+}
+
+extern "C" int exo_seed(ExoHandle* h, const uint32_t* seeds, void* stream) {
+    if (!h || !seeds) return fail(EXO_ERR_ARG, "exo_seed: bad arguments");
+    if (!h->have_types) return fail(EXO_ERR_STATE, "call exo_load_motions and exo_set_env_types first");
+    CK(cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    CK(cudaMemcpyAsync(h->d_seeds, seeds, sizeof(uint32_t) * h->n, cudaMemcpyHostToDevice, s));
+    uint32_t* mt = h->cfg.precision == EXO_F32 ? h->Af.mt : h->Ad.mt;
+    launch_seed(mt, h->n, h->stride, h->d_seeds, h->cfg.reference_ctor ? 1 : 0, s);
+    h->launches += 1;
+    CK(cudaGetLastError());
+    h->seeded = true;
+    if (h->cfg.reference_ctor) {             // the constructor's own initialize_movement (Exoskeleton_env.py:172)
+        int rc = h->cfg.precision == EXO_F32 ? reset_t(h, h->Af, h->Cf, nullptr, nullptr, s) : reset_t(h, h->Ad, h->Cd, nullptr, nullptr, s);
+        if (rc) return rc;
+    }
+    CK(cudaStreamSynchronize(s));            // seeds is a host buffer the caller may free
+    return 0;
+}
+
+extern "C" int exo_reset(ExoHandle* h, const uint8_t* mask_dev, float* obs_dev, void* stream) {
+    if (int rc = check_ready(h, "exo_reset")) return rc;
+    if (!obs_dev) return fail(EXO_ERR_ARG, "exo_reset: obs_dev is null");
+    cudaStream_t s = (cudaStream_t)stream;
+    return h->cfg.precision == EXO_F32 ? reset_t(h, h->Af, h->Cf, mask_dev, obs_dev, s) : reset_t(h, h->Ad, h->Cd, mask_dev, obs_dev, s);
+}
+
+template <typename R>
+static int step_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const float* actions, float* obs, void* reward,
+                  uint8_t* done, const ExoInfo* info, cudaStream_t s) {
+    const StepConst<R> K = step_const<R>(h);
+    InfoPtrs<R> ip;
+    memset(&ip, 0, sizeof(ip));
+    const bool want_info = info != nullptr || h->cfg.metrics;
+    if (info) {
+        ip.actuator_torques = (R*)info->actuator_torques; ip.torque_val = (R*)info->torque_val; ip.ampl_val = (R*)info->ampl_val;
+        ip.tremor_torque_val = (R*)info->tremor_torque_val; ip.tremor_ampl_val = (R*)info->tremor_ampl_val;
+        ip.reward_parts = (R*)info->reward_parts; ip.amp_metric = (R*)info->amp_metric;
+    }
+    launch_step<R>(A, C, K, h->nax, want_info, actions, obs, (R*)reward, done, ip, s);
+    h->launches += 1;
+    CK(cudaGetLastError());
+    if (h->cfg.auto_reset) return reset_t(h, A, C, done, obs, s);
+    return 0;
+}
+
+extern "C" int exo_step(ExoHandle* h, const float* actions_dev, float* obs_dev, void* reward_dev, uint8_t* done_dev,
+                        const ExoInfo* info, void* stream) {
+    if (int rc = check_ready(h, "exo_step")) return rc;
+    if (!actions_dev || !obs_dev || !reward_dev || !done_dev) return fail(EXO_ERR_ARG, "exo_step: null buffer");
+    cudaStream_t s = (cudaStream_t)stream;
+    return h->cfg.precision == EXO_F32 ? step_t(h, h->Af, h->Cf, actions_dev, obs_dev, reward_dev, done_dev, info, s)
+                                       : step_t(h, h->Ad, h->Cd, actions_dev, obs_dev, reward_dev, done_dev, info, s);
+}
+
+extern "C" int exo_step_host(ExoHandle* h, const float* actions_host, float* obs_host, void* reward_host, uint8_t* done_host, void* stream) {
+    if (int rc = check_ready(h, "exo_step_host")) return rc;
+    if (!actions_host || !obs_host || !reward_host || !done_host) return fail(EXO_ERR_ARG, "exo_step_host: null buffer");
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t n = h->n, rsz = h->cfg.precision == EXO_F32 ? 4 : 8;
+    CK(cudaMemcpyAsync(h->d_act, actions_host, n * 7 * sizeof(float), cudaMemcpyHostToDevice, s));
+    if (int rc = exo_step(h, h->d_act, h->d_obs, h->d_rew, h->d_done, nullptr, stream)) return rc;
+    CK(cudaMemcpyAsync(obs_host, h->d_obs, n * 80 * sizeof(float), cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(reward_host, h->d_rew, n * rsz, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(done_host, h->d_done, n, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return 0;
+}
+
+extern "C" int exo_reset_host(ExoHandle* h, const uint8_t* mask_host, float* obs_host, void* stream) {
+    if (int rc = check_ready(h, "exo_reset_host")) return rc;
+    if (!obs_host) return fail(EXO_ERR_ARG, "exo_reset_host: null buffer");
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t n = h->n;
+    if (mask_host) CK(cudaMemcpyAsync(h->d_mask, mask_host, n, cudaMemcpyHostToDevice, s));
+    if (int rc = exo_reset(h, mask_host ? h->d_mask : nullptr, h->d_obs, stream)) return rc;
+    CK(cudaMemcpyAsync(obs_host, h->d_obs, n * 80 * sizeof(float), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return 0;
+}
+
+template <typename R>
+static void fill_view(const ExoHandle* h, const EnvArrays<R>& A, ExoStateView* v) {
+    v->n_envs = h->n; v->stride = h->stride; v->precision = h->cfg.precision; v->table_len = A.table_len; v->table_axes = h->nax;
+    v->q = A.q; v->q_lag = A.qlag; v->pos_vec = A.posvec; v->elbow_ref = A.elref; v->prev_action = A.fprev; v->prev_action2 = A.fprev2;
+    v->force_max = A.fmax; v->shift = A.shift; v->G = A.G; v->IDS = A.IDS; v->tremor_table = A.tt; v->tremor_mag = A.mag;
+    v->counts = A.counts; v->meta = A.meta; v->mt_state = A.mt; v->ep_return = A.ret;
+}
+
+extern "C" int exo_get_state(ExoHandle* h, ExoStateView* out) {
+    if (!h || !out) return fail(EXO_ERR_ARG, "exo_get_state: bad arguments");
+    if (!h->have_types) return fail(EXO_ERR_STATE, "exo_get_state: env types not set yet");
+    if (h->cfg.precision == EXO_F32) fill_view(h, h->Af, out); else fill_view(h, h->Ad, out);
+    return 0;
+}
+
+extern "C" int exo_stats(ExoHandle* h, double* out_dev, int32_t reset, void* stream) {
+    if (int rc = check_ready(h, "exo_stats")) return rc;
+    if (!out_dev) return fail(EXO_ERR_ARG, "exo_stats: null buffer");
+    cudaStream_t s = (cudaStream_t)stream;
+    double* st = h->cfg.precision == EXO_F32 ? h->Af.stats : h->Ad.stats;
+    CK(cudaMemcpyAsync(out_dev, st, sizeof(double) * EXO_N_STATS, cudaMemcpyDeviceToDevice, s));
+    if (reset) CK(cudaMemsetAsync(st, 0, sizeof(double) * EXO_N_STATS, s));
+    return 0;
+}
+
+extern "C" int64_t exo_launch_count(const ExoHandle* h) { return h ? h->launches : 0; }
+
+extern "C" int exo_forward_kinematics(ExoHandle* h, const void* theta_dev, void* p_dev, int32_t n, double L1, double L2, double L3, void* stream) {
+    if (!h || !theta_dev || !p_dev || n <= 0) return fail(EXO_ERR_ARG, "exo_forward_kinematics: bad arguments");
+    (void)L3;                                // unused by the reference too (a = 0 in every D-H row)
+    CK(cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    if (h->cfg.precision == EXO_F32) launch_fk<float>((const float*)theta_dev, (float*)p_dev, n, (float)L1, (float)L2, s);
+    else launch_fk<double>((const double*)theta_dev, (double*)p_dev, n, L1, L2, s);
+    h->launches += 1;
+    CK(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,354 @@
+"""Host-side mirror of the reference's environment interface, backed by libexo_env.so.
+
+  BatchedExoskeletonEnv   N environments resident on one B200: reset() / step(actions[N,7]) -> (obs, reward, done)
+  ExoskeletonEnv_train    single-env facade with the reference's constructor and return types
+                          (Environment/Exoskeleton_env.py:34-605), so Simulation/Exoskeleton_agent_train.py's loop,
+                          Agent.select_action and LAP.add consume it unchanged.
+
+PyTorch is used for device memory and streams only; all env arithmetic runs in the CUDA kernels.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _capi, motions as _motions, urdf as _urdf
+
+INFO_KEYS = ("actuator_torques", "torque_val", "ampl_val", "tremor_torque_val", "tremor_ampl_val")
+REWARD_KEYS = ("reward_unwanted", "reward_torque", "reward_axis", "reward_control", "reward_smoothness")
+STAT_NAMES = ("episodes", "return_sum", "length_sum", "env_steps", "limit_crossings", "steps_with_arm_reduction",
+              "amp_metric_neg_sum", "amp_metric_neg_count")
+
+_TYPESTR = {torch.float32: "<f4", torch.float64: "<f8", torch.int32: "<i4"}
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+class _DeviceArray(object):
+    """Carries a raw device address into torch through __cuda_array_interface__ (no copy, no ownership)."""
+
+    def __init__(self, ptr, shape, dtype):
+        self.__cuda_array_interface__ = dict(shape=tuple(shape), typestr=_TYPESTR[dtype], data=(int(ptr), False), version=2)
+
+
+class BatchedExoskeletonEnv(object):
+    """N independent ExoskeletonEnv_train instances stepped by one fused kernel launch.
+
+    motion_ids[i] / tremor_sequences[i] / seeds[i] are env i's `reference_motion_file_num`, `tremor_sequence`
+    and the argument of the `np.random.seed` call that precedes its construction in the reference
+    (Utilities/seed_setting_.py:9). Every env owns a private numpy-legacy MT19937 stream on the device, so env i
+    reproduces, draw for draw, a reference env built right after np.random.seed(seeds[i]).
+    """
+
+    def __init__(self, motion_ids, tremor_sequences, seeds=None, *, tremor_amplitude_range, first_harmonics_interval,
+                 second_harmonics_interval, max_force_shoulder, max_force_elbow, dr_actuator_end_pos_shift=0.02,
+                 dr_actuator_range=0.1, matrix_noise_fraction=0.1, device="cuda:0", precision="fp32", auto_reset=False,
+                 reference_ctor=True, link_state_lag=1, joint_limits="off", metrics=False, motions=None, urdf=None,
+                 humerus_length=0.4, forearm_length=0.4, hand_length=0.05):
+        self.lib = _capi.load()
+        if not torch.cuda.is_available():
+            raise _capi.ExoError("no CUDA device: the batched env runs on a B200 only (there is no CPU fallback)")
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise _capi.ExoError("device must be a CUDA device, got %s" % device)
+        motion_ids = np.ascontiguousarray(motion_ids, dtype=np.int32).reshape(-1)
+        self.n = int(motion_ids.size)
+        seqs = np.ascontiguousarray(tremor_sequences, dtype=np.uint8)
+        if seqs.ndim == 1:
+            seqs = np.broadcast_to(seqs, (self.n, 7)).copy()
+        if seqs.shape != (self.n, 7):
+            raise ValueError("tremor_sequences must be [N,7] or [7]")
+        if seeds is None:
+            seeds = np.arange(self.n, dtype=np.uint32)
+        seeds = np.ascontiguousarray(np.asarray(seeds, dtype=np.int64) & 0xFFFFFFFF, dtype=np.uint32).reshape(-1)
+        if seeds.size != self.n:
+            raise ValueError("seeds must have one entry per env")
+        self.motion_ids, self.tremor_sequences, self.seeds = motion_ids, seqs, seeds
+        self.precision = {"fp32": _capi.F32, "fp64": _capi.F64}[precision]
+        self.real = torch.float32 if self.precision == _capi.F32 else torch.float64
+        self.auto_reset = bool(auto_reset)
+
+        cfg = _capi.ExoConfig()
+        cfg.tremor_amplitude_range[:] = [float(x) for x in tremor_amplitude_range]
+        cfg.first_harmonics_interval[:] = [float(x) for x in first_harmonics_interval]
+        cfg.second_harmonics_interval[:] = [float(x) for x in second_harmonics_interval]
+        cfg.max_force_shoulder, cfg.max_force_elbow = float(max_force_shoulder), float(max_force_elbow)
+        cfg.dr_actuator_end_pos_shift = float(dr_actuator_end_pos_shift)
+        cfg.dr_actuator_range = float(dr_actuator_range)
+        cfg.matrix_noise_fraction = float(matrix_noise_fraction)
+        cfg.humerus_length, cfg.forearm_length, cfg.hand_length = float(humerus_length), float(forearm_length), float(hand_length)
+        cfg.link_state_lag = int(link_state_lag)
+        cfg.joint_limits = {"off": 0, "clamp": 1}[joint_limits]
+        cfg.precision = self.precision
+        cfg.ode = _capi.ODE_PROPAGATOR
+        cfg.auto_reset = int(self.auto_reset)
+        cfg.reference_ctor = int(bool(reference_ctor))
+        cfg.metrics = int(bool(metrics))
+        self.cfg = cfg
+        self.max_force_shoulder, self.max_force_elbow = float(max_force_shoulder), float(max_force_elbow)
+
+        self.geometry = _urdf.load_geometry(urdf)
+        geo = _urdf.to_struct(self.geometry)
+        self.motions = _motions.load_motions(motions)
+        tables, lengths = _motions.pack(self.motions)
+        self.motion_lengths = lengths
+        self.max_count = lengths[motion_ids]                            # per env (Exoskeleton_env.py:63)
+        self.max_reward = seqs.sum(1) * 0.5 + 0.9 + 0.05 + 0.05 + 0.5   # Exoskeleton_env.py:167-169
+
+        dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.device = torch.device("cuda", dev_index)
+        self.h = C.c_void_p()
+        with torch.cuda.device(dev_index):
+            _capi.check(self.lib.exo_create(C.byref(cfg), C.byref(geo), self.n, dev_index, C.byref(self.h)))
+            _capi.check(self.lib.exo_load_motions(self.h, tables.ctypes.data_as(C.POINTER(C.c_double)),
+                                                  lengths.ctypes.data_as(C.POINTER(C.c_int32)), len(self.motions),
+                                                  tables.shape[2]))
+            _capi.check(self.lib.exo_set_env_types(self.h, seqs.ctypes.data_as(C.POINTER(C.c_uint8)),
+                                                   motion_ids.ctypes.data_as(C.POINTER(C.c_int32))))
+            _capi.check(self.lib.exo_seed(self.h, seeds.ctypes.data_as(C.POINTER(C.c_uint32)), self._stream()))
+        dev = self.device
+        self._obs = [torch.zeros(self.n, 80, dtype=torch.float32, device=dev) for _ in range(2)]
+        self._flip = 0
+        self._reward = torch.zeros(self.n, dtype=self.real, device=dev)
+        self._done = torch.zeros(self.n, dtype=torch.uint8, device=dev)
+        self._info = None
+        self._stats = torch.zeros(_capi.N_STATS, dtype=torch.float64, device=dev)
+        self._host = None
+
+    # ------------------------------------------------------------------ plumbing
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h:
+            self.lib.exo_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launch_count(self):
+        return int(self.lib.exo_launch_count(self.h))
+
+    # ------------------------------------------------------------------ reference-shaped API, vectorised
+    def reset(self, mask=None):
+        """env.reset() for all envs (mask=None) or those with mask[i] != 0. Returns obs[N,80] (float32, device)."""
+        obs = self._obs[self._flip]
+        m = None
+        if mask is not None:
+            m = torch.as_tensor(mask, device=self.device).to(torch.uint8).contiguous()
+        _capi.check(self.lib.exo_reset(self.h, _ptr(m), _ptr(obs), self._stream()))
+        return obs
+
+    def step(self, actions, with_info=False):
+        """env.step for every env. actions: float32 [N,7] on the device. Returns (obs, reward, done) and, with
+        with_info, the reference's info dict as [N,7] / [N] tensors. The obs tensor returned by the previous call
+        stays valid (double buffered) so a replay buffer can store (obs, action, next_obs)."""
+        a = torch.as_tensor(actions, device=self.device, dtype=torch.float32).contiguous()
+        if a.shape != (self.n, 7):
+            raise ValueError("actions must be [N,7]")
+        self._flip ^= 1
+        obs = self._obs[self._flip]
+        if not self.auto_reset:
+            obs.copy_(self._obs[self._flip ^ 1])     # idle (finished) envs keep their last observation
+        info_struct = None
+        if with_info:
+            if self._info is None:
+                self._info = {k: torch.zeros(self.n, 7, dtype=self.real, device=self.device) for k in INFO_KEYS}
+                self._info["reward_parts"] = torch.zeros(self.n, 5, dtype=self.real, device=self.device)
+                self._info["amp_metric"] = torch.zeros(self.n, dtype=self.real, device=self.device)
+            s = _capi.ExoInfo()
+            for k in INFO_KEYS + ("reward_parts", "amp_metric"):
+                setattr(s, k, self._info[k].data_ptr())
+            info_struct = C.byref(s)
+        _capi.check(self.lib.exo_step(self.h, _ptr(a), _ptr(obs), _ptr(self._reward), _ptr(self._done), info_struct,
+                                      self._stream()))
+        if with_info:
+            return obs, self._reward, self._done.bool(), self._info
+        return obs, self._reward, self._done.bool()
+
+    def _host_buffers(self):
+        if self._host is None:
+            self._host = dict(obs=torch.zeros(self.n, 80, dtype=torch.float32).pin_memory(),
+                              reward=torch.zeros(self.n, dtype=self.real).pin_memory(),
+                              done=torch.zeros(self.n, dtype=torch.uint8).pin_memory())
+        return self._host
+
+    def step_host(self, actions_host):
+        """The same step through HOST buffers (exo_step_host): H2D actions, kernels, D2H obs/reward/done, sync.
+        actions_host: contiguous float32 CPU tensor [N,7] (pinned for full speed). Returns pinned CPU tensors
+        (reused between calls)."""
+        o = self._host_buffers()
+        if actions_host.dtype != torch.float32 or actions_host.device.type != "cpu" or not actions_host.is_contiguous():
+            raise ValueError("actions_host must be a contiguous float32 CPU tensor")
+        _capi.check(self.lib.exo_step_host(self.h, _ptr(actions_host), _ptr(o["obs"]), _ptr(o["reward"]), _ptr(o["done"]),
+                                           self._stream()))
+        return o["obs"], o["reward"], o["done"]
+
+    def reset_host(self, mask_host=None):
+        o = self._host_buffers()
+        m = None
+        if mask_host is not None:
+            m = torch.as_tensor(mask_host).to(torch.uint8).contiguous()
+        _capi.check(self.lib.exo_reset_host(self.h, _ptr(m), _ptr(o["obs"]), self._stream()))
+        return o["obs"]
+
+    def stats(self, reset=False):
+        """Device-side episode statistics, float64 [16] (see STAT_NAMES); the vector ranks all-reduce over NCCL."""
+        _capi.check(self.lib.exo_stats(self.h, _ptr(self._stats), int(reset), self._stream()))
+        return self._stats
+
+    def forward_kinematics(self, theta, L1=0.4, L2=0.4, L3=0.05):
+        th = torch.as_tensor(theta, device=self.device, dtype=self.real).contiguous().reshape(-1, 7)
+        p = torch.empty(th.shape[0], 3, dtype=self.real, device=self.device)
+        _capi.check(self.lib.exo_forward_kinematics(self.h, _ptr(th), _ptr(p), th.shape[0], L1, L2, L3, self._stream()))
+        return p
+
+    # ------------------------------------------------------------------ state views (tests, checkpoints)
+    _FIELDS = dict(q=5, q_lag=5, pos_vec=21, elbow_ref=3, prev_action=7, prev_action2=7, force_max=2, shift=42, G=49,
+                   ep_return=1)
+
+    def _view(self):
+        v = _capi.ExoStateView()
+        _capi.check(self.lib.exo_get_state(self.h, C.byref(v)))
+        return v
+
+    def _wrap(self, ptr, rows, dtype):
+        """torch view (no copy) of a field-major [rows, stride] device array owned by the handle."""
+        v = self._view()
+        return torch.as_tensor(_DeviceArray(ptr, (rows, v.stride), dtype), device=self.device)
+
+    def _raw(self, name):
+        v = self._view()
+        if name in self._FIELDS:
+            return self._wrap(getattr(v, name), self._FIELDS[name], self.real)
+        if name == "IDS":
+            return self._wrap(v.IDS, 147, torch.float64)
+        if name == "tremor_mag":
+            return self._wrap(v.tremor_mag, 1, torch.float64)
+        if name in ("counts", "meta"):
+            return self._wrap(getattr(v, name), 1, torch.int32)
+        if name == "mt_state":
+            return self._wrap(v.mt_state, 625, torch.int32)
+        if name == "tremor_table":
+            return self._wrap(v.tremor_table, v.table_len * v.table_axes, self.real)
+        raise KeyError(name)
+
+    def get_field(self, name):
+        """Copy of one state field as an env-major tensor [N, k] (tremor_table: [N, table_len, axes])."""
+        t = self._raw(name)[:, :self.n].t().contiguous()
+        if name == "tremor_table":
+            v = self._view()
+            return t.reshape(self.n, v.table_len, v.table_axes)
+        return t
+
+    def set_field(self, name, value):
+        t = self._raw(name)
+        val = torch.as_tensor(value, device=self.device, dtype=t.dtype).reshape(self.n, -1)
+        t[:, :self.n] = val.t()
+
+    CHECKPOINT_FIELDS = ("q", "q_lag", "pos_vec", "elbow_ref", "prev_action", "prev_action2", "force_max", "shift", "G",
+                         "ep_return", "IDS", "tremor_mag", "counts", "tremor_table", "mt_state")
+
+    def state_dict(self):
+        """Everything needed to resume: a handful of SoA tensors."""
+        return {k: self.get_field(k) for k in self.CHECKPOINT_FIELDS}
+
+    def load_state_dict(self, sd):
+        for k in self.CHECKPOINT_FIELDS:
+            self.set_field(k, sd[k])
+
+
+class _Box(object):
+    """Stand-in for gym.spaces.Box (gym is optional): shape/low/high/dtype, which is all callers read
+    (Exoskeleton_agent_train.py:80)."""
+
+    def __init__(self, low, high, dtype=np.float32):
+        self.low = np.asarray(low, dtype=dtype)
+        self.high = np.asarray(high, dtype=dtype)
+        self.shape = self.low.shape
+        self.dtype = np.dtype(dtype)
+
+    def sample(self):
+        return np.random.uniform(self.low, self.high).astype(self.dtype)
+
+
+class ExoskeletonEnv_train(object):
+    """Drop-in for Environment.Exoskeleton_env.ExoskeletonEnv_train: same constructor arguments
+    (Exoskeleton_env.py:38-48), reset() -> (obs[80] float32, 2) (:473-478), step(a[7]) -> (obs, reward: float,
+    done: bool, False, info) (:368-471) with the same info keys, and the helper methods callers use.
+
+    Difference that cannot be hidden: the reference draws episode parameters from numpy's *global* stream, shared
+    with every other env and with the warm-up policy; here each env owns a private MT19937 stream on the device,
+    seeded with `seed` (default: one draw from numpy's global stream, so seeding numpy upstream stays reproducible).
+    """
+    metadata = {"render.modes": ["human"]}
+
+    def __init__(self, reference_motion_file_num, tremor_sequence, tremor_amplitude_range, first_harmonics_interval,
+                 second_harmonics_interval, max_force_shoulder, max_force_elbow, dr_actuator_end_pos_shift=0.02,
+                 dr_actuator_range=0.1, matrix_noise_fraction=0.1, *, seed=None, device="cuda:0", precision="fp64", **kw):
+        if seed is None:
+            seed = int(np.random.randint(0, 2 ** 31 - 1))
+        self.file_num = str(reference_motion_file_num)
+        self.tremor_input_sequence = np.asarray(tremor_sequence)
+        self.batch = BatchedExoskeletonEnv([int(self.file_num)], [self.tremor_input_sequence.astype(np.uint8)], [seed],
+                                           tremor_amplitude_range=tremor_amplitude_range,
+                                           first_harmonics_interval=first_harmonics_interval,
+                                           second_harmonics_interval=second_harmonics_interval,
+                                           max_force_shoulder=max_force_shoulder, max_force_elbow=max_force_elbow,
+                                           dr_actuator_end_pos_shift=dr_actuator_end_pos_shift,
+                                           dr_actuator_range=dr_actuator_range, matrix_noise_fraction=matrix_noise_fraction,
+                                           device=device, precision=precision, auto_reset=False, **kw)
+        self.max_count = int(self.batch.max_count[0])
+        self.max_reward = float(self.batch.max_reward[0])
+        self.dt = 1 / 40
+        self.counts = 2
+        self.action_space = _Box(-np.ones(7), np.ones(7))
+        low = np.concatenate([np.repeat(0.0, 14), np.repeat(-15.0, 12), np.repeat(-2.0, 54)])
+        high = np.concatenate([np.repeat(1.5, 14), np.repeat(15.0, 12), np.repeat(2.0, 54)])
+        self.observation_space = _Box(low, high)
+        self.state = None
+
+    def reset(self):
+        obs = self.batch.reset()
+        self.counts = 2
+        self.state = obs[0].cpu().numpy()
+        return self.state, self.counts
+
+    def step(self, action):
+        a = torch.as_tensor(np.asarray(action, dtype=np.float32).reshape(1, 7))
+        obs, reward, done, info = self.batch.step(a.to(self.batch.device), with_info=True)
+        self.counts += 1
+        host = {k: info[k][0].cpu().numpy().astype(np.float64) for k in INFO_KEYS}
+        parts = info["reward_parts"][0].cpu().numpy().astype(np.float64)
+        for k, v in zip(REWARD_KEYS, parts):
+            host[k] = float(v)
+        host["amp_metric"] = float(info["amp_metric"][0].item())
+        self.state = obs[0].cpu().numpy()
+        return self.state, float(reward[0].item()), bool(done[0].item()), False, host
+
+    def return_generated_tremor_data(self):
+        tt = self.batch.get_field("tremor_table")[0]          # [L, axes]
+        mx = np.zeros(7)
+        mx[:tt.shape[1]] = tt[:self.max_count].max(0).values.cpu().numpy()
+        return self.tremor_input_sequence, mx
+
+    def return_max_length(self):
+        return self.max_count
+
+    def return_original_joint_angles(self):
+        m = self.batch.motions[int(self.file_num)]
+        c = self.counts
+        return [m[2, c], m[3, c], m[4, c], m[0, c], m[1, c], 0, 0]
+
+    def render(self, mode="human"):
+        raise NotImplementedError("p.GUI needs a graphics stack: unavailable on this box")
+
+    def close(self):
+        self.batch.close()

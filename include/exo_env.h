@@ -1,0 +1,156 @@
+/* exo_env.h — C-ABI of libexo_env.so: the batched, B200-resident replacement of the reference's
+ * `ExoskeletonEnv_train` reset()/step() hot path (Environment/Exoskeleton_env.py:34-605 and everything it
+ * calls in Environment/Exoskeleton_sim_pybullet.py and Utilities/*.py; map in DESIGN.md).
+ *
+ * Conventions
+ *  - plain C types only; one handle per GPU; a handle is not thread-safe.
+ *  - every function returns 0 on success or a negative ExoStatus; exo_last_error() gives the text
+ *    (thread-local). Nothing falls back to the CPU: without a usable sm_100 device exo_create fails.
+ *  - "dev" pointers are device pointers owned by the caller (e.g. torch tensors); "host" pointers are
+ *    host memory. Kernels are launched on the caller-supplied cudaStream_t (passed as void*); device
+ *    entry points never synchronise, host-buffer entry points synchronise that stream before returning.
+ *  - `real` below is float when ExoConfig.precision == EXO_F32 and double when EXO_F64.
+ *  - env arrays are row-major [n_envs, k] at this boundary; inside the handle state is structure-of-arrays.
+ */
+#ifndef EXO_ENV_H
+#define EXO_ENV_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EXO_OBS_DIM 80      /* Exoskeleton_env.py:99-111,487-570 */
+#define EXO_ACT_DIM 7       /* Exoskeleton_env.py:74 */
+#define EXO_NLINKS 19       /* Simulation/exo_v3.urdf: 5 revolute + 14 prismatic joints */
+#define EXO_N_STATS 16
+
+typedef enum {
+    EXO_OK = 0, EXO_ERR_ARG = -1, EXO_ERR_CUDA = -2, EXO_ERR_STATE = -3, EXO_ERR_TOPOLOGY = -4, EXO_ERR_NOMEM = -5
+} ExoStatus;
+
+enum { EXO_F32 = 0, EXO_F64 = 1 };
+enum { EXO_ODE_PROPAGATOR = 0, EXO_ODE_RK45 = 1 };
+
+/* Constructor arguments of ExoskeletonEnv_train (Exoskeleton_env.py:38-48), shared by all envs of a handle,
+ * plus the knobs of the restated pybullet boundary (oracle/minibullet.py) and kernel options. */
+typedef struct {
+    double tremor_amplitude_range[2];
+    double first_harmonics_interval[2];
+    double second_harmonics_interval[2];
+    double max_force_shoulder, max_force_elbow;
+    double dr_actuator_end_pos_shift, dr_actuator_range, matrix_noise_fraction;
+    double humerus_length, forearm_length, hand_length;   /* Exoskeleton_agent_train.py:37-41, amplitude metric */
+    int32_t link_state_lag;   /* 1: getLinkState lags the joint state by one stepSimulation (default), 0: no lag */
+    int32_t joint_limits;     /* 0: motor row wins (default), 1: clamp to the URDF limits */
+    int32_t precision;        /* EXO_F32 | EXO_F64 */
+    int32_t ode;              /* EXO_ODE_PROPAGATOR (exact solution, default) | EXO_ODE_RK45 (scipy RK45 restated, fp64) */
+    int32_t auto_reset;       /* 1: exo_step re-initialises finished envs in the same call (obs = first obs of next episode) */
+    int32_t reference_ctor;   /* 1: exo_seed also performs the constructor's draws: one rand() (Exoskeleton_env.py:70)
+                                 and one initialize_movement (:172), so streams line up with the reference */
+    int32_t metrics;          /* 1: accumulate the training script's per-step suppression metrics on device */
+    int32_t reserved;
+} ExoConfig;
+
+/* Kinematic tree of the URDF in Bullet numbering (pre-order DFS over child joints in file order, base = -1). */
+typedef struct {
+    int32_t parent[EXO_NLINKS];
+    int32_t joint_type[EXO_NLINKS];       /* 0 revolute, 1 prismatic */
+    double  origin_xyz[EXO_NLINKS][3];
+    double  origin_R[EXO_NLINKS][9];      /* row-major rotation of the joint origin rpy (Rz*Ry*Rx) */
+    double  axis[EXO_NLINKS][3];
+    double  com_xyz[EXO_NLINKS][3];       /* inertial origin: getLinkState(...)[0] is the COM */
+    double  lower[EXO_NLINKS], upper[EXO_NLINKS];
+    double  base_pos[3];                  /* world position of the base link frame (loadURDF basePosition) */
+    int32_t act_link[14];                 /* link handles act11,act12,act21,...,act72 (Exoskeleton_sim_pybullet.py:48-61) */
+    int32_t shoulder_link, elbow_link;    /* Exoskeleton_sim_pybullet.py:62-63 */
+} ExoGeometry;
+
+/* Optional per-step outputs = the reference's `info` dict (Exoskeleton_env.py:464-469). Any pointer may be NULL. */
+typedef struct {
+    void* actuator_torques;   /* real [n,7] */
+    void* torque_val;         /* real [n,7] */
+    void* ampl_val;           /* real [n,7] degrees */
+    void* tremor_torque_val;  /* real [n,7] */
+    void* tremor_ampl_val;    /* real [n,7] degrees */
+    void* reward_parts;       /* real [n,5]: unwanted, torque, axis, control, smoothness (Exoskeleton_env.py:358-364) */
+    void* amp_metric;         /* real [n]: end-effector amplitude change % (Exoskeleton_agent_train.py:158-170) */
+} ExoInfo;
+
+/* Read/write views of the resident state (device pointers, field-major [k][n_envs] with `stride` elements
+ * between fields). For parity tests and checkpoint/restore. */
+typedef struct {
+    int32_t n_envs, stride, precision, table_len, table_axes;
+    void* q;            /* real [5]  Bullet joint positions: shoulder z,y,x, elbow y,z (rad) */
+    void* q_lag;        /* real [5]  joint positions the link-state cache was computed from */
+    void* pos_vec;      /* real [21] position_vectors (Exoskeleton_env.py:386) */
+    void* elbow_ref;    /* real [3]  act_elbow_reference_positions as last read */
+    void* prev_action;  /* real [7]  Newtons (Exoskeleton_env.py:455) */
+    void* prev_action2; /* real [7]  (Exoskeleton_env.py:454) */
+    void* force_max;    /* real [2]  domain-randomised max_output_shoulder, max_output_elbow (:216-217) */
+    void* shift;        /* real [42] dummy_shift_coordinates (Exoskeleton_sim_pybullet.py:103-107) */
+    void* G;            /* real [49] propagator of I q'' + D q' + S q = T over one dt from rest: q(dt) = G T (rad/Nm) */
+    void* IDS;          /* double [147] I_current, D_current, S_current (Exoskeleton_env.py:208-210) */
+    void* tremor_table; /* real [table_len][table_axes] tremor_torque_values, time-major */
+    void* tremor_mag;   /* double [1] tremor_magnitude (:199) */
+    int32_t* counts;    /* [1] self.counts */
+    int32_t* meta;      /* [1] bits 0-6 tremor_sequence, bits 8-15 motion id */
+    uint32_t* mt_state; /* [625] numpy legacy MT19937 key + position */
+    void* ep_return;    /* real [1] running episode return */
+} ExoStateView;
+
+typedef struct ExoHandle ExoHandle;
+
+const char* exo_last_error(void);
+int exo_abi_version(void);
+
+/* ExoskeletonEnv_train.__init__ for n_envs environments at once (Exoskeleton_env.py:38-175, URDF load
+ * Exoskeleton_sim_pybullet.py:14-18). Fails unless `device` is an sm_100 GPU. */
+int exo_create(const ExoConfig* cfg, const ExoGeometry* geo, int32_t n_envs, int32_t device, ExoHandle** out);
+int exo_destroy(ExoHandle* h);
+
+/* read_env_texts result (Utilities/read_txt_env.py:73-170), columns 0-4 only:
+ * tables[m][r][k], r = elbow_y, elbow_z, shoulder_x, shoulder_y, shoulder_z in degrees, padded to max_len. Host pointers. */
+int exo_load_motions(ExoHandle* h, const double* tables, const int32_t* lengths, int32_t n_motions, int32_t max_len);
+
+/* Per-env constructor arguments: tremor_sequence[7] (0/1) and reference_motion_file_num. Host pointers. */
+int exo_set_env_types(ExoHandle* h, const uint8_t* tremor_sequence /*[n,7]*/, const int32_t* motion_id /*[n]*/);
+
+/* np.random.seed(seeds[i]) for env i's private legacy-MT19937 stream (Utilities/seed_setting_.py:9), then,
+ * if cfg.reference_ctor, the constructor's draws. Host pointer. Must follow exo_load_motions + exo_set_env_types. */
+int exo_seed(ExoHandle* h, const uint32_t* seeds /*[n]*/, void* stream);
+
+/* env.reset() (Exoskeleton_env.py:473-478 -> initialize_movement :193-254) for the envs whose mask byte is
+ * non-zero (mask_dev == NULL: all). Writes obs rows of those envs only. */
+int exo_reset(ExoHandle* h, const uint8_t* mask_dev, float* obs_dev /*[n,80]*/, void* stream);
+
+/* env.step(action) (Exoskeleton_env.py:368-471) for every env. reward_dev is real [n]. */
+int exo_step(ExoHandle* h, const float* actions_dev /*[n,7]*/, float* obs_dev /*[n,80]*/, void* reward_dev,
+             uint8_t* done_dev /*[n]*/, const ExoInfo* info /*NULL: off*/, void* stream);
+
+/* Same step with HOST buffers (pinned for full speed): H2D of actions, step, D2H of obs/reward/done, stream sync.
+ * This is the call the single-env facade and the end-to-end benchmark use. */
+int exo_step_host(ExoHandle* h, const float* actions_host, float* obs_host, void* reward_host, uint8_t* done_host,
+                  void* stream);
+int exo_reset_host(ExoHandle* h, const uint8_t* mask_host, float* obs_host, void* stream);
+
+int exo_get_state(ExoHandle* h, ExoStateView* out);
+
+/* Episode statistics accumulated on device since the last call with reset != 0:
+ * out_dev[0..EXO_N_STATS) doubles: 0 episodes, 1 sum return, 2 sum length, 3 env-steps, 4 joint-limit crossings,
+ * 5 steps with |torque|<|tremor| on >=1 of the 4 arm axes, 6 sum amplitude metric over steps where it is < 0,
+ * 7 count of those steps, 8.. reserved. This vector is what ranks all-reduce over NCCL. */
+int exo_stats(ExoHandle* h, double* out_dev, int32_t reset, void* stream);
+
+/* Number of kernels this handle has launched so far (for bench.py's gpu_launches). */
+int64_t exo_launch_count(const ExoHandle* h);
+
+/* Standalone batched forward_kinematics (Utilities/calculate_arm_end_effector_points.py:18-50):
+ * theta_dev real [n,7] rad -> p_dev real [n,3]. */
+int exo_forward_kinematics(ExoHandle* h, const void* theta_dev, void* p_dev, int32_t n, double L1, double L2, double L3,
+                           void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
