@@ -58,6 +58,7 @@ SIGNATURES = {
     "exo_reset_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "exo_get_state": (C.c_int, [C.c_void_p, C.POINTER(ExoStateView)]),
     "exo_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
+    "exo_set_auto_reset": (C.c_int, [C.c_void_p, C.c_int32]),
     "exo_launch_count": (C.c_int64, [C.c_void_p]),
     "exo_forward_kinematics": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_void_p]),
 }

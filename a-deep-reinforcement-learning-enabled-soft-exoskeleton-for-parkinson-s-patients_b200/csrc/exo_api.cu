@@ -381,6 +381,12 @@ extern "C" int exo_stats(ExoHandle* h, double* out_dev, int32_t reset, void* str
     return 0;
 }
 
+extern "C" int exo_set_auto_reset(ExoHandle* h, int32_t on) {
+    if (!h) return fail(EXO_ERR_ARG, "exo_set_auto_reset: null handle");
+    h->cfg.auto_reset = on ? 1 : 0;
+    return 0;
+}
+
 extern "C" int64_t exo_launch_count(const ExoHandle* h) { return h ? h->launches : 0; }
 
 extern "C" int exo_forward_kinematics(ExoHandle* h, const void* theta_dev, void* p_dev, int32_t n, double L1, double L2, double L3, void* stream) {

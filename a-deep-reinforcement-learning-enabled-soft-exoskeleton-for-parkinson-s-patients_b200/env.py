@@ -132,6 +132,10 @@ class BatchedExoskeletonEnv(object):
         except Exception:
             pass
 
+    def set_auto_reset(self, on):
+        _capi.check(self.lib.exo_set_auto_reset(self.h, int(bool(on))))
+        self.auto_reset = bool(on)
+
     @property
     def launch_count(self):
         return int(self.lib.exo_launch_count(self.h))
@@ -146,16 +150,17 @@ class BatchedExoskeletonEnv(object):
         _capi.check(self.lib.exo_reset(self.h, _ptr(m), _ptr(obs), self._stream()))
         return obs
 
-    def step(self, actions, with_info=False):
+    def step(self, actions, with_info=False, keep_idle_obs=True):
         """env.step for every env. actions: float32 [N,7] on the device. Returns (obs, reward, done) and, with
         with_info, the reference's info dict as [N,7] / [N] tensors. The obs tensor returned by the previous call
-        stays valid (double buffered) so a replay buffer can store (obs, action, next_obs)."""
+        stays valid (double buffered) so a replay buffer can store (obs, action, next_obs). Without auto_reset,
+        envs that already reported done idle; keep_idle_obs carries their last observation into the new buffer."""
         a = torch.as_tensor(actions, device=self.device, dtype=torch.float32).contiguous()
         if a.shape != (self.n, 7):
             raise ValueError("actions must be [N,7]")
         self._flip ^= 1
         obs = self._obs[self._flip]
-        if not self.auto_reset:
+        if keep_idle_obs and not self.auto_reset:
             obs.copy_(self._obs[self._flip ^ 1])     # idle (finished) envs keep their last observation
         info_struct = None
         if with_info:

@@ -1,0 +1,290 @@
+#!/usr/bin/env python
+"""bench.py — batched env-steps/s of the Exoskeleton env hot path on N B200s (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--envs-per-gpu E] [--impl reference]
+
+A "step" is one env.step() of every resident environment (one control period dt = 1/40 s each).
+Workload (config.workload): BASELINE config 3 per GPU — 65 536 envs/GPU, training domain randomisation
+(Exoskeleton_agent_train.py:30-35,43-44), the 8 bundled reference motions in contiguous blocks, the 15 tremor
+types round-robin, auto-reset on, U(-1,1)^7 actions generated on the device before timing. Envs shard over
+ranks with no data-path collective (weak scaling); NCCL only all-reduces the episode-statistics vector.
+
+Timing: every step sits between its own pair of CUDA events on the launching stream; between steps a 512 MiB
+buffer is overwritten to flush the 126 MB L2 (the per-step working set of 65 536 envs would otherwise stay L2
+resident). The timed region is bracketed by barrier + synchronize; the reported time is the max over ranks of the
+summed per-step device times.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+TYPES15 = [[(m >> 3) & 1, (m >> 2) & 1, (m >> 1) & 1, m & 1, 0, 0, 0] for m in range(1, 16)]
+TRAIN = dict(tremor_amplitude_range=[0.1, 1.0], first_harmonics_interval=[4.0, 6.0], second_harmonics_interval=[8.0, 10.0],
+             max_force_shoulder=40.0, max_force_elbow=20.0, dr_actuator_end_pos_shift=0.02, dr_actuator_range=0.03,
+             matrix_noise_fraction=0.1)
+METRIC = "batched env-steps/sec"
+UNIT = "env-steps/s"
+# Compulsory HBM traffic of one env-step of exo_step_kernel<float,false,4> (DESIGN.md "Algorithmic bytes"):
+# reads 520 B + writes 525 B.
+ALGO_BYTES_PER_ENV_STEP = 1045
+
+
+def population(n_per_gpu, rank, world):
+    """This rank's shard of the cfg-3/4 population (exo_b200.sharding.benchmark_population)."""
+    from exo_b200 import sharding
+    return sharding.benchmark_population(n_per_gpu * world, rank, world)
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks/throttle reasons sampled while the timed region runs (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            parts = [p.strip() for p in r.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nme, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baseline(sample_envs, steps, threads=0, seed0=0):
+    """The oracle port (oracle/exo_oracle.c, fp64, scipy-RK45-faithful = the reference's arithmetic) on host threads.
+    Returns (env_steps_per_s, threads_used, seconds)."""
+    sys.path.insert(0, os.path.join(REPO, "oracle"))
+    import oracle as O
+    motion, seqs, seeds = population(sample_envs, 0, 1)
+    batch = O.OracleBatch(motion, seqs, seeds + seed0, ode_mode=0, **TRAIN)
+    batch.reset()
+    rs = np.random.RandomState(1)
+    acts = rs.uniform(-1, 1, (4, sample_envs, 7))
+    nthreads = O.lib().orc_max_threads() if threads <= 0 else threads
+    batch.step(acts[0], auto_reset=True, threads=nthreads)
+    t0 = time.perf_counter()
+    for t in range(steps):
+        batch.step(acts[t % 4], auto_reset=True, threads=nthreads)
+    dt = time.perf_counter() - t0
+    return sample_envs * steps / dt, nthreads, dt
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU algorithm (oracle port; the Python reference cannot travel to the GPU box
+    and needs pybullet) on all host threads, rank 0 only."""
+    if rank != 0:
+        return
+    sample = args.ref_sample
+    # warm-up
+    cpu_baseline(sample, max(1, min(args.warmup, 20)))
+    t0 = time.perf_counter()
+    v, cores, secs = cpu_baseline(sample, args.steps)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "cfg3 population, bounded sample of %d envs per step on host threads" % sample,
+                       "envs_per_step": sample},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": "%d envs x %d steps, oracle/exo_oracle.c (fp64, RK45 as scipy), %d pthreads" % (sample, args.steps, cores)},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=1000)
+    ap.add_argument("--warmup", type=int, default=100)
+    ap.add_argument("--envs-per-gpu", type=int, default=65536)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "fp64"])
+    ap.add_argument("--e2e-steps", type=int, default=30)
+    ap.add_argument("--kernel-steps", type=int, default=100)
+    ap.add_argument("--cpu-sample", type=int, default=4096, help="envs in the bounded CPU-baseline sample")
+    ap.add_argument("--cpu-steps", type=int, default=2000)
+    ap.add_argument("--ref-sample", type=int, default=4096)
+    ap.add_argument("--no-flush", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    import exo_b200
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    n = args.envs_per_gpu
+    motion, seqs, seeds = population(n, rank, world)
+    env = exo_b200.BatchedExoskeletonEnv(motion, seqs, seeds, device=dev, precision=args.precision, auto_reset=True, **TRAIN)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(1234 + rank)
+    n_act = 8
+    actions = torch.rand(n_act, n, 7, device=dev, generator=gen) * 2 - 1
+    flush = None if args.no_flush else torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    stats_sum = torch.zeros(16, dtype=torch.float64, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    env.reset()
+    for t in range(args.warmup):
+        env.step(actions[t % n_act])
+    env.stats(reset=True)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev0 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ev1 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    launches0 = env.launch_count
+    wall0 = time.perf_counter()
+    for t in range(args.steps):
+        if flush is not None:
+            flush.zero_()
+        ev0[t].record()
+        env.step(actions[t % n_act])
+        if world > 1 and (t + 1) % 344 == 0:          # episode statistics: the only collective (cfg 4)
+            stats_sum += exo_b200.sharding.reduce_stats(env.stats(reset=True).clone())
+        ev1[t].record()
+    barrier()
+    wall = time.perf_counter() - wall0
+    launches = env.launch_count - launches0
+    per_step = np.array([a.elapsed_time(b) for a, b in zip(ev0, ev1)])
+    total_ms = torch.tensor([per_step.sum()], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    total_ms = float(total_ms.item())
+    stats_sum += exo_b200.sharding.reduce_stats(env.stats(reset=True).clone())
+    value = world * n * args.steps / (total_ms * 1e-3)
+
+    # ---- dominant kernel alone (exo_step_kernel): auto-reset off, all envs live, flush between launches
+    env.set_auto_reset(False)
+    env.reset()
+    ksteps = min(args.kernel_steps, 200)
+    for t in range(3):
+        env.step(actions[t % n_act], keep_idle_obs=False)
+    k0 = [torch.cuda.Event(enable_timing=True) for _ in range(ksteps)]
+    k1 = [torch.cuda.Event(enable_timing=True) for _ in range(ksteps)]
+    torch.cuda.synchronize(dev)
+    for t in range(ksteps):
+        if flush is not None:
+            flush.zero_()
+        k0[t].record()
+        env.step(actions[t % n_act], keep_idle_obs=False)
+        k1[t].record()
+    torch.cuda.synchronize(dev)
+    kms = float(np.mean([a.elapsed_time(b) for a, b in zip(k0, k1)]))
+    clocks = sampler.stop()
+
+    # ---- end to end through the host-buffer C-ABI call (exo_step_host): pinned H2D + kernels + D2H + sync per step
+    env.set_auto_reset(True)
+    env.reset()
+    host_actions = [(torch.rand(n, 7) * 2 - 1).pin_memory() for _ in range(4)]
+    for t in range(3):
+        env.step_host(host_actions[t % 4])
+    e0 = [torch.cuda.Event(enable_timing=True) for _ in range(args.e2e_steps)]
+    e1 = [torch.cuda.Event(enable_timing=True) for _ in range(args.e2e_steps)]
+    barrier()
+    for t in range(args.e2e_steps):
+        if flush is not None:
+            flush.zero_()
+        e0[t].record()
+        env.step_host(host_actions[t % 4])
+        e1[t].record()
+    barrier()
+    e2e_ms = torch.tensor([sum(a.elapsed_time(b) for a, b in zip(e0, e1))], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    e2e_value = world * n * args.e2e_steps / (float(e2e_ms.item()) * 1e-3)
+    rbytes = 4 if args.precision == "fp32" else 8
+
+    if rank == 0:
+        peaks = {}
+        try:
+            with open(os.path.join(REPO, "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        achieved = ALGO_BYTES_PER_ENV_STEP * n / (kms * 1e-3) / 1e9
+        cpu_v, cpu_cores, cpu_secs = cpu_baseline(args.cpu_sample, args.cpu_steps)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if args.precision == "fp32" else "f64", "data": "synthetic",
+            "config": {"workload": "BASELINE cfg3 per GPU: %d envs/GPU, training DR (0.02/0.03/0.1), 8 reference motions x 15 tremor "
+                                   "types, auto-reset, U(-1,1)^7 device actions" % n,
+                       "envs_per_gpu": n, "total_envs": world * n, "l2": "flushed between steps (512 MiB overwrite, untimed)"
+                       if flush is not None else "not flushed", "episodes_finished": stats_sum[0].item(),
+                       "mean_return": (stats_sum[1] / stats_sum[0]).item() if stats_sum[0].item() > 0 else None,
+                       "wall_s_timed_region": wall},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "kernel": "exo_step_kernel", "kernel_ms": kms,
+                         "algorithmic_bytes_per_env_step": ALGO_BYTES_PER_ENV_STEP,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)"},
+            "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cpu_cores, "kind": "port",
+                             "sample": "%d envs x %d steps (%.1f s) of the same population, oracle/exo_oracle.c fp64 with scipy-RK45 "
+                                       "restated, %d pthreads" % (args.cpu_sample, args.cpu_steps, cpu_secs, cpu_cores)},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 7 * 4, "d2h_bytes_per_step": n * (80 * 4 + rbytes + 1),
+                    "steps": args.e2e_steps, "call": "exo_step_host (pinned host buffers)"},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

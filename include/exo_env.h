@@ -142,6 +142,9 @@ int exo_get_state(ExoHandle* h, ExoStateView* out);
  * 7 count of those steps, 8.. reserved. This vector is what ranks all-reduce over NCCL. */
 int exo_stats(ExoHandle* h, double* out_dev, int32_t reset, void* stream);
 
+/* Toggle ExoConfig.auto_reset after creation (e.g. to time the step kernel alone). */
+int exo_set_auto_reset(ExoHandle* h, int32_t on);
+
 /* Number of kernels this handle has launched so far (for bench.py's gpu_launches). */
 int64_t exo_launch_count(const ExoHandle* h);
 

@@ -1,0 +1,342 @@
+"""GPU: the CUDA path (through the C-ABI, libexo_env.so) against the CPU oracle on the same seeded inputs and
+against the committed reference goldens. Tolerances are stated per quantity:
+
+  RNG-derived episode parameters (tremor magnitude, I/D/S noise, shifts, force scale)   bit-exact (fp64 draws)
+  tremor table: fp32 build == float32(reference table) exactly; fp64 build <= 4e-14 abs (device sin vs glibc sin)
+  fp64 kernel vs oracle with the same (exact) ODE solution      1e-9 relative on info vectors, 1e-10 on reward
+  fp32 kernel vs oracle                                         1e-4 relative on torques/angles, 2e-5 abs on reward parts,
+                                                                1e-6 abs on observations and joint angles
+  either kernel vs the REFERENCE (scipy RK45, rtol 1e-3)        1e-3 relative on ampl_val (the integrator's own truncation
+                                                                error), 1e-5 abs on obs and Bullet joint angles
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import EVAL, GOLDEN, NODR, TRAIN, TYPES15, case_settings
+
+pytestmark = pytest.mark.gpu
+
+INFO = ["actuator_torques", "torque_val", "ampl_val", "tremor_torque_val", "tremor_ampl_val"]
+REW = ["reward_unwanted", "reward_torque", "reward_axis", "reward_control", "reward_smoothness"]
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b)) / max(1e-300, np.max(np.abs(b))))
+
+
+def population(n_types=15, n_motions=8, seed0=100):
+    mids, seqs, seeds = [], [], []
+    for ti in range(n_types):
+        for m in range(n_motions):
+            mids.append(m); seqs.append(TYPES15[ti]); seeds.append(seed0 + ti * 8 + m)
+    return mids, seqs, seeds
+
+
+def axis_reward_is_tie(info, eps=1e-6):
+    """|torque| within eps (relative) of |tremor| on some axis: the 0.5-step of axis_reward may flip under rounding."""
+    a, b = np.abs(info["torque_val"]), np.abs(info["tremor_torque_val"])
+    return bool(np.any(np.abs(a - b) <= eps * np.maximum(b, 1e-30)) and np.any(b > 0))
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+@pytest.mark.parametrize("settings", [NODR, TRAIN], ids=["cfg2_noDR", "cfg3_DR"])
+def test_step_parity_all_types_and_motions(exo, oracle_mod, precision, settings):
+    """BASELINE config 2 shape: every tremor type x every motion, single-step and 50-step trajectories."""
+    O = oracle_mod
+    mids, seqs, seeds = population()
+    n = len(mids)
+    env = exo.BatchedExoskeletonEnv(mids, seqs, seeds, precision=precision, **settings)
+    orc = [O.OracleEnv(mids[i], seqs[i], seeds[i], ode_mode=1, **settings) for i in range(n)]
+    f32 = precision == "fp32"
+    real = np.float32 if f32 else np.float64
+    obs = env.reset().cpu().numpy()
+    obs_o = np.stack([o.reset()[0] for o in orc])
+    assert np.max(np.abs(obs - obs_o)) <= (2e-7 if f32 else 0.0)
+    # ---- episode parameters
+    E = [o.episode() for o in orc]
+    ids = env.get_field("IDS").cpu().numpy()
+    for i in range(n):
+        assert np.array_equal(ids[i], np.concatenate([E[i]["I"].ravel(), E[i]["D"].ravel(), E[i]["S"].ravel()]))
+    assert np.array_equal(env.get_field("tremor_mag").cpu().numpy()[:, 0], np.array([e["mag"] for e in E]))
+    sh, fm = env.get_field("shift").cpu().numpy(), env.get_field("force_max").cpu().numpy()
+    tt, G = env.get_field("tremor_table").cpu().numpy(), env.get_field("G").cpu().numpy()
+    for i in range(n):
+        assert np.array_equal(sh[i], E[i]["shift"].ravel().astype(real))
+        assert np.array_equal(fm[i], E[i]["fmax"].astype(real))
+        L = orc[i].len
+        ref = E[i]["tt"][:tt.shape[2], :L].T
+        if f32:
+            assert np.array_equal(tt[i, :L], ref.astype(np.float32))
+        else:
+            assert np.max(np.abs(tt[i, :L] - ref)) <= 4e-14
+        assert rel(G[i].reshape(7, 7), O.propagator(E[i]["I"], E[i]["D"], E[i]["S"])) <= (2e-7 if f32 else 1e-11)
+    # ---- 50 steps
+    rs = np.random.RandomState(7)
+    tol_vec = 1e-4 if f32 else 1e-9
+    tol_rew = 2e-5 if f32 else 1e-10
+    for t in range(50):
+        a = rs.uniform(-1, 1, (n, 7)).astype(np.float32)
+        ob, rw, dn, info = env.step(torch.from_numpy(a).cuda(), with_info=True)
+        ob, rw, dn = ob.cpu().numpy(), rw.cpu().numpy(), dn.cpu().numpy()
+        inf = {k: v.cpu().numpy() for k, v in info.items()}
+        qb = env.get_field("q").cpu().numpy()
+        for i in range(n):
+            o_ob, o_r, o_d, _, o_inf = orc[i].step(a[i].astype(np.float64))
+            assert bool(dn[i]) == o_d
+            assert np.max(np.abs(ob[i] - o_ob)) <= (1e-6 if f32 else 1.2e-7), (t, i)
+            assert np.max(np.abs(qb[i] - orc[i].bullet_q())) <= (1e-6 if f32 else 1e-12)
+            for k in INFO:
+                assert rel(inf[k][i], o_inf[k]) <= tol_vec, (t, i, k)
+            parts = np.array([o_inf[k] for k in REW])
+            tie = axis_reward_is_tie(o_inf)
+            if not tie:
+                assert np.max(np.abs(inf["reward_parts"][i] - parts)) <= tol_rew, (t, i)
+                assert abs(float(rw[i]) - o_r) <= tol_rew, (t, i)
+            am = orc[i].amplitude_metric(o_inf["ampl_val"], o_inf["tremor_ampl_val"])
+            assert abs(float(inf["amp_metric"][i]) - am) <= (5e-3 if f32 else 1e-8) * max(1.0, abs(am))
+    env.close()
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_against_reference_goldens_cfg2(exo, precision):
+    """Reference Python (numpy RNG + scipy RK45 + restated pybullet) -> tests/golden/ref_cfg2_types_x_motions.npz."""
+    g = np.load(os.path.join(GOLDEN, "ref_cfg2_types_x_motions.npz"))
+    cases = ["B%d" % i for i in range(120)]
+    mids = [int(g[c + "/meta_motion"]) for c in cases]
+    seqs = [g[c + "/meta_seq"] for c in cases]
+    seeds = [int(g[c + "/meta_seed"]) for c in cases]
+    env = exo.BatchedExoskeletonEnv(mids, seqs, seeds, precision=precision, **case_settings(g, "B0"))
+    f32 = precision == "fp32"
+    obs = env.reset().cpu().numpy()
+    tt = env.get_field("tremor_table").cpu().numpy()
+    for i, c in enumerate(cases):
+        assert np.max(np.abs(obs[i] - g[c + "/ep_obs0"][0])) <= 2e-7
+        L = int(g[c + "/meta_max_count"])
+        ref = g[c + "/ep_tt"][0][:4, :L].T
+        if f32:
+            assert np.array_equal(tt[i, :L], ref.astype(np.float32))            # bit-exact table in the fp32 build
+        else:
+            assert np.max(np.abs(tt[i, :L] - ref)) <= 4e-14
+    for t in range(30):
+        a = np.stack([g[c + "/action"][t] for c in cases]).astype(np.float32)
+        ob, rw, dn, info = env.step(torch.from_numpy(a).cuda(), with_info=True)
+        ob = ob.cpu().numpy()
+        inf = {k: v.cpu().numpy() for k, v in info.items()}
+        qb = env.get_field("q").cpu().numpy()
+        for i, c in enumerate(cases):
+            assert np.max(np.abs(ob[i] - g[c + "/obs"][t])) <= 1e-5
+            assert np.max(np.abs(qb[i] - g[c + "/qb"][t])) <= 1e-5
+            assert rel(inf["ampl_val"][i], g[c + "/ampl_val"][t]) <= 1e-3          # RK45 rtol=1e-3 vs exact solution
+            assert rel(inf["tremor_ampl_val"][i], g[c + "/tremor_ampl_val"][t]) <= 1e-3
+            assert rel(inf["torque_val"][i], g[c + "/torque_val"][t]) <= 2e-4
+            assert rel(inf["tremor_torque_val"][i], g[c + "/tremor_torque_val"][t]) <= 1e-6
+    env.close()
+
+
+def _replay_golden_episodes(exo, g, cases, precision, settings_case):
+    mids = [int(g[c + "/meta_motion"]) for c in cases]
+    seqs = [g[c + "/meta_seq"] for c in cases]
+    seeds = [int(g[c + "/meta_seed"]) for c in cases]
+    env = exo.BatchedExoskeletonEnv(mids, seqs, seeds, precision=precision, auto_reset=True, **case_settings(g, settings_case))
+    obs = env.reset().cpu().numpy()
+    nsteps = [len(g[c + "/action"]) for c in cases]
+    ep = [0] * len(cases)
+    for i, c in enumerate(cases):
+        assert np.max(np.abs(obs[i] - g[c + "/ep_obs0"][0])) <= 2e-7
+    worst_obs, worst_q, worst_r, ties = 0.0, 0.0, 0.0, 0
+    for t in range(max(nsteps)):
+        a = np.stack([g[c + "/action"][min(t, nsteps[i] - 1)] for i, c in enumerate(cases)]).astype(np.float32)
+        ob, rw, dn = env.step(torch.from_numpy(a).cuda())
+        ob, rw, dn = ob.cpu().numpy(), rw.cpu().numpy(), dn.cpu().numpy()
+        qb = env.get_field("q").cpu().numpy()
+        mag = env.get_field("tremor_mag").cpu().numpy()
+        ids = env.get_field("IDS").cpu().numpy()
+        for i, c in enumerate(cases):
+            if t >= nsteps[i]:
+                continue
+            assert bool(dn[i]) == bool(g[c + "/done"][t])
+            worst_q = max(worst_q, float(np.max(np.abs(qb[i] - g[c + "/qb"][t]))))
+            ta, tb = np.abs(g[c + "/torque_val"][t]), np.abs(g[c + "/tremor_torque_val"][t])
+            tie = bool(np.any((np.abs(ta - tb) <= 1e-5 * np.maximum(tb, 1e-30)) & (tb > 0)))
+            ties += tie
+            if not tie:     # axis_reward is a 0.5-step at |torque| == |tremor| (Exoskeleton_env.py:301-304); a saturated
+                            # actor (action == -1 -> zero force) sits exactly on it
+                worst_r = max(worst_r, abs(float(rw[i]) - float(g[c + "/reward"][t])))
+            if dn[i]:       # auto-reset: the returned obs is the first obs of the next episode
+                ep[i] += 1
+                assert np.max(np.abs(ob[i] - g[c + "/ep_obs0"][ep[i]])) <= 1e-5
+                assert mag[i, 0] == float(g[c + "/ep_mag"][ep[i]])                       # stream continues bit-exactly
+                assert np.array_equal(ids[i, :49], g[c + "/ep_I"][ep[i]].ravel())
+            else:
+                worst_obs = max(worst_obs, float(np.max(np.abs(ob[i] - g[c + "/obs"][t]))))
+    env.close()
+    assert ties <= 0.5 * sum(nsteps)
+    return worst_obs, worst_q, worst_r
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_against_reference_goldens_cfg3_full_episodes_with_auto_reset(exo, precision):
+    """Training DR, one full episode per motion, reset, 20 more steps: state carried over the reset
+    (Bullet joint state and prev_action are NOT reset by the reference) and the per-env RNG stream continues."""
+    g = np.load(os.path.join(GOLDEN, "ref_cfg3_dr_episodes.npz"))
+    wo, wq, wr = _replay_golden_episodes(exo, g, ["C%d" % m for m in range(8)], precision, "C0")
+    assert wo <= 1e-5 and wq <= 1e-5 and wr <= 2e-3, (wo, wq, wr)
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_against_reference_goldens_cfg1_trained_actor_1000_steps(exo, precision):
+    """BASELINE config 1: motion 0, type [1,1,1,1], seed 0, evaluation settings, the shipped TD7 checkpoint actor's
+    actions, 1000 steps over 4+ episodes."""
+    g = np.load(os.path.join(GOLDEN, "ref_cfg1_trained_actor.npz"))
+    wo, wq, wr = _replay_golden_episodes(exo, g, ["A0"], precision, "A0")
+    assert wo <= 1e-5 and wq <= 1e-5 and wr <= 2e-3, (wo, wq, wr)
+
+
+def test_single_env_facade_matches_reference_signatures(exo):
+    g = np.load(os.path.join(GOLDEN, "ref_cfg1_trained_actor.npz"))
+    env = exo.ExoskeletonEnv_train("0", np.array([1, 1, 1, 1, 0, 0, 0]), seed=0, **EVAL)
+    assert env.observation_space.shape[0] == 80 and env.action_space.shape[0] == 7
+    assert env.return_max_length() == 232 and abs(env.max_reward - 3.5) < 1e-12
+    obs, score = env.reset()
+    assert obs.dtype == np.float32 and obs.shape == (80,) and score == 2
+    assert np.max(np.abs(obs - g["A0/ep_obs0"][0])) <= 2e-7
+    seq, mx = env.return_generated_tremor_data()
+    assert np.allclose(mx[:4], g["A0/ep_tt"][0][:4].max(1), atol=1e-12) and list(seq) == [1, 1, 1, 1, 0, 0, 0]
+    for t in range(5):
+        out = env.step(g["A0/action"][t])
+        obs, reward, done, trunc, info = out
+        assert isinstance(reward, float) and isinstance(done, bool) and trunc is False
+        assert set(info) >= set(INFO) | set(REW)
+        assert np.max(np.abs(obs - g["A0/obs"][t])) <= 1e-5
+        assert abs(reward - g["A0/reward"][t]) <= 1e-3
+        ang = env.return_original_joint_angles()
+        assert len(ang) == 7 and ang[5] == 0 and ang[6] == 0
+    env.close()
+
+
+def test_host_buffer_entry_equals_device_entry(exo):
+    mids, seqs, seeds = population(4, 8)
+    a_env = exo.BatchedExoskeletonEnv(mids, seqs, seeds, **TRAIN)
+    b_env = exo.BatchedExoskeletonEnv(mids, seqs, seeds, **TRAIN)
+    o1 = a_env.reset().cpu()
+    o2 = b_env.reset_host().clone()
+    assert torch.equal(o1, o2)
+    rs = np.random.RandomState(0)
+    for t in range(5):
+        a = torch.from_numpy(rs.uniform(-1, 1, (len(mids), 7)).astype(np.float32))
+        ob, rw, dn = a_env.step(a.cuda())
+        hob, hrw, hdn = b_env.step_host(a.pin_memory())
+        assert torch.equal(ob.cpu(), hob) and torch.equal(rw.cpu(), hrw) and torch.equal(dn.cpu(), hdn.bool())
+    a_env.close(); b_env.close()
+
+
+def test_masked_reset_idle_envs_and_ragged_batch(exo, oracle_mod):
+    """Edge cases: batch size not a multiple of the block, partial reset masks, envs idling after done."""
+    n = 77
+    mids = [i % 8 for i in range(n)]
+    seqs = [TYPES15[i % 15] for i in range(n)]
+    seeds = list(range(500, 500 + n))
+    env = exo.BatchedExoskeletonEnv(mids, seqs, seeds, precision="fp64", **TRAIN)
+    orc = [oracle_mod.OracleEnv(mids[i], seqs[i], seeds[i], ode_mode=1, **TRAIN) for i in range(n)]
+    env.reset()
+    for o in orc:
+        o.reset()
+    rs = np.random.RandomState(1)
+    for t in range(3):
+        a = rs.uniform(-1, 1, (n, 7)).astype(np.float32)
+        env.step(torch.from_numpy(a).cuda())
+        for i, o in enumerate(orc):
+            o.step(a[i].astype(np.float64))
+    mask = np.zeros(n, np.uint8)
+    mask[::3] = 1
+    obs = env.reset(mask).cpu().numpy()
+    for i in np.nonzero(mask)[0]:
+        assert np.max(np.abs(obs[i] - orc[i].reset()[0])) <= 1.2e-7
+    counts = env.get_field("counts").cpu().numpy()[:, 0]
+    assert np.all(counts[mask == 1] == 2) and np.all(counts[mask == 0] == 5)
+    # run everyone past the end of the shortest motion without auto-reset: finished envs idle, done stays set
+    done_seen = np.zeros(n, bool)
+    for t in range(232):
+        a = rs.uniform(-1, 1, (n, 7)).astype(np.float32)
+        ob, rw, dn = env.step(torch.from_numpy(a).cuda())
+        dn = dn.cpu().numpy()
+        assert np.all(dn[done_seen])                     # idle envs keep reporting done
+        assert np.all(rw.cpu().numpy()[done_seen] == 0)
+        done_seen |= dn
+    assert done_seen[np.array(mids) == 0].all() and not done_seen[np.array(mids) == 5].any()
+    env.close()
+
+
+def test_checkpoint_restore_round_trip(exo):
+    mids, seqs, seeds = population(3, 8)
+    env = exo.BatchedExoskeletonEnv(mids, seqs, seeds, auto_reset=True, **TRAIN)
+    env.reset()
+    rs = np.random.RandomState(2)
+    acts = torch.from_numpy(rs.uniform(-1, 1, (300, len(mids), 7)).astype(np.float32)).cuda()
+    for t in range(10):
+        env.step(acts[t])
+    sd = env.state_dict()
+    ref = [tuple(x.clone() for x in env.step(acts[t])) for t in range(10, 300)]     # crosses auto-resets
+    env2 = exo.BatchedExoskeletonEnv(mids, seqs, [0] * len(mids), auto_reset=True, **TRAIN)
+    env2.reset()
+    env2.load_state_dict(sd)
+    for t in range(10, 300):
+        ob, rw, dn = env2.step(acts[t])
+        assert torch.equal(ob, ref[t - 10][0]) and torch.equal(rw, ref[t - 10][1]) and torch.equal(dn, ref[t - 10][2])
+    env.close(); env2.close()
+
+
+def test_forward_kinematics_kernel_known_answers(exo, oracle_mod):
+    d = oracle_mod.data()
+    env = exo.BatchedExoskeletonEnv([0], [TYPES15[14]], [0], precision="fp64", **NODR)
+    p = env.forward_kinematics(d["fk/theta"]).cpu().numpy()
+    assert np.max(np.abs(p - d["fk/p"])) <= 1e-15 + 2e-16          # cos(pi/2) taken as exactly 0
+    rs = np.random.RandomState(0)
+    th = rs.uniform(-3, 3, (4096, 7))
+    p = env.forward_kinematics(th).cpu().numpy()
+    ref = np.stack([oracle_mod.forward_kinematics(t) for t in th])
+    assert np.max(np.abs(p - ref)) <= 1e-14
+    env.close()
+
+
+def test_full_size_properties_65536_envs(exo):
+    """BASELINE config 3 size. Size-independent properties: (1) determinism — two handles with the same seeds agree
+    bit for bit over 400 steps incl. auto-resets; (2) the result for an env does not depend on its neighbours or on
+    the batch it sits in (a 4096-env slice run alone is identical); (3) episode bookkeeping: every env of motion m
+    finishes exactly floor(steps / (L_m - 3)) episodes; (4) rewards stay in (0, 1]."""
+    from exo_b200 import sharding
+    n, steps = 65536, 400
+    motion, seqs, seeds = sharding.benchmark_population(n)
+    env = exo.BatchedExoskeletonEnv(motion, seqs, seeds, auto_reset=True, **TRAIN)
+    sl = slice(8192 * 3 - 2048, 8192 * 3 + 2048)                   # straddles a motion boundary
+    sub = exo.BatchedExoskeletonEnv(motion[sl], seqs[sl], seeds[sl], auto_reset=True, **TRAIN)
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(0)
+    acts = torch.rand(8, n, 7, device="cuda", generator=gen) * 2 - 1
+    o, s = env.reset(), sub.reset()
+    assert torch.equal(o[sl], s)
+    chk = torch.zeros((), dtype=torch.float64, device="cuda")
+    for t in range(steps):
+        ob, rw, dn = env.step(acts[t % 8])
+        sob, srw, sdn = sub.step(acts[t % 8][sl].contiguous())
+        if t % 50 == 0 or t > steps - 3:
+            assert torch.equal(ob[sl], sob) and torch.equal(rw[sl], srw) and torch.equal(dn[sl], sdn)
+        assert bool((rw > 0).all()) and bool((rw <= 1).all())
+        chk += ob.double().sum() + rw.double().sum()
+    st = env.stats().cpu().numpy()
+    L = np.array([232, 316, 282, 295, 270, 347, 266, 273])
+    assert st[0] == sum(8192 * (steps // (l - 3)) for l in L)
+    assert st[3] == n * steps
+    env2 = exo.BatchedExoskeletonEnv(motion, seqs, seeds, auto_reset=True, **TRAIN)
+    env2.reset()
+    chk2 = torch.zeros((), dtype=torch.float64, device="cuda")
+    for t in range(steps):
+        ob, rw, dn = env2.step(acts[t % 8])
+        chk2 += ob.double().sum() + rw.double().sum()
+    assert chk.item() == chk2.item()
+    for e in (env, sub, env2):
+        e.close()

@@ -1,0 +1,142 @@
+"""CPU: host-side logic of the product — URDF/motion parsing, the C-ABI surface, sharding. No compute calls."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, REPO
+
+PKG = "a-deep-reinforcement-learning-enabled-soft-exoskeleton-for-parkinson-s-patients_b200"
+
+
+def test_alias_and_package_import(exo):
+    import importlib
+    assert importlib.import_module(PKG).BatchedExoskeletonEnv is exo.BatchedExoskeletonEnv
+    assert exo.ExoskeletonEnv_train.__init__.__code__.co_varnames[1:11] == (
+        "reference_motion_file_num", "tremor_sequence", "tremor_amplitude_range", "first_harmonics_interval",
+        "second_harmonics_interval", "max_force_shoulder", "max_force_elbow", "dr_actuator_end_pos_shift",
+        "dr_actuator_range", "matrix_noise_fraction")          # Exoskeleton_env.py:38-48, same names and order
+
+
+def test_geometry_matches_independent_urdf_parse(exo):
+    """The product's parser (urdf.py) and the oracle's (minibullet.py) read the reference URDF independently."""
+    tree = exo.urdf.load_geometry()
+    d = np.load(os.path.join(GOLDEN, "ref_data_and_units.npz"))
+    links = tree["links"]
+    assert [l["name"] for l in links] == list(d["geo/names"])
+    assert [l["parent"] for l in links] == list(d["geo/parent"])
+    assert [l["joint_type"] for l in links] == list(d["geo/joint_type"])
+    for key in ("origin_xyz", "origin_R", "axis", "com_xyz", "lower", "upper"):
+        assert np.allclose(np.array([l[key] for l in links]), d["geo/" + key], atol=1e-15), key
+    assert np.allclose(tree["base_pos"], d["geo/base_pos"])
+    # link handles hard-coded by the reference (Exoskeleton_sim_pybullet.py:48-63) point at the right links
+    names = [l["name"] for l in links]
+    want = ["k11", "k12", "k21", "k22", "k31", "k32", "k41", "k42", "k51", "k52", "k61", "k62", "k71", "k72"]
+    assert [names[i] for i in tree["act_link"]] == want
+    assert names[tree["shoulder_link"]] == "auxlink1" and names[tree["elbow_link"]] == "auxlink3"
+
+
+def test_urdf_parser_on_a_file(tmp_path, exo):
+    urdf = tmp_path / "two.urdf"
+    urdf.write_text("""<?xml version="1.0"?><robot name="r"><link name="b"/><link name="a"><inertial><origin xyz="0 0.5 0"/></inertial></link>
+    <link name="c"/><joint type="revolute" name="j0"><axis xyz="0 0 1"/><limit lower="-1" upper="2"/><parent link="b"/><child link="a"/>
+    <origin xyz="1 2 3" rpy="0 0 1.5707963267948966"/></joint>
+    <joint type="prismatic" name="j1"><axis xyz="0 0 1"/><parent link="a"/><child link="c"/><origin xyz="0 0 1" rpy="0 0 0"/></joint></robot>""")
+    t = exo.urdf.parse_urdf(str(urdf), base_position=(0, 0, 0))
+    assert [l["name"] for l in t["links"]] == ["a", "c"] and [l["parent"] for l in t["links"]] == [-1, 0]
+    assert np.allclose(np.array(t["links"][0]["origin_R"]).reshape(3, 3), [[0, -1, 0], [1, 0, 0], [0, 0, 1]], atol=1e-15)
+    assert t["links"][0]["com_xyz"] == [0.0, 0.5, 0.0] and t["links"][0]["lower"] == -1 and t["links"][1]["joint_type"] == 1
+
+
+def test_motion_tables(tmp_path, exo):
+    d = np.load(os.path.join(GOLDEN, "ref_data_and_units.npz"))
+    ms = exo.motions.load_motions()
+    assert [m.shape[1] for m in ms] == [232, 316, 282, 295, 270, 347, 266, 273]
+    for i, m in enumerate(ms):
+        assert np.array_equal(m, d["motion/%d" % i])          # bit-identical to the reference's read_env_texts
+    # text parser: 17 columns, first five kept; ragged / short rows rejected
+    f = tmp_path / "ref_motion_0.txt"
+    rows = np.arange(3 * 17, dtype=np.float64).reshape(3, 17) / 7
+    f.write_text("\n".join(" ".join(repr(float(x)) for x in r) for r in rows) + "\n\n")
+    got = exo.motions.read_motion_file(str(f))
+    assert got.shape == (5, 3) and np.array_equal(got, rows[:, :5].T)
+    f.write_text("1 2 3\n")
+    with pytest.raises(ValueError):
+        exo.motions.read_motion_file(str(f))
+    tables, lengths = exo.motions.pack(ms)
+    assert tables.shape == (8, 5, 347) and list(lengths) == [m.shape[1] for m in ms] and tables[0, :, 232:].sum() == 0
+
+
+def _header_functions():
+    text = open(os.path.join(REPO, "include", "exo_env.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(exo_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol(exo):
+    lib = exo.load_library()                                  # dlopen works without a GPU
+    declared = _header_functions()
+    assert len(declared) >= 16
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert sorted(exo._capi.SIGNATURES) == declared           # the ctypes table binds exactly the header's surface
+    assert lib.exo_abi_version() == 1
+
+
+def test_ctypes_structs_match_the_header(tmp_path, exo):
+    src = tmp_path / "sz.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "exo_env.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu\\n",'
+                   'sizeof(ExoConfig),sizeof(ExoGeometry),sizeof(ExoInfo),sizeof(ExoStateView),offsetof(ExoConfig,link_state_lag),'
+                   'offsetof(ExoGeometry,act_link));return 0;}\n')
+    exe = tmp_path / "sz"
+    subprocess.check_call(["gcc", "-I", os.path.join(REPO, "include"), str(src), "-o", str(exe)])
+    sizes = [int(x) for x in subprocess.check_output([str(exe)]).split()]
+    c = exo._capi
+    assert sizes == [ctypes.sizeof(c.ExoConfig), ctypes.sizeof(c.ExoGeometry), ctypes.sizeof(c.ExoInfo),
+                     ctypes.sizeof(c.ExoStateView), c.ExoConfig.link_state_lag.offset, c.ExoGeometry.act_link.offset]
+
+
+def test_no_gpu_means_loud_failure(exo):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(exo.ExoError):
+        exo.BatchedExoskeletonEnv([0], [[1, 1, 1, 1, 0, 0, 0]], [0], tremor_amplitude_range=[1, 1], first_harmonics_interval=[4, 6],
+                                  second_harmonics_interval=[8, 10], max_force_shoulder=40, max_force_elbow=20)
+    # and the C-ABI itself refuses rather than computing on the host
+    lib = exo.load_library()
+    h = ctypes.c_void_p()
+    cfg = exo._capi.ExoConfig()
+    geo = exo.urdf.to_struct(exo.urdf.load_geometry())
+    rc = lib.exo_create(ctypes.byref(cfg), ctypes.byref(geo), 4, 0, ctypes.byref(h))
+    assert rc < 0 and lib.exo_last_error()
+
+
+def test_product_never_imports_the_oracle():
+    """The oracle is a checker: nothing under the package (or its C sources) may reference it."""
+    bad = []
+    for root, _, files in os.walk(os.path.join(REPO, PKG)):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(root, f), errors="ignore").read()
+                if re.search(r"^\s*(import|from)\s+(oracle|minibullet)|exo_oracle|libexo_oracle|#include\s+\"[^\"]*oracle", text, flags=re.M):
+                    bad.append(f)
+    assert not bad, bad
+
+
+def test_shard_ranges_partition_the_population(exo):
+    sh = exo.sharding
+    for n, w in ((1_048_576, 8), (65_536, 1), (1000, 3), (7, 8)):
+        spans = [sh.shard_range(n, r, w) for r in range(w)]
+        assert spans[0][0] == 0 and spans[-1][1] == n and all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+    m, s, seeds = sh.benchmark_population(65_536, 0, 1)
+    assert np.array_equal(np.bincount(m), np.full(8, 8192)) and np.all(np.diff(m) >= 0)     # cfg 3: 8192 envs per motion, contiguous
+    assert len({tuple(x) for x in s}) == 15 and s[:, :4].sum(1).min() >= 1 and s[:, 4:].sum() == 0
+    # global ids/seeds do not depend on the number of ranks
+    parts = [sh.benchmark_population(4096, r, 4) for r in range(4)]
+    assert np.array_equal(np.concatenate([p[2] for p in parts]), np.arange(4096))
+    assert np.array_equal(np.concatenate([p[1] for p in parts]), sh.benchmark_population(4096, 0, 1)[1])
