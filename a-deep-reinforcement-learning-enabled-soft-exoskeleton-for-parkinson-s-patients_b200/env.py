@@ -247,7 +247,7 @@ class BatchedExoskeletonEnv(object):
 
     def get_field(self, name):
         """Copy of one state field as an env-major tensor [N, k] (tremor_table: [N, table_len, axes])."""
-        t = self._raw(name)[:, :self.n].t().contiguous()
+        t = self._raw(name)[:, :self.n].t().clone(memory_format=torch.contiguous_format)   # a copy, never a live view
         if name == "tremor_table":
             v = self._view()
             return t.reshape(self.n, v.table_len, v.table_axes)
