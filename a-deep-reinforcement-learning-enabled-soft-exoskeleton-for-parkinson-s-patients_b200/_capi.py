@@ -35,12 +35,11 @@ class ExoInfo(C.Structure):
                                           "tremor_ampl_val", "reward_parts", "amp_metric")]
 
 
-class ExoStateView(C.Structure):
-    _fields_ = [("n_envs", C.c_int32), ("stride", C.c_int32), ("precision", C.c_int32), ("table_len", C.c_int32),
-                ("table_axes", C.c_int32)] + \
-               [(k, C.c_void_p) for k in ("q", "q_lag", "pos_vec", "elbow_ref", "prev_action", "prev_action2", "force_max",
-                                          "shift", "G", "IDS", "tremor_table", "tremor_mag", "counts", "meta", "mt_state",
-                                          "ep_return")]
+# EXO_FIELD_* (include/exo_env.h): name -> id; EXO_DT_* -> torch dtype name
+FIELDS = {name: i for i, name in enumerate(
+    ("q", "q_lag", "pos_vec", "elbow_ref", "prev_action", "prev_action2", "force_max", "shift", "G", "IDS", "tremor_table",
+     "tremor_mag", "counts", "meta", "mt_state", "ep_return"))}
+DT_REAL, DT_F64, DT_I32, DT_U32 = 0, 1, 2, 3
 
 
 # name -> (restype, argtypes); also the list tests check against include/exo_env.h
@@ -56,7 +55,9 @@ SIGNATURES = {
     "exo_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(ExoInfo), C.c_void_p]),
     "exo_step_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "exo_reset_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
-    "exo_get_state": (C.c_int, [C.c_void_p, C.POINTER(ExoStateView)]),
+    "exo_field_info": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "exo_get_field": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
+    "exo_set_field": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     "exo_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
     "exo_set_auto_reset": (C.c_int, [C.c_void_p, C.c_int32]),
     "exo_launch_count": (C.c_int64, [C.c_void_p]),

@@ -33,7 +33,7 @@ extern "C" int exo_abi_version(void) { return 1; }
 struct ExoHandle {
     ExoConfig cfg;
     ExoGeometry geo;
-    int n, stride, device, nax, max_len, n_motions;
+    int n, stride, device, nax, max_len, n_motions, n_sm, parity;
     bool have_motions, have_types, seeded;
     int64_t launches;
     std::vector<void*> allocs;
@@ -123,15 +123,15 @@ static int build_chain(ExoHandle* h) {
 
 template <typename R>
 static int alloc_arrays(ExoHandle* h, EnvArrays<R>& A) {
-    const size_t st = h->stride;
+    const size_t st = h->stride, n = h->n;
     memset(&A, 0, sizeof(A));
     A.n = h->n; A.stride = h->stride;
-#define AL(field, T, k) if (int rc = dev_alloc(h, (void**)&A.field, sizeof(T) * (size_t)(k) * st)) return rc
-    AL(q, R, 5); AL(qlag, R, 5); AL(posvec, R, 21); AL(elref, R, 3); AL(fprev, R, 7); AL(fprev2, R, 7); AL(ret, R, 1);
-    AL(counts, int, 1); AL(fmax, R, 2); AL(shift, R, 42); AL(G, R, 49); AL(IDS, double, 147); AL(mag, double, 1);
-    AL(meta, int, 1); AL(mt, uint32_t, 625);
+#define AL(field, T, count) if (int rc = dev_alloc(h, (void**)&A.field, sizeof(T) * (size_t)(count))) return rc
+    AL(state, V4<R>, NV_STATE * st); AL(ep, V4<R>, NV_EP * st); AL(G, V4<R>, NV_G * st);
+    AL(ret, R, st); AL(counts, int, st); AL(meta, int, st); AL(mag, double, st);
+    AL(IDS, double, n * EXO_IDS_PITCH); AL(mt, uint32_t, n * EXO_MT_PITCH);
+    AL(stats, double, EXO_N_STATS); AL(fin_count, int, 2); AL(fin_list, int, 2 * st);
 #undef AL
-    if (int rc = dev_alloc(h, (void**)&A.stats, sizeof(double) * EXO_N_STATS)) return rc;
     return 0;
 }
 
@@ -149,6 +149,7 @@ extern "C" int exo_create(const ExoConfig* cfg, const ExoGeometry* geo, int32_t 
     ExoHandle* h = new ExoHandle();
     h->cfg = *cfg; h->geo = *geo; h->n = n_envs; h->stride = (n_envs + 31) & ~31; h->device = device;
     h->nax = 4; h->max_len = 0; h->n_motions = 0; h->have_motions = h->have_types = h->seeded = false; h->launches = 0;
+    h->n_sm = prop.multiProcessorCount; h->parity = 0;
     h->d_act = nullptr; h->d_obs = nullptr; h->d_rew = nullptr; h->d_done = nullptr; h->d_mask = nullptr; h->d_seeds = nullptr;
     if (int rc = build_chain(h)) { delete h; return rc; }
     int rc = (cfg->precision == EXO_F32) ? alloc_arrays(h, h->Af) : alloc_arrays(h, h->Ad);
@@ -203,13 +204,8 @@ static int alloc_tables(ExoHandle* h, EnvArrays<R>& A) {
     int tl = 0;
     for (int l : h->motion_len) tl = l > tl ? l : tl;
     A.table_len = tl;
-    const size_t st = h->stride;
-    if (int rc = dev_alloc(h, (void**)&A.tt, sizeof(R) * (size_t)tl * h->nax * st)) return rc;
-    if (int rc = dev_alloc(h, (void**)&A.sc_noise, sizeof(double) * (size_t)tl * st, false)) return rc;
-    if (int rc = dev_alloc(h, (void**)&A.sc_w1, sizeof(double) * (size_t)tl * st, false)) return rc;
-    if (int rc = dev_alloc(h, (void**)&A.sc_w2, sizeof(double) * (size_t)tl * st, false)) return rc;
-    if (int rc = dev_alloc(h, (void**)&A.sc_sign, sizeof(uint32_t) * 7 * EXO_SIGN_WORDS * st, false)) return rc;
-    return 0;
+    const size_t naxv = (h->nax + 3) / 4;
+    return dev_alloc(h, (void**)&A.tt, sizeof(V4<R>) * (size_t)tl * h->stride * naxv);
 }
 
 extern "C" int exo_set_env_types(ExoHandle* h, const uint8_t* seq, const int32_t* motion_id) {
@@ -242,6 +238,8 @@ template <typename R>
 static StepConst<R> step_const(const ExoHandle* h) {
     StepConst<R> K;
     K.fmax_sh0 = (R)h->cfg.max_force_shoulder; K.fmax_el0 = (R)h->cfg.max_force_elbow;
+    K.inv_fmax_sh0 = R(1) / K.fmax_sh0; K.inv_fmax_el0 = R(1) / K.fmax_el0;
+    K.parity = h->parity;
     K.L1 = (R)h->cfg.humerus_length; K.L2 = (R)h->cfg.forearm_length;
     K.lag = h->cfg.link_state_lag; K.limits = h->cfg.joint_limits; K.auto_reset = h->cfg.auto_reset; K.metrics = h->cfg.metrics;
     return K;
@@ -256,15 +254,19 @@ static ResetConst reset_const(const ExoHandle* h) {
     K.fmax_sh0 = h->cfg.max_force_shoulder; K.fmax_el0 = h->cfg.max_force_elbow;
     K.dt = 1.0 / 40.0;                       // Exoskeleton_env.py:59
     K.lag = h->cfg.link_state_lag;
+    K.ctor_skip = 0; K.list_parity = -1;
     return K;
 }
 
+// list_parity >= 0: the envs the step of that parity appended to the finished-list; otherwise by mask (NULL: all)
 template <typename R>
-static int reset_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const uint8_t* mask, float* obs, cudaStream_t s) {
-    const ResetConst K = reset_const(h);
-    const StepConst<R> SK = step_const<R>(h);
-    launch_reset<R>(A, C, K, SK, h->nax, mask, obs, s);
-    h->launches += 2;
+static int reset_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const uint8_t* mask, float* obs, int list_parity,
+                   int ctor_skip, cudaStream_t s) {
+    ResetConst K = reset_const(h);
+    K.list_parity = list_parity; K.ctor_skip = ctor_skip;
+    if (int e = launch_reset<R>(A, C, K, h->nax, h->n_sm, mask, obs, s))
+        return fail(EXO_ERR_CUDA, "exo_reset_kernel setup: %s", cudaGetErrorString((cudaError_t)e));
+    h->launches += 1;
     CK(cudaGetLastError());
     return 0;
 }
@@ -283,12 +285,13 @@ extern "C" int exo_seed(ExoHandle* h, const uint32_t* seeds, void* stream) {
     cudaStream_t s = (cudaStream_t)stream;
     CK(cudaMemcpyAsync(h->d_seeds, seeds, sizeof(uint32_t) * h->n, cudaMemcpyHostToDevice, s));
     uint32_t* mt = h->cfg.precision == EXO_F32 ? h->Af.mt : h->Ad.mt;
-    launch_seed(mt, h->n, h->stride, h->d_seeds, h->cfg.reference_ctor ? 1 : 0, s);
+    launch_seed(mt, h->n, h->d_seeds, s);
     h->launches += 1;
     CK(cudaGetLastError());
     h->seeded = true;
-    if (h->cfg.reference_ctor) {             // the constructor's own initialize_movement (Exoskeleton_env.py:172)
-        int rc = h->cfg.precision == EXO_F32 ? reset_t(h, h->Af, h->Cf, nullptr, nullptr, s) : reset_t(h, h->Ad, h->Cd, nullptr, nullptr, s);
+    if (h->cfg.reference_ctor) {             // the constructor's rand() (Exoskeleton_env.py:70) and its own initialize_movement (:172)
+        int rc = h->cfg.precision == EXO_F32 ? reset_t(h, h->Af, h->Cf, nullptr, nullptr, -1, 2, s)
+                                             : reset_t(h, h->Ad, h->Cd, nullptr, nullptr, -1, 2, s);
         if (rc) return rc;
     }
     CK(cudaStreamSynchronize(s));            // seeds is a host buffer the caller may free
@@ -299,12 +302,14 @@ extern "C" int exo_reset(ExoHandle* h, const uint8_t* mask_dev, float* obs_dev, 
     if (int rc = check_ready(h, "exo_reset")) return rc;
     if (!obs_dev) return fail(EXO_ERR_ARG, "exo_reset: obs_dev is null");
     cudaStream_t s = (cudaStream_t)stream;
-    return h->cfg.precision == EXO_F32 ? reset_t(h, h->Af, h->Cf, mask_dev, obs_dev, s) : reset_t(h, h->Ad, h->Cd, mask_dev, obs_dev, s);
+    return h->cfg.precision == EXO_F32 ? reset_t(h, h->Af, h->Cf, mask_dev, obs_dev, -1, 0, s)
+                                       : reset_t(h, h->Ad, h->Cd, mask_dev, obs_dev, -1, 0, s);
 }
 
 template <typename R>
 static int step_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const float* actions, float* obs, void* reward,
                   uint8_t* done, const ExoInfo* info, cudaStream_t s) {
+    h->parity ^= 1;
     const StepConst<R> K = step_const<R>(h);
     InfoPtrs<R> ip;
     memset(&ip, 0, sizeof(ip));
@@ -317,7 +322,7 @@ static int step_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const f
     launch_step<R>(A, C, K, h->nax, want_info, actions, obs, (R*)reward, done, ip, s);
     h->launches += 1;
     CK(cudaGetLastError());
-    if (h->cfg.auto_reset) return reset_t(h, A, C, done, obs, s);
+    if (h->cfg.auto_reset) return reset_t(h, A, C, nullptr, obs, K.parity, 0, s);
     return 0;
 }
 
@@ -356,19 +361,45 @@ extern "C" int exo_reset_host(ExoHandle* h, const uint8_t* mask_host, float* obs
     return 0;
 }
 
-template <typename R>
-static void fill_view(const ExoHandle* h, const EnvArrays<R>& A, ExoStateView* v) {
-    v->n_envs = h->n; v->stride = h->stride; v->precision = h->cfg.precision; v->table_len = A.table_len; v->table_axes = h->nax;
-    v->q = A.q; v->q_lag = A.qlag; v->pos_vec = A.posvec; v->elbow_ref = A.elref; v->prev_action = A.fprev; v->prev_action2 = A.fprev2;
-    v->force_max = A.fmax; v->shift = A.shift; v->G = A.G; v->IDS = A.IDS; v->tremor_table = A.tt; v->tremor_mag = A.mag;
-    v->counts = A.counts; v->meta = A.meta; v->mt_state = A.mt; v->ep_return = A.ret;
+// elements per env and dtype of each EXO_FIELD_*
+static int field_shape(const ExoHandle* h, int field, int* k, int* dtype) {
+    static const int K0[EXO_N_FIELDS] = {5, 5, 21, 3, 7, 7, 2, 42, 49, 147, 0, 1, 1, 1, 625, 1};
+    static const int D0[EXO_N_FIELDS] = {0, 0, 0, 0, 0, 0, 0, 0, 0, EXO_DT_F64, 0, EXO_DT_F64, EXO_DT_I32, EXO_DT_I32, EXO_DT_U32, 0};
+    if (field < 0 || field >= EXO_N_FIELDS) return -1;
+    *k = K0[field]; *dtype = D0[field];
+    if (field == EXO_FIELD_TREMOR_TABLE) *k = (h->cfg.precision == EXO_F32 ? h->Af.table_len : h->Ad.table_len) * h->nax;
+    return 0;
 }
 
-extern "C" int exo_get_state(ExoHandle* h, ExoStateView* out) {
-    if (!h || !out) return fail(EXO_ERR_ARG, "exo_get_state: bad arguments");
-    if (!h->have_types) return fail(EXO_ERR_STATE, "exo_get_state: env types not set yet");
-    if (h->cfg.precision == EXO_F32) fill_view(h, h->Af, out); else fill_view(h, h->Ad, out);
+extern "C" int exo_field_info(ExoHandle* h, int32_t field, int32_t* k, int32_t* dtype) {
+    if (!h || !k || !dtype) return fail(EXO_ERR_ARG, "exo_field_info: bad arguments");
+    if (!h->have_types) return fail(EXO_ERR_STATE, "exo_field_info: env types not set yet");
+    int kk, dd;
+    if (field_shape(h, field, &kk, &dd)) return fail(EXO_ERR_ARG, "exo_field_info: unknown field %d", field);
+    *k = kk; *dtype = dd;
     return 0;
+}
+
+static int field_io(ExoHandle* h, int32_t field, void* buf, int set, void* stream, const char* who) {
+    if (!h || !buf) return fail(EXO_ERR_ARG, "%s: bad arguments", who);
+    if (!h->have_types) return fail(EXO_ERR_STATE, "%s: env types not set yet", who);
+    int k, dt;
+    if (field_shape(h, field, &k, &dt)) return fail(EXO_ERR_ARG, "%s: unknown field %d", who, field);
+    CK(cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const int naxv = (h->nax + 3) / 4;
+    if (h->cfg.precision == EXO_F32) launch_field<float>(h->Af, field, k, dt, naxv, buf, set, s);
+    else launch_field<double>(h->Ad, field, k, dt, naxv, buf, set, s);
+    h->launches += 1;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int exo_get_field(ExoHandle* h, int32_t field, void* out_dev, void* stream) {
+    return field_io(h, field, out_dev, 0, stream, "exo_get_field");
+}
+extern "C" int exo_set_field(ExoHandle* h, int32_t field, const void* in_dev, void* stream) {
+    return field_io(h, field, const_cast<void*>(in_dev), 1, stream, "exo_set_field");
 }
 
 extern "C" int exo_stats(ExoHandle* h, double* out_dev, int32_t reset, void* stream) {

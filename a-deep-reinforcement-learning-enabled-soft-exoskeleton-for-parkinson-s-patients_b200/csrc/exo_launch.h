@@ -7,10 +7,16 @@ namespace exo {
 template <typename R>
 void launch_step(const EnvArrays<R>& A, const ChainConst<R>& C, const StepConst<R>& K, int nax, bool info_on,
                  const float* actions, float* obs, R* reward, uint8_t* done, const InfoPtrs<R>& ip, cudaStream_t s);
+// One kernel: draws, tremor table, parameters, first observation and propagator. K.list_parity >= 0 resets the envs
+// of that finished-list (auto-reset), otherwise the envs selected by mask (NULL: all). Returns a cudaError_t.
 template <typename R>
-void launch_reset(const EnvArrays<R>& A, const ChainConst<R>& C, const ResetConst& K, const StepConst<R>& SK, int nax,
-                  const uint8_t* mask, float* obs, cudaStream_t s);   // 2 kernels: reset + propagator
+int launch_reset(const EnvArrays<R>& A, const ChainConst<R>& C, const ResetConst& K, int nax, int n_sm,
+                 const uint8_t* mask, float* obs, cudaStream_t s);
 template <typename R>
 void launch_fk(const R* theta, R* p, int n, R L1, R L2, cudaStream_t s);
-void launch_seed(uint32_t* mt, int n, int stride, const uint32_t* seeds, int ctor_draw, cudaStream_t s);
+// gather (set = 0) / scatter (set = 1) one field between the resident layout and an env-major [n, k] buffer;
+// dtype: 0 real, 1 f64, 2 i32, 3 u32
+template <typename R>
+void launch_field(const EnvArrays<R>& A, int field, int k, int dtype, int naxv, void* buf, int set, cudaStream_t s);
+void launch_seed(uint32_t* mt, int n, const uint32_t* seeds, cudaStream_t s);
 }  // namespace exo

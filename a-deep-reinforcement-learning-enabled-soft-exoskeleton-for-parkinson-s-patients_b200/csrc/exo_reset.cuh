@@ -1,15 +1,19 @@
-// exo_reset.cuh — episode (re)initialisation kernels: everything ExoskeletonEnv_train.reset() does
-// (Exoskeleton_env.py:473-478 -> initialize_movement :193-254) for the envs selected by a mask.
+// exo_reset.cuh — episode (re)initialisation: everything ExoskeletonEnv_train.reset() does
+// (Exoskeleton_env.py:473-478 -> initialize_movement :193-254), ONE WARP PER ENVIRONMENT, one kernel.
 //
-//   exo_seed_kernel        np.random.seed(s) per env: MT19937 init_genrand (Utilities/seed_setting_.py:9)
-//   exo_reset_kernel       numpy legacy-RNG draws in the reference's order, tremor table synthesis
-//                          (Utilities/generate_parkinson_tremor.py:5-73), symmetric matrix noise
-//                          (Utilities/domain_randomization_anatomical_matrices.py:4-27), actuator end shifts
-//                          (Exoskeleton_sim_pybullet.py:98-107), force-range scale (:216-217), counts = 2 (:220),
-//                          position vectors (:236-250) and the first observation (:252)
-//   exo_propagator_kernel  one warp per env: G = [I 0] * int_0^dt e^{As} ds * [0; I^-1] (fp64, scaling and
-//                          squaring), so that each later step replaces scipy's RK45 (calculate_joint_angles.py:5-22,
-//                          zero initial state every step, env:141,409) by q(dt) = G * T.
+//   exo_seed_kernel    np.random.seed(s) per env: MT19937 init_genrand (Utilities/seed_setting_.py:9)
+//   exo_reset_kernel   for each env of the work list (finished envs compacted by the step kernel, or a mask):
+//     1. the env's MT19937 key is streamed into shared memory and twisted warp-parallel; the 416 + 9 L 32-bit
+//        outputs the episode consumes are tempered into a shared-memory stream, so every later draw is a
+//        random-access read and the L-long loops run one sample per lane;
+//     2. numpy legacy-RNG draws in the reference's order (a17): tremor magnitude, f1, f2, noise[L], per axis a1, a2,
+//        sign[L]; tremor table synthesis (Utilities/generate_parkinson_tremor.py:5-73); symmetric matrix noise
+//        (Utilities/domain_randomization_anatomical_matrices.py:4-27); actuator end shifts
+//        (Exoskeleton_sim_pybullet.py:98-107); force-range scale (:216-217); counts = 2 (:220); position vectors
+//        (:236-250) and the first observation (:252);
+//     3. the propagator G = [I 0] * int_0^dt e^{As} ds * [0; I^-1] (fp64 Taylor + scaling and squaring in shared
+//        memory), so that each later step replaces scipy's RK45 (calculate_joint_angles.py:5-22, zero initial
+//        state every step, env:141,409) by q(dt) = G * T.
 //
 // All random draws are fp64 and bit-identical to numpy's RandomState: random_sample = (a>>5, b>>6)/2^53 from two
 // 32-bit MT outputs, uniform = lo + (hi-lo)*u, choice([-1,1]) = one 32-bit output & 1. Arithmetic that feeds stored
@@ -22,72 +26,55 @@ namespace exo {
 
 #define MT_N 624
 #define MT_M 397
+#define RST_WARPS 4
+#define PD 14
 
-// In-place twist of one env's 624-word key (global memory, stride-N layout -> coalesced across the warp).
-__device__ inline void mt_twist(uint32_t* s, int stride) {
-#define MT_AT(i) s[(size_t)(i) * stride]
-    uint32_t cur = MT_AT(0);
-    uint32_t y, nxt;
-    int i = 0;
-    uint32_t first_new = 0;
-    for (; i < MT_N - MT_M; i++) {
-        nxt = MT_AT(i + 1);
-        y = (cur & 0x80000000u) | (nxt & 0x7fffffffu);
-        const uint32_t v = MT_AT(i + MT_M) ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
-        MT_AT(i) = v;
-        if (i == 0) first_new = v;
-        cur = nxt;
-    }
-    for (; i < MT_N - 1; i++) {
-        nxt = MT_AT(i + 1);
-        y = (cur & 0x80000000u) | (nxt & 0x7fffffffu);
-        MT_AT(i) = MT_AT(i + (MT_M - MT_N)) ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
-        cur = nxt;
-    }
-    y = (cur & 0x80000000u) | (first_new & 0x7fffffffu);
-    MT_AT(MT_N - 1) = MT_AT(MT_M - 1) ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
-#undef MT_AT
+__device__ __forceinline__ uint32_t mt_temper(uint32_t y) {
+    y ^= (y >> 11);
+    y ^= (y << 7) & 0x9d2c5680u;
+    y ^= (y << 15) & 0xefc60000u;
+    y ^= (y >> 18);
+    return y;
 }
 
-struct Mt {
-    uint32_t* s;
-    int stride, pos;
-    __device__ __forceinline__ uint32_t next32() {
-        if (pos >= MT_N) { mt_twist(s, stride); pos = 0; }
-        uint32_t y = s[(size_t)pos * stride];
-        pos++;
-        y ^= (y >> 11);
-        y ^= (y << 7) & 0x9d2c5680u;
-        y ^= (y << 15) & 0xefc60000u;
-        y ^= (y >> 18);
-        return y;
-    }
-    __device__ __forceinline__ double sample() {                  // legacy random_sample / rand()
-        const uint32_t a = next32() >> 5, b = next32() >> 6;
-        return __ddiv_rn(__dadd_rn(__dmul_rn((double)a, 67108864.0), (double)b), 9007199254740992.0);
-    }
-    __device__ __forceinline__ double uniform(double lo, double hi) {  // lo + (hi-lo)*u
-        return __dadd_rn(lo, __dmul_rn(__dsub_rn(hi, lo), sample()));
-    }
-    __device__ __forceinline__ void skip(int nwords) {            // consume outputs without using them
-        while (nwords > 0) {
-            if (pos >= MT_N) { mt_twist(s, stride); pos = 0; }
-            const int take = min(nwords, MT_N - pos);
-            pos += take; nwords -= take;
+// Warp-parallel in-place twist of a 624-word key in shared memory. new[i] depends on old[i], old[i+1] and
+// (i < 227) old[i+397] / (i >= 227) new[i-227], so batches of 32 consecutive words are independent as long as the
+// batch reads complete before its writes; word 623 uses new[0].
+__device__ __forceinline__ void mt_twist_warp(uint32_t* s, int lane) {
+    for (int b = 0; b < MT_N; b += 32) {
+        const int i = b + lane;
+        uint32_t v = 0;
+        if (i < MT_N) {
+            const uint32_t cur = s[i], nxt = s[i + 1 < MT_N ? i + 1 : 0];
+            const uint32_t y = (cur & 0x80000000u) | (nxt & 0x7fffffffu);
+            const int m = i + MT_M < MT_N ? i + MT_M : i + MT_M - MT_N;
+            v = s[m] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
         }
+        __syncwarp();
+        if (i < MT_N) s[i] = v;
+        __syncwarp();
     }
-};
+}
 
-static __global__ void exo_seed_kernel(uint32_t* mt, int n, int stride, const uint32_t* __restrict__ seeds, int ctor_draw) {
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= n) return;
-    uint32_t* s = mt + e;
-    uint32_t v = seeds[e];
-    s[0] = v;
-    for (int i = 1; i < MT_N; i++) { v = 1812433253u * (v ^ (v >> 30)) + (uint32_t)i; s[(size_t)i * stride] = v; }
-    Mt g{s, stride, MT_N};
-    if (ctor_draw) (void)g.sample();                              // Exoskeleton_env.py:70
-    s[(size_t)MT_N * stride] = (uint32_t)g.pos;
+// 32 envs per warp: each lane runs init_genrand for its env, 32 words at a time, through a shared tile so the
+// env-major key array is written with coalesced 128 B rows.
+static __global__ void __launch_bounds__(32) exo_seed_kernel(uint32_t* mt, int n, const uint32_t* __restrict__ seeds) {
+    __shared__ uint32_t tile[32][33];
+    const int lane = threadIdx.x, base = blockIdx.x * 32, e = base + lane;
+    uint32_t v = e < n ? seeds[e] : 0u;
+    for (int chunk = 0; chunk < (MT_N + 31) / 32; chunk++) {
+        for (int w = 0; w < 32; w++) {
+            const int i = chunk * 32 + w;
+            if (i > 0) v = 1812433253u * (v ^ (v >> 30)) + (uint32_t)i;
+            tile[lane][w] = v;
+        }
+        __syncwarp();
+        const int i = chunk * 32 + lane;
+        for (int r = 0; r < 32 && base + r < n; r++)
+            if (i < MT_N) mt[(size_t)(base + r) * EXO_MT_PITCH + i] = tile[r][lane];
+        __syncwarp();
+    }
+    if (e < n) mt[(size_t)e * EXO_MT_PITCH + MT_N] = MT_N;            // position: the first draw twists
 }
 
 // seven_by_seven (Utilities/differential_eq_matrices.py:41-69)
@@ -105,142 +92,25 @@ static __constant__ double c_S7[49] = {
     0, 0, 0, 0, 0.291, -0.099, 2.920};
 static __constant__ double c_JMAX[7] = {2.5, 5, 10, 5, 5, 0.5, 0.5};    // generate_parkinson_tremor.py:59
 
-template <typename R, int NAX>
-__global__ void __launch_bounds__(64)
-exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, StepConst<R> SK, const uint8_t* __restrict__ mask,
-                 float* __restrict__ obs) {
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= S.n) return;
-    if (mask != nullptr && mask[e] == 0) return;
-    const int st = S.stride;
-    const int meta = S.meta[e];
-    const int mid = (meta >> 8) & 0xff;
-    const int L = S.motion_len[mid];
-    Mt g{S.mt + e, st, (int)S.mt[(size_t)MT_N * st + e]};
-
-    // ---- tremor magnitude (:198-199)
-    const double mag = __dadd_rn(K.amp_lo, __dmul_rn(g.sample(), __dsub_rn(K.amp_hi, K.amp_lo)));
-    S.mag[e] = mag;
-    // ---- generate_tremor_frequency (tremor:5-21): f1, f2, white noise, time base, the two harmonics
-    const double f1 = g.uniform(K.f1_lo, K.f1_hi);
-    const double f2 = g.uniform(K.f2_lo, K.f2_hi);
-    const double stop = __dmul_rn((double)L, K.dt), tstep = __ddiv_rn(stop, (double)(L - 1));   // np.linspace(0, L*dt, L)
-    const double w1c = __dmul_rn(__dmul_rn(2.0, 3.141592653589793), f1), w2c = __dmul_rn(__dmul_rn(2.0, 3.141592653589793), f2);
-    for (int k = 0; k < L; k++) {
-        S.sc_noise[(size_t)k * st + e] = __dmul_rn(g.sample(), 0.001);
-        const double t = (k == L - 1) ? stop : __dmul_rn((double)k, tstep);
-        S.sc_w1[(size_t)k * st + e] = sin(__dmul_rn(w1c, t));
-        S.sc_w2[(size_t)k * st + e] = sin(__dmul_rn(w2c, t));
-    }
-    // ---- per axis: amplitudes (tremor:24-28), min/max of the raw wave (tremor:64), per-sample sign bits (tremor:70)
-    double a1[7], a2[7], mn[7], mx[7];
-#pragma unroll
-    for (int j = 0; j < 7; j++) {
-        a1[j] = pow(10.0, __ddiv_rn(g.uniform(-5.0, 0.0), 20.0));
-        a2[j] = pow(10.0, __ddiv_rn(g.uniform(-20.0, -10.0), 20.0));
-        if (j < NAX && ((meta >> j) & 1)) {
-            uint32_t w = 0;
-            for (int k = 0; k < L; k++) {
-                w |= (g.next32() & 1u) << (k & 31);
-                if ((k & 31) == 31 || k == L - 1) { S.sc_sign[(size_t)(j * EXO_SIGN_WORDS + (k >> 5)) * st + e] = w; w = 0; }
-            }
-        } else {
-            g.skip(L);
-        }
-        mn[j] = INFINITY; mx[j] = -INFINITY;
-    }
-    for (int k = 0; k < L; k++) {
-        const double w1 = S.sc_w1[(size_t)k * st + e], w2 = S.sc_w2[(size_t)k * st + e], nz = S.sc_noise[(size_t)k * st + e];
-#pragma unroll
-        for (int j = 0; j < NAX; j++) {
-            const double gk = __dadd_rn(__dadd_rn(__dmul_rn(a1[j], w1), __dmul_rn(a2[j], w2)), nz);
-            mn[j] = fmin(mn[j], gk); mx[j] = fmax(mx[j], gk);
-        }
-    }
-    for (int k = 0; k < L; k++) {
-        const double w1 = S.sc_w1[(size_t)k * st + e], w2 = S.sc_w2[(size_t)k * st + e], nz = S.sc_noise[(size_t)k * st + e];
-#pragma unroll
-        for (int j = 0; j < NAX; j++) {
-            double v = 0.0;
-            if ((meta >> j) & 1) {
-                const double gk = __dadd_rn(__dadd_rn(__dmul_rn(a1[j], w1), __dmul_rn(a2[j], w2)), nz);
-                const double jm = __dmul_rn(c_JMAX[j], mag);
-                v = __dmul_rn(__dadd_rn(-1.0, __ddiv_rn(__dmul_rn(2.0, __dsub_rn(gk, mn[j])), __dsub_rn(mx[j], mn[j]))), jm);
-                if (isnan(v) || isinf(v)) v = 0.0;                                                  // tremor:67
-                const uint32_t w = S.sc_sign[(size_t)(j * EXO_SIGN_WORDS + (k >> 5)) * st + e];
-                if (((w >> (k & 31)) & 1u) == 0) v = -v;
-            }
-            S.tt[((size_t)k * NAX + j) * st + e] = (R)v;
-        }
-    }
-    // ---- add_symmetric_noise on I, D, S (:208-210): raw draws first, then (n + n^T)/2 pairwise in place
-    for (int m = 0; m < 3; m++) {
-        const double* M0 = (m == 0) ? c_I7 : (m == 1 ? c_D7 : c_S7);
-        double* out = S.IDS + (size_t)(m * 49) * st + e;
-        for (int i = 0; i < 49; i++) out[(size_t)i * st] = g.uniform(-K.noise_frac, K.noise_frac);
-        for (int i = 0; i < 7; i++)
-            for (int j = i; j < 7; j++) {
-                const double nij = out[(size_t)(i * 7 + j) * st], nji = out[(size_t)(j * 7 + i) * st];
-                const double sij = __ddiv_rn(__dadd_rn(nij, nji), 2.0), sji = __ddiv_rn(__dadd_rn(nji, nij), 2.0);
-                out[(size_t)(i * 7 + j) * st] = __dadd_rn(M0[i * 7 + j], __dmul_rn(sij, M0[i * 7 + j]));
-                out[(size_t)(j * 7 + i) * st] = __dadd_rn(M0[j * 7 + i], __dmul_rn(sji, M0[j * 7 + i]));
-            }
-    }
-    // ---- actuator end shifts (sim:98-107) and force range scale (:216-217)
-    for (int i = 0; i < 42; i++) S.shift[(size_t)i * st + e] = (R)g.uniform(-K.shift_range, K.shift_range);
-    const double lo = __dsub_rn(1.0, K.act_range), hi = __dadd_rn(1.0, K.act_range);
-    const double fsh = __dmul_rn(K.fmax_sh0, g.uniform(lo, hi));
-    const double fel = __dmul_rn(K.fmax_el0, g.uniform(lo, hi));
-    S.fmax[e] = (R)fsh; S.fmax[st + e] = (R)fel;
-    S.mt[(size_t)MT_N * st + e] = (uint32_t)g.pos;
-
-    // ---- counts = 2 (:220); two position reads of the unchanged link-state cache (:230-250)
-    S.counts[e] = 2;
-    S.ret[e] = R(0);
-    R qs[5];
-#pragma unroll
-    for (int j = 0; j < 5; j++) qs[j] = K.lag ? S.qlag[j * st + e] : S.q[j * st + e];
-    ChainPose<R> P;
-    chain_fk(C, qs, P);
-    R el_old[3];
-#pragma unroll
-    for (int k = 0; k < 3; k++) { el_old[k] = S.elref[k * st + e]; S.elref[k * st + e] = P.elref[k]; }
-    float* o = obs ? obs + (size_t)e * 80 : nullptr;
-#pragma unroll
-    for (int i = 0; i < 7; i++) {
-        R a2[3];
-        if (i < 2) affine(P.R4, P.p4, C.off_alk[i], a2);
-        else affine(P.R2, P.p2, C.off_hum[i], a2);
-#pragma unroll
-        for (int k = 0; k < 3; k++) {
-            a2[k] += (R)S.shift[(size_t)((2 * i + 1) * 3 + k) * st + e];
-            const R prev = a2[k] - (i < 2 ? el_old[k] : C.sh_ref[k]);      // stale elbow ref on the first read (:237)
-            const R cur = a2[k] - (i < 2 ? P.elref[k] : C.sh_ref[k]);      // refreshed before the second (:238,249)
-            S.posvec[(size_t)(i * 3 + k) * st + e] = cur;
-            if (o) { o[26 + i * 3 + k] = (float)prev; o[47 + i * 3 + k] = (float)cur; }
-        }
-    }
-    if (o) {
-        for (int i = 0; i < 14; i++) o[i] = 0.0f;                          // force history zeroed (:195)
-        const R nrm[4] = {R(10), R(10), R(10), R(5)};
-        for (int h = 0; h < 3; h++)
-            for (int j = 0; j < 4; j++) o[14 + h * 4 + j] = (float)(S.tt[((size_t)h * NAX + j) * st + e] / nrm[j]);
-        for (int k = 0; k < 3; k++) {
-            o[68 + k] = (float)C.sh_ref[k]; o[71 + k] = (float)P.elref[k];
-            o[74 + k] = (float)C.sh_ref[k]; o[77 + k] = (float)P.elref[k];
-        }
-    }
-    (void)SK;
+// legacy random_sample from two consecutive 32-bit outputs of the stream
+__device__ __forceinline__ double rs_sample(const uint32_t* strm, int idx) {
+    const uint32_t a = strm[idx] >> 5, b = strm[idx + 1] >> 6;
+    return __ddiv_rn(__dadd_rn(__dmul_rn((double)a, 67108864.0), (double)b), 9007199254740992.0);
+}
+__device__ __forceinline__ double rs_uniform(const uint32_t* strm, int idx, double lo, double hi) {   // lo + (hi-lo)*u
+    return __dadd_rn(lo, __dmul_rn(__dsub_rn(hi, lo), rs_sample(strm, idx)));
 }
 
-// ---------------------------------------------------------------------------------------------------------
-// Propagator: one warp per env, matrices in shared memory (fp64).
-//   A = [[0, 1], [-I^-1 S, -I^-1 D]] (14x14),  B = [0; I^-1] (14x7)
-//   E = e^{A h}, Phi = sum_k (A h)^k/(k+1)!  (Taylor, degree 14, h = dt/2^s with ||A h||_inf <= 1/4)
-//   F = h * Phi * B, then s times: F <- (E + 1) F ; E <- E E.  G = rows 0..6 of F.
-// ---------------------------------------------------------------------------------------------------------
-#define PW_WARPS 4
-#define PD 14
+__device__ __forceinline__ double warp_min(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
 
 __device__ __forceinline__ void warp_matmul14(const double* A, const double* B, double* Cm, int ncol, int lane, double scale) {
     // Cm[14 x ncol] = scale * A[14x14] * B[14 x ncol]
@@ -253,16 +123,15 @@ __device__ __forceinline__ void warp_matmul14(const double* A, const double* B, 
     }
 }
 
-template <typename R>
-__global__ void __launch_bounds__(PW_WARPS * 32)
-exo_propagator_kernel(EnvArrays<R> S, double dt, const uint8_t* __restrict__ mask) {
-    __shared__ double sm[PW_WARPS][5 * PD * PD + 2 * 49 + 8];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int e = blockIdx.x * PW_WARPS + warp;
-    if (e >= S.n) return;
-    if (mask != nullptr && mask[e] == 0) return;
-    const int st = S.stride;
-    double* Ah = sm[warp];
+// ---------------------------------------------------------------------------------------------------------
+// Propagator (one warp, matrices in shared memory, fp64).
+//   A = [[0, 1], [-I^-1 S, -I^-1 D]] (14x14),  B = [0; I^-1] (14x7)
+//   E = e^{A h}, Phi = sum_k (A h)^k/(k+1)!  (Taylor, degree 14, h = dt/2^s with ||A h||_inf <= 1/4)
+//   F = h * Phi * B, then s times: F <- (E + 1) F ; E <- E E.  G = rows 0..6 of F.
+// ids: I, D, S (3 x 49, shared). sm: scratch of 5*196 + 98 doubles. Result left in sm[3*196 .. +49] (rows 0..6 of F).
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ const double* warp_propagator(const double* ids, double* sm, double dt, int lane) {
+    double* Ah = sm;
     double* E = Ah + PD * PD;
     double* Phi = E + PD * PD;
     double* P = Phi + PD * PD;
@@ -270,7 +139,7 @@ exo_propagator_kernel(EnvArrays<R> S, double dt, const uint8_t* __restrict__ mas
     double* LU = T + PD * PD;        // 49: I, factorised in place (Gauss-Jordan -> I^-1)
     double* Iinv = LU + 49;          // 49
     // ---- I^-1 by Gauss-Jordan with partial pivoting (lane-parallel over columns of [I | 1])
-    for (int i = lane; i < 49; i += 32) { LU[i] = S.IDS[(size_t)i * st + e]; Iinv[i] = (i / 7 == i % 7) ? 1.0 : 0.0; }
+    for (int i = lane; i < 49; i += 32) { LU[i] = ids[i]; Iinv[i] = (i / 7 == i % 7) ? 1.0 : 0.0; }
     __syncwarp();
     for (int k = 0; k < 7; k++) {
         int p = k; double best = fabs(LU[k * 7 + k]);
@@ -303,11 +172,11 @@ exo_propagator_kernel(EnvArrays<R> S, double dt, const uint8_t* __restrict__ mas
         double v = 0;
         if (i < 7) v = (j == i + 7) ? 1.0 : 0.0;
         else {
-            const double* M = S.IDS + (size_t)((j < 7 ? 98 : 49)) * st + e;   // S for the q block, D for the qdot block
+            const double* M = ids + (j < 7 ? 98 : 49);   // S for the q block, D for the qdot block
             const int jj = j < 7 ? j : j - 7;
             double acc = 0;
 #pragma unroll
-            for (int k = 0; k < 7; k++) acc = fma(Iinv[(i - 7) * 7 + k], M[(size_t)(k * 7 + jj) * st], acc);
+            for (int k = 0; k < 7; k++) acc = fma(Iinv[(i - 7) * 7 + k], M[k * 7 + jj], acc);
             v = -acc;
         }
         Ah[idx] = v;
@@ -356,7 +225,199 @@ exo_propagator_kernel(EnvArrays<R> S, double dt, const uint8_t* __restrict__ mas
             __syncwarp();
         }
     }
-    for (int idx = lane; idx < 49; idx += 32) S.G[(size_t)idx * st + e] = (R)F[idx];   // rows 0..6
+    return F;
+}
+
+// Shared memory per warp (bytes): key 2496 | stream 4*(2+416+9*table_len) | waves 3*8*table_len | ids 147*8 |
+// small 64*8. The propagator scratch (5*196+98 doubles = 8624 B) aliases the stream, which is dead by then.
+__host__ __device__ inline size_t reset_stream_words(int table_len) { return (size_t)((2 + 416 + 9 * table_len + 3) & ~3); }
+__host__ __device__ inline size_t reset_smem_per_warp(int table_len) {
+    size_t strm = 4 * reset_stream_words(table_len);
+    if (strm < (5 * PD * PD + 98) * 8) strm = (5 * PD * PD + 98) * 8;
+    return 2496 + strm + 3 * 8 * (size_t)((table_len + 1) & ~1) + 148 * 8 + 160 * 8;      // multiple of 16
+}
+
+template <typename R, int NAX>
+__global__ void __launch_bounds__(RST_WARPS * 32)
+exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* __restrict__ mask, float* __restrict__ obs) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int NAXV = (NAX + 3) / 4;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int TL = (S.table_len + 1) & ~1, st = S.stride;   // wave pitch (even: keeps every region 16-byte aligned)
+    unsigned char* wsm = smem_raw + (size_t)wid * reset_smem_per_warp(S.table_len);
+    size_t strm_bytes = 4 * reset_stream_words(S.table_len);
+    if (strm_bytes < (5 * PD * PD + 98) * 8) strm_bytes = (5 * PD * PD + 98) * 8;
+    double* strm_d = reinterpret_cast<double*>(wsm);                       // stream / propagator scratch (8-aligned first)
+    uint32_t* strm = reinterpret_cast<uint32_t*>(wsm);
+    double* wav = reinterpret_cast<double*>(wsm + strm_bytes);             // [3][TL]: sin w1 t, sin w2 t, noise
+    double* ids = wav + 3 * (size_t)TL;                                    // [148]
+    double* sml = ids + 148;                                               // [160] small per-env scratch
+    uint32_t* key = reinterpret_cast<uint32_t*>(sml + 160);                // [624]
+    // sml layout: 0..13 a1[7],a2[7] | 16..57 shift[42] | 58,59 fmax | 64..75 first three table rows [3][4] | 80..159 obs row (as float)
+    float* s_ob = reinterpret_cast<float*>(sml + 80);
+
+    const int total_warps = gridDim.x * RST_WARPS;
+    const int gw = blockIdx.x * RST_WARPS + wid;
+    const int* list = nullptr;
+    int work = S.n;
+    if (K.list_parity >= 0) { work = S.fin_count[K.list_parity]; list = S.fin_list + (size_t)K.list_parity * st; }
+
+    for (int wi = gw; wi < work; wi += total_warps) {
+        const int e = list ? list[wi] : wi;
+        if (!list && mask != nullptr && mask[e] == 0) continue;
+        const int meta = S.meta[e];
+        const int mid = (meta >> 8) & 0xff;
+        const int L = S.motion_len[mid];
+        // ---- 1. MT19937: key -> shared, generate the episode's outputs into the stream
+        uint32_t* gkey = S.mt + (size_t)e * EXO_MT_PITCH;
+        for (int i = lane; i < MT_N; i += 32) key[i] = gkey[i];
+        int pos = (int)gkey[MT_N];
+        __syncwarp();
+        const int W = K.ctor_skip + 416 + 9 * L;
+        for (int have = 0; have < W;) {
+            if (pos >= MT_N) { mt_twist_warp(key, lane); pos = 0; }
+            const int take = min(MT_N - pos, W - have);
+            for (int i = lane; i < take; i += 32) strm[have + i] = mt_temper(key[pos + i]);
+            have += take; pos += take;
+        }
+        __syncwarp();
+        for (int i = lane; i < MT_N; i += 32) gkey[i] = key[i];
+        if (lane == 0) gkey[MT_N] = (uint32_t)pos;
+        // stream offsets (draw order of initialize_movement)
+        const int o_mag = K.ctor_skip, o_f1 = o_mag + 2, o_f2 = o_mag + 4, o_noise = o_mag + 6;
+        const int o_axis = o_noise + 2 * L;                     // per axis: a1 (2), a2 (2), sign (L)
+        const int o_mat = o_axis + 7 * (4 + L);                 // I, D, S: 49 x 2 each
+        const int o_shift = o_mat + 294, o_fsh = o_shift + 84, o_fel = o_fsh + 2;
+        // ---- tremor magnitude (:198-199)
+        const double mag = __dadd_rn(K.amp_lo, __dmul_rn(rs_sample(strm, o_mag), __dsub_rn(K.amp_hi, K.amp_lo)));
+        // ---- generate_tremor_frequency (tremor:5-21): f1, f2, white noise, time base, the two harmonics
+        const double f1 = rs_uniform(strm, o_f1, K.f1_lo, K.f1_hi);
+        const double f2 = rs_uniform(strm, o_f2, K.f2_lo, K.f2_hi);
+        const double stop = __dmul_rn((double)L, K.dt), tstep = __ddiv_rn(stop, (double)(L - 1));   // np.linspace(0, L*dt, L)
+        const double w1c = __dmul_rn(__dmul_rn(2.0, 3.141592653589793), f1), w2c = __dmul_rn(__dmul_rn(2.0, 3.141592653589793), f2);
+        for (int k = lane; k < L; k += 32) {
+            const double t = (k == L - 1) ? stop : __dmul_rn((double)k, tstep);
+            wav[k] = sin(__dmul_rn(w1c, t));
+            wav[TL + k] = sin(__dmul_rn(w2c, t));
+            wav[2 * TL + k] = __dmul_rn(rs_sample(strm, o_noise + 2 * k), 0.001);
+        }
+        // ---- per-axis amplitudes (tremor:24-28): lanes 0..13 take one pow each
+        if (lane < 14) {
+            const int j = lane >> 1, o = o_axis + j * (4 + L) + 2 * (lane & 1);
+            const double db = (lane & 1) ? rs_uniform(strm, o, -20.0, -10.0) : rs_uniform(strm, o, -5.0, 0.0);
+            sml[(lane & 1) * 7 + j] = pow(10.0, __ddiv_rn(db, 20.0));
+        }
+        // ---- add_symmetric_noise on I, D, S (:208-210): (n + n^T)/2, M + n*M
+        for (int idx = lane; idx < 147; idx += 32) {
+            const int m = idx / 49, ij = idx - m * 49, i = ij / 7, j = ij - i * 7;
+            const double* M0 = (m == 0) ? c_I7 : (m == 1 ? c_D7 : c_S7);
+            const double nij = rs_uniform(strm, o_mat + m * 98 + 2 * (i * 7 + j), -K.noise_frac, K.noise_frac);
+            const double nji = rs_uniform(strm, o_mat + m * 98 + 2 * (j * 7 + i), -K.noise_frac, K.noise_frac);
+            const double sij = __ddiv_rn(__dadd_rn(nij, nji), 2.0);
+            const double v = __dadd_rn(M0[ij], __dmul_rn(sij, M0[ij]));
+            ids[idx] = v;
+            S.IDS[(size_t)e * EXO_IDS_PITCH + idx] = v;
+        }
+        // ---- actuator end shifts (sim:98-107) and force range scale (:216-217)
+        for (int i = lane; i < 42; i += 32) sml[16 + i] = rs_uniform(strm, o_shift + 2 * i, -K.shift_range, K.shift_range);
+        if (lane < 2) {
+            const double lo = __dsub_rn(1.0, K.act_range), hi = __dadd_rn(1.0, K.act_range);
+            sml[58 + lane] = __dmul_rn(lane == 0 ? K.fmax_sh0 : K.fmax_el0, rs_uniform(strm, lane == 0 ? o_fsh : o_fel, lo, hi));
+        }
+        __syncwarp();
+        // ---- min/max of the raw wave per axis (tremor:64), then the normalised, sign-flipped table (tremor:64-70)
+        double a1[NAX], a2[NAX], mn[NAX], mx[NAX];
+#pragma unroll
+        for (int j = 0; j < NAX; j++) { a1[j] = sml[j]; a2[j] = sml[7 + j]; mn[j] = INFINITY; mx[j] = -INFINITY; }
+        for (int k = lane; k < L; k += 32) {
+            const double w1 = wav[k], w2 = wav[TL + k], nz = wav[2 * TL + k];
+#pragma unroll
+            for (int j = 0; j < NAX; j++) {
+                const double gk = __dadd_rn(__dadd_rn(__dmul_rn(a1[j], w1), __dmul_rn(a2[j], w2)), nz);
+                mn[j] = fmin(mn[j], gk); mx[j] = fmax(mx[j], gk);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < NAX; j++) { mn[j] = warp_min(mn[j]); mx[j] = warp_max(mx[j]); }
+        for (int k = lane; k < L; k += 32) {
+            const double w1 = wav[k], w2 = wav[TL + k], nz = wav[2 * TL + k];
+            R row[4 * NAXV];
+#pragma unroll
+            for (int j = 0; j < 4 * NAXV; j++) {
+                double v = 0.0;
+                if (j < NAX && ((meta >> j) & 1)) {
+                    const double gk = __dadd_rn(__dadd_rn(__dmul_rn(a1[j], w1), __dmul_rn(a2[j], w2)), nz);
+                    const double jm = __dmul_rn(c_JMAX[j], mag);
+                    v = __dmul_rn(__dadd_rn(-1.0, __ddiv_rn(__dmul_rn(2.0, __dsub_rn(gk, mn[j])), __dsub_rn(mx[j], mn[j]))), jm);
+                    if (isnan(v) || isinf(v)) v = 0.0;                                                  // tremor:67
+                    if ((strm[o_axis + j * (4 + L) + 4 + k] & 1u) == 0) v = -v;                         // choice([-1, 1]) (tremor:70)
+                }
+                row[j] = (R)v;
+            }
+#pragma unroll
+            for (int h = 0; h < NAXV; h++) st4(S.tt + ((size_t)k * st + e) * NAXV + h, row + 4 * h);
+            if (k < 3) {
+#pragma unroll
+                for (int j = 0; j < 4; j++) sml[64 + k * 4 + j] = (double)row[j];
+            }
+        }
+        // ---- per-episode parameter record: 42 shifts + 2 force maxima, one 16-byte vector per lane
+        if (lane < NV_EP) {
+            R pv[4];
+#pragma unroll
+            for (int c4 = 0; c4 < 4; c4++) { const int w = lane * 4 + c4; pv[c4] = (R)(w < 42 ? sml[16 + w] : sml[58 + (w - 42)]); }
+            st4(S.ep + (size_t)lane * st + e, pv);
+        }
+        if (lane == 0) { S.mag[e] = mag; S.counts[e] = 2; S.ret[e] = R(0); }     // counts = 2 (:220)
+        __syncwarp();
+        // ---- two position reads of the unchanged link-state cache (:230-250) and the first observation (:252);
+        //      every lane evaluates the (identical) chain, lane 0 stores
+        {
+            R qs[5];
+#pragma unroll
+            for (int j = 0; j < 5; j++) qs[j] = *exo_word(S.state, (K.lag ? W_QLAG : W_Q) + j, e, st);
+            ChainPose<R> P;
+            chain_fk(C, qs, P);
+            R el_old[3];
+#pragma unroll
+            for (int k = 0; k < 3; k++) el_old[k] = *exo_word(S.state, W_ELREF + k, e, st);
+            __syncwarp();
+            if (lane == 0) {
+#pragma unroll
+                for (int k = 0; k < 3; k++) *exo_word(S.state, W_ELREF + k, e, st) = P.elref[k];
+#pragma unroll
+                for (int i = 0; i < 7; i++) {
+                    R a2[3];
+                    if (i < 2) affine(P.R4, P.p4, C.off_alk[i], a2);
+                    else affine(P.R2, P.p2, C.off_hum[i], a2);
+#pragma unroll
+                    for (int k = 0; k < 3; k++) {
+                        a2[k] += (R)sml[16 + (2 * i + 1) * 3 + k];
+                        const R prev = a2[k] - (i < 2 ? el_old[k] : C.sh_ref[k]);      // stale elbow ref on the first read (:237)
+                        const R cur = a2[k] - (i < 2 ? P.elref[k] : C.sh_ref[k]);      // refreshed before the second (:238,249)
+                        *exo_word(S.state, W_POSVEC + i * 3 + k, e, st) = cur;
+                        s_ob[26 + i * 3 + k] = (float)prev; s_ob[47 + i * 3 + k] = (float)cur;
+                    }
+                }
+                for (int i = 0; i < 14; i++) s_ob[i] = 0.0f;                          // force history zeroed (:195)
+                const R nrm[4] = {R(10), R(10), R(10), R(5)};
+                for (int h = 0; h < 3; h++)
+                    for (int j = 0; j < 4; j++) s_ob[14 + h * 4 + j] = (float)((R)sml[64 + h * 4 + j] / nrm[j]);
+                for (int k = 0; k < 3; k++) {
+                    s_ob[68 + k] = (float)C.sh_ref[k]; s_ob[71 + k] = (float)P.elref[k];
+                    s_ob[74 + k] = (float)C.sh_ref[k]; s_ob[77 + k] = (float)P.elref[k];
+                }
+            }
+            __syncwarp();
+            if (obs != nullptr && lane < 20)
+                reinterpret_cast<float4*>(obs + (size_t)e * 80)[lane] = reinterpret_cast<const float4*>(s_ob)[lane];
+        }
+        __syncwarp();
+        // ---- 3. propagator from this episode's I, D, S; scratch aliases the (now dead) stream
+        const double* F = warp_propagator(ids, strm_d, K.dt, lane);
+        for (int idx = lane; idx < 49; idx += 32) *exo_word(S.G, exo_g_word(idx / 7, idx % 7), e, st) = (R)F[idx];   // rows 0..6
+        __syncwarp();
+    }
 }
 
 }  // namespace exo

@@ -1,22 +1,40 @@
 #define REAL double
-// Instantiates the reset + propagator kernels for one arithmetic type (see exo_reset.cuh).
+// Instantiates the reset kernel for one arithmetic type (see exo_reset.cuh).
 #include "exo_launch.h"
 #include "exo_reset.cuh"
 
 namespace exo {
-template <typename R>
-void launch_reset(const EnvArrays<R>& A, const ChainConst<R>& C, const ResetConst& K, const StepConst<R>& SK, int nax,
-                  const uint8_t* mask, float* obs, cudaStream_t s) {
-    const int n = A.n;
-    if (nax == 4) exo_reset_kernel<R, 4><<<(n + 63) / 64, 64, 0, s>>>(A, C, K, SK, mask, obs);
-    else exo_reset_kernel<R, 7><<<(n + 63) / 64, 64, 0, s>>>(A, C, K, SK, mask, obs);
-    exo_propagator_kernel<R><<<(n + PW_WARPS - 1) / PW_WARPS, PW_WARPS * 32, 0, s>>>(A, K.dt, mask);
+template <typename R, int NAX>
+static int launch_reset_nax(const EnvArrays<R>& A, const ChainConst<R>& C, const ResetConst& K, int n_sm,
+                            const uint8_t* mask, float* obs, cudaStream_t s) {
+    const size_t smem = RST_WARPS * reset_smem_per_warp(A.table_len);
+    static size_t configured[64] = {0};           // per device: the attribute belongs to the device's copy of the kernel
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (smem > configured[dev & 63]) {
+        cudaError_t e = cudaFuncSetAttribute(exo_reset_kernel<R, NAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        configured[dev & 63] = smem;
+    }
+    // persistent-style grid: as many blocks as fit (shared memory bound), each warp strides over the work list
+    int per_sm = (int)((227 * 1024) / (smem + 1024));
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm > 4) per_sm = 4;
+    int grid = n_sm * per_sm;
+    if (K.list_parity < 0) { const int need = (A.n + RST_WARPS - 1) / RST_WARPS; if (need < grid) grid = need; }
+    exo_reset_kernel<R, NAX><<<grid, RST_WARPS * 32, smem, s>>>(A, C, K, mask, obs);
+    return 0;
 }
-template void launch_reset<REAL>(const EnvArrays<REAL>&, const ChainConst<REAL>&, const ResetConst&, const StepConst<REAL>&, int,
-                                 const uint8_t*, float*, cudaStream_t);
+template <typename R>
+int launch_reset(const EnvArrays<R>& A, const ChainConst<R>& C, const ResetConst& K, int nax, int n_sm,
+                 const uint8_t* mask, float* obs, cudaStream_t s) {
+    return nax == 4 ? launch_reset_nax<R, 4>(A, C, K, n_sm, mask, obs, s) : launch_reset_nax<R, 7>(A, C, K, n_sm, mask, obs, s);
+}
+template int launch_reset<REAL>(const EnvArrays<REAL>&, const ChainConst<REAL>&, const ResetConst&, int, int, const uint8_t*,
+                                float*, cudaStream_t);
 #ifdef EXO_WITH_SEED
-void launch_seed(uint32_t* mt, int n, int stride, const uint32_t* seeds, int ctor_draw, cudaStream_t s) {
-    exo_seed_kernel<<<(n + 127) / 128, 128, 0, s>>>(mt, n, stride, seeds, ctor_draw);
+void launch_seed(uint32_t* mt, int n, const uint32_t* seeds, cudaStream_t s) {
+    exo_seed_kernel<<<(n + 31) / 32, 32, 0, s>>>(mt, n, seeds);
 }
 #endif
 }  // namespace exo

@@ -8,9 +8,12 @@
 //   get_reward :341-366 | update_state_vector :487-570 | done :457
 //   + the caller-side amplitude metric of Exoskeleton_agent_train.py:158-170 (forward_kinematics x3).
 //
-// Roofline: HBM-bound. Per env-step the kernel moves ~1.3 KB (DESIGN.md "algorithmic bytes") for ~2 kflop,
-// so tensor cores are irrelevant; what matters is that every load/store below is a coalesced SoA access and
-// that the row-major [n,7] / [n,80] boundary arrays go through a shared-memory transpose.
+// Roofline: HBM-bound (1045 B of compulsory traffic per env-step for ~1.5 kflop). The kernel is a
+// single wave (65 536 envs = 13.8 warps per SM), so what matters is bytes in flight per instruction and
+// instruction count: all resident state moves as 128-bit vector loads/stores of the vector-major SoA
+// (exo_types.cuh), the row-major boundary arrays actions[n,7] / obs[n,80] are transposed per WARP through
+// shared memory (no block barrier: STS.128 into a 21-chunk pitch, LDS.128 + STG.128 out), and the fp32 build
+// uses MUFU-based reciprocal / rsqrt / exp where the stated tolerances allow.
 #pragma once
 #include "exo_types.cuh"
 
@@ -18,12 +21,42 @@ namespace exo {
 
 __device__ __forceinline__ void sincos_r(float x, float* s, float* c) { sincosf(x, s, c); }
 __device__ __forceinline__ void sincos_r(double x, double* s, double* c) { sincos(x, s, c); }
-__device__ __forceinline__ float exp_r(float x) { return expf(x); }
+__device__ __forceinline__ float exp_r(float x) { return __expf(x); }
 __device__ __forceinline__ double exp_r(double x) { return exp(x); }
 __device__ __forceinline__ float sqrt_r(float x) { return sqrtf(x); }
 __device__ __forceinline__ double sqrt_r(double x) { return sqrt(x); }
 __device__ __forceinline__ float abs_r(float x) { return fabsf(x); }
 __device__ __forceinline__ double abs_r(double x) { return fabs(x); }
+__device__ __forceinline__ float div_r(float a, float b) { return __fdividef(a, b); }
+__device__ __forceinline__ double div_r(double a, double b) { return a / b; }
+// d / sqrt(r2), the "direction cosine" cos(atan2(., .)) of sim:222-230
+__device__ __forceinline__ float dircos_r(float d, float r2) { return d * rsqrtf(r2); }
+__device__ __forceinline__ double dircos_r(double d, double r2) { return d / sqrt(r2); }
+
+__device__ __forceinline__ void ld4(const V4<float>* p, float* o) {
+    const float4 t = *reinterpret_cast<const float4*>(p);
+    o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
+}
+__device__ __forceinline__ void ld4(const V4<double>* p, double* o) {
+    const double2 a = reinterpret_cast<const double2*>(p)[0], b = reinterpret_cast<const double2*>(p)[1];
+    o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
+}
+// read-only data (per-episode parameters): non-coherent path
+__device__ __forceinline__ void ld4_ro(const V4<float>* p, float* o) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(p));
+    o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
+}
+__device__ __forceinline__ void ld4_ro(const V4<double>* p, double* o) {
+    const double2 a = __ldg(reinterpret_cast<const double2*>(p)), b = __ldg(reinterpret_cast<const double2*>(p) + 1);
+    o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
+}
+__device__ __forceinline__ void st4(V4<float>* p, const float* o) {
+    *reinterpret_cast<float4*>(p) = make_float4(o[0], o[1], o[2], o[3]);
+}
+__device__ __forceinline__ void st4(V4<double>* p, const double* o) {
+    reinterpret_cast<double2*>(p)[0] = make_double2(o[0], o[1]);
+    reinterpret_cast<double2*>(p)[1] = make_double2(o[2], o[3]);
+}
 
 // out = A * B * Rz(angle); A,B row-major 3x3
 template <typename R>
@@ -95,302 +128,375 @@ __device__ __forceinline__ void dh_end_effector(const R* th, R L1, R L2, R* p) {
     }
 }
 
-template <typename R>
-__device__ __forceinline__ R warp_sum(R v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
-
-#define EXO_OBS_PAD 81
-
 template <typename R, bool INFO, int NAX>
-__global__ void __launch_bounds__(EXO_STEP_THREADS)
+__global__ void __launch_bounds__(EXO_STEP_THREADS, (sizeof(R) == 4 && !INFO) ? EXO_STEP_MIN_BLOCKS : 4)
 exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __restrict__ actions,
                 float* __restrict__ obs, R* __restrict__ reward, uint8_t* __restrict__ done, InfoPtrs<R> info) {
-    __shared__ float s_obs[EXO_STEP_THREADS * EXO_OBS_PAD];
-    __shared__ float s_act[EXO_STEP_THREADS * 7];
-    __shared__ uint8_t s_live[EXO_STEP_THREADS];
+    constexpr int WARPS = EXO_STEP_THREADS / 32;
+    constexpr int NAXV = (NAX + 3) / 4;                               // vectors per tremor-table row
+    __shared__ __align__(16) float s_obs[WARPS][32 * EXO_OBS_PITCH];
+    __shared__ float s_act[WARPS][32 * 7];
 
-    const int tid = threadIdx.x;
-    const int base = blockIdx.x * EXO_STEP_THREADS;
-    const int e = base + tid;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int wbase = blockIdx.x * EXO_STEP_THREADS + wid * 32;     // first env of this warp
+    const int e = wbase + lane;
     const int n = S.n, st = S.stride;
+    if (blockIdx.x == 0 && tid == 0) S.fin_count[K.parity ^ 1] = 0;  // consumed by the previous step's reset
+    if (wbase >= n) return;                                          // whole warp past the end
 
-    // ---- stage this block's action rows (row-major [n,7]) through shared memory: coalesced
+    // ---- this warp's 32 action rows (row-major [n,7], contiguous) -> shared memory, coalesced
     {
-        const int lim = min(EXO_STEP_THREADS, n - base) * 7;
-        const float* src = actions + (size_t)base * 7;
-        for (int i = tid; i < lim; i += EXO_STEP_THREADS) s_act[i] = src[i];
+        const int lim = min(32, n - wbase) * 7;
+        const float* src = actions + (size_t)wbase * 7;
+        for (int i = lane; i < lim; i += 32) s_act[wid][i] = src[i];
     }
-    __syncthreads();
+    __syncwarp();
 
-    bool live = false;
+    bool live = false, fin = false;
+    int v_cross = 0, v_red = 0, v_len = 0;
+    R v_ret = 0, v_amp = 0;
+    int meta = 0, mid = 0, L = 0, c = 0;
     if (e < n) {
-        const int meta = S.meta[e];
-        const int mid = (meta >> 8) & 0xff;
-        const int L = S.motion_len[mid];
-        const int c = S.counts[e];
+        meta = S.meta[e];
+        mid = (meta >> 8) & 0xff;
+        L = S.motion_len[mid];
+        c = S.counts[e];
         live = c < L - 1;                     // an env that already reported done idles (Exoskeleton_agent_train.py:139)
         if (!live) { done[e] = 1; reward[e] = R(0); }
-        if (live) {
-            float* so = s_obs + tid * EXO_OBS_PAD;
-            const R* mo = S.motion + (size_t)mid * 5 * S.max_len;
-            // ---- transform_action (:256-266)
-            const R fm_sh = S.fmax[e], fm_el = S.fmax[st + e];
-            R F[7];
+    }
+    if (live) {
+        const R* mo = S.motion + (size_t)mid * 5 * S.max_len;
+        // ---- resident records: 12 state vectors, 11 parameter vectors, 3 table rows, G
+        R s[4 * NV_STATE], p[4 * NV_EP];
 #pragma unroll
-            for (int i = 0; i < 7; i++) F[i] = ((R(s_act[tid * 7 + i]) + R(1)) / R(2)) * (i < 2 ? fm_el : fm_sh);
-            // ---- link-state cache -> world points (getLinkState reads, sim:129-142,194-195)
-            R qb[5], qs[5];
+        for (int v = 0; v < NV_STATE; v++) ld4(S.state + (size_t)v * st + e, s + 4 * v);
 #pragma unroll
-            for (int j = 0; j < 5; j++) qb[j] = S.q[j * st + e];
-            if (K.lag) {
+        for (int v = 0; v < NV_EP; v++) ld4_ro(S.ep + (size_t)v * st + e, p + 4 * v);
+        R tm[4 * NAXV], tc[4 * NAXV], tp[4 * NAXV];                 // tremor rows c-1, c, c+1
 #pragma unroll
-                for (int j = 0; j < 5; j++) qs[j] = S.qlag[j * st + e];
+        for (int h = 0; h < NAXV; h++) {
+            ld4_ro(S.tt + ((size_t)(c - 1) * st + e) * NAXV + h, tm + 4 * h);
+            ld4_ro(S.tt + ((size_t)c * st + e) * NAXV + h, tc + 4 * h);
+            ld4_ro(S.tt + ((size_t)(c + 1) * st + e) * NAXV + h, tp + 4 * h);
+        }
+        constexpr int NGV = (INFO || NAX > 4) ? NV_G : 4;
+        R g[4 * NGV];
+#pragma unroll
+        for (int v = 0; v < NGV; v++) ld4_ro(S.G + (size_t)v * st + e, g + 4 * v);
+        const R ret0 = S.ret[e];
+
+        float ob[80];
+        // ---- transform_action (:256-266)
+        const R fm_sh = p[W_FMAX], fm_el = p[W_FMAX + 1];
+        R F[7];
+#pragma unroll
+        for (int i = 0; i < 7; i++) F[i] = ((R(s_act[wid][lane * 7 + i]) + R(1)) / R(2)) * (i < 2 ? fm_el : fm_sh);
+        // ---- link-state cache -> world points (getLinkState reads, sim:129-142,194-195)
+        R qb[5], qs[5];
+#pragma unroll
+        for (int j = 0; j < 5; j++) { qb[j] = s[W_Q + j]; qs[j] = K.lag ? s[W_QLAG + j] : qb[j]; }
+        ChainPose<R> P;
+        chain_fk(C, qs, P);
+        R el_old[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) el_old[k] = s[W_ELREF + k];
+        // previous pos_vec becomes prev_position_vectors (:385) -> obs[26:47]; new pos_vec -> obs[47:68]
+#pragma unroll
+        for (int i = 0; i < 21; i++) ob[26 + i] = (float)s[W_POSVEC + i];
+        // ---- per actuator: endpoints, force direction, pos_vec, torque (sim:207-336, env:177-187)
+        R at0 = 0, at1 = 0, at2 = 0, ty0 = 0, ty1 = 0;
+        const int order[7] = {0, 1, 2, 3, 4, 6, 5};          // summation order of :395-397 (3,4,5,7,6)
+        const int fix_of[7] = {-1, -1, 0, 1, 2, 3, 4};       // fixed slot of act_i1 for the shoulder actuators
+#pragma unroll
+        for (int oi = 0; oi < 7; oi++) {
+            const int i = order[oi];
+            R a1[3], a2[3];
+            if (i < 2) {
+                affine(P.R2, P.p2, C.off_hum[i], a1);                   // act11 / act21 ride on the humerus
+                affine(P.R4, P.p4, C.off_alk[i], a2);                   // act12 / act22 ride on the forearm
             } else {
-#pragma unroll
-                for (int j = 0; j < 5; j++) qs[j] = qb[j];
-            }
-            ChainPose<R> P;
-            chain_fk(C, qs, P);
-            R el_old[3];
-#pragma unroll
-            for (int k = 0; k < 3; k++) el_old[k] = S.elref[k * st + e];
-            // previous pos_vec becomes prev_position_vectors (:385) -> obs[26:47]; new pos_vec -> obs[47:68]
-#pragma unroll
-            for (int i = 0; i < 21; i++) so[26 + i] = (float)S.posvec[i * st + e];
-            // ---- per actuator: endpoints, force direction, pos_vec, torque (sim:207-336, env:177-187)
-            R at0 = 0, at1 = 0, at2 = 0, ty0 = 0, ty1 = 0;
-            const int order[7] = {0, 1, 2, 3, 4, 6, 5};          // summation order of :395-397 (3,4,5,7,6)
-            const int hum_of[7] = {0, 1, 2, 3, 4, 5, 6};         // off_hum slot holding: act11,act21 (origin ends) / act32..act72 (insertion ends)
-            const int fix_of[7] = {-1, -1, 0, 1, 2, 3, 4};       // fixed slot of act_i1 for the shoulder actuators
-#pragma unroll
-            for (int oi = 0; oi < 7; oi++) {
-                const int i = order[oi];
-                R a1[3], a2[3];
-                if (i < 2) {
-                    affine(P.R2, P.p2, C.off_hum[hum_of[i]], a1);           // act11 / act21 ride on the humerus
-                    affine(P.R4, P.p4, C.off_alk[i], a2);                   // act12 / act22 ride on the forearm
-                } else {
-                    a1[0] = C.fixed[fix_of[i]][0]; a1[1] = C.fixed[fix_of[i]][1]; a1[2] = C.fixed[fix_of[i]][2];
-                    affine(P.R2, P.p2, C.off_hum[hum_of[i]], a2);
-                }
-#pragma unroll
-                for (int k = 0; k < 3; k++) {
-                    a1[k] += S.shift[((2 * i) * 3 + k) * st + e];
-                    a2[k] += S.shift[((2 * i + 1) * 3 + k) * st + e];
-                }
-                R dx, dy, dz;
-                if (sizeof(R) == 8) {   // the reference's +5 shift (sim:212) only matters at fp64 resolution
-                    dx = (a2[0] + R(5)) - (a1[0] + R(5)); dy = (a2[1] + R(5)) - (a1[1] + R(5)); dz = (a2[2] + R(5)) - (a1[2] + R(5));
-                } else { dx = a2[0] - a1[0]; dy = a2[1] - a1[1]; dz = a2[2] - a1[2]; }
-                // cos(atan2(dy,dx)), cos(atan2(dx,dy)), cos(atan2(dz,dx))  (not a unit vector; reproduced as is)
-                const R rxy = sqrt_r(dx * dx + dy * dy), rxz = sqrt_r(dx * dx + dz * dz);
-                const R fx = F[i] * (rxy > R(0) ? dx / rxy : R(1));
-                const R fy = F[i] * (rxy > R(0) ? dy / rxy : R(1));
-                const R fz = F[i] * (rxz > R(0) ? dx / rxz : R(1));
-                const R* stale = (i < 2) ? el_old : C.sh_ref;               // refs cached by the previous read (sim:300-336)
-                const R* fresh = (i < 2) ? P.elref : C.sh_ref;
-                R pv[3], r[3];
-#pragma unroll
-                for (int k = 0; k < 3; k++) { pv[k] = a2[k] - stale[k]; r[k] = fresh[k] - a2[k]; }
-#pragma unroll
-                for (int k = 0; k < 3; k++) { S.posvec[(i * 3 + k) * st + e] = pv[k]; so[47 + i * 3 + k] = (float)pv[k]; }
-                const R tx = fy * r[2] - fz * r[1], ty = fz * r[0] - fx * r[2], tz = fx * r[1] - fy * r[0];   // cross(F, r) :179
-                if (i == 0) ty0 = ty;
-                else if (i == 1) ty1 = ty;
-                else { at0 += ty; at1 += tx; at2 += tz; }
-            }
-            const R at[4] = {at0, at1, at2, abs_r(ty0) - abs_r(ty1)};      // :394-400
-            // ---- tremor lookup (:403-406) and the rows the observation needs (:502-513)
-            const R* tt = S.tt;
-            R ttc[7], tv[7];
-#pragma unroll
-            for (int j = 0; j < 7; j++) {
-                ttc[j] = (j < NAX) ? tt[((size_t)c * NAX + j) * st + e] : R(0);
-                tv[j] = ttc[j] + (j < 4 ? at[j] : R(0));
-            }
-            const R nrm[4] = {R(10), R(10), R(10), R(5)};
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                so[14 + j] = (float)(tt[((size_t)(c - 1) * NAX + j) * st + e] / nrm[j]);
-                so[18 + j] = (float)(ttc[j] / nrm[j]);
-                so[22 + j] = (float)(tt[((size_t)(c + 1) * NAX + j) * st + e] / nrm[j]);
-            }
-            // ---- joint model: q(dt) = G * T from rest (:409-418); rows 0..3 drive the motors
-            const R r2d = R(57.29577951308232087679815481410517), d2r = R(0.017453292519943295769236907684886);
-            R qa[7], qt[7];
-            constexpr int ROWS = INFO ? 7 : 4;
-#pragma unroll
-            for (int i = 0; i < ROWS; i++) {
-                R acc = 0, acc2 = 0;
-#pragma unroll
-                for (int j = 0; j < 7; j++) {
-                    if (j < 4 || j < NAX) {
-                        const R g = S.G[(i * 7 + j) * st + e];
-                        acc += g * tv[j];
-                        if (INFO) acc2 += g * ttc[j];
-                    }
-                }
-                qa[i] = acc * r2d;
-                if (INFO) qt[i] = acc2 * r2d;
-            }
-            // ---- angle composition + position motors + one Bullet step (:421-433, oracle/minibullet.py)
-            const R tgt[5] = {(mo[4 * S.max_len + c] + qa[2]) * d2r, (mo[3 * S.max_len + c] + qa[0]) * d2r,
-                              (mo[2 * S.max_len + c] + qa[1]) * d2r, (mo[0 * S.max_len + c] + qa[3]) * d2r,
-                              mo[1 * S.max_len + c] * d2r};
-            int crossed = 0;
-#pragma unroll
-            for (int j = 0; j < 5; j++) {
-                R qn = qb[j] + R(0.025) * ((R(0.1) * (tgt[j] - qb[j])) / R(0.025));   // q + dt*v*, v* = kp*(target-q)/dt
-                if (qn < C.lower[j] || qn > C.upper[j]) {
-                    crossed++;
-                    if (K.limits) qn = qn < C.lower[j] ? C.lower[j] : C.upper[j];
-                }
-                S.q[j * st + e] = qn;
-                if (K.lag) S.qlag[j * st + e] = qb[j];
-            }
-#pragma unroll
-            for (int k = 0; k < 3; k++) S.elref[k * st + e] = P.elref[k];
-            // ---- reward (:268-366)
-            const R eps = R(1e-10);
-            const R m = fm_el + fm_sh;
-            int nax = 0;
-#pragma unroll
-            for (int j = 0; j < 7; j++) nax += (meta >> j) & 1;
-            const R nf = (R)nax;
-            R sum_unw = 0, sum_tor = 0, sumF = 0, smooth = 0;
-            int axis_cnt = 0, arm_red = 0;
-#pragma unroll
-            for (int j = 0; j < 7; j++) {
-                const R a = abs_r(tv[j]), b = abs_r(ttc[j]);
-                if (j < 4) {
-                    if ((meta >> j) & 1) sum_tor += (a - b) / b + R(1);
-                    else sum_unw += a;
-                }
-                const R red = (a - b) / (b + eps) * R(100);
-                if (red < R(0)) { axis_cnt++; if (j < 4) arm_red = 1; }      // nan/inf -> 0 -> not counted (:302-303)
-            }
-            R fp1[7];
-#pragma unroll
-            for (int i = 0; i < 7; i++) {
-                fp1[i] = S.fprev[i * st + e];
-                const R fp2 = S.fprev2[i * st + e];
-                const R d = F[i] - R(2) * fp1[i] + fp2;
-                smooth += d * d;
-                sumF += F[i];
-                S.fprev2[i * st + e] = fp1[i];
-                S.fprev[i * st + e] = F[i];
-            }
-            const R r_unw = exp_r(-(sum_unw / (m / R(4) / nf)) + eps) * R(0.5);
-            const R r_tor = exp_r((-sum_tor + eps) / nf) * R(0.9);
-            const R r_axis = (R)axis_cnt * R(0.5);
-            const R r_ctl = exp_r(-(sumF / (m / R(2))) + eps) * R(0.05);
-            const R r_smo = R(0.05) * exp_r(-((smooth / R(7)) / (m / R(4))) + eps);
-            const R max_reward = nf * R(0.5) + R(0.9) + R(0.05) + R(0.05) + R(0.5);
-            const R rew = (r_axis + r_tor + r_smo + r_ctl + r_unw) / max_reward;
-            reward[e] = rew;
-            // ---- counts, observation head, done (:448-457)
-            const int k1 = c + 1;
-            S.counts[e] = k1;
-#pragma unroll
-            for (int i = 0; i < 7; i++) {
-                const R f0 = i < 2 ? K.fmax_el0 : K.fmax_sh0;
-                so[i] = (c >= 3) ? (float)(fp1[i] / f0) : 0.0f;       // forces[k-2]; the history is zeroed at reset (:195)
-                so[7 + i] = (float)(F[i] / f0);                       // forces[k-1]
+                a1[0] = C.fixed[fix_of[i]][0]; a1[1] = C.fixed[fix_of[i]][1]; a1[2] = C.fixed[fix_of[i]][2];
+                affine(P.R2, P.p2, C.off_hum[i], a2);
             }
 #pragma unroll
             for (int k = 0; k < 3; k++) {
-                so[68 + k] = (float)C.sh_ref[k]; so[71 + k] = (float)el_old[k];     // ref_prev (:383)
-                so[74 + k] = (float)C.sh_ref[k]; so[77 + k] = (float)P.elref[k];    // ref (:387)
+                a1[k] += p[W_SHIFT + (2 * i) * 3 + k];
+                a2[k] += p[W_SHIFT + (2 * i + 1) * 3 + k];
             }
-            const bool dn = k1 >= L - 1;
-            done[e] = dn ? 1 : 0;
-            // ---- episode statistics (device-side; all-reduced over NCCL by the host)
-            const R ret = S.ret[e] + rew;
-            S.ret[e] = dn ? R(0) : ret;
-            R amp = 0;
-            if (INFO || K.metrics) {
-                if (INFO) {
-                    // Exoskeleton_agent_train.py:158-170 with return_original_joint_angles at the incremented counts
-                    R b[7] = {mo[2 * S.max_len + k1] * d2r, mo[3 * S.max_len + k1] * d2r, mo[4 * S.max_len + k1] * d2r,
-                              mo[0 * S.max_len + k1] * d2r, mo[1 * S.max_len + k1] * d2r, R(0), R(0)};
-                    R th[7], p0[3], p1[3], p2[3];
-                    dh_end_effector(b, K.L1, K.L2, p0);
+            R dx, dy, dz;
+            if (sizeof(R) == 8) {   // the reference's +5 shift (sim:212) only matters at fp64 resolution
+                dx = (a2[0] + R(5)) - (a1[0] + R(5)); dy = (a2[1] + R(5)) - (a1[1] + R(5)); dz = (a2[2] + R(5)) - (a1[2] + R(5));
+            } else { dx = a2[0] - a1[0]; dy = a2[1] - a1[1]; dz = a2[2] - a1[2]; }
+            // cos(atan2(dy,dx)), cos(atan2(dx,dy)), cos(atan2(dz,dx))  (not a unit vector; reproduced as is)
+            const R rxy2 = dx * dx + dy * dy, rxz2 = dx * dx + dz * dz;
+            const R fx = F[i] * (rxy2 > R(0) ? dircos_r(dx, rxy2) : R(1));
+            const R fy = F[i] * (rxy2 > R(0) ? dircos_r(dy, rxy2) : R(1));
+            const R fz = F[i] * (rxz2 > R(0) ? dircos_r(dx, rxz2) : R(1));
+            const R* stale = (i < 2) ? el_old : C.sh_ref;               // refs cached by the previous read (sim:300-336)
+            const R* fresh = (i < 2) ? P.elref : C.sh_ref;
+            R r[3];
 #pragma unroll
-                    for (int i = 0; i < 7; i++) th[i] = qa[i] * d2r + b[i];
-                    dh_end_effector(th, K.L1, K.L2, p1);
-#pragma unroll
-                    for (int i = 0; i < 7; i++) th[i] = qt[i] * d2r + b[i];
-                    dh_end_effector(th, K.L1, K.L2, p2);
-                    const R ds = sqrt_r((p1[0] - p0[0]) * (p1[0] - p0[0]) + (p1[1] - p0[1]) * (p1[1] - p0[1]) + (p1[2] - p0[2]) * (p1[2] - p0[2]));
-                    const R du = sqrt_r((p2[0] - p0[0]) * (p2[0] - p0[0]) + (p2[1] - p0[1]) * (p2[1] - p0[1]) + (p2[2] - p0[2]) * (p2[2] - p0[2]));
-                    amp = ((ds - du) / du) * R(100);
-                }
+            for (int k = 0; k < 3; k++) {
+                const R pv = a2[k] - stale[k];
+                r[k] = fresh[k] - a2[k];
+                s[W_POSVEC + i * 3 + k] = pv;
+                ob[47 + i * 3 + k] = (float)pv;
             }
-            if (INFO) {
+            const R tx = fy * r[2] - fz * r[1], ty = fz * r[0] - fx * r[2], tz = fx * r[1] - fy * r[0];   // cross(F, r) :179
+            if (i == 0) ty0 = ty;
+            else if (i == 1) ty1 = ty;
+            else { at0 += ty; at1 += tx; at2 += tz; }
+        }
+        const R at[4] = {at0, at1, at2, abs_r(ty0) - abs_r(ty1)};      // :394-400
+        // ---- tremor lookup (:403-406) and the rows the observation needs (:502-513)
+        R ttc[7], tv[7];
 #pragma unroll
-                for (int j = 0; j < 7; j++) {
-                    if (info.actuator_torques) info.actuator_torques[(size_t)e * 7 + j] = j < 4 ? at[j] : R(0);
-                    if (info.torque_val) info.torque_val[(size_t)e * 7 + j] = tv[j];
-                    if (info.ampl_val) info.ampl_val[(size_t)e * 7 + j] = qa[j];
-                    if (info.tremor_torque_val) info.tremor_torque_val[(size_t)e * 7 + j] = ttc[j];
-                    if (info.tremor_ampl_val) info.tremor_ampl_val[(size_t)e * 7 + j] = qt[j];
-                }
-                if (info.reward_parts) {
-                    R* rp = info.reward_parts + (size_t)e * 5;
-                    rp[0] = r_unw; rp[1] = r_tor; rp[2] = r_axis; rp[3] = r_ctl; rp[4] = r_smo;
-                }
-                if (info.amp_metric) info.amp_metric[e] = amp;
-            }
-            // warp-aggregated statistics: one RED per warp and counter
-            {
-                const unsigned mask = __activemask();
-                const int lane = tid & 31;
-                const int leader = __ffs(mask) - 1;
-                double v_ep = dn ? 1.0 : 0.0, v_ret = dn ? (double)ret : 0.0, v_len = dn ? (double)(k1 - 2) : 0.0;
-                double v_cross = (double)crossed, v_red = (double)arm_red;
-                double v_amp = (INFO && amp < R(0)) ? (double)amp : 0.0, v_ampn = (INFO && amp < R(0)) ? 1.0 : 0.0;
-                double v_steps = 1.0;
-                for (int o = 16; o > 0; o >>= 1) {
-                    v_ep += __shfl_xor_sync(mask, v_ep, o); v_ret += __shfl_xor_sync(mask, v_ret, o);
-                    v_len += __shfl_xor_sync(mask, v_len, o); v_cross += __shfl_xor_sync(mask, v_cross, o);
-                    v_red += __shfl_xor_sync(mask, v_red, o); v_steps += __shfl_xor_sync(mask, v_steps, o);
-                    if (INFO) { v_amp += __shfl_xor_sync(mask, v_amp, o); v_ampn += __shfl_xor_sync(mask, v_ampn, o); }
-                }
-                if (mask == 0xffffffffu && lane == leader) {
-                    if (v_ep != 0.0) { atomicAdd(S.stats + 0, v_ep); atomicAdd(S.stats + 1, v_ret); atomicAdd(S.stats + 2, v_len); }
-                    atomicAdd(S.stats + 3, v_steps);
-                    if (v_cross != 0.0) atomicAdd(S.stats + 4, v_cross);
-                    if (v_red != 0.0) atomicAdd(S.stats + 5, v_red);
-                    if (INFO && v_ampn != 0.0) { atomicAdd(S.stats + 6, v_amp); atomicAdd(S.stats + 7, v_ampn); }
-                } else if (mask != 0xffffffffu) {
-                    // partially active warp (tail block / mixed idle): xor-shuffles over a partial mask are not a
-                    // reduction, so every active lane contributes its own values
-                    if (dn) { atomicAdd(S.stats + 0, 1.0); atomicAdd(S.stats + 1, (double)ret); atomicAdd(S.stats + 2, (double)(k1 - 2)); }
-                    atomicAdd(S.stats + 3, 1.0);
-                    if (crossed) atomicAdd(S.stats + 4, (double)crossed);
-                    if (arm_red) atomicAdd(S.stats + 5, 1.0);
-                    if (INFO && amp < R(0)) { atomicAdd(S.stats + 6, (double)amp); atomicAdd(S.stats + 7, 1.0); }
-                }
+        for (int j = 0; j < 7; j++) {
+            ttc[j] = (j < NAX) ? tc[j] : R(0);
+            tv[j] = ttc[j] + (j < 4 ? at[j] : R(0));
+        }
+        const R inrm[4] = {R(0.1), R(0.1), R(0.1), R(0.2)};
+        const R nrm[4] = {R(10), R(10), R(10), R(5)};
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (sizeof(R) == 8) {
+                ob[14 + j] = (float)(tm[j] / nrm[j]); ob[18 + j] = (float)(tc[j] / nrm[j]); ob[22 + j] = (float)(tp[j] / nrm[j]);
+            } else {
+                ob[14 + j] = (float)(tm[j] * inrm[j]); ob[18 + j] = (float)(tc[j] * inrm[j]); ob[22 + j] = (float)(tp[j] * inrm[j]);
             }
         }
+        // ---- joint model: q(dt) = G * T from rest (:409-418); rows 0..3 drive the motors
+        const R r2d = R(57.29577951308232087679815481410517), d2r = R(0.017453292519943295769236907684886);
+        R qa[7], qt[7];
+        constexpr int ROWS = INFO ? 7 : 4;
+#pragma unroll
+        for (int i = 0; i < ROWS; i++) {
+            R acc = 0, acc2 = 0;
+#pragma unroll
+            for (int j = 0; j < 7; j++) {
+                if (j < 4 || j < NAX) {
+                    const R gij = g[exo_g_word(i, j)];
+                    acc += gij * tv[j];
+                    if (INFO) acc2 += gij * ttc[j];
+                }
+            }
+            qa[i] = acc * r2d;
+            if (INFO) qt[i] = acc2 * r2d;
+        }
+        // ---- angle composition + position motors + one Bullet step (:421-433, oracle/minibullet.py)
+        const R tgt[5] = {(mo[4 * S.max_len + c] + qa[2]) * d2r, (mo[3 * S.max_len + c] + qa[0]) * d2r,
+                          (mo[2 * S.max_len + c] + qa[1]) * d2r, (mo[0 * S.max_len + c] + qa[3]) * d2r,
+                          mo[1 * S.max_len + c] * d2r};
+        int crossed = 0;
+#pragma unroll
+        for (int j = 0; j < 5; j++) {
+            R qn = qb[j] + R(0.025) * div_r(R(0.1) * (tgt[j] - qb[j]), R(0.025));   // q + dt*v*, v* = kp*(target-q)/dt
+            if (qn < C.lower[j] || qn > C.upper[j]) {
+                crossed++;
+                if (K.limits) qn = qn < C.lower[j] ? C.lower[j] : C.upper[j];
+            }
+            s[W_Q + j] = qn;
+            if (K.lag) s[W_QLAG + j] = qb[j];
+        }
+#pragma unroll
+        for (int k = 0; k < 3; k++) s[W_ELREF + k] = P.elref[k];
+        // ---- reward (:268-366)
+        const R eps = R(1e-10);
+        const R m = fm_el + fm_sh;
+        const int nax = __popc(meta & 0x7f);
+        const R nf = (R)nax;
+        R sum_unw = 0, sum_tor = 0, sumF = 0, smooth = 0;
+        int axis_cnt = 0, arm_red = 0;
+#pragma unroll
+        for (int j = 0; j < 7; j++) {
+            const R a = abs_r(tv[j]), b = abs_r(ttc[j]);
+            if (j < 4) {
+                if ((meta >> j) & 1) sum_tor += div_r(a - b, b) + R(1);
+                else sum_unw += a;
+            }
+            if (j < 4 || j < NAX) {
+                const R red = div_r(a - b, b + eps) * R(100);
+                if (red < R(0)) { axis_cnt++; if (j < 4) arm_red = 1; }      // nan/inf -> 0 -> not counted (:302-303)
+            }   // axes without a table entry: a == b == 0 -> reduction 0 -> not counted
+        }
+        R fp1[7];
+#pragma unroll
+        for (int i = 0; i < 7; i++) {
+            fp1[i] = s[W_FPREV + i];
+            const R fp2 = s[W_FPREV2 + i];
+            const R d = F[i] - R(2) * fp1[i] + fp2;
+            smooth += d * d;
+            sumF += F[i];
+            s[W_FPREV2 + i] = fp1[i];
+            s[W_FPREV + i] = F[i];
+        }
+        const R r_unw = exp_r(-div_r(sum_unw, div_r(m / R(4), nf)) + eps) * R(0.5);
+        const R r_tor = exp_r(div_r(-sum_tor + eps, nf)) * R(0.9);
+        const R r_axis = (R)axis_cnt * R(0.5);
+        const R r_ctl = exp_r(-div_r(sumF, m / R(2)) + eps) * R(0.05);
+        const R r_smo = R(0.05) * exp_r(-div_r(div_r(smooth, R(7)), m / R(4)) + eps);
+        const R max_reward = nf * R(0.5) + R(0.9) + R(0.05) + R(0.05) + R(0.5);
+        const R rew = div_r(r_axis + r_tor + r_smo + r_ctl + r_unw, max_reward);
+        reward[e] = rew;
+        // ---- write the carried state back
+#pragma unroll
+        for (int v = 0; v < NV_STATE; v++) st4(S.state + (size_t)v * st + e, s + 4 * v);
+        // ---- counts, observation head, done (:448-457)
+        const int k1 = c + 1;
+        S.counts[e] = k1;
+#pragma unroll
+        for (int i = 0; i < 7; i++) {
+            const R f0i = i < 2 ? K.inv_fmax_el0 : K.inv_fmax_sh0, f0 = i < 2 ? K.fmax_el0 : K.fmax_sh0;
+            if (sizeof(R) == 8) {
+                ob[i] = (c >= 3) ? (float)(fp1[i] / f0) : 0.0f;       // forces[k-2]; the history is zeroed at reset (:195)
+                ob[7 + i] = (float)(F[i] / f0);                       // forces[k-1]
+            } else {
+                ob[i] = (c >= 3) ? (float)(fp1[i] * f0i) : 0.0f;
+                ob[7 + i] = (float)(F[i] * f0i);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            ob[68 + k] = (float)C.sh_ref[k]; ob[71 + k] = (float)el_old[k];     // ref_prev (:383)
+            ob[74 + k] = (float)C.sh_ref[k]; ob[77 + k] = (float)P.elref[k];    // ref (:387)
+        }
+        {   // this env's observation row -> the warp's staging tile (16-byte chunks, pitch 21 chunks: conflict-free)
+            float4* so = reinterpret_cast<float4*>(&s_obs[wid][lane * EXO_OBS_PITCH]);
+#pragma unroll
+            for (int ch = 0; ch < 20; ch++) so[ch] = make_float4(ob[4 * ch], ob[4 * ch + 1], ob[4 * ch + 2], ob[4 * ch + 3]);
+        }
+        const bool dn = k1 >= L - 1;
+        done[e] = dn ? 1 : 0;
+        fin = dn;
+        // ---- episode statistics (device-side; all-reduced over NCCL by the host)
+        const R ret = ret0 + rew;
+        S.ret[e] = dn ? R(0) : ret;
+        R amp = 0;
+        if (INFO) {
+            // Exoskeleton_agent_train.py:158-170 with return_original_joint_angles at the incremented counts
+            R b[7] = {mo[2 * S.max_len + k1] * d2r, mo[3 * S.max_len + k1] * d2r, mo[4 * S.max_len + k1] * d2r,
+                      mo[0 * S.max_len + k1] * d2r, mo[1 * S.max_len + k1] * d2r, R(0), R(0)};
+            R th[7], p0[3], p1[3], p2[3];
+            dh_end_effector(b, K.L1, K.L2, p0);
+#pragma unroll
+            for (int i = 0; i < 7; i++) th[i] = qa[i] * d2r + b[i];
+            dh_end_effector(th, K.L1, K.L2, p1);
+#pragma unroll
+            for (int i = 0; i < 7; i++) th[i] = qt[i] * d2r + b[i];
+            dh_end_effector(th, K.L1, K.L2, p2);
+            const R ds = sqrt_r((p1[0] - p0[0]) * (p1[0] - p0[0]) + (p1[1] - p0[1]) * (p1[1] - p0[1]) + (p1[2] - p0[2]) * (p1[2] - p0[2]));
+            const R du = sqrt_r((p2[0] - p0[0]) * (p2[0] - p0[0]) + (p2[1] - p0[1]) * (p2[1] - p0[1]) + (p2[2] - p0[2]) * (p2[2] - p0[2]));
+            amp = ((ds - du) / du) * R(100);
+#pragma unroll
+            for (int j = 0; j < 7; j++) {
+                if (info.actuator_torques) info.actuator_torques[(size_t)e * 7 + j] = j < 4 ? at[j] : R(0);
+                if (info.torque_val) info.torque_val[(size_t)e * 7 + j] = tv[j];
+                if (info.ampl_val) info.ampl_val[(size_t)e * 7 + j] = qa[j];
+                if (info.tremor_torque_val) info.tremor_torque_val[(size_t)e * 7 + j] = ttc[j];
+                if (info.tremor_ampl_val) info.tremor_ampl_val[(size_t)e * 7 + j] = qt[j];
+            }
+            if (info.reward_parts) {
+                R* rp = info.reward_parts + (size_t)e * 5;
+                rp[0] = r_unw; rp[1] = r_tor; rp[2] = r_axis; rp[3] = r_ctl; rp[4] = r_smo;
+            }
+            if (info.amp_metric) info.amp_metric[e] = amp;
+        }
+        v_cross = crossed; v_red = arm_red;
+        if (dn) { v_len = k1 - 2; v_ret = ret; }
+        if (INFO && amp < R(0)) v_amp = amp;
     }
-    s_live[tid] = live ? 1 : 0;
-    __syncthreads();
-    // ---- observation tile -> row-major [n,80] with 128-bit coalesced stores
+    // ---- warp-level epilogue: every lane of the warp arrives here
+    const unsigned full = 0xffffffffu;
+    const unsigned live_mask = __ballot_sync(full, live);
+    const unsigned fin_mask = __ballot_sync(full, fin);
+    if (live_mask == 0) return;
+    // observation tile -> row-major [n,80]: the warp's 32 rows are 10 240 contiguous bytes, 128-bit coalesced stores
     if (obs != nullptr) {
-        const int rows = min(EXO_STEP_THREADS, n - base);
-        float4* dst = reinterpret_cast<float4*>(obs + (size_t)base * 80);
-        for (int v = tid; v < rows * 20; v += EXO_STEP_THREADS) {
-            const int row = v / 20, col = (v - row * 20) * 4;
-            if (s_live[row]) {
-                const float* sp = s_obs + row * EXO_OBS_PAD + col;
-                dst[v] = make_float4(sp[0], sp[1], sp[2], sp[3]);
-            }
+        float4* dst = reinterpret_cast<float4*>(obs + (size_t)wbase * 80);
+        const float4* src = reinterpret_cast<const float4*>(&s_obs[wid][0]);
+#pragma unroll 4
+        for (int it = 0; it < 20; it++) {
+            const int v = it * 32 + lane;
+            const int row = v / 20, ch = v - row * 20;
+            if ((live_mask >> row) & 1u) dst[v] = src[row * (EXO_OBS_PITCH / 4) + ch];
         }
     }
+    // finished envs -> the auto-reset work list (one atomic per warp that has any)
+    if (K.auto_reset && fin_mask) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(S.fin_count + K.parity, __popc(fin_mask));
+        base = __shfl_sync(full, base, 0);
+        if (fin) S.fin_list[(size_t)K.parity * st + base + __popc(fin_mask & ((1u << lane) - 1u))] = e;
+    }
+    // statistics: integer counters by warp-reduce, the real-valued ones only in warps where an episode ended
+    {
+        const int n_live = __popc(live_mask);
+        const int t_cross = __reduce_add_sync(full, v_cross);
+        const int t_red = __reduce_add_sync(full, v_red);
+        double t_ret = 0.0, t_amp = 0.0;
+        int t_len = 0, t_ampn = 0;
+        if (fin_mask) {
+            t_len = __reduce_add_sync(full, v_len);
+            double x = (double)v_ret;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(full, x, o);
+            t_ret = x;
+        }
+        if (INFO) {
+            const unsigned am = __ballot_sync(full, v_amp < R(0));
+            t_ampn = __popc(am);
+            if (am) {
+                double x = (double)v_amp;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(full, x, o);
+                t_amp = x;
+            }
+        }
+        if (lane == 0) {
+            if (fin_mask) {
+                atomicAdd(S.stats + 0, (double)__popc(fin_mask)); atomicAdd(S.stats + 1, t_ret); atomicAdd(S.stats + 2, (double)t_len);
+            }
+            atomicAdd(S.stats + 3, (double)n_live);
+            if (t_cross) atomicAdd(S.stats + 4, (double)t_cross);
+            if (t_red) atomicAdd(S.stats + 5, (double)t_red);
+            if (INFO && t_ampn) { atomicAdd(S.stats + 6, t_amp); atomicAdd(S.stats + 7, (double)t_ampn); }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// exo_get_field / exo_set_field: gather/scatter between the resident layout and env-major [n, k] buffers.
+// ---------------------------------------------------------------------------------------------------------
+template <typename R, typename T, bool SET>
+__global__ void exo_field_kernel(EnvArrays<R> S, int field, int k, int naxv, T* __restrict__ buf) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t)S.n * k) return;
+    const int e = (int)(idx / k), i = (int)(idx - (size_t)e * k), st = S.stride;
+    T* a = nullptr;
+    switch (field) {
+        case F_Q: a = (T*)exo_word(S.state, W_Q + i, e, st); break;
+        case F_Q_LAG: a = (T*)exo_word(S.state, W_QLAG + i, e, st); break;
+        case F_POS_VEC: a = (T*)exo_word(S.state, W_POSVEC + i, e, st); break;
+        case F_ELBOW_REF: a = (T*)exo_word(S.state, W_ELREF + i, e, st); break;
+        case F_PREV_ACTION: a = (T*)exo_word(S.state, W_FPREV + i, e, st); break;
+        case F_PREV_ACTION2: a = (T*)exo_word(S.state, W_FPREV2 + i, e, st); break;
+        case F_FORCE_MAX: a = (T*)exo_word(S.ep, W_FMAX + i, e, st); break;
+        case F_SHIFT: a = (T*)exo_word(S.ep, W_SHIFT + i, e, st); break;
+        case F_G: a = (T*)exo_word(S.G, exo_g_word(i / 7, i % 7), e, st); break;
+        case F_IDS: a = (T*)(S.IDS + (size_t)e * EXO_IDS_PITCH + i); break;
+        case F_TREMOR_TABLE: {
+            const int nax = k / S.table_len, row = i / nax, j = i - row * nax;
+            a = (T*)&S.tt[((size_t)row * st + e) * naxv + (j >> 2)].v[j & 3];
+            break;
+        }
+        case F_TREMOR_MAG: a = (T*)(S.mag + e); break;
+        case F_COUNTS: a = (T*)(S.counts + e); break;
+        case F_META: a = (T*)(S.meta + e); break;
+        case F_MT_STATE: a = (T*)(S.mt + (size_t)e * EXO_MT_PITCH + i); break;
+        case F_EP_RETURN: a = (T*)(S.ret + e); break;
+        default: return;
+    }
+    if (SET) *a = buf[idx]; else buf[idx] = *a;
 }
 
 }  // namespace exo

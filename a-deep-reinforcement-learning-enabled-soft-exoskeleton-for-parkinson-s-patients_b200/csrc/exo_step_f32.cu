@@ -31,7 +31,23 @@ template <typename R>
 void launch_fk(const R* theta, R* p, int n, R L1, R L2, cudaStream_t s) {
     exo_fk_kernel<R><<<(n + 127) / 128, 128, 0, s>>>(theta, p, n, L1, L2);
 }
+template <typename R>
+void launch_field(const EnvArrays<R>& A, int field, int k, int dtype, int naxv, void* buf, int set, cudaStream_t s) {
+    const size_t total = (size_t)A.n * k;
+    const int grid = (int)((total + 255) / 256);
+#define EXO_FIELD_GO(T)                                                                                  \
+    do {                                                                                                 \
+        if (set) exo_field_kernel<R, T, true><<<grid, 256, 0, s>>>(A, field, k, naxv, (T*)buf);          \
+        else exo_field_kernel<R, T, false><<<grid, 256, 0, s>>>(A, field, k, naxv, (T*)buf);             \
+    } while (0)
+    if (dtype == 0) EXO_FIELD_GO(R);
+    else if (dtype == 1) EXO_FIELD_GO(double);
+    else if (dtype == 2) EXO_FIELD_GO(int);
+    else EXO_FIELD_GO(uint32_t);
+#undef EXO_FIELD_GO
+}
 template void launch_step<REAL>(const EnvArrays<REAL>&, const ChainConst<REAL>&, const StepConst<REAL>&, int, bool, const float*,
                                 float*, REAL*, uint8_t*, const InfoPtrs<REAL>&, cudaStream_t);
 template void launch_fk<REAL>(const REAL*, REAL*, int, REAL, REAL, cudaStream_t);
+template void launch_field<REAL>(const EnvArrays<REAL>&, int, int, int, int, void*, int, cudaStream_t);
 }  // namespace exo

@@ -1,47 +1,74 @@
 // exo_types.cuh — device-side layouts shared by the kernels of libexo_env.so.
 //
-// HBM layout: every per-env quantity is a field-major structure-of-arrays, element (field f, env e) at
-// base[f * stride + e] with stride = n_envs rounded up to 32, so a warp touching one field of 32
-// consecutive envs issues one fully coalesced 128 B (fp32) / 256 B (fp64) transaction.
+// HBM layout. Two access patterns meet in this library:
+//   * exo_step_kernel   one THREAD per env, every control step: wants field-major arrays so that a warp touching
+//                       one field of 32 consecutive envs issues one contiguous transaction;
+//   * exo_reset_kernel  one WARP per env, once per episode: wants an env's private data contiguous.
+// Everything the step touches is therefore stored as "vector-major SoA": the per-env record is cut into
+// 4-word vectors V4<R> (16 B fp32 / 32 B fp64) and vector v of env e lives at base[v * stride + e]
+// (stride = n_envs rounded up to 32). A warp loads vector v of its 32 envs as ONE 512 B (fp32) contiguous
+// request made of 128-bit loads: a quarter of the load/store instructions of a word-major SoA and 4x the bytes
+// in flight per instruction, which is what a latency-bound single-wave kernel needs. Data only the reset
+// touches (MT19937 key, the fp64 I/D/S matrices) is env-major so the warp streams it coalesced.
 #pragma once
 #include <stdint.h>
 
 #define EXO_MAX_LEN 512          // >= longest reference motion (347 rows)
-#define EXO_SIGN_WORDS (EXO_MAX_LEN / 32)
-#define EXO_STEP_THREADS 128
+
+#define EXO_STEP_THREADS 64      // 2 warps per block: 65 536 envs -> 1024 blocks ~ 6.9 per SM (balanced single wave)
+#define EXO_STEP_MIN_BLOCKS 8    // <= 128 registers per thread: all 14 warps an SM owns at 65 536 envs stay resident
+#define EXO_OBS_PITCH 84         // floats per staged observation row: 21 16-byte chunks, odd -> conflict-free STS.128
+
+// ---- word offsets inside the per-env records -------------------------------------------------------------
+// carried state, 48 words = 12 vectors, rewritten every step
+#define W_Q 0        // [5]  Bullet joint positions (rad): shoulder z,y,x, elbow y,z
+#define W_QLAG 5     // [5]  joint positions the link-state cache was computed from
+#define W_ELREF 10   // [3]  act_elbow_reference_positions as last read
+#define W_POSVEC 13  // [21] position_vectors
+#define W_FPREV 34   // [7]  prev_action (N)
+#define W_FPREV2 41  // [7]  second_prev_action (N)
+#define NV_STATE 12
+// per-episode parameters, 44 words = 11 vectors, written at reset
+#define W_SHIFT 0    // [42] dummy_shift_coordinates
+#define W_FMAX 42    // [2]  max_output_shoulder, max_output_elbow (domain-randomised)
+#define NV_EP 11
+// propagator G (7x7) reordered so that the 4x4 block the plain step needs is vectors 0..3
+#define NV_G 13
+#define EXO_MT_PITCH 640         // words per env in the MT19937 array: 624 key + position (+pad to 128 B multiple)
+#define EXO_IDS_PITCH 148        // doubles per env: I, D, S (3 x 49) + pad
+
+__host__ __device__ __forceinline__ int exo_g_word(int r, int c) {
+    return (r < 4) ? (c < 4 ? r * 4 + c : 16 + r * 3 + (c - 4)) : 28 + (r - 4) * 7 + c;
+}
+
+template <typename R>
+struct __align__(16) V4 { R v[4]; };
+
+// scalar word w of env e inside a vector-major array
+template <typename R>
+__host__ __device__ __forceinline__ R* exo_word(V4<R>* base, int w, int e, int stride) {
+    return &base[(size_t)(w >> 2) * stride + e].v[w & 3];
+}
 
 template <typename R>
 struct EnvArrays {
     int n, stride;
-    // carried state
-    R* q;          // [5]  Bullet joint positions
-    R* qlag;       // [5]  joint positions behind the link-state cache
-    R* posvec;     // [21]
-    R* elref;      // [3]
-    R* fprev;      // [7]
-    R* fprev2;     // [7]
-    R* ret;        // [1] running episode return
-    int* counts;   // [1]
-    // per-episode parameters
-    R* fmax;       // [2] shoulder, elbow
-    R* shift;      // [42]
-    R* G;          // [49]
-    R* tt;         // [table_len][NAX]
-    double* IDS;   // [147]
-    double* mag;   // [1]
-    // per-env constants
-    int* meta;     // bits 0-6 tremor_sequence, bits 8-15 motion id
-    uint32_t* mt;  // [625]
-    // reset scratch (fp64)
-    double* sc_noise;  // [max_len]
-    double* sc_w1;     // [max_len]
-    double* sc_w2;     // [max_len]
-    uint32_t* sc_sign; // [7][EXO_SIGN_WORDS]
-    // shared tables
+    V4<R>* state;    // [NV_STATE][stride]
+    V4<R>* ep;       // [NV_EP][stride]
+    V4<R>* G;        // [NV_G][stride]
+    V4<R>* tt;       // [table_len][stride][NAXP/4]  tremor table, time-major: one step reads rows c-1, c, c+1
+    R* ret;          // [stride] running episode return
+    int* counts;     // [stride] self.counts
+    int* meta;       // [stride] bits 0-6 tremor_sequence, bits 8-15 motion id
+    double* IDS;     // [n][EXO_IDS_PITCH]  I_current, D_current, S_current (fp64, env-major)
+    double* mag;     // [stride] tremor_magnitude
+    uint32_t* mt;    // [n][EXO_MT_PITCH]   numpy legacy MT19937 key + position (env-major)
     const R* motion;         // [n_motions][5][max_len] degrees
     const int* motion_len;   // [n_motions]
     int max_len, n_motions, table_len;
     double* stats;           // [EXO_N_STATS]
+    int* fin_count;          // [2]          envs that finished in the step of parity p (auto-reset work list)
+    int* fin_list;           // [2][stride]
 };
 
 // Geometry of the 5-revolute chain, flattened on the host from the URDF tree (exo_api.cu: build_chain).
@@ -61,8 +88,10 @@ struct ChainConst {
 template <typename R>
 struct StepConst {
     R fmax_sh0, fmax_el0;          // un-randomised maxima (obs normalisation, Exoskeleton_env.py:488-501)
+    R inv_fmax_sh0, inv_fmax_el0;
     R L1, L2;                      // humerus / forearm length for the amplitude metric
     int lag, limits, auto_reset, metrics;
+    int parity;                    // which finished-list this step appends to (the other counter is cleared)
 };
 
 struct ResetConst {
@@ -71,9 +100,17 @@ struct ResetConst {
     double fmax_sh0, fmax_el0;
     double dt;
     int lag;
+    int ctor_skip;     // 32-bit outputs consumed before the episode draws (2 for the constructor's rand(), env:70)
+    int list_parity;   // >= 0: reset the envs of fin_list[parity]; < 0: reset by mask
 };
 
 template <typename R>
 struct InfoPtrs {
     R *actuator_torques, *torque_val, *ampl_val, *tremor_torque_val, *tremor_ampl_val, *reward_parts, *amp_metric;
+};
+
+// field ids of exo_get_field / exo_set_field (include/exo_env.h EXO_FIELD_*)
+enum {
+    F_Q = 0, F_Q_LAG, F_POS_VEC, F_ELBOW_REF, F_PREV_ACTION, F_PREV_ACTION2, F_FORCE_MAX, F_SHIFT, F_G, F_IDS,
+    F_TREMOR_TABLE, F_TREMOR_MAG, F_COUNTS, F_META, F_MT_STATE, F_EP_RETURN, F_N_FIELDS
 };

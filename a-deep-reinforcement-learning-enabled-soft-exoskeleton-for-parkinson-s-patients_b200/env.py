@@ -19,18 +19,9 @@ REWARD_KEYS = ("reward_unwanted", "reward_torque", "reward_axis", "reward_contro
 STAT_NAMES = ("episodes", "return_sum", "length_sum", "env_steps", "limit_crossings", "steps_with_arm_reduction",
               "amp_metric_neg_sum", "amp_metric_neg_count")
 
-_TYPESTR = {torch.float32: "<f4", torch.float64: "<f8", torch.int32: "<i4"}
-
 
 def _ptr(t):
     return C.c_void_p(t.data_ptr()) if t is not None else None
-
-
-class _DeviceArray(object):
-    """Carries a raw device address into torch through __cuda_array_interface__ (no copy, no ownership)."""
-
-    def __init__(self, ptr, shape, dtype):
-        self.__cuda_array_interface__ = dict(shape=tuple(shape), typestr=_TYPESTR[dtype], data=(int(ptr), False), version=2)
 
 
 class BatchedExoskeletonEnv(object):
@@ -215,48 +206,29 @@ class BatchedExoskeletonEnv(object):
         _capi.check(self.lib.exo_forward_kinematics(self.h, _ptr(th), _ptr(p), th.shape[0], L1, L2, L3, self._stream()))
         return p
 
-    # ------------------------------------------------------------------ state views (tests, checkpoints)
-    _FIELDS = dict(q=5, q_lag=5, pos_vec=21, elbow_ref=3, prev_action=7, prev_action2=7, force_max=2, shift=42, G=49,
-                   ep_return=1)
-
-    def _view(self):
-        v = _capi.ExoStateView()
-        _capi.check(self.lib.exo_get_state(self.h, C.byref(v)))
-        return v
-
-    def _wrap(self, ptr, rows, dtype):
-        """torch view (no copy) of a field-major [rows, stride] device array owned by the handle."""
-        v = self._view()
-        return torch.as_tensor(_DeviceArray(ptr, (rows, v.stride), dtype), device=self.device)
-
-    def _raw(self, name):
-        v = self._view()
-        if name in self._FIELDS:
-            return self._wrap(getattr(v, name), self._FIELDS[name], self.real)
-        if name == "IDS":
-            return self._wrap(v.IDS, 147, torch.float64)
-        if name == "tremor_mag":
-            return self._wrap(v.tremor_mag, 1, torch.float64)
-        if name in ("counts", "meta"):
-            return self._wrap(getattr(v, name), 1, torch.int32)
-        if name == "mt_state":
-            return self._wrap(v.mt_state, 625, torch.int32)
-        if name == "tremor_table":
-            return self._wrap(v.tremor_table, v.table_len * v.table_axes, self.real)
-        raise KeyError(name)
+    # ------------------------------------------------------------------ resident state by field (tests, checkpoints)
+    def _field_info(self, name):
+        k, dt = C.c_int32(), C.c_int32()
+        _capi.check(self.lib.exo_field_info(self.h, _capi.FIELDS[name], C.byref(k), C.byref(dt)))
+        dtype = {_capi.DT_REAL: self.real, _capi.DT_F64: torch.float64, _capi.DT_I32: torch.int32, _capi.DT_U32: torch.int32}[dt.value]
+        return k.value, dtype
 
     def get_field(self, name):
-        """Copy of one state field as an env-major tensor [N, k] (tremor_table: [N, table_len, axes])."""
-        t = self._raw(name)[:, :self.n].t().clone(memory_format=torch.contiguous_format)   # a copy, never a live view
+        """Copy of one state field as an env-major tensor [N, k] (tremor_table: [N, table_len, axes]); the layout
+        inside the handle is private (exo_get_field gathers it on the device)."""
+        k, dtype = self._field_info(name)
+        out = torch.empty(self.n, k, dtype=dtype, device=self.device)
+        _capi.check(self.lib.exo_get_field(self.h, _capi.FIELDS[name], _ptr(out), self._stream()))
         if name == "tremor_table":
-            v = self._view()
-            return t.reshape(self.n, v.table_len, v.table_axes)
-        return t
+            axes = 7 if int(self.tremor_sequences[:, 4:].max(initial=0)) else 4
+            return out.reshape(self.n, k // axes, axes)
+        return out
 
     def set_field(self, name, value):
-        t = self._raw(name)
-        val = torch.as_tensor(value, device=self.device, dtype=t.dtype).reshape(self.n, -1)
-        t[:, :self.n] = val.t()
+        k, dtype = self._field_info(name)
+        val = torch.as_tensor(value, device=self.device).to(dtype).reshape(self.n, k).contiguous()
+        _capi.check(self.lib.exo_set_field(self.h, _capi.FIELDS[name], _ptr(val), self._stream()))
+        torch.cuda.current_stream(self.device).synchronize()      # `val` may be a temporary
 
     CHECKPOINT_FIELDS = ("q", "q_lag", "pos_vec", "elbow_ref", "prev_action", "prev_action2", "force_max", "shift", "G",
                          "ep_return", "IDS", "tremor_mag", "counts", "tremor_table", "mt_state")

@@ -11,6 +11,9 @@
  *    entry points never synchronise, host-buffer entry points synchronise that stream before returning.
  *  - `real` below is float when ExoConfig.precision == EXO_F32 and double when EXO_F64.
  *  - env arrays are row-major [n_envs, k] at this boundary; inside the handle state is structure-of-arrays.
+ *  - with auto_reset, exo_step appends the envs that finished to a device-side work list and the reset kernel
+ *    consumes it in the same call: no host synchronisation, and a step in which nothing finished pays one
+ *    empty launch.
  */
 #ifndef EXO_ENV_H
 #define EXO_ENV_H
@@ -77,27 +80,29 @@ typedef struct {
     void* amp_metric;         /* real [n]: end-effector amplitude change % (Exoskeleton_agent_train.py:158-170) */
 } ExoInfo;
 
-/* Read/write views of the resident state (device pointers, field-major [k][n_envs] with `stride` elements
- * between fields). For parity tests and checkpoint/restore. */
-typedef struct {
-    int32_t n_envs, stride, precision, table_len, table_axes;
-    void* q;            /* real [5]  Bullet joint positions: shoulder z,y,x, elbow y,z (rad) */
-    void* q_lag;        /* real [5]  joint positions the link-state cache was computed from */
-    void* pos_vec;      /* real [21] position_vectors (Exoskeleton_env.py:386) */
-    void* elbow_ref;    /* real [3]  act_elbow_reference_positions as last read */
-    void* prev_action;  /* real [7]  Newtons (Exoskeleton_env.py:455) */
-    void* prev_action2; /* real [7]  (Exoskeleton_env.py:454) */
-    void* force_max;    /* real [2]  domain-randomised max_output_shoulder, max_output_elbow (:216-217) */
-    void* shift;        /* real [42] dummy_shift_coordinates (Exoskeleton_sim_pybullet.py:103-107) */
-    void* G;            /* real [49] propagator of I q'' + D q' + S q = T over one dt from rest: q(dt) = G T (rad/Nm) */
-    void* IDS;          /* double [147] I_current, D_current, S_current (Exoskeleton_env.py:208-210) */
-    void* tremor_table; /* real [table_len][table_axes] tremor_torque_values, time-major */
-    void* tremor_mag;   /* double [1] tremor_magnitude (:199) */
-    int32_t* counts;    /* [1] self.counts */
-    int32_t* meta;      /* [1] bits 0-6 tremor_sequence, bits 8-15 motion id */
-    uint32_t* mt_state; /* [625] numpy legacy MT19937 key + position */
-    void* ep_return;    /* real [1] running episode return */
-} ExoStateView;
+/* Resident per-env state, addressed by field. The layout inside the handle (vector-major structure-of-arrays,
+ * DESIGN.md) is private; exo_get_field / exo_set_field gather/scatter env-major [n_envs, k] device buffers.
+ * For parity tests and checkpoint/restore. */
+typedef enum {
+    EXO_FIELD_Q = 0,          /* real [5]   Bullet joint positions: shoulder z,y,x, elbow y,z (rad) */
+    EXO_FIELD_Q_LAG,          /* real [5]   joint positions the link-state cache was computed from */
+    EXO_FIELD_POS_VEC,        /* real [21]  position_vectors (Exoskeleton_env.py:386) */
+    EXO_FIELD_ELBOW_REF,      /* real [3]   act_elbow_reference_positions as last read */
+    EXO_FIELD_PREV_ACTION,    /* real [7]   Newtons (Exoskeleton_env.py:455) */
+    EXO_FIELD_PREV_ACTION2,   /* real [7]   (Exoskeleton_env.py:454) */
+    EXO_FIELD_FORCE_MAX,      /* real [2]   domain-randomised max_output_shoulder, max_output_elbow (:216-217) */
+    EXO_FIELD_SHIFT,          /* real [42]  dummy_shift_coordinates (Exoskeleton_sim_pybullet.py:103-107) */
+    EXO_FIELD_G,              /* real [49]  propagator of I q'' + D q' + S q = T over one dt from rest: q(dt) = G T (rad/Nm) */
+    EXO_FIELD_IDS,            /* f64  [147] I_current, D_current, S_current (Exoskeleton_env.py:208-210) */
+    EXO_FIELD_TREMOR_TABLE,   /* real [table_len * table_axes] tremor_torque_values, time-major */
+    EXO_FIELD_TREMOR_MAG,     /* f64  [1]   tremor_magnitude (:199) */
+    EXO_FIELD_COUNTS,         /* i32  [1]   self.counts */
+    EXO_FIELD_META,           /* i32  [1]   bits 0-6 tremor_sequence, bits 8-15 motion id */
+    EXO_FIELD_MT_STATE,       /* u32  [625] numpy legacy MT19937 key + position */
+    EXO_FIELD_EP_RETURN,      /* real [1]   running episode return */
+    EXO_N_FIELDS
+} ExoField;
+enum { EXO_DT_REAL = 0, EXO_DT_F64 = 1, EXO_DT_I32 = 2, EXO_DT_U32 = 3 };
 
 typedef struct ExoHandle ExoHandle;
 
@@ -134,7 +139,11 @@ int exo_step_host(ExoHandle* h, const float* actions_host, float* obs_host, void
                   void* stream);
 int exo_reset_host(ExoHandle* h, const uint8_t* mask_host, float* obs_host, void* stream);
 
-int exo_get_state(ExoHandle* h, ExoStateView* out);
+/* k = elements per env, dtype = EXO_DT_* of a field (valid after exo_set_env_types). */
+int exo_field_info(ExoHandle* h, int32_t field, int32_t* k, int32_t* dtype);
+/* resident state -> out_dev [n_envs, k] (env-major), and back. Asynchronous on `stream`. */
+int exo_get_field(ExoHandle* h, int32_t field, void* out_dev, void* stream);
+int exo_set_field(ExoHandle* h, int32_t field, const void* in_dev, void* stream);
 
 /* Episode statistics accumulated on device since the last call with reset != 0:
  * out_dev[0..EXO_N_STATS) doubles: 0 episodes, 1 sum return, 2 sum length, 3 env-steps, 4 joint-limit crossings,

@@ -89,15 +89,15 @@ def test_library_exports_every_declared_symbol(exo):
 
 def test_ctypes_structs_match_the_header(tmp_path, exo):
     src = tmp_path / "sz.c"
-    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "exo_env.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu\\n",'
-                   'sizeof(ExoConfig),sizeof(ExoGeometry),sizeof(ExoInfo),sizeof(ExoStateView),offsetof(ExoConfig,link_state_lag),'
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "exo_env.h"\nint main(){printf("%zu %zu %zu %d %zu %zu\\n",'
+                   'sizeof(ExoConfig),sizeof(ExoGeometry),sizeof(ExoInfo),(int)EXO_N_FIELDS,offsetof(ExoConfig,link_state_lag),'
                    'offsetof(ExoGeometry,act_link));return 0;}\n')
     exe = tmp_path / "sz"
     subprocess.check_call(["gcc", "-I", os.path.join(REPO, "include"), str(src), "-o", str(exe)])
     sizes = [int(x) for x in subprocess.check_output([str(exe)]).split()]
     c = exo._capi
     assert sizes == [ctypes.sizeof(c.ExoConfig), ctypes.sizeof(c.ExoGeometry), ctypes.sizeof(c.ExoInfo),
-                     ctypes.sizeof(c.ExoStateView), c.ExoConfig.link_state_lag.offset, c.ExoGeometry.act_link.offset]
+                     len(c.FIELDS), c.ExoConfig.link_state_lag.offset, c.ExoGeometry.act_link.offset]
 
 
 def test_no_gpu_means_loud_failure(exo):
