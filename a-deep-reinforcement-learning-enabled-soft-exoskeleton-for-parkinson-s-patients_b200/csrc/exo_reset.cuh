@@ -112,31 +112,107 @@ __device__ __forceinline__ double warp_max(double v) {
     return v;
 }
 
-__device__ __forceinline__ void warp_matmul14(const double* A, const double* B, double* Cm, int ncol, int lane, double scale) {
-    // Cm[14 x ncol] = scale * A[14x14] * B[14 x ncol]
-    for (int idx = lane; idx < PD * ncol; idx += 32) {
-        const int i = idx / ncol, j = idx - i * ncol;
-        double acc = 0;
-#pragma unroll
-        for (int k = 0; k < PD; k++) acc = fma(A[i * PD + k], B[k * ncol + j], acc);
-        Cm[idx] = acc * scale;
+// ---------------------------------------------------------------------------------------------------------
+// MT19937 stream consumption, warp-cooperative. `pos` is the next unread word of the shared key.
+// ---------------------------------------------------------------------------------------------------------
+// next n tempered outputs -> dst[0..n)
+__device__ __forceinline__ void mt_fill_words(uint32_t* key, int& pos, uint32_t* dst, int n, int lane) {
+    for (int done = 0; done < n;) {
+        if (pos >= MT_N) { mt_twist_warp(key, lane); pos = 0; }
+        const int take = min(MT_N - pos, n - done);
+        for (int i = lane; i < take; i += 32) dst[done + i] = mt_temper(key[pos + i]);
+        done += take; pos += take;
+    }
+}
+// next n outputs -> bit k of bits[] = (output k) & 1   (np.random.choice([-1, 1]) draws, tremor:70)
+__device__ __forceinline__ void mt_fill_bits(uint32_t* key, int& pos, uint32_t* bits, int n, int lane) {
+    for (int done = 0; done < n;) {
+        if (pos >= MT_N) { mt_twist_warp(key, lane); pos = 0; }
+        const int take = min(min(MT_N - pos, n - done), 32 - (done & 31));      // never straddles a 32-bit word
+        const uint32_t y = lane < take ? mt_temper(key[pos + lane]) : 0u;
+        const uint32_t b = __ballot_sync(0xffffffffu, (y & 1u) != 0u) << (done & 31);
+        if (lane == 0) { if ((done & 31) == 0) bits[done >> 5] = b; else bits[done >> 5] |= b; }
+        done += take; pos += take;
+    }
+}
+// consume n outputs without using them (the state still has to advance)
+__device__ __forceinline__ void mt_skip(uint32_t* key, int& pos, int n, int lane) {
+    while (n > 0) {
+        if (pos >= MT_N) { mt_twist_warp(key, lane); pos = 0; }
+        const int take = min(MT_N - pos, n);
+        pos += take; n -= take;
     }
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Propagator (one warp, matrices in shared memory, fp64).
+// Propagator (one warp, fp64 on the tensor cores: mma.sync m8n8k4 f64 = DMMA).
 //   A = [[0, 1], [-I^-1 S, -I^-1 D]] (14x14),  B = [0; I^-1] (14x7)
 //   E = e^{A h}, Phi = sum_k (A h)^k/(k+1)!  (Taylor, degree 14, h = dt/2^s with ||A h||_inf <= 1/4)
 //   F = h * Phi * B, then s times: F <- (E + 1) F ; E <- E E.  G = rows 0..6 of F.
-// ids: I, D, S (3 x 49, shared). sm: scratch of 5*196 + 98 doubles. Result left in sm[3*196 .. +49] (rows 0..6 of F).
+// Matrices are padded to 16x16 (pitch PP doubles, pads stay exactly zero); E, Phi, P and F live in registers as
+// accumulator fragments, shared memory only converts accumulator layout into operand layout between products.
+// Fragment maps (PTX ISA, m8n8k4 .f64): A(8x4) row = lane/4, col = lane%4 | B(4x8) row = lane%4, col = lane/4 |
+// C(8x8) row = lane/4, cols = 2*(lane%4) + {0,1}.
+// ids: I, D, S (3 x 49, shared). sm: 3 * 16 * PP + 98 doubles of scratch.
 // ---------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ const double* warp_propagator(const double* ids, double* sm, double dt, int lane) {
-    double* Ah = sm;
-    double* E = Ah + PD * PD;
-    double* Phi = E + PD * PD;
-    double* P = Phi + PD * PD;
-    double* T = P + PD * PD;
-    double* LU = T + PD * PD;        // 49: I, factorised in place (Gauss-Jordan -> I^-1)
+#define PP 20      // pitch (doubles): bank = (8 row + 2 col) mod 32 -> conflict-free operand loads per half-warp
+#define PROP_SCRATCH_DOUBLES (3 * 16 * PP + 98)
+
+__device__ __forceinline__ void dmma(double& d0, double& d1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+// accumulator fragments of a 16x16 matrix: c[(rt*2+ct)*2 + i] = M[rt*8 + lane/4][ct*8 + 2*(lane%4) + i]
+__device__ __forceinline__ void frag_store_c(double* M, const double* c, int lane) {
+    const int r = lane >> 2, q = (lane & 3) * 2;
+#pragma unroll
+    for (int rt = 0; rt < 2; rt++)
+#pragma unroll
+        for (int ct = 0; ct < 2; ct++)
+            *reinterpret_cast<double2*>(&M[(rt * 8 + r) * PP + ct * 8 + q]) = make_double2(c[(rt * 2 + ct) * 2], c[(rt * 2 + ct) * 2 + 1]);
+}
+__device__ __forceinline__ void frag_load_c(const double* M, double* c, int lane) {
+    const int r = lane >> 2, q = (lane & 3) * 2;
+#pragma unroll
+    for (int rt = 0; rt < 2; rt++)
+#pragma unroll
+        for (int ct = 0; ct < 2; ct++) {
+            const double2 v = *reinterpret_cast<const double2*>(&M[(rt * 8 + r) * PP + ct * 8 + q]);
+            c[(rt * 2 + ct) * 2] = v.x; c[(rt * 2 + ct) * 2 + 1] = v.y;
+        }
+}
+// left-operand fragments: a[rt*4 + kt] = M[rt*8 + lane/4][kt*4 + lane%4]
+__device__ __forceinline__ void frag_load_a(const double* M, double* a, int lane) {
+#pragma unroll
+    for (int rt = 0; rt < 2; rt++)
+#pragma unroll
+        for (int kt = 0; kt < 4; kt++) a[rt * 4 + kt] = M[(rt * 8 + (lane >> 2)) * PP + kt * 4 + (lane & 3)];
+}
+// right-operand fragments: b[kt*NCT + ct] = M[kt*4 + lane%4][ct*8 + lane/4]
+template <int NCT>
+__device__ __forceinline__ void frag_load_b(const double* M, double* b, int lane) {
+#pragma unroll
+    for (int kt = 0; kt < 4; kt++)
+#pragma unroll
+        for (int ct = 0; ct < NCT; ct++) b[kt * NCT + ct] = M[(kt * 4 + (lane & 3)) * PP + ct * 8 + (lane >> 2)];
+}
+// c (16 x 8*NCT, accumulator fragments) += a (16x16) * b (16 x 8*NCT)
+template <int NCT>
+__device__ __forceinline__ void frag_mma(double* c, const double* a, const double* b) {
+#pragma unroll
+    for (int rt = 0; rt < 2; rt++)
+#pragma unroll
+        for (int ct = 0; ct < NCT; ct++)
+#pragma unroll
+            for (int kt = 0; kt < 4; kt++) dmma(c[(rt * NCT + ct) * 2], c[(rt * NCT + ct) * 2 + 1], a[rt * 4 + kt], b[kt * NCT + ct]);
+}
+
+// Returns this lane's accumulator fragments of F (16x8): f[rt*2 + i] = F[rt*8 + lane/4][2*(lane%4) + i].
+__device__ __forceinline__ void warp_propagator(const double* ids, double* sm, double dt, int lane, double* f) {
+    double* M0 = sm;                 // A h, later B = [0; I^-1]
+    double* M1 = M0 + 16 * PP;       // P / Phi / E in operand layout
+    double* M2 = M1 + 16 * PP;       // F in operand layout
+    double* LU = M2 + 16 * PP;       // 49: I, factorised in place (Gauss-Jordan -> I^-1)
     double* Iinv = LU + 49;          // 49
     // ---- I^-1 by Gauss-Jordan with partial pivoting (lane-parallel over columns of [I | 1])
     for (int i = lane; i < 49; i += 32) { LU[i] = ids[i]; Iinv[i] = (i / 7 == i % 7) ? 1.0 : 0.0; }
@@ -154,24 +230,24 @@ __device__ __forceinline__ const double* warp_propagator(const double* ids, doub
         __syncwarp();
         if (lane < 14) { double* M = lane < 7 ? LU : Iinv; M[k * 7 + lane % 7] /= d; }
         __syncwarp();
-        double f[7];
+        double fk[7];
 #pragma unroll
-        for (int i = 0; i < 7; i++) f[i] = LU[i * 7 + k];
+        for (int i = 0; i < 7; i++) fk[i] = LU[i * 7 + k];
         __syncwarp();
         if (lane < 14) {
             double* M = lane < 7 ? LU : Iinv; const int j = lane % 7;
             const double pk = M[k * 7 + j];
 #pragma unroll
-            for (int i = 0; i < 7; i++) if (i != k) M[i * 7 + j] -= f[i] * pk;
+            for (int i = 0; i < 7; i++) if (i != k) M[i * 7 + j] -= fk[i] * pk;
         }
         __syncwarp();
     }
-    // ---- A (unscaled) into Ah, row-sum norm
-    for (int idx = lane; idx < PD * PD; idx += 32) {
-        const int i = idx / PD, j = idx - i * PD;
+    // ---- A (unscaled, zero-padded to 16 x PP) into M0, row-sum norm
+    for (int idx = lane; idx < 16 * PP; idx += 32) {
+        const int i = idx / PP, j = idx - i * PP;
         double v = 0;
         if (i < 7) v = (j == i + 7) ? 1.0 : 0.0;
-        else {
+        else if (i < PD && j < PD) {
             const double* M = ids + (j < 7 ? 98 : 49);   // S for the q block, D for the qdot block
             const int jj = j < 7 ? j : j - 7;
             double acc = 0;
@@ -179,63 +255,97 @@ __device__ __forceinline__ const double* warp_propagator(const double* ids, doub
             for (int k = 0; k < 7; k++) acc = fma(Iinv[(i - 7) * 7 + k], M[k * 7 + jj], acc);
             v = -acc;
         }
-        Ah[idx] = v;
+        M0[idx] = v;
     }
     __syncwarp();
     double nrm = 0;
-    if (lane < PD) { for (int j = 0; j < PD; j++) nrm += fabs(Ah[lane * PD + j]); }
+    if (lane < PD) { for (int j = 0; j < PD; j++) nrm += fabs(M0[lane * PP + j]); }
     for (int o = 16; o > 0; o >>= 1) nrm = fmax(nrm, __shfl_xor_sync(0xffffffffu, nrm, o));
     nrm *= dt;
     int s = 0;
     while (nrm > 0.25 && s < 40) { nrm *= 0.5; s++; }
     const double h = ldexp(dt, -s);
-    for (int idx = lane; idx < PD * PD; idx += 32) {
-        Ah[idx] *= h;
-        const double id = (idx / PD == idx % PD) ? 1.0 : 0.0;
-        E[idx] = id; Phi[idx] = id; P[idx] = id;
-    }
+    for (int idx = lane; idx < 16 * PP; idx += 32) M0[idx] *= h;
     __syncwarp();
-    for (int k = 1; k <= 14; k++) {
-        warp_matmul14(P, Ah, T, PD, lane, 1.0 / k);      // P_k = P_{k-1} (A h) / k
-        __syncwarp();
-        for (int idx = lane; idx < PD * PD; idx += 32) { const double v = T[idx]; P[idx] = v; E[idx] += v; Phi[idx] += v / (k + 1); }
-        __syncwarp();
-    }
-    // F = h * Phi * B = h * Phi[:, 7:14] * I^-1   (14 x 7), kept in P; T is scratch
-    double* F = P;
-    for (int idx = lane; idx < PD * 7; idx += 32) {
-        const int i = idx / 7, j = idx - i * 7;
-        double acc = 0;
+    // ---- Taylor: P_1 = A h; P_k = P_{k-1} (A h) / k; E = 1 + sum P_k; Phi = 1 + sum P_k / (k+1)
+    double bA[8], P[8], E[8], Phi[8];
+    frag_load_b<2>(M0, bA, lane);
+    frag_load_c(M0, P, lane);
 #pragma unroll
-        for (int k = 0; k < 7; k++) acc = fma(Phi[i * PD + 7 + k], Iinv[k * 7 + j], acc);
-        T[idx] = acc * h;
+    for (int t = 0; t < 8; t++) {
+        const int row = (t >> 2) * 8 + (lane >> 2), col = ((t >> 1) & 1) * 8 + (lane & 3) * 2 + (t & 1);
+        const double id = (row == col) ? 1.0 : 0.0;
+        E[t] = id + P[t]; Phi[t] = id + P[t] / 2.0;
+    }
+    for (int k = 2; k <= 14; k++) {
+        frag_store_c(M1, P, lane);
+        __syncwarp();
+        double a[8];
+        frag_load_a(M1, a, lane);
+#pragma unroll
+        for (int t = 0; t < 8; t++) P[t] = 0.0;
+        frag_mma<2>(P, a, bA);
+        const double inv = 1.0 / k;
+#pragma unroll
+        for (int t = 0; t < 8; t++) { P[t] *= inv; E[t] += P[t]; Phi[t] += P[t] / (k + 1); }
+        __syncwarp();
+    }
+    // ---- F = h * Phi * B,  B[7 + r][c] = I^-1[r][c]  (16 x 8 operand in M0)
+    frag_store_c(M1, Phi, lane);
+    for (int idx = lane; idx < 16 * PP; idx += 32) {
+        const int i = idx / PP, j = idx - i * PP;
+        M0[idx] = (i >= 7 && i < PD && j < 7) ? Iinv[(i - 7) * 7 + j] : 0.0;
     }
     __syncwarp();
-    for (int idx = lane; idx < PD * 7; idx += 32) F[idx] = T[idx];
+    {
+        double a[8], b[4];
+        frag_load_a(M1, a, lane);
+        frag_load_b<1>(M0, b, lane);
+#pragma unroll
+        for (int t = 0; t < 4; t++) f[t] = 0.0;
+        frag_mma<1>(f, a, b);
+#pragma unroll
+        for (int t = 0; t < 4; t++) f[t] *= h;
+    }
     __syncwarp();
+    // ---- undo the scaling: F <- F + E F ; E <- E E
     for (int it = 0; it < s; it++) {
-        warp_matmul14(E, F, T, 7, lane, 1.0);            // T = E F
-        __syncwarp();
-        for (int idx = lane; idx < PD * 7; idx += 32) F[idx] += T[idx];
-        __syncwarp();
-        if (it + 1 < s) {
-            warp_matmul14(E, E, T, PD, lane, 1.0);
-            __syncwarp();
-            for (int idx = lane; idx < PD * PD; idx += 32) E[idx] = T[idx];
-            __syncwarp();
+        frag_store_c(M1, E, lane);
+        {   // F (16 x 8) in operand layout
+            const int r = lane >> 2, q = (lane & 3) * 2;
+            *reinterpret_cast<double2*>(&M2[r * PP + q]) = make_double2(f[0], f[1]);
+            *reinterpret_cast<double2*>(&M2[(8 + r) * PP + q]) = make_double2(f[2], f[3]);
         }
+        __syncwarp();
+        double a[8], b[4];
+        frag_load_a(M1, a, lane);
+        frag_load_b<1>(M2, b, lane);
+        frag_mma<1>(f, a, b);
+        if (it + 1 < s) {
+            double bE[8];
+            frag_load_b<2>(M1, bE, lane);
+#pragma unroll
+            for (int t = 0; t < 8; t++) E[t] = 0.0;
+            frag_mma<2>(E, a, bE);
+        }
+        __syncwarp();
     }
-    return F;
 }
 
-// Shared memory per warp (bytes): key 2496 | stream 4*(2+416+9*table_len) | waves 3*8*table_len | ids 147*8 |
-// small 64*8. The propagator scratch (5*196+98 doubles = 8624 B) aliases the stream, which is dead by then.
-__host__ __device__ inline size_t reset_stream_words(int table_len) { return (size_t)((2 + 416 + 9 * table_len + 3) & ~3); }
-__host__ __device__ inline size_t reset_smem_per_warp(int table_len) {
-    size_t strm = 4 * reset_stream_words(table_len);
-    if (strm < (5 * PD * PD + 98) * 8) strm = (5 * PD * PD + 98) * 8;
-    return 2496 + strm + 3 * 8 * (size_t)((table_len + 1) & ~1) + 148 * 8 + 160 * 8;      // multiple of 16
+// Shared memory per warp (bytes): region A = stream words 4*(416 + 2*TL) | sign bits 7*4*ceil(TL/32) |
+// waves 3*8*TL, aliased by the propagator scratch (which runs after they are dead) | ids 148*8 | small 160*8 |
+// MT key 2496.
+__host__ __device__ inline size_t reset_stream_words(int table_len) { return (size_t)((416 + 2 * table_len + 3) & ~3); }
+__host__ __device__ inline size_t reset_sign_words(int table_len) { return (size_t)((((table_len + 31) / 32) * 7 + 3) & ~3); }
+__host__ __device__ inline size_t reset_region_a(int table_len) {
+    size_t a = 4 * reset_stream_words(table_len) + 4 * reset_sign_words(table_len) + 3 * 8 * (size_t)((table_len + 1) & ~1);
+    const size_t scratch = PROP_SCRATCH_DOUBLES * 8;
+    return ((a > scratch ? a : scratch) + 15) & ~(size_t)15;
 }
+__host__ __device__ inline size_t reset_smem_per_warp(int table_len) {
+    return reset_region_a(table_len) + 148 * 8 + 160 * 8 + 2496;          // multiple of 16
+}
+
 
 template <typename R, int NAX>
 __global__ void __launch_bounds__(RST_WARPS * 32)
@@ -245,12 +355,12 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int TL = (S.table_len + 1) & ~1, st = S.stride;   // wave pitch (even: keeps every region 16-byte aligned)
     unsigned char* wsm = smem_raw + (size_t)wid * reset_smem_per_warp(S.table_len);
-    size_t strm_bytes = 4 * reset_stream_words(S.table_len);
-    if (strm_bytes < (5 * PD * PD + 98) * 8) strm_bytes = (5 * PD * PD + 98) * 8;
-    double* strm_d = reinterpret_cast<double*>(wsm);                       // stream / propagator scratch (8-aligned first)
-    uint32_t* strm = reinterpret_cast<uint32_t*>(wsm);
-    double* wav = reinterpret_cast<double*>(wsm + strm_bytes);             // [3][TL]: sin w1 t, sin w2 t, noise
-    double* ids = wav + 3 * (size_t)TL;                                    // [148]
+    double* scratch = reinterpret_cast<double*>(wsm);                      // propagator scratch aliases region A
+    uint32_t* strm = reinterpret_cast<uint32_t*>(wsm);                     // compact stream: head | 7 x 4 amplitude words | tail
+    uint32_t* sbits = strm + reset_stream_words(S.table_len);              // [7][SW] sign bits
+    const int SW = (S.table_len + 31) / 32;
+    double* wav = reinterpret_cast<double*>(sbits + reset_sign_words(S.table_len));   // [3][TL]: sin w1 t, sin w2 t, noise
+    double* ids = reinterpret_cast<double*>(wsm + reset_region_a(S.table_len));   // [148]
     double* sml = ids + 148;                                               // [160] small per-env scratch
     uint32_t* key = reinterpret_cast<uint32_t*>(sml + 160);                // [624]
     // sml layout: 0..13 a1[7],a2[7] | 16..57 shift[42] | 58,59 fmax | 64..75 first three table rows [3][4] | 80..159 obs row (as float)
@@ -273,21 +383,23 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
         for (int i = lane; i < MT_N; i += 32) key[i] = gkey[i];
         int pos = (int)gkey[MT_N];
         __syncwarp();
-        const int W = K.ctor_skip + 416 + 9 * L;
-        for (int have = 0; have < W;) {
-            if (pos >= MT_N) { mt_twist_warp(key, lane); pos = 0; }
-            const int take = min(MT_N - pos, W - have);
-            for (int i = lane; i < take; i += 32) strm[have + i] = mt_temper(key[pos + i]);
-            have += take; pos += take;
+        // draw order of initialize_movement: [ctor rand()] mag f1 f2 noise[L] | per axis a1 a2 sign[L] | I D S
+        // noise (3 x 49) shifts (42) force scales (2). Full words are kept for the fp64 draws, one bit per sign draw.
+        const int o_mag = 0, o_f1 = 2, o_f2 = 4, o_noise = 6;
+        const int o_axis = o_noise + 2 * L;                     // 7 x (a1, a2) = 4 words each
+        const int o_mat = o_axis + 28;                          // I, D, S: 49 x 2 each
+        const int o_shift = o_mat + 294, o_fsh = o_shift + 84, o_fel = o_fsh + 2;
+        mt_skip(key, pos, K.ctor_skip, lane);
+        mt_fill_words(key, pos, strm, o_axis, lane);
+        for (int j = 0; j < 7; j++) {
+            mt_fill_words(key, pos, strm + o_axis + 4 * j, 4, lane);
+            if (j < NAX && ((meta >> j) & 1)) mt_fill_bits(key, pos, sbits + j * SW, L, lane);
+            else mt_skip(key, pos, L, lane);
         }
+        mt_fill_words(key, pos, strm + o_mat, 382, lane);
         __syncwarp();
         for (int i = lane; i < MT_N; i += 32) gkey[i] = key[i];
         if (lane == 0) gkey[MT_N] = (uint32_t)pos;
-        // stream offsets (draw order of initialize_movement)
-        const int o_mag = K.ctor_skip, o_f1 = o_mag + 2, o_f2 = o_mag + 4, o_noise = o_mag + 6;
-        const int o_axis = o_noise + 2 * L;                     // per axis: a1 (2), a2 (2), sign (L)
-        const int o_mat = o_axis + 7 * (4 + L);                 // I, D, S: 49 x 2 each
-        const int o_shift = o_mat + 294, o_fsh = o_shift + 84, o_fel = o_fsh + 2;
         // ---- tremor magnitude (:198-199)
         const double mag = __dadd_rn(K.amp_lo, __dmul_rn(rs_sample(strm, o_mag), __dsub_rn(K.amp_hi, K.amp_lo)));
         // ---- generate_tremor_frequency (tremor:5-21): f1, f2, white noise, time base, the two harmonics
@@ -303,7 +415,7 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
         }
         // ---- per-axis amplitudes (tremor:24-28): lanes 0..13 take one pow each
         if (lane < 14) {
-            const int j = lane >> 1, o = o_axis + j * (4 + L) + 2 * (lane & 1);
+            const int j = lane >> 1, o = o_axis + 4 * j + 2 * (lane & 1);
             const double db = (lane & 1) ? rs_uniform(strm, o, -20.0, -10.0) : rs_uniform(strm, o, -5.0, 0.0);
             sml[(lane & 1) * 7 + j] = pow(10.0, __ddiv_rn(db, 20.0));
         }
@@ -350,7 +462,7 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
                     const double jm = __dmul_rn(c_JMAX[j], mag);
                     v = __dmul_rn(__dadd_rn(-1.0, __ddiv_rn(__dmul_rn(2.0, __dsub_rn(gk, mn[j])), __dsub_rn(mx[j], mn[j]))), jm);
                     if (isnan(v) || isinf(v)) v = 0.0;                                                  // tremor:67
-                    if ((strm[o_axis + j * (4 + L) + 4 + k] & 1u) == 0) v = -v;                         // choice([-1, 1]) (tremor:70)
+                    if (((sbits[j * SW + (k >> 5)] >> (k & 31)) & 1u) == 0) v = -v;                     // choice([-1, 1]) (tremor:70)
                 }
                 row[j] = (R)v;
             }
@@ -413,9 +525,16 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
                 reinterpret_cast<float4*>(obs + (size_t)e * 80)[lane] = reinterpret_cast<const float4*>(s_ob)[lane];
         }
         __syncwarp();
-        // ---- 3. propagator from this episode's I, D, S; scratch aliases the (now dead) stream
-        const double* F = warp_propagator(ids, strm_d, K.dt, lane);
-        for (int idx = lane; idx < 49; idx += 32) *exo_word(S.G, exo_g_word(idx / 7, idx % 7), e, st) = (R)F[idx];   // rows 0..6
+        // ---- 3. propagator from this episode's I, D, S on the fp64 tensor cores; scratch aliases region A (dead by now)
+        {
+            double f[4];
+            warp_propagator(ids, scratch, K.dt, lane, f);
+            const int row = lane >> 2, col = (lane & 3) * 2;               // rows 0..6 of F are in the first row tile
+            if (row < 7) {
+                *exo_word(S.G, exo_g_word(row, col), e, st) = (R)f[0];
+                if (col + 1 < 7) *exo_word(S.G, exo_g_word(row, col + 1), e, st) = (R)f[1];
+            }
+        }
         __syncwarp();
     }
 }
