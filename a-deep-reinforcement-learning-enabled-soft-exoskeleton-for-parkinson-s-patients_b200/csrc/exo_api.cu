@@ -223,7 +223,7 @@ extern "C" int exo_set_env_types(ExoHandle* h, const uint8_t* seq, const int32_t
         }
         if (bits >> 4) nax = 7;
         if (motion_id[e] < 0 || motion_id[e] >= h->n_motions) return fail(EXO_ERR_ARG, "env %d: motion id %d out of range", e, motion_id[e]);
-        meta[e] = bits | (motion_id[e] << 8);
+        meta[e] = bits | (motion_id[e] << 8) | (h->motion_len[motion_id[e]] << 16);   // episode length rides along: no dependent load in the kernels
     }
     h->nax = nax;
     int* dmeta = h->cfg.precision == EXO_F32 ? h->Af.meta : h->Ad.meta;

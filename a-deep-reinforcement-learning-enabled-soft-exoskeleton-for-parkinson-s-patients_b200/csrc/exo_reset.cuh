@@ -50,10 +50,10 @@ __device__ __forceinline__ void mt_twist_warp(uint32_t* s, int lane) {
             const int m = i + MT_M < MT_N ? i + MT_M : i + MT_M - MT_N;
             v = s[m] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
         }
-        __syncwarp();
+        __syncwarp();                 // all reads of this batch precede its writes; the next batch reads nothing this one wrote
         if (i < MT_N) s[i] = v;
-        __syncwarp();
     }
+    __syncwarp();
 }
 
 // 32 envs per warp: each lane runs init_genrand for its env, 32 words at a time, through a shared tile so the
@@ -91,11 +91,15 @@ static __constant__ double c_S7[49] = {
     2.670, 0, 0, 8.670, 0, 0, 0,           0, 0, 0, 0, 0.756, 0.018, 0.291,   0, 0, 0, 0, 0.018, 0.992, -0.099,
     0, 0, 0, 0, 0.291, -0.099, 2.920};
 static __constant__ double c_JMAX[7] = {2.5, 5, 10, 5, 5, 0.5, 0.5};    // generate_parkinson_tremor.py:59
+// 1/k for the Taylor series of the propagator (a division would take the slow path on every exact zero of the
+// padded 16x16 operands: 38 % of the kernel's instructions in the r01c profile)
+static __constant__ double c_RCP[16] = {0.0, 1.0, 1.0 / 2, 1.0 / 3, 1.0 / 4, 1.0 / 5, 1.0 / 6, 1.0 / 7, 1.0 / 8, 1.0 / 9, 1.0 / 10,
+                                        1.0 / 11, 1.0 / 12, 1.0 / 13, 1.0 / 14, 1.0 / 15};
 
 // legacy random_sample from two consecutive 32-bit outputs of the stream
 __device__ __forceinline__ double rs_sample(const uint32_t* strm, int idx) {
     const uint32_t a = strm[idx] >> 5, b = strm[idx + 1] >> 6;
-    return __ddiv_rn(__dadd_rn(__dmul_rn((double)a, 67108864.0), (double)b), 9007199254740992.0);
+    return __dmul_rn(__dadd_rn(__dmul_rn((double)a, 67108864.0), (double)b), 1.1102230246251565e-16);   // / 2^53, exact
 }
 __device__ __forceinline__ double rs_uniform(const uint32_t* strm, int idx, double lo, double hi) {   // lo + (hi-lo)*u
     return __dadd_rn(lo, __dmul_rn(__dsub_rn(hi, lo), rs_sample(strm, idx)));
@@ -275,7 +279,7 @@ __device__ __forceinline__ void warp_propagator(const double* ids, double* sm, d
     for (int t = 0; t < 8; t++) {
         const int row = (t >> 2) * 8 + (lane >> 2), col = ((t >> 1) & 1) * 8 + (lane & 3) * 2 + (t & 1);
         const double id = (row == col) ? 1.0 : 0.0;
-        E[t] = id + P[t]; Phi[t] = id + P[t] / 2.0;
+        E[t] = id + P[t]; Phi[t] = id + P[t] * 0.5;
     }
     for (int k = 2; k <= 14; k++) {
         frag_store_c(M1, P, lane);
@@ -285,9 +289,9 @@ __device__ __forceinline__ void warp_propagator(const double* ids, double* sm, d
 #pragma unroll
         for (int t = 0; t < 8; t++) P[t] = 0.0;
         frag_mma<2>(P, a, bA);
-        const double inv = 1.0 / k;
+        const double inv = c_RCP[k], inv1 = c_RCP[k + 1];
 #pragma unroll
-        for (int t = 0; t < 8; t++) { P[t] *= inv; E[t] += P[t]; Phi[t] += P[t] / (k + 1); }
+        for (int t = 0; t < 8; t++) { P[t] *= inv; E[t] += P[t]; Phi[t] = fma(P[t], inv1, Phi[t]); }
         __syncwarp();
     }
     // ---- F = h * Phi * B,  B[7 + r][c] = I^-1[r][c]  (16 x 8 operand in M0)
@@ -333,17 +337,20 @@ __device__ __forceinline__ void warp_propagator(const double* ids, double* sm, d
 }
 
 // Shared memory per warp (bytes): region A = stream words 4*(416 + 2*TL) | sign bits 7*4*ceil(TL/32) |
-// waves 3*8*TL, aliased by the propagator scratch (which runs after they are dead) | ids 148*8 | small 160*8 |
-// MT key 2496.
+// waves 2*8*TL (sin w1 t, sin w2 t; first the MT key, 2496 B, dead before the waves are written); the whole of
+// region A is aliased by the propagator scratch (which runs after all of it is dead) | ids 148*8 | small 160*8.
+// 12.5 KB per warp at table_len 347 -> 4 blocks of 4 warps per SM.
 __host__ __device__ inline size_t reset_stream_words(int table_len) { return (size_t)((416 + 2 * table_len + 3) & ~3); }
 __host__ __device__ inline size_t reset_sign_words(int table_len) { return (size_t)((((table_len + 31) / 32) * 7 + 3) & ~3); }
 __host__ __device__ inline size_t reset_region_a(int table_len) {
-    size_t a = 4 * reset_stream_words(table_len) + 4 * reset_sign_words(table_len) + 3 * 8 * (size_t)((table_len + 1) & ~1);
+    size_t w = 2 * 8 * (size_t)((table_len + 1) & ~1);
+    if (w < 2496) w = 2496;
+    size_t a = 4 * reset_stream_words(table_len) + 4 * reset_sign_words(table_len) + w;
     const size_t scratch = PROP_SCRATCH_DOUBLES * 8;
     return ((a > scratch ? a : scratch) + 15) & ~(size_t)15;
 }
 __host__ __device__ inline size_t reset_smem_per_warp(int table_len) {
-    return reset_region_a(table_len) + 148 * 8 + 160 * 8 + 2496;          // multiple of 16
+    return reset_region_a(table_len) + 148 * 8 + 160 * 8;                 // multiple of 16
 }
 
 
@@ -359,10 +366,10 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
     uint32_t* strm = reinterpret_cast<uint32_t*>(wsm);                     // compact stream: head | 7 x 4 amplitude words | tail
     uint32_t* sbits = strm + reset_stream_words(S.table_len);              // [7][SW] sign bits
     const int SW = (S.table_len + 31) / 32;
-    double* wav = reinterpret_cast<double*>(sbits + reset_sign_words(S.table_len));   // [3][TL]: sin w1 t, sin w2 t, noise
+    double* wav = reinterpret_cast<double*>(sbits + reset_sign_words(S.table_len));   // [2][TL]: sin w1 t, sin w2 t
+    uint32_t* key = reinterpret_cast<uint32_t*>(wav);                      // [624] MT key: dead before wav is written
     double* ids = reinterpret_cast<double*>(wsm + reset_region_a(S.table_len));   // [148]
     double* sml = ids + 148;                                               // [160] small per-env scratch
-    uint32_t* key = reinterpret_cast<uint32_t*>(sml + 160);                // [624]
     // sml layout: 0..13 a1[7],a2[7] | 16..57 shift[42] | 58,59 fmax | 64..75 first three table rows [3][4] | 80..159 obs row (as float)
     float* s_ob = reinterpret_cast<float*>(sml + 80);
 
@@ -377,7 +384,7 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
         if (!list && mask != nullptr && mask[e] == 0) continue;
         const int meta = S.meta[e];
         const int mid = (meta >> 8) & 0xff;
-        const int L = S.motion_len[mid];
+        const int L = meta >> 16;
         // ---- 1. MT19937: key -> shared, generate the episode's outputs into the stream
         uint32_t* gkey = S.mt + (size_t)e * EXO_MT_PITCH;
         for (int i = lane; i < MT_N; i += 32) key[i] = gkey[i];
@@ -400,6 +407,7 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
         __syncwarp();
         for (int i = lane; i < MT_N; i += 32) gkey[i] = key[i];
         if (lane == 0) gkey[MT_N] = (uint32_t)pos;
+        __syncwarp();                                           // the key's shared copy is dead: its space becomes wav
         // ---- tremor magnitude (:198-199)
         const double mag = __dadd_rn(K.amp_lo, __dmul_rn(rs_sample(strm, o_mag), __dsub_rn(K.amp_hi, K.amp_lo)));
         // ---- generate_tremor_frequency (tremor:5-21): f1, f2, white noise, time base, the two harmonics
@@ -411,7 +419,6 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
             const double t = (k == L - 1) ? stop : __dmul_rn((double)k, tstep);
             wav[k] = sin(__dmul_rn(w1c, t));
             wav[TL + k] = sin(__dmul_rn(w2c, t));
-            wav[2 * TL + k] = __dmul_rn(rs_sample(strm, o_noise + 2 * k), 0.001);
         }
         // ---- per-axis amplitudes (tremor:24-28): lanes 0..13 take one pow each
         if (lane < 14) {
@@ -442,25 +449,33 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
 #pragma unroll
         for (int j = 0; j < NAX; j++) { a1[j] = sml[j]; a2[j] = sml[7 + j]; mn[j] = INFINITY; mx[j] = -INFINITY; }
         for (int k = lane; k < L; k += 32) {
-            const double w1 = wav[k], w2 = wav[TL + k], nz = wav[2 * TL + k];
+            const double w1 = wav[k], w2 = wav[TL + k], nz = __dmul_rn(rs_sample(strm, o_noise + 2 * k), 0.001);   // tremor:12
 #pragma unroll
             for (int j = 0; j < NAX; j++) {
                 const double gk = __dadd_rn(__dadd_rn(__dmul_rn(a1[j], w1), __dmul_rn(a2[j], w2)), nz);
                 mn[j] = fmin(mn[j], gk); mx[j] = fmax(mx[j], gk);
             }
         }
+        // (g - min) / (max - min) as a correctly rounded division from ONE reciprocal per axis (Markstein: y = RN(1/d),
+        // q = RN(x y), r = x - d q exactly, RN(q + r y) = RN(x / d)) instead of a ~25-instruction division per sample
+        double dd[NAX], ry[NAX], jm[NAX];
 #pragma unroll
-        for (int j = 0; j < NAX; j++) { mn[j] = warp_min(mn[j]); mx[j] = warp_max(mx[j]); }
+        for (int j = 0; j < NAX; j++) {
+            mn[j] = warp_min(mn[j]); mx[j] = warp_max(mx[j]);
+            dd[j] = __dsub_rn(mx[j], mn[j]); ry[j] = __drcp_rn(dd[j]); jm[j] = __dmul_rn(c_JMAX[j], mag);
+        }
         for (int k = lane; k < L; k += 32) {
-            const double w1 = wav[k], w2 = wav[TL + k], nz = wav[2 * TL + k];
+            const double w1 = wav[k], w2 = wav[TL + k], nz = __dmul_rn(rs_sample(strm, o_noise + 2 * k), 0.001);
             R row[4 * NAXV];
 #pragma unroll
             for (int j = 0; j < 4 * NAXV; j++) {
                 double v = 0.0;
                 if (j < NAX && ((meta >> j) & 1)) {
                     const double gk = __dadd_rn(__dadd_rn(__dmul_rn(a1[j], w1), __dmul_rn(a2[j], w2)), nz);
-                    const double jm = __dmul_rn(c_JMAX[j], mag);
-                    v = __dmul_rn(__dadd_rn(-1.0, __ddiv_rn(__dmul_rn(2.0, __dsub_rn(gk, mn[j])), __dsub_rn(mx[j], mn[j]))), jm);
+                    const double x = __dmul_rn(2.0, __dsub_rn(gk, mn[j]));
+                    const double q0 = __dmul_rn(x, ry[j]);
+                    const double q = __fma_rn(__fma_rn(-dd[j], q0, x), ry[j], q0);
+                    v = __dmul_rn(__dadd_rn(-1.0, q), jm[j]);
                     if (isnan(v) || isinf(v)) v = 0.0;                                                  // tremor:67
                     if (((sbits[j * SW + (k >> 5)] >> (k & 31)) & 1u) == 0) v = -v;                     // choice([-1, 1]) (tremor:70)
                 }
@@ -494,31 +509,32 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
 #pragma unroll
             for (int k = 0; k < 3; k++) el_old[k] = *exo_word(S.state, W_ELREF + k, e, st);
             __syncwarp();
+            if (lane < 7) {                                                           // one actuator per lane
+                const int i = lane;
+                R a2[3];
+                if (i < 2) affine(P.R4, P.p4, C.off_alk[i], a2);
+                else affine(P.R2, P.p2, C.off_hum[i], a2);
+#pragma unroll
+                for (int k = 0; k < 3; k++) {
+                    a2[k] += (R)sml[16 + (2 * i + 1) * 3 + k];
+                    const R prev = a2[k] - (i < 2 ? el_old[k] : C.sh_ref[k]);      // stale elbow ref on the first read (:237)
+                    const R cur = a2[k] - (i < 2 ? P.elref[k] : C.sh_ref[k]);      // refreshed before the second (:238,249)
+                    *exo_word(S.state, W_POSVEC + i * 3 + k, e, st) = cur;
+                    s_ob[26 + i * 3 + k] = (float)prev; s_ob[47 + i * 3 + k] = (float)cur;
+                }
+            }
+            if (lane < 14) s_ob[lane] = 0.0f;                                         // force history zeroed (:195)
             if (lane == 0) {
 #pragma unroll
                 for (int k = 0; k < 3; k++) *exo_word(S.state, W_ELREF + k, e, st) = P.elref[k];
-#pragma unroll
-                for (int i = 0; i < 7; i++) {
-                    R a2[3];
-                    if (i < 2) affine(P.R4, P.p4, C.off_alk[i], a2);
-                    else affine(P.R2, P.p2, C.off_hum[i], a2);
-#pragma unroll
-                    for (int k = 0; k < 3; k++) {
-                        a2[k] += (R)sml[16 + (2 * i + 1) * 3 + k];
-                        const R prev = a2[k] - (i < 2 ? el_old[k] : C.sh_ref[k]);      // stale elbow ref on the first read (:237)
-                        const R cur = a2[k] - (i < 2 ? P.elref[k] : C.sh_ref[k]);      // refreshed before the second (:238,249)
-                        *exo_word(S.state, W_POSVEC + i * 3 + k, e, st) = cur;
-                        s_ob[26 + i * 3 + k] = (float)prev; s_ob[47 + i * 3 + k] = (float)cur;
-                    }
-                }
-                for (int i = 0; i < 14; i++) s_ob[i] = 0.0f;                          // force history zeroed (:195)
-                const R nrm[4] = {R(10), R(10), R(10), R(5)};
-                for (int h = 0; h < 3; h++)
-                    for (int j = 0; j < 4; j++) s_ob[14 + h * 4 + j] = (float)((R)sml[64 + h * 4 + j] / nrm[j]);
                 for (int k = 0; k < 3; k++) {
                     s_ob[68 + k] = (float)C.sh_ref[k]; s_ob[71 + k] = (float)P.elref[k];
                     s_ob[74 + k] = (float)C.sh_ref[k]; s_ob[77 + k] = (float)P.elref[k];
                 }
+            }
+            if (lane >= 16 && lane < 28) {                                            // tremor rows 0..2 (:502-513)
+                const int idx = lane - 16;
+                s_ob[14 + idx] = (float)((R)sml[64 + idx] / ((idx & 3) == 3 ? R(5) : R(10)));
             }
             __syncwarp();
             if (obs != nullptr && lane < 20)

@@ -50,6 +50,45 @@ __device__ __forceinline__ void ld4_ro(const V4<double>* p, double* o) {
     const double2 a = __ldg(reinterpret_cast<const double2*>(p)), b = __ldg(reinterpret_cast<const double2*>(p) + 1);
     o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
 }
+// Ordered variants: `asm volatile` keeps these in program order, so the kernel decides which loads are in flight
+// before the first dependent instruction (the compiler's own schedule put count-dependent loads in front of the
+// independent ones and spilled freshly loaded registers, serialising the memory latency).
+__device__ __forceinline__ void ld4_ord(const V4<float>* p, float* o) {
+    asm volatile("ld.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(o[0]), "=f"(o[1]), "=f"(o[2]), "=f"(o[3]) : "l"(p));
+}
+__device__ __forceinline__ void ld4_ord(const V4<double>* p, double* o) {
+    asm volatile("ld.global.v2.f64 {%0,%1}, [%2];" : "=d"(o[0]), "=d"(o[1]) : "l"(p));
+    asm volatile("ld.global.v2.f64 {%0,%1}, [%2+16];" : "=d"(o[2]), "=d"(o[3]) : "l"(p));
+}
+__device__ __forceinline__ void ld4_ro_ord(const V4<float>* p, float* o) {
+    asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(o[0]), "=f"(o[1]), "=f"(o[2]), "=f"(o[3]) : "l"(p));
+}
+__device__ __forceinline__ void ld4_ro_ord(const V4<double>* p, double* o) {
+    asm volatile("ld.global.nc.v2.f64 {%0,%1}, [%2];" : "=d"(o[0]), "=d"(o[1]) : "l"(p));
+    asm volatile("ld.global.nc.v2.f64 {%0,%1}, [%2+16];" : "=d"(o[2]), "=d"(o[3]) : "l"(p));
+}
+__device__ __forceinline__ int ld_int_ord(const int* p) {
+    int v;
+    asm volatile("ld.global.s32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float ld_ro_ord(const float* p) {
+    float v;
+    asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ double ld_ro_ord(const double* p) {
+    double v;
+    asm volatile("ld.global.nc.f64 %0, [%1];" : "=d"(v) : "l"(p));
+    return v;
+}
+// 16-byte asynchronous global -> shared copy (LDGSTS): no register, no scoreboard until cp_async_wait
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 __device__ __forceinline__ void st4(V4<float>* p, const float* o) {
     *reinterpret_cast<float4*>(p) = make_float4(o[0], o[1], o[2], o[3]);
 }
@@ -134,8 +173,12 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
                 float* __restrict__ obs, R* __restrict__ reward, uint8_t* __restrict__ done, InfoPtrs<R> info) {
     constexpr int WARPS = EXO_STEP_THREADS / 32;
     constexpr int NAXV = (NAX + 3) / 4;                               // vectors per tremor-table row
-    __shared__ __align__(16) float s_obs[WARPS][32 * EXO_OBS_PITCH];
-    __shared__ float s_act[WARPS][32 * 7];
+    // Per-warp staging (no block barrier anywhere): obs chunks 0..10 | per-episode parameter vectors, later reused for
+    // obs chunks 11..19 | the warp's 32 action rows. Pitches of 11 and 9 sixteen-byte chunks are odd: conflict-free.
+    constexpr int EPB_BYTES = (NV_EP * 32 * (int)sizeof(V4<R>) > 32 * 9 * 16) ? NV_EP * 32 * (int)sizeof(V4<R>) : 32 * 9 * 16;
+    __shared__ __align__(16) float4 s_obsA[WARPS][32 * 11];
+    __shared__ __align__(16) unsigned char s_epB[WARPS][EPB_BYTES];
+    __shared__ __align__(16) float s_act[WARPS][32 * 7];
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int wbase = blockIdx.x * EXO_STEP_THREADS + wid * 32;     // first env of this warp
@@ -144,53 +187,117 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
     if (blockIdx.x == 0 && tid == 0) S.fin_count[K.parity ^ 1] = 0;  // consumed by the previous step's reset
     if (wbase >= n) return;                                          // whole warp past the end
 
-    // ---- this warp's 32 action rows (row-major [n,7], contiguous) -> shared memory, coalesced
-    {
-        const int lim = min(32, n - wbase) * 7;
-        const float* src = actions + (size_t)wbase * 7;
-        for (int i = lane; i < lim; i += 32) s_act[wid][i] = src[i];
+    // ---- every global access of the step is issued up front, in this order and unconditionally (a lane past the end
+    //      or an idle env re-reads a valid record and discards it): counts/meta first (the second-level addresses
+    //      depend on them), then the per-episode parameters and the action rows as asynchronous global->shared copies
+    //      (no registers), then state and G as 128-bit register loads, then - one memory latency later - the three
+    //      tremor rows and the motion row addressed by counts.
+    const bool valid = e < n;
+    const int ec = valid ? e : n - 1;
+    const int c_raw = ld_int_ord(S.counts + ec);
+    const int meta = ld_int_ord(S.meta + ec);
+    V4<R>* sp = reinterpret_cast<V4<R>*>(&s_epB[wid][0]);            // [NV_EP][32]
+#pragma unroll
+    for (int v = 0; v < NV_EP; v++) {
+        const char* src = reinterpret_cast<const char*>(S.ep + (size_t)v * st + ec);
+        char* dst = reinterpret_cast<char*>(sp + v * 32 + lane);
+#pragma unroll
+        for (int h = 0; h < (int)sizeof(V4<R>) / 16; h++) cp_async16(dst + 16 * h, src + 16 * h);
     }
+    const int rows_here = min(32, n - wbase);
+    const float* asrc = actions + (size_t)wbase * 7;
+    const bool act_async = rows_here == 32 && (reinterpret_cast<size_t>(asrc) & 15) == 0;   // warp-uniform
+    float araw[7];
+    if (act_async) {                                                  // 896 contiguous bytes = 56 chunks
+        cp_async16(&s_act[wid][lane * 4], asrc + lane * 4);
+        if (lane < 24) cp_async16(&s_act[wid][(lane + 32) * 4], asrc + (lane + 32) * 4);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 7; k++) araw[k] = (lane + 32 * k < rows_here * 7) ? ld_ro_ord(asrc + lane + 32 * k) : 0.0f;
+    }
+    cp_async_commit();
+    R s[4 * NV_STATE];
+#pragma unroll
+    for (int v = 0; v < NV_STATE; v++) ld4_ord(S.state + (size_t)v * st + ec, s + 4 * v);
+    constexpr int NGV = (INFO || NAX > 4) ? NV_G : 4;
+    R g[4 * NGV];
+#pragma unroll
+    for (int v = 0; v < NGV; v++) ld4_ro_ord(S.G + (size_t)v * st + ec, g + 4 * v);
+    const R ret0 = S.ret[ec];
+    // second level (clamped so the addresses are always inside the tables; a live env has 2 <= counts <= L - 2, so
+    // the clamp never changes what a live env reads)
+    const int mid = (meta >> 8) & 0xff, L = meta >> 16;
+    const int c = min(max(c_raw, 1), S.table_len - 2);
+    R tm[4 * NAXV], tc[4 * NAXV], tp[4 * NAXV];                       // tremor rows c-1, c, c+1
+#pragma unroll
+    for (int h = 0; h < NAXV; h++) {
+        ld4_ro_ord(S.tt + ((size_t)(c - 1) * st + ec) * NAXV + h, tm + 4 * h);
+        ld4_ro_ord(S.tt + ((size_t)c * st + ec) * NAXV + h, tc + 4 * h);
+        ld4_ro_ord(S.tt + ((size_t)(c + 1) * st + ec) * NAXV + h, tp + 4 * h);
+    }
+    const R* mo = S.motion + (size_t)mid * 5 * S.max_len;
+    R mrow[5], mnext[5];
+#pragma unroll
+    for (int r = 0; r < 5; r++) {
+        mrow[r] = ld_ro_ord(mo + r * S.max_len + c);
+        mnext[r] = INFO ? ld_ro_ord(mo + r * S.max_len + c + 1) : R(0);
+    }
+    if (!act_async) {
+#pragma unroll
+        for (int k = 0; k < 7; k++) s_act[wid][lane + 32 * k] = araw[k];
+    }
+    cp_async_wait_all();
     __syncwarp();
 
-    bool live = false, fin = false;
+    const bool live = valid && c_raw < L - 1;   // an env that already reported done idles (Exoskeleton_agent_train.py:139)
+    bool fin = false;
     int v_cross = 0, v_red = 0, v_len = 0;
     R v_ret = 0, v_amp = 0;
-    int meta = 0, mid = 0, L = 0, c = 0;
-    if (e < n) {
-        meta = S.meta[e];
-        mid = (meta >> 8) & 0xff;
-        L = S.motion_len[mid];
-        c = S.counts[e];
-        live = c < L - 1;                     // an env that already reported done idles (Exoskeleton_agent_train.py:139)
-        if (!live) { done[e] = 1; reward[e] = R(0); }
-    }
+    if (valid && !live) { done[e] = 1; reward[e] = R(0); }
+    const unsigned full = 0xffffffffu;
+    const unsigned live_mask = __ballot_sync(full, live);
     if (live) {
-        const R* mo = S.motion + (size_t)mid * 5 * S.max_len;
-        // ---- resident records: 12 state vectors, 11 parameter vectors, 3 table rows, G
-        R s[4 * NV_STATE], p[4 * NV_EP];
-#pragma unroll
-        for (int v = 0; v < NV_STATE; v++) ld4(S.state + (size_t)v * st + e, s + 4 * v);
-#pragma unroll
-        for (int v = 0; v < NV_EP; v++) ld4_ro(S.ep + (size_t)v * st + e, p + 4 * v);
-        R tm[4 * NAXV], tc[4 * NAXV], tp[4 * NAXV];                 // tremor rows c-1, c, c+1
-#pragma unroll
-        for (int h = 0; h < NAXV; h++) {
-            ld4_ro(S.tt + ((size_t)(c - 1) * st + e) * NAXV + h, tm + 4 * h);
-            ld4_ro(S.tt + ((size_t)c * st + e) * NAXV + h, tc + 4 * h);
-            ld4_ro(S.tt + ((size_t)(c + 1) * st + e) * NAXV + h, tp + 4 * h);
-        }
-        constexpr int NGV = (INFO || NAX > 4) ? NV_G : 4;
-        R g[4 * NGV];
-#pragma unroll
-        for (int v = 0; v < NGV; v++) ld4_ro(S.G + (size_t)v * st + e, g + 4 * v);
-        const R ret0 = S.ret[e];
-
         float ob[80];
         // ---- transform_action (:256-266)
-        const R fm_sh = p[W_FMAX], fm_el = p[W_FMAX + 1];
+        R pf[4];
+        ld4(sp + (W_FMAX >> 2) * 32 + lane, pf);                      // staged parameter vector 10: shifts 40,41 + force maxima
+        const R fm_sh = pf[W_FMAX & 3], fm_el = pf[(W_FMAX + 1) & 3];
         R F[7];
 #pragma unroll
         for (int i = 0; i < 7; i++) F[i] = ((R(s_act[wid][lane * 7 + i]) + R(1)) / R(2)) * (i < 2 ? fm_el : fm_sh);
+        // ---- observation chunks that only need loaded data go to the staging tile NOW (frees ~44 registers for the
+        //      arithmetic below): forces[k-2], forces[k-1] (:488-501), tremor rows k-2..k (:502-513; the obs is built
+        //      after counts += 1, so rows c-1, c, c+1), prev_position_vectors (:385)
+        float4* so = &s_obsA[wid][lane * 11];
+        R fp1[7];
+#pragma unroll
+        for (int i = 0; i < 7; i++) {
+            fp1[i] = s[W_FPREV + i];
+            const R f0i = i < 2 ? K.inv_fmax_el0 : K.inv_fmax_sh0, f0 = i < 2 ? K.fmax_el0 : K.fmax_sh0;
+            if (sizeof(R) == 8) {
+                ob[i] = (c >= 3) ? (float)(fp1[i] / f0) : 0.0f;       // forces[k-2]; the history is zeroed at reset (:195)
+                ob[7 + i] = (float)(F[i] / f0);                       // forces[k-1]
+            } else {
+                ob[i] = (c >= 3) ? (float)(fp1[i] * f0i) : 0.0f;
+                ob[7 + i] = (float)(F[i] * f0i);
+            }
+        }
+        {
+            const R inrm[4] = {R(0.1), R(0.1), R(0.1), R(0.2)};
+            const R nrm[4] = {R(10), R(10), R(10), R(5)};
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                if (sizeof(R) == 8) {
+                    ob[14 + j] = (float)(tm[j] / nrm[j]); ob[18 + j] = (float)(tc[j] / nrm[j]); ob[22 + j] = (float)(tp[j] / nrm[j]);
+                } else {
+                    ob[14 + j] = (float)(tm[j] * inrm[j]); ob[18 + j] = (float)(tc[j] * inrm[j]); ob[22 + j] = (float)(tp[j] * inrm[j]);
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 21; i++) ob[26 + i] = (float)s[W_POSVEC + i];
+#pragma unroll
+        for (int ch = 0; ch < 11; ch++) so[ch] = make_float4(ob[4 * ch], ob[4 * ch + 1], ob[4 * ch + 2], ob[4 * ch + 3]);
         // ---- link-state cache -> world points (getLinkState reads, sim:129-142,194-195)
         R qb[5], qs[5];
 #pragma unroll
@@ -200,9 +307,7 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
         R el_old[3];
 #pragma unroll
         for (int k = 0; k < 3; k++) el_old[k] = s[W_ELREF + k];
-        // previous pos_vec becomes prev_position_vectors (:385) -> obs[26:47]; new pos_vec -> obs[47:68]
-#pragma unroll
-        for (int i = 0; i < 21; i++) ob[26 + i] = (float)s[W_POSVEC + i];
+        // new pos_vec -> obs[47:68]
         // ---- per actuator: endpoints, force direction, pos_vec, torque (sim:207-336, env:177-187)
         R at0 = 0, at1 = 0, at2 = 0, ty0 = 0, ty1 = 0;
         const int order[7] = {0, 1, 2, 3, 4, 6, 5};          // summation order of :395-397 (3,4,5,7,6)
@@ -218,10 +323,18 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
                 a1[0] = C.fixed[fix_of[i]][0]; a1[1] = C.fixed[fix_of[i]][1]; a1[2] = C.fixed[fix_of[i]][2];
                 affine(P.R2, P.p2, C.off_hum[i], a2);
             }
+            {   // dummy_shift_coordinates of this actuator's two ends: words 6i..6i+5 of the staged record = two vectors
+                constexpr int W0 = W_SHIFT;
+                const int w = W0 + 6 * i, va = w >> 2;
+                R pa[4], pb[4];
+                ld4(sp + va * 32 + lane, pa);
+                ld4(sp + (va + 1) * 32 + lane, pb);
 #pragma unroll
-            for (int k = 0; k < 3; k++) {
-                a1[k] += p[W_SHIFT + (2 * i) * 3 + k];
-                a2[k] += p[W_SHIFT + (2 * i + 1) * 3 + k];
+                for (int k = 0; k < 3; k++) {
+                    const int w1 = w + k, w2 = w + 3 + k;
+                    a1[k] += (w1 >> 2) == va ? pa[w1 & 3] : pb[w1 & 3];
+                    a2[k] += (w2 >> 2) == va ? pa[w2 & 3] : pb[w2 & 3];
+                }
             }
             R dx, dy, dz;
             if (sizeof(R) == 8) {   // the reference's +5 shift (sim:212) only matters at fp64 resolution
@@ -255,16 +368,6 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
             ttc[j] = (j < NAX) ? tc[j] : R(0);
             tv[j] = ttc[j] + (j < 4 ? at[j] : R(0));
         }
-        const R inrm[4] = {R(0.1), R(0.1), R(0.1), R(0.2)};
-        const R nrm[4] = {R(10), R(10), R(10), R(5)};
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            if (sizeof(R) == 8) {
-                ob[14 + j] = (float)(tm[j] / nrm[j]); ob[18 + j] = (float)(tc[j] / nrm[j]); ob[22 + j] = (float)(tp[j] / nrm[j]);
-            } else {
-                ob[14 + j] = (float)(tm[j] * inrm[j]); ob[18 + j] = (float)(tc[j] * inrm[j]); ob[22 + j] = (float)(tp[j] * inrm[j]);
-            }
-        }
         // ---- joint model: q(dt) = G * T from rest (:409-418); rows 0..3 drive the motors
         const R r2d = R(57.29577951308232087679815481410517), d2r = R(0.017453292519943295769236907684886);
         R qa[7], qt[7];
@@ -284,9 +387,8 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
             if (INFO) qt[i] = acc2 * r2d;
         }
         // ---- angle composition + position motors + one Bullet step (:421-433, oracle/minibullet.py)
-        const R tgt[5] = {(mo[4 * S.max_len + c] + qa[2]) * d2r, (mo[3 * S.max_len + c] + qa[0]) * d2r,
-                          (mo[2 * S.max_len + c] + qa[1]) * d2r, (mo[0 * S.max_len + c] + qa[3]) * d2r,
-                          mo[1 * S.max_len + c] * d2r};
+        const R tgt[5] = {(mrow[4] + qa[2]) * d2r, (mrow[3] + qa[0]) * d2r, (mrow[2] + qa[1]) * d2r, (mrow[0] + qa[3]) * d2r,
+                          mrow[1] * d2r};
         int crossed = 0;
 #pragma unroll
         for (int j = 0; j < 5; j++) {
@@ -319,10 +421,8 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
                 if (red < R(0)) { axis_cnt++; if (j < 4) arm_red = 1; }      // nan/inf -> 0 -> not counted (:302-303)
             }   // axes without a table entry: a == b == 0 -> reduction 0 -> not counted
         }
-        R fp1[7];
 #pragma unroll
         for (int i = 0; i < 7; i++) {
-            fp1[i] = s[W_FPREV + i];
             const R fp2 = s[W_FPREV2 + i];
             const R d = F[i] - R(2) * fp1[i] + fp2;
             smooth += d * d;
@@ -345,25 +445,15 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
         const int k1 = c + 1;
         S.counts[e] = k1;
 #pragma unroll
-        for (int i = 0; i < 7; i++) {
-            const R f0i = i < 2 ? K.inv_fmax_el0 : K.inv_fmax_sh0, f0 = i < 2 ? K.fmax_el0 : K.fmax_sh0;
-            if (sizeof(R) == 8) {
-                ob[i] = (c >= 3) ? (float)(fp1[i] / f0) : 0.0f;       // forces[k-2]; the history is zeroed at reset (:195)
-                ob[7 + i] = (float)(F[i] / f0);                       // forces[k-1]
-            } else {
-                ob[i] = (c >= 3) ? (float)(fp1[i] * f0i) : 0.0f;
-                ob[7 + i] = (float)(F[i] * f0i);
-            }
-        }
-#pragma unroll
         for (int k = 0; k < 3; k++) {
             ob[68 + k] = (float)C.sh_ref[k]; ob[71 + k] = (float)el_old[k];     // ref_prev (:383)
             ob[74 + k] = (float)C.sh_ref[k]; ob[77 + k] = (float)P.elref[k];    // ref (:387)
         }
-        {   // this env's observation row -> the warp's staging tile (16-byte chunks, pitch 21 chunks: conflict-free)
-            float4* so = reinterpret_cast<float4*>(&s_obs[wid][lane * EXO_OBS_PITCH]);
+        __syncwarp(live_mask);            // every live lane has read its staged parameters: the region becomes obs chunks 11..19
+        {
+            float4* sob = reinterpret_cast<float4*>(&s_epB[wid][0]) + lane * 9;
 #pragma unroll
-            for (int ch = 0; ch < 20; ch++) so[ch] = make_float4(ob[4 * ch], ob[4 * ch + 1], ob[4 * ch + 2], ob[4 * ch + 3]);
+            for (int ch = 11; ch < 20; ch++) sob[ch - 11] = make_float4(ob[4 * ch], ob[4 * ch + 1], ob[4 * ch + 2], ob[4 * ch + 3]);
         }
         const bool dn = k1 >= L - 1;
         done[e] = dn ? 1 : 0;
@@ -374,8 +464,7 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
         R amp = 0;
         if (INFO) {
             // Exoskeleton_agent_train.py:158-170 with return_original_joint_angles at the incremented counts
-            R b[7] = {mo[2 * S.max_len + k1] * d2r, mo[3 * S.max_len + k1] * d2r, mo[4 * S.max_len + k1] * d2r,
-                      mo[0 * S.max_len + k1] * d2r, mo[1 * S.max_len + k1] * d2r, R(0), R(0)};
+            R b[7] = {mnext[2] * d2r, mnext[3] * d2r, mnext[4] * d2r, mnext[0] * d2r, mnext[1] * d2r, R(0), R(0)};
             R th[7], p0[3], p1[3], p2[3];
             dh_end_effector(b, K.L1, K.L2, p0);
 #pragma unroll
@@ -406,19 +495,26 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
         if (INFO && amp < R(0)) v_amp = amp;
     }
     // ---- warp-level epilogue: every lane of the warp arrives here
-    const unsigned full = 0xffffffffu;
-    const unsigned live_mask = __ballot_sync(full, live);
     const unsigned fin_mask = __ballot_sync(full, fin);
     if (live_mask == 0) return;
-    // observation tile -> row-major [n,80]: the warp's 32 rows are 10 240 contiguous bytes, 128-bit coalesced stores
+    __syncwarp();
+    // staging tiles -> row-major [n,80]: the warp's 32 rows are 10 240 contiguous bytes; both tiles are read
+    // linearly (conflict-free LDS.128) and written as 128-bit stores, 176 B + 144 B per row
     if (obs != nullptr) {
         float4* dst = reinterpret_cast<float4*>(obs + (size_t)wbase * 80);
-        const float4* src = reinterpret_cast<const float4*>(&s_obs[wid][0]);
-#pragma unroll 4
-        for (int it = 0; it < 20; it++) {
+        const float4* srcA = &s_obsA[wid][0];
+        const float4* srcB = reinterpret_cast<const float4*>(&s_epB[wid][0]);
+#pragma unroll
+        for (int it = 0; it < 11; it++) {
             const int v = it * 32 + lane;
-            const int row = v / 20, ch = v - row * 20;
-            if ((live_mask >> row) & 1u) dst[v] = src[row * (EXO_OBS_PITCH / 4) + ch];
+            const int row = v / 11, ch = v - row * 11;
+            if ((live_mask >> row) & 1u) dst[row * 20 + ch] = srcA[v];
+        }
+#pragma unroll
+        for (int it = 0; it < 9; it++) {
+            const int v = it * 32 + lane;
+            const int row = v / 9, ch = v - row * 9;
+            if ((live_mask >> row) & 1u) dst[row * 20 + 11 + ch] = srcB[v];
         }
     }
     // finished envs -> the auto-reset work list (one atomic per warp that has any)

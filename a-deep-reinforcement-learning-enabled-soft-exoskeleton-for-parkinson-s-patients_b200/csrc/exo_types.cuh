@@ -16,7 +16,7 @@
 #define EXO_MAX_LEN 512          // >= longest reference motion (347 rows)
 
 #define EXO_STEP_THREADS 64      // 2 warps per block: 65 536 envs -> 1024 blocks ~ 6.9 per SM (balanced single wave)
-#define EXO_STEP_MIN_BLOCKS 8    // <= 128 registers per thread: all 14 warps an SM owns at 65 536 envs stay resident
+#define EXO_STEP_MIN_BLOCKS 7    // <= 144 registers per thread: the 7 blocks (14 warps) an SM owns at 65 536 envs stay resident
 #define EXO_OBS_PITCH 84         // floats per staged observation row: 21 16-byte chunks, odd -> conflict-free STS.128
 
 // ---- word offsets inside the per-env records -------------------------------------------------------------
@@ -59,7 +59,7 @@ struct EnvArrays {
     V4<R>* tt;       // [table_len][stride][NAXP/4]  tremor table, time-major: one step reads rows c-1, c, c+1
     R* ret;          // [stride] running episode return
     int* counts;     // [stride] self.counts
-    int* meta;       // [stride] bits 0-6 tremor_sequence, bits 8-15 motion id
+    int* meta;       // [stride] bits 0-6 tremor_sequence, bits 8-15 motion id, bits 16-31 motion length (max_count)
     double* IDS;     // [n][EXO_IDS_PITCH]  I_current, D_current, S_current (fp64, env-major)
     double* mag;     // [stride] tremor_magnitude
     uint32_t* mt;    // [n][EXO_MT_PITCH]   numpy legacy MT19937 key + position (env-major)

@@ -104,6 +104,7 @@ class BatchedExoskeletonEnv(object):
         self._flip = 0
         self._reward = torch.zeros(self.n, dtype=self.real, device=dev)
         self._done = torch.zeros(self.n, dtype=torch.uint8, device=dev)
+        self._done_bool = self._done.view(torch.bool)      # the kernel writes 0/1 bytes: a view, not a conversion kernel
         self._info = None
         self._stats = torch.zeros(_capi.N_STATS, dtype=torch.float64, device=dev)
         self._host = None
@@ -166,8 +167,8 @@ class BatchedExoskeletonEnv(object):
         _capi.check(self.lib.exo_step(self.h, _ptr(a), _ptr(obs), _ptr(self._reward), _ptr(self._done), info_struct,
                                       self._stream()))
         if with_info:
-            return obs, self._reward, self._done.bool(), self._info
-        return obs, self._reward, self._done.bool()
+            return obs, self._reward, self._done_bool, self._info
+        return obs, self._reward, self._done_bool
 
     def _host_buffers(self):
         if self._host is None:

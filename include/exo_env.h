@@ -97,7 +97,7 @@ typedef enum {
     EXO_FIELD_TREMOR_TABLE,   /* real [table_len * table_axes] tremor_torque_values, time-major */
     EXO_FIELD_TREMOR_MAG,     /* f64  [1]   tremor_magnitude (:199) */
     EXO_FIELD_COUNTS,         /* i32  [1]   self.counts */
-    EXO_FIELD_META,           /* i32  [1]   bits 0-6 tremor_sequence, bits 8-15 motion id */
+    EXO_FIELD_META,           /* i32  [1]   bits 0-6 tremor_sequence, bits 8-15 motion id, bits 16-31 max_count */
     EXO_FIELD_MT_STATE,       /* u32  [625] numpy legacy MT19937 key + position */
     EXO_FIELD_EP_RETURN,      /* real [1]   running episode return */
     EXO_N_FIELDS
