@@ -38,22 +38,33 @@ __device__ __forceinline__ uint32_t mt_temper(uint32_t y) {
 }
 
 // Warp-parallel in-place twist of a 624-word key in shared memory. new[i] depends on old[i], old[i+1] and
-// (i < 227) old[i+397] / (i >= 227) new[i-227], so batches of 32 consecutive words are independent as long as the
-// batch reads complete before its writes; word 623 uses new[0].
-__device__ __forceinline__ void mt_twist_warp(uint32_t* s, int lane) {
-    for (int b = 0; b < MT_N; b += 32) {
-        const int i = b + lane;
-        uint32_t v = 0;
-        if (i < MT_N) {
-            const uint32_t cur = s[i], nxt = s[i + 1 < MT_N ? i + 1 : 0];
-            const uint32_t y = (cur & 0x80000000u) | (nxt & 0x7fffffffu);
-            const int m = i + MT_M < MT_N ? i + MT_M : i + MT_M - MT_N;
-            v = s[m] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+// (i < 227) old[i+397] / (i >= 227) new[i-227]. Rounds of 128 consecutive words (4 per lane) are independent as long
+// as a round's reads complete before its writes: what a round reads of new[] (indices >= 99 below its start) was
+// written by earlier rounds, and old[i+1] / old[i+397] lie above everything written so far. Word 623 uses new[0].
+// Five rounds with four-way instruction-level parallelism instead of twenty serial 32-word batches. One copy in
+// the kernel (__noinline__): the r01d profile showed 33 % of the stall samples waiting on instruction fetch.
+static __device__ __noinline__ void mt_twist_warp(uint32_t* s, int lane) {
+    for (int b = 0; b < MT_N; b += 128) {
+        uint32_t v[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int i = b + 32 * u + lane;
+            v[u] = 0;
+            if (i < MT_N) {
+                const uint32_t cur = s[i], nxt = s[i + 1 < MT_N ? i + 1 : 0];
+                const uint32_t y = (cur & 0x80000000u) | (nxt & 0x7fffffffu);
+                const int m = i + MT_M < MT_N ? i + MT_M : i + MT_M - MT_N;
+                v[u] = s[m] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+            }
         }
-        __syncwarp();                 // all reads of this batch precede its writes; the next batch reads nothing this one wrote
-        if (i < MT_N) s[i] = v;
+        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int i = b + 32 * u + lane;
+            if (i < MT_N) s[i] = v[u];
+        }
+        __syncwarp();
     }
-    __syncwarp();
 }
 
 // 32 envs per warp: each lane runs init_genrand for its env, 32 words at a time, through a shared tile so the
@@ -120,7 +131,7 @@ __device__ __forceinline__ double warp_max(double v) {
 // MT19937 stream consumption, warp-cooperative. `pos` is the next unread word of the shared key.
 // ---------------------------------------------------------------------------------------------------------
 // next n tempered outputs -> dst[0..n)
-__device__ __forceinline__ void mt_fill_words(uint32_t* key, int& pos, uint32_t* dst, int n, int lane) {
+static __device__ __noinline__ void mt_fill_words(uint32_t* key, int& pos, uint32_t* dst, int n, int lane) {
     for (int done = 0; done < n;) {
         if (pos >= MT_N) { mt_twist_warp(key, lane); pos = 0; }
         const int take = min(MT_N - pos, n - done);
@@ -129,7 +140,7 @@ __device__ __forceinline__ void mt_fill_words(uint32_t* key, int& pos, uint32_t*
     }
 }
 // next n outputs -> bit k of bits[] = (output k) & 1   (np.random.choice([-1, 1]) draws, tremor:70)
-__device__ __forceinline__ void mt_fill_bits(uint32_t* key, int& pos, uint32_t* bits, int n, int lane) {
+static __device__ __noinline__ void mt_fill_bits(uint32_t* key, int& pos, uint32_t* bits, int n, int lane) {
     for (int done = 0; done < n;) {
         if (pos >= MT_N) { mt_twist_warp(key, lane); pos = 0; }
         const int take = min(min(MT_N - pos, n - done), 32 - (done & 31));      // never straddles a 32-bit word
@@ -140,7 +151,7 @@ __device__ __forceinline__ void mt_fill_bits(uint32_t* key, int& pos, uint32_t* 
     }
 }
 // consume n outputs without using them (the state still has to advance)
-__device__ __forceinline__ void mt_skip(uint32_t* key, int& pos, int n, int lane) {
+static __device__ __noinline__ void mt_skip(uint32_t* key, int& pos, int n, int lane) {
     while (n > 0) {
         if (pos >= MT_N) { mt_twist_warp(key, lane); pos = 0; }
         const int take = min(MT_N - pos, n);
@@ -212,7 +223,7 @@ __device__ __forceinline__ void frag_mma(double* c, const double* a, const doubl
 }
 
 // Returns this lane's accumulator fragments of F (16x8): f[rt*2 + i] = F[rt*8 + lane/4][2*(lane%4) + i].
-__device__ __forceinline__ void warp_propagator(const double* ids, double* sm, double dt, int lane, double* f) {
+static __device__ __noinline__ void warp_propagator(const double* ids, double* sm, double dt, int lane, double* f) {
     double* M0 = sm;                 // A h, later B = [0; I^-1]
     double* M1 = M0 + 16 * PP;       // P / Phi / E in operand layout
     double* M2 = M1 + 16 * PP;       // F in operand layout
@@ -377,6 +388,9 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
     const int gw = blockIdx.x * RST_WARPS + wid;
     const int* list = nullptr;
     int work = S.n;
+    // launched as a programmatic dependent of the step kernel (auto-reset): everything above overlapped its tail;
+    // from here on its writes (work list, state) are visible. A no-op for an ordinary launch.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     if (K.list_parity >= 0) { work = S.fin_count[K.list_parity]; list = S.fin_list + (size_t)K.list_parity * st; }
 
     for (int wi = gw; wi < work; wi += total_warps) {
@@ -415,10 +429,10 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
         const double f2 = rs_uniform(strm, o_f2, K.f2_lo, K.f2_hi);
         const double stop = __dmul_rn((double)L, K.dt), tstep = __ddiv_rn(stop, (double)(L - 1));   // np.linspace(0, L*dt, L)
         const double w1c = __dmul_rn(__dmul_rn(2.0, 3.141592653589793), f1), w2c = __dmul_rn(__dmul_rn(2.0, 3.141592653589793), f2);
-        for (int k = lane; k < L; k += 32) {
+        for (int kk = lane; kk < 2 * L; kk += 32) {            // one sin() call site: both harmonics in one loop
+            const int hsel = kk >= L, k = hsel ? kk - L : kk;
             const double t = (k == L - 1) ? stop : __dmul_rn((double)k, tstep);
-            wav[k] = sin(__dmul_rn(w1c, t));
-            wav[TL + k] = sin(__dmul_rn(w2c, t));
+            wav[hsel * TL + k] = sin(__dmul_rn(hsel ? w2c : w1c, t));
         }
         // ---- per-axis amplitudes (tremor:24-28): lanes 0..13 take one pow each
         if (lane < 14) {

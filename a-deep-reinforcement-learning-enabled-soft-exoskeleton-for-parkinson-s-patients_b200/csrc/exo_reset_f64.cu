@@ -22,8 +22,16 @@ static int launch_reset_nax(const EnvArrays<R>& A, const ChainConst<R>& C, const
     if (per_sm > 4) per_sm = 4;
     int grid = n_sm * per_sm;
     if (K.list_parity < 0) { const int need = (A.n + RST_WARPS - 1) / RST_WARPS; if (need < grid) grid = need; }
-    exo_reset_kernel<R, NAX><<<grid, RST_WARPS * 32, smem, s>>>(A, C, K, mask, obs);
-    return 0;
+    // Auto-reset launches follow the step kernel in the same stream: programmatic dependent launch lets this grid be
+    // scheduled while the step kernel drains (it signals at its start); the kernel waits with griddepcontrol.wait
+    // before it touches the work list, so an empty list costs almost nothing on the device timeline.
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(RST_WARPS * 32); cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = K.list_parity >= 0 ? 1 : 0;
+    return (int)cudaLaunchKernelEx(&cfg, exo_reset_kernel<R, NAX>, A, C, K, mask, obs);
 }
 template <typename R>
 int launch_reset(const EnvArrays<R>& A, const ChainConst<R>& C, const ResetConst& K, int nax, int n_sm,

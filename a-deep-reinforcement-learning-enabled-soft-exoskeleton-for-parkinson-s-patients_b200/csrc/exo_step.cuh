@@ -184,6 +184,7 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
     const int wbase = blockIdx.x * EXO_STEP_THREADS + wid * 32;     // first env of this warp
     const int e = wbase + lane;
     const int n = S.n, st = S.stride;
+    asm volatile("griddepcontrol.launch_dependents;");               // the auto-reset kernel may be scheduled behind this grid
     if (blockIdx.x == 0 && tid == 0) S.fin_count[K.parity ^ 1] = 0;  // consumed by the previous step's reset
     if (wbase >= n) return;                                          // whole warp past the end
 
