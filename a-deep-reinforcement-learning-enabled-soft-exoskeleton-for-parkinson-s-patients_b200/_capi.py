@@ -62,6 +62,20 @@ SIGNATURES = {
     "exo_set_auto_reset": (C.c_int, [C.c_void_p, C.c_int32]),
     "exo_launch_count": (C.c_int64, [C.c_void_p]),
     "exo_forward_kinematics": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_void_p]),
+    # include/exo_lap.h
+    "exo_lap_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_double, C.c_int32, C.c_int32,
+                                 C.POINTER(C.c_void_p)]),
+    "exo_lap_destroy": (C.c_int, [C.c_void_p]),
+    "exo_lap_add": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                              C.c_int32, C.c_void_p]),
+    "exo_lap_sample": (C.c_int, [C.c_void_p] * 8 + [C.c_void_p]),
+    "exo_lap_update_priority": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "exo_lap_reset_max_priority": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "exo_lap_reset_buffer": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "exo_lap_counters": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                                   C.POINTER(C.c_double), C.c_void_p]),
+    "exo_lap_storage": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
+    "exo_lap_launch_count": (C.c_int64, [C.c_void_p]),
 }
 
 _lib = None

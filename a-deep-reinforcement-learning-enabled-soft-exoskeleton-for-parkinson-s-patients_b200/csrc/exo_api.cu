@@ -27,6 +27,14 @@ static int fail(int code, const char* fmt, ...) {
         if (_e != cudaSuccess) return fail(EXO_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); \
     } while (0)
 
+// shared with exo_lap.cu (one thread-local error string per library)
+int exo_set_error(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
 extern "C" const char* exo_last_error(void) { return g_err; }
 extern "C" int exo_abi_version(void) { return 1; }
 
