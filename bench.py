@@ -110,6 +110,53 @@ def cpu_baseline(sample_envs, steps, threads=0, seed0=0):
     return sample_envs * steps / dt, nthreads, dt
 
 
+def bench_lap(exo_b200, env, actions, dev, flush):
+    """Next row N1: the device-resident replay buffer fed by the env's own output tensors.
+    Reference hyper-parameters (TD7_multi_agent.py:15-16 Hyperparameters: batch_size 128, buffer_size 2.5e5; 8 rows).
+    Reports add throughput (transitions/s and algorithmic GB/s: 2*80+7+3 words written, 2*80+7+2 read per
+    transition), and the latency of one sample() + update_priority() over a full buffer."""
+    import torch
+    n = env.n
+    E, MAX, B = 8, 250000, 128
+    buf = exo_b200.LAP(80, 7, dev, E, max_size=MAX, batch_size=B)
+    obs = env.reset().clone()
+    evs = []
+    steps = 40
+    for t in range(steps):
+        nobs, rew, done = env.step(actions[t % actions.shape[0]])
+        if flush is not None:
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        buf.add_batch(obs, actions[t % actions.shape[0]], nobs, rew, done)
+        b.record()
+        evs.append((a, b))
+        obs = nobs
+    torch.cuda.synchronize(dev)
+    add_ms = float(np.mean([a.elapsed_time(b) for a, b in evs[5:]]))
+    size = buf.size
+    u = torch.rand(E * B, device=dev)
+    pr = torch.rand(E * B, device=dev) + 0.1
+    sev = []
+    for t in range(25):
+        if flush is not None:
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        buf.sample(uniforms=u)
+        buf.update_priority(pr)
+        b.record()
+        sev.append((a, b))
+    torch.cuda.synchronize(dev)
+    samp_ms = float(np.mean([a.elapsed_time(b) for a, b in sev[5:]]))
+    bytes_add = n * ((2 * 80 + 7 + 3) + (2 * 80 + 7 + 2)) * 4
+    out = {"rows": E, "max_size": MAX, "batch_size": B, "filled_slots_per_row": int(size),
+           "add_transitions_per_s": n / (add_ms * 1e-3), "add_ms": add_ms, "add_gbs": bytes_add / (add_ms * 1e-3) / 1e9,
+           "sample_plus_update_ms": samp_ms, "l2": "flushed between calls" if flush is not None else "not flushed"}
+    buf.close()
+    return out
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU algorithm (oracle port; the Python reference cannot travel to the GPU box
     and needs pybullet) on all host threads, rank 0 only."""
@@ -146,6 +193,7 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=2000)
     ap.add_argument("--ref-sample", type=int, default=4096)
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--no-lap", action="store_true", help="skip the replay-buffer (next row N1) measurement")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -249,6 +297,9 @@ def main():
     e2e_value = world * n * args.e2e_steps / (float(e2e_ms.item()) * 1e-3)
     rbytes = 4 if args.precision == "fp32" else 8
 
+    lap_line = None
+    if rank == 0 and not args.no_lap:
+        lap_line = bench_lap(exo_b200, env, actions, dev, flush)
     if rank == 0:
         peaks = {}
         try:
@@ -281,6 +332,8 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
         }
+        if lap_line is not None:
+            line["lap"] = lap_line
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
