@@ -97,6 +97,17 @@ __global__ void __launch_bounds__(256) lap_add_kernel(LapView B, const float* __
                                                       const int* __restrict__ rank, int k, const int* __restrict__ winner, int nwin) {
     const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (j >= k) return;
+    const int sd = B.sd, ad = B.ad;
+    const float* s = state + (size_t)j * sd;
+    const float* ns = next_state + (size_t)j * sd;
+    // the common shape (state_dim <= 128, 16-byte aligned rows): the transition's payload is requested before the
+    // counters / rank / winner chain resolves, so the copy pays one memory latency instead of three
+    const bool vec = (sd & 3) == 0 && sd <= 128 && ((reinterpret_cast<size_t>(s) | reinterpret_cast<size_t>(ns)) & 15) == 0;
+    float4 vs = make_float4(0, 0, 0, 0), vn = vs;
+    if (vec && lane < (sd >> 2)) { vs = __ldg(reinterpret_cast<const float4*>(s) + lane); vn = __ldg(reinterpret_cast<const float4*>(ns) + lane); }
+    const float va = lane < ad ? action[(size_t)j * ad + lane] : 0.0f;
+    const float vr = reward[j];
+    const uint8_t vd = done[j];
     const int r = rank ? rank[j] : j;
     if (r < 0) return;
     const long long c0 = B.ctr->count, c = c0 + r;
@@ -106,23 +117,18 @@ __global__ void __launch_bounds__(256) lap_add_kernel(LapView B, const float* __
     if (winner[win * B.num_envs + row] != r) return;                       // overwritten later in this same call
     const long long slot = (B.ctr->ptr + win) % B.max_size;
     const long long t = (long long)row * B.max_size + slot;
-    const int sd = B.sd, ad = B.ad;
-    const float* s = state + (size_t)j * sd;
-    const float* ns = next_state + (size_t)j * sd;
     float* ds = B.state + t * sd;
     float* dns = B.next_state + t * sd;
-    if ((sd & 3) == 0 && ((reinterpret_cast<size_t>(s) | reinterpret_cast<size_t>(ns)) & 15) == 0) {
-        for (int i = lane; i < (sd >> 2); i += 32) {
-            reinterpret_cast<float4*>(ds)[i] = __ldg(reinterpret_cast<const float4*>(s) + i);
-            reinterpret_cast<float4*>(dns)[i] = __ldg(reinterpret_cast<const float4*>(ns) + i);
-        }
+    if (vec) {
+        if (lane < (sd >> 2)) { reinterpret_cast<float4*>(ds)[lane] = vs; reinterpret_cast<float4*>(dns)[lane] = vn; }
     } else {
         for (int i = lane; i < sd; i += 32) { ds[i] = s[i]; dns[i] = ns[i]; }
     }
-    for (int i = lane; i < ad; i += 32) B.action[t * ad + i] = action[(size_t)j * ad + i] / B.norm;
+    if (lane < ad) B.action[t * ad + lane] = va / B.norm;
+    for (int i = lane + 32; i < ad; i += 32) B.action[t * ad + i] = action[(size_t)j * ad + i] / B.norm;
     if (lane == 0) {
-        B.reward[t] = reward[j];
-        B.not_done[t] = 1.0f - (done[j] ? 1.0f : 0.0f);
+        B.reward[t] = vr;
+        B.not_done[t] = 1.0f - (vd ? 1.0f : 0.0f);
         B.priority[t] = B.ctr->max_priority;
     }
 }
@@ -168,7 +174,9 @@ __global__ void __launch_bounds__(256) lap_chunk_sum_kernel(LapView B, double* _
     }
 }
 
-// One block per row: exclusive prefix over the row's chunk sums, then one warp per sample: searchsorted(cumsum, val)
+// Blocks (row, slice): every block rebuilds the exclusive prefix over its row's chunk sums (<= 1 K doubles, cheap) and
+// serves one sample per warp, so a batch of 128 per row spreads over 16 blocks per row instead of one SM per row
+// (r01g ncu: 250 us with one block per row). Per sample: searchsorted(cumsum, val)
 // (first index whose running sum is >= val) by locating the chunk and scanning it 32 priorities at a time, then
 // the warp gathers that transition into the output batch.
 __global__ void __launch_bounds__(256) lap_sample_kernel(LapView B, const double* __restrict__ chunk_sum, int nchunk_max,
@@ -195,7 +203,7 @@ __global__ void __launch_bounds__(256) lap_sample_kernel(LapView B, const double
     __syncthreads();
     const float total = (float)prefix[nchunk];        // csum[-1] (float32 in the reference)
     const float* prow = B.priority + (long long)row * B.max_size;
-    for (int b = wid; b < B.batch; b += nwarp) {
+    for (int b = blockIdx.y * nwarp + wid; b < B.batch; b += gridDim.y * nwarp) {
         const int o = row * B.batch + b;
         long long idx = 0;
         if (size > 0) {
@@ -393,7 +401,7 @@ extern "C" int exo_lap_sample(ExoLap* b, const float* uniform_dev, float* state_
     const size_t smem = sizeof(double) * (size_t)(b->nchunk_max + 1);
     if (smem > 200 * 1024) return exo_set_error(EXO_ERR_ARG, "exo_lap_sample: max_size too large for the chunk prefix (%d chunks)", b->nchunk_max);
     if (smem > 48 * 1024) LCK(cudaFuncSetAttribute(lap_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lap_sample_kernel<<<v.num_envs, 256, smem, s>>>(v, b->chunk_sum, b->nchunk_max, uniform_dev, state_dev, action_dev, next_state_dev,
+    lap_sample_kernel<<<dim3(v.num_envs, (v.batch + 7) / 8), 256, smem, s>>>(v, b->chunk_sum, b->nchunk_max, uniform_dev, state_dev, action_dev, next_state_dev,
                                                     reward_dev, not_done_dev, b->ind, ind_dev);
     b->launches += 2;
     LCK(cudaGetLastError());
