@@ -36,6 +36,9 @@ UNIT = "env-steps/s"
 # Compulsory HBM traffic of one env-step of exo_step_kernel<float,false,4> (DESIGN.md "Algorithmic bytes"):
 # reads 520 B + writes 525 B.
 ALGO_BYTES_PER_ENV_STEP = 1045
+# dram__bytes_read.sum + dram__bytes_write.sum of one exo_step_kernel<float,false,4> launch over 65 536 envs
+# (profiles/r01g_ncu_full_step.txt): 34.130944 MB + 0.103424 MB
+STEP_KERNEL_DRAM_BYTES_65536 = 34234368
 
 
 def population(n_per_gpu, rank, world):
@@ -321,7 +324,10 @@ def main():
                        "mean_return": (stats_sum[1] / stats_sum[0]).item() if stats_sum[0].item() > 0 else None,
                        "wall_s_timed_region": wall},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "exo_step_kernel", "kernel_ms": kms,
+                         "traffic": STEP_KERNEL_DRAM_BYTES_65536 if (n == 65536 and args.precision == "fp32") else None,
+                         "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of one launch, "
+                                           "profiles/r01g_ncu_full_step.txt (writes stay in L2 inside the launch)",
+                         "kernel": "exo_step_kernel", "kernel_ms": kms,
                          "algorithmic_bytes_per_env_step": ALGO_BYTES_PER_ENV_STEP,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)"},
             "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cpu_cores, "kind": "port",
