@@ -3,7 +3,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libexo_env.so")
+LIB_PATH = os.environ.get("EXO_LIB", os.path.join(HERE, "libexo_env.so"))   # EXO_LIB: tuning builds of the same sources
 
 OBS_DIM, ACT_DIM, NLINKS, N_STATS = 80, 7, 19, 16
 F32, F64 = 0, 1

@@ -13,10 +13,11 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "_obj")
-LIB = os.path.join(HERE, "libexo_env.so")
+LIB = os.environ.get("EXO_LIB_OUT", os.path.join(HERE, "libexo_env.so"))
 UNITS = ["exo_api.cu", "exo_step_f32.cu", "exo_step_f64.cu", "exo_reset_f32.cu", "exo_reset_f64.cu", "exo_lap.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
+FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"] + \
+    os.environ.get("EXO_EXTRA_NVCC_FLAGS", "").split()      # tuning experiments only (e.g. -DEXO_STEP_THREADS=32)
 
 
 def _sources():

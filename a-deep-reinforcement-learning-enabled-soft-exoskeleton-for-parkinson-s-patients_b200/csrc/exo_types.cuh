@@ -15,8 +15,10 @@
 
 #define EXO_MAX_LEN 512          // >= longest reference motion (347 rows)
 
+#ifndef EXO_STEP_THREADS
 #define EXO_STEP_THREADS 64      // 2 warps per block: 65 536 envs -> 1024 blocks ~ 6.9 per SM (balanced single wave)
 #define EXO_STEP_MIN_BLOCKS 7    // <= 144 registers per thread: the 7 blocks (14 warps) an SM owns at 65 536 envs stay resident
+#endif
 #define EXO_OBS_PITCH 84         // floats per staged observation row: 21 16-byte chunks, odd -> conflict-free STS.128
 
 // ---- word offsets inside the per-env records -------------------------------------------------------------
