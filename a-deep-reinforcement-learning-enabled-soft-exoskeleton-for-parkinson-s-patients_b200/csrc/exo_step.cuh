@@ -181,9 +181,9 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
     __shared__ __align__(16) float s_act[WARPS][32 * 7];
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int wbase = blockIdx.x * EXO_STEP_THREADS + wid * 32;     // first env of this warp
+    const int wbase = K.env0 + blockIdx.x * EXO_STEP_THREADS + wid * 32;     // first env of this warp
     const int e = wbase + lane;
-    const int n = S.n, st = S.stride;
+    const int n = K.env1, st = S.stride;                            // this launch covers envs [K.env0, K.env1)
     asm volatile("griddepcontrol.launch_dependents;");               // the auto-reset kernel may be scheduled behind this grid
     if (blockIdx.x == 0 && tid == 0) S.fin_count[K.parity ^ 1] = 0;  // consumed by the previous step's reset
     if (wbase >= n) return;                                          // whole warp past the end

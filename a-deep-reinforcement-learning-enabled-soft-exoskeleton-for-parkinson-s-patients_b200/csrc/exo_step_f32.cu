@@ -18,7 +18,7 @@ __global__ void exo_fk_kernel(const R* __restrict__ theta, R* __restrict__ p, in
 template <typename R>
 void launch_step(const EnvArrays<R>& A, const ChainConst<R>& C, const StepConst<R>& K, int nax, bool info_on,
                  const float* actions, float* obs, R* reward, uint8_t* done, const InfoPtrs<R>& ip, cudaStream_t s) {
-    const int grid = (A.n + EXO_STEP_THREADS - 1) / EXO_STEP_THREADS;
+    const int grid = (K.env1 - K.env0 + EXO_STEP_THREADS - 1) / EXO_STEP_THREADS;
     if (nax == 4) {
         if (info_on) exo_step_kernel<R, true, 4><<<grid, EXO_STEP_THREADS, 0, s>>>(A, C, K, actions, obs, reward, done, ip);
         else exo_step_kernel<R, false, 4><<<grid, EXO_STEP_THREADS, 0, s>>>(A, C, K, actions, obs, reward, done, ip);

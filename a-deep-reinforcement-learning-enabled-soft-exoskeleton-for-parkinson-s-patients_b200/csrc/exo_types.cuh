@@ -94,6 +94,8 @@ struct StepConst {
     R L1, L2;                      // humerus / forearm length for the amplitude metric
     int lag, limits, auto_reset, metrics;
     int parity;                    // which finished-list this step appends to (the other counter is cleared)
+    int env0, env1;                // env range [env0, env1) of this launch (env0 a multiple of 32): exo_step_host pipelines
+                                   // chunks of the population against their PCIe copies
 };
 
 struct ResetConst {

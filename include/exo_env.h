@@ -134,7 +134,9 @@ int exo_step(ExoHandle* h, const float* actions_dev /*[n,7]*/, float* obs_dev /*
              uint8_t* done_dev /*[n]*/, const ExoInfo* info /*NULL: off*/, void* stream);
 
 /* Same step with HOST buffers (pinned for full speed): H2D of actions, step, D2H of obs/reward/done, stream sync.
- * This is the call the single-env facade and the end-to-end benchmark use. */
+ * This is the call the single-env facade and the end-to-end benchmark use. From 16 384 envs up the population is
+ * cut into 4 chunks (environment variable EXO_HOST_CHUNKS=1..8 overrides) whose copies and kernels overlap on
+ * internal streams; results are identical to exo_step. */
 int exo_step_host(ExoHandle* h, const float* actions_host, float* obs_host, void* reward_host, uint8_t* done_host,
                   void* stream);
 int exo_reset_host(ExoHandle* h, const uint8_t* mask_host, float* obs_host, void* stream);

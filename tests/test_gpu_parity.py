@@ -234,6 +234,33 @@ def test_host_buffer_entry_equals_device_entry(exo):
     a_env.close(); b_env.close()
 
 
+def test_pipelined_host_entry_equals_device_entry_across_auto_resets(exo):
+    """Above 16 384 envs exo_step_host cuts the population into chunks whose copies and kernels overlap on three
+    streams; results must be bit-identical to the one-launch device path, through episode ends (auto-reset writes the
+    first observation of the next episode into the same rows) and for a population that is not a multiple of the
+    chunk or block size."""
+    n = 16384 + 1000 + 37
+    mids = [0] * n                                  # motion 0: 229-step episodes
+    seqs = [[1, 1, 0, 1, 0, 0, 0]] * n
+    seeds = list(range(n))
+    a_env = exo.BatchedExoskeletonEnv(mids, seqs, seeds, auto_reset=True, **TRAIN)
+    b_env = exo.BatchedExoskeletonEnv(mids, seqs, seeds, auto_reset=True, **TRAIN)
+    assert torch.equal(a_env.reset().cpu(), b_env.reset_host().clone())
+    g = torch.Generator(); g.manual_seed(5)
+    acts = [(torch.rand(n, 7, generator=g) * 2 - 1).pin_memory() for _ in range(3)]
+    dones = 0
+    for t in range(232):
+        ob, rw, dn = a_env.step(acts[t % 3].cuda())
+        hob, hrw, hdn = b_env.step_host(acts[t % 3])
+        if t % 20 == 0 or t > 224:
+            assert torch.equal(ob.cpu(), hob) and torch.equal(rw.cpu(), hrw) and torch.equal(dn.cpu(), hdn.bool()), t
+        dones += int(hdn.sum())
+    assert dones == n                               # every env finished exactly one episode and was re-initialised
+    sa, sb = a_env.stats().cpu(), b_env.stats().cpu()
+    assert torch.equal(sa[:6], sb[:6])
+    a_env.close(); b_env.close()
+
+
 def test_masked_reset_idle_envs_and_ragged_batch(exo, oracle_mod):
     """Edge cases: batch size not a multiple of the block, partial reset masks, envs idling after done."""
     n = 77
