@@ -30,6 +30,12 @@ class ExoGeometry(C.Structure):
                 ("act_link", C.c_int32 * 14), ("shoulder_link", C.c_int32), ("elbow_link", C.c_int32)]
 
 
+class ExoPolicyWeights(C.Structure):
+    """include/exo_policy.h: host pointers to torch.nn.Linear parameters (weight [out, in] row-major float32, bias [out])."""
+    NAMES = ("zs1", "zs2", "zs3", "l0", "l1", "l2", "l3")
+    _fields_ = [(n + s, C.POINTER(C.c_float)) for n in NAMES for s in ("_w", "_b")]
+
+
 class ExoInfo(C.Structure):
     _fields_ = [(k, C.c_void_p) for k in ("actuator_torques", "torque_val", "ampl_val", "tremor_torque_val",
                                           "tremor_ampl_val", "reward_parts", "amp_metric")]
@@ -76,6 +82,12 @@ SIGNATURES = {
                                    C.POINTER(C.c_double), C.c_void_p]),
     "exo_lap_storage": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
     "exo_lap_launch_count": (C.c_int64, [C.c_void_p]),
+    # include/exo_policy.h
+    "exo_policy_create": (C.c_int, [C.c_int32, C.POINTER(C.c_void_p)]),
+    "exo_policy_destroy": (C.c_int, [C.c_void_p]),
+    "exo_policy_set_weights": (C.c_int, [C.c_void_p, C.POINTER(ExoPolicyWeights), C.c_int32, C.c_int32, C.c_int32]),
+    "exo_policy_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "exo_policy_launch_count": (C.c_int64, [C.c_void_p]),
 }
 
 _lib = None

@@ -1,0 +1,507 @@
+// exo_policy.cu — fused policy forward pass on the 5th-generation tensor cores (include/exo_policy.h).
+//
+//   encoder.zs + actor of Agent/TD7_multi_agent_Pink_noise.py:66-105, evaluated as select_action does (:208-228), for
+//   observations resident in HBM. ~1.0 MFLOP per observation in seven small GEMMs: the one GEMM-shaped piece of the
+//   env -> agent loop, so this is where tcgen05 is used (the env step itself is HBM-bound 7x7 work).
+//
+// One persistent CTA per SM, 128 observations (= the 128 TMEM lanes = UMMA M) per tile, 192 threads:
+//   warp 0 / lane 0   weight producer: cp.async.bulk (TMA engine, 1-D) global -> shared stages, mbarrier complete_tx
+//   warp 1            TMEM allocation; lane 0 issues every tcgen05.mma (kind::tf32, cta_group::1, M=128)
+//   warps 2..5        epilogue: tcgen05.ld the fp32 accumulator row (one row per thread), bias + activation, round to
+//                     TF32, store as the next layer's A operand in shared memory
+// Shared memory (225 920 B): X = 128 x 304 activations (152 KB), S = 128 x 80 observations (40 KB), 3 weight stages
+// of 9 728 B, mbarriers. Operands use the K-major no-swizzle canonical layout (8 rows x 16 B core matrices;
+// LBO = distance of the two 16 B K-chunks of one MMA, SBO = distance of 8-row groups), which the host packs the
+// weights into once, so a stage is ONE contiguous bulk copy and needs no tensor map.
+// Tensor memory: accumulator P = columns 0..303 of the CTA's 512.
+//
+// Per tile (G = MMAs, E = epilogue; hidden width 300 padded to 304 with zero weights/bias, so pads stay exactly 0):
+//   E0 obs -> S | G1 S*l0' -> E1 a0 = AvgL1Norm -> L2 scratch | G2 S*zs1' -> E2 ELU -> X | G3 X*zs2' -> E3 ELU -> X |
+//   G4 X*zs3' -> E4 zs = AvgL1Norm -> X | G5a P = X*l1[:,300:600]' | bulk-reload X <- a0 | G5b P += X*l1[:,0:300]' ->
+//   E5 ReLU -> X | G6 X*l2' -> E6 ReLU -> X | G7 X*l3' (N=16) -> E7 tanh, clip, * max_action -> actions
+// (a0 takes the detour through an L2-resident per-CTA scratch because X + a second 152 KB operand do not fit in
+// shared memory and two 304-column accumulators do not fit in TMEM.)
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <vector>
+
+#include "../../include/exo_env.h"
+#include "../../include/exo_policy.h"
+
+extern "C" const char* exo_last_error(void);
+int exo_set_error(int code, const char* fmt, ...);     // exo_api.cu
+
+#define PCK(call)                                                                                          \
+    do {                                                                                                   \
+        cudaError_t _e = (call);                                                                           \
+        if (_e != cudaSuccess) return exo_set_error(EXO_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); \
+    } while (0)
+
+namespace {
+
+constexpr int SD = EXO_POLICY_STATE_DIM, HD = EXO_POLICY_HIDDEN_DIM, AD = EXO_POLICY_ACTION_DIM;
+constexpr int HP = 304;                     // hidden width padded: multiple of 8 (MMA K of tf32) and of 16 (MMA N)
+constexpr int OUTP = 16;                    // l3 rows padded to the smallest MMA N
+constexpr int TILE_M = 128;
+constexpr int KS_S = SD / 8;                // 10 k-steps over the observation
+constexpr int KS_H = HP / 8;                // 38 k-steps over a hidden vector
+constexpr int STAGE_BYTES = HP * 32;        // 9 728: one k-step (8 tf32 = 32 B per row) of a 304-row weight matrix
+constexpr int L3_KS_PER_STAGE = STAGE_BYTES / (OUTP * 32);   // 19 k-steps of the 16-row l3 per stage
+constexpr int L3_STAGES = KS_H / L3_KS_PER_STAGE;            // 2
+constexpr int X_BYTES = TILE_M * HP * 4;    // 155 648
+constexpr int S_BYTES = TILE_M * SD * 4;    // 40 960
+constexpr int X_SBO = HP * 32;              // 9 728: 8 rows x (304 * 4 B)
+constexpr int S_SBO = SD * 32;              // 2 560
+constexpr int NSLOT = 3;
+constexpr int N_PHASE = 8;
+constexpr int STAGES_PER_TILE = 2 * KS_S + 5 * KS_H + L3_STAGES;     // 212
+constexpr int PACK_BYTES = STAGES_PER_TILE * STAGE_BYTES;            // 2 062 336
+constexpr int N_BIAS = 6 * HP + OUTP;
+
+constexpr int OFF_X = 0;
+constexpr int OFF_S = OFF_X + X_BYTES;
+constexpr int OFF_W = OFF_S + S_BYTES;
+constexpr int OFF_BAR = OFF_W + NSLOT * STAGE_BYTES;
+constexpr int SMEM_BYTES = OFF_BAR + 128;
+static_assert(SMEM_BYTES <= 232448, "over the 227 KB per-CTA shared memory limit");
+static_assert(L3_STAGES * L3_KS_PER_STAGE == KS_H, "l3 stage split");
+
+constexpr int N_THREADS = 192;
+constexpr int N_EPI = 128;
+
+// bias block offsets (floats) in the order the epilogues use them
+enum { B_L0 = 0, B_ZS1 = HP, B_ZS2 = 2 * HP, B_ZS3 = 3 * HP, B_L1 = 4 * HP, B_L2 = 5 * HP, B_L3 = 6 * HP };
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// A wait that never returns would hang the GPU box: after ~2 s of polling, trap instead.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    long long t0 = 0;
+    for (uint32_t spins = 0; !done; ++spins) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (!done && (spins & 1023u) == 1023u) {
+            const long long t = clock64();
+            if (t0 == 0) t0 = t;
+            else if (t - t0 > 4000000000ll) __trap();
+        }
+    }
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, both operands K-major, tf32 inputs, fp32 accumulate
+__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ float to_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+
+// Shared-memory matrix descriptor (sm_100 UMMA): start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46), version 1 [46,48),
+// layout type 0 = no swizzle [61,64).
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo, uint32_t sbo) {
+    return (uint64_t)((addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo >> 4) & 0x3FFFu) << 16) | ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) |
+           (1ull << 46);
+}
+// Instruction descriptor: D fp32 (1<<4), A and B tf32 (2<<7, 2<<10), both K-major, N>>3 at bit 17, M>>4 at bit 24.
+__host__ __device__ constexpr uint32_t idesc_tf32(int n) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
+}
+
+struct PolicyArgs {
+    const float* obs;            // [n, 80]
+    const unsigned char* pack;   // STAGES_PER_TILE stages of STAGE_BYTES, in consumption order
+    const float* bias;           // N_BIAS floats
+    unsigned char* scratch;      // gridDim.x * X_BYTES (a0 in operand layout)
+    float* actions;              // [n, 7]
+    float* zs;                   // [n, 300] or null
+    long long n;
+    float max_action;
+    int n_tiles;
+};
+
+// stages per phase: G1, G2, G3, G4, G5a, G5b, G6, G7
+__device__ __constant__ int PH_STAGES[N_PHASE] = {KS_S, KS_S, KS_H, KS_H, KS_H, KS_H, KS_H, L3_STAGES};
+
+// ---- epilogues (one accumulator row per thread) ----------------------------------------------------------
+// act: 0 ELU, 1 ReLU. Writes the row into an operand-layout buffer in shared memory.
+template <int ACT>
+__device__ __forceinline__ void epi_act_to_x(uint32_t taddr, const float* __restrict__ bias, unsigned char* xrow) {
+#pragma unroll 1
+    for (int cb = 0; cb < HP / 16; ++cb) {
+        float v[16];
+        tmem_ld16(taddr + cb * 16, v);
+#pragma unroll
+        for (int j4 = 0; j4 < 4; ++j4) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(bias + cb * 16 + j4 * 4));
+            float o[4] = {v[j4 * 4] + b.x, v[j4 * 4 + 1] + b.y, v[j4 * 4 + 2] + b.z, v[j4 * 4 + 3] + b.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float x = o[j];
+                if (ACT == 0) x = x > 0.f ? x : (__expf(x) - 1.f);
+                else x = fmaxf(x, 0.f);
+                o[j] = to_tf32(x);
+            }
+            *reinterpret_cast<float4*>(xrow + (cb * 4 + j4) * 128) = make_float4(o[0], o[1], o[2], o[3]);
+        }
+    }
+}
+
+// AvgL1Norm (:59-60): x / clamp(mean|x|, 1e-8). dst is an operand-layout row (shared memory or the global scratch);
+// zs_row (optional) receives the un-rounded fp32 values row-major.
+__device__ __forceinline__ void epi_avgl1(uint32_t taddr, const float* __restrict__ bias, unsigned char* dst, float* zs_row) {
+    float s = 0.f;
+#pragma unroll 1
+    for (int cb = 0; cb < HP / 16; ++cb) {
+        float v[16];
+        tmem_ld16(taddr + cb * 16, v);
+#pragma unroll
+        for (int j4 = 0; j4 < 4; ++j4) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(bias + cb * 16 + j4 * 4));
+            s += fabsf(v[j4 * 4] + b.x) + fabsf(v[j4 * 4 + 1] + b.y) + fabsf(v[j4 * 4 + 2] + b.z) + fabsf(v[j4 * 4 + 3] + b.w);
+        }
+    }
+    const float denom = fmaxf(s / (float)HD, 1e-8f);     // pad columns are exactly 0 and do not touch the sum
+#pragma unroll 1
+    for (int cb = 0; cb < HP / 16; ++cb) {
+        float v[16];
+        tmem_ld16(taddr + cb * 16, v);
+#pragma unroll
+        for (int j4 = 0; j4 < 4; ++j4) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(bias + cb * 16 + j4 * 4));
+            float o[4] = {(v[j4 * 4] + b.x) / denom, (v[j4 * 4 + 1] + b.y) / denom, (v[j4 * 4 + 2] + b.z) / denom,
+                          (v[j4 * 4 + 3] + b.w) / denom};
+            if (zs_row) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (cb * 16 + j4 * 4 + j < HD) zs_row[cb * 16 + j4 * 4 + j] = o[j];
+            }
+            *reinterpret_cast<float4*>(dst + (cb * 4 + j4) * 128) = make_float4(to_tf32(o[0]), to_tf32(o[1]), to_tf32(o[2]), to_tf32(o[3]));
+        }
+    }
+}
+
+__global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyArgs a) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t sbase = smem_u32(smem);
+    // barriers: full[3], empty[3], acc_full, a_ready, x_free, xr_full; then the TMEM base address
+    const uint32_t bar_full = sbase + OFF_BAR, bar_empty = bar_full + 8 * NSLOT;
+    const uint32_t bar_acc = bar_empty + 8 * NSLOT, bar_aready = bar_acc + 8, bar_xfree = bar_aready + 8, bar_xr = bar_xfree + 8;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + OFF_BAR + 96);
+
+    if (tid == 0) {
+        for (int s = 0; s < NSLOT; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+        mbar_init(bar_acc, 1);
+        mbar_init(bar_aready, N_EPI);
+        mbar_init(bar_xfree, 1);
+        mbar_init(bar_xr, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== weight producer ==========================================================================
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+                for (int i = 0; i < STAGES_PER_TILE; ++i, ++it) {
+                    const uint32_t slot = it % NSLOT, use = it / NSLOT;
+                    mbar_wait(bar_empty + 8 * slot, (use & 1) ^ 1);
+                    mbar_expect_tx(bar_full + 8 * slot, STAGE_BYTES);
+                    bulk_g2s(sbase + OFF_W + slot * STAGE_BYTES, a.pack + (size_t)i * STAGE_BYTES, STAGE_BYTES, bar_full + 8 * slot);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer ===============================================================================
+        if (lane == 0) {
+            uint32_t it = 0, par_ar = 0, par_xr = 0;
+            constexpr uint32_t ID256 = idesc_tf32(256), ID48 = idesc_tf32(48), ID16 = idesc_tf32(OUTP);
+            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+#pragma unroll 1
+                for (int ph = 0; ph < N_PHASE; ++ph) {
+                    if (ph == 5) { mbar_wait(bar_xr, par_xr); par_xr ^= 1; }
+                    else { mbar_wait(bar_aready, par_ar); par_ar ^= 1; }
+                    tc_fence_after();
+                    const uint32_t a_base = sbase + (ph < 2 ? OFF_S : OFF_X);
+                    const uint32_t a_sbo = ph < 2 ? S_SBO : X_SBO;
+                    const int nst = PH_STAGES[ph];
+#pragma unroll 1
+                    for (int st = 0; st < nst; ++st, ++it) {
+                        const uint32_t slot = it % NSLOT, use = it / NSLOT;
+                        mbar_wait(bar_full + 8 * slot, use & 1);
+                        tc_fence_after();
+                        const uint32_t w = sbase + OFF_W + slot * STAGE_BYTES;
+                        if (ph < 7) {
+                            const uint64_t ad = smem_desc(a_base + st * 256, 128, a_sbo);
+                            const uint32_t acc = (st > 0 || ph == 5) ? 1u : 0u;
+                            tc_mma_tf32(tmem, ad, smem_desc(w, 128, 256), ID256, acc);
+                            tc_mma_tf32(tmem + 256, ad, smem_desc(w + 32 * 256, 128, 256), ID48, acc);
+                        } else {
+#pragma unroll 1
+                            for (int j = 0; j < L3_KS_PER_STAGE; ++j) {
+                                const int ks = st * L3_KS_PER_STAGE + j;
+                                tc_mma_tf32(tmem, smem_desc(a_base + ks * 256, 128, a_sbo), smem_desc(w + j * (OUTP * 32), 128, 256), ID16,
+                                            ks > 0 ? 1u : 0u);
+                            }
+                        }
+                        tc_commit(bar_empty + 8 * slot);      // frees the stage once these MMAs have read it
+                    }
+                    tc_commit(ph == 4 ? bar_xfree : bar_acc);  // G5a: X may be reloaded; otherwise: accumulator ready
+                }
+            }
+        }
+    } else {
+        // ===== epilogue warps ===========================================================================
+        const int et = tid - 64;                       // 0..127
+        const int q = warp & 3;                        // TMEM lane quarter this warp may read
+        const int r = q * 32 + lane;                   // accumulator row = observation within the tile
+        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
+        unsigned char* xrow = smem + OFF_X + (r >> 3) * X_SBO + (r & 7) * 16;
+        unsigned char* scratch = a.scratch + (size_t)blockIdx.x * X_BYTES;
+        unsigned char* srow = scratch + (r >> 3) * X_SBO + (r & 7) * 16;
+        uint32_t par_acc = 0, par_xf = 0;
+        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+            const long long row0 = (long long)tile * TILE_M;
+            // E0: observations -> S (coalesced 16 B reads, rounded to TF32)
+#pragma unroll 4
+            for (int i = 0; i < (TILE_M * SD / 4) / N_EPI; ++i) {
+                const int idx = i * N_EPI + et, rr = idx / (SD / 4), c = idx % (SD / 4);
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (row0 + rr < a.n) v = __ldg(reinterpret_cast<const float4*>(a.obs + (row0 + rr) * SD) + c);
+                *reinterpret_cast<float4*>(smem + OFF_S + (rr >> 3) * S_SBO + c * 128 + (rr & 7) * 16) =
+                    make_float4(to_tf32(v.x), to_tf32(v.y), to_tf32(v.z), to_tf32(v.w));
+            }
+            fence_proxy_async_smem();
+            tc_fence_before();
+            mbar_arrive(bar_aready);
+            // E1: a0 = AvgL1Norm(l0(obs)) -> scratch
+            mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
+            epi_avgl1(taddr, a.bias + B_L0, srow, nullptr);
+            __threadfence();
+            fence_proxy_async_all();
+            tc_fence_before();
+            mbar_arrive(bar_aready);
+            asm volatile("bar.sync 1, 128;" ::: "memory");   // all 128 rows of a0 are out before anyone reloads them
+            // E2, E3: ELU
+            mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
+            epi_act_to_x<0>(taddr, a.bias + B_ZS1, xrow);
+            fence_proxy_async_smem(); tc_fence_before(); mbar_arrive(bar_aready);
+            mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
+            epi_act_to_x<0>(taddr, a.bias + B_ZS2, xrow);
+            fence_proxy_async_smem(); tc_fence_before(); mbar_arrive(bar_aready);
+            // E4: zs = AvgL1Norm(zs3(.))
+            mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
+            epi_avgl1(taddr, a.bias + B_ZS3, xrow, (a.zs && row0 + r < a.n) ? a.zs + (row0 + r) * HD : nullptr);
+            fence_proxy_async_smem(); tc_fence_before(); mbar_arrive(bar_aready);
+            // after G5a has read zs out of X, bring a0 back (16 bulk copies of one 8-row group each)
+            if (et == 0) {
+                mbar_wait(bar_xfree, par_xf);
+                mbar_expect_tx(bar_xr, X_BYTES);
+                for (int g = 0; g < TILE_M / 8; ++g)
+                    bulk_g2s(sbase + OFF_X + g * X_SBO, scratch + (size_t)g * X_SBO, X_SBO, bar_xr);
+            }
+            par_xf ^= 1;
+            // E5, E6: ReLU
+            mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
+            epi_act_to_x<1>(taddr, a.bias + B_L1, xrow);
+            fence_proxy_async_smem(); tc_fence_before(); mbar_arrive(bar_aready);
+            mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
+            epi_act_to_x<1>(taddr, a.bias + B_L2, xrow);
+            fence_proxy_async_smem(); tc_fence_before(); mbar_arrive(bar_aready);
+            // E7: actions
+            mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
+            {
+                float v[16];
+                tmem_ld16(taddr, v);
+                if (row0 + r < a.n) {
+                    float* out = a.actions + (row0 + r) * AD;
+#pragma unroll
+                    for (int j = 0; j < AD; ++j) {
+                        const float t = tanhf(v[j] + __ldg(a.bias + B_L3 + j));
+                        out[j] = fminf(fmaxf(t, -1.f), 1.f) * a.max_action;
+                    }
+                }
+            }
+            tc_fence_before();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        __syncwarp();
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+    }
+}
+
+// ---- host side ------------------------------------------------------------------------------------------
+inline float round_tf32(float x) {            // cvt.rna.tf32.f32: round to nearest, ties away from zero, 10-bit mantissa
+    uint32_t u;
+    memcpy(&u, &x, 4);
+    if ((u & 0x7F800000u) != 0x7F800000u) u = (u + 0x1000u) & 0xFFFFE000u;
+    memcpy(&x, &u, 4);
+    return x;
+}
+
+// W[n_rows, ld] (columns col0 .. col0+k_real-1 used) -> `ksteps` k-steps of an `n_pad`-row K-major no-swizzle operand:
+// byte offset of element (n, k) = (k/8)*n_pad*32 + (n/8)*256 + ((k%8)/4)*128 + (n%8)*16 + (k%4)*4
+void pack_matrix(unsigned char* dst, const float* W, int n_rows, int ld, int col0, int k_real, int n_pad, int ksteps) {
+    memset(dst, 0, (size_t)ksteps * n_pad * 32);
+    for (int n = 0; n < n_rows; ++n)
+        for (int k = 0; k < k_real; ++k) {
+            const size_t off = (size_t)(k / 8) * n_pad * 32 + (size_t)(n / 8) * 256 + ((k % 8) / 4) * 128 + (n % 8) * 16 + (k % 4) * 4;
+            const float v = round_tf32(W[(size_t)n * ld + col0 + k]);
+            memcpy(dst + off, &v, 4);
+        }
+}
+
+}  // namespace
+
+struct ExoPolicy {
+    int device, n_sm;
+    bool loaded;
+    unsigned char *pack, *scratch;
+    float* bias;
+    int64_t launches;
+};
+
+extern "C" int exo_policy_create(int32_t device, ExoPolicy** out) {
+    if (!out) return exo_set_error(EXO_ERR_ARG, "exo_policy_create: null out");
+    int ndev = 0;
+    PCK(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return exo_set_error(EXO_ERR_CUDA, "device %d not present: this library has no CPU path", device);
+    cudaDeviceProp prop;
+    PCK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return exo_set_error(EXO_ERR_CUDA, "device %d is sm_%d%d; libexo_env.so carries sm_100a code only", device, prop.major, prop.minor);
+    PCK(cudaSetDevice(device));
+    ExoPolicy* p = new ExoPolicy();
+    p->device = device; p->n_sm = prop.multiProcessorCount; p->loaded = false; p->launches = 0;
+    p->pack = p->scratch = nullptr; p->bias = nullptr;
+    cudaError_t e = cudaMalloc((void**)&p->pack, PACK_BYTES);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&p->scratch, (size_t)p->n_sm * X_BYTES);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&p->bias, N_BIAS * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemset(p->scratch, 0, (size_t)p->n_sm * X_BYTES);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(exo_policy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) {
+        exo_policy_destroy(p);
+        return exo_set_error(EXO_ERR_CUDA, "exo_policy_create: %s", cudaGetErrorString(e));
+    }
+    *out = p;
+    return EXO_OK;
+}
+
+extern "C" int exo_policy_destroy(ExoPolicy* p) {
+    if (!p) return EXO_OK;
+    cudaSetDevice(p->device);
+    cudaFree(p->pack); cudaFree(p->scratch); cudaFree(p->bias);
+    delete p;
+    return EXO_OK;
+}
+
+extern "C" int exo_policy_set_weights(ExoPolicy* p, const ExoPolicyWeights* w, int32_t state_dim, int32_t hidden_dim, int32_t action_dim) {
+    if (!p || !w) return exo_set_error(EXO_ERR_ARG, "exo_policy_set_weights: null argument");
+    if (state_dim != SD || hidden_dim != HD || action_dim != AD)
+        return exo_set_error(EXO_ERR_ARG, "exo_policy_set_weights: built for state %d / hidden %d / action %d, got %d / %d / %d", SD, HD, AD,
+                             state_dim, hidden_dim, action_dim);
+    const float* ptrs[] = {w->zs1_w, w->zs1_b, w->zs2_w, w->zs2_b, w->zs3_w, w->zs3_b, w->l0_w, w->l0_b,
+                           w->l1_w,  w->l1_b,  w->l2_w,  w->l2_b,  w->l3_w,  w->l3_b};
+    for (const float* q : ptrs)
+        if (!q) return exo_set_error(EXO_ERR_ARG, "exo_policy_set_weights: null matrix");
+    std::vector<unsigned char> pack(PACK_BYTES);
+    std::vector<float> bias(N_BIAS, 0.f);
+    unsigned char* d = pack.data();
+    // consumption order of the kernel: G1 l0, G2 zs1, G3 zs2, G4 zs3, G5a l1[:,300:600], G5b l1[:,0:300], G6 l2, G7 l3
+    pack_matrix(d, w->l0_w, HD, SD, 0, SD, HP, KS_S);        d += (size_t)KS_S * STAGE_BYTES;
+    pack_matrix(d, w->zs1_w, HD, SD, 0, SD, HP, KS_S);       d += (size_t)KS_S * STAGE_BYTES;
+    pack_matrix(d, w->zs2_w, HD, HD, 0, HD, HP, KS_H);       d += (size_t)KS_H * STAGE_BYTES;
+    pack_matrix(d, w->zs3_w, HD, HD, 0, HD, HP, KS_H);       d += (size_t)KS_H * STAGE_BYTES;
+    pack_matrix(d, w->l1_w, HD, 2 * HD, HD, HD, HP, KS_H);   d += (size_t)KS_H * STAGE_BYTES;
+    pack_matrix(d, w->l1_w, HD, 2 * HD, 0, HD, HP, KS_H);    d += (size_t)KS_H * STAGE_BYTES;
+    pack_matrix(d, w->l2_w, HD, HD, 0, HD, HP, KS_H);        d += (size_t)KS_H * STAGE_BYTES;
+    pack_matrix(d, w->l3_w, AD, HD, 0, HD, OUTP, KS_H);      d += (size_t)L3_STAGES * STAGE_BYTES;
+    if (d != pack.data() + PACK_BYTES) return exo_set_error(EXO_ERR_STATE, "exo_policy_set_weights: pack size mismatch");
+    memcpy(&bias[B_L0], w->l0_b, HD * 4);   memcpy(&bias[B_ZS1], w->zs1_b, HD * 4); memcpy(&bias[B_ZS2], w->zs2_b, HD * 4);
+    memcpy(&bias[B_ZS3], w->zs3_b, HD * 4); memcpy(&bias[B_L1], w->l1_b, HD * 4);   memcpy(&bias[B_L2], w->l2_b, HD * 4);
+    memcpy(&bias[B_L3], w->l3_b, AD * 4);
+    PCK(cudaSetDevice(p->device));
+    PCK(cudaMemcpy(p->pack, pack.data(), PACK_BYTES, cudaMemcpyHostToDevice));
+    PCK(cudaMemcpy(p->bias, bias.data(), N_BIAS * sizeof(float), cudaMemcpyHostToDevice));
+    p->loaded = true;
+    return EXO_OK;
+}
+
+extern "C" int exo_policy_forward(ExoPolicy* p, const float* obs_dev, int64_t n, float max_action, float* actions_dev, float* zs_dev,
+                                  void* stream) {
+    if (!p || !obs_dev || !actions_dev || n < 0) return exo_set_error(EXO_ERR_ARG, "exo_policy_forward: bad arguments");
+    if (!p->loaded) return exo_set_error(EXO_ERR_STATE, "exo_policy_forward: no weights (exo_policy_set_weights first)");
+    if (((uintptr_t)obs_dev & 15) != 0) return exo_set_error(EXO_ERR_ARG, "exo_policy_forward: obs must be 16-byte aligned");
+    if (n == 0) return EXO_OK;
+    PolicyArgs a;
+    a.obs = obs_dev; a.pack = p->pack; a.bias = p->bias; a.scratch = p->scratch; a.actions = actions_dev; a.zs = zs_dev;
+    a.n = n; a.max_action = max_action;
+    const long long tiles = (n + TILE_M - 1) / TILE_M;
+    if (tiles > 0x7FFFFFFF) return exo_set_error(EXO_ERR_ARG, "exo_policy_forward: too many observations");
+    a.n_tiles = (int)tiles;
+    const int grid = (int)(tiles < p->n_sm ? tiles : p->n_sm);
+    exo_policy_kernel<<<grid, N_THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(a);
+    PCK(cudaGetLastError());
+    p->launches += 1;
+    return EXO_OK;
+}
+
+extern "C" int64_t exo_policy_launch_count(const ExoPolicy* p) { return p ? p->launches : 0; }
