@@ -9,14 +9,14 @@
 //   warp 1            TMEM allocation; lane 0 issues every tcgen05.mma (kind::tf32, cta_group::1, M=128)
 //   warps 2..5        epilogue: tcgen05.ld the fp32 accumulator row (one row per thread), bias + activation, round to
 //                     TF32, store as the next layer's A operand in shared memory
-// Shared memory (225 920 B): X = 128 x 304 activations (152 KB), S = 128 x 80 observations (40 KB), 3 weight stages
-// of 9 728 B, mbarriers. Operands use the K-major no-swizzle canonical layout (8 rows x 16 B core matrices;
+// Shared memory (223 904 B): X = 128 x 304 activations (152 KB; the observations sit in its first 80 columns until the
+// first hidden layer overwrites them), 7 weight stages of 9 728 B, mbarriers. Operands use the K-major no-swizzle canonical layout (8 rows x 16 B core matrices;
 // LBO = distance of the two 16 B K-chunks of one MMA, SBO = distance of 8-row groups), which the host packs the
 // weights into once, so a stage is ONE contiguous bulk copy and needs no tensor map.
 // Tensor memory: accumulator P = columns 0..303 of the CTA's 512.
 //
 // Per tile (G = MMAs, E = epilogue; hidden width 300 padded to 304 with zero weights/bias, so pads stay exactly 0):
-//   E0 obs -> S | G1 S*l0' -> E1 a0 = AvgL1Norm -> L2 scratch | G2 S*zs1' -> E2 ELU -> X | G3 X*zs2' -> E3 ELU -> X |
+//   E0 obs -> X | G1 X*l0' -> E1 a0 = AvgL1Norm -> L2 scratch | G2 X*zs1' -> E2 ELU -> X | G3 X*zs2' -> E3 ELU -> X |
 //   G4 X*zs3' -> E4 zs = AvgL1Norm -> X | G5a P = X*l1[:,300:600]' | bulk-reload X <- a0 | G5b P += X*l1[:,0:300]' ->
 //   E5 ReLU -> X | G6 X*l2' -> E6 ReLU -> X | G7 X*l3' (N=16) -> E7 tanh, clip, * max_action -> actions
 // (a0 takes the detour through an L2-resident per-CTA scratch because X + a second 152 KB operand do not fit in
@@ -51,20 +51,17 @@ constexpr int STAGE_BYTES = HP * 32;        // 9 728: one k-step (8 tf32 = 32 B 
 constexpr int L3_KS_PER_STAGE = STAGE_BYTES / (OUTP * 32);   // 19 k-steps of the 16-row l3 per stage
 constexpr int L3_STAGES = KS_H / L3_KS_PER_STAGE;            // 2
 constexpr int X_BYTES = TILE_M * HP * 4;    // 155 648
-constexpr int S_BYTES = TILE_M * SD * 4;    // 40 960
 constexpr int X_SBO = HP * 32;              // 9 728: 8 rows x (304 * 4 B)
-constexpr int S_SBO = SD * 32;              // 2 560
-constexpr int NSLOT = 3;
+constexpr int NSLOT = 7;
 constexpr int N_PHASE = 8;
 constexpr int STAGES_PER_TILE = 2 * KS_S + 5 * KS_H + L3_STAGES;     // 212
 constexpr int PACK_BYTES = STAGES_PER_TILE * STAGE_BYTES;            // 2 062 336
 constexpr int N_BIAS = 6 * HP + OUTP;
 
 constexpr int OFF_X = 0;
-constexpr int OFF_S = OFF_X + X_BYTES;
-constexpr int OFF_W = OFF_S + S_BYTES;
+constexpr int OFF_W = OFF_X + X_BYTES;
 constexpr int OFF_BAR = OFF_W + NSLOT * STAGE_BYTES;
-constexpr int SMEM_BYTES = OFF_BAR + 128;
+constexpr int SMEM_BYTES = OFF_BAR + 8 * (2 * NSLOT + 4) + 16;
 static_assert(SMEM_BYTES <= 232448, "over the 227 KB per-CTA shared memory limit");
 static_assert(L3_STAGES * L3_KS_PER_STAGE == KS_H, "l3 stage split");
 
@@ -143,11 +140,17 @@ __device__ __forceinline__ float to_tf32(float x) {
     return __uint_as_float(r);
 }
 
-// Shared-memory matrix descriptor (sm_100 UMMA): start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46), version 1 [46,48),
-// layout type 0 = no swizzle [61,64).
-__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo, uint32_t sbo) {
-    return (uint64_t)((addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo >> 4) & 0x3FFFu) << 16) | ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) |
-           (1ull << 46);
+// Shared-memory matrix descriptor (sm_100 UMMA): start>>4 [0,14), LBO>>4 [16,30) (unused by a K-major swizzled operand
+// whose K extent is one swizzle atom; set to 1), SBO>>4 [32,46) = distance of 8-row groups, version 1 [46,48),
+// layout type [61,64) = 6: SWIZZLE_32B.
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t sbo) {
+    return (uint64_t)((addr >> 4) & 0x3FFFu) | (1ull << 16) | ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46) | (6ull << 61);
+}
+// Byte offset of 16-byte chunk `c` (4 tf32 of K) of row `r` inside an operand whose 8-row groups are `sbo` bytes apart:
+// K-major SWIZZLE_32B canonical layout - one 8-row x 32 B atom (256 B) per k-step, rows 32 B apart, and address bit 4
+// XORed with bit 7, i.e. the two chunks of rows 4..7 of a group trade places.
+__host__ __device__ __forceinline__ uint32_t op_off(uint32_t r, uint32_t c, uint32_t sbo) {
+    return (r >> 3) * sbo + (c >> 1) * 256u + (r & 7u) * 32u + (((c & 1u) ^ ((r >> 2) & 1u)) << 4);
 }
 // Instruction descriptor: D fp32 (1<<4), A and B tf32 (2<<7, 2<<10), both K-major, N>>3 at bit 17, M>>4 at bit 24.
 __host__ __device__ constexpr uint32_t idesc_tf32(int n) {
@@ -164,6 +167,7 @@ struct PolicyArgs {
     long long n;
     float max_action;
     int n_tiles;
+    long long* dbg;              // exo_policy_profile: clock64 stamps of CTA 0's first tile, or null
 };
 
 // stages per phase: G1, G2, G3, G4, G5a, G5b, G6, G7
@@ -172,7 +176,7 @@ __device__ __constant__ int PH_STAGES[N_PHASE] = {KS_S, KS_S, KS_H, KS_H, KS_H, 
 // ---- epilogues (one accumulator row per thread) ----------------------------------------------------------
 // act: 0 ELU, 1 ReLU. Writes the row into an operand-layout buffer in shared memory.
 template <int ACT>
-__device__ __forceinline__ void epi_act_to_x(uint32_t taddr, const float* __restrict__ bias, unsigned char* xrow) {
+__device__ __forceinline__ void epi_act_to_x(uint32_t taddr, const float* __restrict__ bias, unsigned char* xrow, uint32_t rsw) {
 #pragma unroll 1
     for (int cb = 0; cb < HP / 16; ++cb) {
         float v[16];
@@ -188,14 +192,14 @@ __device__ __forceinline__ void epi_act_to_x(uint32_t taddr, const float* __rest
                 else x = fmaxf(x, 0.f);
                 o[j] = to_tf32(x);
             }
-            *reinterpret_cast<float4*>(xrow + (cb * 4 + j4) * 128) = make_float4(o[0], o[1], o[2], o[3]);
+            *reinterpret_cast<float4*>(xrow + (cb * 2 + (j4 >> 1)) * 256 + (((j4 & 1) ^ rsw) << 4)) = make_float4(o[0], o[1], o[2], o[3]);
         }
     }
 }
 
 // AvgL1Norm (:59-60): x / clamp(mean|x|, 1e-8). dst is an operand-layout row (shared memory or the global scratch);
 // zs_row (optional) receives the un-rounded fp32 values row-major.
-__device__ __forceinline__ void epi_avgl1(uint32_t taddr, const float* __restrict__ bias, unsigned char* dst, float* zs_row) {
+__device__ __forceinline__ void epi_avgl1(uint32_t taddr, const float* __restrict__ bias, unsigned char* dst, uint32_t rsw, float* zs_row) {
     float s = 0.f;
 #pragma unroll 1
     for (int cb = 0; cb < HP / 16; ++cb) {
@@ -222,7 +226,8 @@ __device__ __forceinline__ void epi_avgl1(uint32_t taddr, const float* __restric
                 for (int j = 0; j < 4; ++j)
                     if (cb * 16 + j4 * 4 + j < HD) zs_row[cb * 16 + j4 * 4 + j] = o[j];
             }
-            *reinterpret_cast<float4*>(dst + (cb * 4 + j4) * 128) = make_float4(to_tf32(o[0]), to_tf32(o[1]), to_tf32(o[2]), to_tf32(o[3]));
+            *reinterpret_cast<float4*>(dst + (cb * 2 + (j4 >> 1)) * 256 + (((j4 & 1) ^ rsw) << 4)) =
+                make_float4(to_tf32(o[0]), to_tf32(o[1]), to_tf32(o[2]), to_tf32(o[3]));
         }
     }
 }
@@ -231,10 +236,10 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
     extern __shared__ __align__(1024) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t sbase = smem_u32(smem);
-    // barriers: full[3], empty[3], acc_full, a_ready, x_free, xr_full; then the TMEM base address
+    // barriers: full[NSLOT], empty[NSLOT], acc_full, a_ready, x_free, xr_full; then the TMEM base address
     const uint32_t bar_full = sbase + OFF_BAR, bar_empty = bar_full + 8 * NSLOT;
     const uint32_t bar_acc = bar_empty + 8 * NSLOT, bar_aready = bar_acc + 8, bar_xfree = bar_aready + 8, bar_xr = bar_xfree + 8;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + OFF_BAR + 96);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + OFF_BAR + 8 * (2 * NSLOT + 4));
 
     if (tid == 0) {
         for (int s = 0; s < NSLOT; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
@@ -277,8 +282,10 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
                     if (ph == 5) { mbar_wait(bar_xr, par_xr); par_xr ^= 1; }
                     else { mbar_wait(bar_aready, par_ar); par_ar ^= 1; }
                     tc_fence_after();
-                    const uint32_t a_base = sbase + (ph < 2 ? OFF_S : OFF_X);
-                    const uint32_t a_sbo = ph < 2 ? S_SBO : X_SBO;
+                    const bool stamp = a.dbg && tile == 0;
+                    if (stamp) a.dbg[2 * ph] = clock64();
+                    const uint32_t a_base = sbase + OFF_X;
+                    const uint32_t a_sbo = X_SBO;
                     const int nst = PH_STAGES[ph];
 #pragma unroll 1
                     for (int st = 0; st < nst; ++st, ++it) {
@@ -287,21 +294,22 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
                         tc_fence_after();
                         const uint32_t w = sbase + OFF_W + slot * STAGE_BYTES;
                         if (ph < 7) {
-                            const uint64_t ad = smem_desc(a_base + st * 256, 128, a_sbo);
+                            const uint64_t ad = smem_desc(a_base + st * 256, a_sbo);
                             const uint32_t acc = (st > 0 || ph == 5) ? 1u : 0u;
-                            tc_mma_tf32(tmem, ad, smem_desc(w, 128, 256), ID256, acc);
-                            tc_mma_tf32(tmem + 256, ad, smem_desc(w + 32 * 256, 128, 256), ID48, acc);
+                            tc_mma_tf32(tmem, ad, smem_desc(w, 256), ID256, acc);
+                            tc_mma_tf32(tmem + 256, ad, smem_desc(w + 32 * 256, 256), ID48, acc);
                         } else {
 #pragma unroll 1
                             for (int j = 0; j < L3_KS_PER_STAGE; ++j) {
                                 const int ks = st * L3_KS_PER_STAGE + j;
-                                tc_mma_tf32(tmem, smem_desc(a_base + ks * 256, 128, a_sbo), smem_desc(w + j * (OUTP * 32), 128, 256), ID16,
+                                tc_mma_tf32(tmem, smem_desc(a_base + ks * 256, a_sbo), smem_desc(w + j * (OUTP * 32), 256), ID16,
                                             ks > 0 ? 1u : 0u);
                             }
                         }
                         tc_commit(bar_empty + 8 * slot);      // frees the stage once these MMAs have read it
                     }
                     tc_commit(ph == 4 ? bar_xfree : bar_acc);  // G5a: X may be reloaded; otherwise: accumulator ready
+                    if (stamp) a.dbg[2 * ph + 1] = clock64();
                 }
             }
         }
@@ -311,43 +319,55 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
         const int q = warp & 3;                        // TMEM lane quarter this warp may read
         const int r = q * 32 + lane;                   // accumulator row = observation within the tile
         const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
-        unsigned char* xrow = smem + OFF_X + (r >> 3) * X_SBO + (r & 7) * 16;
+        unsigned char* xrow = smem + OFF_X + (r >> 3) * X_SBO + (r & 7) * 32;      // this thread's row; rsw: its chunk swizzle
+        const uint32_t rsw = ((uint32_t)r >> 2) & 1u;
         unsigned char* scratch = a.scratch + (size_t)blockIdx.x * X_BYTES;
-        unsigned char* srow = scratch + (r >> 3) * X_SBO + (r & 7) * 16;
+        unsigned char* srow = scratch + (r >> 3) * X_SBO + (r & 7) * 32;
         uint32_t par_acc = 0, par_xf = 0;
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
             const long long row0 = (long long)tile * TILE_M;
-            // E0: observations -> S (coalesced 16 B reads, rounded to TF32)
+            if (a.dbg && tile == 0 && et == 0) a.dbg[16] = clock64();
+            // E0: observations -> the first 20 chunks of X (coalesced 16 B reads, rounded to TF32); both layers that read
+            // them (l0, zs1) are done before E2 overwrites X
 #pragma unroll 4
             for (int i = 0; i < (TILE_M * SD / 4) / N_EPI; ++i) {
                 const int idx = i * N_EPI + et, rr = idx / (SD / 4), c = idx % (SD / 4);
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (row0 + rr < a.n) v = __ldg(reinterpret_cast<const float4*>(a.obs + (row0 + rr) * SD) + c);
-                *reinterpret_cast<float4*>(smem + OFF_S + (rr >> 3) * S_SBO + c * 128 + (rr & 7) * 16) =
+                *reinterpret_cast<float4*>(smem + OFF_X + op_off(rr, c, X_SBO)) =
                     make_float4(to_tf32(v.x), to_tf32(v.y), to_tf32(v.z), to_tf32(v.w));
             }
             fence_proxy_async_smem();
             tc_fence_before();
+            if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 0] = clock64();
             mbar_arrive(bar_aready);
             // E1: a0 = AvgL1Norm(l0(obs)) -> scratch
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
-            epi_avgl1(taddr, a.bias + B_L0, srow, nullptr);
+            if (a.dbg && tile == 0 && et == 0) a.dbg[16 + 2 * 1] = clock64();
+            epi_avgl1(taddr, a.bias + B_L0, srow, rsw, nullptr);
             __threadfence();
             fence_proxy_async_all();
             tc_fence_before();
+            if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 1] = clock64();
             mbar_arrive(bar_aready);
             asm volatile("bar.sync 1, 128;" ::: "memory");   // all 128 rows of a0 are out before anyone reloads them
             // E2, E3: ELU
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
-            epi_act_to_x<0>(taddr, a.bias + B_ZS1, xrow);
-            fence_proxy_async_smem(); tc_fence_before(); mbar_arrive(bar_aready);
+            if (a.dbg && tile == 0 && et == 0) a.dbg[16 + 2 * 2] = clock64();
+            epi_act_to_x<0>(taddr, a.bias + B_ZS1, xrow, rsw);
+            fence_proxy_async_smem(); tc_fence_before(); if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 2] = clock64();
+            mbar_arrive(bar_aready);
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
-            epi_act_to_x<0>(taddr, a.bias + B_ZS2, xrow);
-            fence_proxy_async_smem(); tc_fence_before(); mbar_arrive(bar_aready);
+            if (a.dbg && tile == 0 && et == 0) a.dbg[16 + 2 * 3] = clock64();
+            epi_act_to_x<0>(taddr, a.bias + B_ZS2, xrow, rsw);
+            fence_proxy_async_smem(); tc_fence_before(); if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 3] = clock64();
+            mbar_arrive(bar_aready);
             // E4: zs = AvgL1Norm(zs3(.))
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
-            epi_avgl1(taddr, a.bias + B_ZS3, xrow, (a.zs && row0 + r < a.n) ? a.zs + (row0 + r) * HD : nullptr);
-            fence_proxy_async_smem(); tc_fence_before(); mbar_arrive(bar_aready);
+            if (a.dbg && tile == 0 && et == 0) a.dbg[16 + 2 * 4] = clock64();
+            epi_avgl1(taddr, a.bias + B_ZS3, xrow, rsw, (a.zs && row0 + r < a.n) ? a.zs + (row0 + r) * HD : nullptr);
+            fence_proxy_async_smem(); tc_fence_before(); if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 4] = clock64();
+            mbar_arrive(bar_aready);
             // after G5a has read zs out of X, bring a0 back (16 bulk copies of one 8-row group each)
             if (et == 0) {
                 mbar_wait(bar_xfree, par_xf);
@@ -358,13 +378,18 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
             par_xf ^= 1;
             // E5, E6: ReLU
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
-            epi_act_to_x<1>(taddr, a.bias + B_L1, xrow);
-            fence_proxy_async_smem(); tc_fence_before(); mbar_arrive(bar_aready);
+            if (a.dbg && tile == 0 && et == 0) a.dbg[16 + 2 * 5] = clock64();
+            epi_act_to_x<1>(taddr, a.bias + B_L1, xrow, rsw);
+            fence_proxy_async_smem(); tc_fence_before(); if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 5] = clock64();
+            mbar_arrive(bar_aready);
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
-            epi_act_to_x<1>(taddr, a.bias + B_L2, xrow);
-            fence_proxy_async_smem(); tc_fence_before(); mbar_arrive(bar_aready);
+            if (a.dbg && tile == 0 && et == 0) a.dbg[16 + 2 * 6] = clock64();
+            epi_act_to_x<1>(taddr, a.bias + B_L2, xrow, rsw);
+            fence_proxy_async_smem(); tc_fence_before(); if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 6] = clock64();
+            mbar_arrive(bar_aready);
             // E7: actions
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
+            if (a.dbg && tile == 0 && et == 0) a.dbg[16 + 2 * 7] = clock64();
             {
                 float v[16];
                 tmem_ld16(taddr, v);
@@ -377,6 +402,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
                     }
                 }
             }
+            if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 7] = clock64();
             tc_fence_before();
         }
     }
@@ -398,13 +424,13 @@ inline float round_tf32(float x) {            // cvt.rna.tf32.f32: round to near
     return x;
 }
 
-// W[n_rows, ld] (columns col0 .. col0+k_real-1 used) -> `ksteps` k-steps of an `n_pad`-row K-major no-swizzle operand:
-// byte offset of element (n, k) = (k/8)*n_pad*32 + (n/8)*256 + ((k%8)/4)*128 + (n%8)*16 + (k%4)*4
+// W[n_rows, ld] (columns col0 .. col0+k_real-1 used) -> `ksteps` k-steps of an `n_pad`-row K-major SWIZZLE_32B operand:
+// byte offset of element (n, k) = (k/8)*n_pad*32 + op_off(n, (k%8)/4, 256) + (k%4)*4
 void pack_matrix(unsigned char* dst, const float* W, int n_rows, int ld, int col0, int k_real, int n_pad, int ksteps) {
     memset(dst, 0, (size_t)ksteps * n_pad * 32);
     for (int n = 0; n < n_rows; ++n)
         for (int k = 0; k < k_real; ++k) {
-            const size_t off = (size_t)(k / 8) * n_pad * 32 + (size_t)(n / 8) * 256 + ((k % 8) / 4) * 128 + (n % 8) * 16 + (k % 4) * 4;
+            const size_t off = (size_t)(k / 8) * n_pad * 32 + op_off((uint32_t)n, (uint32_t)((k % 8) / 4), 256u) + (k % 4) * 4;
             const float v = round_tf32(W[(size_t)n * ld + col0 + k]);
             memcpy(dst + off, &v, 4);
         }
@@ -418,6 +444,7 @@ struct ExoPolicy {
     unsigned char *pack, *scratch;
     float* bias;
     int64_t launches;
+    long long* dbg;
 };
 
 extern "C" int exo_policy_create(int32_t device, ExoPolicy** out) {
@@ -431,7 +458,7 @@ extern "C" int exo_policy_create(int32_t device, ExoPolicy** out) {
     PCK(cudaSetDevice(device));
     ExoPolicy* p = new ExoPolicy();
     p->device = device; p->n_sm = prop.multiProcessorCount; p->loaded = false; p->launches = 0;
-    p->pack = p->scratch = nullptr; p->bias = nullptr;
+    p->pack = p->scratch = nullptr; p->bias = nullptr; p->dbg = nullptr;
     cudaError_t e = cudaMalloc((void**)&p->pack, PACK_BYTES);
     if (e == cudaSuccess) e = cudaMalloc((void**)&p->scratch, (size_t)p->n_sm * X_BYTES);
     if (e == cudaSuccess) e = cudaMalloc((void**)&p->bias, N_BIAS * sizeof(float));
@@ -493,7 +520,7 @@ extern "C" int exo_policy_forward(ExoPolicy* p, const float* obs_dev, int64_t n,
     if (n == 0) return EXO_OK;
     PolicyArgs a;
     a.obs = obs_dev; a.pack = p->pack; a.bias = p->bias; a.scratch = p->scratch; a.actions = actions_dev; a.zs = zs_dev;
-    a.n = n; a.max_action = max_action;
+    a.n = n; a.max_action = max_action; a.dbg = p->dbg;
     const long long tiles = (n + TILE_M - 1) / TILE_M;
     if (tiles > 0x7FFFFFFF) return exo_set_error(EXO_ERR_ARG, "exo_policy_forward: too many observations");
     a.n_tiles = (int)tiles;
@@ -501,6 +528,24 @@ extern "C" int exo_policy_forward(ExoPolicy* p, const float* obs_dev, int64_t n,
     exo_policy_kernel<<<grid, N_THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(a);
     PCK(cudaGetLastError());
     p->launches += 1;
+    return EXO_OK;
+}
+
+extern "C" int exo_policy_profile(ExoPolicy* p, const float* obs_dev, int64_t n, float* actions_dev, int64_t* clocks_host, void* stream) {
+    if (!p || !clocks_host) return exo_set_error(EXO_ERR_ARG, "exo_policy_profile: bad arguments");
+    long long* d = nullptr;
+    PCK(cudaSetDevice(p->device));
+    PCK(cudaMalloc((void**)&d, 32 * sizeof(long long)));
+    PCK(cudaMemsetAsync(d, 0, 32 * sizeof(long long), (cudaStream_t)stream));
+    p->dbg = d;
+    const int rc = exo_policy_forward(p, obs_dev, n, 1.0f, actions_dev, nullptr, stream);
+    p->dbg = nullptr;
+    if (rc) { cudaFree(d); return rc; }
+    long long h[32];
+    PCK(cudaMemcpyAsync(h, d, sizeof(h), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    PCK(cudaStreamSynchronize((cudaStream_t)stream));
+    PCK(cudaFree(d));
+    for (int i = 0; i < 32; ++i) clocks_host[i] = h[i];
     return EXO_OK;
 }
 
