@@ -4,11 +4,14 @@
 //   observations resident in HBM. ~1.0 MFLOP per observation in seven small GEMMs: the one GEMM-shaped piece of the
 //   env -> agent loop, so this is where tcgen05 is used (the env step itself is HBM-bound 7x7 work).
 //
-// One persistent CTA per SM, 128 observations (= the 128 TMEM lanes = UMMA M) per tile, 192 threads:
+// One persistent CTA per SM, 128 observations (= the 128 TMEM lanes = UMMA M) per tile, 320 threads:
 //   warp 0 / lane 0   weight producer: cp.async.bulk (TMA engine, 1-D) global -> shared stages, mbarrier complete_tx
-//   warp 1            TMEM allocation; lane 0 issues every tcgen05.mma (kind::tf32, cta_group::1, M=128)
-//   warps 2..5        epilogue: tcgen05.ld the fp32 accumulator row (one row per thread), bias + activation, round to
-//                     TF32, store as the next layer's A operand in shared memory
+//   warp 1            TMEM allocation; one elected lane issues every tcgen05.mma (kind::tf32, cta_group::1, M=128,
+//                     N = 160 + 144 per k-step) - the warp stays converged so the issue path is the uniform datapath
+//   warps 2..9        epilogue: two warps per TMEM lane quarter (columns 0..159 / 160..303): tcgen05.ld 32 accumulator
+//                     columns at a time, activation, round to TF32, store as the next layer's A operand in shared memory
+// The biases ride in the GEMMs: every A operand carries a constant-1 column (index 300 of a hidden vector, 80 of an
+// observation) and the packed weights hold the bias there, so the epilogues load nothing but the accumulator.
 // Shared memory (223 904 B): X = 128 x 304 activations (152 KB; the observations sit in its first 80 columns until the
 // first hidden layer overwrites them), 7 weight stages of 9 728 B, mbarriers. Operands use the K-major no-swizzle canonical layout (8 rows x 16 B core matrices;
 // LBO = distance of the two 16 B K-chunks of one MMA, SBO = distance of 8-row groups), which the host packs the
@@ -39,14 +42,17 @@ int exo_set_error(int code, const char* fmt, ...);     // exo_api.cu
         if (_e != cudaSuccess) return exo_set_error(EXO_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); \
     } while (0)
 
+
 namespace {
 
 constexpr int SD = EXO_POLICY_STATE_DIM, HD = EXO_POLICY_HIDDEN_DIM, AD = EXO_POLICY_ACTION_DIM;
 constexpr int HP = 304;                     // hidden width padded: multiple of 8 (MMA K of tf32) and of 16 (MMA N)
+constexpr int SP = 88;                      // observation width padded to hold the constant-1 column (index 80)
 constexpr int OUTP = 16;                    // l3 rows padded to the smallest MMA N
 constexpr int TILE_M = 128;
-constexpr int KS_S = SD / 8;                // 10 k-steps over the observation
+constexpr int KS_S = SP / 8;                // 11 k-steps over the observation
 constexpr int KS_H = HP / 8;                // 38 k-steps over a hidden vector
+constexpr int N_LO = 160, N_HI = HP - N_LO; // the two MMAs of a k-step (N <= 256 per instruction) = the two epilogue halves
 constexpr int STAGE_BYTES = HP * 32;        // 9 728: one k-step (8 tf32 = 32 B per row) of a 304-row weight matrix
 constexpr int L3_KS_PER_STAGE = STAGE_BYTES / (OUTP * 32);   // 19 k-steps of the 16-row l3 per stage
 constexpr int L3_STAGES = KS_H / L3_KS_PER_STAGE;            // 2
@@ -54,22 +60,21 @@ constexpr int X_BYTES = TILE_M * HP * 4;    // 155 648
 constexpr int X_SBO = HP * 32;              // 9 728: 8 rows x (304 * 4 B)
 constexpr int NSLOT = 7;
 constexpr int N_PHASE = 8;
-constexpr int STAGES_PER_TILE = 2 * KS_S + 5 * KS_H + L3_STAGES;     // 212
-constexpr int PACK_BYTES = STAGES_PER_TILE * STAGE_BYTES;            // 2 062 336
-constexpr int N_BIAS = 6 * HP + OUTP;
+constexpr int STAGES_PER_TILE = 2 * KS_S + 5 * KS_H + L3_STAGES;     // 214
+constexpr int PACK_BYTES = STAGES_PER_TILE * STAGE_BYTES;            // 2 081 792
 
 constexpr int OFF_X = 0;
 constexpr int OFF_W = OFF_X + X_BYTES;
 constexpr int OFF_BAR = OFF_W + NSLOT * STAGE_BYTES;
-constexpr int SMEM_BYTES = OFF_BAR + 8 * (2 * NSLOT + 4) + 16;
+constexpr int OFF_PART = OFF_BAR + 8 * (2 * NSLOT + 4) + 16;       // AvgL1Norm partial sums [2][128] floats
+constexpr int SMEM_BYTES = OFF_PART + 2 * TILE_M * 4;
 static_assert(SMEM_BYTES <= 232448, "over the 227 KB per-CTA shared memory limit");
 static_assert(L3_STAGES * L3_KS_PER_STAGE == KS_H, "l3 stage split");
+static_assert(N_LO % 32 == 0 && N_HI % 16 == 0 && N_HI > 128, "epilogue column split");
 
-constexpr int N_THREADS = 192;
-constexpr int N_EPI = 128;
-
-// bias block offsets (floats) in the order the epilogues use them
-enum { B_L0 = 0, B_ZS1 = HP, B_ZS2 = 2 * HP, B_ZS3 = 3 * HP, B_L1 = 4 * HP, B_L2 = 5 * HP, B_L3 = 6 * HP };
+constexpr int N_EPI = 256;
+constexpr int N_THREADS = 64 + N_EPI;
+constexpr int OBS_V4_PER_THREAD = (TILE_M * SD / 4) / N_EPI;       // 10
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -123,21 +128,30 @@ __device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t a_desc, ui
         ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
-    uint32_t r[16];
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]),
+          "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]),
+          "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
         : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
           "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
         : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
-__device__ __forceinline__ float to_tf32(float x) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-    return __uint_as_float(r);
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// cvt.rna.tf32.f32 (round to nearest, ties away from zero, 10-bit mantissa) as two integer operations
+__device__ __forceinline__ float to_tf32(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u); }
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\telect.sync rx|px, %1;\n\tselp.b32 %0, 1, 0, px;\n\t}" : "=r"(pred) : "r"(0xFFFFFFFFu));
+    return pred != 0;
 }
 
 // Shared-memory matrix descriptor (sm_100 UMMA): start>>4 [0,14), LBO>>4 [16,30) (unused by a K-major swizzled operand
@@ -160,7 +174,6 @@ __host__ __device__ constexpr uint32_t idesc_tf32(int n) {
 struct PolicyArgs {
     const float* obs;            // [n, 80]
     const unsigned char* pack;   // STAGES_PER_TILE stages of STAGE_BYTES, in consumption order
-    const float* bias;           // N_BIAS floats
     unsigned char* scratch;      // gridDim.x * X_BYTES (a0 in operand layout)
     float* actions;              // [n, 7]
     float* zs;                   // [n, 300] or null
@@ -173,64 +186,96 @@ struct PolicyArgs {
 // stages per phase: G1, G2, G3, G4, G5a, G5b, G6, G7
 __device__ __constant__ int PH_STAGES[N_PHASE] = {KS_S, KS_S, KS_H, KS_H, KS_H, KS_H, KS_H, L3_STAGES};
 
-// ---- epilogues (one accumulator row per thread) ----------------------------------------------------------
-// act: 0 ELU, 1 ReLU. Writes the row into an operand-layout buffer in shared memory.
-template <int ACT>
-__device__ __forceinline__ void epi_act_to_x(uint32_t taddr, const float* __restrict__ bias, unsigned char* xrow, uint32_t rsw) {
-#pragma unroll 1
-    for (int cb = 0; cb < HP / 16; ++cb) {
-        float v[16];
-        tmem_ld16(taddr + cb * 16, v);
+// ---- epilogues: a thread owns row r of the tile and the column half `half` (0: 0..159, 1: 160..303) ---------------
+// Stores 4 consecutive columns (chunk index c of the row) of an operand-layout row.
+__device__ __forceinline__ void st_chunk(unsigned char* row, uint32_t rsw, int c, float a, float b, float cc, float d) {
+    *reinterpret_cast<float4*>(row + (c >> 1) * 256 + ((((uint32_t)c & 1u) ^ rsw) << 4)) = make_float4(a, b, cc, d);
+}
+
+// ACT 0: ELU, 1: ReLU, 2: multiply by `scale` (second pass of AvgL1Norm). Processes NCOL (32 or 16) accumulator columns
+// starting at column col0 and writes them, rounded to TF32, into the operand row; column 300 becomes the constant 1.
+template <int ACT, int NCOL>
+__device__ __forceinline__ void epi_block(const uint32_t* v, int col0, unsigned char* row, uint32_t rsw, float scale, float* zs_row) {
 #pragma unroll
-        for (int j4 = 0; j4 < 4; ++j4) {
-            const float4 b = __ldg(reinterpret_cast<const float4*>(bias + cb * 16 + j4 * 4));
-            float o[4] = {v[j4 * 4] + b.x, v[j4 * 4 + 1] + b.y, v[j4 * 4 + 2] + b.z, v[j4 * 4 + 3] + b.w};
+    for (int j4 = 0; j4 < NCOL / 4; ++j4) {
+        float o[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                float x = o[j];
-                if (ACT == 0) x = x > 0.f ? x : (__expf(x) - 1.f);
-                else x = fmaxf(x, 0.f);
-                o[j] = to_tf32(x);
-            }
-            *reinterpret_cast<float4*>(xrow + (cb * 2 + (j4 >> 1)) * 256 + (((j4 & 1) ^ rsw) << 4)) = make_float4(o[0], o[1], o[2], o[3]);
+        for (int j = 0; j < 4; ++j) {
+            float x = __uint_as_float(v[j4 * 4 + j]);
+            if (ACT == 0) { const float e = __expf(fminf(x, 0.f)) - 1.f; x = x > 0.f ? x : e; }
+            else if (ACT == 1) x = fmaxf(x, 0.f);
+            else x *= scale;
+            o[j] = x;
         }
+        if (ACT == 2 && zs_row) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (col0 + j4 * 4 + j < HD) zs_row[col0 + j4 * 4 + j] = o[j];
+        }
+        if (col0 + j4 * 4 == HD) o[0] = 1.0f;              // the bias column of the next GEMM
+        st_chunk(row, rsw, (col0 >> 2) + j4, to_tf32(o[0]), to_tf32(o[1]), to_tf32(o[2]), to_tf32(o[3]));
     }
 }
 
-// AvgL1Norm (:59-60): x / clamp(mean|x|, 1e-8). dst is an operand-layout row (shared memory or the global scratch);
-// zs_row (optional) receives the un-rounded fp32 values row-major.
-__device__ __forceinline__ void epi_avgl1(uint32_t taddr, const float* __restrict__ bias, unsigned char* dst, uint32_t rsw, float* zs_row) {
-    float s = 0.f;
+template <int ACT>
+__device__ __forceinline__ void epi_half(uint32_t taddr, int half, unsigned char* row, uint32_t rsw, float scale, float* zs_row) {
+    uint32_t v[32];
+    const int c0 = half * N_LO;
 #pragma unroll 1
-    for (int cb = 0; cb < HP / 16; ++cb) {
-        float v[16];
-        tmem_ld16(taddr + cb * 16, v);
-#pragma unroll
-        for (int j4 = 0; j4 < 4; ++j4) {
-            const float4 b = __ldg(reinterpret_cast<const float4*>(bias + cb * 16 + j4 * 4));
-            s += fabsf(v[j4 * 4] + b.x) + fabsf(v[j4 * 4 + 1] + b.y) + fabsf(v[j4 * 4 + 2] + b.z) + fabsf(v[j4 * 4 + 3] + b.w);
-        }
+    for (int b = 0; b < 4; ++b) {
+        tmem_ld32(taddr + c0 + b * 32, v);
+        tmem_ld_wait();
+        epi_block<ACT, 32>(v, c0 + b * 32, row, rsw, scale, zs_row);
     }
-    const float denom = fmaxf(s / (float)HD, 1e-8f);     // pad columns are exactly 0 and do not touch the sum
-#pragma unroll 1
-    for (int cb = 0; cb < HP / 16; ++cb) {
-        float v[16];
-        tmem_ld16(taddr + cb * 16, v);
-#pragma unroll
-        for (int j4 = 0; j4 < 4; ++j4) {
-            const float4 b = __ldg(reinterpret_cast<const float4*>(bias + cb * 16 + j4 * 4));
-            float o[4] = {(v[j4 * 4] + b.x) / denom, (v[j4 * 4 + 1] + b.y) / denom, (v[j4 * 4 + 2] + b.z) / denom,
-                          (v[j4 * 4 + 3] + b.w) / denom};
-            if (zs_row) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    if (cb * 16 + j4 * 4 + j < HD) zs_row[cb * 16 + j4 * 4 + j] = o[j];
-            }
-            *reinterpret_cast<float4*>(dst + (cb * 2 + (j4 >> 1)) * 256 + (((j4 & 1) ^ rsw) << 4)) =
-                make_float4(to_tf32(o[0]), to_tf32(o[1]), to_tf32(o[2]), to_tf32(o[3]));
-        }
+    if (half == 0) {
+        tmem_ld32(taddr + 128, v);
+        tmem_ld_wait();
+        epi_block<ACT, 32>(v, 128, row, rsw, scale, zs_row);
+    } else {
+        tmem_ld16(taddr + N_LO + 128, v);
+        tmem_ld_wait();
+        epi_block<ACT, 16>(v, N_LO + 128, row, rsw, scale, zs_row);
     }
 }
+
+// sum of |accumulator| over this thread's column half
+__device__ __forceinline__ float epi_abs_sum(uint32_t taddr, int half) {
+    uint32_t v[32];
+    const int c0 = half * N_LO;
+    float s = 0.f;
+#pragma unroll 1
+    for (int b = 0; b < 4; ++b) {
+        tmem_ld32(taddr + c0 + b * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) s += fabsf(__uint_as_float(v[j]));
+    }
+    if (half == 0) {
+        tmem_ld32(taddr + 128, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) s += fabsf(__uint_as_float(v[j]));
+    } else {
+        tmem_ld16(taddr + N_LO + 128, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) s += fabsf(__uint_as_float(v[j]));
+    }
+    return s;
+}
+
+// AvgL1Norm (:59-60): x / clamp(mean|x|, 1e-8); the two column halves of a row exchange their partial sums through
+// shared memory (pad columns are exactly 0 and do not touch the sum). Returns 1 / denominator.
+__device__ __forceinline__ float avgl1_scale(uint32_t taddr, int half, int r, float* part) {
+    const float s = epi_abs_sum(taddr, half);
+    part[half * TILE_M + r] = s;
+    asm volatile("bar.sync 2, 256;" ::: "memory");
+    const float tot = s + part[(half ^ 1) * TILE_M + r];
+    asm volatile("bar.sync 2, 256;" ::: "memory");       // part[] may be rewritten by the next normalisation
+    return 1.0f / fmaxf(tot * (1.0f / (float)HD), 1e-8f);
+}
+
+#define STAMP(i) do { if (a.dbg && tile == 0 && et == 0) a.dbg[i] = clock64(); } while (0)
 
 __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
@@ -261,112 +306,139 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
     if (warp == 0) {
         // ===== weight producer ==========================================================================
         if (lane == 0) {
-            uint32_t it = 0;
+            uint32_t slot = 0, par = 1;
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
-                for (int i = 0; i < STAGES_PER_TILE; ++i, ++it) {
-                    const uint32_t slot = it % NSLOT, use = it / NSLOT;
-                    mbar_wait(bar_empty + 8 * slot, (use & 1) ^ 1);
+                const unsigned char* src = a.pack;
+#pragma unroll 1
+                for (int i = 0; i < STAGES_PER_TILE; ++i, src += STAGE_BYTES) {
+                    mbar_wait(bar_empty + 8 * slot, par);
                     mbar_expect_tx(bar_full + 8 * slot, STAGE_BYTES);
-                    bulk_g2s(sbase + OFF_W + slot * STAGE_BYTES, a.pack + (size_t)i * STAGE_BYTES, STAGE_BYTES, bar_full + 8 * slot);
+                    bulk_g2s(sbase + OFF_W + slot * STAGE_BYTES, src, STAGE_BYTES, bar_full + 8 * slot);
+                    if (++slot == NSLOT) { slot = 0; par ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer ===============================================================================
-        if (lane == 0) {
-            uint32_t it = 0, par_ar = 0, par_xr = 0;
-            constexpr uint32_t ID256 = idesc_tf32(256), ID48 = idesc_tf32(48), ID16 = idesc_tf32(OUTP);
-            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+        // ===== MMA issuer: the whole warp walks the pipeline, one elected lane issues =====================
+        uint32_t slot = 0, par = 0, par_ar = 0, par_xr = 0;
+        constexpr uint32_t IDLO = idesc_tf32(N_LO), IDHI = idesc_tf32(N_HI), ID16 = idesc_tf32(OUTP);
+        const uint64_t a_desc0 = smem_desc(sbase + OFF_X, X_SBO);
+        const uint64_t b_desc0 = smem_desc(sbase + OFF_W, 256);
+        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
 #pragma unroll 1
-                for (int ph = 0; ph < N_PHASE; ++ph) {
-                    if (ph == 5) { mbar_wait(bar_xr, par_xr); par_xr ^= 1; }
-                    else { mbar_wait(bar_aready, par_ar); par_ar ^= 1; }
+            for (int ph = 0; ph < N_PHASE; ++ph) {
+                if (ph == 5) { mbar_wait(bar_xr, par_xr); par_xr ^= 1; }
+                else { mbar_wait(bar_aready, par_ar); par_ar ^= 1; }
+                tc_fence_after();
+                const bool stamp = a.dbg && tile == 0 && lane == 0;
+                if (stamp) a.dbg[2 * ph] = clock64();
+                const int nst = PH_STAGES[ph];
+                uint64_t ad = a_desc0;
+#pragma unroll 1
+                for (int st = 0; st < nst; ++st) {
+                    mbar_wait(bar_full + 8 * slot, par);
                     tc_fence_after();
-                    const bool stamp = a.dbg && tile == 0;
-                    if (stamp) a.dbg[2 * ph] = clock64();
-                    const uint32_t a_base = sbase + OFF_X;
-                    const uint32_t a_sbo = X_SBO;
-                    const int nst = PH_STAGES[ph];
-#pragma unroll 1
-                    for (int st = 0; st < nst; ++st, ++it) {
-                        const uint32_t slot = it % NSLOT, use = it / NSLOT;
-                        mbar_wait(bar_full + 8 * slot, use & 1);
-                        tc_fence_after();
-                        const uint32_t w = sbase + OFF_W + slot * STAGE_BYTES;
+                    const uint64_t bd = b_desc0 + (uint64_t)(slot * (STAGE_BYTES >> 4));
+                    if (elect_one()) {
                         if (ph < 7) {
-                            const uint64_t ad = smem_desc(a_base + st * 256, a_sbo);
                             const uint32_t acc = (st > 0 || ph == 5) ? 1u : 0u;
-                            tc_mma_tf32(tmem, ad, smem_desc(w, 256), ID256, acc);
-                            tc_mma_tf32(tmem + 256, ad, smem_desc(w + 32 * 256, 256), ID48, acc);
+                            tc_mma_tf32(tmem, ad, bd, IDLO, acc);
+                            tc_mma_tf32(tmem + N_LO, ad, bd + (uint64_t)((N_LO / 8) * 256 >> 4), IDHI, acc);
                         } else {
-#pragma unroll 1
-                            for (int j = 0; j < L3_KS_PER_STAGE; ++j) {
-                                const int ks = st * L3_KS_PER_STAGE + j;
-                                tc_mma_tf32(tmem, smem_desc(a_base + ks * 256, a_sbo), smem_desc(w + j * (OUTP * 32), 256), ID16,
-                                            ks > 0 ? 1u : 0u);
-                            }
+#pragma unroll
+                            for (int j = 0; j < L3_KS_PER_STAGE; ++j)
+                                tc_mma_tf32(tmem, ad + (uint64_t)(j * 16), bd + (uint64_t)(j * (OUTP * 32 >> 4)), ID16, (st > 0 || j > 0) ? 1u : 0u);
                         }
                         tc_commit(bar_empty + 8 * slot);      // frees the stage once these MMAs have read it
                     }
-                    tc_commit(ph == 4 ? bar_xfree : bar_acc);  // G5a: X may be reloaded; otherwise: accumulator ready
-                    if (stamp) a.dbg[2 * ph + 1] = clock64();
+                    __syncwarp();
+                    ad += (ph < 7) ? 16u : (uint64_t)(L3_KS_PER_STAGE * 16);    // 256 B (one k-step) >> 4
+                    if (++slot == NSLOT) { slot = 0; par ^= 1; }
                 }
+                if (elect_one()) tc_commit(ph == 4 ? bar_xfree : bar_acc);  // G5a: X may be reloaded; else: accumulator ready
+                __syncwarp();
+                if (stamp) a.dbg[2 * ph + 1] = clock64();
             }
         }
     } else {
         // ===== epilogue warps ===========================================================================
-        const int et = tid - 64;                       // 0..127
+        const int et = tid - 64;                       // 0..255
+        const int half = et >> 7;                      // column half
         const int q = warp & 3;                        // TMEM lane quarter this warp may read
         const int r = q * 32 + lane;                   // accumulator row = observation within the tile
         const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
-        unsigned char* xrow = smem + OFF_X + (r >> 3) * X_SBO + (r & 7) * 32;      // this thread's row; rsw: its chunk swizzle
-        const uint32_t rsw = ((uint32_t)r >> 2) & 1u;
+        const uint32_t rsw = ((uint32_t)r >> 2) & 1u;  // chunk swizzle of this row
+        unsigned char* xrow = smem + OFF_X + (r >> 3) * X_SBO + (r & 7) * 32;
         unsigned char* scratch = a.scratch + (size_t)blockIdx.x * X_BYTES;
         unsigned char* srow = scratch + (r >> 3) * X_SBO + (r & 7) * 32;
+        float* part = reinterpret_cast<float*>(smem + OFF_PART);
         uint32_t par_acc = 0, par_xf = 0;
+        float4 ob[OBS_V4_PER_THREAD];                  // this thread's share of the next tile's observations
+        auto load_obs = [&](int tile) {
+            const long long row0 = (long long)tile * TILE_M;
+#pragma unroll
+            for (int i = 0; i < OBS_V4_PER_THREAD; ++i) {
+                const int idx = i * N_EPI + et, rr = idx / (SD / 4), c = idx % (SD / 4);
+                ob[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (tile < a.n_tiles && row0 + rr < a.n) ob[i] = __ldg(reinterpret_cast<const float4*>(a.obs + (row0 + rr) * SD) + c);
+            }
+        };
+        load_obs(blockIdx.x);
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
             const long long row0 = (long long)tile * TILE_M;
-            if (a.dbg && tile == 0 && et == 0) a.dbg[16] = clock64();
-            // E0: observations -> the first 20 chunks of X (coalesced 16 B reads, rounded to TF32); both layers that read
-            // them (l0, zs1) are done before E2 overwrites X
-#pragma unroll 4
-            for (int i = 0; i < (TILE_M * SD / 4) / N_EPI; ++i) {
+            STAMP(16);
+            // E0: observations -> the first 22 chunks of X (80 values, the constant 1, 7 zeros), rounded to TF32; both
+            // layers that read them (l0, zs1) are done before E2 overwrites X. Then prefetch the next tile's.
+#pragma unroll
+            for (int i = 0; i < OBS_V4_PER_THREAD; ++i) {
                 const int idx = i * N_EPI + et, rr = idx / (SD / 4), c = idx % (SD / 4);
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (row0 + rr < a.n) v = __ldg(reinterpret_cast<const float4*>(a.obs + (row0 + rr) * SD) + c);
                 *reinterpret_cast<float4*>(smem + OFF_X + op_off(rr, c, X_SBO)) =
-                    make_float4(to_tf32(v.x), to_tf32(v.y), to_tf32(v.z), to_tf32(v.w));
+                    make_float4(to_tf32(ob[i].x), to_tf32(ob[i].y), to_tf32(ob[i].z), to_tf32(ob[i].w));
+            }
+            {
+                const int rr = et & 127, c = SD / 4 + half;           // chunk 20: (1,0,0,0); chunk 21: zeros
+                *reinterpret_cast<float4*>(smem + OFF_X + op_off(rr, c, X_SBO)) = make_float4(half ? 0.f : 1.f, 0.f, 0.f, 0.f);
             }
             fence_proxy_async_smem();
             tc_fence_before();
-            if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 0] = clock64();
+            STAMP(17);
             mbar_arrive(bar_aready);
+            load_obs(tile + gridDim.x);
             // E1: a0 = AvgL1Norm(l0(obs)) -> scratch
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
-            if (a.dbg && tile == 0 && et == 0) a.dbg[16 + 2 * 1] = clock64();
-            epi_avgl1(taddr, a.bias + B_L0, srow, rsw, nullptr);
+            STAMP(18);
+            {
+                const float sc = avgl1_scale(taddr, half, r, part);
+                epi_half<2>(taddr, half, srow, rsw, sc, nullptr);
+            }
             __threadfence();
             fence_proxy_async_all();
             tc_fence_before();
-            if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 1] = clock64();
+            STAMP(19);
             mbar_arrive(bar_aready);
-            asm volatile("bar.sync 1, 128;" ::: "memory");   // all 128 rows of a0 are out before anyone reloads them
+            asm volatile("bar.sync 1, 256;" ::: "memory");   // all of a0 is out before anyone reloads it
             // E2, E3: ELU
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
-            if (a.dbg && tile == 0 && et == 0) a.dbg[16 + 2 * 2] = clock64();
-            epi_act_to_x<0>(taddr, a.bias + B_ZS1, xrow, rsw);
-            fence_proxy_async_smem(); tc_fence_before(); if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 2] = clock64();
+            STAMP(20);
+            epi_half<0>(taddr, half, xrow, rsw, 0.f, nullptr);
+            fence_proxy_async_smem(); tc_fence_before();
+            STAMP(21);
             mbar_arrive(bar_aready);
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
-            if (a.dbg && tile == 0 && et == 0) a.dbg[16 + 2 * 3] = clock64();
-            epi_act_to_x<0>(taddr, a.bias + B_ZS2, xrow, rsw);
-            fence_proxy_async_smem(); tc_fence_before(); if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 3] = clock64();
+            STAMP(22);
+            epi_half<0>(taddr, half, xrow, rsw, 0.f, nullptr);
+            fence_proxy_async_smem(); tc_fence_before();
+            STAMP(23);
             mbar_arrive(bar_aready);
             // E4: zs = AvgL1Norm(zs3(.))
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
-            if (a.dbg && tile == 0 && et == 0) a.dbg[16 + 2 * 4] = clock64();
-            epi_avgl1(taddr, a.bias + B_ZS3, xrow, rsw, (a.zs && row0 + r < a.n) ? a.zs + (row0 + r) * HD : nullptr);
-            fence_proxy_async_smem(); tc_fence_before(); if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 4] = clock64();
+            STAMP(24);
+            {
+                const float sc = avgl1_scale(taddr, half, r, part);
+                epi_half<2>(taddr, half, xrow, rsw, sc, (a.zs && row0 + r < a.n) ? a.zs + (row0 + r) * HD : nullptr);
+            }
+            fence_proxy_async_smem(); tc_fence_before();
+            STAMP(25);
             mbar_arrive(bar_aready);
             // after G5a has read zs out of X, bring a0 back (16 bulk copies of one 8-row group each)
             if (et == 0) {
@@ -378,31 +450,31 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
             par_xf ^= 1;
             // E5, E6: ReLU
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
-            if (a.dbg && tile == 0 && et == 0) a.dbg[16 + 2 * 5] = clock64();
-            epi_act_to_x<1>(taddr, a.bias + B_L1, xrow, rsw);
-            fence_proxy_async_smem(); tc_fence_before(); if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 5] = clock64();
+            STAMP(26);
+            epi_half<1>(taddr, half, xrow, rsw, 0.f, nullptr);
+            fence_proxy_async_smem(); tc_fence_before();
+            STAMP(27);
             mbar_arrive(bar_aready);
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
-            if (a.dbg && tile == 0 && et == 0) a.dbg[16 + 2 * 6] = clock64();
-            epi_act_to_x<1>(taddr, a.bias + B_L2, xrow, rsw);
-            fence_proxy_async_smem(); tc_fence_before(); if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 6] = clock64();
+            STAMP(28);
+            epi_half<1>(taddr, half, xrow, rsw, 0.f, nullptr);
+            fence_proxy_async_smem(); tc_fence_before();
+            STAMP(29);
             mbar_arrive(bar_aready);
-            // E7: actions
+            // E7: actions (column half 0 only; the other warps just keep the barrier phases)
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
-            if (a.dbg && tile == 0 && et == 0) a.dbg[16 + 2 * 7] = clock64();
-            {
-                float v[16];
+            STAMP(30);
+            if (half == 0) {
+                uint32_t v[16];
                 tmem_ld16(taddr, v);
+                tmem_ld_wait();
                 if (row0 + r < a.n) {
                     float* out = a.actions + (row0 + r) * AD;
 #pragma unroll
-                    for (int j = 0; j < AD; ++j) {
-                        const float t = tanhf(v[j] + __ldg(a.bias + B_L3 + j));
-                        out[j] = fminf(fmaxf(t, -1.f), 1.f) * a.max_action;
-                    }
+                    for (int j = 0; j < AD; ++j) out[j] = fminf(fmaxf(tanhf(__uint_as_float(v[j])), -1.f), 1.f) * a.max_action;
                 }
             }
-            if (a.dbg && tile == 0 && et == 0) a.dbg[17 + 2 * 7] = clock64();
+            STAMP(31);
             tc_fence_before();
         }
     }
@@ -425,13 +497,15 @@ inline float round_tf32(float x) {            // cvt.rna.tf32.f32: round to near
 }
 
 // W[n_rows, ld] (columns col0 .. col0+k_real-1 used) -> `ksteps` k-steps of an `n_pad`-row K-major SWIZZLE_32B operand:
-// byte offset of element (n, k) = (k/8)*n_pad*32 + op_off(n, (k%8)/4, 256) + (k%4)*4
-void pack_matrix(unsigned char* dst, const float* W, int n_rows, int ld, int col0, int k_real, int n_pad, int ksteps) {
+// byte offset of element (n, k) = (k/8)*n_pad*32 + op_off(n, (k%8)/4, 256) + (k%4)*4. If `bias` is given it becomes
+// column k_real (the A operand holds the constant 1 there), rounded to TF32 like the weights.
+void pack_matrix(unsigned char* dst, const float* W, const float* bias, int n_rows, int ld, int col0, int k_real, int n_pad, int ksteps) {
     memset(dst, 0, (size_t)ksteps * n_pad * 32);
     for (int n = 0; n < n_rows; ++n)
-        for (int k = 0; k < k_real; ++k) {
+        for (int k = 0; k <= k_real; ++k) {
+            if (k == k_real && !bias) break;
             const size_t off = (size_t)(k / 8) * n_pad * 32 + op_off((uint32_t)n, (uint32_t)((k % 8) / 4), 256u) + (k % 4) * 4;
-            const float v = round_tf32(W[(size_t)n * ld + col0 + k]);
+            const float v = round_tf32(k < k_real ? W[(size_t)n * ld + col0 + k] : bias[n]);
             memcpy(dst + off, &v, 4);
         }
 }
@@ -442,7 +516,6 @@ struct ExoPolicy {
     int device, n_sm;
     bool loaded;
     unsigned char *pack, *scratch;
-    float* bias;
     int64_t launches;
     long long* dbg;
 };
@@ -458,10 +531,9 @@ extern "C" int exo_policy_create(int32_t device, ExoPolicy** out) {
     PCK(cudaSetDevice(device));
     ExoPolicy* p = new ExoPolicy();
     p->device = device; p->n_sm = prop.multiProcessorCount; p->loaded = false; p->launches = 0;
-    p->pack = p->scratch = nullptr; p->bias = nullptr; p->dbg = nullptr;
+    p->pack = p->scratch = nullptr; p->dbg = nullptr;
     cudaError_t e = cudaMalloc((void**)&p->pack, PACK_BYTES);
     if (e == cudaSuccess) e = cudaMalloc((void**)&p->scratch, (size_t)p->n_sm * X_BYTES);
-    if (e == cudaSuccess) e = cudaMalloc((void**)&p->bias, N_BIAS * sizeof(float));
     if (e == cudaSuccess) e = cudaMemset(p->scratch, 0, (size_t)p->n_sm * X_BYTES);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(exo_policy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) {
@@ -475,7 +547,7 @@ extern "C" int exo_policy_create(int32_t device, ExoPolicy** out) {
 extern "C" int exo_policy_destroy(ExoPolicy* p) {
     if (!p) return EXO_OK;
     cudaSetDevice(p->device);
-    cudaFree(p->pack); cudaFree(p->scratch); cudaFree(p->bias);
+    cudaFree(p->pack); cudaFree(p->scratch);
     delete p;
     return EXO_OK;
 }
@@ -490,24 +562,20 @@ extern "C" int exo_policy_set_weights(ExoPolicy* p, const ExoPolicyWeights* w, i
     for (const float* q : ptrs)
         if (!q) return exo_set_error(EXO_ERR_ARG, "exo_policy_set_weights: null matrix");
     std::vector<unsigned char> pack(PACK_BYTES);
-    std::vector<float> bias(N_BIAS, 0.f);
     unsigned char* d = pack.data();
     // consumption order of the kernel: G1 l0, G2 zs1, G3 zs2, G4 zs3, G5a l1[:,300:600], G5b l1[:,0:300], G6 l2, G7 l3
-    pack_matrix(d, w->l0_w, HD, SD, 0, SD, HP, KS_S);        d += (size_t)KS_S * STAGE_BYTES;
-    pack_matrix(d, w->zs1_w, HD, SD, 0, SD, HP, KS_S);       d += (size_t)KS_S * STAGE_BYTES;
-    pack_matrix(d, w->zs2_w, HD, HD, 0, HD, HP, KS_H);       d += (size_t)KS_H * STAGE_BYTES;
-    pack_matrix(d, w->zs3_w, HD, HD, 0, HD, HP, KS_H);       d += (size_t)KS_H * STAGE_BYTES;
-    pack_matrix(d, w->l1_w, HD, 2 * HD, HD, HD, HP, KS_H);   d += (size_t)KS_H * STAGE_BYTES;
-    pack_matrix(d, w->l1_w, HD, 2 * HD, 0, HD, HP, KS_H);    d += (size_t)KS_H * STAGE_BYTES;
-    pack_matrix(d, w->l2_w, HD, HD, 0, HD, HP, KS_H);        d += (size_t)KS_H * STAGE_BYTES;
-    pack_matrix(d, w->l3_w, AD, HD, 0, HD, OUTP, KS_H);      d += (size_t)L3_STAGES * STAGE_BYTES;
+    // (the l1 bias rides with the a0 half: G5b's operand is the reloaded a0, whose column 300 is the constant 1)
+    pack_matrix(d, w->l0_w, w->l0_b, HD, SD, 0, SD, HP, KS_S);        d += (size_t)KS_S * STAGE_BYTES;
+    pack_matrix(d, w->zs1_w, w->zs1_b, HD, SD, 0, SD, HP, KS_S);      d += (size_t)KS_S * STAGE_BYTES;
+    pack_matrix(d, w->zs2_w, w->zs2_b, HD, HD, 0, HD, HP, KS_H);      d += (size_t)KS_H * STAGE_BYTES;
+    pack_matrix(d, w->zs3_w, w->zs3_b, HD, HD, 0, HD, HP, KS_H);      d += (size_t)KS_H * STAGE_BYTES;
+    pack_matrix(d, w->l1_w, nullptr, HD, 2 * HD, HD, HD, HP, KS_H);   d += (size_t)KS_H * STAGE_BYTES;
+    pack_matrix(d, w->l1_w, w->l1_b, HD, 2 * HD, 0, HD, HP, KS_H);    d += (size_t)KS_H * STAGE_BYTES;
+    pack_matrix(d, w->l2_w, w->l2_b, HD, HD, 0, HD, HP, KS_H);        d += (size_t)KS_H * STAGE_BYTES;
+    pack_matrix(d, w->l3_w, w->l3_b, AD, HD, 0, HD, OUTP, KS_H);      d += (size_t)L3_STAGES * STAGE_BYTES;
     if (d != pack.data() + PACK_BYTES) return exo_set_error(EXO_ERR_STATE, "exo_policy_set_weights: pack size mismatch");
-    memcpy(&bias[B_L0], w->l0_b, HD * 4);   memcpy(&bias[B_ZS1], w->zs1_b, HD * 4); memcpy(&bias[B_ZS2], w->zs2_b, HD * 4);
-    memcpy(&bias[B_ZS3], w->zs3_b, HD * 4); memcpy(&bias[B_L1], w->l1_b, HD * 4);   memcpy(&bias[B_L2], w->l2_b, HD * 4);
-    memcpy(&bias[B_L3], w->l3_b, AD * 4);
     PCK(cudaSetDevice(p->device));
     PCK(cudaMemcpy(p->pack, pack.data(), PACK_BYTES, cudaMemcpyHostToDevice));
-    PCK(cudaMemcpy(p->bias, bias.data(), N_BIAS * sizeof(float), cudaMemcpyHostToDevice));
     p->loaded = true;
     return EXO_OK;
 }
@@ -519,7 +587,7 @@ extern "C" int exo_policy_forward(ExoPolicy* p, const float* obs_dev, int64_t n,
     if (((uintptr_t)obs_dev & 15) != 0) return exo_set_error(EXO_ERR_ARG, "exo_policy_forward: obs must be 16-byte aligned");
     if (n == 0) return EXO_OK;
     PolicyArgs a;
-    a.obs = obs_dev; a.pack = p->pack; a.bias = p->bias; a.scratch = p->scratch; a.actions = actions_dev; a.zs = zs_dev;
+    a.obs = obs_dev; a.pack = p->pack; a.scratch = p->scratch; a.actions = actions_dev; a.zs = zs_dev;
     a.n = n; a.max_action = max_action; a.dbg = p->dbg;
     const long long tiles = (n + TILE_M - 1) / TILE_M;
     if (tiles > 0x7FFFFFFF) return exo_set_error(EXO_ERR_ARG, "exo_policy_forward: too many observations");

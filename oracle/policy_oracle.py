@@ -10,7 +10,7 @@ Pinned against the reference's own torch modules with the shipped [1,1,1,1] chec
 (tests/golden/ref_policy.npz; tests/test_policy.py::test_oracle_matches_reference_modules).
 
 mode "fp32": float32 throughout, as torch's default matmul.
-mode "tf32": the arithmetic of csrc/exo_policy.cu - weights, observations and every stored activation rounded to TF32
+mode "tf32": the arithmetic of csrc/exo_policy.cu - weights, biases, observations and every stored activation rounded to TF32
              (round to nearest, ties away: cvt.rna.tf32.f32), products accumulated in float32 (float64 here, which
              differs from any float32 summation order by < 1e-6), bias/activation in float32.
 """
@@ -43,6 +43,7 @@ class PolicyOracle(object):
         self.b = {k: np.asarray(weights[k + ".bias"], dtype=np.float32) for k in KEYS}
         if mode == "tf32":
             self.w = {k: round_tf32(v) for k, v in self.w.items()}
+            self.b = {k: round_tf32(v) for k, v in self.b.items()}      # the biases ride in the GEMMs as a K column
 
     def _lin(self, name, x):
         if self.mode == "tf32":
