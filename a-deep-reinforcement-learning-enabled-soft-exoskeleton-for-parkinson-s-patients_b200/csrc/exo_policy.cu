@@ -58,7 +58,10 @@ constexpr int L3_KS_PER_STAGE = STAGE_BYTES / (OUTP * 32);   // 19 k-steps of th
 constexpr int L3_STAGES = KS_H / L3_KS_PER_STAGE;            // 2
 constexpr int X_BYTES = TILE_M * HP * 4;    // 155 648
 constexpr int X_SBO = HP * 32;              // 9 728: 8 rows x (304 * 4 B)
-constexpr int NSLOT = 7;
+#ifndef EXO_POLICY_NSLOT
+#define EXO_POLICY_NSLOT 7
+#endif
+constexpr int NSLOT = EXO_POLICY_NSLOT;   // weight stages in flight (tuning builds: -DEXO_POLICY_NSLOT=n)
 constexpr int N_PHASE = 8;
 constexpr int STAGES_PER_TILE = 2 * KS_S + 5 * KS_H + L3_STAGES;     // 214
 constexpr int PACK_BYTES = STAGES_PER_TILE * STAGE_BYTES;            // 2 081 792
@@ -312,8 +315,13 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
 #pragma unroll 1
                 for (int i = 0; i < STAGES_PER_TILE; ++i, src += STAGE_BYTES) {
                     mbar_wait(bar_empty + 8 * slot, par);
+#ifdef EXO_POLICY_TINYLOAD       // timing experiment only (wrong results): is the k-step paced by the bytes a stage brings in?
+                    mbar_expect_tx(bar_full + 8 * slot, 16);
+                    bulk_g2s(sbase + OFF_W + slot * STAGE_BYTES, src, 16, bar_full + 8 * slot);
+#else
                     mbar_expect_tx(bar_full + 8 * slot, STAGE_BYTES);
                     bulk_g2s(sbase + OFF_W + slot * STAGE_BYTES, src, STAGE_BYTES, bar_full + 8 * slot);
+#endif
                     if (++slot == NSLOT) { slot = 0; par ^= 1; }
                 }
             }
