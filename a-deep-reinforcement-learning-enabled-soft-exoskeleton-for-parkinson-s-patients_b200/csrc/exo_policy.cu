@@ -53,26 +53,29 @@ constexpr int TILE_M = 128;
 constexpr int KS_S = SP / 8;                // 11 k-steps over the observation
 constexpr int KS_H = HP / 8;                // 38 k-steps over a hidden vector
 constexpr int N_LO = 160, N_HI = HP - N_LO; // the two MMAs of a k-step (N <= 256 per instruction) = the two epilogue halves
-constexpr int STAGE_BYTES = HP * 32;        // 9 728: one k-step (8 tf32 = 32 B per row) of a 304-row weight matrix
-constexpr int L3_KS_PER_STAGE = STAGE_BYTES / (OUTP * 32);   // 19 k-steps of the 16-row l3 per stage
-constexpr int L3_STAGES = KS_H / L3_KS_PER_STAGE;            // 2
-constexpr int X_BYTES = TILE_M * HP * 4;    // 155 648
-constexpr int X_SBO = HP * 32;              // 9 728: 8 rows x (304 * 4 B)
+// Operands are K-major SWIZZLE_128B: a swizzle atom is 8 rows x 128 B (32 tf32 of K = 4 k-steps), atoms of one K range
+// stacked along the rows (SBO 1024), K ranges ("k-atoms") one after the other.
+constexpr int ATOMS_S = (SP + 31) / 32;     // 3 k-atoms over the observation (the last one 3 k-steps)
+constexpr int ATOMS_H = (HP + 31) / 32;     // 10 k-atoms over a hidden vector (the last one 2 k-steps)
+constexpr int A_ATOM_BYTES = TILE_M * 128;  // 16 384: one k-atom of the 128-row activation tile
+constexpr int X_BYTES = ATOMS_H * A_ATOM_BYTES;              // 163 840
+constexpr int B_LO_BYTES = N_LO * 128, B_HI_BYTES = N_HI * 128;   // 20 480 / 18 432: one k-atom of weight rows 0..159 / 160..303
+constexpr int SLOT_BYTES = B_LO_BYTES;      // a weight stage = one (k-atom, row half); all of l3 (10 k-atoms x 16 rows) is one stage too
+static_assert(ATOMS_H * OUTP * 128 == SLOT_BYTES, "l3 fills exactly one stage");
 #ifndef EXO_POLICY_NSLOT
-#define EXO_POLICY_NSLOT 7
+#define EXO_POLICY_NSLOT 3
 #endif
 constexpr int NSLOT = EXO_POLICY_NSLOT;   // weight stages in flight (tuning builds: -DEXO_POLICY_NSLOT=n)
 constexpr int N_PHASE = 8;
-constexpr int STAGES_PER_TILE = 2 * KS_S + 5 * KS_H + L3_STAGES;     // 214
-constexpr int PACK_BYTES = STAGES_PER_TILE * STAGE_BYTES;            // 2 081 792
+constexpr int PACK_BYTES = (2 * ATOMS_S + 5 * ATOMS_H) * (B_LO_BYTES + B_HI_BYTES) + SLOT_BYTES;     // 2 199 552
 
 constexpr int OFF_X = 0;
 constexpr int OFF_W = OFF_X + X_BYTES;
-constexpr int OFF_BAR = OFF_W + NSLOT * STAGE_BYTES;
-constexpr int OFF_PART = OFF_BAR + 8 * (2 * NSLOT + 4) + 16;       // AvgL1Norm partial sums [2][128] floats
+constexpr int OFF_BAR = OFF_W + NSLOT * SLOT_BYTES;
+constexpr int N_BAR = 2 * NSLOT + 3 + ATOMS_H;                     // full[], empty[], acc_full, a_ready, xr_full, xa_free[]
+constexpr int OFF_PART = OFF_BAR + 8 * N_BAR + 16;                 // AvgL1Norm partial sums [2][128] floats
 constexpr int SMEM_BYTES = OFF_PART + 2 * TILE_M * 4;
 static_assert(SMEM_BYTES <= 232448, "over the 227 KB per-CTA shared memory limit");
-static_assert(L3_STAGES * L3_KS_PER_STAGE == KS_H, "l3 stage split");
 static_assert(N_LO % 32 == 0 && N_HI % 16 == 0 && N_HI > 128, "epilogue column split");
 
 constexpr int N_EPI = 256;
@@ -158,16 +161,18 @@ __device__ __forceinline__ bool elect_one() {
 }
 
 // Shared-memory matrix descriptor (sm_100 UMMA): start>>4 [0,14), LBO>>4 [16,30) (unused by a K-major swizzled operand
-// whose K extent is one swizzle atom; set to 1), SBO>>4 [32,46) = distance of 8-row groups, version 1 [46,48),
-// layout type [61,64) = 6: SWIZZLE_32B.
-__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t sbo) {
-    return (uint64_t)((addr >> 4) & 0x3FFFu) | (1ull << 16) | ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46) | (6ull << 61);
+// whose MMA K extent lies inside one swizzle atom; set to 1), SBO>>4 [32,46) = distance of 8-row groups = 1024,
+// version 1 [46,48), layout type [61,64) = 2: SWIZZLE_128B. A k-step inside the atom is selected by adding its 32 B to
+// the start address. (Measured, tools/ubench/mma_fetch.cu: 159 cycles per N=160+144 k-step with this layout, 201 with
+// SWIZZLE_32B; the first version's no-swizzle layout was slower still.)
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr) {
+    return (uint64_t)((addr >> 4) & 0x3FFFu) | (1ull << 16) | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
-// Byte offset of 16-byte chunk `c` (4 tf32 of K) of row `r` inside an operand whose 8-row groups are `sbo` bytes apart:
-// K-major SWIZZLE_32B canonical layout - one 8-row x 32 B atom (256 B) per k-step, rows 32 B apart, and address bit 4
-// XORed with bit 7, i.e. the two chunks of rows 4..7 of a group trade places.
-__host__ __device__ __forceinline__ uint32_t op_off(uint32_t r, uint32_t c, uint32_t sbo) {
-    return (r >> 3) * sbo + (c >> 1) * 256u + (r & 7u) * 32u + (((c & 1u) ^ ((r >> 2) & 1u)) << 4);
+// Byte offset of 16-byte chunk `c` (4 tf32 of K; c = k / 4) of row `r` in an operand whose k-atoms are `atom_bytes` apart:
+// rows 128 B apart inside an 8-row atom, atoms of later rows 1024 B further, and address bits [4,7) XORed with bits
+// [7,10), i.e. chunk (c & 7) of row r sits at position (c & 7) ^ (r & 7).
+__host__ __device__ __forceinline__ uint32_t op_off(uint32_t r, uint32_t c, uint32_t atom_bytes) {
+    return (c >> 3) * atom_bytes + (r >> 3) * 1024u + (r & 7u) * 128u + (((c & 7u) ^ (r & 7u)) << 4);
 }
 // Instruction descriptor: D fp32 (1<<4), A and B tf32 (2<<7, 2<<10), both K-major, N>>3 at bit 17, M>>4 at bit 24.
 __host__ __device__ constexpr uint32_t idesc_tf32(int n) {
@@ -176,7 +181,7 @@ __host__ __device__ constexpr uint32_t idesc_tf32(int n) {
 
 struct PolicyArgs {
     const float* obs;            // [n, 80]
-    const unsigned char* pack;   // STAGES_PER_TILE stages of STAGE_BYTES, in consumption order
+    const unsigned char* pack;   // the weight stages of one tile, in consumption order (PACK_BYTES)
     unsigned char* scratch;      // gridDim.x * X_BYTES (a0 in operand layout)
     float* actions;              // [n, 7]
     float* zs;                   // [n, 300] or null
@@ -186,13 +191,14 @@ struct PolicyArgs {
     long long* dbg;              // exo_policy_profile: clock64 stamps of CTA 0's first tile, or null
 };
 
-// stages per phase: G1, G2, G3, G4, G5a, G5b, G6, G7
-__device__ __constant__ int PH_STAGES[N_PHASE] = {KS_S, KS_S, KS_H, KS_H, KS_H, KS_H, KS_H, L3_STAGES};
+// k-atoms per phase (G1, G2, G3, G4, G5a, G5b, G6, G7) and k-steps in the last one
+__device__ __forceinline__ int ph_atoms(int ph) { return ph < 2 ? ATOMS_S : ATOMS_H; }
+__device__ __forceinline__ int ph_last_ks(int ph) { return ph < 2 ? KS_S - 4 * (ATOMS_S - 1) : KS_H - 4 * (ATOMS_H - 1); }
 
 // ---- epilogues: a thread owns row r of the tile and the column half `half` (0: 0..159, 1: 160..303) ---------------
 // Stores 4 consecutive columns (chunk index c of the row) of an operand-layout row.
 __device__ __forceinline__ void st_chunk(unsigned char* row, uint32_t rsw, int c, float a, float b, float cc, float d) {
-    *reinterpret_cast<float4*>(row + (c >> 1) * 256 + ((((uint32_t)c & 1u) ^ rsw) << 4)) = make_float4(a, b, cc, d);
+    *reinterpret_cast<float4*>(row + (c >> 3) * A_ATOM_BYTES + ((((uint32_t)c & 7u) ^ rsw) << 4)) = make_float4(a, b, cc, d);
 }
 
 // ACT 0: ELU, 1: ReLU, 2: multiply by `scale` (second pass of AvgL1Norm). Processes NCOL (32 or 16) accumulator columns
@@ -284,17 +290,17 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
     extern __shared__ __align__(1024) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t sbase = smem_u32(smem);
-    // barriers: full[NSLOT], empty[NSLOT], acc_full, a_ready, x_free, xr_full; then the TMEM base address
+    // barriers: full[NSLOT], empty[NSLOT], acc_full, a_ready, xr_full, xa_free[ATOMS_H]; then the TMEM base address
     const uint32_t bar_full = sbase + OFF_BAR, bar_empty = bar_full + 8 * NSLOT;
-    const uint32_t bar_acc = bar_empty + 8 * NSLOT, bar_aready = bar_acc + 8, bar_xfree = bar_aready + 8, bar_xr = bar_xfree + 8;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + OFF_BAR + 8 * (2 * NSLOT + 4));
+    const uint32_t bar_acc = bar_empty + 8 * NSLOT, bar_aready = bar_acc + 8, bar_xr = bar_aready + 8, bar_xafree = bar_xr + 8;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + OFF_BAR + 8 * N_BAR);
 
     if (tid == 0) {
         for (int s = 0; s < NSLOT; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
         mbar_init(bar_acc, 1);
         mbar_init(bar_aready, N_EPI);
-        mbar_init(bar_xfree, 1);
         mbar_init(bar_xr, 1);
+        for (int g = 0; g < ATOMS_H; ++g) mbar_init(bar_xafree + 8 * g, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -310,28 +316,35 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
         // ===== weight producer ==========================================================================
         if (lane == 0) {
             uint32_t slot = 0, par = 1;
+            auto stage = [&](const unsigned char* src, uint32_t bytes) {
+                mbar_wait(bar_empty + 8 * slot, par);
+#ifdef EXO_POLICY_TINYLOAD       // timing experiment only (wrong results): is the k-step paced by the bytes a stage brings in?
+                bytes = 16;
+#endif
+                mbar_expect_tx(bar_full + 8 * slot, bytes);
+                bulk_g2s(sbase + OFF_W + slot * SLOT_BYTES, src, bytes, bar_full + 8 * slot);
+                if (++slot == NSLOT) { slot = 0; par ^= 1; }
+            };
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
                 const unsigned char* src = a.pack;
 #pragma unroll 1
-                for (int i = 0; i < STAGES_PER_TILE; ++i, src += STAGE_BYTES) {
-                    mbar_wait(bar_empty + 8 * slot, par);
-#ifdef EXO_POLICY_TINYLOAD       // timing experiment only (wrong results): is the k-step paced by the bytes a stage brings in?
-                    mbar_expect_tx(bar_full + 8 * slot, 16);
-                    bulk_g2s(sbase + OFF_W + slot * STAGE_BYTES, src, 16, bar_full + 8 * slot);
-#else
-                    mbar_expect_tx(bar_full + 8 * slot, STAGE_BYTES);
-                    bulk_g2s(sbase + OFF_W + slot * STAGE_BYTES, src, STAGE_BYTES, bar_full + 8 * slot);
-#endif
-                    if (++slot == NSLOT) { slot = 0; par ^= 1; }
+                for (int ph = 0; ph < 7; ++ph) {
+                    const int na = ph_atoms(ph);
+#pragma unroll 1
+                    for (int at = 0; at < na; ++at) {
+                        stage(src, B_LO_BYTES); src += B_LO_BYTES;
+                        stage(src, B_HI_BYTES); src += B_HI_BYTES;
+                    }
                 }
+                stage(src, SLOT_BYTES);
             }
         }
     } else if (warp == 1) {
         // ===== MMA issuer: the whole warp walks the pipeline, one elected lane issues =====================
         uint32_t slot = 0, par = 0, par_ar = 0, par_xr = 0;
         constexpr uint32_t IDLO = idesc_tf32(N_LO), IDHI = idesc_tf32(N_HI), ID16 = idesc_tf32(OUTP);
-        const uint64_t a_desc0 = smem_desc(sbase + OFF_X, X_SBO);
-        const uint64_t b_desc0 = smem_desc(sbase + OFF_W, 256);
+        const uint64_t a_desc0 = smem_desc(sbase + OFF_X);
+        const uint64_t b_desc0 = smem_desc(sbase + OFF_W);
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
 #pragma unroll 1
             for (int ph = 0; ph < N_PHASE; ++ph) {
@@ -340,31 +353,51 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
                 tc_fence_after();
                 const bool stamp = a.dbg && tile == 0 && lane == 0;
                 if (stamp) a.dbg[2 * ph] = clock64();
-                const int nst = PH_STAGES[ph];
-                uint64_t ad = a_desc0;
+                const int na = ph_atoms(ph), last_ks = ph_last_ks(ph);
+                if (ph < 7) {
 #pragma unroll 1
-                for (int st = 0; st < nst; ++st) {
+                    for (int st = 0; st < 2 * na; ++st) {          // stage = (k-atom st/2, weight-row half st&1)
+                        mbar_wait(bar_full + 8 * slot, par);
+                        tc_fence_after();
+                        const int at = st >> 1, hi = st & 1;
+                        const uint64_t ad = a_desc0 + (uint64_t)(at * (A_ATOM_BYTES >> 4));
+                        const uint64_t bd = b_desc0 + (uint64_t)(slot * (SLOT_BYTES >> 4));
+                        const int nk = at == na - 1 ? last_ks : 4;
+                        if (elect_one()) {
+                            const uint32_t d = tmem + (hi ? N_LO : 0);
+                            const uint32_t id = hi ? IDHI : IDLO;
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                if (j < nk) tc_mma_tf32(d, ad + (uint64_t)(2 * j), bd + (uint64_t)(2 * j), id, (at > 0 || j > 0 || ph == 5) ? 1u : 0u);
+                            tc_commit(bar_empty + 8 * slot);      // frees the stage once these MMAs have read it
+                            if (ph == 4 && hi) tc_commit(bar_xafree + 8 * at);    // G5a is done with this k-atom of X: a0 may come back
+                        }
+                        __syncwarp();
+                        if (++slot == NSLOT) { slot = 0; par ^= 1; }
+                    }
+                } else {                                            // l3: all ten k-atoms of its 16 rows in one stage
                     mbar_wait(bar_full + 8 * slot, par);
                     tc_fence_after();
-                    const uint64_t bd = b_desc0 + (uint64_t)(slot * (STAGE_BYTES >> 4));
+                    const uint64_t bd = b_desc0 + (uint64_t)(slot * (SLOT_BYTES >> 4));
                     if (elect_one()) {
-                        if (ph < 7) {
-                            const uint32_t acc = (st > 0 || ph == 5) ? 1u : 0u;
-                            tc_mma_tf32(tmem, ad, bd, IDLO, acc);
-                            tc_mma_tf32(tmem + N_LO, ad, bd + (uint64_t)((N_LO / 8) * 256 >> 4), IDHI, acc);
-                        } else {
+#pragma unroll 1
+                        for (int at = 0; at < ATOMS_H; ++at) {
+                            const int nk = at == ATOMS_H - 1 ? last_ks : 4;
 #pragma unroll
-                            for (int j = 0; j < L3_KS_PER_STAGE; ++j)
-                                tc_mma_tf32(tmem, ad + (uint64_t)(j * 16), bd + (uint64_t)(j * (OUTP * 32 >> 4)), ID16, (st > 0 || j > 0) ? 1u : 0u);
+                            for (int j = 0; j < 4; ++j)
+                                if (j < nk)
+                                    tc_mma_tf32(tmem, a_desc0 + (uint64_t)(at * (A_ATOM_BYTES >> 4) + 2 * j),
+                                                bd + (uint64_t)(at * (OUTP * 128 >> 4) + 2 * j), ID16, (at > 0 || j > 0) ? 1u : 0u);
                         }
-                        tc_commit(bar_empty + 8 * slot);      // frees the stage once these MMAs have read it
+                        tc_commit(bar_empty + 8 * slot);
                     }
                     __syncwarp();
-                    ad += (ph < 7) ? 16u : (uint64_t)(L3_KS_PER_STAGE * 16);    // 256 B (one k-step) >> 4
                     if (++slot == NSLOT) { slot = 0; par ^= 1; }
                 }
-                if (elect_one()) tc_commit(ph == 4 ? bar_xfree : bar_acc);  // G5a: X may be reloaded; else: accumulator ready
-                __syncwarp();
+                if (ph != 4) {                                  // (G5a's accumulator is completed by G5b)
+                    if (elect_one()) tc_commit(bar_acc);
+                    __syncwarp();
+                }
                 if (stamp) a.dbg[2 * ph + 1] = clock64();
             }
         }
@@ -375,10 +408,10 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
         const int q = warp & 3;                        // TMEM lane quarter this warp may read
         const int r = q * 32 + lane;                   // accumulator row = observation within the tile
         const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
-        const uint32_t rsw = ((uint32_t)r >> 2) & 1u;  // chunk swizzle of this row
-        unsigned char* xrow = smem + OFF_X + (r >> 3) * X_SBO + (r & 7) * 32;
+        const uint32_t rsw = (uint32_t)r & 7u;         // chunk swizzle of this row
+        unsigned char* xrow = smem + OFF_X + (r >> 3) * 1024 + (r & 7) * 128;
         unsigned char* scratch = a.scratch + (size_t)blockIdx.x * X_BYTES;
-        unsigned char* srow = scratch + (r >> 3) * X_SBO + (r & 7) * 32;
+        unsigned char* srow = scratch + (r >> 3) * 1024 + (r & 7) * 128;
         float* part = reinterpret_cast<float*>(smem + OFF_PART);
         uint32_t par_acc = 0, par_xf = 0;
         float4 ob[OBS_V4_PER_THREAD];                  // this thread's share of the next tile's observations
@@ -395,17 +428,17 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
             const long long row0 = (long long)tile * TILE_M;
             STAMP(16);
-            // E0: observations -> the first 22 chunks of X (80 values, the constant 1, 7 zeros), rounded to TF32; both
+            // E0: observations -> the first 22 chunks of X's rows (80 values, the constant 1, 7 zeros), rounded to TF32; both
             // layers that read them (l0, zs1) are done before E2 overwrites X. Then prefetch the next tile's.
 #pragma unroll
             for (int i = 0; i < OBS_V4_PER_THREAD; ++i) {
                 const int idx = i * N_EPI + et, rr = idx / (SD / 4), c = idx % (SD / 4);
-                *reinterpret_cast<float4*>(smem + OFF_X + op_off(rr, c, X_SBO)) =
+                *reinterpret_cast<float4*>(smem + OFF_X + op_off(rr, c, A_ATOM_BYTES)) =
                     make_float4(to_tf32(ob[i].x), to_tf32(ob[i].y), to_tf32(ob[i].z), to_tf32(ob[i].w));
             }
             {
                 const int rr = et & 127, c = SD / 4 + half;           // chunk 20: (1,0,0,0); chunk 21: zeros
-                *reinterpret_cast<float4*>(smem + OFF_X + op_off(rr, c, X_SBO)) = make_float4(half ? 0.f : 1.f, 0.f, 0.f, 0.f);
+                *reinterpret_cast<float4*>(smem + OFF_X + op_off(rr, c, A_ATOM_BYTES)) = make_float4(half ? 0.f : 1.f, 0.f, 0.f, 0.f);
             }
             fence_proxy_async_smem();
             tc_fence_before();
@@ -419,12 +452,12 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
                 const float sc = avgl1_scale(taddr, half, r, part);
                 epi_half<2>(taddr, half, srow, rsw, sc, nullptr);
             }
-            __threadfence();
-            fence_proxy_async_all();
             tc_fence_before();
             STAMP(19);
-            mbar_arrive(bar_aready);
-            asm volatile("bar.sync 1, 256;" ::: "memory");   // all of a0 is out before anyone reloads it
+            mbar_arrive(bar_aready);                         // the accumulator is drained: zs1 may start while the stores land
+            __threadfence();
+            fence_proxy_async_all();
+            asm volatile("bar.sync 1, 256;" ::: "memory");   // all of a0 is out (and visible to the bulk copies) before the reload
             // E2, E3: ELU
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
             STAMP(20);
@@ -448,12 +481,13 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
             fence_proxy_async_smem(); tc_fence_before();
             STAMP(25);
             mbar_arrive(bar_aready);
-            // after G5a has read zs out of X, bring a0 back (16 bulk copies of one 8-row group each)
+            // as G5a finishes reading each k-atom of zs out of X, bring that k-atom of a0 back (one bulk copy each)
             if (et == 0) {
-                mbar_wait(bar_xfree, par_xf);
                 mbar_expect_tx(bar_xr, X_BYTES);
-                for (int g = 0; g < TILE_M / 8; ++g)
-                    bulk_g2s(sbase + OFF_X + g * X_SBO, scratch + (size_t)g * X_SBO, X_SBO, bar_xr);
+                for (int g = 0; g < ATOMS_H; ++g) {
+                    mbar_wait(bar_xafree + 8 * g, par_xf);
+                    bulk_g2s(sbase + OFF_X + g * A_ATOM_BYTES, scratch + (size_t)g * A_ATOM_BYTES, A_ATOM_BYTES, bar_xr);
+                }
             }
             par_xf ^= 1;
             // E5, E6: ReLU
@@ -504,18 +538,22 @@ inline float round_tf32(float x) {            // cvt.rna.tf32.f32: round to near
     return x;
 }
 
-// W[n_rows, ld] (columns col0 .. col0+k_real-1 used) -> `ksteps` k-steps of an `n_pad`-row K-major SWIZZLE_32B operand:
-// byte offset of element (n, k) = (k/8)*n_pad*32 + op_off(n, (k%8)/4, 256) + (k%4)*4. If `bias` is given it becomes
-// column k_real (the A operand holds the constant 1 there), rounded to TF32 like the weights.
-void pack_matrix(unsigned char* dst, const float* W, const float* bias, int n_rows, int ld, int col0, int k_real, int n_pad, int ksteps) {
-    memset(dst, 0, (size_t)ksteps * n_pad * 32);
+// Packs W[n_rows, ld] (columns col0 .. col0+k_real-1; `bias`, if given, becomes column k_real - the A operand holds the
+// constant 1 there) as the kernel consumes it: for each k-atom (32 columns) the rows 0..n_lo-1 as one K-major
+// SWIZZLE_128B block, then the rows n_lo..n_lo+n_hi-1 (n_hi may be 0). Values rounded to TF32. Returns the bytes written.
+size_t pack_matrix(unsigned char* dst, const float* W, const float* bias, int n_rows, int ld, int col0, int k_real, int n_lo, int n_hi,
+                   int atoms) {
+    const size_t atom_bytes = (size_t)(n_lo + n_hi) * 128;
+    memset(dst, 0, atoms * atom_bytes);
     for (int n = 0; n < n_rows; ++n)
         for (int k = 0; k <= k_real; ++k) {
             if (k == k_real && !bias) break;
-            const size_t off = (size_t)(k / 8) * n_pad * 32 + op_off((uint32_t)n, (uint32_t)((k % 8) / 4), 256u) + (k % 4) * 4;
+            const int hi = n >= n_lo, nl = hi ? n - n_lo : n;
+            const size_t off = (size_t)(k / 32) * atom_bytes + (hi ? (size_t)n_lo * 128 : 0) + op_off((uint32_t)nl, (uint32_t)((k % 32) / 4), 0u) + (k % 4) * 4;
             const float v = round_tf32(k < k_real ? W[(size_t)n * ld + col0 + k] : bias[n]);
             memcpy(dst + off, &v, 4);
         }
+    return atoms * atom_bytes;
 }
 
 }  // namespace
@@ -573,14 +611,14 @@ extern "C" int exo_policy_set_weights(ExoPolicy* p, const ExoPolicyWeights* w, i
     unsigned char* d = pack.data();
     // consumption order of the kernel: G1 l0, G2 zs1, G3 zs2, G4 zs3, G5a l1[:,300:600], G5b l1[:,0:300], G6 l2, G7 l3
     // (the l1 bias rides with the a0 half: G5b's operand is the reloaded a0, whose column 300 is the constant 1)
-    pack_matrix(d, w->l0_w, w->l0_b, HD, SD, 0, SD, HP, KS_S);        d += (size_t)KS_S * STAGE_BYTES;
-    pack_matrix(d, w->zs1_w, w->zs1_b, HD, SD, 0, SD, HP, KS_S);      d += (size_t)KS_S * STAGE_BYTES;
-    pack_matrix(d, w->zs2_w, w->zs2_b, HD, HD, 0, HD, HP, KS_H);      d += (size_t)KS_H * STAGE_BYTES;
-    pack_matrix(d, w->zs3_w, w->zs3_b, HD, HD, 0, HD, HP, KS_H);      d += (size_t)KS_H * STAGE_BYTES;
-    pack_matrix(d, w->l1_w, nullptr, HD, 2 * HD, HD, HD, HP, KS_H);   d += (size_t)KS_H * STAGE_BYTES;
-    pack_matrix(d, w->l1_w, w->l1_b, HD, 2 * HD, 0, HD, HP, KS_H);    d += (size_t)KS_H * STAGE_BYTES;
-    pack_matrix(d, w->l2_w, w->l2_b, HD, HD, 0, HD, HP, KS_H);        d += (size_t)KS_H * STAGE_BYTES;
-    pack_matrix(d, w->l3_w, w->l3_b, AD, HD, 0, HD, OUTP, KS_H);      d += (size_t)L3_STAGES * STAGE_BYTES;
+    d += pack_matrix(d, w->l0_w, w->l0_b, HD, SD, 0, SD, N_LO, N_HI, ATOMS_S);
+    d += pack_matrix(d, w->zs1_w, w->zs1_b, HD, SD, 0, SD, N_LO, N_HI, ATOMS_S);
+    d += pack_matrix(d, w->zs2_w, w->zs2_b, HD, HD, 0, HD, N_LO, N_HI, ATOMS_H);
+    d += pack_matrix(d, w->zs3_w, w->zs3_b, HD, HD, 0, HD, N_LO, N_HI, ATOMS_H);
+    d += pack_matrix(d, w->l1_w, nullptr, HD, 2 * HD, HD, HD, N_LO, N_HI, ATOMS_H);
+    d += pack_matrix(d, w->l1_w, w->l1_b, HD, 2 * HD, 0, HD, N_LO, N_HI, ATOMS_H);
+    d += pack_matrix(d, w->l2_w, w->l2_b, HD, HD, 0, HD, N_LO, N_HI, ATOMS_H);
+    d += pack_matrix(d, w->l3_w, w->l3_b, AD, HD, 0, HD, OUTP, 0, ATOMS_H);
     if (d != pack.data() + PACK_BYTES) return exo_set_error(EXO_ERR_STATE, "exo_policy_set_weights: pack size mismatch");
     PCK(cudaSetDevice(p->device));
     PCK(cudaMemcpy(p->pack, pack.data(), PACK_BYTES, cudaMemcpyHostToDevice));
