@@ -160,6 +160,59 @@ def bench_lap(exo_b200, env, actions, dev, flush):
     return out
 
 
+POLICY_FLOP_PER_OBS = 2 * (80 * 300 * 2 + 300 * 300 * 3 + 600 * 300 + 300 * 7)
+
+
+def bench_policy(exo_b200, env, dev, flush, peaks):
+    """Next row N2: select_action's networks (encoder.zs + actor, TD7_multi_agent_Pink_noise.py:66-105)
+    as one tcgen05 kernel reading the env's obs tensor. Weights: the shipped [1,1,1,1] checkpoint (tests/golden/ref_policy.npz).
+    Reports the forward pass alone (CUDA events, L2 flushed) against the tensor-core roofline - kind::tf32 issues at half
+    the bf16 MMA rate, so peak = MEASURED_PEAKS bf16_tflops / 2 - and the closed loop obs -> policy -> env.step."""
+    import torch
+    n = env.n
+    g = np.load(os.path.join(REPO, "tests", "golden", "ref_policy.npz"))
+    sd = {k: g[k] for k in g.files if "." in k}
+    pol = exo_b200.DevicePolicy(dev)
+    pol.set_networks(sd, sd, "checkpoint")
+    obs = env.reset().clone()
+    act = torch.empty(n, 7, device=dev)
+    for _ in range(3):
+        pol.forward(obs, use_checkpoint=True, out=act)
+    evs = []
+    for _ in range(30):
+        if flush is not None:
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        pol.forward(obs, use_checkpoint=True, out=act)
+        b.record()
+        evs.append((a, b))
+    torch.cuda.synchronize(dev)
+    fwd_ms = float(np.mean([a.elapsed_time(b) for a, b in evs[3:]]))
+    # closed loop: the policy's actions drive the env (auto-reset on), no host copy anywhere
+    steps = 60
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    a.record()
+    for _ in range(steps):
+        pol.forward(obs, use_checkpoint=True, out=act)
+        obs, rew, done = env.step(act)
+    b.record()
+    torch.cuda.synchronize(dev)
+    loop_ms = a.elapsed_time(b) / steps
+    tf = n * POLICY_FLOP_PER_OBS / (fwd_ms * 1e-3) / 1e12
+    bf16 = float(peaks.get("bf16_tflops", 2250.0))
+    out = {"kernel": "exo_policy_kernel", "observations": n, "forward_ms": fwd_ms, "observations_per_s": n / (fwd_ms * 1e-3),
+           "flop_per_observation": POLICY_FLOP_PER_OBS, "dtype": "tf32 products, f32 accumulate",
+           "roofline": {"bound": "tensor", "achieved": tf, "peak": bf16 / 2, "unit": "TFLOP/s", "frac": tf / (bf16 / 2),
+                        "peak_source": ("MEASURED_PEAKS.json bf16_tflops / 2 (kind::tf32 = half the bf16 MMA rate)" if peaks else
+                                        "fallback 2250 / 2")},
+           "closed_loop_env_steps_per_s": n / (loop_ms * 1e-3), "closed_loop_ms_per_step": loop_ms,
+           "launches": pol.launch_count(), "weights": "shipped [1,1,1,1] checkpoint actor + encoder"}
+    pol.close()
+    return out
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU algorithm (oracle port; the Python reference cannot travel to the GPU box
     and needs pybullet) on all host threads, rank 0 only."""
@@ -197,6 +250,7 @@ def main():
     ap.add_argument("--ref-sample", type=int, default=4096)
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--no-lap", action="store_true", help="skip the replay-buffer (next row N1) measurement")
+    ap.add_argument("--no-policy", action="store_true", help="skip the policy forward pass (next row N2) measurement")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -303,13 +357,16 @@ def main():
     lap_line = None
     if rank == 0 and not args.no_lap:
         lap_line = bench_lap(exo_b200, env, actions, dev, flush)
+    peaks = {}
+    try:
+        with open(os.path.join(REPO, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except OSError:
+        pass
+    policy_line = None
+    if rank == 0 and not args.no_policy:
+        policy_line = bench_policy(exo_b200, env, dev, flush, peaks)
     if rank == 0:
-        peaks = {}
-        try:
-            with open(os.path.join(REPO, "MEASURED_PEAKS.json")) as f:
-                peaks = json.load(f)
-        except OSError:
-            pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         achieved = ALGO_BYTES_PER_ENV_STEP * n / (kms * 1e-3) / 1e9
         cpu_v, cpu_cores, cpu_secs = cpu_baseline(args.cpu_sample, args.cpu_steps)
@@ -340,6 +397,8 @@ def main():
         }
         if lap_line is not None:
             line["lap"] = lap_line
+        if policy_line is not None:
+            line["policy"] = policy_line
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
