@@ -12,15 +12,15 @@
 //                     columns at a time, activation, round to TF32, store as the next layer's A operand in shared memory
 // The biases ride in the GEMMs: every A operand carries a constant-1 column (index 300 of a hidden vector, 80 of an
 // observation) and the packed weights hold the bias there, so the epilogues load nothing but the accumulator.
-// Shared memory (223 904 B): X = 128 x 304 activations (152 KB; the observations sit in its first 80 columns until the
-// first hidden layer overwrites them), 7 weight stages of 9 728 B, mbarriers. Operands use the K-major no-swizzle canonical layout (8 rows x 16 B core matrices;
-// LBO = distance of the two 16 B K-chunks of one MMA, SBO = distance of 8-row groups), which the host packs the
-// weights into once, so a stage is ONE contiguous bulk copy and needs no tensor map.
+// Shared memory (226 KB): X = 128 x 320 activations (160 KB = ten 32-column k-atoms; the observations sit in its first
+// three until the first hidden layer overwrites them), 3 weight stages of 20 KB (one k-atom of 160 or 144 weight rows =
+// 4 MMAs), mbarriers. Operands use the K-major SWIZZLE_128B canonical layout (8 rows x 128 B atoms, SBO 1024), which the
+// host packs the weights into once, so a stage is ONE contiguous bulk copy and needs no tensor map.
 // Tensor memory: accumulator P = columns 0..303 of the CTA's 512.
 //
 // Per tile (G = MMAs, E = epilogue; hidden width 300 padded to 304 with zero weights/bias, so pads stay exactly 0):
 //   E0 obs -> X | G1 X*l0' -> E1 a0 = AvgL1Norm -> L2 scratch | G2 X*zs1' -> E2 ELU -> X | G3 X*zs2' -> E3 ELU -> X |
-//   G4 X*zs3' -> E4 zs = AvgL1Norm -> X | G5a P = X*l1[:,300:600]' | bulk-reload X <- a0 | G5b P += X*l1[:,0:300]' ->
+//   G4 X*zs3' -> E4 zs = AvgL1Norm -> X | G5a P = X*l1[:,300:600]' | bulk-reload X <- a0, k-atom by k-atom behind G5a | G5b P += X*l1[:,0:300]' ->
 //   E5 ReLU -> X | G6 X*l2' -> E6 ReLU -> X | G7 X*l3' (N=16) -> E7 tanh, clip, * max_action -> actions
 // (a0 takes the detour through an L2-resident per-CTA scratch because X + a second 152 KB operand do not fit in
 // shared memory and two 304-column accumulators do not fit in TMEM.)

@@ -254,6 +254,8 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
     bool fin = false;
     int v_cross = 0, v_red = 0, v_len = 0;
     R v_ret = 0, v_amp = 0;
+    int v_cge = 0, v_clt = 0, v_ntr = 0, v_nam = 0;      // training-script suppression metrics (INFO mode only)
+    R v_str = 0, v_sam = 0;
     if (valid && !live) { done[e] = 1; reward[e] = R(0); }
     const unsigned full = 0xffffffffu;
     const unsigned live_mask = __ballot_sync(full, live);
@@ -490,6 +492,18 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
                 rp[0] = r_unw; rp[1] = r_tor; rp[2] = r_axis; rp[3] = r_ctl; rp[4] = r_smo;
             }
             if (info.amp_metric) info.amp_metric[e] = amp;
+            // Exoskeleton_agent_train.py:150-155,172-173,186-188: per-axis suppression percentages with nan/inf -> 0
+            // (a zero tremor value), occurrence counters over the four arm axes, and - with the script's `disregard`
+            // masking, positive values dropped - the sums/counts behind its mean-of-non-zero suppression figures
+#pragma unroll
+            for (int j = 0; j < 7; j++) {
+                const R tb = abs_r(ttc[j]), ab = abs_r(qt[j]);
+                const R tr = tb > R(0) ? (abs_r(tv[j]) - tb) / tb * R(100) : R(0);
+                const R ta = ab > R(0) ? (abs_r(qa[j]) - ab) / ab * R(100) : R(0);
+                if (j < 4) { if (tr >= R(0)) v_cge++; else v_clt++; }
+                if (tr < R(0)) { v_str += tr; v_ntr++; }
+                if (ta < R(0)) { v_sam += ta; v_nam++; }
+            }
         }
         v_cross = crossed; v_red = arm_red;
         if (dn) { v_len = k1 - 2; v_ret = ret; }
@@ -557,6 +571,18 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
             if (t_cross) atomicAdd(S.stats + 4, (double)t_cross);
             if (t_red) atomicAdd(S.stats + 5, (double)t_red);
             if (INFO && t_ampn) { atomicAdd(S.stats + 6, t_amp); atomicAdd(S.stats + 7, (double)t_ampn); }
+        }
+        if (INFO) {
+            const int t_cge = __reduce_add_sync(full, v_cge), t_clt = __reduce_add_sync(full, v_clt);
+            const int t_ntr = __reduce_add_sync(full, v_ntr), t_nam = __reduce_add_sync(full, v_nam);
+            double xs = (double)v_str, xa = (double)v_sam;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { xs += __shfl_xor_sync(full, xs, o); xa += __shfl_xor_sync(full, xa, o); }
+            if (lane == 0) {
+                atomicAdd(S.stats + 8, (double)t_cge); atomicAdd(S.stats + 9, (double)t_clt);
+                if (t_ntr) { atomicAdd(S.stats + 10, xs); atomicAdd(S.stats + 11, (double)t_ntr); }
+                if (t_nam) { atomicAdd(S.stats + 12, xa); atomicAdd(S.stats + 13, (double)t_nam); }
+            }
         }
     }
 }

@@ -17,7 +17,8 @@ from . import _capi, motions as _motions, urdf as _urdf
 INFO_KEYS = ("actuator_torques", "torque_val", "ampl_val", "tremor_torque_val", "tremor_ampl_val")
 REWARD_KEYS = ("reward_unwanted", "reward_torque", "reward_axis", "reward_control", "reward_smoothness")
 STAT_NAMES = ("episodes", "return_sum", "length_sum", "env_steps", "limit_crossings", "steps_with_arm_reduction",
-              "amp_metric_neg_sum", "amp_metric_neg_count")
+              "amp_metric_neg_sum", "amp_metric_neg_count", "arm_axis_no_reduction_count", "arm_axis_reduction_count",
+              "torque_reduction_neg_sum", "torque_reduction_neg_count", "ampl_reduction_neg_sum", "ampl_reduction_neg_count")
 
 
 def _ptr(t):

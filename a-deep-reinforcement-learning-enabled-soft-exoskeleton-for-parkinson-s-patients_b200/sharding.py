@@ -40,4 +40,9 @@ def summarize(stats):
     ep = max(s[0], 1.0)
     return dict(episodes=s[0], mean_return=s[1] / ep, mean_length=s[2] / ep, env_steps=s[3], limit_crossings=s[4],
                 frac_steps_with_arm_reduction=s[5] / max(s[3], 1.0),
-                mean_negative_amp_metric=s[6] / max(s[7], 1.0))
+                mean_negative_amp_metric=s[6] / max(s[7], 1.0),
+                # the training script's console figures (Exoskeleton_agent_train.py:232-262), over all envs of the shard
+                tremor_occurrence_pct=100.0 * s[9] / max(s[8] + s[9], 1.0),
+                tremor_suppression_avg_pct=s[10] / max(s[11], 1.0),
+                tremor_ampl_suppression_avg_pct=s[12] / max(s[13], 1.0),
+                tremor_ampl_total_occurrence_pct=100.0 * s[7] / max(s[3], 1.0))

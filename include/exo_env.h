@@ -150,7 +150,11 @@ int exo_set_field(ExoHandle* h, int32_t field, const void* in_dev, void* stream)
 /* Episode statistics accumulated on device since the last call with reset != 0:
  * out_dev[0..EXO_N_STATS) doubles: 0 episodes, 1 sum return, 2 sum length, 3 env-steps, 4 joint-limit crossings,
  * 5 steps with |torque|<|tremor| on >=1 of the 4 arm axes, 6 sum amplitude metric over steps where it is < 0,
- * 7 count of those steps, 8.. reserved. This vector is what ranks all-reduce over NCCL. */
+ * 7 count of those steps; with `info` requested also the training script's suppression metrics
+ * (Simulation/Exoskeleton_agent_train.py:150-193): 8 / 9 arm-axis samples with torque reduction >= 0 / < 0 (tremor_when_reduction),
+ * 10 / 11 sum and count of negative torque-reduction percentages over the 7 axes, 12 / 13 the same for the amplitude
+ * reduction (positive values dropped as by the script's `disregard`), 14.. reserved.
+ * This vector is what ranks all-reduce over NCCL. */
 int exo_stats(ExoHandle* h, double* out_dev, int32_t reset, void* stream);
 
 /* Toggle ExoConfig.auto_reset after creation (e.g. to time the step kernel alone). */

@@ -367,3 +367,45 @@ def test_full_size_properties_65536_envs(exo):
     assert chk.item() == chk2.item()
     for e in (env, sub, env2):
         e.close()
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_training_script_suppression_metrics_on_device(exo, precision):
+    """Next row N3: the per-step suppression metrics of Simulation/Exoskeleton_agent_train.py:150-193,
+    accumulated by the step kernel, against the script's own numpy arithmetic applied to the kernel's info outputs
+    (nan_to_num(nan=0, posinf=0, neginf=0), tremor_when_reduction counters, `disregard` masking). Counts are exact;
+    sums agree to the accumulation order (fp64 atomics) - 1e-9 relative in fp64, 1e-5 in fp32."""
+    n, steps = 960, 40
+    env = exo.BatchedExoskeletonEnv([i % 8 for i in range(n)], [TYPES15[i % 15] for i in range(n)], list(range(n)),
+                                    precision=precision, auto_reset=True, **TRAIN)
+    env.reset()
+    env.stats(reset=True)
+    rs = np.random.RandomState(3)
+    ge = lt = ntr = nam = nampt = 0
+    s_tr = s_am = s_ampt = 0.0
+    for t in range(steps):
+        a = torch.from_numpy(rs.uniform(-1, 1, (n, 7)).astype(np.float32)).cuda()
+        _, _, _, info = env.step(a, with_info=True)
+        inf = {k: v.double().cpu().numpy() for k, v in info.items()}
+        with np.errstate(divide="ignore", invalid="ignore"):
+            tr = (np.abs(inf["torque_val"]) - np.abs(inf["tremor_torque_val"])) / np.abs(inf["tremor_torque_val"]) * 100
+            ta = (np.abs(inf["ampl_val"]) - np.abs(inf["tremor_ampl_val"])) / np.abs(inf["tremor_ampl_val"]) * 100
+        tr = np.nan_to_num(tr, nan=0, posinf=0, neginf=0)
+        ta = np.nan_to_num(ta, nan=0, posinf=0, neginf=0)
+        ge += int(np.sum(tr[:, :4] >= 0)); lt += int(np.sum(tr[:, :4] < 0))
+        s_tr += float(tr[tr < 0].sum()); ntr += int(np.sum(tr < 0))
+        s_am += float(ta[ta < 0].sum()); nam += int(np.sum(ta < 0))
+        am = inf["amp_metric"]
+        s_ampt += float(am[am < 0].sum()); nampt += int(np.sum(am < 0))
+    st = env.stats().cpu().numpy()
+    names = exo.STAT_NAMES
+    assert names[8:14] == ("arm_axis_no_reduction_count", "arm_axis_reduction_count", "torque_reduction_neg_sum",
+                           "torque_reduction_neg_count", "ampl_reduction_neg_sum", "ampl_reduction_neg_count")
+    assert st[3] == n * steps and st[8] + st[9] == 4 * n * steps
+    assert (st[8], st[9], st[11], st[13], st[7]) == (ge, lt, ntr, nam, nampt)
+    tol = 1e-9 if precision == "fp64" else 1e-5
+    assert abs(st[10] - s_tr) <= tol * abs(s_tr) and abs(st[12] - s_am) <= tol * abs(s_am) and abs(st[6] - s_ampt) <= tol * abs(s_ampt)
+    from exo_b200 import sharding
+    summ = sharding.summarize(st)
+    assert 0 < summ["tremor_occurrence_pct"] < 100 and summ["tremor_suppression_avg_pct"] < 0
+    env.close()
