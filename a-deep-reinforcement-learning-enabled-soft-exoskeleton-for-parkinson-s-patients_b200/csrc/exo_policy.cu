@@ -22,8 +22,11 @@
 //   E0 obs -> X | G1 X*l0' -> E1 a0 = AvgL1Norm -> L2 scratch | G2 X*zs1' -> E2 ELU -> X | G3 X*zs2' -> E3 ELU -> X |
 //   G4 X*zs3' -> E4 zs = AvgL1Norm -> X | G5a P = X*l1[:,300:600]' | bulk-reload X <- a0, k-atom by k-atom behind G5a | G5b P += X*l1[:,0:300]' ->
 //   E5 ReLU -> X | G6 X*l2' -> E6 ReLU -> X | G7 X*l3' (N=16) -> E7 tanh, clip, * max_action -> actions
-// (a0 takes the detour through an L2-resident per-CTA scratch because X + a second 152 KB operand do not fit in
+// (a0 takes the detour through an L2-resident per-CTA scratch because X + a second 160 KB operand do not fit in
 // shared memory and two 304-column accumulators do not fit in TMEM.)
+// Tried and measured slower: a second low-half accumulator in the spare TMEM columns so that the low
+// half of GEMM k+1 runs under epilogue k (all low-half MMAs of a layer then form ONE dependent accumulation chain:
+// 0.250 ms instead of 0.227), and four 80/64-column chains per stage (per-MMA cost dominates: 0.284 ms).
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
