@@ -30,6 +30,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <vector>
 
@@ -38,6 +39,10 @@
 
 extern "C" const char* exo_last_error(void);
 int exo_set_error(int code, const char* fmt, ...);     // exo_api.cu
+
+#ifndef EXO_POLICY_PAIR_DEFAULT
+#define EXO_POLICY_PAIR_DEFAULT false
+#endif
 
 #define PCK(call)                                                                                          \
     do {                                                                                                   \
@@ -75,7 +80,13 @@ constexpr int PACK_BYTES = (2 * ATOMS_S + 5 * ATOMS_H) * (B_LO_BYTES + B_HI_BYTE
 constexpr int OFF_X = 0;
 constexpr int OFF_W = OFF_X + X_BYTES;
 constexpr int OFF_BAR = OFF_W + NSLOT * SLOT_BYTES;
-constexpr int N_BAR = 2 * NSLOT + 3 + ATOMS_H;                     // full[], empty[], acc_full, a_ready, xr_full, xa_free[]
+constexpr int N_BAR = 3 * NSLOT + 4 + ATOMS_H;                     // full[], empty[], acc_full, a_ready, xr_full, xa_free[]; pair mode: pfull[], pxr
+// CTA-pair mode (cta_group::2, M = 256 = two 128-row tiles): each CTA of the pair stages HALF of the weight rows of an MMA
+// (rows 0..79 | 80..159 of the low half, 160..231 | 232..303 of the high half); one stage = one k-atom of both = 8 MMAs.
+constexpr int B2_LO_BYTES = (N_LO / 2) * 128, B2_HI_BYTES = (N_HI / 2) * 128;     // 10 240 / 9 216
+constexpr int B2_STAGE_BYTES = B2_LO_BYTES + B2_HI_BYTES;                         // 19 456 per CTA and k-atom
+constexpr int B2_L3_BYTES = ATOMS_H * 8 * 128;                                    // 10 240: l3, 8 of its 16 (padded) rows per CTA
+static_assert(B2_STAGE_BYTES <= SLOT_BYTES && B2_LO_BYTES % 1024 == 0, "pair-mode stage layout");
 constexpr int OFF_PART = OFF_BAR + 8 * N_BAR + 16;                 // AvgL1Norm partial sums [2][128] floats
 constexpr int SMEM_BYTES = OFF_PART + 2 * TILE_M * 4;
 static_assert(SMEM_BYTES <= 232448, "over the 227 KB per-CTA shared memory limit");
@@ -120,6 +131,49 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
                  "l"(src), "r"(bytes), "r"(bar)
                  : "memory");
+}
+// ---- CTA-pair (cluster of 2) helpers
+__device__ __forceinline__ uint32_t cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the mbarrier at the same shared-memory offset in CTA `cta` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t cta) {
+    asm volatile("{\n\t.reg .b32 ra;\n\tmapa.shared::cluster.u32 ra, %0, %1;\n\t"
+                 "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(bar), "r"(cta) : "memory");
+}
+// wait on a barrier that the peer CTA arrives on (cluster-scope acquire)
+__device__ __forceinline__ void mbar_wait_cl(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    long long t0 = 0;
+    for (uint32_t spins = 0; !done; ++spins) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (!done && (spins & 1023u) == 1023u) {
+            const long long t = clock64();
+            if (t0 == 0) t0 = t;
+            else if (t - t0 > 4000000000ll) __trap();
+        }
+    }
+}
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {      // arrives on `bar` in BOTH CTAs of the pair
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+                 "h"((unsigned short)3)
+                 : "memory");
+}
+// M = 256 over the CTA pair: each CTA multiplies its own 128 rows of A by B = [this CTA's N/2 rows ; the peer's N/2 rows]
+__device__ __forceinline__ void tc_mma_tf32_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
@@ -178,8 +232,8 @@ __host__ __device__ __forceinline__ uint32_t op_off(uint32_t r, uint32_t c, uint
     return (c >> 3) * atom_bytes + (r >> 3) * 1024u + (r & 7u) * 128u + (((c & 7u) ^ (r & 7u)) << 4);
 }
 // Instruction descriptor: D fp32 (1<<4), A and B tf32 (2<<7, 2<<10), both K-major, N>>3 at bit 17, M>>4 at bit 24.
-__host__ __device__ constexpr uint32_t idesc_tf32(int n) {
-    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
+__host__ __device__ constexpr uint32_t idesc_tf32(int n, int m = TILE_M) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 struct PolicyArgs {
@@ -289,29 +343,44 @@ __device__ __forceinline__ float avgl1_scale(uint32_t taddr, int half, int r, fl
 
 #define STAMP(i) do { if (a.dbg && tile == 0 && et == 0) a.dbg[i] = clock64(); } while (0)
 
+// PAIR = false: every CTA works alone (cta_group::1). PAIR = true: launched in clusters of 2; CTA rank 0 of a pair issues
+// tcgen05.mma.cta_group::2 for both 128-row tiles (M = 256), each CTA streams half of the weight rows, rank 1's warp 1
+// relays "my half has landed" to rank 0. Epilogues, operand X, scratch and the tile <-> CTA mapping are the same.
+template <bool PAIR>
 __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t rank = PAIR ? cluster_rank() : 0u;
+    const int n_iter = (a.n_tiles + (int)gridDim.x - 1) / (int)gridDim.x;     // the same for every CTA: a pair stays in step
     const uint32_t sbase = smem_u32(smem);
     // barriers: full[NSLOT], empty[NSLOT], acc_full, a_ready, xr_full, xa_free[ATOMS_H]; then the TMEM base address
     const uint32_t bar_full = sbase + OFF_BAR, bar_empty = bar_full + 8 * NSLOT;
     const uint32_t bar_acc = bar_empty + 8 * NSLOT, bar_aready = bar_acc + 8, bar_xr = bar_aready + 8, bar_xafree = bar_xr + 8;
+    const uint32_t bar_pfull = bar_xafree + 8 * ATOMS_H, bar_pxr = bar_pfull + 8 * NSLOT;   // pair mode, used in rank 0: the peer's full[] / xr
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + OFF_BAR + 8 * N_BAR);
 
     if (tid == 0) {
         for (int s = 0; s < NSLOT; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
         mbar_init(bar_acc, 1);
-        mbar_init(bar_aready, N_EPI);
+        mbar_init(bar_aready, PAIR ? 2 * N_EPI : N_EPI);          // pair mode: both CTAs' epilogue threads arrive at rank 0
         mbar_init(bar_xr, 1);
         for (int g = 0; g < ATOMS_H; ++g) mbar_init(bar_xafree + 8 * g, 1);
+        for (int s = 0; s < NSLOT; ++s) mbar_init(bar_pfull + 8 * s, 1);
+        mbar_init(bar_pxr, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (PAIR) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tc_fence_before();
     __syncthreads();
+    if (PAIR) cluster_sync();          // both CTAs' barriers exist before anything arrives on them remotely
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
 
@@ -328,18 +397,113 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
                 bulk_g2s(sbase + OFF_W + slot * SLOT_BYTES, src, bytes, bar_full + 8 * slot);
                 if (++slot == NSLOT) { slot = 0; par ^= 1; }
             };
-            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+            for (int it = 0; it < n_iter; ++it) {
                 const unsigned char* src = a.pack;
 #pragma unroll 1
                 for (int ph = 0; ph < 7; ++ph) {
                     const int na = ph_atoms(ph);
 #pragma unroll 1
                     for (int at = 0; at < na; ++at) {
-                        stage(src, B_LO_BYTES); src += B_LO_BYTES;
-                        stage(src, B_HI_BYTES); src += B_HI_BYTES;
+                        if (PAIR) {                              // this CTA's half of the k-atom: [rank 0 block][rank 1 block]
+                            stage(src + rank * B2_STAGE_BYTES, B2_STAGE_BYTES); src += 2 * B2_STAGE_BYTES;
+                        } else {
+                            stage(src, B_LO_BYTES); src += B_LO_BYTES;
+                            stage(src, B_HI_BYTES); src += B_HI_BYTES;
+                        }
                     }
                 }
-                stage(src, SLOT_BYTES);
+                if (PAIR) stage(src + rank * B2_L3_BYTES, B2_L3_BYTES);
+                else stage(src, SLOT_BYTES);
+            }
+        }
+    } else if (warp == 1 && PAIR) {
+        uint32_t slot = 0, par = 0, par_ar = 0, par_xr = 0;
+        if (rank == 0) {
+            // ===== pair mode, rank 0: MMA issuer for both tiles =============================================
+            constexpr uint32_t IDLO = idesc_tf32(N_LO, 256), IDHI = idesc_tf32(N_HI, 256), ID16 = idesc_tf32(OUTP, 256);
+            const uint64_t a_desc0 = smem_desc(sbase + OFF_X);
+            const uint64_t b_desc0 = smem_desc(sbase + OFF_W);
+            for (int it = 0; it < n_iter; ++it) {
+#pragma unroll 1
+                for (int ph = 0; ph < N_PHASE; ++ph) {
+                    if (ph == 5) { mbar_wait(bar_xr, par_xr); mbar_wait_cl(bar_pxr, par_xr); par_xr ^= 1; }
+                    else { mbar_wait_cl(bar_aready, par_ar); par_ar ^= 1; }
+                    tc_fence_after();
+                    const bool stamp = a.dbg && it == 0 && blockIdx.x == 0 && lane == 0;
+                    if (stamp) a.dbg[2 * ph] = clock64();
+                    const int na = ph_atoms(ph), last_ks = ph_last_ks(ph);
+                    if (ph < 7) {
+#pragma unroll 1
+                        for (int at = 0; at < na; ++at) {          // stage = one k-atom: both column halves, 8 MMAs
+                            mbar_wait(bar_full + 8 * slot, par);
+                            mbar_wait_cl(bar_pfull + 8 * slot, par);
+                            tc_fence_after();
+                            const uint64_t ad = a_desc0 + (uint64_t)(at * (A_ATOM_BYTES >> 4));
+                            const uint64_t bd = b_desc0 + (uint64_t)(slot * (SLOT_BYTES >> 4));
+                            const int nk = at == na - 1 ? last_ks : 4;
+                            if (elect_one()) {
+                                const uint32_t acc0 = (at > 0 || ph == 5) ? 1u : 0u;
+                                // k-step by k-step, the two column halves alternating: consecutive MMAs never share an accumulator
+                                // (tools/ubench/mma_fetch.cu: 159 cycles per alternating pair, ~200 per MMA in a one-accumulator chain)
+#pragma unroll
+                                for (int j = 0; j < 4; ++j)
+                                    if (j < nk) {
+                                        tc_mma_tf32_pair(tmem, ad + (uint64_t)(2 * j), bd + (uint64_t)(2 * j), IDLO, (j > 0) ? 1u : acc0);
+                                        tc_mma_tf32_pair(tmem + N_LO, ad + (uint64_t)(2 * j), bd + (uint64_t)((B2_LO_BYTES >> 4) + 2 * j), IDHI,
+                                                         (j > 0) ? 1u : acc0);
+                                    }
+                                tc_commit_pair(bar_empty + 8 * slot);          // both CTAs' stages are free once these MMAs have read them
+                                if (ph == 4) tc_commit_pair(bar_xafree + 8 * at);   // G5a is done with this k-atom of X (in both CTAs)
+                            }
+                            __syncwarp();
+                            if (++slot == NSLOT) { slot = 0; par ^= 1; }
+                        }
+                    } else {                                        // l3: 8 of its 16 padded rows from each CTA, all k-atoms in one stage
+                        mbar_wait(bar_full + 8 * slot, par);
+                        mbar_wait_cl(bar_pfull + 8 * slot, par);
+                        tc_fence_after();
+                        const uint64_t bd = b_desc0 + (uint64_t)(slot * (SLOT_BYTES >> 4));
+                        if (elect_one()) {
+#pragma unroll 1
+                            for (int at = 0; at < ATOMS_H; ++at) {
+                                const int nk = at == ATOMS_H - 1 ? last_ks : 4;
+#pragma unroll
+                                for (int j = 0; j < 4; ++j)
+                                    if (j < nk)
+                                        tc_mma_tf32_pair(tmem, a_desc0 + (uint64_t)(at * (A_ATOM_BYTES >> 4) + 2 * j),
+                                                         bd + (uint64_t)(at * (8 * 128 >> 4) + 2 * j), ID16, (at > 0 || j > 0) ? 1u : 0u);
+                            }
+                            tc_commit_pair(bar_empty + 8 * slot);
+                        }
+                        __syncwarp();
+                        if (++slot == NSLOT) { slot = 0; par ^= 1; }
+                    }
+                    if (ph != 4) {
+                        if (elect_one()) tc_commit_pair(bar_acc);                // both CTAs' epilogues may read their accumulators
+                        __syncwarp();
+                    }
+                    if (stamp) a.dbg[2 * ph + 1] = clock64();
+                }
+            }
+        } else {
+            // ===== pair mode, rank 1: tell rank 0 when this CTA's weight halves / reloaded a0 have landed ===========
+            for (int it = 0; it < n_iter; ++it) {
+#pragma unroll 1
+                for (int ph = 0; ph < N_PHASE; ++ph) {
+                    if (ph == 5) {
+                        mbar_wait(bar_xr, par_xr); par_xr ^= 1;
+                        if (lane == 0) mbar_arrive_remote(bar_pxr, 0);
+                        __syncwarp();
+                    }
+                    const int nst = ph < 7 ? ph_atoms(ph) : 1;
+#pragma unroll 1
+                    for (int st = 0; st < nst; ++st) {
+                        mbar_wait(bar_full + 8 * slot, par);
+                        if (lane == 0) mbar_arrive_remote(bar_pfull + 8 * slot, 0);
+                        __syncwarp();
+                        if (++slot == NSLOT) { slot = 0; par ^= 1; }
+                    }
+                }
             }
         }
     } else if (warp == 1) {
@@ -348,7 +512,8 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
         constexpr uint32_t IDLO = idesc_tf32(N_LO), IDHI = idesc_tf32(N_HI), ID16 = idesc_tf32(OUTP);
         const uint64_t a_desc0 = smem_desc(sbase + OFF_X);
         const uint64_t b_desc0 = smem_desc(sbase + OFF_W);
-        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+        for (int it = 0; it < n_iter; ++it) {
+            const int tile = blockIdx.x + it * gridDim.x;
 #pragma unroll 1
             for (int ph = 0; ph < N_PHASE; ++ph) {
                 if (ph == 5) { mbar_wait(bar_xr, par_xr); par_xr ^= 1; }
@@ -427,8 +592,14 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
                 if (tile < a.n_tiles && row0 + rr < a.n) ob[i] = __ldg(reinterpret_cast<const float4*>(a.obs + (row0 + rr) * SD) + c);
             }
         };
+        // "the previous epilogue is done" goes to the MMA issuer: this CTA's, or in pair mode the one in rank 0
+        auto arrive_aready = [&]() {
+            if (PAIR && rank != 0) mbar_arrive_remote(bar_aready, 0);
+            else mbar_arrive(bar_aready);
+        };
         load_obs(blockIdx.x);
-        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+        for (int it = 0; it < n_iter; ++it) {
+            const int tile = blockIdx.x + it * gridDim.x;          // may lie past the end in the last round: every row is masked then
             const long long row0 = (long long)tile * TILE_M;
             STAMP(16);
             // E0: observations -> the first 22 chunks of X's rows (80 values, the constant 1, 7 zeros), rounded to TF32; both
@@ -446,7 +617,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
             fence_proxy_async_smem();
             tc_fence_before();
             STAMP(17);
-            mbar_arrive(bar_aready);
+            arrive_aready();
             load_obs(tile + gridDim.x);
             // E1: a0 = AvgL1Norm(l0(obs)) -> scratch
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
@@ -457,7 +628,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
             }
             tc_fence_before();
             STAMP(19);
-            mbar_arrive(bar_aready);                         // the accumulator is drained: zs1 may start while the stores land
+            arrive_aready();                         // the accumulator is drained: zs1 may start while the stores land
             __threadfence();
             fence_proxy_async_all();
             asm volatile("bar.sync 1, 256;" ::: "memory");   // all of a0 is out (and visible to the bulk copies) before the reload
@@ -467,13 +638,13 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
             epi_half<0>(taddr, half, xrow, rsw, 0.f, nullptr);
             fence_proxy_async_smem(); tc_fence_before();
             STAMP(21);
-            mbar_arrive(bar_aready);
+            arrive_aready();
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
             STAMP(22);
             epi_half<0>(taddr, half, xrow, rsw, 0.f, nullptr);
             fence_proxy_async_smem(); tc_fence_before();
             STAMP(23);
-            mbar_arrive(bar_aready);
+            arrive_aready();
             // E4: zs = AvgL1Norm(zs3(.))
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
             STAMP(24);
@@ -483,7 +654,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
             }
             fence_proxy_async_smem(); tc_fence_before();
             STAMP(25);
-            mbar_arrive(bar_aready);
+            arrive_aready();
             // as G5a finishes reading each k-atom of zs out of X, bring that k-atom of a0 back (one bulk copy each)
             if (et == 0) {
                 mbar_expect_tx(bar_xr, X_BYTES);
@@ -499,13 +670,13 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
             epi_half<1>(taddr, half, xrow, rsw, 0.f, nullptr);
             fence_proxy_async_smem(); tc_fence_before();
             STAMP(27);
-            mbar_arrive(bar_aready);
+            arrive_aready();
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
             STAMP(28);
             epi_half<1>(taddr, half, xrow, rsw, 0.f, nullptr);
             fence_proxy_async_smem(); tc_fence_before();
             STAMP(29);
-            mbar_arrive(bar_aready);
+            arrive_aready();
             // E7: actions (column half 0 only; the other warps just keep the barrier phases)
             mbar_wait(bar_acc, par_acc); par_acc ^= 1; tc_fence_after();
             STAMP(30);
@@ -525,10 +696,12 @@ __global__ void __launch_bounds__(N_THREADS, 1) exo_policy_kernel(const PolicyAr
     }
     tc_fence_before();
     __syncthreads();
+    if (PAIR) cluster_sync();          // the peer may still be reading this CTA's weight stages / arriving on its barriers
     if (warp == 1) {
         __syncwarp();
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+        if (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
     }
 }
 
@@ -559,12 +732,35 @@ size_t pack_matrix(unsigned char* dst, const float* W, const float* bias, int n_
     return atoms * atom_bytes;
 }
 
+// The same matrix for the CTA-pair kernel: per k-atom [rank 0 block][rank 1 block], a block = this CTA's half of the low
+// rows (n_lo/2) followed by its half of the high rows (n_hi/2). With n_hi == 0 (l3) the blocks are per rank: all k-atoms
+// of its n_lo/2 rows. Returns the bytes written.
+size_t pack_matrix_pair(unsigned char* dst, const float* W, const float* bias, int n_rows, int ld, int col0, int k_real, int n_lo, int n_hi,
+                        int atoms) {
+    const int lo2 = n_lo / 2, hi2 = n_hi / 2;
+    const size_t blk = (size_t)(lo2 + hi2) * 128;
+    memset(dst, 0, 2 * atoms * blk);
+    for (int n = 0; n < n_rows; ++n)
+        for (int k = 0; k <= k_real; ++k) {
+            if (k == k_real && !bias) break;
+            const int hi = n >= n_lo, m = hi ? n - n_lo : n, half = hi ? hi2 : lo2;
+            const int rank = m / half, nl = m % half, at = k / 32;
+            const size_t base = n_hi ? ((size_t)at * 2 + rank) * blk + (hi ? (size_t)lo2 * 128 : 0)
+                                     : (size_t)rank * atoms * blk + (size_t)at * blk;
+            const size_t off = base + op_off((uint32_t)nl, (uint32_t)((k % 32) / 4), 0u) + (k % 4) * 4;
+            const float v = round_tf32(k < k_real ? W[(size_t)n * ld + col0 + k] : bias[n]);
+            memcpy(dst + off, &v, 4);
+        }
+    return 2 * atoms * blk;
+}
+
 }  // namespace
 
 struct ExoPolicy {
     int device, n_sm;
     bool loaded;
-    unsigned char *pack, *scratch;
+    bool pair;                       // CTA-pair kernel (cta_group::2); EXO_POLICY_PAIR=0 selects the single-CTA kernel
+    unsigned char *pack, *pack2, *scratch;
     int64_t launches;
     long long* dbg;
 };
@@ -580,11 +776,15 @@ extern "C" int exo_policy_create(int32_t device, ExoPolicy** out) {
     PCK(cudaSetDevice(device));
     ExoPolicy* p = new ExoPolicy();
     p->device = device; p->n_sm = prop.multiProcessorCount; p->loaded = false; p->launches = 0;
-    p->pack = p->scratch = nullptr; p->dbg = nullptr;
+    p->pack = p->pack2 = p->scratch = nullptr; p->dbg = nullptr;
+    const char* pm = getenv("EXO_POLICY_PAIR");
+    p->pair = pm ? (pm[0] != '0') : EXO_POLICY_PAIR_DEFAULT;
     cudaError_t e = cudaMalloc((void**)&p->pack, PACK_BYTES);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&p->pack2, PACK_BYTES);
     if (e == cudaSuccess) e = cudaMalloc((void**)&p->scratch, (size_t)p->n_sm * X_BYTES);
     if (e == cudaSuccess) e = cudaMemset(p->scratch, 0, (size_t)p->n_sm * X_BYTES);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(exo_policy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(exo_policy_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(exo_policy_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) {
         exo_policy_destroy(p);
         return exo_set_error(EXO_ERR_CUDA, "exo_policy_create: %s", cudaGetErrorString(e));
@@ -596,7 +796,7 @@ extern "C" int exo_policy_create(int32_t device, ExoPolicy** out) {
 extern "C" int exo_policy_destroy(ExoPolicy* p) {
     if (!p) return EXO_OK;
     cudaSetDevice(p->device);
-    cudaFree(p->pack); cudaFree(p->scratch);
+    cudaFree(p->pack); cudaFree(p->pack2); cudaFree(p->scratch);
     delete p;
     return EXO_OK;
 }
@@ -625,6 +825,17 @@ extern "C" int exo_policy_set_weights(ExoPolicy* p, const ExoPolicyWeights* w, i
     if (d != pack.data() + PACK_BYTES) return exo_set_error(EXO_ERR_STATE, "exo_policy_set_weights: pack size mismatch");
     PCK(cudaSetDevice(p->device));
     PCK(cudaMemcpy(p->pack, pack.data(), PACK_BYTES, cudaMemcpyHostToDevice));
+    d = pack.data();                 // and the CTA-pair layout of the same matrices
+    d += pack_matrix_pair(d, w->l0_w, w->l0_b, HD, SD, 0, SD, N_LO, N_HI, ATOMS_S);
+    d += pack_matrix_pair(d, w->zs1_w, w->zs1_b, HD, SD, 0, SD, N_LO, N_HI, ATOMS_S);
+    d += pack_matrix_pair(d, w->zs2_w, w->zs2_b, HD, HD, 0, HD, N_LO, N_HI, ATOMS_H);
+    d += pack_matrix_pair(d, w->zs3_w, w->zs3_b, HD, HD, 0, HD, N_LO, N_HI, ATOMS_H);
+    d += pack_matrix_pair(d, w->l1_w, nullptr, HD, 2 * HD, HD, HD, N_LO, N_HI, ATOMS_H);
+    d += pack_matrix_pair(d, w->l1_w, w->l1_b, HD, 2 * HD, 0, HD, N_LO, N_HI, ATOMS_H);
+    d += pack_matrix_pair(d, w->l2_w, w->l2_b, HD, HD, 0, HD, N_LO, N_HI, ATOMS_H);
+    d += pack_matrix_pair(d, w->l3_w, w->l3_b, AD, HD, 0, HD, OUTP, 0, ATOMS_H);
+    if (d != pack.data() + PACK_BYTES) return exo_set_error(EXO_ERR_STATE, "exo_policy_set_weights: pair pack size mismatch");
+    PCK(cudaMemcpy(p->pack2, pack.data(), PACK_BYTES, cudaMemcpyHostToDevice));
     p->loaded = true;
     return EXO_OK;
 }
@@ -641,8 +852,24 @@ extern "C" int exo_policy_forward(ExoPolicy* p, const float* obs_dev, int64_t n,
     const long long tiles = (n + TILE_M - 1) / TILE_M;
     if (tiles > 0x7FFFFFFF) return exo_set_error(EXO_ERR_ARG, "exo_policy_forward: too many observations");
     a.n_tiles = (int)tiles;
-    const int grid = (int)(tiles < p->n_sm ? tiles : p->n_sm);
-    exo_policy_kernel<<<grid, N_THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(a);
+    if (p->pair) {
+        // clusters of 2 CTAs: an even grid; a CTA whose tile lies past the end works on masked rows to keep its peer company
+        const long long want = (tiles + 1) & ~1ll, cap = p->n_sm & ~1;
+        a.pack = p->pack2;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(want < cap ? want : cap));
+        cfg.blockDim = dim3(N_THREADS);
+        cfg.dynamicSmemBytes = SMEM_BYTES;
+        cfg.stream = (cudaStream_t)stream;
+        cudaLaunchAttribute attr;
+        attr.id = cudaLaunchAttributeClusterDimension;
+        attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+        cfg.attrs = &attr; cfg.numAttrs = 1;
+        PCK(cudaLaunchKernelEx(&cfg, exo_policy_kernel<true>, a));
+    } else {
+        const int grid = (int)(tiles < p->n_sm ? tiles : p->n_sm);
+        exo_policy_kernel<false><<<grid, N_THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(a);
+    }
     PCK(cudaGetLastError());
     p->launches += 1;
     return EXO_OK;

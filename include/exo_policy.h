@@ -45,7 +45,8 @@ typedef struct ExoPolicyWeights {
     const float *l3_w, *l3_b;     /* [7, 300],   [7]   */
 } ExoPolicyWeights;
 
-/* Fails unless `device` is an sm_100 GPU (there is no CPU path). */
+/* Fails unless `device` is an sm_100 GPU (there is no CPU path). Environment EXO_POLICY_PAIR=1 selects the CTA-pair
+ * (cta_group::2) variant of the kernel for this handle; results are bit-identical. */
 int exo_policy_create(int32_t device, ExoPolicy** out);
 int exo_policy_destroy(ExoPolicy* p);
 

@@ -154,3 +154,26 @@ def test_policy_consumes_env_obs_directly(exo, gold):
     assert torch.isfinite(tot).all() and float(tot.mean()) > 0
     assert p.launch_count() == 20
     env.close(); p.close()
+
+
+@pytest.mark.gpu
+def test_cta_pair_kernel_is_bit_identical(exo, gold, monkeypatch):
+    """EXO_POLICY_PAIR=1 selects the cta_group::2 kernel (clusters of two CTAs, M = 256, each CTA staging half of the
+    weight rows). Same products, same accumulation order: its actions and zs equal the single-CTA kernel's bit for bit,
+    for sizes that leave the last pair with one real tile, one masked tile, or a single partial tile."""
+    import torch
+    base = torch.from_numpy(gold["obs"]).cuda()
+    outs = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("EXO_POLICY_PAIR", mode)
+        p = _policy(exo, gold)
+        res = []
+        for n in (1, 128, 129, 769, 148 * 128 + 5, 40000):
+            obs = base[torch.arange(n, device="cuda") % base.shape[0]].contiguous()
+            act, zs = p.forward(obs, use_checkpoint=True, return_zs=True)
+            res.append((act.clone(), zs.clone()))
+        torch.cuda.synchronize()
+        outs[mode] = res
+        p.close()
+    for (a0, z0), (a1, z1) in zip(outs["0"], outs["1"]):
+        assert torch.equal(a0, a1) and torch.equal(z0, z1)

@@ -25,13 +25,19 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 __host__ __device__ constexpr uint32_t idesc(int n) { return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | (8u << 24); }
-__global__ void k(int mode, int reps, long long* out) {
+__global__ void k(int mode, int reps, int fill, int spin, long long* out) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    __shared__ uint64_t bar;
+    __shared__ uint64_t bar, never;
+    __shared__ volatile int stop;
     __shared__ uint32_t tslot;
-    for (int i = threadIdx.x; i < 224 * 1024 / 4; i += blockDim.x) ((uint32_t*)smem)[i] = 0;
+    for (int i = threadIdx.x; i < 224 * 1024 / 4; i += blockDim.x) {
+        uint32_t h = (uint32_t)i * 2654435761u; h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+        ((float*)smem)[i] = fill ? ((float)(h & 0xFFFF) / 65536.0f - 0.5f) : 0.0f;      // zeros vs values in (-0.5, 0.5): is the rate data dependent?
+    }
     if (threadIdx.x == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&never)));
+        stop = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (threadIdx.x < 32) {
@@ -81,7 +87,10 @@ __global__ void k(int mode, int reps, long long* out) {
         __syncwarp();
         while (!mbar_try(smem_u32(&bar), 0)) {}
         const long long t2 = clock64();
-        if (threadIdx.x == 0) { out[0] = t1 - t0; out[1] = t2 - t0; }
+        if (threadIdx.x == 0) { out[0] = t1 - t0; out[1] = t2 - t0; stop = 1; }
+    } else if (spin) {
+        // the epilogue warps of the real kernel: polling an mbarrier while the MMAs run
+        while (!stop) mbar_try(smem_u32(&never), 0);
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -92,12 +101,14 @@ int main() {
     cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
     const int reps = 10;
     printf("mode(0 sw32, 1 sw128, 2 sw32 N=160 only, 3 sw32 same operands) issue_cyc_per_kstep total_cyc_per_kstep\n");
+    for (int spin = 0; spin < 2; ++spin)
     for (int mode = 0; mode < 4; ++mode) {
-        k<<<1, 128, 224 * 1024>>>(mode, reps, d);
+        const int fill = 1;
+        k<<<1, 320, 224 * 1024>>>(mode, reps, fill, spin, d);
         long long h[2];
         cudaError_t e = cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }
-        printf("%d %.1f %.1f\n", mode, (double)h[0] / (reps * 38), (double)h[1] / (reps * 38));
+        printf("spin=%d %d %.1f %.1f\n", spin, mode, (double)h[0] / (reps * 38), (double)h[1] / (reps * 38));
     }
     return 0;
 }
