@@ -36,6 +36,7 @@
 
 #include "../../include/exo_env.h"
 #include "../../include/exo_policy.h"
+#include "exo_policy_fp32.h"
 
 extern "C" const char* exo_last_error(void);
 int exo_set_error(int code, const char* fmt, ...);     // exo_api.cu
@@ -761,6 +762,7 @@ struct ExoPolicy {
     bool loaded;
     bool pair;                       // CTA-pair kernel (cta_group::2); EXO_POLICY_PAIR=0 selects the single-CTA kernel
     unsigned char *pack, *pack2, *scratch;
+    ExoPolicyF32* f32;               // the float32 path (exo_policy_fp32.cu)
     int64_t launches;
     long long* dbg;
 };
@@ -776,7 +778,7 @@ extern "C" int exo_policy_create(int32_t device, ExoPolicy** out) {
     PCK(cudaSetDevice(device));
     ExoPolicy* p = new ExoPolicy();
     p->device = device; p->n_sm = prop.multiProcessorCount; p->loaded = false; p->launches = 0;
-    p->pack = p->pack2 = p->scratch = nullptr; p->dbg = nullptr;
+    p->pack = p->pack2 = p->scratch = nullptr; p->dbg = nullptr; p->f32 = nullptr;
     const char* pm = getenv("EXO_POLICY_PAIR");
     p->pair = pm ? (pm[0] != '0') : EXO_POLICY_PAIR_DEFAULT;
     cudaError_t e = cudaMalloc((void**)&p->pack, PACK_BYTES);
@@ -789,6 +791,10 @@ extern "C" int exo_policy_create(int32_t device, ExoPolicy** out) {
         exo_policy_destroy(p);
         return exo_set_error(EXO_ERR_CUDA, "exo_policy_create: %s", cudaGetErrorString(e));
     }
+    if (int rc = exo_policy_f32_create(device, p->n_sm, &p->f32)) {
+        exo_policy_destroy(p);
+        return rc;
+    }
     *out = p;
     return EXO_OK;
 }
@@ -797,6 +803,7 @@ extern "C" int exo_policy_destroy(ExoPolicy* p) {
     if (!p) return EXO_OK;
     cudaSetDevice(p->device);
     cudaFree(p->pack); cudaFree(p->pack2); cudaFree(p->scratch);
+    exo_policy_f32_destroy(p->f32);
     delete p;
     return EXO_OK;
 }
@@ -836,6 +843,7 @@ extern "C" int exo_policy_set_weights(ExoPolicy* p, const ExoPolicyWeights* w, i
     d += pack_matrix_pair(d, w->l3_w, w->l3_b, AD, HD, 0, HD, OUTP, 0, ATOMS_H);
     if (d != pack.data() + PACK_BYTES) return exo_set_error(EXO_ERR_STATE, "exo_policy_set_weights: pair pack size mismatch");
     PCK(cudaMemcpy(p->pack2, pack.data(), PACK_BYTES, cudaMemcpyHostToDevice));
+    if (int rc = exo_policy_f32_set_weights(p->f32, w)) return rc;
     p->loaded = true;
     return EXO_OK;
 }
@@ -871,6 +879,17 @@ extern "C" int exo_policy_forward(ExoPolicy* p, const float* obs_dev, int64_t n,
         exo_policy_kernel<false><<<grid, N_THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(a);
     }
     PCK(cudaGetLastError());
+    p->launches += 1;
+    return EXO_OK;
+}
+
+extern "C" int exo_policy_forward_fp32(ExoPolicy* p, const float* obs_dev, int64_t n, float max_action, float* actions_dev, float* zs_dev,
+                                       void* stream) {
+    if (!p || !obs_dev || !actions_dev || n < 0) return exo_set_error(EXO_ERR_ARG, "exo_policy_forward_fp32: bad arguments");
+    if (!p->loaded) return exo_set_error(EXO_ERR_STATE, "exo_policy_forward_fp32: no weights (exo_policy_set_weights first)");
+    if (((uintptr_t)obs_dev & 15) != 0) return exo_set_error(EXO_ERR_ARG, "exo_policy_forward_fp32: obs must be 16-byte aligned");
+    if (n == 0) return EXO_OK;
+    if (int rc = exo_policy_f32_forward(p->f32, obs_dev, n, max_action, actions_dev, zs_dev, stream)) return rc;
     p->launches += 1;
     return EXO_OK;
 }

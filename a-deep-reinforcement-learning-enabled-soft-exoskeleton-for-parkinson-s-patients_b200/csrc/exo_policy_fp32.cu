@@ -1,0 +1,275 @@
+// exo_policy_fp32.cu — the policy forward pass of include/exo_policy.h in the reference's own arithmetic: float32
+// products and sums on the FP32 pipe (torch's default matmul), for runs that must reproduce the reference's actions to
+// summation order (evaluation replays, parity tests). The fast path is the TF32 tensor-core kernel of exo_policy.cu.
+//
+//   encoder.zs + actor of Agent/TD7_multi_agent_Pink_noise.py:59-105 as select_action evaluates them (:208-228).
+//
+// One fused kernel, 64 observations per CTA tile, 256 threads: warp w owns rows 8w..8w+7 of the tile, lane l the columns
+// l, l+32, ..., l+288 (80 accumulators per thread). Activations ping-pong between two 64 x 304 shared-memory buffers;
+// every layer streams its weights (host-transposed to [K][320], zero padded) from L2 in 16-row chunks through a
+// cp.async double buffer. cat[a0, zs] * l1' is two accumulating passes; a0 waits in an L2-resident per-CTA scratch.
+// FP32-pipe bound: 12 shared-memory loads per 80 FFMA in the inner loop.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string.h>
+#include <vector>
+
+#include "../../include/exo_env.h"
+#include "../../include/exo_policy.h"
+#include "exo_policy_fp32.h"
+
+int exo_set_error(int code, const char* fmt, ...);     // exo_api.cu
+
+namespace {
+
+constexpr int SD = EXO_POLICY_STATE_DIM, HD = EXO_POLICY_HIDDEN_DIM, AD = EXO_POLICY_ACTION_DIM;
+constexpr int HP = 304;          // activation row pitch / K of a hidden layer (300 padded to a multiple of the 16-row chunk)
+constexpr int WP = 320;          // weight row pitch: 10 columns per lane
+constexpr int TM = 64, KC = 16, NT = 256, NC = WP / 32;
+constexpr int BUF_FLOATS = TM * HP;
+constexpr int SMEM_BYTES = (2 * BUF_FLOATS + 2 * KC * WP) * 4;      // 196 608
+
+// transposed weight blocks in the order of use, each [K_pad][WP]; biases [7][WP]
+constexpr int K_OBS = SD, K_HID = HP;
+constexpr size_t OFF_L0 = 0, OFF_ZS1 = OFF_L0 + (size_t)K_OBS * WP, OFF_ZS2 = OFF_ZS1 + (size_t)K_OBS * WP,
+                 OFF_ZS3 = OFF_ZS2 + (size_t)K_HID * WP, OFF_L1B = OFF_ZS3 + (size_t)K_HID * WP, OFF_L1A = OFF_L1B + (size_t)K_HID * WP,
+                 OFF_L2 = OFF_L1A + (size_t)K_HID * WP, OFF_L3 = OFF_L2 + (size_t)K_HID * WP, WT_FLOATS = OFF_L3 + (size_t)AD * HP;
+enum { B_L0 = 0, B_ZS1 = WP, B_ZS2 = 2 * WP, B_ZS3 = 3 * WP, B_L1 = 4 * WP, B_L2 = 5 * WP, B_L3 = 6 * WP, BIAS_FLOATS = 7 * WP };
+
+struct F32Args {
+    const float *obs, *wt, *bias;
+    float *scratch, *actions, *zs;
+    long long n;
+    float max_action;
+    int n_tiles;
+};
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// acc[r][c] += sum_k X[8*warp + r][k] * WT[k][lane + 32 c], k < K (a multiple of 16). All 256 threads.
+__device__ __forceinline__ void gemm_acc(float (&acc)[8][NC], const float* __restrict__ X, const float* __restrict__ wt, int K, float* ws,
+                                         int warp, int lane, int tid) {
+    const int nchunk = K / KC;
+    auto load_chunk = [&](int c, int buf) {
+        const float4* src = reinterpret_cast<const float4*>(wt + (size_t)c * KC * WP);
+        float4* dst = reinterpret_cast<float4*>(ws + buf * KC * WP);
+        for (int i = tid; i < KC * WP / 4; i += NT) cp_async16(dst + i, src + i);
+        cp_async_commit();
+    };
+    load_chunk(0, 0);
+    for (int c = 0; c < nchunk; ++c) {
+        cp_async_wait_all();
+        __syncthreads();                           // chunk c has landed for everyone; chunk c-1's buffer is free
+        if (c + 1 < nchunk) load_chunk(c + 1, (c + 1) & 1);
+        const float* w = ws + (c & 1) * KC * WP + lane;
+        const float* x = X + (size_t)(warp * 8) * HP + c * KC;
+#pragma unroll
+        for (int k4 = 0; k4 < KC; k4 += 4) {
+            float4 xv[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) xv[r] = *reinterpret_cast<const float4*>(x + r * HP + k4);     // warp-wide broadcast
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                float wv[NC];
+#pragma unroll
+                for (int cc = 0; cc < NC; ++cc) wv[cc] = w[(k4 + kk) * WP + 32 * cc];
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    const float xs = kk == 0 ? xv[r].x : kk == 1 ? xv[r].y : kk == 2 ? xv[r].z : xv[r].w;
+#pragma unroll
+                    for (int cc = 0; cc < NC; ++cc) acc[r][cc] = fmaf(xs, wv[cc], acc[r][cc]);
+                }
+            }
+        }
+    }
+    __syncthreads();                               // every warp is done with X and with the last chunk
+}
+
+__device__ __forceinline__ void zero_acc(float (&acc)[8][NC]) {
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+#pragma unroll
+        for (int c = 0; c < NC; ++c) acc[r][c] = 0.f;
+}
+
+// ACT 0 ELU, 1 ReLU, 2 AvgL1Norm (:59-60). Adds the bias, applies ACT, stores the thread's 8 x 10 values at dst[row * pitch + col]
+// (columns >= 304 are dropped; 300..303 are exactly 0: zero weights and bias).
+template <int ACT>
+__device__ __forceinline__ void store_act(float (&acc)[8][NC], const float* __restrict__ bias, float* dst, int pitch, int warp, int lane,
+                                          float* zs_out, long long row0, long long n) {
+    float b[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) b[c] = __ldg(bias + lane + 32 * c);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        float v[NC];
+        float s = 0.f;
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            v[c] = acc[r][c] + b[c];
+            if (ACT == 0) v[c] = v[c] > 0.f ? v[c] : expm1f(v[c]);
+            if (ACT == 1) v[c] = fmaxf(v[c], 0.f);
+            if (ACT == 2) s += fabsf(v[c]);
+        }
+        if (ACT == 2) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            const float denom = fmaxf(s / (float)HD, 1e-8f);
+#pragma unroll
+            for (int c = 0; c < NC; ++c) v[c] = v[c] / denom;
+        }
+        const int row = warp * 8 + r;
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            const int col = lane + 32 * c;
+            if (col < HP) dst[(size_t)row * pitch + col] = v[c];
+            if (ACT == 2 && zs_out && col < HD && row0 + row < n) zs_out[(row0 + row) * HD + col] = v[c];
+        }
+    }
+}
+
+__global__ void __launch_bounds__(NT, 1) exo_policy_fp32_kernel(const F32Args a) {
+    extern __shared__ __align__(16) float sm[];
+    float* bufA = sm;
+    float* bufB = sm + BUF_FLOATS;
+    float* ws = sm + 2 * BUF_FLOATS;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    float* scratch = a.scratch + (size_t)blockIdx.x * BUF_FLOATS;
+    float acc[8][NC];
+    for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+        const long long row0 = (long long)tile * TM;
+        // observations -> bufA[:, 0:80]
+        for (int i = tid; i < TM * SD / 4; i += NT) {
+            const int r = i / (SD / 4), c = i % (SD / 4);
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (row0 + r < a.n) v = __ldg(reinterpret_cast<const float4*>(a.obs + (row0 + r) * SD) + c);
+            *reinterpret_cast<float4*>(bufA + r * HP + 4 * c) = v;
+        }
+        __syncthreads();
+        // a0 = AvgL1Norm(l0(obs)) -> scratch
+        zero_acc(acc);
+        gemm_acc(acc, bufA, a.wt + OFF_L0, K_OBS, ws, warp, lane, tid);
+        store_act<2>(acc, a.bias + B_L0, scratch, HP, warp, lane, nullptr, row0, a.n);
+        // zs = AvgL1Norm(zs3(elu(zs2(elu(zs1(obs))))))
+        zero_acc(acc);
+        gemm_acc(acc, bufA, a.wt + OFF_ZS1, K_OBS, ws, warp, lane, tid);
+        store_act<0>(acc, a.bias + B_ZS1, bufB, HP, warp, lane, nullptr, row0, a.n);
+        __syncthreads();
+        zero_acc(acc);
+        gemm_acc(acc, bufB, a.wt + OFF_ZS2, K_HID, ws, warp, lane, tid);
+        store_act<0>(acc, a.bias + B_ZS2, bufA, HP, warp, lane, nullptr, row0, a.n);
+        __syncthreads();
+        zero_acc(acc);
+        gemm_acc(acc, bufA, a.wt + OFF_ZS3, K_HID, ws, warp, lane, tid);
+        store_act<2>(acc, a.bias + B_ZS3, bufB, HP, warp, lane, a.zs, row0, a.n);
+        __syncthreads();
+        // l1(cat[a0, zs]) = l1[:, 300:600] zs + l1[:, 0:300] a0 + b: the zs half first, a0 comes back from the scratch meanwhile
+        for (int i = tid; i < BUF_FLOATS / 4; i += NT)
+            reinterpret_cast<float4*>(bufA)[i] = reinterpret_cast<const float4*>(scratch)[i];     // this CTA's own writes (L2/L1 coherent within the CTA after the barriers)
+        zero_acc(acc);
+        gemm_acc(acc, bufB, a.wt + OFF_L1B, K_HID, ws, warp, lane, tid);
+        gemm_acc(acc, bufA, a.wt + OFF_L1A, K_HID, ws, warp, lane, tid);
+        store_act<1>(acc, a.bias + B_L1, bufB, HP, warp, lane, nullptr, row0, a.n);
+        __syncthreads();
+        zero_acc(acc);
+        gemm_acc(acc, bufB, a.wt + OFF_L2, K_HID, ws, warp, lane, tid);
+        store_act<1>(acc, a.bias + B_L2, bufA, HP, warp, lane, nullptr, row0, a.n);
+        __syncthreads();
+        // l3 + tanh + clip: warp w, rows 8w..8w+7; lane l sums k = l, l+32, ...
+        const float* w3 = a.wt + OFF_L3;
+#pragma unroll 1
+        for (int r = 0; r < 8; ++r) {
+            const int row = warp * 8 + r;
+            float s[AD];
+#pragma unroll
+            for (int j = 0; j < AD; ++j) s[j] = 0.f;
+            for (int k = lane; k < HD; k += 32) {
+                const float x = bufA[row * HP + k];
+#pragma unroll
+                for (int j = 0; j < AD; ++j) s[j] = fmaf(x, __ldg(w3 + j * HP + k), s[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < AD; ++j)
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) s[j] += __shfl_xor_sync(0xffffffffu, s[j], o);
+            if (lane < AD && row0 + row < a.n) {
+                float v = 0.f;
+#pragma unroll
+                for (int j = 0; j < AD; ++j) if (lane == j) v = s[j];
+                v = tanhf(v + __ldg(a.bias + B_L3 + lane));
+                a.actions[(row0 + row) * AD + lane] = fminf(fmaxf(v, -1.f), 1.f) * a.max_action;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+void transpose_into(float* dst, const float* W, int n_rows, int ld, int col0, int k_real) {     // dst[k][WP] = W[n][col0 + k]
+    for (int n = 0; n < n_rows; ++n)
+        for (int k = 0; k < k_real; ++k) dst[(size_t)k * WP + n] = W[(size_t)n * ld + col0 + k];
+}
+
+}  // namespace
+
+struct ExoPolicyF32 {
+    int device, n_sm;
+    float *wt, *bias, *scratch;
+};
+
+int exo_policy_f32_create(int device, int n_sm, ExoPolicyF32** out) {
+    ExoPolicyF32* p = new ExoPolicyF32();
+    p->device = device; p->n_sm = n_sm; p->wt = p->bias = p->scratch = nullptr;
+    cudaError_t e = cudaMalloc((void**)&p->wt, WT_FLOATS * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&p->bias, BIAS_FLOATS * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&p->scratch, (size_t)n_sm * BUF_FLOATS * sizeof(float));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(exo_policy_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) {
+        exo_policy_f32_destroy(p);
+        return exo_set_error(EXO_ERR_CUDA, "exo_policy (fp32 path): %s", cudaGetErrorString(e));
+    }
+    *out = p;
+    return EXO_OK;
+}
+
+void exo_policy_f32_destroy(ExoPolicyF32* p) {
+    if (!p) return;
+    cudaFree(p->wt); cudaFree(p->bias); cudaFree(p->scratch);
+    delete p;
+}
+
+int exo_policy_f32_set_weights(ExoPolicyF32* p, const ExoPolicyWeights* w) {
+    std::vector<float> wt(WT_FLOATS, 0.f), bias(BIAS_FLOATS, 0.f);
+    transpose_into(&wt[OFF_L0], w->l0_w, HD, SD, 0, SD);
+    transpose_into(&wt[OFF_ZS1], w->zs1_w, HD, SD, 0, SD);
+    transpose_into(&wt[OFF_ZS2], w->zs2_w, HD, HD, 0, HD);
+    transpose_into(&wt[OFF_ZS3], w->zs3_w, HD, HD, 0, HD);
+    transpose_into(&wt[OFF_L1B], w->l1_w, HD, 2 * HD, HD, HD);
+    transpose_into(&wt[OFF_L1A], w->l1_w, HD, 2 * HD, 0, HD);
+    transpose_into(&wt[OFF_L2], w->l2_w, HD, HD, 0, HD);
+    for (int j = 0; j < AD; ++j) memcpy(&wt[OFF_L3 + (size_t)j * HP], w->l3_w + (size_t)j * HD, HD * sizeof(float));
+    memcpy(&bias[B_L0], w->l0_b, HD * 4);   memcpy(&bias[B_ZS1], w->zs1_b, HD * 4); memcpy(&bias[B_ZS2], w->zs2_b, HD * 4);
+    memcpy(&bias[B_ZS3], w->zs3_b, HD * 4); memcpy(&bias[B_L1], w->l1_b, HD * 4);   memcpy(&bias[B_L2], w->l2_b, HD * 4);
+    memcpy(&bias[B_L3], w->l3_b, AD * 4);
+    cudaError_t e = cudaMemcpy(p->wt, wt.data(), WT_FLOATS * sizeof(float), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(p->bias, bias.data(), BIAS_FLOATS * sizeof(float), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return exo_set_error(EXO_ERR_CUDA, "exo_policy_set_weights (fp32 path): %s", cudaGetErrorString(e));
+    return EXO_OK;
+}
+
+int exo_policy_f32_forward(ExoPolicyF32* p, const float* obs_dev, long long n, float max_action, float* actions_dev, float* zs_dev, void* stream) {
+    F32Args a;
+    a.obs = obs_dev; a.wt = p->wt; a.bias = p->bias; a.scratch = p->scratch; a.actions = actions_dev; a.zs = zs_dev;
+    a.n = n; a.max_action = max_action;
+    const long long tiles = (n + TM - 1) / TM;
+    if (tiles > 0x7FFFFFFF) return exo_set_error(EXO_ERR_ARG, "exo_policy_forward: too many observations");
+    a.n_tiles = (int)tiles;
+    const int grid = (int)(tiles < p->n_sm ? tiles : p->n_sm);
+    exo_policy_fp32_kernel<<<grid, NT, SMEM_BYTES, (cudaStream_t)stream>>>(a);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return exo_set_error(EXO_ERR_CUDA, "exo_policy_forward (fp32 path): %s", cudaGetErrorString(e));
+    return EXO_OK;
+}

@@ -70,7 +70,13 @@ class _Net(object):
 class DevicePolicy(object):
     """select_action's networks on one B200. `max_action` as Agent.max_action."""
 
-    def __init__(self, device="cuda:0", max_action=1.0):
+    def __init__(self, device="cuda:0", max_action=1.0, precision="tf32"):
+        """precision: "tf32" = the tensor-core kernel (TF32 products, float32 accumulation; torch's allow_tf32 arithmetic),
+        "fp32" = float32 products on the FP32 pipe (torch's default matmul; reproduces the reference's actions to
+        summation order, ~8x slower). forward(..., precision=...) overrides it per call."""
+        if precision not in ("tf32", "fp32"):
+            raise ValueError("precision must be 'tf32' or 'fp32'")
+        self.precision = precision
         self.lib = _capi.load()
         if not torch.cuda.is_available():
             raise _capi.ExoError("no CUDA device: the policy runs on B200 tensor cores (there is no CPU fallback)")
@@ -100,7 +106,7 @@ class DevicePolicy(object):
         self.set_networks(rd("_checkpoint_actor"), rd("_checkpoint_encoder"), "checkpoint")
 
     # ------------------------------------------------------------------ forward
-    def forward(self, obs, use_checkpoint=False, out=None, return_zs=False):
+    def forward(self, obs, use_checkpoint=False, out=None, return_zs=False, precision=None):
         """obs: float32 CUDA tensor [N,80] (e.g. BatchedExoskeletonEnv.step's obs). Returns actions [N,7] on the device,
         clip(actor(obs, zs), -1, 1) * max_action; with return_zs also encoder.zs(obs) [N,300]."""
         which = "checkpoint" if use_checkpoint else "current"
@@ -114,8 +120,9 @@ class DevicePolicy(object):
             out = torch.empty(n, ACTION_DIM, device=self.device, dtype=torch.float32)
         zs = torch.empty(n, HIDDEN_DIM, device=self.device, dtype=torch.float32) if return_zs else None
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
-        _capi.check(self.lib.exo_policy_forward(self._nets[which].h, C.c_void_p(obs.data_ptr()), n, self.max_action,
-                                                C.c_void_p(out.data_ptr()), C.c_void_p(zs.data_ptr()) if return_zs else None, stream))
+        fn = self.lib.exo_policy_forward if (precision or self.precision) == "tf32" else self.lib.exo_policy_forward_fp32
+        _capi.check(fn(self._nets[which].h, C.c_void_p(obs.data_ptr()), n, self.max_action,
+                    C.c_void_p(out.data_ptr()), C.c_void_p(zs.data_ptr()) if return_zs else None, stream))
         return (out, zs) if return_zs else out
 
     __call__ = forward

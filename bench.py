@@ -189,6 +189,18 @@ def bench_policy(exo_b200, env, dev, flush, peaks):
         evs.append((a, b))
     torch.cuda.synchronize(dev)
     fwd_ms = float(np.mean([a.elapsed_time(b) for a, b in evs[3:]]))
+    # the float32 path (FP32 pipe, the reference's own arithmetic), same call
+    evs32 = []
+    for _ in range(8):
+        if flush is not None:
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        pol.forward(obs, use_checkpoint=True, out=act, precision="fp32")
+        b.record()
+        evs32.append((a, b))
+    torch.cuda.synchronize(dev)
+    fp32_ms = float(np.mean([a.elapsed_time(b) for a, b in evs32[2:]]))
     # closed loop: the policy's actions drive the env (auto-reset on), no host copy anywhere
     steps = 60
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -207,6 +219,8 @@ def bench_policy(exo_b200, env, dev, flush, peaks):
            "roofline": {"bound": "tensor", "achieved": tf, "peak": bf16 / 2, "unit": "TFLOP/s", "frac": tf / (bf16 / 2),
                         "peak_source": ("MEASURED_PEAKS.json bf16_tflops / 2 (kind::tf32 = half the bf16 MMA rate)" if peaks else
                                         "fallback 2250 / 2")},
+           "fp32_path": {"kernel": "exo_policy_fp32_kernel", "forward_ms": fp32_ms, "observations_per_s": n / (fp32_ms * 1e-3),
+                         "tflops": n * POLICY_FLOP_PER_OBS / (fp32_ms * 1e-3) / 1e12, "dtype": "f32 products and sums (FP32 pipe)"},
            "closed_loop_env_steps_per_s": n / (loop_ms * 1e-3), "closed_loop_ms_per_step": loop_ms,
            "launches": pol.launch_count(), "weights": "shipped [1,1,1,1] checkpoint actor + encoder"}
     pol.close()

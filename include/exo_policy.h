@@ -59,6 +59,12 @@ int exo_policy_set_weights(ExoPolicy* p, const ExoPolicyWeights* w, int32_t stat
 int exo_policy_forward(ExoPolicy* p, const float* obs_dev, int64_t n, float max_action, float* actions_dev, float* zs_dev,
                        void* stream);
 
+/* The same forward pass in the reference's own arithmetic - float32 products and sums on the FP32 pipe, as torch's
+ * default matmul (csrc/exo_policy_fp32.cu) - for runs that must reproduce the reference's actions to summation order.
+ * About 8x slower than the tensor-core kernel. Same arguments as exo_policy_forward. */
+int exo_policy_forward_fp32(ExoPolicy* p, const float* obs_dev, int64_t n, float max_action, float* actions_dev, float* zs_dev,
+                            void* stream);
+
 /* One forward pass (max_action 1) that also records the SM clock (clock64) of CTA 0's first tile; synchronises.
  * clocks_host[32]: [2*g], [2*g+1] = MMA issuer starts / has issued GEMM phase g (0..7: l0, zs1, zs2, zs3, l1-zs half,
  * l1-a0 half, l2, l3); [16+2*k], [17+2*k] = epilogue k (0 = observation load, 1..7 after each accumulator) begins /

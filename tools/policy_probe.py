@@ -63,6 +63,8 @@ def main():
     res = {"n": n, "flop_per_obs": FLOP_PER_OBS}
     m, b = timeit(lambda: p.forward(obs, use_checkpoint=True, out=out), reps, flush)
     res["kernel_ms"] = m; res["kernel_ms_min"] = b; res["kernel_tflops"] = n * FLOP_PER_OBS / m / 1e9; res["kernel_obs_per_s"] = n / m * 1e3
+    m, b = timeit(lambda: p.forward(obs, use_checkpoint=True, out=out, precision="fp32"), max(3, reps // 3), flush)
+    res["fp32_path_ms"] = m; res["fp32_path_tflops"] = n * FLOP_PER_OBS / m / 1e9
     import ctypes as C
     clk = (C.c_int64 * 32)()
     exo_b200._capi.check(p.lib.exo_policy_profile(p._nets["checkpoint"].h, C.c_void_p(obs.data_ptr()), n, C.c_void_p(out.data_ptr()), clk,
