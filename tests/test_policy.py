@@ -205,3 +205,43 @@ def test_fp32_path_reproduces_the_reference_modules(exo, gold, PO):
     sa = q.select_action(gold["obs"][:16], use_checkpoint=True, use_exploration=False)
     assert np.array_equal(sa, act[:16])
     p.close(); q.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_config1_closed_loop_rollout_with_the_device_policy(exo, gold, precision):
+    """BASELINE config 1 end to end on the device: motion 0, type [1,1,1,1], seed 0, evaluation settings, 1000 steps over
+    4+ episodes, the shipped checkpoint actor evaluated by OUR policy kernel on the env's own observations (no teacher
+    forcing), against the reference's rollout (tests/golden/ref_cfg1_trained_actor.npz: reference env + reference torch
+    modules). fp32 path: the rollout tracks the reference's step for step (actions, observations, rewards). tf32 kernel:
+    the same policy up to its rounding, so the episode returns agree closely but not the individual steps."""
+    import torch
+    from conftest import case_settings
+    g = np.load(os.path.join(GOLDEN, "ref_cfg1_trained_actor.npz"))
+    env = exo.BatchedExoskeletonEnv([int(g["A0/meta_motion"])], [g["A0/meta_seq"]], [int(g["A0/meta_seed"])], precision="fp64",
+                                    auto_reset=True, **case_settings(g, "A0"))
+    p = exo.DevicePolicy("cuda:0", precision=precision)
+    sd = {k: gold[k] for k in gold.files if "." in k}
+    p.set_networks(sd, sd, "checkpoint")
+    obs = env.reset()
+    n = len(g["A0/action"])
+    acts, obss, rews = [], [], []
+    for t in range(n):
+        a = p.forward(obs.float(), use_checkpoint=True)
+        obs, rw, dn = env.step(a)
+        acts.append(a.clone()); obss.append(obs.clone()); rews.append(rw.clone())
+    torch.cuda.synchronize()
+    acts = torch.cat(acts).cpu().numpy(); obss = torch.cat(obss).float().cpu().numpy(); rews = torch.cat(rews).double().cpu().numpy()
+    done = g["A0/done"]
+    ea = np.abs(acts - g["A0/action"])
+    eo = np.abs(obss - g["A0/obs"])[~done]                   # at done the returned obs is the next episode's first one
+    ret, ret_ref = rews.sum(), g["A0/reward"].sum()
+    print("cfg1 closed loop (%s): action max %.2e p99 %.2e | obs max %.2e | return %.4f vs %.4f" %
+          (precision, ea.max(), np.percentile(ea, 99), eo.max(), ret, ret_ref))
+    if precision == "fp32":
+        # measured on B200: action max 1.2e-5, obs max 6.3e-6, return 542.7521 vs 542.7521
+        assert ea.max() <= 1e-4 and eo.max() <= 5e-5 and abs(ret - ret_ref) <= 1e-5 * abs(ret_ref)
+    else:
+        # measured: action max 2.9e-2 / p99 3.9e-3, obs max 1.5e-2, return 542.7361 vs 542.7521
+        assert ea.max() <= 6e-2 and np.percentile(ea, 99) <= 1e-2 and abs(ret - ret_ref) <= 1e-3 * abs(ret_ref)
+    env.close(); p.close()
