@@ -4,11 +4,12 @@
 //
 //   encoder.zs + actor of Agent/TD7_multi_agent_Pink_noise.py:59-105 as select_action evaluates them (:208-228).
 //
-// One fused kernel, 64 observations per CTA tile, 256 threads: warp w owns rows 8w..8w+7 of the tile, lane l the columns
-// l, l+32, ..., l+288 (80 accumulators per thread). Activations ping-pong between two 64 x 304 shared-memory buffers;
+// One fused kernel, 64 observations per CTA tile, 512 threads: warp w owns rows 8(w&7)..8(w&7)+7 of the tile and the column
+// half w>>3 (0..159 / 160..319), lane l the columns l, l+32, ..., l+128 of that half (40 accumulators per thread; four warps
+// per scheduler - the first version, 8 warps with 80 accumulators each, left the FMA pipe at 47 %). Activations ping-pong between two 64 x 304 shared-memory buffers;
 // every layer streams its weights (host-transposed to [K][320], zero padded) from L2 in 16-row chunks through a
 // cp.async double buffer. cat[a0, zs] * l1' is two accumulating passes; a0 waits in an L2-resident per-CTA scratch.
-// FP32-pipe bound: 12 shared-memory loads per 80 FFMA in the inner loop.
+// FP32-pipe bound: 7 shared-memory loads per 40 FFMA in the inner loop.
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string.h>
@@ -25,7 +26,7 @@ namespace {
 constexpr int SD = EXO_POLICY_STATE_DIM, HD = EXO_POLICY_HIDDEN_DIM, AD = EXO_POLICY_ACTION_DIM;
 constexpr int HP = 304;          // activation row pitch / K of a hidden layer (300 padded to a multiple of the 16-row chunk)
 constexpr int WP = 320;          // weight row pitch: 10 columns per lane
-constexpr int TM = 64, KC = 16, NT = 256, NC = WP / 32;
+constexpr int TM = 64, KC = 16, NT = 512, NC = WP / 64, HALF = WP / 2;
 constexpr int BUF_FLOATS = TM * HP;
 constexpr int SMEM_BYTES = (2 * BUF_FLOATS + 2 * KC * WP) * 4;      // 196 608
 
@@ -50,9 +51,10 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-// acc[r][c] += sum_k X[8*warp + r][k] * WT[k][lane + 32 c], k < K (a multiple of 16). All 256 threads.
+// acc[r][c] += sum_k X[8*rg + r][k] * WT[k][col0 + 32 c], k < K (a multiple of 16); rg = warp & 7, col0 = (warp >> 3)*160 + lane.
 __device__ __forceinline__ void gemm_acc(float (&acc)[8][NC], const float* __restrict__ X, const float* __restrict__ wt, int K, float* ws,
                                          int warp, int lane, int tid) {
+    const int rg = warp & 7, col0 = (warp >> 3) * HALF + lane;
     const int nchunk = K / KC;
     auto load_chunk = [&](int c, int buf) {
         const float4* src = reinterpret_cast<const float4*>(wt + (size_t)c * KC * WP);
@@ -65,8 +67,8 @@ __device__ __forceinline__ void gemm_acc(float (&acc)[8][NC], const float* __res
         cp_async_wait_all();
         __syncthreads();                           // chunk c has landed for everyone; chunk c-1's buffer is free
         if (c + 1 < nchunk) load_chunk(c + 1, (c + 1) & 1);
-        const float* w = ws + (c & 1) * KC * WP + lane;
-        const float* x = X + (size_t)(warp * 8) * HP + c * KC;
+        const float* w = ws + (c & 1) * KC * WP + col0;
+        const float* x = X + (size_t)(rg * 8) * HP + c * KC;
 #pragma unroll
         for (int k4 = 0; k4 < KC; k4 += 4) {
             float4 xv[8];
@@ -100,32 +102,46 @@ __device__ __forceinline__ void zero_acc(float (&acc)[8][NC]) {
 // (columns >= 304 are dropped; 300..303 are exactly 0: zero weights and bias).
 template <int ACT>
 __device__ __forceinline__ void store_act(float (&acc)[8][NC], const float* __restrict__ bias, float* dst, int pitch, int warp, int lane,
-                                          float* zs_out, long long row0, long long n) {
+                                          float* zs_out, long long row0, long long n, float* part /* smem [2][TM] */) {
+    const int rg = warp & 7, half = warp >> 3, col0 = half * HALF + lane;
     float b[NC];
 #pragma unroll
-    for (int c = 0; c < NC; ++c) b[c] = __ldg(bias + lane + 32 * c);
+    for (int c = 0; c < NC; ++c) b[c] = __ldg(bias + col0 + 32 * c);
+    float tot[8];
+    if (ACT == 2) {                                  // row sums of |x|: this warp's half, then the other half's through shared memory
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            float s = 0.f;
+#pragma unroll
+            for (int c = 0; c < NC; ++c) s += fabsf(acc[r][c] + b[c]);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            tot[r] = s;
+            if (lane == 0) part[half * TM + rg * 8 + r] = s;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < 8; ++r) tot[r] += part[(half ^ 1) * TM + rg * 8 + r];
+        __syncthreads();
+    }
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         float v[NC];
-        float s = 0.f;
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
             v[c] = acc[r][c] + b[c];
             if (ACT == 0) v[c] = v[c] > 0.f ? v[c] : expm1f(v[c]);
             if (ACT == 1) v[c] = fmaxf(v[c], 0.f);
-            if (ACT == 2) s += fabsf(v[c]);
         }
         if (ACT == 2) {
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            const float denom = fmaxf(s / (float)HD, 1e-8f);
+            const float denom = fmaxf(tot[r] / (float)HD, 1e-8f);
 #pragma unroll
             for (int c = 0; c < NC; ++c) v[c] = v[c] / denom;
         }
-        const int row = warp * 8 + r;
+        const int row = rg * 8 + r;
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
-            const int col = lane + 32 * c;
+            const int col = col0 + 32 * c;
             if (col < HP) dst[(size_t)row * pitch + col] = v[c];
             if (ACT == 2 && zs_out && col < HD && row0 + row < n) zs_out[(row0 + row) * HD + col] = v[c];
         }
@@ -137,6 +153,7 @@ __global__ void __launch_bounds__(NT, 1) exo_policy_fp32_kernel(const F32Args a)
     float* bufA = sm;
     float* bufB = sm + BUF_FLOATS;
     float* ws = sm + 2 * BUF_FLOATS;
+    __shared__ float part[2 * TM];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     float* scratch = a.scratch + (size_t)blockIdx.x * BUF_FLOATS;
     float acc[8][NC];
@@ -153,19 +170,19 @@ __global__ void __launch_bounds__(NT, 1) exo_policy_fp32_kernel(const F32Args a)
         // a0 = AvgL1Norm(l0(obs)) -> scratch
         zero_acc(acc);
         gemm_acc(acc, bufA, a.wt + OFF_L0, K_OBS, ws, warp, lane, tid);
-        store_act<2>(acc, a.bias + B_L0, scratch, HP, warp, lane, nullptr, row0, a.n);
+        store_act<2>(acc, a.bias + B_L0, scratch, HP, warp, lane, nullptr, row0, a.n, part);
         // zs = AvgL1Norm(zs3(elu(zs2(elu(zs1(obs))))))
         zero_acc(acc);
         gemm_acc(acc, bufA, a.wt + OFF_ZS1, K_OBS, ws, warp, lane, tid);
-        store_act<0>(acc, a.bias + B_ZS1, bufB, HP, warp, lane, nullptr, row0, a.n);
+        store_act<0>(acc, a.bias + B_ZS1, bufB, HP, warp, lane, nullptr, row0, a.n, part);
         __syncthreads();
         zero_acc(acc);
         gemm_acc(acc, bufB, a.wt + OFF_ZS2, K_HID, ws, warp, lane, tid);
-        store_act<0>(acc, a.bias + B_ZS2, bufA, HP, warp, lane, nullptr, row0, a.n);
+        store_act<0>(acc, a.bias + B_ZS2, bufA, HP, warp, lane, nullptr, row0, a.n, part);
         __syncthreads();
         zero_acc(acc);
         gemm_acc(acc, bufA, a.wt + OFF_ZS3, K_HID, ws, warp, lane, tid);
-        store_act<2>(acc, a.bias + B_ZS3, bufB, HP, warp, lane, a.zs, row0, a.n);
+        store_act<2>(acc, a.bias + B_ZS3, bufB, HP, warp, lane, a.zs, row0, a.n, part);
         __syncthreads();
         // l1(cat[a0, zs]) = l1[:, 300:600] zs + l1[:, 0:300] a0 + b: the zs half first, a0 comes back from the scratch meanwhile
         for (int i = tid; i < BUF_FLOATS / 4; i += NT)
@@ -173,17 +190,17 @@ __global__ void __launch_bounds__(NT, 1) exo_policy_fp32_kernel(const F32Args a)
         zero_acc(acc);
         gemm_acc(acc, bufB, a.wt + OFF_L1B, K_HID, ws, warp, lane, tid);
         gemm_acc(acc, bufA, a.wt + OFF_L1A, K_HID, ws, warp, lane, tid);
-        store_act<1>(acc, a.bias + B_L1, bufB, HP, warp, lane, nullptr, row0, a.n);
+        store_act<1>(acc, a.bias + B_L1, bufB, HP, warp, lane, nullptr, row0, a.n, part);
         __syncthreads();
         zero_acc(acc);
         gemm_acc(acc, bufB, a.wt + OFF_L2, K_HID, ws, warp, lane, tid);
-        store_act<1>(acc, a.bias + B_L2, bufA, HP, warp, lane, nullptr, row0, a.n);
+        store_act<1>(acc, a.bias + B_L2, bufA, HP, warp, lane, nullptr, row0, a.n, part);
         __syncthreads();
-        // l3 + tanh + clip: warp w, rows 8w..8w+7; lane l sums k = l, l+32, ...
+        // l3 + tanh + clip: warp w, rows 4w..4w+3; lane l sums k = l, l+32, ...
         const float* w3 = a.wt + OFF_L3;
 #pragma unroll 1
-        for (int r = 0; r < 8; ++r) {
-            const int row = warp * 8 + r;
+        for (int r = 0; r < TM / (NT / 32); ++r) {
+            const int row = warp * (TM / (NT / 32)) + r;
             float s[AD];
 #pragma unroll
             for (int j = 0; j < AD; ++j) s[j] = 0.f;
