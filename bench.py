@@ -212,6 +212,22 @@ def bench_policy(exo_b200, env, dev, flush, peaks):
     b.record()
     torch.cuda.synchronize(dev)
     loop_ms = a.elapsed_time(b) / steps
+    # the acting side of the training loop (Exoskeleton_agent_train.py:123-147), all on the device:
+    # select_action -> env.step -> replay_buffer.add, for every env, per step
+    buf = exo_b200.LAP(80, 7, dev, 8, max_size=250000, batch_size=128)
+    prev = obs
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    a.record()
+    for _ in range(steps):
+        pol.forward(prev, use_checkpoint=True, out=act)
+        obs, rew, done = env.step(act)
+        buf.add_batch(prev, act, obs, rew, done)
+        prev = obs
+    b.record()
+    torch.cuda.synchronize(dev)
+    act_ms = a.elapsed_time(b) / steps
+    buf.close()
     tf = n * POLICY_FLOP_PER_OBS / (fwd_ms * 1e-3) / 1e12
     bf16 = float(peaks.get("bf16_tflops", 2250.0))
     out = {"kernel": "exo_policy_kernel", "observations": n, "forward_ms": fwd_ms, "observations_per_s": n / (fwd_ms * 1e-3),
@@ -222,6 +238,8 @@ def bench_policy(exo_b200, env, dev, flush, peaks):
            "fp32_path": {"kernel": "exo_policy_fp32_kernel", "forward_ms": fp32_ms, "observations_per_s": n / (fp32_ms * 1e-3),
                          "tflops": n * POLICY_FLOP_PER_OBS / (fp32_ms * 1e-3) / 1e12, "dtype": "f32 products and sums (FP32 pipe)"},
            "closed_loop_env_steps_per_s": n / (loop_ms * 1e-3), "closed_loop_ms_per_step": loop_ms,
+           "acting_loop_env_steps_per_s": n / (act_ms * 1e-3), "acting_loop_ms_per_step": act_ms,
+           "acting_loop": "policy.forward -> env.step -> LAP.add_batch per step, device resident, no host copy",
            "launches": pol.launch_count(), "weights": "shipped [1,1,1,1] checkpoint actor + encoder"}
     pol.close()
     return out
