@@ -4,6 +4,7 @@ The importable alias of this package is `exo_b200` (the directory name carries h
 from ._capi import ExoError, load as load_library  # noqa: F401
 from .lap import LAP  # noqa: F401
 from .policy import DevicePolicy, load_reference_policy  # noqa: F401
+from .td7 import DeviceTD7, Hyperparameters  # noqa: F401
 from .env import BatchedExoskeletonEnv, ExoskeletonEnv_train, INFO_KEYS, REWARD_KEYS, STAT_NAMES  # noqa: F401
 
-__all__ = ["LAP", "DevicePolicy", "load_reference_policy", "BatchedExoskeletonEnv", "ExoskeletonEnv_train", "ExoError", "load_library", "INFO_KEYS", "REWARD_KEYS", "STAT_NAMES"]
+__all__ = ["LAP", "DevicePolicy", "load_reference_policy", "DeviceTD7", "Hyperparameters", "BatchedExoskeletonEnv", "ExoskeletonEnv_train", "ExoError", "load_library", "INFO_KEYS", "REWARD_KEYS", "STAT_NAMES"]

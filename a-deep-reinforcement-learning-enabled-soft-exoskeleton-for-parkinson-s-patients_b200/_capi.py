@@ -36,6 +36,15 @@ class ExoPolicyWeights(C.Structure):
     _fields_ = [(n + s, C.POINTER(C.c_float)) for n in NAMES for s in ("_w", "_b")]
 
 
+class ExoTD7Config(C.Structure):
+    """include/exo_td7.h: Hyperparameters + network sizes of the TD7 learner."""
+    _fields_ = [(k, C.c_int32) for k in ("state_dim", "action_dim", "zs_dim", "enc_hdim", "critic_hdim", "actor_hdim", "batch_rows",
+                                         "target_update_rate", "policy_freq")] + \
+               [(k, C.c_float) for k in ("discount", "target_policy_noise", "noise_clip", "policy_noise_decrease", "alpha",
+                                         "min_priority", "actor_lr", "critic_lr", "encoder_lr", "weight_decay")] + \
+               [("seed", C.c_uint64)]
+
+
 class ExoInfo(C.Structure):
     _fields_ = [(k, C.c_void_p) for k in ("actuator_torques", "torque_val", "ampl_val", "tremor_torque_val",
                                           "tremor_ampl_val", "reward_parts", "amp_metric")]
@@ -90,6 +99,19 @@ SIGNATURES = {
     "exo_policy_forward_fp32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
     "exo_policy_profile": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(C.c_int64), C.c_void_p]),
     "exo_policy_launch_count": (C.c_int64, [C.c_void_p]),
+    # include/exo_td7.h
+    "exo_td7_create": (C.c_int, [C.c_int32, C.POINTER(ExoTD7Config), C.POINTER(C.c_void_p)]),
+    "exo_td7_destroy": (C.c_int, [C.c_void_p]),
+    "exo_td7_net_size": (C.c_int64, [C.c_void_p, C.c_int32]),
+    "exo_td7_set_net": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64]),
+    "exo_td7_get_net": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64]),
+    "exo_td7_copy_net": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
+    "exo_td7_set_opt": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_int64]),
+    "exo_td7_get_opt": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
+    "exo_td7_train": (C.c_int, [C.c_void_p] + [C.c_void_p] * 7 + [C.POINTER(C.c_int32), C.c_void_p]),
+    "exo_td7_scalars": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
+    "exo_td7_set_scalars": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
+    "exo_td7_launch_count": (C.c_int64, [C.c_void_p]),
 }
 
 _lib = None

@@ -1,0 +1,756 @@
+// exo_td7.cu — the TD7 update of include/exo_td7.h: one Agent.train() iteration (Agent/TD7_multi_agent_Pink_noise.py
+// :230-312) with every network, gradient and Adam state resident in HBM.
+//
+// Building blocks (float32 on the FP32 pipe, the reference's arithmetic):
+//   sgemm_kernel<TA,TB>   C = op(A) op(B) on 64 x 64 x 16 tiles, 256 threads, 4 x 4 accumulators per thread, the next
+//                         k-tile prefetched into registers while the current one is multiplied. One kernel serves
+//                           forward      Y  = act(X W^T + b)                      (TA=0, TB=1, bias + activation epilogue)
+//                           input grad   dX = (dY W[:, c0:c1]) * act'(saved out)  (TA=0, TB=0, derivative epilogue)
+//                           weight grad  dW += dY^T X                             (TA=1, TB=0, split over the batch,
+//                                                                                  atomicAdd epilogue)
+//                         torch.cat is never materialised for outputs: producers write into column slices (ld*).
+//   row kernels           AvgL1Norm forward / backward (one warp per row), column sums (bias gradients), the loss
+//                         heads (mse, LAP_huber + priorities, target value with clipping and the running max / min).
+//   adam_kernel           torch.optim.Adam over a network's flat parameter vector (one launch per optimiser).
+// The orchestration (exo_td7_train) is a fixed launch sequence on the caller's stream; nothing synchronises.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+#include <algorithm>
+#include <initializer_list>
+#include <utility>
+#include <vector>
+
+#include "../../include/exo_env.h"
+#include "../../include/exo_td7.h"
+
+int exo_set_error(int code, const char* fmt, ...);     // exo_api.cu
+
+namespace {
+
+enum { ACT_NONE = 0, ACT_RELU = 1, ACT_ELU = 2, ACT_TANH = 3 };
+enum { OUT_STORE = 0, OUT_ADD = 1, OUT_ATOMIC = 2 };
+
+struct GemmArgs {
+    const float* A; int lda;
+    const float* B; int ldb;
+    float* C; int ldc;
+    int M, N, K, kchunk;
+    const float* bias; int act;          // forward epilogue
+    const float* D; int ldd; int dact;   // backward epilogue: multiply by act'(D(m,n)), D = the saved forward OUTPUT
+    int out;
+};
+
+__device__ __forceinline__ float act_fwd(float v, int act) {
+    if (act == ACT_RELU) return fmaxf(v, 0.f);
+    if (act == ACT_ELU) return v > 0.f ? v : expm1f(v);
+    if (act == ACT_TANH) return tanhf(v);
+    return v;
+}
+__device__ __forceinline__ float act_bwd(float y, int act) {      // derivative from the output y
+    if (act == ACT_RELU) return y > 0.f ? 1.f : 0.f;
+    if (act == ACT_ELU) return y > 0.f ? 1.f : y + 1.f;
+    if (act == ACT_TANH) return 1.f - y * y;
+    return 1.f;
+}
+
+constexpr int TM = 64, TN = 64, TK = 16, PITCH = 68;
+
+template <bool TA, bool TB>
+__global__ void __launch_bounds__(256) sgemm_kernel(GemmArgs g) {
+    __shared__ __align__(16) float As[TK][PITCH];
+    __shared__ __align__(16) float Bs[TK][PITCH];
+    const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
+    const int m0 = blockIdx.y * TM, n0 = blockIdx.x * TN;
+    const int kbeg = blockIdx.z * g.kchunk;
+    const int kend = min(g.K, kbeg + g.kchunk);
+    // element (mm, kk) of the A tile / (kk, nn) of the B tile this thread moves, 4 each, laid out so that the global
+    // reads are contiguous along the operand's fast axis
+    int a_m[4], a_k[4], b_n[4], b_k[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (TA) { a_m[i] = t & 63; a_k[i] = (t >> 6) + 4 * i; } else { a_k[i] = t & 15; a_m[i] = (t >> 4) + 16 * i; }
+        if (TB) { b_k[i] = t & 15; b_n[i] = (t >> 4) + 16 * i; } else { b_n[i] = t & 63; b_k[i] = (t >> 6) + 4 * i; }
+    }
+    float ra[4], rb[4];
+    auto fetch = [&](int k0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int gm = m0 + a_m[i], gk = k0 + a_k[i];
+            ra[i] = (gm < g.M && gk < kend) ? (TA ? g.A[(size_t)gk * g.lda + gm] : g.A[(size_t)gm * g.lda + gk]) : 0.f;
+            const int gn = n0 + b_n[i], hk = k0 + b_k[i];
+            rb[i] = (gn < g.N && hk < kend) ? (TB ? g.B[(size_t)gn * g.ldb + hk] : g.B[(size_t)hk * g.ldb + gn]) : 0.f;
+        }
+    };
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    if (kbeg < kend) fetch(kbeg);
+    for (int k0 = kbeg; k0 < kend; k0 += TK) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { As[a_k[i]][a_m[i]] = ra[i]; Bs[b_k[i]][b_n[i]] = rb[i]; }
+        __syncthreads();
+        if (k0 + TK < kend) fetch(k0 + TK);
+#pragma unroll
+        for (int kk = 0; kk < TK; ++kk) {
+            const float4 a = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
+            const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int m = m0 + ty * 4 + i;
+        if (m >= g.M) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int n = n0 + tx * 4 + j;
+            if (n >= g.N) continue;
+            float v = acc[i][j];
+            if (g.bias) v += g.bias[n];
+            v = act_fwd(v, g.act);
+            if (g.D) v *= act_bwd(g.D[(size_t)m * g.ldd + n], g.dact);
+            float* c = g.C + (size_t)m * g.ldc + n;
+            if (g.out == OUT_STORE) *c = v;
+            else if (g.out == OUT_ADD) *c += v;
+            else atomicAdd(c, v);
+        }
+    }
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// y = x / max(mean|x|, 1e-8) per row (:59-60); one warp per row
+__global__ void avgl1_fwd_kernel(const float* x, int ldx, float* y, int ldy, int rows, int n) {
+    const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (r >= rows) return;
+    const float* xr = x + (size_t)r * ldx;
+    float s = 0.f;
+    for (int c = lane; c < n; c += 32) s += fabsf(xr[c]);
+    const float d = fmaxf(warp_sum(s) / (float)n, 1e-8f);
+    float* yr = y + (size_t)r * ldy;
+    for (int c = lane; c < n; c += 32) yr[c] = xr[c] / d;
+}
+
+// dx = dy / d - sign(x) (sum dy x) / (n d^2), the second term only where mean|x| >= 1e-8 (clamp's gradient)
+__global__ void avgl1_bwd_kernel(const float* dy, int lddy, const float* x, int ldx, float* dx, int lddx, int rows, int n) {
+    const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (r >= rows) return;
+    const float* xr = x + (size_t)r * ldx;
+    const float* gr = dy + (size_t)r * lddy;
+    float s = 0.f, p = 0.f;
+    for (int c = lane; c < n; c += 32) { s += fabsf(xr[c]); p += gr[c] * xr[c]; }
+    const float m = warp_sum(s) / (float)n;
+    p = warp_sum(p);
+    const float d = fmaxf(m, 1e-8f);
+    const float k = m >= 1e-8f ? p / ((float)n * d * d) : 0.f;
+    float* o = dx + (size_t)r * lddx;
+    for (int c = lane; c < n; c += 32) {
+        const float xv = xr[c];
+        const float sg = xv > 0.f ? 1.f : (xv < 0.f ? -1.f : 0.f);
+        o[c] = gr[c] / d - sg * k;
+    }
+}
+
+__global__ void copy_cols_kernel(float* dst, int ldd, const float* src, int lds, int rows, int cols) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)rows * cols) return;
+    const int r = (int)(i / cols), c = (int)(i % cols);
+    dst[(size_t)r * ldd + c] = src[(size_t)r * lds + c];
+}
+
+// gb[n] += sum_rows dy[r, n]: block = 32 columns x 8 row lanes
+__global__ void colsum_kernel(const float* dy, int ld, float* gb, int rows, int n) {
+    __shared__ float part[8][33];
+    const int c = blockIdx.x * 32 + threadIdx.x;
+    float s = 0.f;
+    if (c < n)
+        for (int r = threadIdx.y; r < rows; r += 8) s += dy[(size_t)r * ld + c];
+    part[threadIdx.y][threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < n) {
+        for (int k = 1; k < 8; ++k) s += part[k][threadIdx.x];
+        gb[c] += s;
+    }
+}
+
+// device scalars of the learner
+enum { SC_MAX = 0, SC_MIN, SC_MAX_TARGET, SC_MIN_TARGET, SC_ENC_LOSS, SC_CRITIC_LOSS, SC_ACTOR_LOSS, SC_COUNT };
+
+__device__ __forceinline__ float block_sum(float v, float* sh) {
+    v = warp_sum(v);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float r = 0.f;
+    if (threadIdx.x < 32) {
+        r = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.f;
+        r = warp_sum(r);
+    }
+    __syncthreads();
+    return r;       // valid in warp 0
+}
+
+// F.mse_loss(pred, next_zs) (:243): d = 2 (pred - next) / count, loss accumulated into sc[SC_ENC_LOSS]
+__global__ void mse_grad_kernel(const float* pred, const float* next, float* d, size_t count, float* sc) {
+    __shared__ float sh[32];
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    float e = 0.f;
+    if (i < count) {
+        e = pred[i] - next[i];
+        d[i] = e * (2.0f / (float)count);
+    }
+    const float s = block_sum(e * e, sh);
+    if (threadIdx.x == 0) atomicAdd(&sc[SC_ENC_LOSS], s / (float)count);
+}
+
+// next_action = (actor_target(...) + (randn * sigma).clamp(-clip, clip)).clamp(-1, 1)   (:254-256)
+__global__ void target_action_kernel(float* na, const float* randn, int count, float sigma, float clip) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const float nz = fminf(fmaxf(randn[i] * sigma, -clip), clip);
+    na[i] = fminf(fmaxf(na[i] + nz, -1.f), 1.f);
+}
+
+// Q_target = reward + not_done * discount * min_h(Q_h).clamp(min_target, max_target); running max / min (:260-264).
+// One block: the running extrema are updated without atomics.
+__global__ void q_target_kernel(const float* q2, const float* reward, const float* not_done, float* qt, int rows, float discount, float* sc) {
+    __shared__ float smax[32], smin[32];
+    const float lo = sc[SC_MIN_TARGET], hi = sc[SC_MAX_TARGET];
+    float mx = -INFINITY, mn = INFINITY;
+    for (int b = threadIdx.x; b < rows; b += blockDim.x) {
+        float q = fminf(q2[2 * b], q2[2 * b + 1]);
+        q = fminf(fmaxf(q, lo), hi);
+        const float v = reward[b] + not_done[b] * discount * q;
+        qt[b] = v;
+        mx = fmaxf(mx, v); mn = fminf(mn, v);
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) { mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o)); mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o)); }
+    if ((threadIdx.x & 31) == 0) { smax[threadIdx.x >> 5] = mx; smin[threadIdx.x >> 5] = mn; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { mx = fmaxf(mx, smax[w]); mn = fminf(mn, smin[w]); }
+        sc[SC_MAX] = fmaxf(sc[SC_MAX], mx);
+        sc[SC_MIN] = fminf(sc[SC_MIN], mn);
+    }
+}
+
+// td = |Q - Q_target|; LAP_huber (:63-64) and its gradient; priority = max_h td .clamp(min_priority) ** alpha (:281)
+__global__ void td_head_kernel(const float* q2, const float* qt, float* dq, float* prio, int rows, float min_priority, float alpha, float* sc) {
+    __shared__ float sh[32];
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    float loss = 0.f;
+    if (b < rows) {
+        float tmax = 0.f;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const float d = q2[2 * b + h] - qt[b];
+            const float td = fabsf(d);
+            const float sg = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
+            loss += td < min_priority ? 0.5f * td * td : min_priority * td;
+            dq[2 * b + h] = (td < min_priority ? td : min_priority) * sg / (float)rows;
+            tmax = fmaxf(tmax, td);
+        }
+        prio[b] = powf(fmaxf(tmax, min_priority), alpha);
+    }
+    const float s = block_sum(loss, sh);
+    if (threadIdx.x == 0) atomicAdd(&sc[SC_CRITIC_LOSS], s / (float)rows);
+}
+
+// actor_loss = -Q.mean() over [rows, 2] (:291): dQ = -1 / (2 rows)
+__global__ void actor_head_kernel(const float* q2, float* dq, int rows, float* sc) {
+    __shared__ float sh[32];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    float q = 0.f;
+    if (i < 2 * rows) { q = q2[i]; dq[i] = -1.0f / (float)(2 * rows); }
+    const float s = block_sum(q, sh);
+    if (threadIdx.x == 0) atomicAdd(&sc[SC_ACTOR_LOSS], -s / (float)(2 * rows));
+}
+
+// d = (da + db) * (1 - act^2): the two gradient paths into the actor's tanh output
+__global__ void tanh_bwd_kernel(float* d, const float* da, const float* db, const float* act, int count) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const float y = act[i];
+    d[i] = (da[i] + db[i]) * (1.f - y * y);
+}
+
+// torch.optim.Adam, single-tensor arithmetic: g += wd p; m.lerp_(g, 1-b1); v = b2 v + (1-b2) g g;
+// p -= (lr / bc1) * m / (sqrt(v) / sqrt(bc2) + eps)
+__global__ void adam_kernel(float* p, const float* g, float* m, float* v, size_t n, float wd, float step_size, float bc2_sqrt) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float b1 = 0.9f, b2 = 0.999f, eps = 1e-8f;
+    const float pv = p[i];
+    const float gv = g[i] + wd * pv;
+    const float mv = m[i] + (gv - m[i]) * (1.f - b1);
+    const float vv = v[i] * b2 + gv * gv * (1.f - b2);
+    m[i] = mv; v[i] = vv;
+    const float denom = sqrtf(vv) / bc2_sqrt + eps;
+    p[i] = pv - step_size * (mv / denom);
+}
+
+// standard normals for the target-policy noise when the caller passes none: splitmix64 counter hash + Box-Muller
+__global__ void randn_kernel(float* out, int count, uint64_t seed, uint64_t step) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    uint64_t z = seed + 0x9E3779B97F4A7C15ull * (step * 0x100000000ull + (uint64_t)i + 1);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    const float u1 = ((float)(uint32_t)(z >> 40) + 1.0f) * (1.0f / 16777216.0f);      // (0, 1]
+    const float u2 = (float)(uint32_t)((z >> 8) & 0xFFFFFF) * (1.0f / 16777216.0f);
+    out[i] = sqrtf(-2.f * logf(u1)) * cospif(2.f * u2);
+}
+
+struct Lin { int out, in; size_t w, b; };
+struct NetDef { std::vector<Lin> L; size_t size = 0; };
+
+NetDef make_def(std::initializer_list<std::pair<int, int>> layers) {
+    NetDef d;
+    for (auto& l : layers) {
+        Lin x;
+        x.out = l.first; x.in = l.second;
+        x.w = d.size; d.size += (size_t)x.out * x.in;
+        x.b = d.size; d.size += (size_t)x.out;
+        d.L.push_back(x);
+    }
+    return d;
+}
+
+inline int kind_of(int net) { return net <= EXO_TD7_CHECKPOINT_ACTOR ? 0 : (net <= EXO_TD7_CRITIC_TARGET ? 1 : 2); }
+const int OPT_NET[3] = {EXO_TD7_ACTOR, EXO_TD7_CRITIC, EXO_TD7_ENCODER};
+
+}  // namespace
+
+struct ExoTD7 {
+    int device = 0, n_sm = 148;
+    ExoTD7Config c;
+    int64_t launches = 0, steps = 0;
+    double sigma = 0;                       // hp.target_policy_noise, decays by policy_noise_decrease per iteration
+    NetDef def[3];                          // actor, critic, encoder
+    float* net[EXO_TD7_N_NETS] = {};
+    float *grad[3] = {}, *m[3] = {}, *v[3] = {};
+    int64_t opt_step[3] = {0, 0, 0};
+    float* sc = nullptr;
+    std::vector<float*> owned;
+    // activations ([batch_rows, *])
+    float *t_h1, *t_h2, *t_z3, *next_zs;                       // no-grad encoder passes
+    float *e_h1, *e_h2, *e_z3, *e_cat, *e_g1, *e_g2, *e_pred;  // encoder update
+    float *tzs, *t_cat, *tzsa, *na, *rn;                       // target
+    float *a_u, *a_cat, *a_h1, *a_h2, *act;                    // actor (target pass, then the actor update's cache)
+    float *fzs, *f_cat, *f_g1, *f_g2, *fzsa;                   // fixed encoder
+    float *c_sa, *c_u[2], *c_cat[2], *c_h1[2], *c_h2[2], *q2, *qt, *dq;   // critic
+    float *dA, *dB, *d_zsa, *d_act1, *d_act2, *dT;             // gradients in flight
+};
+
+namespace {
+
+struct Ctx {
+    ExoTD7* t;
+    cudaStream_t s;
+    int B;
+
+    void gemm(bool ta, bool tb, GemmArgs g, int splits) {
+        if (g.M <= 0 || g.N <= 0 || g.K <= 0) return;
+        g.kchunk = splits <= 1 ? g.K : (((g.K + splits - 1) / splits + TK - 1) / TK) * TK;
+        dim3 grid((g.N + TN - 1) / TN, (g.M + TM - 1) / TM, (g.K + g.kchunk - 1) / g.kchunk);
+        if (!ta && tb) sgemm_kernel<false, true><<<grid, 256, 0, s>>>(g);
+        else if (!ta && !tb) sgemm_kernel<false, false><<<grid, 256, 0, s>>>(g);
+        else sgemm_kernel<true, false><<<grid, 256, 0, s>>>(g);
+        t->launches++;
+    }
+    // Y = act(X W^T + b)
+    void fwd(const float* net, const Lin& L, const float* X, int ldx, float* Y, int ldy, int act) {
+        GemmArgs g = {};
+        g.A = X; g.lda = ldx; g.B = net + L.w; g.ldb = L.in; g.C = Y; g.ldc = ldy;
+        g.M = B; g.N = L.out; g.K = L.in; g.bias = net + L.b; g.act = act; g.out = OUT_STORE;
+        gemm(false, true, g, 1);
+    }
+    // dX[:, 0:nc] (=|+=) dY W[:, c0:c0+nc] (* act'(D))
+    void dx(const float* net, const Lin& L, const float* dY, int lddy, float* dX, int lddx, int c0, int nc,
+            const float* D, int ldd, int dact, int out = OUT_STORE) {
+        GemmArgs g = {};
+        g.A = dY; g.lda = lddy; g.B = net + L.w + c0; g.ldb = L.in; g.C = dX; g.ldc = lddx;
+        g.M = B; g.N = nc; g.K = L.out; g.D = D; g.ldd = ldd; g.dact = dact; g.out = out;
+        gemm(false, false, g, 1);
+    }
+    // gW += dY^T X, gb += colsum(dY)   (the gradient vector was zeroed at the start of the backward pass)
+    void dw(float* grad, const Lin& L, const float* dY, int lddy, const float* X, int ldx) {
+        GemmArgs g = {};
+        g.A = dY; g.lda = lddy; g.B = X; g.ldb = ldx; g.C = grad + L.w; g.ldc = L.in;
+        g.M = L.out; g.N = L.in; g.K = B; g.out = OUT_ATOMIC;
+        const int tiles = ((L.out + TM - 1) / TM) * ((L.in + TN - 1) / TN);
+        int splits = (2 * t->n_sm + tiles - 1) / tiles;
+        splits = std::max(1, std::min(splits, (B + 63) / 64));
+        gemm(true, false, g, splits);
+        colsum_kernel<<<(L.out + 31) / 32, dim3(32, 8), 0, s>>>(dY, lddy, grad + L.b, B, L.out);
+        t->launches++;
+    }
+    void avgl1(const float* x, int ldx, float* y, int ldy, int n) {
+        avgl1_fwd_kernel<<<(B + 7) / 8, 256, 0, s>>>(x, ldx, y, ldy, B, n);
+        t->launches++;
+    }
+    void avgl1_bwd(const float* dy, int lddy, const float* x, int ldx, float* dxp, int lddx, int n) {
+        avgl1_bwd_kernel<<<(B + 7) / 8, 256, 0, s>>>(dy, lddy, x, ldx, dxp, lddx, B, n);
+        t->launches++;
+    }
+    void copy(float* dst, int ldd, const float* src, int lds, int cols) {
+        const size_t n = (size_t)B * cols;
+        copy_cols_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(dst, ldd, src, lds, B, cols);
+        t->launches++;
+    }
+    void adam(int opt, float lr) {
+        const int net = OPT_NET[opt];
+        const size_t n = t->def[kind_of(net)].size;
+        const int64_t k = ++t->opt_step[opt];
+        const double bc1 = 1.0 - pow(0.9, (double)k), bc2 = 1.0 - pow(0.999, (double)k);
+        adam_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(t->net[net], t->grad[opt], t->m[opt], t->v[opt], n, t->c.weight_decay,
+                                                                (float)((double)lr / bc1), (float)sqrt(bc2));
+        t->launches++;
+    }
+    void zero_grad(int opt) { cudaMemsetAsync(t->grad[opt], 0, t->def[kind_of(OPT_NET[opt])].size * sizeof(float), s); }
+
+    // Encoder.zs (:101-105) -> zs (column slice allowed); caches h1, h2 (post-ELU) and z3 (pre-norm)
+    void enc_zs(const float* net, const float* X, float* zs, int ldzs, float* h1, float* h2, float* z3) {
+        const NetDef& d = t->def[2];
+        const int S = t->c.state_dim, H = t->c.enc_hdim, Z = t->c.zs_dim;
+        fwd(net, d.L[0], X, S, h1, H, ACT_ELU);
+        fwd(net, d.L[1], h1, H, h2, H, ACT_ELU);
+        fwd(net, d.L[2], h2, H, z3, Z, ACT_NONE);
+        avgl1(z3, Z, zs, ldzs, Z);
+    }
+    // Encoder.zsa (:107-111) on a filled cat[zs, a]
+    void enc_zsa(const float* net, const float* cat, float* g1, float* g2, float* out) {
+        const NetDef& d = t->def[2];
+        const int H = t->c.enc_hdim, Z = t->c.zs_dim, A = t->c.action_dim;
+        fwd(net, d.L[3], cat, Z + A, g1, H, ACT_ELU);
+        fwd(net, d.L[4], g1, H, g2, H, ACT_ELU);
+        fwd(net, d.L[5], g2, H, out, Z, ACT_NONE);
+    }
+    // Actor.forward (:79-84); caches u (l0 pre-norm), cat[a0, zs], h1, h2 (post-ReLU)
+    void actor_fwd(const float* net, const float* X, const float* zs, float* out) {
+        const NetDef& d = t->def[0];
+        const int S = t->c.state_dim, Ha = t->c.actor_hdim, Z = t->c.zs_dim, A = t->c.action_dim;
+        fwd(net, d.L[0], X, S, t->a_u, Ha, ACT_NONE);
+        avgl1(t->a_u, Ha, t->a_cat, Ha + Z, Ha);
+        copy(t->a_cat + Ha, Ha + Z, zs, Z, Z);
+        fwd(net, d.L[1], t->a_cat, Ha + Z, t->a_h1, Ha, ACT_RELU);
+        fwd(net, d.L[2], t->a_h1, Ha, t->a_h2, Ha, ACT_RELU);
+        fwd(net, d.L[3], t->a_h2, Ha, out, A, ACT_TANH);
+    }
+    // Critic.forward (:128-144): sa = cat[s, a], per head cat[AvgL1Norm(q0h(sa)), zsa, zs] -> q2[:, h]
+    void critic_fwd(const float* net, const float* X, const float* a, const float* zsa, const float* zs) {
+        const NetDef& d = t->def[1];
+        const int S = t->c.state_dim, A = t->c.action_dim, C = t->c.critic_hdim, Z = t->c.zs_dim, W = C + 2 * Z;
+        copy(t->c_sa, S + A, X, S, S);
+        copy(t->c_sa + S, S + A, a, A, A);
+        for (int h = 0; h < 2; ++h) {
+            copy(t->c_cat[h] + C, W, zsa, Z, Z);
+            copy(t->c_cat[h] + C + Z, W, zs, Z, Z);
+            const Lin* L = &d.L[4 * h];
+            fwd(net, L[0], t->c_sa, S + A, t->c_u[h], C, ACT_NONE);
+            avgl1(t->c_u[h], C, t->c_cat[h], W, C);
+            fwd(net, L[1], t->c_cat[h], W, t->c_h1[h], C, ACT_ELU);
+            fwd(net, L[2], t->c_h1[h], C, t->c_h2[h], C, ACT_ELU);
+            fwd(net, L[3], t->c_h2[h], C, t->q2 + h, 2, ACT_NONE);
+        }
+    }
+};
+
+}  // namespace
+
+#define TCK(call)                                                                                      \
+    do {                                                                                               \
+        cudaError_t e_ = (call);                                                                       \
+        if (e_ != cudaSuccess) return exo_set_error(EXO_ERR_CUDA, "exo_td7: %s", cudaGetErrorString(e_)); \
+    } while (0)
+
+extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const float* sN, const float* sR, const float* sD,
+                             const float* randn_dev, float* prio, int32_t* rolled_over, void* stream) {
+    if (!t || !sS || !sA || !sN || !sR || !sD || !prio) return exo_set_error(EXO_ERR_ARG, "exo_td7_train: null argument");
+    TCK(cudaSetDevice(t->device));
+    const ExoTD7Config& c = t->c;
+    const int B = c.batch_rows, S = c.state_dim, A = c.action_dim, Z = c.zs_dim, H = c.enc_hdim, C = c.critic_hdim, Ha = c.actor_hdim;
+    Ctx x{t, (cudaStream_t)stream, B};
+    cudaStream_t s = x.s;
+    const NetDef &DA = t->def[0], &DC = t->def[1], &DE = t->def[2];
+    float* enc = t->net[EXO_TD7_ENCODER];
+    const float* fe = t->net[EXO_TD7_FIXED_ENCODER];
+    const float* fet = t->net[EXO_TD7_FIXED_ENCODER_TARGET];
+    float* critic = t->net[EXO_TD7_CRITIC];
+    float* actor = t->net[EXO_TD7_ACTOR];
+    t->steps++;
+    TCK(cudaMemsetAsync(t->sc + SC_ENC_LOSS, 0, 2 * sizeof(float), s));
+
+    // ---- encoder update (:238-246)
+    x.enc_zs(enc, sN, t->next_zs, Z, t->t_h1, t->t_h2, t->t_z3);
+    x.enc_zs(enc, sS, t->e_cat, Z + A, t->e_h1, t->e_h2, t->e_z3);
+    x.copy(t->e_cat + Z, Z + A, sA, A, A);
+    x.enc_zsa(enc, t->e_cat, t->e_g1, t->e_g2, t->e_pred);
+    {
+        const size_t n = (size_t)B * Z;
+        mse_grad_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(t->e_pred, t->next_zs, t->dA, n, t->sc);
+        t->launches++;
+    }
+    x.zero_grad(EXO_TD7_OPT_ENCODER);
+    {
+        float* g = t->grad[EXO_TD7_OPT_ENCODER];
+        x.dw(g, DE.L[5], t->dA, Z, t->e_g2, H);
+        x.dx(enc, DE.L[5], t->dA, Z, t->dB, H, 0, H, t->e_g2, H, ACT_ELU);
+        x.dw(g, DE.L[4], t->dB, H, t->e_g1, H);
+        x.dx(enc, DE.L[4], t->dB, H, t->dA, H, 0, H, t->e_g1, H, ACT_ELU);
+        x.dw(g, DE.L[3], t->dA, H, t->e_cat, Z + A);
+        x.dx(enc, DE.L[3], t->dA, H, t->dB, Z, 0, Z, nullptr, 0, ACT_NONE);
+        x.avgl1_bwd(t->dB, Z, t->e_z3, Z, t->dB, Z, Z);
+        x.dw(g, DE.L[2], t->dB, Z, t->e_h2, H);
+        x.dx(enc, DE.L[2], t->dB, Z, t->dA, H, 0, H, t->e_h2, H, ACT_ELU);
+        x.dw(g, DE.L[1], t->dA, H, t->e_h1, H);
+        x.dx(enc, DE.L[1], t->dA, H, t->dB, H, 0, H, t->e_h1, H, ACT_ELU);
+        x.dw(g, DE.L[0], t->dB, H, sS, S);
+    }
+    x.adam(EXO_TD7_OPT_ENCODER, c.encoder_lr);
+
+    // ---- critic target (:251-264)
+    x.enc_zs(fet, sN, t->tzs, Z, t->t_h1, t->t_h2, t->t_z3);
+    x.actor_fwd(t->net[EXO_TD7_ACTOR_TARGET], sN, t->tzs, t->na);
+    const float* rn = randn_dev;
+    if (!rn) {
+        randn_kernel<<<(B * A + 255) / 256, 256, 0, s>>>(t->rn, B * A, c.seed, (uint64_t)t->steps);
+        t->launches++;
+        rn = t->rn;
+    }
+    target_action_kernel<<<(B * A + 255) / 256, 256, 0, s>>>(t->na, rn, B * A, (float)t->sigma, c.noise_clip);
+    t->launches++;
+    t->sigma -= (double)c.policy_noise_decrease;
+    x.copy(t->t_cat, Z + A, t->tzs, Z, Z);
+    x.copy(t->t_cat + Z, Z + A, t->na, A, A);
+    x.enc_zsa(fet, t->t_cat, t->t_h1, t->t_h2, t->tzsa);
+    x.critic_fwd(t->net[EXO_TD7_CRITIC_TARGET], sN, t->na, t->tzsa, t->tzs);
+    q_target_kernel<<<1, 1024, 0, s>>>(t->q2, sR, sD, t->qt, B, c.discount, t->sc);
+    t->launches++;
+
+    // ---- critic update (:266-276) and priorities (:281)
+    x.enc_zs(fe, sS, t->fzs, Z, t->t_h1, t->t_h2, t->t_z3);
+    x.copy(t->f_cat, Z + A, t->fzs, Z, Z);
+    x.copy(t->f_cat + Z, Z + A, sA, A, A);
+    x.enc_zsa(fe, t->f_cat, t->f_g1, t->f_g2, t->fzsa);
+    x.critic_fwd(critic, sS, sA, t->fzsa, t->fzs);
+    td_head_kernel<<<(B + 255) / 256, 256, 0, s>>>(t->q2, t->qt, t->dq, prio, B, c.min_priority, c.alpha, t->sc);
+    t->launches++;
+    x.zero_grad(EXO_TD7_OPT_CRITIC);
+    for (int h = 0; h < 2; ++h) {
+        float* g = t->grad[EXO_TD7_OPT_CRITIC];
+        const Lin* L = &DC.L[4 * h];
+        const int W = C + 2 * Z;
+        x.dw(g, L[3], t->dq + h, 2, t->c_h2[h], C);
+        x.dx(critic, L[3], t->dq + h, 2, t->dA, C, 0, C, t->c_h2[h], C, ACT_ELU);
+        x.dw(g, L[2], t->dA, C, t->c_h1[h], C);
+        x.dx(critic, L[2], t->dA, C, t->dB, C, 0, C, t->c_h1[h], C, ACT_ELU);
+        x.dw(g, L[1], t->dB, C, t->c_cat[h], W);
+        x.dx(critic, L[1], t->dB, C, t->dA, C, 0, C, nullptr, 0, ACT_NONE);
+        x.avgl1_bwd(t->dA, C, t->c_u[h], C, t->dA, C, C);
+        x.dw(g, L[0], t->dA, C, t->c_sa, S + A);
+    }
+    x.adam(EXO_TD7_OPT_CRITIC, c.critic_lr);
+
+    // ---- actor update (:287-298)
+    if (t->steps % c.policy_freq == 0) {
+        TCK(cudaMemsetAsync(t->sc + SC_ACTOR_LOSS, 0, sizeof(float), s));
+        x.actor_fwd(actor, sS, t->fzs, t->act);
+        x.copy(t->f_cat + Z, Z + A, t->act, A, A);
+        x.enc_zsa(fe, t->f_cat, t->f_g1, t->f_g2, t->fzsa);
+        x.critic_fwd(critic, sS, t->act, t->fzsa, t->fzs);
+        actor_head_kernel<<<(2 * B + 255) / 256, 256, 0, s>>>(t->q2, t->dq, B, t->sc);
+        t->launches++;
+        for (int h = 0; h < 2; ++h) {            // the critic's input gradients: d action (through sa) and d zsa
+            const Lin* L = &DC.L[4 * h];
+            const int mode = h ? OUT_ADD : OUT_STORE;
+            x.dx(critic, L[3], t->dq + h, 2, t->dA, C, 0, C, t->c_h2[h], C, ACT_ELU);
+            x.dx(critic, L[2], t->dA, C, t->dB, C, 0, C, t->c_h1[h], C, ACT_ELU);
+            x.dx(critic, L[1], t->dB, C, t->d_zsa, Z, C, Z, nullptr, 0, ACT_NONE, mode);
+            x.dx(critic, L[1], t->dB, C, t->dA, C, 0, C, nullptr, 0, ACT_NONE);
+            x.avgl1_bwd(t->dA, C, t->c_u[h], C, t->dA, C, C);
+            x.dx(critic, L[0], t->dA, C, t->d_act1, A, S, A, nullptr, 0, ACT_NONE, mode);
+        }
+        x.dx(fe, DE.L[5], t->d_zsa, Z, t->dA, H, 0, H, t->f_g2, H, ACT_ELU);       // fixed_encoder.zsa's d action
+        x.dx(fe, DE.L[4], t->dA, H, t->dB, H, 0, H, t->f_g1, H, ACT_ELU);
+        x.dx(fe, DE.L[3], t->dB, H, t->d_act2, A, Z, A, nullptr, 0, ACT_NONE);
+        tanh_bwd_kernel<<<(B * A + 255) / 256, 256, 0, s>>>(t->dT, t->d_act1, t->d_act2, t->act, B * A);
+        t->launches++;
+        x.zero_grad(EXO_TD7_OPT_ACTOR);
+        float* g = t->grad[EXO_TD7_OPT_ACTOR];
+        x.dw(g, DA.L[3], t->dT, A, t->a_h2, Ha);
+        x.dx(actor, DA.L[3], t->dT, A, t->dA, Ha, 0, Ha, t->a_h2, Ha, ACT_RELU);
+        x.dw(g, DA.L[2], t->dA, Ha, t->a_h1, Ha);
+        x.dx(actor, DA.L[2], t->dA, Ha, t->dB, Ha, 0, Ha, t->a_h1, Ha, ACT_RELU);
+        x.dw(g, DA.L[1], t->dB, Ha, t->a_cat, Ha + Z);
+        x.dx(actor, DA.L[1], t->dB, Ha, t->dA, Ha, 0, Ha, nullptr, 0, ACT_NONE);
+        x.avgl1_bwd(t->dA, Ha, t->a_u, Ha, t->dA, Ha, Ha);
+        x.dw(g, DA.L[0], t->dA, Ha, sS, S);
+        x.adam(EXO_TD7_OPT_ACTOR, c.actor_lr);
+    }
+
+    // ---- roll-over (:303-312)
+    const bool roll = t->steps % c.target_update_rate == 0;
+    if (roll) {
+        TCK(cudaMemcpyAsync(t->net[EXO_TD7_ACTOR_TARGET], actor, DA.size * sizeof(float), cudaMemcpyDeviceToDevice, s));
+        TCK(cudaMemcpyAsync(t->net[EXO_TD7_CRITIC_TARGET], critic, DC.size * sizeof(float), cudaMemcpyDeviceToDevice, s));
+        TCK(cudaMemcpyAsync(t->net[EXO_TD7_FIXED_ENCODER_TARGET], fe, DE.size * sizeof(float), cudaMemcpyDeviceToDevice, s));
+        TCK(cudaMemcpyAsync(t->net[EXO_TD7_FIXED_ENCODER], enc, DE.size * sizeof(float), cudaMemcpyDeviceToDevice, s));
+        TCK(cudaMemcpyAsync(t->sc + SC_MAX_TARGET, t->sc + SC_MAX, 2 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    }
+    if (rolled_over) *rolled_over = roll ? 1 : 0;
+    TCK(cudaGetLastError());
+    return EXO_OK;
+}
+
+extern "C" int exo_td7_destroy(ExoTD7* t) {
+    if (!t) return EXO_OK;
+    cudaSetDevice(t->device);
+    for (float* p : t->owned) cudaFree(p);
+    delete t;
+    return EXO_OK;
+}
+
+extern "C" int exo_td7_create(int32_t device, const ExoTD7Config* cfg, ExoTD7** out) {
+    if (!out || !cfg) return exo_set_error(EXO_ERR_ARG, "exo_td7_create: null argument");
+    const ExoTD7Config& c = *cfg;
+    if (c.state_dim < 1 || c.action_dim < 1 || c.zs_dim < 1 || c.enc_hdim < 1 || c.critic_hdim < 1 || c.actor_hdim < 1 || c.batch_rows < 1 ||
+        c.target_update_rate < 1 || c.policy_freq < 1)
+        return exo_set_error(EXO_ERR_ARG, "exo_td7_create: sizes and periods must be positive");
+    int ndev = 0;
+    TCK(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return exo_set_error(EXO_ERR_CUDA, "device %d not present: this library has no CPU path", device);
+    cudaDeviceProp prop;
+    TCK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return exo_set_error(EXO_ERR_CUDA, "device %d is sm_%d%d; libexo_env.so carries sm_100a code only", device, prop.major, prop.minor);
+    TCK(cudaSetDevice(device));
+    ExoTD7* t = new ExoTD7();
+    t->device = device; t->n_sm = prop.multiProcessorCount; t->c = c; t->sigma = c.target_policy_noise;
+    const int B = c.batch_rows, S = c.state_dim, A = c.action_dim, Z = c.zs_dim, H = c.enc_hdim, C = c.critic_hdim, Ha = c.actor_hdim;
+    t->def[0] = make_def({{Ha, S}, {Ha, Z + Ha}, {Ha, Ha}, {A, Ha}});
+    t->def[1] = make_def({{C, S + A}, {C, 2 * Z + C}, {C, C}, {1, C}, {C, S + A}, {C, 2 * Z + C}, {C, C}, {1, C}});
+    t->def[2] = make_def({{H, S}, {H, H}, {Z, H}, {H, Z + A}, {H, H}, {Z, H}});
+    cudaError_t err = cudaSuccess;
+    auto alloc = [&](size_t n) -> float* {
+        float* p = nullptr;
+        if (err != cudaSuccess) return nullptr;
+        err = cudaMalloc((void**)&p, std::max<size_t>(n, 1) * sizeof(float));
+        if (err == cudaSuccess) { t->owned.push_back(p); err = cudaMemset(p, 0, std::max<size_t>(n, 1) * sizeof(float)); }
+        return p;
+    };
+    for (int n = 0; n < EXO_TD7_N_NETS; ++n) t->net[n] = alloc(t->def[kind_of(n)].size);
+    for (int o = 0; o < 3; ++o) {
+        const size_t n = t->def[kind_of(OPT_NET[o])].size;
+        t->grad[o] = alloc(n); t->m[o] = alloc(n); t->v[o] = alloc(n);
+    }
+    t->sc = alloc(SC_COUNT);
+    auto rows = [&](int w) { return alloc((size_t)B * w); };
+    t->t_h1 = rows(H); t->t_h2 = rows(H); t->t_z3 = rows(Z); t->next_zs = rows(Z);
+    t->e_h1 = rows(H); t->e_h2 = rows(H); t->e_z3 = rows(Z); t->e_cat = rows(Z + A); t->e_g1 = rows(H); t->e_g2 = rows(H); t->e_pred = rows(Z);
+    t->tzs = rows(Z); t->t_cat = rows(Z + A); t->tzsa = rows(Z); t->na = rows(A); t->rn = rows(A);
+    t->a_u = rows(Ha); t->a_cat = rows(Ha + Z); t->a_h1 = rows(Ha); t->a_h2 = rows(Ha); t->act = rows(A);
+    t->fzs = rows(Z); t->f_cat = rows(Z + A); t->f_g1 = rows(H); t->f_g2 = rows(H); t->fzsa = rows(Z);
+    t->c_sa = rows(S + A);
+    for (int h = 0; h < 2; ++h) { t->c_u[h] = rows(C); t->c_cat[h] = rows(C + 2 * Z); t->c_h1[h] = rows(C); t->c_h2[h] = rows(C); }
+    t->q2 = rows(2); t->qt = rows(1); t->dq = rows(2);
+    const int wmax = std::max(std::max(H, C), std::max(Ha, Z));
+    t->dA = rows(wmax); t->dB = rows(wmax); t->d_zsa = rows(Z); t->d_act1 = rows(A); t->d_act2 = rows(A); t->dT = rows(A);
+    if (err == cudaSuccess) {
+        const float init[SC_COUNT] = {-1e8f, 1e8f, 0.f, 0.f, 0.f, 0.f, 0.f};      // Agent.__init__ :179-182
+        err = cudaMemcpy(t->sc, init, sizeof(init), cudaMemcpyHostToDevice);
+    }
+    if (err != cudaSuccess) {
+        exo_td7_destroy(t);
+        return exo_set_error(EXO_ERR_CUDA, "exo_td7_create: %s", cudaGetErrorString(err));
+    }
+    *out = t;
+    return EXO_OK;
+}
+
+extern "C" int64_t exo_td7_net_size(const ExoTD7* t, int32_t net) {
+    if (!t || net < 0 || net >= EXO_TD7_N_NETS) return -1;
+    return (int64_t)t->def[kind_of(net)].size;
+}
+
+static int td7_vec(ExoTD7* t, float* dev, size_t size, const float* src, float* dst, int64_t n, const char* what) {
+    if (!t || (!src && !dst)) return exo_set_error(EXO_ERR_ARG, "%s: null argument", what);
+    if ((size_t)n != size) return exo_set_error(EXO_ERR_ARG, "%s: vector has %lld floats, the network has %zu", what, (long long)n, size);
+    TCK(cudaSetDevice(t->device));
+    TCK(cudaDeviceSynchronize());
+    if (src) TCK(cudaMemcpy(dev, src, size * sizeof(float), cudaMemcpyHostToDevice));
+    else TCK(cudaMemcpy(dst, dev, size * sizeof(float), cudaMemcpyDeviceToHost));
+    return EXO_OK;
+}
+
+extern "C" int exo_td7_set_net(ExoTD7* t, int32_t net, const float* host, int64_t n) {
+    if (!t || net < 0 || net >= EXO_TD7_N_NETS) return exo_set_error(EXO_ERR_ARG, "exo_td7_set_net: bad network id");
+    return td7_vec(t, t->net[net], t->def[kind_of(net)].size, host, nullptr, n, "exo_td7_set_net");
+}
+extern "C" int exo_td7_get_net(ExoTD7* t, int32_t net, float* host, int64_t n) {
+    if (!t || net < 0 || net >= EXO_TD7_N_NETS) return exo_set_error(EXO_ERR_ARG, "exo_td7_get_net: bad network id");
+    return td7_vec(t, t->net[net], t->def[kind_of(net)].size, nullptr, host, n, "exo_td7_get_net");
+}
+extern "C" int exo_td7_copy_net(ExoTD7* t, int32_t dst, int32_t src) {
+    if (!t || dst < 0 || dst >= EXO_TD7_N_NETS || src < 0 || src >= EXO_TD7_N_NETS || kind_of(dst) != kind_of(src))
+        return exo_set_error(EXO_ERR_ARG, "exo_td7_copy_net: the two networks must be of the same kind");
+    TCK(cudaSetDevice(t->device));
+    TCK(cudaDeviceSynchronize());
+    if (dst != src) TCK(cudaMemcpy(t->net[dst], t->net[src], t->def[kind_of(src)].size * sizeof(float), cudaMemcpyDeviceToDevice));
+    return EXO_OK;
+}
+
+static float* td7_opt_vec(ExoTD7* t, int32_t opt, int32_t which) {
+    if (!t || opt < 0 || opt > 2) return nullptr;
+    return which == EXO_TD7_EXP_AVG ? t->m[opt] : which == EXO_TD7_EXP_AVG_SQ ? t->v[opt] : which == EXO_TD7_GRAD ? t->grad[opt] : nullptr;
+}
+extern "C" int exo_td7_set_opt(ExoTD7* t, int32_t opt, int32_t which, const float* host, int64_t n, int64_t step) {
+    float* d = td7_opt_vec(t, opt, which);
+    if (!d || which == EXO_TD7_GRAD || step < 0) return exo_set_error(EXO_ERR_ARG, "exo_td7_set_opt: bad optimiser / vector id or step");
+    if (int rc = td7_vec(t, d, t->def[kind_of(OPT_NET[opt])].size, host, nullptr, n, "exo_td7_set_opt")) return rc;
+    t->opt_step[opt] = step;
+    return EXO_OK;
+}
+extern "C" int exo_td7_get_opt(ExoTD7* t, int32_t opt, int32_t which, float* host, int64_t n, int64_t* step) {
+    float* d = td7_opt_vec(t, opt, which);
+    if (!d) return exo_set_error(EXO_ERR_ARG, "exo_td7_get_opt: bad optimiser / vector id");
+    if (step) *step = t->opt_step[opt];
+    return td7_vec(t, d, t->def[kind_of(OPT_NET[opt])].size, nullptr, host, n, "exo_td7_get_opt");
+}
+
+extern "C" int exo_td7_scalars(ExoTD7* t, double* out) {
+    if (!t || !out) return exo_set_error(EXO_ERR_ARG, "exo_td7_scalars: null argument");
+    TCK(cudaSetDevice(t->device));
+    TCK(cudaDeviceSynchronize());
+    float h[SC_COUNT];
+    TCK(cudaMemcpy(h, t->sc, sizeof(h), cudaMemcpyDeviceToHost));
+    out[0] = h[SC_MAX]; out[1] = h[SC_MIN]; out[2] = h[SC_MAX_TARGET]; out[3] = h[SC_MIN_TARGET];
+    out[4] = t->sigma; out[5] = (double)t->steps;
+    out[6] = h[SC_ENC_LOSS]; out[7] = h[SC_CRITIC_LOSS]; out[8] = h[SC_ACTOR_LOSS];
+    return EXO_OK;
+}
+extern "C" int exo_td7_set_scalars(ExoTD7* t, const double* in) {
+    if (!t || !in) return exo_set_error(EXO_ERR_ARG, "exo_td7_set_scalars: null argument");
+    TCK(cudaSetDevice(t->device));
+    TCK(cudaDeviceSynchronize());
+    const float h[4] = {(float)in[0], (float)in[1], (float)in[2], (float)in[3]};
+    TCK(cudaMemcpy(t->sc, h, sizeof(h), cudaMemcpyHostToDevice));
+    t->sigma = in[4];
+    t->steps = (int64_t)in[5];
+    return EXO_OK;
+}
+
+extern "C" int64_t exo_td7_launch_count(const ExoTD7* t) { return t ? t->launches : 0; }

@@ -73,7 +73,7 @@ def test_motion_tables(tmp_path, exo):
 
 def _header_functions():
     text = open(os.path.join(REPO, "include", "exo_env.h")).read() + open(os.path.join(REPO, "include", "exo_lap.h")).read() + \
-        open(os.path.join(REPO, "include", "exo_policy.h")).read()
+        open(os.path.join(REPO, "include", "exo_policy.h")).read() + open(os.path.join(REPO, "include", "exo_td7.h")).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     return sorted(set(re.findall(r"\b(exo_[a-z0-9_]+)\s*\(", text)))
 

@@ -1,0 +1,222 @@
+"""Next row N2, second half: the TD7 update. CPU tests pin the numpy oracle (oracle/td7_oracle.py) to the
+reference's own Agent.train() (tests/golden/ref_td7.npz, written by oracle/gen_golden_td7.py from the unmodified
+reference); GPU tests compare the CUDA path (include/exo_td7.h through exo_b200.DeviceTD7) with that golden and, at the
+reference's full layer sizes, with the oracle.
+
+Tolerances (float32 arithmetic, different summation orders):
+  priorities, Q extrema          1e-5 absolute
+  gradients                      1e-5 + 1e-4 relative to the largest entry of the tensor (vs the float64 oracle)
+  parameters after k Adam steps  Adam's update is lr * m / (sqrt(v) + eps): for a gradient entry at rounding-noise level the
+                                 quotient is O(1) with either sign, so single entries may differ by up to 2 * lr * k; the
+                                 tests bound the maximum by that and require 99.9 % of the entries within 2e-6.
+"""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(REPO, "oracle"))
+import td7_oracle  # noqa: E402
+
+GOLD = os.path.join(REPO, "tests", "golden", "ref_td7.npz")
+BATCH_KEYS = ("state", "action", "next_state", "reward", "not_done", "randn")
+ALL_NETS = ("actor", "actor_target", "checkpoint_actor", "critic", "critic_target", "encoder", "fixed_encoder",
+            "fixed_encoder_target", "checkpoint_encoder")
+
+
+def _init_params(g):
+    return {n: {k.split("/", 2)[2]: g[k] for k in g.files if k.startswith("init/%s/" % n)} for n in ("actor", "critic", "encoder")}
+
+
+def _oracle_from_golden(g, dtype):
+    hy = g["hyper"]
+    return td7_oracle.TD7Oracle(_init_params(g), dtype, discount=hy[0], target_update_rate=int(hy[1]), policy_freq=int(hy[2]),
+                                target_policy_noise=hy[3], noise_clip=hy[4], policy_noise_decrease=hy[5], alpha=hy[6],
+                                min_priority=hy[7], actor_lr=hy[8], critic_lr=hy[9], encoder_lr=hy[10], weight_decay=hy[11])
+
+
+def test_oracle_matches_reference_train():
+    g = np.load(GOLD)
+    for dtype, tol in ((np.float32, 1e-6), (np.float64, 1e-6)):
+        o = _oracle_from_golden(g, dtype)
+        for t in range(1, 7):
+            prio, rolled = o.train(*[g["step%d/%s" % (t, k)] for k in BATCH_KEYS])
+            assert rolled == (t == 4)
+            assert np.abs(prio - g["step%d/priority" % t]).max() < tol
+            sc = g["step%d/scalars" % t]
+            assert np.allclose([o.max, o.min, o.max_target, o.min_target, o.target_policy_noise], sc, atol=1e-6)
+            if t in (3, 6):
+                for n in (("actor", "critic", "encoder") if t == 3 else ALL_NETS):
+                    net = getattr(o, n)
+                    for k, v in net.p.items():
+                        assert np.abs(v - g["after%d/%s/%s" % (t, n, k)]).max() < tol, (t, n, k)
+
+
+def test_oracle_gradients_match_finite_differences():
+    """The hand-derived backward passes against central differences of the float64 losses (encoder mse)."""
+    g = np.load(GOLD)
+    batch = [g["step1/%s" % k] for k in BATCH_KEYS]
+    o = _oracle_from_golden(g, np.float64)
+    o.encoder_opt.lr = o.critic_opt.lr = o.actor_opt.lr = 0.0
+    o.encoder_opt.wd = 0.0
+    o.train(*batch)
+    grad = {k: v.copy() for k, v in o.encoder.g.items()}
+
+    T = td7_oracle.TD7Oracle
+    base_net = _oracle_from_golden(g, np.float64).encoder
+    s64, a64, ns64 = (np.asarray(x, np.float64) for x in batch[:3])
+    next_zs = T.enc_zs(base_net, ns64)[0]                     # torch.no_grad(): a constant of the loss (:238-239)
+
+    def loss(params):
+        net = td7_oracle.Net(params, np.float64)
+        return float(np.mean((T.enc_zsa(net, T.enc_zs(net, s64)[0], a64)[0] - next_zs) ** 2))
+    rs = np.random.RandomState(0)
+    for k in ("zs1.weight", "zs3.bias", "zsa1.weight", "zsa3.weight"):
+        base = {kk: v.copy() for kk, v in _oracle_from_golden(g, np.float64).encoder.p.items()}
+        idx = tuple(rs.randint(0, s) for s in base[k].shape)
+        eps = 1e-6
+        hi = {kk: v.copy() for kk, v in base.items()}
+        lo = {kk: v.copy() for kk, v in base.items()}
+        hi[k][idx] += eps
+        lo[k][idx] -= eps
+        fd = (loss(hi) - loss(lo)) / (2 * eps)
+        assert abs(fd - grad[k][idx]) < 1e-7 + 1e-5 * abs(fd), (k, idx, fd, grad[k][idx])
+
+
+def test_flat_layout_round_trip(exo):
+    hp = exo.Hyperparameters(zs_dim=5, enc_hdim=4, critic_hdim=6, actor_hdim=3)
+    shapes = exo.td7.layer_shapes(11, 2, hp)
+    assert [n for n, _, _ in shapes["critic"]] == ["q01", "q1", "q2", "q3", "q02", "q4", "q5", "q6"]
+    assert shapes["critic"][1][1:] == (6, 16) and shapes["encoder"][3][1:] == (4, 7) and shapes["actor"][1][1:] == (3, 8)
+    rs = np.random.RandomState(1)
+    sd = {}
+    for n, o, i in shapes["encoder"]:
+        sd[n + ".weight"], sd[n + ".bias"] = rs.randn(o, i).astype(np.float32), rs.randn(o).astype(np.float32)
+    v = exo.td7.flatten(sd, shapes["encoder"])
+    assert v.size == sum(o * i + o for _, o, i in shapes["encoder"])
+    back = exo.td7.unflatten(v, shapes["encoder"])
+    assert list(back) == [n + s for n, _, _ in shapes["encoder"] for s in (".weight", ".bias")]
+    for k in sd:
+        assert np.array_equal(back[k].numpy(), sd[k])
+    sd["zs2.weight"] = sd["zs2.weight"][:, :-1]
+    with pytest.raises(exo.ExoError):
+        exo.td7.flatten(sd, shapes["encoder"])
+
+
+def test_no_gpu_is_an_error_not_a_fallback(exo):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(exo.ExoError):
+        exo.DeviceTD7(80, 7, replay_buffer=False)
+
+
+# ------------------------------------------------------------------------------------------------ GPU: the CUDA path
+def _learner_from_golden(exo, g):
+    S, A, Z, H, Cd, Ha, B = (int(v) for v in g["dims"])
+    hy = g["hyper"]
+    envs = 3
+    hp = exo.Hyperparameters(batch_size=B // envs, buffer_size=64, discount=float(hy[0]), target_update_rate=int(hy[1]),
+                             policy_freq=int(hy[2]), target_policy_noise=float(hy[3]), noise_clip=float(hy[4]), alpha=float(hy[6]),
+                             min_priority=float(hy[7]), zs_dim=Z, enc_hdim=H, critic_hdim=Cd, actor_hdim=Ha,
+                             actor_lr=float(hy[8]), critic_lr=float(hy[9]), encoder_lr=float(hy[10]))
+    t = exo.DeviceTD7(S, A, 1, learning_steps=100, hp=hp, env_num=envs, device="cuda:0", replay_buffer=False)
+    for n, sd in _init_params(g).items():
+        t.load_state_dict(n, sd)
+    t.sync_copies()
+    return t
+
+
+def _dev_batch(g, t, step):
+    import torch
+    return [torch.from_numpy(np.ascontiguousarray(g["step%d/%s" % (step, k)], dtype=np.float32)).cuda() for k in BATCH_KEYS]
+
+
+def _param_diff(sd, ref):
+    d = np.concatenate([np.abs(sd[k].numpy().astype(np.float64) - np.asarray(ref[k], np.float64)).reshape(-1) for k in sd])
+    return d
+
+
+@pytest.mark.gpu
+def test_cuda_update_reproduces_the_reference_train(exo):
+    g = np.load(GOLD)
+    t = _learner_from_golden(exo, g)
+    lr = float(g["hyper"][8])
+    for step in range(1, 7):
+        prio, rolled = t.train_on_batch(*_dev_batch(g, t, step))
+        assert rolled == (step == 4)
+        assert np.abs(prio.cpu().numpy() - g["step%d/priority" % step]).max() < 1e-5
+        sc = t.scalars()
+        ref = g["step%d/scalars" % step]
+        assert np.allclose([sc["max"], sc["min"], sc["max_target"], sc["min_target"], sc["target_policy_noise"]], ref, atol=1e-5)
+        assert sc["training_steps"] == step
+        if step in (3, 6):
+            for n in (("actor", "critic", "encoder") if step == 3 else ALL_NETS):
+                ref_sd = {k.split("/", 2)[2]: g[k] for k in g.files if k.startswith("after%d/%s/" % (step, n))}
+                d = _param_diff(t.state_dict(n), ref_sd)
+                assert d.max() <= 2 * lr * step + 1e-7, (step, n, d.max())
+                assert np.mean(d < 2e-6) >= 0.999, (step, n, np.mean(d < 2e-6))
+    t.close()
+
+
+@pytest.mark.gpu
+def test_cuda_gradients_match_the_float64_oracle(exo):
+    g = np.load(GOLD)
+    t = _learner_from_golden(exo, g)
+    o = _oracle_from_golden(g, np.float64)
+    for step in (1, 2):                                   # step 2 runs the actor update
+        t.train_on_batch(*_dev_batch(g, t, step))
+        o.train(*[g["step%d/%s" % (step, k)] for k in BATCH_KEYS])
+        for opt in (("encoder", "critic") if step == 1 else ("encoder", "critic", "actor")):
+            got = t.gradients(opt)
+            ref = getattr(o, opt).g
+            for k, v in got.items():
+                e = np.abs(v.numpy() - ref[k]).max()
+                assert e < 1e-5 + 1e-4 * np.abs(ref[k]).max(), (step, opt, k, e)
+        # keep the two in lock step: rounding-level gradients may step Adam differently
+        for n in ALL_NETS:
+            t.load_state_dict(n, {k: v.astype(np.float32) for k, v in getattr(o, n).p.items()})
+        for i, opt in enumerate(("actor", "critic", "encoder")):
+            ad = getattr(o, opt + "_opt")
+            keys = list(ad.m)
+            t.load_optimizer_state_dict(opt, {"state": {j: {"step": float(ad.t), "exp_avg": ad.m[k].astype(np.float32),
+                                                            "exp_avg_sq": ad.v[k].astype(np.float32)} for j, k in enumerate(keys)} if ad.t else {}})
+    t.close()
+
+
+@pytest.mark.gpu
+def test_full_size_update_against_the_oracle(exo):
+    """The reference's layer sizes (80 / 7 / zs 300 / 300 / 320 / 300), 4 envs x 128 rows, 4 iterations with a roll-over."""
+    import torch
+    hp = exo.Hyperparameters(batch_size=128, buffer_size=1024, target_update_rate=3)
+    t = exo.DeviceTD7(80, 7, 1, learning_steps=1000, hp=hp, env_num=4, device="cuda:0", replay_buffer=False, init_seed=3)
+    params = {n: {k: v.numpy() for k, v in t.state_dict(n).items()} for n in ("actor", "critic", "encoder")}
+    o = td7_oracle.TD7Oracle(params, np.float32, target_update_rate=3, policy_noise_decrease=0.2 / 1000)
+    rs = np.random.RandomState(9)
+    B = 512
+    for step in range(1, 5):
+        batch = [rs.randn(B, 80) * 0.6, np.clip(rs.randn(B, 7) * 0.5, -1, 1), rs.randn(B, 80) * 0.6, rs.randn(B, 1) * 3 + 1,
+                 (rs.rand(B, 1) > 0.1).astype(np.float64), rs.randn(B, 7)]
+        batch = [b.astype(np.float32) for b in batch]
+        prio, rolled = t.train_on_batch(*[torch.from_numpy(b).cuda() for b in batch])
+        ref_prio, ref_rolled = o.train(*batch)
+        assert rolled == ref_rolled == (step == 3)
+        assert np.abs(prio.cpu().numpy() - ref_prio).max() < 2e-5
+        sc = t.scalars()
+        assert abs(sc["max"] - o.max) < 1e-5 and abs(sc["min"] - o.min) < 1e-5
+        assert abs(sc["encoder_loss"] - o.last["encoder_loss"]) < 1e-6 + 1e-4 * o.last["encoder_loss"]
+        assert abs(sc["critic_loss"] - o.last["critic_loss"]) < 1e-5 + 1e-4 * o.last["critic_loss"]
+        if step % 2 == 0:
+            assert abs(sc["actor_loss"] - o.last["actor_loss"]) < 1e-5
+        for opt in ("encoder", "critic") + (("actor",) if step % 2 == 0 else ()):
+            got, ref = t.gradients(opt), getattr(o, opt).g
+            for k, v in got.items():
+                e = np.abs(v.numpy() - ref[k]).max()
+                assert e < 1e-6 + 2e-4 * np.abs(ref[k]).max(), (step, opt, k, e, np.abs(ref[k]).max())
+    for n in ALL_NETS:
+        d = _param_diff(t.state_dict(n), getattr(o, n).p)
+        assert d.max() <= 2 * 3e-4 * 4 + 1e-7 and np.mean(d < 2e-6) >= 0.995, (n, d.max(), np.mean(d < 2e-6))
+    assert t.launch_count() > 100
+    t.close()
