@@ -111,6 +111,7 @@ SIGNATURES = {
     "exo_td7_train": (C.c_int, [C.c_void_p] + [C.c_void_p] * 7 + [C.POINTER(C.c_int32), C.c_void_p]),
     "exo_td7_scalars": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "exo_td7_set_scalars": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
+    "exo_td7_randn": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
     "exo_td7_launch_count": (C.c_int64, [C.c_void_p]),
 }
 

@@ -171,18 +171,19 @@ __global__ void copy_cols_kernel(float* dst, int ldd, const float* src, int lds,
     dst[(size_t)r * ldd + c] = src[(size_t)r * lds + c];
 }
 
-// gb[n] += sum_rows dy[r, n]: block = 32 columns x 8 row lanes
-__global__ void colsum_kernel(const float* dy, int ld, float* gb, int rows, int n) {
+// gb[n] += sum_rows dy[r, n]: block = 32 columns x 8 row lanes over one slice of the rows (gridDim.y slices, atomicAdd)
+__global__ void colsum_kernel(const float* dy, int ld, float* gb, int rows, int n, int rows_per_slice) {
     __shared__ float part[8][33];
     const int c = blockIdx.x * 32 + threadIdx.x;
+    const int r0 = blockIdx.y * rows_per_slice, r1 = min(rows, r0 + rows_per_slice);
     float s = 0.f;
     if (c < n)
-        for (int r = threadIdx.y; r < rows; r += 8) s += dy[(size_t)r * ld + c];
+        for (int r = r0 + threadIdx.y; r < r1; r += 8) s += dy[(size_t)r * ld + c];
     part[threadIdx.y][threadIdx.x] = s;
     __syncthreads();
     if (threadIdx.y == 0 && c < n) {
         for (int k = 1; k < 8; ++k) s += part[k][threadIdx.x];
-        gb[c] += s;
+        atomicAdd(&gb[c], s);
     }
 }
 
@@ -396,7 +397,9 @@ struct Ctx {
         int splits = (2 * t->n_sm + tiles - 1) / tiles;
         splits = std::max(1, std::min(splits, (B + 63) / 64));
         gemm(true, false, g, splits);
-        colsum_kernel<<<(L.out + 31) / 32, dim3(32, 8), 0, s>>>(dY, lddy, grad + L.b, B, L.out);
+        const int slices = std::max(1, std::min((B + 63) / 64, (2 * t->n_sm) / ((L.out + 31) / 32)));
+        const int rps = (B + slices - 1) / slices;
+        colsum_kernel<<<dim3((L.out + 31) / 32, (B + rps - 1) / rps), dim3(32, 8), 0, s>>>(dY, lddy, grad + L.b, B, L.out, rps);
         t->launches++;
     }
     void avgl1(const float* x, int ldx, float* y, int ldy, int n) {
@@ -750,6 +753,15 @@ extern "C" int exo_td7_set_scalars(ExoTD7* t, const double* in) {
     TCK(cudaMemcpy(t->sc, h, sizeof(h), cudaMemcpyHostToDevice));
     t->sigma = in[4];
     t->steps = (int64_t)in[5];
+    return EXO_OK;
+}
+
+extern "C" int exo_td7_randn(ExoTD7* t, float* out_dev, int64_t count, int64_t step, void* stream) {
+    if (!t || !out_dev || count < 0 || count > 0x7FFFFFFF) return exo_set_error(EXO_ERR_ARG, "exo_td7_randn: bad argument");
+    TCK(cudaSetDevice(t->device));
+    if (count) randn_kernel<<<(unsigned)((count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(out_dev, (int)count, t->c.seed, (uint64_t)step);
+    t->launches++;
+    TCK(cudaGetLastError());
     return EXO_OK;
 }
 

@@ -317,6 +317,13 @@ class DeviceTD7(object):
         policy.set_networks(self.state_dict("actor"), self.state_dict("fixed_encoder"), "current")
         policy.set_networks(self.state_dict("checkpoint_actor"), self.state_dict("checkpoint_encoder"), "checkpoint")
 
+    def device_randn(self, count, step):
+        """The standard normals exo_td7_train draws for iteration `step` when it is given none (tests)."""
+        out = torch.empty(int(count), device=self.device, dtype=torch.float32)
+        stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        _capi.check(self.lib.exo_td7_randn(self.h, C.c_void_p(out.data_ptr()), int(count), int(step), stream))
+        return out
+
     def launch_count(self):
         return int(self.lib.exo_td7_launch_count(self.h))
 

@@ -96,6 +96,10 @@ int exo_td7_scalars(ExoTD7* t, double* out9);
 /* Agent.load's counterpart for those scalars (resuming a run). */
 int exo_td7_set_scalars(ExoTD7* t, const double* in6);
 
+/* The generator exo_td7_train uses when randn_dev is NULL, exposed for tests: fills out_dev[count] with the standard
+ * normals of iteration `step` (a counter hash of (seed, step, index) + Box-Muller; not torch's stream). */
+int exo_td7_randn(ExoTD7* t, float* out_dev, int64_t count, int64_t step, void* stream);
+
 /* kernels launched so far through this handle */
 int64_t exo_td7_launch_count(const ExoTD7* t);
 

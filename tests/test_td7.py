@@ -220,3 +220,110 @@ def test_full_size_update_against_the_oracle(exo):
         assert d.max() <= 2 * 3e-4 * 4 + 1e-7 and np.mean(d < 2e-6) >= 0.995, (n, d.max(), np.mean(d < 2e-6))
     assert t.launch_count() > 100
     t.close()
+
+
+@pytest.mark.gpu
+def test_train_loop_with_the_device_replay_buffer(exo):
+    """Agent.train as the training script drives it: LAP.sample -> update -> update_priority, reset_max_priority on roll-over."""
+    import torch
+    hp = exo.Hyperparameters(batch_size=16, buffer_size=256, target_update_rate=4, zs_dim=24, enc_hdim=20, critic_hdim=28, actor_hdim=16)
+    t = exo.DeviceTD7(11, 3, 1, learning_steps=1000, hp=hp, env_num=3, device="cuda:0", init_seed=5)
+    g = torch.Generator(device="cuda").manual_seed(2)
+    for _ in range(40):
+        s, ns = torch.randn(3, 11, device="cuda", generator=g), torch.randn(3, 11, device="cuda", generator=g)
+        a = torch.rand(3, 3, device="cuda", generator=g) * 2 - 1
+        t.replay_buffer.add_batch(s, a, ns, torch.randn(3, device="cuda", generator=g), torch.zeros(3, dtype=torch.bool, device="cuda"))
+    before = {n: t.state_dict(n) for n in ("actor", "critic", "encoder", "critic_target", "fixed_encoder")}
+    pr0 = t.replay_buffer.storage("priority").clone()
+    for _ in range(5):
+        t.train()
+    sc = t.scalars()
+    assert sc["training_steps"] == 5 and sc["max"] > -1e8 and sc["min"] < 1e8
+    assert sc["max_target"] != 0.0 or sc["min_target"] != 0.0                     # rolled over at iteration 4
+    assert np.isfinite([sc["encoder_loss"], sc["critic_loss"], sc["actor_loss"]]).all()
+    after = {n: t.state_dict(n) for n in before}
+    for n in before:
+        assert any(not torch.equal(before[n][k], after[n][k]) for k in before[n]), n
+    assert not torch.equal(pr0, t.replay_buffer.storage("priority"))
+    # maybe_train_and_checkpoint (:315-332): the first episode becomes the checkpoint and trains ep_timesteps iterations
+    t.maybe_train_and_checkpoint(3, 10.0)
+    assert t.training_steps == 8 and t.best_min_return == 10.0 and t.eps_since_update == 0
+    ck, fe = t.state_dict("checkpoint_encoder"), after["fixed_encoder"]
+    t.maybe_train_and_checkpoint(2, 5.0)                                          # worse than the checkpoint: trains, keeps it
+    assert t.training_steps == 10 and t.best_min_return == 10.0
+    assert all(torch.equal(ck[k], t.state_dict("checkpoint_encoder")[k]) for k in ck)
+    t.close()
+
+
+@pytest.mark.gpu
+def test_save_and_load_use_the_reference_files(exo, tmp_path):
+    import torch
+    g = np.load(GOLD)
+    t = _learner_from_golden(exo, g)
+    for step in (1, 2, 3):
+        t.train_on_batch(*_dev_batch(g, t, step))
+    base = str(tmp_path / "[1,0,1,0]")
+    t.save(base)
+    names = sorted(os.listdir(tmp_path))
+    assert names == sorted("[1,0,1,0]_" + s for s in ("actor", "actor_optimizer", "critic", "critic_optimizer", "encoder",
+                                                      "encoder_optimizer", "checkpoint_actor", "checkpoint_encoder"))
+    # the files are what torch modules / torch.optim.Adam of the reference's shapes load (Agent.load, :349-366)
+    sd = torch.load(base + "_critic", weights_only=False)
+    assert list(sd)[:4] == ["q01.weight", "q01.bias", "q1.weight", "q1.bias"] and sd["q3.weight"].shape == (1, 28)
+
+    class Net(torch.nn.Module):
+        def __init__(self, shapes):
+            super().__init__()
+            for name, out, inp in shapes:
+                setattr(self, name, torch.nn.Linear(inp, out))
+    net = Net(t.shapes["critic"])
+    net.load_state_dict(sd)
+    opt = torch.optim.Adam(net.parameters(), lr=3e-4, weight_decay=1e-7)
+    opt.load_state_dict(torch.load(base + "_critic_optimizer", weights_only=False))
+    assert float(opt.state[net.q01.weight]["step"]) == 3.0
+    # a second learner resumes from the files and takes the same next step
+    u = _learner_from_golden(exo, g)
+    u.load(base)
+    for n in ("actor", "critic", "encoder", "checkpoint_actor", "checkpoint_encoder"):
+        a, b = t.state_dict(n), u.state_dict(n)
+        assert all(torch.equal(a[k], b[k]) for k in a), n
+    for opt_name in ("actor", "critic", "encoder"):
+        a, b = t.optimizer_state_dict(opt_name), u.optimizer_state_dict(opt_name)
+        assert a["state"].keys() == b["state"].keys()
+        for i in a["state"]:
+            assert torch.equal(a["state"][i]["exp_avg_sq"], b["state"][i]["exp_avg_sq"]) and a["state"][i]["step"] == b["state"][i]["step"]
+    # Agent.load rebuilds the targets from the loaded networks (:352,357,362-363); give both the same scalars and compare one step
+    for n, src in (("critic_target", "critic"), ("actor_target", "actor"), ("fixed_encoder", "encoder"), ("fixed_encoder_target", "encoder")):
+        t.copy_net(n, src)
+    sc = t.scalars()
+    u.set_scalars(sc["max"], sc["min"], sc["max_target"], sc["min_target"], sc["target_policy_noise"], sc["training_steps"])
+    p1, _ = t.train_on_batch(*_dev_batch(g, t, 4))
+    p2, _ = u.train_on_batch(*_dev_batch(g, u, 4))
+    assert torch.allclose(p1, p2, atol=1e-6)
+    t.close()
+    u.close()
+
+
+@pytest.mark.gpu
+def test_device_noise_is_standard_normal_and_changes_per_iteration(exo):
+    import torch
+    hp = exo.Hyperparameters(batch_size=512, zs_dim=16, enc_hdim=16, critic_hdim=16, actor_hdim=16, target_policy_noise=0.2, noise_clip=10.0)
+    t = exo.DeviceTD7(6, 4, 1, hp=hp, env_num=8, device="cuda:0", replay_buffer=False, init_seed=1, seed=77)
+    B = 4096
+    z = torch.zeros
+    batch = [torch.randn(B, 6).cuda(), z(B, 4).cuda(), torch.randn(B, 6).cuda(), z(B, 1).cuda(), torch.ones(B, 1).cuda()]
+    t.train_on_batch(*batch)            # randn=None: drawn by randn_kernel
+    t.train_on_batch(*batch)
+    x = t.device_randn(1 << 20, 3).double()
+    assert abs(float(x.mean())) < 5e-3 and abs(float(x.std()) - 1) < 5e-3 and abs(float((x ** 4).mean()) - 3) < 0.05
+    assert float(x.abs().max()) > 4.0 and torch.isfinite(x).all()
+    assert not torch.equal(t.device_randn(1024, 3), t.device_randn(1024, 4))
+    assert abs(float((x[:-1] * x[1:]).mean())) < 5e-3                              # no lag-1 correlation
+    u = exo.DeviceTD7(6, 4, 1, hp=hp, env_num=8, device="cuda:0", replay_buffer=False, init_seed=1, seed=78)
+    u.train_on_batch(*batch)
+    u.train_on_batch(*batch)
+    a, b = t.state_dict("critic"), u.state_dict("critic")
+    assert all(torch.isfinite(v).all() for v in a.values())
+    assert any(not torch.equal(a[k], b[k]) for k in a)
+    t.close()
+    u.close()
