@@ -1,9 +1,11 @@
 // exo_td7.cu — the TD7 update of include/exo_td7.h: one Agent.train() iteration (Agent/TD7_multi_agent_Pink_noise.py
 // :230-312) with every network, gradient and Adam state resident in HBM.
 //
-// Building blocks (float32 on the FP32 pipe, the reference's arithmetic):
-//   sgemm_kernel<TA,TB>   C = op(A) op(B) on 64 x 64 x 16 tiles, 256 threads, 4 x 4 accumulators per thread, the next
-//                         k-tile prefetched into registers while the current one is multiplied. One kernel serves
+// Building blocks:
+//   gemm_kernel<TA,TB,TC,TN>  C = op(A) op(B) on 64 x TN x 16 tiles (TN = 64 | 80, picked per launch so the tiles fill one
+//                         wave of SMs), 256 threads, a 4-stage cp.async ring. TC: the products run on the tensor cores as
+//                         3xTF32 (split operands, mma.sync m16n8k8, fp32 accumulation; fp32-class accuracy); !TC
+//                         (EXO_TD7_FFMA=1): float32 FFMA on the FP32 pipe, the reference's exact arithmetic. One kernel serves
 //                           forward      Y  = act(X W^T + b)                      (TA=0, TB=1, bias + activation epilogue)
 //                           input grad   dX = (dY W[:, c0:c1]) * act'(saved out)  (TA=0, TB=0, derivative epilogue)
 //                           weight grad  dW += dY^T X                             (TA=1, TB=0, split over the batch,
@@ -16,6 +18,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 #include <algorithm>
 #include <initializer_list>
@@ -55,74 +58,176 @@ __device__ __forceinline__ float act_bwd(float y, int act) {      // derivative 
     return 1.f;
 }
 
-constexpr int TM = 64, TN = 64, TK = 16, PITCH = 68;
+constexpr int TM = 64, TK = 16, STAGES = 4;
 
-template <bool TA, bool TB>
-__global__ void __launch_bounds__(256) sgemm_kernel(GemmArgs g) {
-    __shared__ __align__(16) float As[TK][PITCH];
-    __shared__ __align__(16) float Bs[TK][PITCH];
-    const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
+// ---- 3xTF32: the GEMM on the tensor cores with fp32-class accuracy. Every operand x is split in registers into
+// hi = x rounded to TF32 (10 explicit mantissa bits, nearest) and lo = x - hi (exact in float32, |lo| <= 2^-11 |x|);
+// a b ~ lo_a hi_b + hi_a lo_b + hi_a hi_b: three mma.sync.m16n8k8 (tf32 in, f32 accumulate) per fragment pair, small
+// terms first. The tensor core reads only the upper 19 bits of lo (truncation, <= 2^-11 |lo|, sign-symmetric), so each
+// product is off by <= 2^-21 |a b| including the dropped lo_a lo_b term - a few float32 roundings.
+// cvt.rna.tf32.f32 is a 4-instruction sequence on sm_100a (Inf/NaN guard included) and made the splits 60 % of the
+// loop's instructions; the integer form below is 3 instructions per operand (finite inputs).
+__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
+    hi = (__float_as_uint(x) + 0x1000u) & 0xffffe000u;
+    lo = __float_as_uint(x - __uint_as_float(hi));
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+__device__ __forceinline__ void gemm_store(const GemmArgs& g, int m, int n, float v) {
+    if (m >= g.M || n >= g.N) return;
+    if (g.bias) v += g.bias[n];
+    v = act_fwd(v, g.act);
+    if (g.D) v *= act_bwd(g.D[(size_t)m * g.ldd + n], g.dact);
+    float* c = g.C + (size_t)m * g.ldc + n;
+    if (g.out == OUT_STORE) *c = v;
+    else if (g.out == OUT_ADD) *c += v;
+    else atomicAdd(c, v);
+}
+
+// C tile 64 x TN per CTA (TN = 64 or 80), 256 threads, k in steps of 16 through a 4-stage cp.async ring (4-byte copies:
+// any alignment, either operand transposed, zero fill outside the matrix). The host picks TN so that the tiles fill one
+// wave of SMs: 1920 x 300 is 30 x 5 = 150 tiles of 64 x 64 - two more than a B200 has SMs, i.e. two waves - but
+// 30 x 4 = 120 tiles of 64 x 80. Global pointers and shared offsets of the copies are set up once; per k-step a copy
+// costs a bound compare, the cp.async and a pointer increment.
+//   TC = false  FP32 pipe: 4 x (TN/16) accumulators per thread, tiles k-major (A pitch 68, float4 reads).
+//   TC = true   tensor cores, 3xTF32: 8 warps as 4 (m) x 2 (n), warp tile 16 x TN/2; tiles k-major with pitch = 8 mod 32
+//               and the column index XOR-ed with 2 ((k >> 2) & 3): conflict-free for the fragment reads (lanes = 4 k x
+//               8 m) and for both staging patterns (lanes along k or along m).
+template <bool TA, bool TB, bool TC, int TN>
+__global__ void __launch_bounds__(256) gemm_kernel(GemmArgs g) {
+    constexpr int PA = TC ? 72 : 68;
+    constexpr int PB = TC ? (TN == 64 ? 72 : 104) : (TN == 64 ? 68 : 84);
+    constexpr int NB = TN * TK / 256;             // B-tile elements per thread: 4 or 5
+    constexpr int NF = TN / 16;                   // TC: n8 fragments per warp; !TC: columns per thread
+    __shared__ __align__(16) float As[STAGES][TK][PA];
+    __shared__ __align__(16) float Bs[STAGES][TK][PB];
+    const int t = threadIdx.x;
     const int m0 = blockIdx.y * TM, n0 = blockIdx.x * TN;
     const int kbeg = blockIdx.z * g.kchunk;
     const int kend = min(g.K, kbeg + g.kchunk);
-    // element (mm, kk) of the A tile / (kk, nn) of the B tile this thread moves, 4 each, laid out so that the global
-    // reads are contiguous along the operand's fast axis
-    int a_m[4], a_k[4], b_n[4], b_k[4];
+    auto swz = [](int k) { return TC ? ((k >> 2) & 3) << 1 : 0; };
+    // copies: element (mm, kk) of the A tile / (kk, nn) of the B tile, contiguous along the operand's fast axis
+    const float* pa[4];
+    const float* pb[NB];
+    uint32_t da[4], db[NB];
+    int ka[4], kb[NB];                            // k offset of the element inside the tile; -1 = outside M / N
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        if (TA) { a_m[i] = t & 63; a_k[i] = (t >> 6) + 4 * i; } else { a_k[i] = t & 15; a_m[i] = (t >> 4) + 16 * i; }
-        if (TB) { b_k[i] = t & 15; b_n[i] = (t >> 4) + 16 * i; } else { b_n[i] = t & 63; b_k[i] = (t >> 6) + 4 * i; }
+        const int mm = TA ? (t & 63) : (t >> 4) + 16 * i, kk = TA ? (t >> 6) + 4 * i : (t & 15);
+        const int gm = m0 + mm;
+        ka[i] = gm < g.M ? kk : -1;
+        pa[i] = gm < g.M ? (TA ? g.A + (size_t)(kbeg + kk) * g.lda + gm : g.A + (size_t)gm * g.lda + kbeg + kk) : g.A;
+        da[i] = (uint32_t)__cvta_generic_to_shared(&As[0][kk][mm ^ swz(kk)]);
     }
-    float ra[4], rb[4];
-    auto fetch = [&](int k0) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int gm = m0 + a_m[i], gk = k0 + a_k[i];
-            ra[i] = (gm < g.M && gk < kend) ? (TA ? g.A[(size_t)gk * g.lda + gm] : g.A[(size_t)gm * g.lda + gk]) : 0.f;
-            const int gn = n0 + b_n[i], hk = k0 + b_k[i];
-            rb[i] = (gn < g.N && hk < kend) ? (TB ? g.B[(size_t)gn * g.ldb + hk] : g.B[(size_t)hk * g.ldb + gn]) : 0.f;
+    for (int i = 0; i < NB; ++i) {
+        const int e = t + 256 * i;
+        const int nn = TB ? e / TK : e % TN, kk = TB ? e % TK : e / TN;
+        const int gn = n0 + nn;
+        kb[i] = gn < g.N ? kk : -1;
+        pb[i] = gn < g.N ? (TB ? g.B + (size_t)gn * g.ldb + kbeg + kk : g.B + (size_t)(kbeg + kk) * g.ldb + gn) : g.B;
+        db[i] = (uint32_t)__cvta_generic_to_shared(&Bs[0][kk][nn ^ swz(kk)]);
+    }
+    const size_t stepa = TA ? (size_t)TK * g.lda : TK, stepb = TB ? TK : (size_t)TK * g.ldb;
+    int knext = kbeg;                             // k of the next tile to copy
+    auto issue = [&](int stage) {
+        if (knext < kend) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const bool ok = ka[i] >= 0 && knext + ka[i] < kend;
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(da[i] + stage * (TK * PA * 4)), "l"(ok ? pa[i] : g.A), "r"(ok ? 4 : 0) : "memory");
+                pa[i] += stepa;
+            }
+#pragma unroll
+            for (int i = 0; i < NB; ++i) {
+                const bool ok = kb[i] >= 0 && knext + kb[i] < kend;
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(db[i] + stage * (TK * PB * 4)), "l"(ok ? pb[i] : g.B), "r"(ok ? 4 : 0) : "memory");
+                pb[i] += stepb;
+            }
+            knext += TK;
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
     };
-    float acc[4][4];
+    const int lane = t & 31, warp = t >> 5, gid = lane >> 2, tig = lane & 3;
+    const int wm = (warp >> 1) * 16, wn = (warp & 1) * (TN / 2);      // TC
+    const int tx = t & 15, ty = t >> 4;                                // !TC
+    float acc[NF * 4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < NF * 4; ++i) acc[i] = 0.f;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-    if (kbeg < kend) fetch(kbeg);
+    for (int s = 0; s < STAGES - 1; ++s) issue(s);
+    int stage = 0;
     for (int k0 = kbeg; k0 < kend; k0 += TK) {
+        asm volatile("cp.async.wait_group %0;" ::"n"(STAGES - 2) : "memory");
+        __syncthreads();                       // tile `stage` has landed for everyone; tile stage-1 is no longer being read
+        issue((stage + STAGES - 1) % STAGES);
+        if (TC) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { As[a_k[i]][a_m[i]] = ra[i]; Bs[b_k[i]][b_n[i]] = rb[i]; }
-        __syncthreads();
-        if (k0 + TK < kend) fetch(k0 + TK);
+            for (int ks = 0; ks < TK; ks += 8) {
+                const int s0 = swz(ks + tig), s1 = swz(ks + tig + 4);
+                uint32_t ah[4], al[4], bh[NF][2], bl[NF][2];
+                const int m = wm + gid;
+                split_tf32(As[stage][ks + tig][m ^ s0], ah[0], al[0]);
+                split_tf32(As[stage][ks + tig][(m + 8) ^ s0], ah[1], al[1]);
+                split_tf32(As[stage][ks + tig + 4][m ^ s1], ah[2], al[2]);
+                split_tf32(As[stage][ks + tig + 4][(m + 8) ^ s1], ah[3], al[3]);
 #pragma unroll
-        for (int kk = 0; kk < TK; ++kk) {
-            const float4 a = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
-            const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
-            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+                for (int j = 0; j < NF; ++j) {
+                    const int n = wn + 8 * j + gid;
+                    split_tf32(Bs[stage][ks + tig][n ^ s0], bh[j][0], bl[j][0]);
+                    split_tf32(Bs[stage][ks + tig + 4][n ^ s1], bh[j][1], bl[j][1]);
+                }
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+                for (int j = 0; j < NF; ++j) {
+                    float(&c)[4] = *reinterpret_cast<float(*)[4]>(&acc[j * 4]);
+                    mma_tf32(c, al, bh[j]);
+                    mma_tf32(c, ah, bl[j]);
+                    mma_tf32(c, ah, bh[j]);
+                }
+            }
+        } else {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+            for (int kk = 0; kk < TK; ++kk) {
+                const float4 a = *reinterpret_cast<const float4*>(&As[stage][kk][ty * 4]);
+                const float av[4] = {a.x, a.y, a.z, a.w};
+                float bv[NF];
+#pragma unroll
+                for (int j = 0; j < NF; ++j) bv[j] = Bs[stage][kk][tx * NF + j];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < NF; ++j) acc[i * NF + j] = fmaf(av[i], bv[j], acc[i * NF + j]);
+            }
         }
-        __syncthreads();
+        stage = (stage + 1) % STAGES;
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    if (TC) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int m = m0 + ty * 4 + i;
-        if (m >= g.M) continue;
+        for (int j = 0; j < NF; ++j)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int n = n0 + tx * 4 + j;
-            if (n >= g.N) continue;
-            float v = acc[i][j];
-            if (g.bias) v += g.bias[n];
-            v = act_fwd(v, g.act);
-            if (g.D) v *= act_bwd(g.D[(size_t)m * g.ldd + n], g.dact);
-            float* c = g.C + (size_t)m * g.ldc + n;
-            if (g.out == OUT_STORE) *c = v;
-            else if (g.out == OUT_ADD) *c += v;
-            else atomicAdd(c, v);
-        }
+            for (int r = 0; r < 4; ++r)
+                gemm_store(g, m0 + wm + gid + ((r >> 1) << 3), n0 + wn + 8 * j + 2 * tig + (r & 1), acc[j * 4 + r]);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < NF; ++j) gemm_store(g, m0 + ty * 4 + i, n0 + tx * NF + j, acc[i * NF + j]);
+    }
+}
+
+template <bool TA, bool TB>
+void launch_gemm(const GemmArgs& g, bool tc, int tn, dim3 grid, cudaStream_t s) {
+    if (tc) {
+        if (tn == 64) gemm_kernel<TA, TB, true, 64><<<grid, 256, 0, s>>>(g);
+        else gemm_kernel<TA, TB, true, 80><<<grid, 256, 0, s>>>(g);
+    } else {
+        if (tn == 64) gemm_kernel<TA, TB, false, 64><<<grid, 256, 0, s>>>(g);
+        else gemm_kernel<TA, TB, false, 80><<<grid, 256, 0, s>>>(g);
     }
 }
 
@@ -338,6 +443,7 @@ const int OPT_NET[3] = {EXO_TD7_ACTOR, EXO_TD7_CRITIC, EXO_TD7_ENCODER};
 
 struct ExoTD7 {
     int device = 0, n_sm = 148;
+    bool ffma = false;                      // EXO_TD7_FFMA=1: the FP32-pipe GEMM instead of the 3xTF32 tensor-core one
     ExoTD7Config c;
     int64_t launches = 0, steps = 0;
     double sigma = 0;                       // hp.target_policy_noise, decays by policy_noise_decrease per iteration
@@ -367,10 +473,14 @@ struct Ctx {
     void gemm(bool ta, bool tb, GemmArgs g, int splits) {
         if (g.M <= 0 || g.N <= 0 || g.K <= 0) return;
         g.kchunk = splits <= 1 ? g.K : (((g.K + splits - 1) / splits + TK - 1) / TK) * TK;
-        dim3 grid((g.N + TN - 1) / TN, (g.M + TM - 1) / TM, (g.K + g.kchunk - 1) / g.kchunk);
-        if (!ta && tb) sgemm_kernel<false, true><<<grid, 256, 0, s>>>(g);
-        else if (!ta && !tb) sgemm_kernel<false, false><<<grid, 256, 0, s>>>(g);
-        else sgemm_kernel<true, false><<<grid, 256, 0, s>>>(g);
+        const int ks = (g.K + g.kchunk - 1) / g.kchunk, mt = (g.M + TM - 1) / TM;
+        // tile width: the one with the shorter critical path = waves of CTAs x columns per tile
+        auto cost = [&](int tn) { return (long)((mt * ((g.N + tn - 1) / tn) * ks + t->n_sm - 1) / t->n_sm) * tn; };
+        const int tn = cost(80) < cost(64) ? 80 : 64;
+        dim3 grid((g.N + tn - 1) / tn, mt, ks);
+        if (!ta && tb) launch_gemm<false, true>(g, !t->ffma, tn, grid, s);
+        else if (!ta && !tb) launch_gemm<false, false>(g, !t->ffma, tn, grid, s);
+        else launch_gemm<true, false>(g, !t->ffma, tn, grid, s);
         t->launches++;
     }
     // Y = act(X W^T + b)
@@ -393,7 +503,7 @@ struct Ctx {
         GemmArgs g = {};
         g.A = dY; g.lda = lddy; g.B = X; g.ldb = ldx; g.C = grad + L.w; g.ldc = L.in;
         g.M = L.out; g.N = L.in; g.K = B; g.out = OUT_ATOMIC;
-        const int tiles = ((L.out + TM - 1) / TM) * ((L.in + TN - 1) / TN);
+        const int tiles = ((L.out + TM - 1) / TM) * ((L.in + 63) / 64);
         int splits = (2 * t->n_sm + tiles - 1) / tiles;
         splits = std::max(1, std::min(splits, (B + 63) / 64));
         gemm(true, false, g, splits);
@@ -643,6 +753,8 @@ extern "C" int exo_td7_create(int32_t device, const ExoTD7Config* cfg, ExoTD7** 
     TCK(cudaSetDevice(device));
     ExoTD7* t = new ExoTD7();
     t->device = device; t->n_sm = prop.multiProcessorCount; t->c = c; t->sigma = c.target_policy_noise;
+    const char* fm = getenv("EXO_TD7_FFMA");
+    t->ffma = fm && fm[0] != '0';
     const int B = c.batch_rows, S = c.state_dim, A = c.action_dim, Z = c.zs_dim, H = c.enc_hdim, C = c.critic_hdim, Ha = c.actor_hdim;
     t->def[0] = make_def({{Ha, S}, {Ha, Z + Ha}, {Ha, Ha}, {A, Ha}});
     t->def[1] = make_def({{C, S + A}, {C, 2 * Z + C}, {C, C}, {1, C}, {C, S + A}, {C, 2 * Z + C}, {C, C}, {1, C}});

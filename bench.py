@@ -245,6 +245,49 @@ def bench_policy(exo_b200, env, dev, flush, peaks):
     return out
 
 
+def bench_td7(exo_b200, dev):
+    """Next row N2, second half: one Agent.train() iteration (TD7_multi_agent_Pink_noise.py:230-312) at the reference's
+    sizes - 15 tremor types x batch_size 128 = 1920 rows, state 80 / action 7 / zs 300 / hidden 300-320 - with the
+    replay buffer on the device: LAP.sample -> update -> update_priority, no host copy, CUDA events."""
+    import torch
+    envs, bs = 15, 128
+    hp = exo_b200.Hyperparameters(batch_size=bs, buffer_size=20000)
+    t = exo_b200.DeviceTD7(80, 7, 1, hp=hp, env_num=envs, device=dev, init_seed=1)
+    g = torch.Generator(device=dev).manual_seed(3)
+    k = 4096
+    for _ in range(4):                                      # 16 384 transitions, spread over the 15 rows
+        t.replay_buffer.add_batch(torch.randn(k, 80, device=dev, generator=g), torch.rand(k, 7, device=dev, generator=g) * 2 - 1,
+                                  torch.randn(k, 80, device=dev, generator=g), torch.randn(k, device=dev, generator=g),
+                                  torch.rand(k, device=dev, generator=g) < 0.003)
+    for _ in range(10):
+        t.train()
+    l0 = t.launch_count()
+    iters = 100
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    a.record()
+    for _ in range(iters):
+        t.train()
+    b.record()
+    torch.cuda.synchronize(dev)
+    ms = a.elapsed_time(b) / iters
+    batch = t.replay_buffer.sample()
+    a.record()
+    for _ in range(iters):
+        t.train_on_batch(*batch)
+    b.record()
+    torch.cuda.synchronize(dev)
+    ms_upd = a.elapsed_time(b) / iters
+    sc = t.scalars()
+    out = {"kernel": "sgemm_kernel (csrc/exo_td7.cu)", "rows": envs * bs, "train_ms": ms, "train_iterations_per_s": 1e3 / ms,
+           "update_only_ms": ms_upd, "transitions_per_s": envs * bs / (ms * 1e-3), "dtype": "f32 products and sums",
+           "launches_per_iteration": (t.launch_count() - l0) / (2.0 * iters),
+           "what": "LAP.sample + encoder/critic/(actor every 2nd) update + Adam + update_priority per iteration, device resident",
+           "losses": {k: sc[k] for k in ("encoder_loss", "critic_loss", "actor_loss")}}
+    t.close()
+    return out
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU algorithm (oracle port; the Python reference cannot travel to the GPU box
     and needs pybullet) on all host threads, rank 0 only."""
@@ -398,6 +441,7 @@ def main():
     policy_line = None
     if rank == 0 and not args.no_policy:
         policy_line = bench_policy(exo_b200, env, dev, flush, peaks)
+        policy_line["td7_update"] = bench_td7(exo_b200, dev)
     if rank == 0:
         peak = float(peaks.get("hbm_gbs", 6650.0))
         achieved = ALGO_BYTES_PER_ENV_STEP * n / (kms * 1e-3) / 1e9

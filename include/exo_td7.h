@@ -14,9 +14,11 @@
  * torch's default betas/eps) in device memory. The offline TD3+BC term (:292-293) is not built (offline=False in the
  * reference's training script).
  *
- * Arithmetic: float32 products and sums on the FP32 pipe (torch's default matmul), csrc/exo_td7.cu. Gradients are
- * hand-derived; weight gradients are summed over the batch with split-K atomics, so two runs agree to summation order,
- * not bit for bit.
+ * Arithmetic (csrc/exo_td7.cu): float32 storage, sums and element-wise math; the matrix products run on the tensor
+ * cores as 3xTF32 (each operand split into two TF32 parts, three MMAs, float32 accumulation: every product within
+ * 2^-21 of the float32 one), or - environment EXO_TD7_FFMA=1 at exo_td7_create - as float32 FFMA on the FP32 pipe, the
+ * arithmetic of torch's default matmul. Gradients are hand-derived; weight gradients are summed over the batch with
+ * split-K atomics, so two runs agree to summation order, not bit for bit. Tolerances: tests/test_td7.py.
  *
  * Conventions as in exo_env.h: plain C types, batch pointers are device pointers owned by the caller, kernels launch on
  * the caller's stream, int status + exo_last_error(). Layer sizes are arguments (the reference's Hyperparameters), not

@@ -117,13 +117,14 @@ def main():
     ap.add_argument("--envs", type=int, default=15)
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--iters", type=int, default=200)
+    ap.add_argument("--device-only", action="store_true", help="skip the torch stand-in (for ncu captures)")
     args = ap.parse_args()
     torch.backends.cuda.matmul.allow_tf32 = False
     torch.backends.cudnn.allow_tf32 = False
     dev = torch.device("cuda:0")
     hp = exo_b200.Hyperparameters(batch_size=args.batch)
     t = exo_b200.DeviceTD7(80, 7, 1, hp=hp, env_num=args.envs, device=dev, replay_buffer=False, init_seed=1)
-    ref = TorchTD7(t, dev)
+    ref = None if args.device_only else TorchTD7(t, dev)
     B = args.envs * args.batch
     g = torch.Generator(device=dev).manual_seed(0)
     def batch():
@@ -134,15 +135,17 @@ def main():
     # parity over a few iterations
     for i in range(6):
         p1, _ = t.train_on_batch(*batches[i])
+        if ref is None:
+            continue
         p2 = ref.train(*batches[i])
         print("iter %d: priority max |diff| %.2e" % (i + 1, float((p1 - p2).abs().max())))
-    for n in ("actor", "critic", "encoder"):
+    for n in (("actor", "critic", "encoder") if ref is not None else ()):
         sd, rd = t.state_dict(n), ref.nets[n].state_dict()
         d = torch.cat([(sd[k] - rd[k].cpu()).abs().reshape(-1) for k in sd])
         print("%-8s params after 6 iterations: max |diff| %.2e, share within 2e-6: %.5f" % (n, float(d.max()), float((d < 2e-6).float().mean())))
     out = {}
     for name, fn in (("device TD7 (libexo_env)", lambda b: t.train_on_batch(*b)), ("torch autograd + Adam", lambda b: ref.train(*b)),
-                     ("torch, no per-iteration readback", lambda b: ref.train(*b, sync_scalars=False))):
+                     ("torch, no per-iteration readback", lambda b: ref.train(*b, sync_scalars=False)))[:1 if ref is None else 3]:
         for i in range(10):
             fn(batches[i % 8])
         torch.cuda.synchronize()
