@@ -454,7 +454,10 @@ struct ExoTD7 {
     float* sc = nullptr;
     std::vector<float*> owned;
     // activations ([batch_rows, *])
-    float *t_h1, *t_h2, *t_z3, *next_zs;                       // no-grad encoder passes
+    cudaStream_t side[2] = {nullptr, nullptr};                 // the target branch and the fixed-encoder branch run beside the encoder update
+    cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
+    float *t_h1, *t_h2, *t_z3, *next_zs;                       // no-grad encoder passes (target branch)
+    float *n_h1, *n_h2, *n_z3, *f_h1, *f_h2, *f_z3;            // the same scratch for the other two branches
     float *e_h1, *e_h2, *e_z3, *e_cat, *e_g1, *e_g2, *e_pred;  // encoder update
     float *tzs, *t_cat, *tzsa, *na, *rn;                       // target
     float *a_u, *a_cat, *a_h1, *a_h2, *act;                    // actor (target pass, then the actor update's cache)
@@ -608,8 +611,42 @@ extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const 
     t->steps++;
     TCK(cudaMemsetAsync(t->sc + SC_ENC_LOSS, 0, 2 * sizeof(float), s));
 
-    // ---- encoder update (:238-246)
-    x.enc_zs(enc, sN, t->next_zs, Z, t->t_h1, t->t_h2, t->t_z3);
+    // Three independent branches until the critic update needs Q_target and fixed_zsa: the encoder update stays on the
+    // caller's stream, the target computation and the fixed-encoder passes run on two side streams (fork / join by events).
+    TCK(cudaEventRecord(t->ev_fork, s));
+    Ctx xt{t, t->side[0], B}, xf{t, t->side[1], B};
+    TCK(cudaStreamWaitEvent(xt.s, t->ev_fork, 0));
+    TCK(cudaStreamWaitEvent(xf.s, t->ev_fork, 0));
+
+    // ---- critic target (:251-264), side stream 0
+    xt.enc_zs(fet, sN, t->tzs, Z, t->t_h1, t->t_h2, t->t_z3);
+    xt.actor_fwd(t->net[EXO_TD7_ACTOR_TARGET], sN, t->tzs, t->na);
+    const float* rn = randn_dev;
+    if (!rn) {
+        randn_kernel<<<(B * A + 255) / 256, 256, 0, xt.s>>>(t->rn, B * A, c.seed, (uint64_t)t->steps);
+        t->launches++;
+        rn = t->rn;
+    }
+    target_action_kernel<<<(B * A + 255) / 256, 256, 0, xt.s>>>(t->na, rn, B * A, (float)t->sigma, c.noise_clip);
+    t->launches++;
+    t->sigma -= (double)c.policy_noise_decrease;
+    xt.copy(t->t_cat, Z + A, t->tzs, Z, Z);
+    xt.copy(t->t_cat + Z, Z + A, t->na, A, A);
+    xt.enc_zsa(fet, t->t_cat, t->t_h1, t->t_h2, t->tzsa);
+    xt.critic_fwd(t->net[EXO_TD7_CRITIC_TARGET], sN, t->na, t->tzsa, t->tzs);
+    q_target_kernel<<<1, 1024, 0, xt.s>>>(t->q2, sR, sD, t->qt, B, c.discount, t->sc);
+    t->launches++;
+    TCK(cudaEventRecord(t->ev_join[0], xt.s));
+
+    // ---- fixed_zs, fixed_zsa (:266-267), side stream 1
+    xf.enc_zs(fe, sS, t->fzs, Z, t->f_h1, t->f_h2, t->f_z3);
+    xf.copy(t->f_cat, Z + A, t->fzs, Z, Z);
+    xf.copy(t->f_cat + Z, Z + A, sA, A, A);
+    xf.enc_zsa(fe, t->f_cat, t->f_g1, t->f_g2, t->fzsa);
+    TCK(cudaEventRecord(t->ev_join[1], xf.s));
+
+    // ---- encoder update (:238-246), caller's stream
+    x.enc_zs(enc, sN, t->next_zs, Z, t->n_h1, t->n_h2, t->n_z3);
     x.enc_zs(enc, sS, t->e_cat, Z + A, t->e_h1, t->e_h2, t->e_z3);
     x.copy(t->e_cat + Z, Z + A, sA, A, A);
     x.enc_zsa(enc, t->e_cat, t->e_g1, t->e_g2, t->e_pred);
@@ -636,30 +673,9 @@ extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const 
     }
     x.adam(EXO_TD7_OPT_ENCODER, c.encoder_lr);
 
-    // ---- critic target (:251-264)
-    x.enc_zs(fet, sN, t->tzs, Z, t->t_h1, t->t_h2, t->t_z3);
-    x.actor_fwd(t->net[EXO_TD7_ACTOR_TARGET], sN, t->tzs, t->na);
-    const float* rn = randn_dev;
-    if (!rn) {
-        randn_kernel<<<(B * A + 255) / 256, 256, 0, s>>>(t->rn, B * A, c.seed, (uint64_t)t->steps);
-        t->launches++;
-        rn = t->rn;
-    }
-    target_action_kernel<<<(B * A + 255) / 256, 256, 0, s>>>(t->na, rn, B * A, (float)t->sigma, c.noise_clip);
-    t->launches++;
-    t->sigma -= (double)c.policy_noise_decrease;
-    x.copy(t->t_cat, Z + A, t->tzs, Z, Z);
-    x.copy(t->t_cat + Z, Z + A, t->na, A, A);
-    x.enc_zsa(fet, t->t_cat, t->t_h1, t->t_h2, t->tzsa);
-    x.critic_fwd(t->net[EXO_TD7_CRITIC_TARGET], sN, t->na, t->tzsa, t->tzs);
-    q_target_kernel<<<1, 1024, 0, s>>>(t->q2, sR, sD, t->qt, B, c.discount, t->sc);
-    t->launches++;
-
-    // ---- critic update (:266-276) and priorities (:281)
-    x.enc_zs(fe, sS, t->fzs, Z, t->t_h1, t->t_h2, t->t_z3);
-    x.copy(t->f_cat, Z + A, t->fzs, Z, Z);
-    x.copy(t->f_cat + Z, Z + A, sA, A, A);
-    x.enc_zsa(fe, t->f_cat, t->f_g1, t->f_g2, t->fzsa);
+    // ---- join; critic update (:268-276) and priorities (:281)
+    TCK(cudaStreamWaitEvent(s, t->ev_join[0], 0));
+    TCK(cudaStreamWaitEvent(s, t->ev_join[1], 0));
     x.critic_fwd(critic, sS, sA, t->fzsa, t->fzs);
     td_head_kernel<<<(B + 255) / 256, 256, 0, s>>>(t->q2, t->qt, t->dq, prio, B, c.min_priority, c.alpha, t->sc);
     t->launches++;
@@ -733,7 +749,13 @@ extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const 
 extern "C" int exo_td7_destroy(ExoTD7* t) {
     if (!t) return EXO_OK;
     cudaSetDevice(t->device);
+    cudaDeviceSynchronize();
     for (float* p : t->owned) cudaFree(p);
+    for (int i = 0; i < 2; ++i) {
+        if (t->side[i]) cudaStreamDestroy(t->side[i]);
+        if (t->ev_join[i]) cudaEventDestroy(t->ev_join[i]);
+    }
+    if (t->ev_fork) cudaEventDestroy(t->ev_fork);
     delete t;
     return EXO_OK;
 }
@@ -775,6 +797,12 @@ extern "C" int exo_td7_create(int32_t device, const ExoTD7Config* cfg, ExoTD7** 
     t->sc = alloc(SC_COUNT);
     auto rows = [&](int w) { return alloc((size_t)B * w); };
     t->t_h1 = rows(H); t->t_h2 = rows(H); t->t_z3 = rows(Z); t->next_zs = rows(Z);
+    t->n_h1 = rows(H); t->n_h2 = rows(H); t->n_z3 = rows(Z); t->f_h1 = rows(H); t->f_h2 = rows(H); t->f_z3 = rows(Z);
+    for (int i = 0; i < 2 && err == cudaSuccess; ++i) {
+        err = cudaStreamCreateWithFlags(&t->side[i], cudaStreamNonBlocking);
+        if (err == cudaSuccess) err = cudaEventCreateWithFlags(&t->ev_join[i], cudaEventDisableTiming);
+    }
+    if (err == cudaSuccess) err = cudaEventCreateWithFlags(&t->ev_fork, cudaEventDisableTiming);
     t->e_h1 = rows(H); t->e_h2 = rows(H); t->e_z3 = rows(Z); t->e_cat = rows(Z + A); t->e_g1 = rows(H); t->e_g2 = rows(H); t->e_pred = rows(Z);
     t->tzs = rows(Z); t->t_cat = rows(Z + A); t->tzsa = rows(Z); t->na = rows(A); t->rn = rows(A);
     t->a_u = rows(Ha); t->a_cat = rows(Ha + Z); t->a_h1 = rows(Ha); t->a_h2 = rows(Ha); t->act = rows(A);
