@@ -454,8 +454,13 @@ struct ExoTD7 {
     float* sc = nullptr;
     std::vector<float*> owned;
     // activations ([batch_rows, *])
-    cudaStream_t side[2] = {nullptr, nullptr};                 // the target branch and the fixed-encoder branch run beside the encoder update
+    // side streams: 0 the target branch, 1 the fixed-encoder branch (both beside the encoder update), 2 the critic's
+    // second head, 3 the weight gradients (off the dX chain, which is the critical path of every backward pass)
+    cudaStream_t side[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
+    cudaEvent_t evs[32] = {};
+    int ev_next = 0;
+    float *G[6], *G2[4];                                        // per-layer gradient buffers of a backward pass (main chain, head 1)
     float *t_h1, *t_h2, *t_z3, *next_zs;                       // no-grad encoder passes (target branch)
     float *n_h1, *n_h2, *n_z3, *f_h1, *f_h2, *f_z3;            // the same scratch for the other two branches
     float *e_h1, *e_h2, *e_z3, *e_cat, *e_g1, *e_g2, *e_pred;  // encoder update
@@ -515,6 +520,22 @@ struct Ctx {
         colsum_kernel<<<dim3((L.out + 31) / 32, (B + rps - 1) / rps), dim3(32, 8), 0, s>>>(dY, lddy, grad + L.b, B, L.out, rps);
         t->launches++;
     }
+    // `other` waits for everything enqueued so far on this stream
+    void before(cudaStream_t other) {
+        cudaEvent_t e = t->evs[t->ev_next++ & 31];
+        cudaEventRecord(e, s);
+        cudaStreamWaitEvent(other, e, 0);
+    }
+    // the weight gradient of a layer on the weight-gradient stream, as soon as this stream has produced dY
+    void dw_side(float* grad, const Lin& L, const float* dY, int lddy, const float* X, int ldx) {
+        Ctx w{t, t->side[3], B};
+        before(w.s);
+        w.dw(grad, L, dY, lddy, X, ldx);
+    }
+    void join_dw() {
+        Ctx w{t, t->side[3], B};
+        w.before(s);
+    }
     void avgl1(const float* x, int ldx, float* y, int ldy, int n) {
         avgl1_fwd_kernel<<<(B + 7) / 8, 256, 0, s>>>(x, ldx, y, ldy, B, n);
         t->launches++;
@@ -567,22 +588,27 @@ struct Ctx {
         fwd(net, d.L[2], t->a_h1, Ha, t->a_h2, Ha, ACT_RELU);
         fwd(net, d.L[3], t->a_h2, Ha, out, A, ACT_TANH);
     }
-    // Critic.forward (:128-144): sa = cat[s, a], per head cat[AvgL1Norm(q0h(sa)), zsa, zs] -> q2[:, h]
+    // Critic.forward (:128-144): sa = cat[s, a], per head cat[AvgL1Norm(q0h(sa)), zsa, zs] -> q2[:, h]; the second head
+    // runs on side stream 2
     void critic_fwd(const float* net, const float* X, const float* a, const float* zsa, const float* zs) {
         const NetDef& d = t->def[1];
         const int S = t->c.state_dim, A = t->c.action_dim, C = t->c.critic_hdim, Z = t->c.zs_dim, W = C + 2 * Z;
         copy(t->c_sa, S + A, X, S, S);
         copy(t->c_sa + S, S + A, a, A, A);
+        Ctx h1{t, t->side[2], B};
+        before(h1.s);
         for (int h = 0; h < 2; ++h) {
-            copy(t->c_cat[h] + C, W, zsa, Z, Z);
-            copy(t->c_cat[h] + C + Z, W, zs, Z, Z);
+            Ctx& x = h ? h1 : *this;
+            x.copy(t->c_cat[h] + C, W, zsa, Z, Z);
+            x.copy(t->c_cat[h] + C + Z, W, zs, Z, Z);
             const Lin* L = &d.L[4 * h];
-            fwd(net, L[0], t->c_sa, S + A, t->c_u[h], C, ACT_NONE);
-            avgl1(t->c_u[h], C, t->c_cat[h], W, C);
-            fwd(net, L[1], t->c_cat[h], W, t->c_h1[h], C, ACT_ELU);
-            fwd(net, L[2], t->c_h1[h], C, t->c_h2[h], C, ACT_ELU);
-            fwd(net, L[3], t->c_h2[h], C, t->q2 + h, 2, ACT_NONE);
+            x.fwd(net, L[0], t->c_sa, S + A, t->c_u[h], C, ACT_NONE);
+            x.avgl1(t->c_u[h], C, t->c_cat[h], W, C);
+            x.fwd(net, L[1], t->c_cat[h], W, t->c_h1[h], C, ACT_ELU);
+            x.fwd(net, L[2], t->c_h1[h], C, t->c_h2[h], C, ACT_ELU);
+            x.fwd(net, L[3], t->c_h2[h], C, t->q2 + h, 2, ACT_NONE);
         }
+        h1.before(s);
     }
 };
 
@@ -652,24 +678,26 @@ extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const 
     x.enc_zsa(enc, t->e_cat, t->e_g1, t->e_g2, t->e_pred);
     {
         const size_t n = (size_t)B * Z;
-        mse_grad_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(t->e_pred, t->next_zs, t->dA, n, t->sc);
+        mse_grad_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(t->e_pred, t->next_zs, t->G[0], n, t->sc);
         t->launches++;
     }
     x.zero_grad(EXO_TD7_OPT_ENCODER);
     {
         float* g = t->grad[EXO_TD7_OPT_ENCODER];
-        x.dw(g, DE.L[5], t->dA, Z, t->e_g2, H);
-        x.dx(enc, DE.L[5], t->dA, Z, t->dB, H, 0, H, t->e_g2, H, ACT_ELU);
-        x.dw(g, DE.L[4], t->dB, H, t->e_g1, H);
-        x.dx(enc, DE.L[4], t->dB, H, t->dA, H, 0, H, t->e_g1, H, ACT_ELU);
-        x.dw(g, DE.L[3], t->dA, H, t->e_cat, Z + A);
-        x.dx(enc, DE.L[3], t->dA, H, t->dB, Z, 0, Z, nullptr, 0, ACT_NONE);
-        x.avgl1_bwd(t->dB, Z, t->e_z3, Z, t->dB, Z, Z);
-        x.dw(g, DE.L[2], t->dB, Z, t->e_h2, H);
-        x.dx(enc, DE.L[2], t->dB, Z, t->dA, H, 0, H, t->e_h2, H, ACT_ELU);
-        x.dw(g, DE.L[1], t->dA, H, t->e_h1, H);
-        x.dx(enc, DE.L[1], t->dA, H, t->dB, H, 0, H, t->e_h1, H, ACT_ELU);
-        x.dw(g, DE.L[0], t->dB, H, sS, S);
+        float** G = t->G;
+        x.dw_side(g, DE.L[5], G[0], Z, t->e_g2, H);
+        x.dx(enc, DE.L[5], G[0], Z, G[1], H, 0, H, t->e_g2, H, ACT_ELU);
+        x.dw_side(g, DE.L[4], G[1], H, t->e_g1, H);
+        x.dx(enc, DE.L[4], G[1], H, G[2], H, 0, H, t->e_g1, H, ACT_ELU);
+        x.dw_side(g, DE.L[3], G[2], H, t->e_cat, Z + A);
+        x.dx(enc, DE.L[3], G[2], H, G[3], Z, 0, Z, nullptr, 0, ACT_NONE);
+        x.avgl1_bwd(G[3], Z, t->e_z3, Z, G[3], Z, Z);
+        x.dw_side(g, DE.L[2], G[3], Z, t->e_h2, H);
+        x.dx(enc, DE.L[2], G[3], Z, G[4], H, 0, H, t->e_h2, H, ACT_ELU);
+        x.dw_side(g, DE.L[1], G[4], H, t->e_h1, H);
+        x.dx(enc, DE.L[1], G[4], H, G[5], H, 0, H, t->e_h1, H, ACT_ELU);
+        x.dw_side(g, DE.L[0], G[5], H, sS, S);
+        x.join_dw();
     }
     x.adam(EXO_TD7_OPT_ENCODER, c.encoder_lr);
 
@@ -680,18 +708,26 @@ extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const 
     td_head_kernel<<<(B + 255) / 256, 256, 0, s>>>(t->q2, t->qt, t->dq, prio, B, c.min_priority, c.alpha, t->sc);
     t->launches++;
     x.zero_grad(EXO_TD7_OPT_CRITIC);
-    for (int h = 0; h < 2; ++h) {
-        float* g = t->grad[EXO_TD7_OPT_CRITIC];
-        const Lin* L = &DC.L[4 * h];
-        const int W = C + 2 * Z;
-        x.dw(g, L[3], t->dq + h, 2, t->c_h2[h], C);
-        x.dx(critic, L[3], t->dq + h, 2, t->dA, C, 0, C, t->c_h2[h], C, ACT_ELU);
-        x.dw(g, L[2], t->dA, C, t->c_h1[h], C);
-        x.dx(critic, L[2], t->dA, C, t->dB, C, 0, C, t->c_h1[h], C, ACT_ELU);
-        x.dw(g, L[1], t->dB, C, t->c_cat[h], W);
-        x.dx(critic, L[1], t->dB, C, t->dA, C, 0, C, nullptr, 0, ACT_NONE);
-        x.avgl1_bwd(t->dA, C, t->c_u[h], C, t->dA, C, C);
-        x.dw(g, L[0], t->dA, C, t->c_sa, S + A);
+    {
+        Ctx h1{t, t->side[2], B};
+        x.before(h1.s);
+        for (int h = 0; h < 2; ++h) {
+            Ctx& y = h ? h1 : x;
+            float** G = h ? t->G2 : t->G;
+            float* g = t->grad[EXO_TD7_OPT_CRITIC];
+            const Lin* L = &DC.L[4 * h];
+            const int W = C + 2 * Z;
+            y.dw_side(g, L[3], t->dq + h, 2, t->c_h2[h], C);
+            y.dx(critic, L[3], t->dq + h, 2, G[0], C, 0, C, t->c_h2[h], C, ACT_ELU);
+            y.dw_side(g, L[2], G[0], C, t->c_h1[h], C);
+            y.dx(critic, L[2], G[0], C, G[1], C, 0, C, t->c_h1[h], C, ACT_ELU);
+            y.dw_side(g, L[1], G[1], C, t->c_cat[h], W);
+            y.dx(critic, L[1], G[1], C, G[2], C, 0, C, nullptr, 0, ACT_NONE);
+            y.avgl1_bwd(G[2], C, t->c_u[h], C, G[2], C, C);
+            y.dw_side(g, L[0], G[2], C, t->c_sa, S + A);
+        }
+        h1.before(s);
+        x.join_dw();
     }
     x.adam(EXO_TD7_OPT_CRITIC, c.critic_lr);
 
@@ -704,15 +740,22 @@ extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const 
         x.critic_fwd(critic, sS, t->act, t->fzsa, t->fzs);
         actor_head_kernel<<<(2 * B + 255) / 256, 256, 0, s>>>(t->q2, t->dq, B, t->sc);
         t->launches++;
-        for (int h = 0; h < 2; ++h) {            // the critic's input gradients: d action (through sa) and d zsa
-            const Lin* L = &DC.L[4 * h];
-            const int mode = h ? OUT_ADD : OUT_STORE;
-            x.dx(critic, L[3], t->dq + h, 2, t->dA, C, 0, C, t->c_h2[h], C, ACT_ELU);
-            x.dx(critic, L[2], t->dA, C, t->dB, C, 0, C, t->c_h1[h], C, ACT_ELU);
-            x.dx(critic, L[1], t->dB, C, t->d_zsa, Z, C, Z, nullptr, 0, ACT_NONE, mode);
-            x.dx(critic, L[1], t->dB, C, t->dA, C, 0, C, nullptr, 0, ACT_NONE);
-            x.avgl1_bwd(t->dA, C, t->c_u[h], C, t->dA, C, C);
-            x.dx(critic, L[0], t->dA, C, t->d_act1, A, S, A, nullptr, 0, ACT_NONE, mode);
+        {                                        // the critic's input gradients: d action (through sa) and d zsa
+            Ctx h1{t, t->side[2], B};
+            x.before(h1.s);
+            for (int h = 0; h < 2; ++h) {
+                Ctx& y = h ? h1 : x;
+                float** G = h ? t->G2 : t->G;
+                const Lin* L = &DC.L[4 * h];
+                y.dx(critic, L[3], t->dq + h, 2, G[0], C, 0, C, t->c_h2[h], C, ACT_ELU);
+                y.dx(critic, L[2], G[0], C, G[1], C, 0, C, t->c_h1[h], C, ACT_ELU);
+                y.dx(critic, L[1], G[1], C, G[2], C, 0, C, nullptr, 0, ACT_NONE);
+                y.avgl1_bwd(G[2], C, t->c_u[h], C, G[2], C, C);
+                if (h) x.before(h1.s);           // head 0 has stored d_zsa and d_act1: head 1 adds to them
+                y.dx(critic, L[1], G[1], C, t->d_zsa, Z, C, Z, nullptr, 0, ACT_NONE, h ? OUT_ADD : OUT_STORE);
+                y.dx(critic, L[0], G[2], C, t->d_act1, A, S, A, nullptr, 0, ACT_NONE, h ? OUT_ADD : OUT_STORE);
+            }
+            h1.before(s);
         }
         x.dx(fe, DE.L[5], t->d_zsa, Z, t->dA, H, 0, H, t->f_g2, H, ACT_ELU);       // fixed_encoder.zsa's d action
         x.dx(fe, DE.L[4], t->dA, H, t->dB, H, 0, H, t->f_g1, H, ACT_ELU);
@@ -721,14 +764,16 @@ extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const 
         t->launches++;
         x.zero_grad(EXO_TD7_OPT_ACTOR);
         float* g = t->grad[EXO_TD7_OPT_ACTOR];
-        x.dw(g, DA.L[3], t->dT, A, t->a_h2, Ha);
-        x.dx(actor, DA.L[3], t->dT, A, t->dA, Ha, 0, Ha, t->a_h2, Ha, ACT_RELU);
-        x.dw(g, DA.L[2], t->dA, Ha, t->a_h1, Ha);
-        x.dx(actor, DA.L[2], t->dA, Ha, t->dB, Ha, 0, Ha, t->a_h1, Ha, ACT_RELU);
-        x.dw(g, DA.L[1], t->dB, Ha, t->a_cat, Ha + Z);
-        x.dx(actor, DA.L[1], t->dB, Ha, t->dA, Ha, 0, Ha, nullptr, 0, ACT_NONE);
-        x.avgl1_bwd(t->dA, Ha, t->a_u, Ha, t->dA, Ha, Ha);
-        x.dw(g, DA.L[0], t->dA, Ha, sS, S);
+        float** G = t->G;
+        x.dw_side(g, DA.L[3], t->dT, A, t->a_h2, Ha);
+        x.dx(actor, DA.L[3], t->dT, A, G[0], Ha, 0, Ha, t->a_h2, Ha, ACT_RELU);
+        x.dw_side(g, DA.L[2], G[0], Ha, t->a_h1, Ha);
+        x.dx(actor, DA.L[2], G[0], Ha, G[1], Ha, 0, Ha, t->a_h1, Ha, ACT_RELU);
+        x.dw_side(g, DA.L[1], G[1], Ha, t->a_cat, Ha + Z);
+        x.dx(actor, DA.L[1], G[1], Ha, G[2], Ha, 0, Ha, nullptr, 0, ACT_NONE);
+        x.avgl1_bwd(G[2], Ha, t->a_u, Ha, G[2], Ha, Ha);
+        x.dw_side(g, DA.L[0], G[2], Ha, sS, S);
+        x.join_dw();
         x.adam(EXO_TD7_OPT_ACTOR, c.actor_lr);
     }
 
@@ -751,10 +796,12 @@ extern "C" int exo_td7_destroy(ExoTD7* t) {
     cudaSetDevice(t->device);
     cudaDeviceSynchronize();
     for (float* p : t->owned) cudaFree(p);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < 4; ++i)
         if (t->side[i]) cudaStreamDestroy(t->side[i]);
+    for (int i = 0; i < 2; ++i)
         if (t->ev_join[i]) cudaEventDestroy(t->ev_join[i]);
-    }
+    for (int i = 0; i < 32; ++i)
+        if (t->evs[i]) cudaEventDestroy(t->evs[i]);
     if (t->ev_fork) cudaEventDestroy(t->ev_fork);
     delete t;
     return EXO_OK;
@@ -798,10 +845,9 @@ extern "C" int exo_td7_create(int32_t device, const ExoTD7Config* cfg, ExoTD7** 
     auto rows = [&](int w) { return alloc((size_t)B * w); };
     t->t_h1 = rows(H); t->t_h2 = rows(H); t->t_z3 = rows(Z); t->next_zs = rows(Z);
     t->n_h1 = rows(H); t->n_h2 = rows(H); t->n_z3 = rows(Z); t->f_h1 = rows(H); t->f_h2 = rows(H); t->f_z3 = rows(Z);
-    for (int i = 0; i < 2 && err == cudaSuccess; ++i) {
-        err = cudaStreamCreateWithFlags(&t->side[i], cudaStreamNonBlocking);
-        if (err == cudaSuccess) err = cudaEventCreateWithFlags(&t->ev_join[i], cudaEventDisableTiming);
-    }
+    for (int i = 0; i < 4 && err == cudaSuccess; ++i) err = cudaStreamCreateWithFlags(&t->side[i], cudaStreamNonBlocking);
+    for (int i = 0; i < 2 && err == cudaSuccess; ++i) err = cudaEventCreateWithFlags(&t->ev_join[i], cudaEventDisableTiming);
+    for (int i = 0; i < 32 && err == cudaSuccess; ++i) err = cudaEventCreateWithFlags(&t->evs[i], cudaEventDisableTiming);
     if (err == cudaSuccess) err = cudaEventCreateWithFlags(&t->ev_fork, cudaEventDisableTiming);
     t->e_h1 = rows(H); t->e_h2 = rows(H); t->e_z3 = rows(Z); t->e_cat = rows(Z + A); t->e_g1 = rows(H); t->e_g2 = rows(H); t->e_pred = rows(Z);
     t->tzs = rows(Z); t->t_cat = rows(Z + A); t->tzsa = rows(Z); t->na = rows(A); t->rn = rows(A);
@@ -811,7 +857,9 @@ extern "C" int exo_td7_create(int32_t device, const ExoTD7Config* cfg, ExoTD7** 
     for (int h = 0; h < 2; ++h) { t->c_u[h] = rows(C); t->c_cat[h] = rows(C + 2 * Z); t->c_h1[h] = rows(C); t->c_h2[h] = rows(C); }
     t->q2 = rows(2); t->qt = rows(1); t->dq = rows(2);
     const int wmax = std::max(std::max(H, C), std::max(Ha, Z));
-    t->dA = rows(wmax); t->dB = rows(wmax); t->d_zsa = rows(Z); t->d_act1 = rows(A); t->d_act2 = rows(A); t->dT = rows(A);
+    t->dA = rows(wmax); t->dB = rows(wmax);
+    for (int i = 0; i < 6; ++i) t->G[i] = rows(wmax);
+    for (int i = 0; i < 4; ++i) t->G2[i] = rows(wmax); t->d_zsa = rows(Z); t->d_act1 = rows(A); t->d_act2 = rows(A); t->dT = rows(A);
     if (err == cudaSuccess) {
         const float init[SC_COUNT] = {-1e8f, 1e8f, 0.f, 0.f, 0.f, 0.f, 0.f};      // Agent.__init__ :179-182
         err = cudaMemcpy(t->sc, init, sizeof(init), cudaMemcpyHostToDevice);
