@@ -45,6 +45,9 @@ class ExoTD7Config(C.Structure):
                [("seed", C.c_uint64)]
 
 
+EXO_TD7_GRAD_HOOK = C.CFUNCTYPE(None, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p)
+
+
 class ExoInfo(C.Structure):
     _fields_ = [(k, C.c_void_p) for k in ("actuator_torques", "torque_val", "ampl_val", "tremor_torque_val",
                                           "tremor_ampl_val", "reward_parts", "amp_metric")]
@@ -111,6 +114,7 @@ SIGNATURES = {
     "exo_td7_train": (C.c_int, [C.c_void_p] + [C.c_void_p] * 7 + [C.POINTER(C.c_int32), C.c_void_p]),
     "exo_td7_scalars": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "exo_td7_set_scalars": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
+    "exo_td7_set_grad_hook": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "exo_td7_randn": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
     "exo_td7_launch_count": (C.c_int64, [C.c_void_p]),
 }

@@ -443,6 +443,8 @@ const int OPT_NET[3] = {EXO_TD7_ACTOR, EXO_TD7_CRITIC, EXO_TD7_ENCODER};
 
 struct ExoTD7 {
     int device = 0, n_sm = 148;
+    ExoTD7GradHook hook = nullptr;
+    void* hook_user = nullptr;
     bool ffma = false;                      // EXO_TD7_FFMA=1: the FP32-pipe GEMM instead of the 3xTF32 tensor-core one
     ExoTD7Config c;
     int64_t launches = 0, steps = 0;
@@ -552,6 +554,7 @@ struct Ctx {
     void adam(int opt, float lr) {
         const int net = OPT_NET[opt];
         const size_t n = t->def[kind_of(net)].size;
+        if (t->hook) t->hook(opt, t->grad[opt], (int64_t)n, (void*)s, t->hook_user);      // data-parallel: all-reduce first
         const int64_t k = ++t->opt_step[opt];
         const double bc1 = 1.0 - pow(0.9, (double)k), bc2 = 1.0 - pow(0.999, (double)k);
         adam_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(t->net[net], t->grad[opt], t->m[opt], t->v[opt], n, t->c.weight_decay,
@@ -941,6 +944,13 @@ extern "C" int exo_td7_set_scalars(ExoTD7* t, const double* in) {
     TCK(cudaMemcpy(t->sc, h, sizeof(h), cudaMemcpyHostToDevice));
     t->sigma = in[4];
     t->steps = (int64_t)in[5];
+    return EXO_OK;
+}
+
+extern "C" int exo_td7_set_grad_hook(ExoTD7* t, ExoTD7GradHook hook, void* user) {
+    if (!t) return exo_set_error(EXO_ERR_ARG, "exo_td7_set_grad_hook: null handle");
+    t->hook = hook;
+    t->hook_user = user;
     return EXO_OK;
 }
 

@@ -20,7 +20,7 @@ import numpy as np
 import torch
 
 from . import _capi
-from .lap import LAP
+from .lap import LAP, _from_device_pointer
 
 NETS = ("actor", "actor_target", "checkpoint_actor", "critic", "critic_target", "encoder", "fixed_encoder",
         "fixed_encoder_target", "checkpoint_encoder")
@@ -103,7 +103,7 @@ class DeviceTD7(object):
     """Agent's learner on one B200. Constructor arguments as Agent.__init__ (:148-149) plus the device."""
 
     def __init__(self, state_dim, action_dim, max_action=1, learning_steps=6000000, offline=False, hp=None, env_num=15,
-                 device="cuda:0", seed=0, replay_buffer=True, init_seed=None):
+                 device="cuda:0", seed=0, replay_buffer=True, init_seed=None, process_group=None):
         if offline:
             raise NotImplementedError("the offline TD3+BC term (:292-293) is not built; the training script runs offline=False")
         self.hp = hp if hp is not None else Hyperparameters()
@@ -143,6 +143,31 @@ class DeviceTD7(object):
         self.best_min_return = -1e8
         if init_seed is not None:
             self.init_networks(init_seed)
+        self._group, self._hook, self._hook_error = None, None, None
+        if process_group is not None:
+            self.set_process_group(process_group)
+
+    # ------------------------------------------------------------------ data-parallel learners
+    def set_process_group(self, group):
+        """One learner per GPU (torch.distributed, NCCL): every rank samples its own batch from its own replay-buffer shard,
+        the gradients are averaged over the ranks before each Adam step (exo_td7_set_grad_hook), and the value bounds are
+        max / min-reduced at roll-over - N ranks x batch_rows rows behave like one Agent.train() on N x batch_rows rows.
+        `group`: a torch.distributed process group, or True for the default group. All ranks must start from the same
+        networks (same init_seed or the same files)."""
+        import torch.distributed as dist
+        self._group = None if group is True else group
+        world = dist.get_world_size(self._group)
+
+        def hook(opt, ptr, n, stream, user):
+            try:
+                g = _from_device_pointer(ptr, n, self.device)
+                dist.all_reduce(g, op=dist.ReduceOp.SUM, group=self._group)       # ordered after the backward pass on the current stream
+                g.mul_(1.0 / world)
+            except BaseException as e:                                            # a ctypes callback cannot raise
+                self._hook_error = e
+        self._hook = _capi.EXO_TD7_GRAD_HOOK(hook)                                # keep the thunk alive
+        self._dist = dist
+        _capi.check(self.lib.exo_td7_set_grad_hook(self.h, C.cast(self._hook, C.c_void_p), None))
 
     # ------------------------------------------------------------------ networks
     def init_networks(self, seed=0):
@@ -235,7 +260,21 @@ class DeviceTD7(object):
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         _capi.check(self.lib.exo_td7_train(self.h, *[C.c_void_p(t.data_ptr()) for t in ts], C.c_void_p(rn.data_ptr()) if rn is not None else None,
                                            C.c_void_p(out.data_ptr()), C.byref(rolled), stream))
+        if self._hook_error is not None:
+            e, self._hook_error = self._hook_error, None
+            raise e
+        if rolled.value and self._hook is not None:
+            self._reduce_value_bounds()
         return out, bool(rolled.value)
+
+    def _reduce_value_bounds(self):
+        """max / min over the ranks at roll-over (:311-312 for the union of the ranks' batches). Synchronises; once per
+        target_update_rate iterations."""
+        sc = self.scalars()
+        v = torch.tensor([sc["max"], -sc["min"]], dtype=torch.float64, device=self.device)
+        self._dist.all_reduce(v, op=self._dist.ReduceOp.MAX, group=self._group)
+        mx, mn = float(v[0]), -float(v[1])
+        self.set_scalars(mx, mn, mx, mn, sc["target_policy_noise"], sc["training_steps"])
 
     def train(self):
         """Agent.train: sample -> update -> priorities (-> reset_max_priority on roll-over)."""

@@ -91,6 +91,15 @@ int exo_td7_train(ExoTD7* t, const float* state_dev, const float* action_dev, co
                   const float* reward_dev, const float* not_done_dev, const float* randn_dev, float* priority_dev,
                   int32_t* rolled_over, void* stream);
 
+/* Data-parallel learners (one process per GPU, each with its own replay-buffer shard and batch): `hook` is called on the
+ * host, inside exo_td7_train, each time the gradient of one optimiser's network is complete on `stream` and before its
+ * Adam step is enqueued. The hook enqueues the exchange on that stream - an all-reduce (mean) of grad_dev[n] over the
+ * ranks (NCCL) - so that every rank takes the same step: N ranks x batch_rows rows behave as one batch of N x batch_rows
+ * (the three losses are means over rows). NULL removes the hook. The value bounds stay per rank; callers that want the
+ * single-batch semantics reduce max / min over the ranks when an iteration rolls over (exo_td7_scalars / _set_scalars). */
+typedef void (*ExoTD7GradHook)(int32_t opt, float* grad_dev, int64_t n, void* stream, void* user);
+int exo_td7_set_grad_hook(ExoTD7* t, ExoTD7GradHook hook, void* user);
+
 /* Synchronises and reads the learner's scalars: out[0..3] = max, min, max_target, min_target (:255-259,311-312),
  * [4] = target_policy_noise, [5] = training_steps, [6..8] = encoder / critic / actor loss of the last iteration that
  * computed them. */

@@ -334,3 +334,68 @@ def test_device_noise_is_standard_normal_and_changes_per_iteration(exo):
     assert any(not torch.equal(a[k], b[k]) for k in a)
     t.close()
     u.close()
+
+
+# ------------------------------------------------------------------------------------------------ data-parallel learners
+def _dp_batch(step, rows, S=11, A=3):
+    rs = np.random.RandomState(100 + step)
+    b = [rs.randn(rows, S) * 0.7, np.clip(rs.randn(rows, A) * 0.6, -1, 1), rs.randn(rows, S) * 0.7, rs.randn(rows, 1) * 2 + 0.5,
+         (rs.rand(rows, 1) > 0.15).astype(np.float64), rs.randn(rows, A)]
+    return [x.astype(np.float32) for x in b]
+
+
+def _dp_hp(exo):
+    return exo.Hyperparameters(batch_size=8, buffer_size=64, target_update_rate=2, zs_dim=24, enc_hdim=20, critic_hdim=28, actor_hdim=16)
+
+
+def _dp_worker(rank, world, port, out_dir):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, REPO)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)          # both ranks share the one GPU of the test box: NCCL
+    import exo_b200 as exo                                                # refuses that, gloo moves CUDA tensors through the host
+    t = exo.DeviceTD7(11, 3, 1, learning_steps=100, hp=_dp_hp(exo), env_num=3, device="cuda:0", replay_buffer=False, init_seed=5,
+                      process_group=True)
+    rows = t.batch_rows
+    prios = []
+    for step in (1, 2, 3):
+        full = _dp_batch(step, rows * world)
+        mine = [torch.from_numpy(np.ascontiguousarray(x[rank * rows:(rank + 1) * rows])).cuda() for x in full]
+        p, rolled = t.train_on_batch(*mine)
+        assert rolled == (step == 2)
+        prios.append(p.cpu().numpy().copy())
+    torch.save(dict(nets={n: t.state_dict(n) for n in ALL_NETS}, prios=prios, scalars=t.scalars()), os.path.join(out_dir, "r%d.pt" % rank))
+    t.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_two_data_parallel_learners_equal_one_learner_on_the_joint_batch(exo, tmp_path):
+    """N>1 for the learner: gradients averaged over the ranks before Adam, value bounds reduced at roll-over. Two ranks x 24
+    rows must take the steps of one learner on the 48 joint rows (all three losses are means over rows)."""
+    import socket
+    import torch
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mp.spawn(_dp_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    r0 = torch.load(str(tmp_path / "r0.pt"), weights_only=False)
+    r1 = torch.load(str(tmp_path / "r1.pt"), weights_only=False)
+    for n in ALL_NETS:                                                    # the ranks stay bit-identical
+        assert all(torch.equal(r0["nets"][n][k], r1["nets"][n][k]) for k in r0["nets"][n]), n
+    one = exo.DeviceTD7(11, 3, 1, learning_steps=100, hp=_dp_hp(exo), env_num=6, device="cuda:0", replay_buffer=False, init_seed=5)
+    for step in (1, 2, 3):
+        p, _ = one.train_on_batch(*[torch.from_numpy(x).cuda() for x in _dp_batch(step, 48)])
+        p = p.cpu().numpy()
+        assert np.abs(p[:24] - r0["prios"][step - 1]).max() < 1e-5 and np.abs(p[24:] - r1["prios"][step - 1]).max() < 1e-5
+    sc = one.scalars()
+    for k in ("max_target", "min_target"):            # rolled over at iteration 2 with the bounds of the joint batch
+        assert abs(sc[k] - r0["scalars"][k]) < 1e-5 and abs(sc[k] - r1["scalars"][k]) < 1e-5, k
+    for n in ALL_NETS:
+        d = _param_diff(one.state_dict(n), {k: v.numpy() for k, v in r0["nets"][n].items()})
+        assert d.max() <= 2 * 3e-4 * 3 + 1e-7 and np.mean(d < 2e-6) >= 0.995, (n, d.max(), np.mean(d < 2e-6))
+    one.close()
