@@ -399,3 +399,45 @@ def test_two_data_parallel_learners_equal_one_learner_on_the_joint_batch(exo, tm
         d = _param_diff(one.state_dict(n), {k: v.numpy() for k, v in r0["nets"][n].items()})
         assert d.max() <= 2 * 3e-4 * 3 + 1e-7 and np.mean(d < 2e-6) >= 0.995, (n, d.max(), np.mean(d < 2e-6))
     one.close()
+
+
+# ------------------------------------------------------------------------------------------------ config 5: the training loop
+def test_pink_noise_has_the_power_law_spectrum(exo):
+    """Agent/colorednoise.py powerlaw_psd_gaussian: PSD ~ 1/f^beta, unit variance."""
+    import torch
+    g = torch.Generator().manual_seed(0)
+    x = exo.pink_noise(512, 7, 346, 1.0, g, torch.device("cpu")).double()
+    # the reference's generator gives variance 1.088 at this length (its normalisation ignores the frozen lowest bin): same here
+    assert x.shape == (512, 7, 346) and abs(float(x.var()) - 1.088) < 0.04 and abs(float(x.mean())) < 0.02
+    psd = (torch.fft.rfft(x, dim=-1).abs() ** 2).mean(dim=(0, 1))[1:-1]
+    f = torch.fft.rfftfreq(346)[1:-1].double()
+    slope = np.polyfit(np.log(f.numpy()), np.log(psd.numpy()), 1)[0]
+    assert abs(slope + 1.0) < 0.05, slope
+    w = exo.pink_noise(256, 7, 346, 0.0, g, torch.device("cpu")).double()           # beta 0: white
+    psd0 = (torch.fft.rfft(w, dim=-1).abs() ** 2).mean(dim=(0, 1))[1:-1]
+    assert abs(np.polyfit(np.log(f.numpy()), np.log(psd0.numpy()), 1)[0]) < 0.05
+
+
+@pytest.mark.gpu
+def test_training_loop_runs_end_to_end_on_the_device(exo):
+    """BASELINE config 5 in small: env -> policy + pink noise -> replay add -> TD7 iterations with checkpointing."""
+    import torch
+    hp = exo.Hyperparameters(batch_size=32, buffer_size=20000, target_update_rate=50)
+    logs = []
+    r = exo.train_device(12000, replicas=2, warmup=3000, hp=hp, device="cuda:0", seed=3, log=logs.append)
+    assert len(r["episode_return"]) >= 3 and np.isfinite(r["episode_return"]).all()
+    assert r["env_steps"] >= 12000 and r["train_iterations"] >= 2 * 200
+    assert all(200 < m < 348 for m in r["episode_len"])
+    sc = r["scalars"]
+    assert sc["training_steps"] == r["train_iterations"] and sc["max"] > sc["min"] and sc["max_target"] != 0.0
+    assert np.isfinite([sc["encoder_loss"], sc["critic_loss"], sc["actor_loss"]]).all()
+    buf = r["agent"].replay_buffer
+    assert int(buf.size) > 500
+    pr = buf.storage("priority")[:, :int(buf.size)]
+    # slots the shared write pointer skipped keep priority 0 (never sampled, as in the reference); updated ones are max(td, 1)^alpha >= 1
+    assert torch.isfinite(pr).all() and float(pr.min()) >= 0 and int(((pr != 0) & (pr != 1)).sum()) >= 1
+    # the exploring policy's actions are the policy's own plus bounded noise: the policy object holds the learner's networks
+    a, b = r["agent"].state_dict("actor"), r["agent"].state_dict("checkpoint_actor")
+    assert any(not torch.equal(a[k], b[k]) for k in a) or r["agent"].eps_since_update == 0
+    for k in ("agent", "policy", "env"):
+        r[k].close()
