@@ -51,13 +51,15 @@ def pink_noise(n, action_dim, steps, beta, generator, device):
 
 def train_device(n_steps, tremor_sequence=(0, 1, 0, 1, 0, 0, 0), replicas=1, num_reference_motions=8, warmup=25000, hp=None,
                  device="cuda:0", seed=0, updates_per_episode_step=1.0, learning_steps=None, process_group=None, precision="tf32",
-                 env_kwargs=None, log=None):
+                 env_kwargs=None, log=None, init_seed=None):
     """Runs the loop until n_steps env-steps (of this rank) have been collected. Returns a dict: episode returns, TD7
     iterations, env-steps, wall seconds and the learner / policy / env objects' final scalars.
 
     replicas: copies of each reference-motion env (the script has 1); the population is replicas x num_reference_motions.
     updates_per_episode_step: TD7 iterations per episode time step (the script: 1 - with `replicas` > 1 the ratio of
-    updates to collected transitions falls accordingly, which is the knob large populations need)."""
+    updates to collected transitions falls accordingly, which is the knob large populations need).
+    process_group: data-parallel learners, one rank per GPU (DeviceTD7.set_process_group); give every rank its own `seed`
+    (envs, exploration) and the same `init_seed` (networks)."""
     hp = hp if hp is not None else Hyperparameters()
     dev = torch.device(device)
     gen = torch.Generator(device=dev).manual_seed(int(seed))
@@ -70,7 +72,7 @@ def train_device(n_steps, tremor_sequence=(0, 1, 0, 1, 0, 0, 0), replicas=1, num
     env = BatchedExoskeletonEnv(motion, np.asarray(tremor_sequence, np.uint8), np.arange(n, dtype=np.uint32) + 1000003 * int(seed),
                                 device=dev, precision="fp32", auto_reset=False, metrics=True, **kw)
     agent = DeviceTD7(80, 7, 1, learning_steps=learning_steps or n_steps, hp=hp, env_num=num_reference_motions, device=dev, seed=seed,
-                      init_seed=seed, process_group=process_group)
+                      init_seed=seed if init_seed is None else init_seed, process_group=process_group)
     policy = DevicePolicy(dev, max_action=1.0, precision=precision)
     agent.export_policy(policy)
     tremor_num = torch.from_numpy(motion).to(dev)
@@ -106,6 +108,14 @@ def train_device(n_steps, tremor_sequence=(0, 1, 0, 1, 0, 0, 0), replicas=1, num
             raise RuntimeError("%d of %d envs did not finish within the longest reference motion" % (n - finished, n))
         steps_count += int(ep_len.sum()) - n
         mean_len, mean_score = float(ep_len.mean()), float(score.mean())
+        if process_group is not None:
+            # data-parallel learners must take the same train / checkpoint decisions (:315-332 compares the episode return with
+            # the checkpoint's): every rank uses the means over all ranks
+            import torch.distributed as dist
+            grp = None if process_group is True else process_group
+            v = torch.tensor([mean_len, mean_score], dtype=torch.float64, device=dev)
+            dist.all_reduce(v, group=grp)
+            mean_len, mean_score = (float(x) / dist.get_world_size(grp) for x in v)
         out["episode_return"].append(mean_score)
         out["episode_len"].append(mean_len)
         before = agent.training_steps
