@@ -441,3 +441,55 @@ def test_training_loop_runs_end_to_end_on_the_device(exo):
     assert any(not torch.equal(a[k], b[k]) for k in a) or r["agent"].eps_since_update == 0
     for k in ("agent", "policy", "env"):
         r[k].close()
+
+
+# ------------------------------------------------------------------------------------------------ row N4: the evaluation log layout
+_LOG_LINES = [
+    r"TREMOR \d statistics: $",
+    r" score -?\d+\.\d{3} avg score -?\d+\.\d{3} median score -?\d+\.\d{3} max score -?\d+\.\d{3} std of scores \d+\.\d{3}$",
+    r"Reward achieved by the agent: -?\d+\.\d{3}, Score in percent to max: -?\d+\.\d{3}, avg rewards in percent: -?\d+\.\d{3}, median rewards in percent: -?\d+\.\d{3}$",
+    r"Tremor torque reduction metrics:$",
+    r" Tremor reduction ep avg \[( *-?\d+\.\d{3}){7}\] $", r" Tremor reduction ep median \[( *-?\d+\.\d{3}){7}\] $", r" Tremor reduction ep std \[( *-?\d+\.\d{3}){7}\]$",
+    r"Tremor reduction occurred in \d+\.\d+ % of all the generated tremor axis in all timesteps$",
+    r"Some sort of tremor reduction occurred along any axis in \d+\.\d+ % of the episode$",
+    r"Tremor amplitude reduction metrics:$",
+    r" Tremor reduction ep avg \[( *-?\d+\.\d{3}){7}\] $", r" Tremor reduction ep median \[( *-?\d+\.\d{3}){7}\] $", r" Tremor reduction ep std \[( *-?\d+\.\d{3}){7}\]$",
+    r"Tremor amplitude reduction occurred in \d+\.\d+ % of all timesteps$",
+    r"Overall tremor suppression avg in the angle axis:  -?\d+\.\d+ %$", r"Overall tremor suppression median in the angle axis:  -?\d+\.\d+ %$",
+    r"Total tremor amplitude suppression -?\d+\.\d+ %$",
+    r"For torque places: \[( *\d\.000){7}\], With maximum Nm of: \[( *\d+\.\d{3}){7}\]$", r"$"]
+
+
+@pytest.mark.gpu
+def test_evaluation_log_layout_and_the_shipped_agents_suppression(exo, tmp_path):
+    """Evaluate_control_performance.py's per-env console block, line by line as in Evaluation_logs/[1,1,1,1], produced on the
+    device with the shipped [1,1,1,1] checkpoint pair. The shipped log's first episode reads 50.5 % score on motion 0; the
+    same agent scores 54 % here. Its suppression figures are weaker here (-16 % against -64 %): the shipped logs were
+    written with per-axis tremor maxima [10, 5, 2.5, 5] Nm ("With maximum Nm of" line), the reference's current
+    generate_joint_torques_train uses [2.5, 5, 10, 5] - which is what the env, its oracle and the goldens implement."""
+    import re
+    g = np.load(os.path.join(REPO, "tests", "golden", "ref_policy.npz"))
+    sd = {k: g[k] for k in g.files if "." in k}
+    pol = exo.DevicePolicy("cuda:0", precision="fp32")
+    pol.set_networks(sd, sd, "checkpoint")
+    path = str(tmp_path / "[1,1,1,1]")
+    metrics, text = exo.evaluate_device(pol, [1, 1, 1, 1, 0, 0, 0], num_eval_episodes=2, device="cuda:0", seed=0, out=path)
+    assert open(path).read() == text
+    lines = text.split("\n")
+    assert lines[0] == "Seed successfully set" and lines[1] == "LOCAL ENV OUTPUTS: "
+    block = len(_LOG_LINES)
+    for e in range(2):
+        start = 2 + e * (1 + 8 * block)
+        for i in range(8):
+            for j, pat in enumerate(_LOG_LINES):
+                ln = lines[start + i * block + j]
+                assert re.match(pat, ln), (e, i, j, ln)
+        assert lines[start + 8 * block] in ("LOCAL ENV OUTPUTS: ", "")
+    for ep in metrics:
+        assert len(ep) == 8
+        for m in ep:
+            assert 25 < m["reward_percentage"] < 80, m["reward_percentage"]
+            assert m["suppression_avg"] < 0 and m["any_axis_pct"] > 80 and m["total_ampl_suppression"] < 0
+            assert np.allclose(m["torque_max"][:4] / np.array([2.5, 5, 10, 5]), 1.0, atol=0.06) and np.all(m["torque_max"][4:] == 0)
+            assert np.all(m["torque_reduction_avg"][:4] < 0) and np.all(m["torque_reduction_avg"][4:] == 0)
+    pol.close()
