@@ -322,9 +322,13 @@ __global__ void mse_grad_kernel(const float* pred, const float* next, float* d, 
 }
 
 // next_action = (actor_target(...) + (randn * sigma).clamp(-clip, clip)).clamp(-1, 1)   (:254-256)
-__global__ void target_action_kernel(float* na, const float* randn, int count, float sigma, float clip) {
+// per-iteration scalars, written by the host before each iteration (so that a captured graph can be replayed unchanged)
+enum { DP_SIGMA = 0, DP_ADAM = 1 /* + 2 opt: step size, sqrt(bias correction 2) */, DP_STEP = 8 /* uint64 */, DP_COUNT = 16 };
+
+__global__ void target_action_kernel(float* na, const float* randn, int count, const float* dp, float clip) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= count) return;
+    const float sigma = dp[DP_SIGMA];
     const float nz = fminf(fmaxf(randn[i] * sigma, -clip), clip);
     na[i] = fminf(fmaxf(na[i] + nz, -1.f), 1.f);
 }
@@ -395,9 +399,10 @@ __global__ void tanh_bwd_kernel(float* d, const float* da, const float* db, cons
 
 // torch.optim.Adam, single-tensor arithmetic: g += wd p; m.lerp_(g, 1-b1); v = b2 v + (1-b2) g g;
 // p -= (lr / bc1) * m / (sqrt(v) / sqrt(bc2) + eps)
-__global__ void adam_kernel(float* p, const float* g, float* m, float* v, size_t n, float wd, float step_size, float bc2_sqrt) {
+__global__ void adam_kernel(float* p, const float* g, float* m, float* v, size_t n, float wd, const float* dp) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    const float step_size = dp[0], bc2_sqrt = dp[1];
     const float b1 = 0.9f, b2 = 0.999f, eps = 1e-8f;
     const float pv = p[i];
     const float gv = g[i] + wd * pv;
@@ -409,9 +414,10 @@ __global__ void adam_kernel(float* p, const float* g, float* m, float* v, size_t
 }
 
 // standard normals for the target-policy noise when the caller passes none: splitmix64 counter hash + Box-Muller
-__global__ void randn_kernel(float* out, int count, uint64_t seed, uint64_t step) {
+__global__ void randn_kernel(float* out, int count, uint64_t seed, const uint64_t* step_ptr) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= count) return;
+    const uint64_t step = *step_ptr;
     uint64_t z = seed + 0x9E3779B97F4A7C15ull * (step * 0x100000000ull + (uint64_t)i + 1);
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
     z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
@@ -462,6 +468,16 @@ struct ExoTD7 {
     cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
     cudaEvent_t evs[32] = {};
     int ev_next = 0;
+    // per-iteration scalars: device block + pinned host ring (the copy is enqueued ahead of the iteration)
+    float* dparams = nullptr;
+    float* hparams = nullptr;
+    uint64_t* dstep_scratch = nullptr;        // exo_td7_randn's own step cell
+    // CUDA graphs of one iteration, per (batch pointers, actor half): replayed on `gstream` between two events
+    struct Graph { const void* key[7]; bool actor; cudaGraphExec_t exec; int64_t kernels; };
+    std::vector<Graph> graphs;
+    cudaStream_t gstream = nullptr;
+    cudaEvent_t g_in = nullptr, g_out = nullptr;
+    bool use_graph = true;                    // EXO_TD7_GRAPH=0: plain stream launches
     float *G[6], *G2[4];                                        // per-layer gradient buffers of a backward pass (main chain, head 1)
     float *t_h1, *t_h2, *t_z3, *next_zs;                       // no-grad encoder passes (target branch)
     float *n_h1, *n_h2, *n_z3, *f_h1, *f_h2, *f_z3;            // the same scratch for the other two branches
@@ -551,14 +567,12 @@ struct Ctx {
         copy_cols_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(dst, ldd, src, lds, B, cols);
         t->launches++;
     }
-    void adam(int opt, float lr) {
+    void adam(int opt) {
         const int net = OPT_NET[opt];
         const size_t n = t->def[kind_of(net)].size;
         if (t->hook) t->hook(opt, t->grad[opt], (int64_t)n, (void*)s, t->hook_user);      // data-parallel: all-reduce first
-        const int64_t k = ++t->opt_step[opt];
-        const double bc1 = 1.0 - pow(0.9, (double)k), bc2 = 1.0 - pow(0.999, (double)k);
         adam_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(t->net[net], t->grad[opt], t->m[opt], t->v[opt], n, t->c.weight_decay,
-                                                                (float)((double)lr / bc1), (float)sqrt(bc2));
+                                                                t->dparams + DP_ADAM + 2 * opt);
         t->launches++;
     }
     void zero_grad(int opt) { cudaMemsetAsync(t->grad[opt], 0, t->def[kind_of(OPT_NET[opt])].size * sizeof(float), s); }
@@ -623,13 +637,12 @@ struct Ctx {
         if (e_ != cudaSuccess) return exo_set_error(EXO_ERR_CUDA, "exo_td7: %s", cudaGetErrorString(e_)); \
     } while (0)
 
-extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const float* sN, const float* sR, const float* sD,
-                             const float* randn_dev, float* prio, int32_t* rolled_over, void* stream) {
-    if (!t || !sS || !sA || !sN || !sR || !sD || !prio) return exo_set_error(EXO_ERR_ARG, "exo_td7_train: null argument");
-    TCK(cudaSetDevice(t->device));
+// One iteration without its host-side bookkeeping: everything here is stream work that a CUDA graph can replay.
+static int td7_iteration(ExoTD7* t, const float* sS, const float* sA, const float* sN, const float* sR, const float* sD,
+                         const float* randn_dev, float* prio, bool actor_half, cudaStream_t stream) {
     const ExoTD7Config& c = t->c;
     const int B = c.batch_rows, S = c.state_dim, A = c.action_dim, Z = c.zs_dim, H = c.enc_hdim, C = c.critic_hdim, Ha = c.actor_hdim;
-    Ctx x{t, (cudaStream_t)stream, B};
+    Ctx x{t, stream, B};
     cudaStream_t s = x.s;
     const NetDef &DA = t->def[0], &DC = t->def[1], &DE = t->def[2];
     float* enc = t->net[EXO_TD7_ENCODER];
@@ -637,7 +650,6 @@ extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const 
     const float* fet = t->net[EXO_TD7_FIXED_ENCODER_TARGET];
     float* critic = t->net[EXO_TD7_CRITIC];
     float* actor = t->net[EXO_TD7_ACTOR];
-    t->steps++;
     TCK(cudaMemsetAsync(t->sc + SC_ENC_LOSS, 0, 2 * sizeof(float), s));
 
     // Three independent branches until the critic update needs Q_target and fixed_zsa: the encoder update stays on the
@@ -652,13 +664,12 @@ extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const 
     xt.actor_fwd(t->net[EXO_TD7_ACTOR_TARGET], sN, t->tzs, t->na);
     const float* rn = randn_dev;
     if (!rn) {
-        randn_kernel<<<(B * A + 255) / 256, 256, 0, xt.s>>>(t->rn, B * A, c.seed, (uint64_t)t->steps);
+        randn_kernel<<<(B * A + 255) / 256, 256, 0, xt.s>>>(t->rn, B * A, c.seed, reinterpret_cast<const uint64_t*>(t->dparams + DP_STEP));
         t->launches++;
         rn = t->rn;
     }
-    target_action_kernel<<<(B * A + 255) / 256, 256, 0, xt.s>>>(t->na, rn, B * A, (float)t->sigma, c.noise_clip);
+    target_action_kernel<<<(B * A + 255) / 256, 256, 0, xt.s>>>(t->na, rn, B * A, t->dparams, c.noise_clip);
     t->launches++;
-    t->sigma -= (double)c.policy_noise_decrease;
     xt.copy(t->t_cat, Z + A, t->tzs, Z, Z);
     xt.copy(t->t_cat + Z, Z + A, t->na, A, A);
     xt.enc_zsa(fet, t->t_cat, t->t_h1, t->t_h2, t->tzsa);
@@ -702,7 +713,7 @@ extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const 
         x.dw_side(g, DE.L[0], G[5], H, sS, S);
         x.join_dw();
     }
-    x.adam(EXO_TD7_OPT_ENCODER, c.encoder_lr);
+    x.adam(EXO_TD7_OPT_ENCODER);
 
     // ---- join; critic update (:268-276) and priorities (:281)
     TCK(cudaStreamWaitEvent(s, t->ev_join[0], 0));
@@ -732,10 +743,10 @@ extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const 
         h1.before(s);
         x.join_dw();
     }
-    x.adam(EXO_TD7_OPT_CRITIC, c.critic_lr);
+    x.adam(EXO_TD7_OPT_CRITIC);
 
     // ---- actor update (:287-298)
-    if (t->steps % c.policy_freq == 0) {
+    if (actor_half) {
         TCK(cudaMemsetAsync(t->sc + SC_ACTOR_LOSS, 0, sizeof(float), s));
         x.actor_fwd(actor, sS, t->fzs, t->act);
         x.copy(t->f_cat + Z, Z + A, t->act, A, A);
@@ -777,16 +788,84 @@ extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const 
         x.avgl1_bwd(G[2], Ha, t->a_u, Ha, G[2], Ha, Ha);
         x.dw_side(g, DA.L[0], G[2], Ha, sS, S);
         x.join_dw();
-        x.adam(EXO_TD7_OPT_ACTOR, c.actor_lr);
+        x.adam(EXO_TD7_OPT_ACTOR);
+    }
+
+    (void)DA;
+    return EXO_OK;
+}
+
+extern "C" int exo_td7_train(ExoTD7* t, const float* sS, const float* sA, const float* sN, const float* sR, const float* sD,
+                             const float* randn_dev, float* prio, int32_t* rolled_over, void* stream) {
+    if (!t || !sS || !sA || !sN || !sR || !sD || !prio) return exo_set_error(EXO_ERR_ARG, "exo_td7_train: null argument");
+    TCK(cudaSetDevice(t->device));
+    const ExoTD7Config& c = t->c;
+    cudaStream_t s = (cudaStream_t)stream;
+    t->steps++;
+    const bool actor_half = t->steps % c.policy_freq == 0;
+    // this iteration's scalars: noise scale, Adam's bias-corrected step sizes, the generator's step
+    float* hp = t->hparams + (size_t)(t->steps & 63) * DP_COUNT;
+    hp[DP_SIGMA] = (float)t->sigma;
+    t->sigma -= (double)c.policy_noise_decrease;
+    const float lrs[3] = {c.actor_lr, c.critic_lr, c.encoder_lr};
+    for (int o = 0; o < 3; ++o) {
+        if (o == EXO_TD7_OPT_ACTOR && !actor_half) continue;
+        const int64_t k = ++t->opt_step[o];
+        hp[DP_ADAM + 2 * o] = (float)((double)lrs[o] / (1.0 - pow(0.9, (double)k)));
+        hp[DP_ADAM + 2 * o + 1] = (float)sqrt(1.0 - pow(0.999, (double)k));
+    }
+    const uint64_t st = (uint64_t)t->steps;
+    memcpy(hp + DP_STEP, &st, sizeof(st));
+    TCK(cudaMemcpyAsync(t->dparams, hp, DP_COUNT * sizeof(float), cudaMemcpyHostToDevice, s));
+
+    const void* key[7] = {sS, sA, sN, sR, sD, randn_dev, prio};
+    if (t->use_graph && !t->hook) {
+        ExoTD7::Graph* g = nullptr;
+        for (auto& e : t->graphs)
+            if (e.actor == actor_half && !memcmp(e.key, key, sizeof(key))) { g = &e; break; }
+        if (!g && t->graphs.size() < 32) {
+            // capture on the library's own stream (the caller's may be the legacy default stream, which cannot be captured)
+            const int64_t l0 = t->launches;
+            TCK(cudaStreamBeginCapture(t->gstream, cudaStreamCaptureModeThreadLocal));
+            int rc = td7_iteration(t, sS, sA, sN, sR, sD, randn_dev, prio, actor_half, t->gstream);
+            cudaGraph_t graph = nullptr;
+            cudaError_t e = cudaStreamEndCapture(t->gstream, &graph);
+            const int64_t kernels = t->launches - l0;
+            t->launches = l0;
+            if (rc != EXO_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+            if (e != cudaSuccess) return exo_set_error(EXO_ERR_CUDA, "exo_td7_train: graph capture: %s", cudaGetErrorString(e));
+            cudaGraphExec_t exec = nullptr;
+            e = cudaGraphInstantiate(&exec, graph, 0);
+            cudaGraphDestroy(graph);
+            if (e != cudaSuccess) return exo_set_error(EXO_ERR_CUDA, "exo_td7_train: graph instantiate: %s", cudaGetErrorString(e));
+            ExoTD7::Graph ng;
+            memcpy(ng.key, key, sizeof(key));
+            ng.actor = actor_half; ng.exec = exec; ng.kernels = kernels;
+            t->graphs.push_back(ng);
+            g = &t->graphs.back();
+        }
+        if (g) {
+            TCK(cudaEventRecord(t->g_in, s));
+            TCK(cudaStreamWaitEvent(t->gstream, t->g_in, 0));
+            TCK(cudaGraphLaunch(g->exec, t->gstream));
+            TCK(cudaEventRecord(t->g_out, t->gstream));
+            TCK(cudaStreamWaitEvent(s, t->g_out, 0));
+            t->launches += g->kernels;
+        } else if (int rc = td7_iteration(t, sS, sA, sN, sR, sD, randn_dev, prio, actor_half, s)) {
+            return rc;
+        }
+    } else if (int rc = td7_iteration(t, sS, sA, sN, sR, sD, randn_dev, prio, actor_half, s)) {
+        return rc;
     }
 
     // ---- roll-over (:303-312)
+    const NetDef &DA = t->def[0], &DC = t->def[1], &DE = t->def[2];
     const bool roll = t->steps % c.target_update_rate == 0;
     if (roll) {
-        TCK(cudaMemcpyAsync(t->net[EXO_TD7_ACTOR_TARGET], actor, DA.size * sizeof(float), cudaMemcpyDeviceToDevice, s));
-        TCK(cudaMemcpyAsync(t->net[EXO_TD7_CRITIC_TARGET], critic, DC.size * sizeof(float), cudaMemcpyDeviceToDevice, s));
-        TCK(cudaMemcpyAsync(t->net[EXO_TD7_FIXED_ENCODER_TARGET], fe, DE.size * sizeof(float), cudaMemcpyDeviceToDevice, s));
-        TCK(cudaMemcpyAsync(t->net[EXO_TD7_FIXED_ENCODER], enc, DE.size * sizeof(float), cudaMemcpyDeviceToDevice, s));
+        TCK(cudaMemcpyAsync(t->net[EXO_TD7_ACTOR_TARGET], t->net[EXO_TD7_ACTOR], DA.size * sizeof(float), cudaMemcpyDeviceToDevice, s));
+        TCK(cudaMemcpyAsync(t->net[EXO_TD7_CRITIC_TARGET], t->net[EXO_TD7_CRITIC], DC.size * sizeof(float), cudaMemcpyDeviceToDevice, s));
+        TCK(cudaMemcpyAsync(t->net[EXO_TD7_FIXED_ENCODER_TARGET], t->net[EXO_TD7_FIXED_ENCODER], DE.size * sizeof(float), cudaMemcpyDeviceToDevice, s));
+        TCK(cudaMemcpyAsync(t->net[EXO_TD7_FIXED_ENCODER], t->net[EXO_TD7_ENCODER], DE.size * sizeof(float), cudaMemcpyDeviceToDevice, s));
         TCK(cudaMemcpyAsync(t->sc + SC_MAX_TARGET, t->sc + SC_MAX, 2 * sizeof(float), cudaMemcpyDeviceToDevice, s));
     }
     if (rolled_over) *rolled_over = roll ? 1 : 0;
@@ -806,6 +885,11 @@ extern "C" int exo_td7_destroy(ExoTD7* t) {
     for (int i = 0; i < 32; ++i)
         if (t->evs[i]) cudaEventDestroy(t->evs[i]);
     if (t->ev_fork) cudaEventDestroy(t->ev_fork);
+    for (auto& g : t->graphs) cudaGraphExecDestroy(g.exec);
+    if (t->gstream) cudaStreamDestroy(t->gstream);
+    if (t->g_in) cudaEventDestroy(t->g_in);
+    if (t->g_out) cudaEventDestroy(t->g_out);
+    if (t->hparams) cudaFreeHost(t->hparams);
     delete t;
     return EXO_OK;
 }
@@ -852,6 +936,14 @@ extern "C" int exo_td7_create(int32_t device, const ExoTD7Config* cfg, ExoTD7** 
     for (int i = 0; i < 2 && err == cudaSuccess; ++i) err = cudaEventCreateWithFlags(&t->ev_join[i], cudaEventDisableTiming);
     for (int i = 0; i < 32 && err == cudaSuccess; ++i) err = cudaEventCreateWithFlags(&t->evs[i], cudaEventDisableTiming);
     if (err == cudaSuccess) err = cudaEventCreateWithFlags(&t->ev_fork, cudaEventDisableTiming);
+    t->dparams = alloc(DP_COUNT + 2);
+    t->dstep_scratch = reinterpret_cast<uint64_t*>(t->dparams + DP_COUNT);
+    if (err == cudaSuccess) err = cudaMallocHost((void**)&t->hparams, 64 * DP_COUNT * sizeof(float));
+    if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&t->gstream, cudaStreamNonBlocking);
+    if (err == cudaSuccess) err = cudaEventCreateWithFlags(&t->g_in, cudaEventDisableTiming);
+    if (err == cudaSuccess) err = cudaEventCreateWithFlags(&t->g_out, cudaEventDisableTiming);
+    const char* gm = getenv("EXO_TD7_GRAPH");
+    t->use_graph = !(gm && gm[0] == '0');
     t->e_h1 = rows(H); t->e_h2 = rows(H); t->e_z3 = rows(Z); t->e_cat = rows(Z + A); t->e_g1 = rows(H); t->e_g2 = rows(H); t->e_pred = rows(Z);
     t->tzs = rows(Z); t->t_cat = rows(Z + A); t->tzsa = rows(Z); t->na = rows(A); t->rn = rows(A);
     t->a_u = rows(Ha); t->a_cat = rows(Ha + Z); t->a_h1 = rows(Ha); t->a_h2 = rows(Ha); t->act = rows(A);
@@ -957,7 +1049,9 @@ extern "C" int exo_td7_set_grad_hook(ExoTD7* t, ExoTD7GradHook hook, void* user)
 extern "C" int exo_td7_randn(ExoTD7* t, float* out_dev, int64_t count, int64_t step, void* stream) {
     if (!t || !out_dev || count < 0 || count > 0x7FFFFFFF) return exo_set_error(EXO_ERR_ARG, "exo_td7_randn: bad argument");
     TCK(cudaSetDevice(t->device));
-    if (count) randn_kernel<<<(unsigned)((count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(out_dev, (int)count, t->c.seed, (uint64_t)step);
+    const uint64_t st = (uint64_t)step;
+    TCK(cudaMemcpyAsync(t->dstep_scratch, &st, sizeof(st), cudaMemcpyHostToDevice, (cudaStream_t)stream));     // pageable source: staged before return
+    if (count) randn_kernel<<<(unsigned)((count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(out_dev, (int)count, t->c.seed, t->dstep_scratch);
     t->launches++;
     TCK(cudaGetLastError());
     return EXO_OK;
