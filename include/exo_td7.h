@@ -86,7 +86,10 @@ int exo_td7_get_opt(ExoTD7* t, int32_t opt, int32_t which, float* host, int64_t 
  * action_dim], reward / not_done [batch_rows] (device, float32, row-major). randn_dev [batch_rows, action_dim] are the
  * standard-normal draws behind the target-policy noise (:254) or NULL to draw them on the device. priority_dev
  * [batch_rows] receives the new priorities. *rolled_over (host, may be NULL) is set to 1 when this iteration rolled the
- * target networks over, i.e. when the caller must also call replay_buffer.reset_max_priority() (:309). Asynchronous. */
+ * target networks over, i.e. when the caller must also call replay_buffer.reset_max_priority() (:309). Asynchronous. The
+ * launch sequence of an iteration is captured into a CUDA graph the first time a set of batch pointers is seen (up to 32
+ * sets; exo_lap_sample always returns the same buffers) and replayed afterwards; EXO_TD7_GRAPH=0 at exo_td7_create or a
+ * gradient hook select plain stream launches. */
 int exo_td7_train(ExoTD7* t, const float* state_dev, const float* action_dev, const float* next_state_dev,
                   const float* reward_dev, const float* not_done_dev, const float* randn_dev, float* priority_dev,
                   int32_t* rolled_over, void* stream);
