@@ -289,6 +289,34 @@ def bench_td7(exo_b200, dev):
     return out
 
 
+def bench_large_population(exo_b200, dev, flush, peak, precision, n_large=524288, steps=40):
+    """The step kernel's roofline fraction away from the single-wave regime: BASELINE config 4 puts 131 072 - 524 288 envs
+    on each GPU (1M envs over 8 / 2 GPUs). Same population recipe, same kernel, timed alone with the L2 flushed."""
+    import torch
+    motion, seqs, seeds = population(n_large, 0, 1)
+    env = exo_b200.BatchedExoskeletonEnv(motion, seqs, seeds, device=dev, precision=precision, auto_reset=True, **TRAIN)
+    gen = torch.Generator(device=dev).manual_seed(99)
+    acts = [torch.rand(n_large, 7, device=dev, generator=gen) * 2 - 1 for _ in range(2)]
+    env.reset()
+    for t in range(5):
+        env.step(acts[t % 2], keep_idle_obs=False)
+    ev = []
+    for t in range(steps):
+        if flush is not None:
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        env.step(acts[t % 2], keep_idle_obs=False)
+        b.record()
+        ev.append((a, b))
+    torch.cuda.synchronize(dev)
+    kms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    env.close()
+    achieved = ALGO_BYTES_PER_ENV_STEP * n_large / (kms * 1e-3) / 1e9
+    return {"envs": n_large, "kernel_ms": kms, "achieved": achieved, "unit": "GB/s", "frac": achieved / peak,
+            "note": "same kernel at config 4's per-GPU population (1M envs over 2 GPUs); 65 536 envs are one wave of 14 warps per SM"}
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU algorithm (oracle port; the Python reference cannot travel to the GPU box
     and needs pybullet) on all host threads, rank 0 only."""
@@ -326,6 +354,7 @@ def main():
     ap.add_argument("--ref-sample", type=int, default=4096)
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--no-lap", action="store_true", help="skip the replay-buffer (next row N1) measurement")
+    ap.add_argument("--no-large", action="store_true", help="skip the 524 288-env roofline measurement of the step kernel")
     ap.add_argument("--no-policy", action="store_true", help="skip the policy forward pass (next row N2) measurement")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -447,6 +476,9 @@ def main():
         peak = float(peaks.get("hbm_gbs", 6650.0))
         achieved = ALGO_BYTES_PER_ENV_STEP * n / (kms * 1e-3) / 1e9
         cpu_v, cpu_cores, cpu_secs = cpu_baseline(args.cpu_sample, args.cpu_steps)
+        large = None
+        if world == 1 and not args.no_large and args.precision == "fp32":
+            large = bench_large_population(exo_b200, dev, flush, peak, args.precision)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -472,6 +504,8 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
         }
+        if large is not None:
+            line["roofline"]["large_population"] = large
         if lap_line is not None:
             line["lap"] = lap_line
         if policy_line is not None:
