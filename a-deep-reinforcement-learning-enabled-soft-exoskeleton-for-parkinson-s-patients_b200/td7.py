@@ -144,6 +144,10 @@ class DeviceTD7(object):
         if init_seed is not None:
             self.init_networks(init_seed)
         self._group, self._hook, self._hook_error = None, None, None
+        self._policy, self._policy_stale = None, True       # select_action's kernel-side copy of the four networks it evaluates
+        self.noise = None
+        self.exploration_noise = float(hp.exploration_noise)
+        self.ep_length = 300                                 # Agent.__init__'s ep_length (:149): length of the pink-noise table
         if process_group is not None:
             self.set_process_group(process_group)
 
@@ -191,10 +195,12 @@ class DeviceTD7(object):
 
     def copy_net(self, dst, src):
         _capi.check(self.lib.exo_td7_copy_net(self.h, NETS.index(dst), NETS.index(src)))
+        self._policy_stale = True
 
     def load_state_dict(self, net, state_dict):
         v = flatten(state_dict, self.shapes[_kind(net)])
         _capi.check(self.lib.exo_td7_set_net(self.h, NETS.index(net), v.ctypes.data_as(C.c_void_p), v.size))
+        self._policy_stale = True
 
     def state_dict(self, net):
         n = int(self.lib.exo_td7_net_size(self.h, NETS.index(net)))
@@ -260,6 +266,7 @@ class DeviceTD7(object):
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         _capi.check(self.lib.exo_td7_train(self.h, *[C.c_void_p(t.data_ptr()) for t in ts], C.c_void_p(rn.data_ptr()) if rn is not None else None,
                                            C.c_void_p(out.data_ptr()), C.byref(rolled), stream))
+        self._policy_stale = True
         if self._hook_error is not None:
             e, self._hook_error = self._hook_error, None
             raise e
@@ -350,6 +357,32 @@ class DeviceTD7(object):
         self.load_state_dict("checkpoint_actor", rd("_checkpoint_actor"))
         self.load_state_dict("checkpoint_encoder", rd("_checkpoint_encoder"))
 
+    # ------------------------------------------------------------------ acting (:203-228)
+    def init_episode_noise(self):
+        """Agent.init_episode_noise (:203-206): a [action_dim, ep_length] pink-noise table, normalised by its absolute maximum
+        and scaled by the current exploration_noise."""
+        from .train import pink_noise
+        n = pink_noise(1, self.action_dim, self.ep_length, self.hp.beta, None, torch.device("cpu"))[0].numpy()
+        self.noise = n / np.max(np.abs(n)) * self.exploration_noise
+
+    def select_action(self, state, timestep=None, first_step=True, use_checkpoint=False, use_exploration=True):
+        """Agent.select_action (:208-228), numpy in / numpy out, evaluated by the policy kernel (state 80 / hidden 300 /
+        action 7 only). The kernel's copy of the networks is refreshed when an update, load or copy has changed them. For the
+        batched env keep the observations on the device and call a DevicePolicy directly (export_policy)."""
+        from .policy import DevicePolicy
+        if self._policy is None:
+            self._policy = DevicePolicy(self.device, max_action=self.max_action, precision="fp32")
+        if self._policy_stale:
+            self.export_policy(self._policy)
+            self._policy_stale = False
+        if use_exploration:
+            if first_step or self.noise is None:
+                self.init_episode_noise()
+            self.exploration_noise -= self.action_noise_decrease
+            self._policy.noise = self.noise
+        return self._policy.select_action(state, timestep=timestep, first_step=first_step, use_checkpoint=use_checkpoint,
+                                          use_exploration=use_exploration)
+
     def export_policy(self, policy):
         """Push (actor, fixed_encoder) and (checkpoint_actor, checkpoint_encoder) into a DevicePolicy - the pairs
         select_action evaluates (:210-217). Only for the 80 / 300 / 7 sizes the policy kernel is built for."""
@@ -372,6 +405,9 @@ class DeviceTD7(object):
             self.h = None
         if getattr(self, "replay_buffer", None) is not None:
             self.replay_buffer.close()
+        if getattr(self, "_policy", None) is not None:
+            self._policy.close()
+            self._policy = None
 
     def __del__(self):
         try:

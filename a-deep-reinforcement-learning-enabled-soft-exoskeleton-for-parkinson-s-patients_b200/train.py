@@ -39,7 +39,7 @@ def pink_noise(n, action_dim, steps, beta, generator, device):
         w[-1] *= 0.5
     sigma = 2.0 * torch.sqrt((w ** 2).sum()) / steps
     shape = (n, action_dim, f.numel())
-    re = torch.randn(shape, device=device, generator=generator) * s
+    re = torch.randn(shape, device=device, generator=generator) * s      # generator None: torch's global stream
     im = torch.randn(shape, device=device, generator=generator) * s
     im[..., 0] = 0.0
     re[..., 0] *= np.sqrt(2.0)

@@ -493,3 +493,52 @@ def test_evaluation_log_layout_and_the_shipped_agents_suppression(exo, tmp_path)
             assert np.allclose(m["torque_max"][:4] / np.array([2.5, 5, 10, 5]), 1.0, atol=0.06) and np.all(m["torque_max"][4:] == 0)
             assert np.all(m["torque_reduction_avg"][:4] < 0) and np.all(m["torque_reduction_avg"][4:] == 0)
     pol.close()
+
+
+def test_hyperparameters_equal_the_reference_dataclass(exo):
+    """Same fields, same defaults as Agent/TD7_multi_agent_Pink_noise.py:12-55 (the three activation callables aside)."""
+    ref = os.environ.get("EXO_REFERENCE", "/root/reference")
+    if not os.path.isdir(os.path.join(ref, "Agent")):
+        pytest.skip("reference tree not present")
+    sys.path.insert(0, ref)
+    try:
+        from Agent.TD7_multi_agent_Pink_noise import Hyperparameters as RefHP
+    finally:
+        sys.path.remove(ref)
+    import dataclasses
+    theirs = {f.name: f.default for f in dataclasses.fields(RefHP) if not f.name.endswith("_activ")}
+    ours = {f.name: f.default for f in dataclasses.fields(exo.Hyperparameters)}
+    assert ours == theirs
+
+
+@pytest.mark.gpu
+def test_select_action_follows_the_learner(exo):
+    """Agent.select_action on the learner object: the policy kernel's copy of (actor, fixed_encoder) / the checkpoint pair
+    is refreshed after updates; exploration adds the episode's pink-noise column and decays exploration_noise."""
+    import torch
+    import policy_oracle as PO
+    t = exo.DeviceTD7(80, 7, 1, learning_steps=1000, hp=exo.Hyperparameters(batch_size=32), env_num=2, device="cuda:0",
+                      replay_buffer=False, init_seed=4)
+    rs = np.random.RandomState(2)
+    state = (rs.randn(5, 80) * 0.5).astype(np.float32)
+
+    def oracle(actor, encoder):
+        w = {k: v.numpy() for k, v in t.state_dict(encoder).items()}
+        w.update({k: v.numpy() for k, v in t.state_dict(actor).items()})
+        return PO.PolicyOracle(w, "fp32").select_action(state)
+    a0 = t.select_action(state, use_exploration=False)
+    assert a0.shape == (5, 7) and np.abs(a0 - oracle("actor", "fixed_encoder")).max() < 1e-4
+    B = t.batch_rows
+    batch = [torch.randn(B, 80).cuda() * 0.6, (torch.rand(B, 7).cuda() * 2 - 1), torch.randn(B, 80).cuda() * 0.6, torch.randn(B, 1).cuda(),
+             torch.ones(B, 1).cuda()]
+    for _ in range(4):
+        t.train_on_batch(*batch)
+    a1 = t.select_action(state, use_exploration=False)
+    assert np.abs(a1 - a0).max() > 1e-6 and np.abs(a1 - oracle("actor", "fixed_encoder")).max() < 1e-4
+    ck = t.select_action(state, use_checkpoint=True, use_exploration=False)        # the checkpoint pair is still the initial one
+    assert np.abs(ck - a0).max() < 1e-6
+    e0 = t.exploration_noise
+    ex = t.select_action(state, timestep=7, first_step=True, use_checkpoint=False, use_exploration=True)
+    assert t.noise.shape == (7, 300) and abs(np.abs(t.noise).max() - e0) < 1e-6
+    assert np.abs(ex - np.clip(a1 + t.noise[:, 7], -1, 1)).max() < 1e-6 and t.exploration_noise < e0
+    t.close()
