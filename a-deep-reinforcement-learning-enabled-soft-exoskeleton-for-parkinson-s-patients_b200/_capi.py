@@ -42,7 +42,7 @@ class ExoTD7Config(C.Structure):
                                          "target_update_rate", "policy_freq")] + \
                [(k, C.c_float) for k in ("discount", "target_policy_noise", "noise_clip", "policy_noise_decrease", "alpha",
                                          "min_priority", "actor_lr", "critic_lr", "encoder_lr", "weight_decay")] + \
-               [("seed", C.c_uint64)]
+               [("seed", C.c_uint64), ("offline", C.c_int32), ("lmbda", C.c_float)]
 
 
 EXO_TD7_GRAD_HOOK = C.CFUNCTYPE(None, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p)

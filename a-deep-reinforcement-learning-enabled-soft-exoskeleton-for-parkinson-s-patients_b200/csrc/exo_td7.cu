@@ -293,7 +293,7 @@ __global__ void colsum_kernel(const float* dy, int ld, float* gb, int rows, int 
 }
 
 // device scalars of the learner
-enum { SC_MAX = 0, SC_MIN, SC_MAX_TARGET, SC_MIN_TARGET, SC_ENC_LOSS, SC_CRITIC_LOSS, SC_ACTOR_LOSS, SC_COUNT };
+enum { SC_MAX = 0, SC_MIN, SC_MAX_TARGET, SC_MIN_TARGET, SC_ENC_LOSS, SC_CRITIC_LOSS, SC_ACTOR_LOSS, SC_ABSQ, SC_BC_MSE, SC_COUNT };
 
 __device__ __forceinline__ float block_sum(float v, float* sh) {
     v = warp_sum(v);
@@ -379,22 +379,40 @@ __global__ void td_head_kernel(const float* q2, const float* qt, float* dq, floa
     if (threadIdx.x == 0) atomicAdd(&sc[SC_CRITIC_LOSS], s / (float)rows);
 }
 
-// actor_loss = -Q.mean() over [rows, 2] (:291): dQ = -1 / (2 rows)
+// actor_loss = -Q.mean() over [rows, 2] (:291): dQ = -1 / (2 rows); also |Q|.mean() for the offline term
 __global__ void actor_head_kernel(const float* q2, float* dq, int rows, float* sc) {
     __shared__ float sh[32];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     float q = 0.f;
     if (i < 2 * rows) { q = q2[i]; dq[i] = -1.0f / (float)(2 * rows); }
     const float s = block_sum(q, sh);
-    if (threadIdx.x == 0) atomicAdd(&sc[SC_ACTOR_LOSS], -s / (float)(2 * rows));
+    const float a = block_sum(fabsf(q), sh);
+    if (threadIdx.x == 0) {
+        atomicAdd(&sc[SC_ACTOR_LOSS], -s / (float)(2 * rows));
+        atomicAdd(&sc[SC_ABSQ], a / (float)(2 * rows));
+    }
 }
 
-// d = (da + db) * (1 - act^2): the two gradient paths into the actor's tanh output
-__global__ void tanh_bwd_kernel(float* d, const float* da, const float* db, const float* act, int count) {
+// d = (da + db [+ bc]) * (1 - act^2): the gradient paths into the actor's tanh output - through the critic's sa input,
+// through fixed_encoder.zsa, and offline (:292-293) bc = lmbda |Q|.mean() * 2 (act - action) / count
+__global__ void tanh_bwd_kernel(float* d, const float* da, const float* db, const float* act, int count, const float* action,
+                                float bc_scale, float* sc) {
+    __shared__ float sh[32];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= count) return;
-    const float y = act[i];
-    d[i] = (da[i] + db[i]) * (1.f - y * y);
+    float e = 0.f;
+    if (i < count) {
+        const float y = act[i];
+        float g = da[i] + db[i];
+        if (bc_scale != 0.f) {
+            e = y - action[i];
+            g += bc_scale * sc[SC_ABSQ] * e;
+        }
+        d[i] = g * (1.f - y * y);
+    }
+    if (bc_scale != 0.f) {                       // uniform per launch
+        const float s = block_sum(e * e, sh);
+        if (threadIdx.x == 0) atomicAdd(&sc[SC_BC_MSE], s / (float)count);
+    }
 }
 
 // torch.optim.Adam, single-tensor arithmetic: g += wd p; m.lerp_(g, 1-b1); v = b2 v + (1-b2) g g;
@@ -747,7 +765,7 @@ static int td7_iteration(ExoTD7* t, const float* sS, const float* sA, const floa
 
     // ---- actor update (:287-298)
     if (actor_half) {
-        TCK(cudaMemsetAsync(t->sc + SC_ACTOR_LOSS, 0, sizeof(float), s));
+        TCK(cudaMemsetAsync(t->sc + SC_ACTOR_LOSS, 0, 3 * sizeof(float), s));
         x.actor_fwd(actor, sS, t->fzs, t->act);
         x.copy(t->f_cat + Z, Z + A, t->act, A, A);
         x.enc_zsa(fe, t->f_cat, t->f_g1, t->f_g2, t->fzsa);
@@ -774,7 +792,8 @@ static int td7_iteration(ExoTD7* t, const float* sS, const float* sA, const floa
         x.dx(fe, DE.L[5], t->d_zsa, Z, t->dA, H, 0, H, t->f_g2, H, ACT_ELU);       // fixed_encoder.zsa's d action
         x.dx(fe, DE.L[4], t->dA, H, t->dB, H, 0, H, t->f_g1, H, ACT_ELU);
         x.dx(fe, DE.L[3], t->dB, H, t->d_act2, A, Z, A, nullptr, 0, ACT_NONE);
-        tanh_bwd_kernel<<<(B * A + 255) / 256, 256, 0, s>>>(t->dT, t->d_act1, t->d_act2, t->act, B * A);
+        tanh_bwd_kernel<<<(B * A + 255) / 256, 256, 0, s>>>(t->dT, t->d_act1, t->d_act2, t->act, B * A, sA,
+                                                            c.offline ? c.lmbda * 2.0f / (float)(B * A) : 0.f, t->sc);
         t->launches++;
         x.zero_grad(EXO_TD7_OPT_ACTOR);
         float* g = t->grad[EXO_TD7_OPT_ACTOR];
@@ -956,7 +975,7 @@ extern "C" int exo_td7_create(int32_t device, const ExoTD7Config* cfg, ExoTD7** 
     for (int i = 0; i < 6; ++i) t->G[i] = rows(wmax);
     for (int i = 0; i < 4; ++i) t->G2[i] = rows(wmax); t->d_zsa = rows(Z); t->d_act1 = rows(A); t->d_act2 = rows(A); t->dT = rows(A);
     if (err == cudaSuccess) {
-        const float init[SC_COUNT] = {-1e8f, 1e8f, 0.f, 0.f, 0.f, 0.f, 0.f};      // Agent.__init__ :179-182
+        const float init[SC_COUNT] = {-1e8f, 1e8f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};      // Agent.__init__ :179-182
         err = cudaMemcpy(t->sc, init, sizeof(init), cudaMemcpyHostToDevice);
     }
     if (err != cudaSuccess) {
@@ -1025,7 +1044,8 @@ extern "C" int exo_td7_scalars(ExoTD7* t, double* out) {
     TCK(cudaMemcpy(h, t->sc, sizeof(h), cudaMemcpyDeviceToHost));
     out[0] = h[SC_MAX]; out[1] = h[SC_MIN]; out[2] = h[SC_MAX_TARGET]; out[3] = h[SC_MIN_TARGET];
     out[4] = t->sigma; out[5] = (double)t->steps;
-    out[6] = h[SC_ENC_LOSS]; out[7] = h[SC_CRITIC_LOSS]; out[8] = h[SC_ACTOR_LOSS];
+    out[6] = h[SC_ENC_LOSS]; out[7] = h[SC_CRITIC_LOSS];
+    out[8] = h[SC_ACTOR_LOSS] + (t->c.offline ? t->c.lmbda * h[SC_ABSQ] * h[SC_BC_MSE] : 0.f);
     return EXO_OK;
 }
 extern "C" int exo_td7_set_scalars(ExoTD7* t, const double* in) {

@@ -104,8 +104,7 @@ class DeviceTD7(object):
 
     def __init__(self, state_dim, action_dim, max_action=1, learning_steps=6000000, offline=False, hp=None, env_num=15,
                  device="cuda:0", seed=0, replay_buffer=True, init_seed=None, process_group=None):
-        if offline:
-            raise NotImplementedError("the offline TD3+BC term (:292-293) is not built; the training script runs offline=False")
+        self.offline = bool(offline)
         self.hp = hp if hp is not None else Hyperparameters()
         hp = self.hp
         self.lib = _capi.load()
@@ -126,7 +125,7 @@ class DeviceTD7(object):
             actor_hdim=hp.actor_hdim, batch_rows=self.batch_rows, target_update_rate=int(hp.target_update_rate),
             policy_freq=int(hp.policy_freq), discount=hp.discount, target_policy_noise=hp.target_policy_noise, noise_clip=hp.noise_clip,
             policy_noise_decrease=self.policy_noise_decrease, alpha=hp.alpha, min_priority=hp.min_priority, actor_lr=hp.actor_lr,
-            critic_lr=hp.critic_lr, encoder_lr=hp.encoder_lr, weight_decay=1e-7, seed=int(seed))
+            critic_lr=hp.critic_lr, encoder_lr=hp.encoder_lr, weight_decay=1e-7, seed=int(seed), offline=int(self.offline), lmbda=hp.lmbda)
         self.h = C.c_void_p()
         with torch.cuda.device(self.device):
             _capi.check(self.lib.exo_td7_create(idx, C.byref(cfg), C.byref(self.h)))

@@ -11,8 +11,7 @@
  *                                             critic_target <- critic, fixed_encoder_target <- fixed_encoder,
  *                                             fixed_encoder <- encoder, max_target/min_target <- max/min
  * and holds the nine networks Agent owns (:151-163) plus the three Adam states (:152,156,160: lr, weight_decay 1e-7,
- * torch's default betas/eps) in device memory. The offline TD3+BC term (:292-293) is not built (offline=False in the
- * reference's training script).
+ * torch's default betas/eps) in device memory. With cfg.offline the actor loss carries the TD3+BC term (:292-293).
  *
  * Arithmetic (csrc/exo_td7.cu): float32 storage, sums and element-wise math; the matrix products run on the tensor
  * cores as 3xTF32 (each operand split into two TF32 parts, three MMAs, float32 accumulation: every product within
@@ -44,6 +43,8 @@ typedef struct ExoTD7Config {
     float alpha, min_priority;
     float actor_lr, critic_lr, encoder_lr, weight_decay;
     uint64_t seed;                 /* of the on-device normal generator used when exo_td7_train gets randn_dev = NULL */
+    int32_t offline;               /* Agent(offline=True): the TD3+BC term of the actor loss (:292-293) */
+    float lmbda;                   /* its weight, hp.lmbda */
 } ExoTD7Config;
 
 /* network ids */

@@ -12,7 +12,8 @@ updates, one roll-over of the target / fixed networks, a decaying target_policy_
 
 Contents: dims, hyper-parameters, init/<net>/<param>, step<k>/{state,action,next_state,reward,not_done,randn,priority,
 scalars = [max, min, max_target, min_target, target_policy_noise]}, after3/<net>/<param> (actor, critic, encoder) and
-after6/<net>/<param> for all nine networks.
+after6/<net>/<param> for all nine networks; off/... = the same batches through an Agent(offline=True) (TD3+BC actor loss), 4
+iterations: off/init/<net>/<param>, off/step<k>/priority, off/after4/<net>/<param>.
 """
 import os
 import sys
@@ -66,6 +67,24 @@ def main():
             for n in (NETS if t == 6 else ("actor", "critic", "encoder")):
                 for k, v in getattr(agent, n).state_dict().items():
                     out["after%d/%s/%s" % (t, n, k)] = v.numpy().copy()
+    # the offline (TD3+BC) actor loss (:292-293): a second Agent with offline=True, 4 iterations from its own initial networks
+    torch.manual_seed(12)
+    hp2 = Hyperparameters(batch_size=bs, buffer_size=64, target_update_rate=4, zs_dim=24, enc_hdim=20, critic_hdim=28, actor_hdim=16)
+    off = Agent(S, A, 1, learning_steps=100, offline=True, hp=hp2, env_num=envs, ep_length=16)
+    for n in ("actor", "critic", "encoder"):
+        for k, v in getattr(off, n).state_dict().items():
+            out["off/init/%s/%s" % (n, k)] = v.numpy().copy()
+    off.replay_buffer.update_priority = lambda p: rec.__setitem__("priority", p.detach().numpy().copy())
+    for t in range(1, 5):
+        batch = {k: out["step%d/%s" % (t, k)] for k in ("state", "action", "next_state", "reward", "not_done")}
+        off.replay_buffer.sample = lambda b=batch: tuple(torch.tensor(b[k], dtype=torch.float) for k in
+                                                         ("state", "action", "next_state", "reward", "not_done"))
+        torch.manual_seed(1000 + t)                      # the same randn draws as step<t>/randn
+        off.train()
+        out["off/step%d/priority" % t] = rec["priority"]
+    for n in ("actor", "critic", "encoder"):
+        for k, v in getattr(off, n).state_dict().items():
+            out["off/after4/%s/%s" % (n, k)] = v.numpy().copy()
     path = os.path.join(REPO, "tests", "golden", "ref_td7.npz")
     np.savez_compressed(path, **out)
     print(path, os.path.getsize(path), "bytes; training_steps", agent.training_steps, "max/min", agent.max, agent.min)

@@ -112,7 +112,7 @@ class TD7Oracle(object):
 
     def __init__(self, params, dtype=np.float32, discount=0.99, target_update_rate=250, policy_freq=2,
                  target_policy_noise=0.2, noise_clip=0.5, policy_noise_decrease=0.0, alpha=0.4, min_priority=1.0,
-                 actor_lr=3e-4, critic_lr=3e-4, encoder_lr=3e-4, weight_decay=1e-7):
+                 actor_lr=3e-4, critic_lr=3e-4, encoder_lr=3e-4, weight_decay=1e-7, offline=False, lmbda=0.1):
         self.dtype = dtype
         self.actor = Net(params["actor"], dtype)
         self.critic = Net(params["critic"], dtype)
@@ -129,6 +129,7 @@ class TD7Oracle(object):
         self.discount, self.target_update_rate, self.policy_freq = discount, target_update_rate, policy_freq
         self.target_policy_noise, self.noise_clip, self.policy_noise_decrease = target_policy_noise, noise_clip, policy_noise_decrease
         self.alpha, self.min_priority = alpha, min_priority
+        self.offline, self.lmbda = offline, lmbda
         self.training_steps = 0
         self.max, self.min, self.max_target, self.min_target = -1e8, 1e8, 0.0, 0.0
         self.last = {}
@@ -252,6 +253,10 @@ class TD7Oracle(object):
             d = fe.lin_bwd("zsa3", d_zsa, g2, True, False) * d_elu(g2)
             d = fe.lin_bwd("zsa2", d, g1, True, False) * d_elu(g1)
             d_act = fe.lin_bwd("zsa1", d, c, True, False)[:, Z:] + d_sa[:, -A:]
+            if self.offline:                    # TD3+BC (:292-293): + lmbda * |Q|.mean().detach() * mse(actor, action)
+                coef = T(self.lmbda) * np.abs(q).mean()
+                self.last["actor_loss"] += float(coef * np.mean((act - a) ** 2))
+                d_act = d_act + coef * T(2.0 / act.size) * (act - a)
             self.actor.zero_grad()
             s_, u, c, h1, h2 = c_a
             d = d_act * (1 - act * act)

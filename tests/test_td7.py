@@ -542,3 +542,55 @@ def test_select_action_follows_the_learner(exo):
     assert t.noise.shape == (7, 300) and abs(np.abs(t.noise).max() - e0) < 1e-6
     assert np.abs(ex - np.clip(a1 + t.noise[:, 7], -1, 1)).max() < 1e-6 and t.exploration_noise < e0
     t.close()
+
+
+# ------------------------------------------------------------------------------------------------ offline mode (TD3+BC actor loss)
+def _off_params(g):
+    return {n: {k.split("/", 3)[3]: g[k] for k in g.files if k.startswith("off/init/%s/" % n)} for n in ("actor", "critic", "encoder")}
+
+
+def test_oracle_matches_reference_train_offline():
+    g = np.load(GOLD)
+    hy = g["hyper"]
+    o = td7_oracle.TD7Oracle(_off_params(g), np.float32, discount=hy[0], target_update_rate=int(hy[1]), policy_freq=int(hy[2]),
+                             target_policy_noise=hy[3], noise_clip=hy[4], policy_noise_decrease=hy[5], alpha=hy[6], min_priority=hy[7],
+                             offline=True, lmbda=0.1)
+    for t in range(1, 5):
+        prio, _ = o.train(*[g["step%d/%s" % (t, k)] for k in BATCH_KEYS])
+        assert np.abs(prio - g["off/step%d/priority" % t]).max() < 1e-6
+    for n in ("actor", "critic", "encoder"):
+        for k, v in getattr(o, n).p.items():
+            assert np.abs(v - g["off/after4/%s/%s" % (n, k)]).max() < 1e-6, (n, k)
+    # the BC term matters: without it the actor ends elsewhere
+    o2 = td7_oracle.TD7Oracle(_off_params(g), np.float32, target_update_rate=int(hy[1]), policy_noise_decrease=hy[5])
+    for t in range(1, 5):
+        o2.train(*[g["step%d/%s" % (t, k)] for k in BATCH_KEYS])
+    assert max(np.abs(o2.actor.p[k] - g["off/after4/actor/" + k]).max() for k in o2.actor.p) > 1e-4
+
+
+@pytest.mark.gpu
+def test_cuda_offline_update_reproduces_the_reference(exo):
+    g = np.load(GOLD)
+    S, A, Z, H, Cd, Ha, B = (int(v) for v in g["dims"])
+    hy = g["hyper"]
+    hp = exo.Hyperparameters(batch_size=B // 3, buffer_size=64, target_update_rate=int(hy[1]), zs_dim=Z, enc_hdim=H, critic_hdim=Cd, actor_hdim=Ha)
+    t = exo.DeviceTD7(S, A, 1, learning_steps=100, offline=True, hp=hp, env_num=3, device="cuda:0", replay_buffer=False)
+    for n, sd in _off_params(g).items():
+        t.load_state_dict(n, sd)
+    t.sync_copies()
+    o = td7_oracle.TD7Oracle(_off_params(g), np.float64, target_update_rate=int(hy[1]), policy_noise_decrease=hy[5], offline=True)
+    for step in range(1, 5):
+        prio, _ = t.train_on_batch(*_dev_batch(g, t, step))
+        o.train(*[g["step%d/%s" % (step, k)] for k in BATCH_KEYS])
+        assert np.abs(prio.cpu().numpy() - g["off/step%d/priority" % step]).max() < 1e-5
+        if step % 2 == 0:
+            got, ref = t.gradients("actor"), o.actor.g
+            for k, v in got.items():
+                assert np.abs(v.numpy() - ref[k]).max() < 1e-5 + 1e-4 * np.abs(ref[k]).max(), (step, k)
+            assert abs(t.scalars()["actor_loss"] - o.last["actor_loss"]) < 1e-5
+        _sync_learner_to_oracle(t, o)
+    for n in ("actor", "critic", "encoder"):
+        ref_sd = {k.split("/", 3)[3]: g[k] for k in g.files if k.startswith("off/after4/%s/" % n)}
+        d = _param_diff(t.state_dict(n), ref_sd)
+        assert d.max() <= 2 * 3e-4 * 4 + 1e-7 and np.mean(d < 2e-6) >= 0.995, (n, d.max())
+    t.close()
