@@ -314,6 +314,9 @@ def bench_large_population(exo_b200, dev, flush, peak, precision, n_large=524288
     env.close()
     achieved = ALGO_BYTES_PER_ENV_STEP * n_large / (kms * 1e-3) / 1e9
     return {"envs": n_large, "kernel_ms": kms, "achieved": achieved, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": 491657728 if (n_large == 524288 and precision == "fp32") else None,
+            "traffic_source": "ncu --set full dram__bytes_read.sum (272.8 MB = the 520 B/env compulsory reads) + dram__bytes_write.sum "
+                              "(218.8 MB of the 525 B/env written; the rest is still in L2 when the launch ends), profiles/r01o_ncu_full_step_524288.txt",
             "note": "same kernel at config 4's per-GPU population (1M envs over 2 GPUs); 65 536 envs are one wave of 14 warps per SM"}
 
 
