@@ -191,6 +191,15 @@ def main():
         out["geo/base_pos"] = np.array(body.base_pos - body.base_com)
         out["geo/names"] = np.array([l.name for l in body.links])
         out["geo/zero_pose_com"] = np.array(body.cache)
+        # dynamics data of the same URDF (masses, principal inertias, inertial-frame rotations, collision boxes):
+        # what minibullet's motor_model="full" (oracle/multibody.py) needs; exo_v3.urdf:3-13,22-33,...
+        out["geo/mass"] = np.array([l.mass for l in body.links])
+        out["geo/inertia_file"] = np.array([l.inertia_file for l in body.links])
+        out["geo/R_inertial"] = np.array([l.R_inertial.reshape(9) for l in body.links])
+        assert all(len(l.boxes) == 1 for l in body.links)
+        out["geo/box_size"] = np.array([l.boxes[0][0] for l in body.links])
+        out["geo/box_xyz"] = np.array([l.boxes[0][1] for l in body.links])
+        out["geo/box_R"] = np.array([l.boxes[0][2].reshape(9) for l in body.links])
         keys = ["elbow_joint_y_positions", "elbow_joint_z_positions", "shoulder_joint_x_positions",
                 "shoulder_joint_y_positions", "shoulder_joint_z_positions"]
         for m in range(8):

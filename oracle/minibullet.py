@@ -34,6 +34,36 @@ be verified against a running Bullet:
 * Joint limits (exo_v3.urdf:17,37,57,77,97): knob `joint_limits` "off" (default: the motor
   row is taken to win) or "clamp" (q+ clipped into [lower, upper]). The oracle reports how
   often a step would have crossed a limit so the regime can be checked.
+
+`motor_model="full"` (round 2) does not ASSUME that closed form: it restates one Bullet
+multibody step for this tree from Bullet's published algorithm (btMultiBodyDynamicsWorld /
+btMultiBody / btMultiBodyJointMotor / btMultiBodyJointLimitConstraint /
+btMultiBodyConstraintSolver, Bullet 3.2x as wrapped by pybullet 3.2.5), so that the closed form
+is a RESULT whose error can be stated (tests/test_multibody_model.py):
+
+  1. forward kinematics of the 19-DoF tree (5 revolute + 14 prismatic); link-state cache refresh
+  2. external forces: gravity m*g on every link COM, Bullet's per-link velocity damping
+     (linear/angular 0.04: force -m*v*(k+k|v|), torque -I*w*(k+k|w|)), gyroscopic term w x Iw
+  3. unconstrained joint accelerations (articulated-body algorithm == M(q)^-1 (tau - bias); here
+     via composite mass matrix + recursive Newton-Euler bias, same result to rounding),
+     qd += dt*qdd
+  4. constraint rows, in the order Bullet's (unstable) quickSort of the world's constraint list
+     [limit_0..limit_18, motor_0..motor_18] leaves them (all in one island):
+       * motor row per joint: Jacobian e_j, desired velocity kp*(target-q)/dt + qd + kd*(vt-qd)
+         (position motors on joints 0-4: kp 0.1, kd 1, impulse cap maxForce*dt = 2500;
+          pybullet's default velocity motors on the 14 prismatic joints: kp 0, kd 1, target 0,
+          impulse cap 1.0), rhs = (desired - J.qd) / (J M^-1 J^T)
+       * joint-limit rows only while q is at/over a bound: unilateral, impulse in [0, 100],
+         rhs = (erp*(-penetration)/dt - J.qd) / (J M^-1 J^T), erp 0.2
+  5. projected Gauss-Seidel ("sequential impulse"): numIterations 50 (pybullet default), sweep
+     direction reversed on even iterations, early exit when the largest squared row velocity
+     error of a sweep is <= leastSquaresResidualThreshold (pybullet sets 1e-7)
+  6. q += dt*qd (semi-implicit Euler); no contacts (no self-collision flag, no ground)
+  Link inertias: pybullet recomputes them from the collision boxes unless
+  URDF_USE_INERTIA_FROM_FILE is passed (the reference passes no flags,
+  Exoskeleton_sim_pybullet.py:18) -> knob `inertia_from` "collision" (default) / "file".
+All of it is [bullet-memory]: restated from the published algorithm, not checked against a running
+Bullet (pybullet is not installable here or on the GPU box, profiles/r02a_pybullet_probe.txt).
 """
 import math
 import xml.etree.ElementTree as ET
@@ -60,21 +90,68 @@ def _vec(s, default=(0.0, 0.0, 0.0)):
 
 class Link(object):
     __slots__ = ("name", "com_xyz", "parent", "joint_type", "axis", "origin_xyz", "origin_R",
-                 "lower", "upper", "children")
+                 "lower", "upper", "children", "mass", "inertia_file", "R_inertial", "boxes")
 
 
 class Body(object):
     """Kinematic tree of one URDF with Bullet's link numbering (base = -1)."""
 
+    @classmethod
+    def from_arrays(cls, d):
+        """Rebuild the tree from the `geo/*` arrays gen_golden.py stored in tests/golden/ref_data_and_units.npz
+        (written by __init__ below from the reference's exo_v3.urdf), so tests run without /root/reference."""
+        self = cls.__new__(cls)
+        self.base_name = "robot_base"
+        self.base_com = np.zeros(3)
+        self.base_pos = np.array(d["geo/base_pos"], dtype=np.float64)
+        self.links, self.index_of = [], {self.base_name: -1}
+        for i in range(len(d["geo/parent"])):
+            ln = Link()
+            ln.name = str(d["geo/names"][i])
+            ln.com_xyz = np.array(d["geo/com_xyz"][i], dtype=np.float64)
+            ln.parent = int(d["geo/parent"][i])
+            ln.joint_type = "revolute" if int(d["geo/joint_type"][i]) == 0 else "prismatic"
+            ln.axis = np.array(d["geo/axis"][i], dtype=np.float64)
+            ln.origin_xyz = np.array(d["geo/origin_xyz"][i], dtype=np.float64)
+            ln.origin_R = np.array(d["geo/origin_R"][i], dtype=np.float64).reshape(3, 3)
+            ln.lower, ln.upper = float(d["geo/lower"][i]), float(d["geo/upper"][i])
+            ln.mass = float(d["geo/mass"][i])
+            ln.inertia_file = np.array(d["geo/inertia_file"][i], dtype=np.float64)
+            ln.R_inertial = np.array(d["geo/R_inertial"][i], dtype=np.float64).reshape(3, 3)
+            ln.boxes = [(np.array(d["geo/box_size"][i], dtype=np.float64), np.array(d["geo/box_xyz"][i], dtype=np.float64),
+                         np.array(d["geo/box_R"][i], dtype=np.float64).reshape(3, 3))]
+            self.index_of[ln.name] = i
+            self.links.append(ln)
+        self.n = len(self.links)
+        self.q, self.qd, self.targets = np.zeros(self.n), np.zeros(self.n), {}
+        self.cache = self.forward_kinematics(self.q)
+        return self
+
     def __init__(self, path, base_position):
         root = ET.parse(path).getroot()
         links = {}
+        self.inertial = {}       # name -> (mass, diag inertia[3], inertial-frame rotation, collision boxes)
         for le in root.findall("link"):
             com = (0.0, 0.0, 0.0)
             ine = le.find("inertial")
             if ine is not None and ine.find("origin") is not None:
                 com = _vec(ine.find("origin").get("xyz"))
             links[le.get("name")] = np.array(com, dtype=np.float64)
+            mass, diag, Rin = 0.0, np.zeros(3), np.eye(3)
+            if ine is not None:
+                mass = float(ine.find("mass").get("value"))
+                it = ine.find("inertia")
+                assert all(float(it.get(k, 0.0)) == 0.0 for k in ("ixy", "ixz", "iyz")), "principal axes expected"
+                diag = np.array([float(it.get(k)) for k in ("ixx", "iyy", "izz")])
+                if ine.find("origin") is not None:
+                    Rin = rpy_matrix(*_vec(ine.find("origin").get("rpy")))
+            boxes = []
+            for ce in le.findall("collision"):
+                org = ce.find("origin")
+                boxes.append((_vec(ce.find("geometry").find("box").get("size")),
+                              _vec(org.get("xyz") if org is not None else None),
+                              rpy_matrix(*_vec(org.get("rpy") if org is not None else None))))
+            self.inertial[le.get("name")] = (mass, diag, Rin, boxes)
         joints = []
         child_names = set()
         for je in root.findall("joint"):
@@ -112,6 +189,7 @@ class Body(object):
                 ln.origin_xyz = j["xyz"]
                 ln.origin_R = rpy_matrix(*j["rpy"])
                 ln.lower, ln.upper = j["lower"], j["upper"]
+                ln.mass, ln.inertia_file, ln.R_inertial, ln.boxes = self.inertial[ln.name]
                 self.index_of[ln.name] = len(self.links)
                 self.links.append(ln)
                 visit(ln.name)
@@ -148,12 +226,16 @@ class Body(object):
 
 
 class World(object):
-    def __init__(self, link_state_lag=1, joint_limits="off", kp=0.1, kd=1.0):
+    def __init__(self, link_state_lag=1, joint_limits="off", kp=0.1, kd=1.0, motor_model="ideal", **full_knobs):
         assert link_state_lag in (0, 1)
         assert joint_limits in ("off", "clamp")
+        assert motor_model in ("ideal", "full")
         self.link_state_lag = link_state_lag
         self.joint_limits = joint_limits
         self.kp, self.kd = kp, kd
+        self.motor_model = motor_model
+        self.full_knobs = full_knobs     # inertia_from, iterations, residual_threshold, row_order, ... (multibody.FullStep)
+        self.full = []
         self.dt = 1.0 / 240.0
         self.gravity = (0.0, 0.0, 0.0)
         self.bodies = []
@@ -161,9 +243,11 @@ class World(object):
 
     def reset_simulation(self):
         self.bodies = []
+        self.full = []
 
     def load_urdf(self, path, base_position):
         self.bodies.append(Body(path, base_position))
+        self.full.append(None)
         return len(self.bodies) - 1
 
     def set_position_targets(self, body, joints, targets):
@@ -175,9 +259,23 @@ class World(object):
         return self.bodies[body].cache[link]
 
     def step_simulation(self):
-        for b in self.bodies:
+        for bi, b in enumerate(self.bodies):
             if self.link_state_lag == 1:
                 b.cache = b.forward_kinematics(b.q)        # FK stage precedes integration
+            if self.motor_model == "full":
+                if self.full[bi] is None:                  # dt / gravity are set after loadURDF by the env's constructor
+                    import multibody
+                    self.full[bi] = multibody.FullStep(b, self.dt, self.gravity, self.kp, self.kd, **self.full_knobs)
+                fs = self.full[bi]
+                fs.dt, fs.gravity = self.dt, self.gravity
+                for j, t in b.targets.items():             # same crossing statistic as the ideal model
+                    qn = b.q[j] + self.kp * (t - b.q[j])
+                    if qn < b.links[j].lower or qn > b.links[j].upper:
+                        self.limit_crossings += 1
+                fs.step()
+                if self.link_state_lag == 0:
+                    b.cache = b.forward_kinematics(b.q)
+                continue
             for j, t in b.targets.items():
                 v = self.kp * (t - b.q[j]) / self.dt + b.qd[j] + self.kd * (0.0 - b.qd[j])
                 qn = b.q[j] + self.dt * v
