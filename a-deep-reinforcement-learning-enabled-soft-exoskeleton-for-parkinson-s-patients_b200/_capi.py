@@ -8,6 +8,7 @@ LIB_PATH = os.environ.get("EXO_LIB", os.path.join(HERE, "libexo_env.so"))   # EX
 OBS_DIM, ACT_DIM, NLINKS, N_STATS = 80, 7, 19, 16
 F32, F64 = 0, 1
 ODE_PROPAGATOR, ODE_RK45 = 0, 1
+MOTOR_IDEAL, MOTOR_FULL = 0, 1
 
 
 class ExoConfig(C.Structure):
@@ -19,7 +20,7 @@ class ExoConfig(C.Structure):
                 ("humerus_length", C.c_double), ("forearm_length", C.c_double), ("hand_length", C.c_double),
                 ("link_state_lag", C.c_int32), ("joint_limits", C.c_int32), ("precision", C.c_int32),
                 ("ode", C.c_int32), ("auto_reset", C.c_int32), ("reference_ctor", C.c_int32),
-                ("metrics", C.c_int32), ("reserved", C.c_int32)]
+                ("metrics", C.c_int32), ("motor_model", C.c_int32)]
 
 
 class ExoGeometry(C.Structure):
@@ -28,6 +29,19 @@ class ExoGeometry(C.Structure):
                 ("axis", (C.c_double * 3) * NLINKS), ("com_xyz", (C.c_double * 3) * NLINKS),
                 ("lower", C.c_double * NLINKS), ("upper", C.c_double * NLINKS), ("base_pos", C.c_double * 3),
                 ("act_link", C.c_int32 * 14), ("shoulder_link", C.c_int32), ("elbow_link", C.c_int32)]
+
+
+class ExoLinkDynamics(C.Structure):
+    _fields_ = [("mass", C.c_double * NLINKS), ("inertia_diag", (C.c_double * 3) * NLINKS),
+                ("inertial_R", (C.c_double * 9) * NLINKS), ("box_size", (C.c_double * 3) * NLINKS),
+                ("box_xyz", (C.c_double * 3) * NLINKS), ("box_R", (C.c_double * 9) * NLINKS)]
+
+
+class ExoMotorModel(C.Structure):
+    _fields_ = [("inertia_from_file", C.c_int32), ("iterations", C.c_int32), ("row_order", C.c_int32), ("reserved", C.c_int32),
+                ("residual_threshold", C.c_double), ("kp", C.c_double), ("kd", C.c_double), ("max_force", C.c_double),
+                ("default_motor_impulse", C.c_double), ("linear_damping", C.c_double), ("angular_damping", C.c_double),
+                ("gravity", C.c_double * 3), ("erp", C.c_double), ("limit_max_impulse", C.c_double)]
 
 
 class ExoPolicyWeights(C.Structure):
@@ -56,7 +70,7 @@ class ExoInfo(C.Structure):
 # EXO_FIELD_* (include/exo_env.h): name -> id; EXO_DT_* -> torch dtype name
 FIELDS = {name: i for i, name in enumerate(
     ("q", "q_lag", "pos_vec", "elbow_ref", "prev_action", "prev_action2", "force_max", "shift", "G", "IDS", "tremor_table",
-     "tremor_mag", "counts", "meta", "mt_state", "ep_return"))}
+     "tremor_mag", "counts", "meta", "mt_state", "ep_return", "qd", "q_pris", "q_pris_lag"))}
 DT_REAL, DT_F64, DT_I32, DT_U32 = 0, 1, 2, 3
 
 
@@ -66,6 +80,8 @@ SIGNATURES = {
     "exo_abi_version": (C.c_int, []),
     "exo_create": (C.c_int, [C.POINTER(ExoConfig), C.POINTER(ExoGeometry), C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
     "exo_destroy": (C.c_int, [C.c_void_p]),
+    "exo_set_motor_model": (C.c_int, [C.c_void_p, C.POINTER(ExoLinkDynamics), C.POINTER(ExoMotorModel)]),
+    "exo_default_motor_model": (None, [C.POINTER(ExoMotorModel)]),
     "exo_load_motions": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int32), C.c_int32, C.c_int32]),
     "exo_set_env_types": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint8), C.POINTER(C.c_int32)]),
     "exo_seed": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p]),

@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "_obj")
 LIB = os.environ.get("EXO_LIB_OUT", os.path.join(HERE, "libexo_env.so"))
-UNITS = ["exo_api.cu", "exo_step_f32.cu", "exo_step_f64.cu", "exo_reset_f32.cu", "exo_reset_f64.cu", "exo_lap.cu", "exo_policy.cu", "exo_policy_fp32.cu", "exo_td7.cu"]
+UNITS = ["exo_api.cu", "exo_step_f32.cu", "exo_step_f64.cu", "exo_motor_f32.cu", "exo_motor_f64.cu", "exo_reset_f32.cu", "exo_reset_f64.cu", "exo_lap.cu", "exo_policy.cu", "exo_policy_fp32.cu", "exo_td7.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"] + \
     os.environ.get("EXO_EXTRA_NVCC_FLAGS", "").split()      # tuning experiments only (e.g. -DEXO_STEP_THREADS=32)

@@ -50,6 +50,10 @@ struct ExoHandle {
     EnvArrays<double> Ad;
     ChainConst<float> Cf;
     ChainConst<double> Cd;
+    DynConst<float> Df;          // EXO_MOTOR_FULL: inertial data + solver settings (exo_set_motor_model)
+    DynConst<double> Dd;
+    bool have_dyn;
+    int dummy_link[EXO_NPRIS];   // URDF link index of dummy d (humerus slots 0..6, forearm 7..8)
     // staging for the host-buffer entry points
     float* d_act; float* d_obs; void* d_rew; uint8_t* d_done; uint8_t* d_mask;
     uint32_t* d_seeds;
@@ -119,8 +123,17 @@ static int build_chain(ExoHandle* h) {
         double off[3];
         const int c = carrier_of(g, g->act_link[a], off);
         if (c != want[a]) return fail(EXO_ERR_TOPOLOGY, "actuator endpoint %d rides on link %d, kernel expects %d", a, c, want[a]);
-        if (c == 2) { memcpy(C.off_hum[hum_slot[a]], off, sizeof(off)); hum++; }
-        else if (c == 4) { memcpy(C.off_alk[alk++], off, sizeof(off)); }
+        // prismatic axis of the dummy in its carrier's frame (the dummy's joint hangs directly off the carrier)
+        const int dl = g->act_link[a];
+        double pax[3] = {0, 0, 0};
+        if (c >= 0) {
+            if (g->joint_type[dl] != 1 || g->parent[dl] != c) return fail(EXO_ERR_TOPOLOGY, "actuator endpoint %d: expected a prismatic leaf on link %d", a, c);
+            const double an = sqrt(g->axis[dl][0] * g->axis[dl][0] + g->axis[dl][1] * g->axis[dl][1] + g->axis[dl][2] * g->axis[dl][2]);
+            for (int i = 0; i < 3; i++)
+                pax[i] = (g->origin_R[dl][i * 3] * g->axis[dl][0] + g->origin_R[dl][i * 3 + 1] * g->axis[dl][1] + g->origin_R[dl][i * 3 + 2] * g->axis[dl][2]) / an;
+        }
+        if (c == 2) { memcpy(C.off_hum[hum_slot[a]], off, sizeof(off)); memcpy(C.pax_hum[hum_slot[a]], pax, sizeof(pax)); h->dummy_link[hum_slot[a]] = dl; hum++; }
+        else if (c == 4) { memcpy(C.off_alk[alk], off, sizeof(off)); memcpy(C.pax_alk[alk], pax, sizeof(pax)); h->dummy_link[7 + alk] = dl; alk++; }
         else { for (int k = 0; k < 3; k++) C.fixed[fix][k] = g->base_pos[k] + off[k]; fix++; }
     }
     double off[3];
@@ -129,8 +142,114 @@ static int build_chain(ExoHandle* h) {
     memcpy(C.sh_ref, C.p0, sizeof(C.p0));
     if (carrier_of(g, g->elbow_link, off) != 3) return fail(EXO_ERR_TOPOLOGY, "elbow reference must ride on link 3");
     memcpy(C.off_elbow, off, sizeof(off));
-    (void)mat3mul;
     cast_chain(C, h->Cf);
+    return 0;
+}
+
+extern "C" void exo_default_motor_model(ExoMotorModel* m) {
+    if (!m) return;
+    memset(m, 0, sizeof(*m));
+    m->inertia_from_file = 0; m->iterations = 50; m->row_order = 0; m->residual_threshold = 1e-7;
+    m->kp = 0.1; m->kd = 1.0; m->max_force = 1.0e5; m->default_motor_impulse = 1.0;
+    m->linear_damping = 0.04; m->angular_damping = 0.04;
+    m->gravity[0] = 0; m->gravity[1] = 0; m->gravity[2] = -9.81;
+    m->erp = 0.2; m->limit_max_impulse = 100.0;
+}
+
+// Order in which btAlignedObjectArray::quickSort leaves n elements whose keys all compare equal (the world's multibody
+// constraints all carry one island id): the partition step swaps symmetric pairs, then both halves recurse.
+static void bullet_quicksort_equal(std::vector<int>& a, int lo, int hi) {
+    int i = lo, j = hi;
+    do {
+        if (i <= j) { std::swap(a[i], a[j]); i++; j--; }
+    } while (i <= j);
+    if (lo < j) bullet_quicksort_equal(a, lo, j);
+    if (i < hi) bullet_quicksort_equal(a, i, hi);
+}
+
+// principal inertias of link l in its inertial frame: the URDF's, or (pybullet default) those of the collision box's AABB
+static void link_inertia_diag(const ExoLinkDynamics* L, int l, bool from_file, double* diag) {
+    if (from_file) { memcpy(diag, L->inertia_diag[l], 3 * sizeof(double)); return; }
+    double ext[3];
+    for (int i = 0; i < 3; i++) {            // |R_inertial^T box_R| * size
+        ext[i] = 0;
+        for (int j = 0; j < 3; j++) {
+            double rij = 0;
+            for (int k = 0; k < 3; k++) rij += L->inertial_R[l][k * 3 + i] * L->box_R[l][k * 3 + j];
+            ext[i] += fabs(rij) * L->box_size[l][j];
+        }
+    }
+    const double m = L->mass[l] / 12.0;
+    diag[0] = m * (ext[1] * ext[1] + ext[2] * ext[2]); diag[1] = m * (ext[0] * ext[0] + ext[2] * ext[2]); diag[2] = m * (ext[0] * ext[0] + ext[1] * ext[1]);
+}
+
+// T = A diag A^T as (xx,xy,xz,yy,yz,zz)
+static void sym_from_diag(const double* A, const double* diag, double* out6) {
+    double M[9];
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) M[i * 3 + j] = A[i * 3] * diag[0] * A[j * 3] + A[i * 3 + 1] * diag[1] * A[j * 3 + 1] + A[i * 3 + 2] * diag[2] * A[j * 3 + 2];
+    out6[0] = M[0]; out6[1] = M[1]; out6[2] = M[2]; out6[3] = M[4]; out6[4] = M[5]; out6[5] = M[8];
+}
+
+template <typename R>
+static void cast_dyn(const DynConst<double>& s, DynConst<R>& d) {
+#define CP(f) for (size_t i = 0; i < sizeof(s.f) / sizeof(double); i++) ((R*)&d.f)[i] = (R)((const double*)&s.f)[i]
+    CP(m_link); CP(com_link); CP(I_link); CP(m_d); CP(I_d); CP(g);
+#undef CP
+    d.kp = (R)s.kp; d.kd = (R)s.kd; d.cap_pos = (R)s.cap_pos; d.cap_vel = (R)s.cap_vel; d.k_lin = (R)s.k_lin; d.k_ang = (R)s.k_ang;
+    d.dt = (R)s.dt; d.erp = (R)s.erp; d.limit_cap = (R)s.limit_cap; d.threshold = (R)s.threshold;
+    d.iterations = s.iterations; d.n_cons = s.n_cons;
+    memcpy(d.cons, s.cons, sizeof(s.cons));
+}
+
+extern "C" int exo_set_motor_model(ExoHandle* h, const ExoLinkDynamics* L, const ExoMotorModel* model) {
+    if (!h || !L) return fail(EXO_ERR_ARG, "exo_set_motor_model: bad arguments");
+    if (h->cfg.motor_model != EXO_MOTOR_FULL) return fail(EXO_ERR_STATE, "exo_set_motor_model: the handle was created with EXO_MOTOR_IDEAL");
+    ExoMotorModel mm;
+    if (model) mm = *model; else exo_default_motor_model(&mm);
+    if (mm.iterations < 1 || mm.iterations > 100000) return fail(EXO_ERR_ARG, "exo_set_motor_model: iterations out of range");
+    const ExoGeometry* g = &h->geo;
+    DynConst<double>& D = h->Dd;
+    memset(&D, 0, sizeof(D));
+    for (int i = 0; i < 5; i++) {
+        double diag[3];
+        link_inertia_diag(L, i, mm.inertia_from_file != 0, diag);
+        D.m_link[i] = L->mass[i];
+        memcpy(D.com_link[i], g->com_xyz[i], 3 * sizeof(double));
+        sym_from_diag(L->inertial_R[i], diag, D.I_link[i]);
+    }
+    for (int d = 0; d < EXO_NPRIS; d++) {
+        const int l = h->dummy_link[d];
+        double diag[3], A[9];
+        link_inertia_diag(L, l, mm.inertia_from_file != 0, diag);
+        mat3mul(g->origin_R[l], L->inertial_R[l], A);          // inertial frame in the carrier frame
+        D.m_d[d] = L->mass[l];
+        if (!(D.m_d[d] > 0)) return fail(EXO_ERR_ARG, "exo_set_motor_model: dummy link %d has no mass", l);
+        sym_from_diag(A, diag, D.I_d[d]);
+    }
+    D.dt = 1.0 / 40.0;                                           // Exoskeleton_env.py:59,117
+    D.kp = mm.kp; D.kd = mm.kd; D.cap_pos = mm.max_force * D.dt; D.cap_vel = mm.default_motor_impulse;
+    D.k_lin = mm.linear_damping; D.k_ang = mm.angular_damping;
+    memcpy(D.g, mm.gravity, sizeof(D.g));
+    D.erp = mm.erp; D.limit_cap = mm.limit_max_impulse; D.threshold = mm.residual_threshold; D.iterations = mm.iterations;
+    // world constraint list: joint-limit constraints in link order (URDF import), then createJointMotors' motors in link order
+    std::vector<int> cons;                     // link index for a motor, -(link+1) for a limit constraint
+    for (int l = 0; l < EXO_NLINKS; l++) if (g->lower[l] <= g->upper[l]) cons.push_back(-(l + 1));
+    for (int l = 0; l < EXO_NLINKS; l++) cons.push_back(l);
+    if (mm.row_order == 0 && cons.size() > 1) bullet_quicksort_equal(cons, 0, (int)cons.size() - 1);
+    int dof_of[EXO_NLINKS];
+    for (int l = 0; l < EXO_NLINKS; l++) dof_of[l] = l < 5 ? l : -1;
+    for (int d = 0; d < EXO_NPRIS; d++) dof_of[h->dummy_link[d]] = 5 + d;
+    D.n_cons = 0;
+    for (int c : cons) {
+        const int l = c >= 0 ? c : -c - 1, dof = dof_of[l];
+        if (dof < 0) continue;                 // the dummies on the fixed base: decoupled, held at rest (exo_motor.cuh header)
+        if (c < 0 && dof >= 5) continue;       // prismatic limits (+-0.5 m) are never reached
+        if (D.n_cons >= EXO_MAX_ROWS) return fail(EXO_ERR_TOPOLOGY, "exo_set_motor_model: too many constraint rows");
+        D.cons[D.n_cons++] = (signed char)(c >= 0 ? dof : -(dof + 1));
+    }
+    cast_dyn(D, h->Df);
+    h->have_dyn = true;
     return 0;
 }
 
@@ -144,6 +263,7 @@ static int alloc_arrays(ExoHandle* h, EnvArrays<R>& A) {
     AL(ret, R, st); AL(counts, int, st); AL(meta, int, st); AL(mag, double, st);
     AL(IDS, double, n * EXO_IDS_PITCH); AL(mt, uint32_t, n * EXO_MT_PITCH);
     AL(stats, double, EXO_N_STATS); AL(fin_count, int, 2); AL(fin_list, int, 2 * st);
+    if (h->cfg.motor_model == EXO_MOTOR_FULL) { AL(dyn, V4<R>, NV_DYN * st); AL(tgt, V4<R>, NV_TGT * st); }
 #undef AL
     return 0;
 }
@@ -152,6 +272,7 @@ extern "C" int exo_create(const ExoConfig* cfg, const ExoGeometry* geo, int32_t 
     if (!cfg || !geo || !out || n_envs <= 0) return fail(EXO_ERR_ARG, "exo_create: bad arguments");
     if (cfg->precision != EXO_F32 && cfg->precision != EXO_F64) return fail(EXO_ERR_ARG, "precision must be EXO_F32 or EXO_F64");
     if (cfg->ode != EXO_ODE_PROPAGATOR) return fail(EXO_ERR_ARG, "ode mode %d is not built in this version", cfg->ode);
+    if (cfg->motor_model != EXO_MOTOR_IDEAL && cfg->motor_model != EXO_MOTOR_FULL) return fail(EXO_ERR_ARG, "motor_model must be EXO_MOTOR_IDEAL or EXO_MOTOR_FULL");
     int ndev = 0;
     CK(cudaGetDeviceCount(&ndev));
     if (device < 0 || device >= ndev) return fail(EXO_ERR_CUDA, "device %d not present (%d CUDA devices): this library has no CPU path", device, ndev);
@@ -162,7 +283,7 @@ extern "C" int exo_create(const ExoConfig* cfg, const ExoGeometry* geo, int32_t 
     ExoHandle* h = new ExoHandle();
     h->cfg = *cfg; h->geo = *geo; h->n = n_envs; h->stride = (n_envs + 31) & ~31; h->device = device;
     h->nax = 4; h->max_len = 0; h->n_motions = 0; h->have_motions = h->have_types = h->seeded = false; h->launches = 0;
-    h->n_sm = prop.multiProcessorCount; h->parity = 0; h->pipe_ready = false;
+    h->n_sm = prop.multiProcessorCount; h->parity = 0; h->pipe_ready = false; h->have_dyn = false;
     h->d_act = nullptr; h->d_obs = nullptr; h->d_rew = nullptr; h->d_done = nullptr; h->d_mask = nullptr; h->d_seeds = nullptr;
     if (int rc = build_chain(h)) { delete h; return rc; }
     int rc = (cfg->precision == EXO_F32) ? alloc_arrays(h, h->Af) : alloc_arrays(h, h->Ad);
@@ -260,6 +381,7 @@ static StepConst<R> step_const(const ExoHandle* h) {
     K.parity = h->parity;
     K.L1 = (R)h->cfg.humerus_length; K.L2 = (R)h->cfg.forearm_length;
     K.lag = h->cfg.link_state_lag; K.limits = h->cfg.joint_limits; K.auto_reset = h->cfg.auto_reset; K.metrics = h->cfg.metrics;
+    K.motor_full = h->cfg.motor_model == EXO_MOTOR_FULL;
     K.env0 = 0; K.env1 = h->n;
     return K;
 }
@@ -273,6 +395,7 @@ static ResetConst reset_const(const ExoHandle* h) {
     K.fmax_sh0 = h->cfg.max_force_shoulder; K.fmax_el0 = h->cfg.max_force_elbow;
     K.dt = 1.0 / 40.0;                       // Exoskeleton_env.py:59
     K.lag = h->cfg.link_state_lag;
+    K.motor_full = h->cfg.motor_model == EXO_MOTOR_FULL;
     K.ctor_skip = 0; K.list_parity = -1;
     return K;
 }
@@ -293,6 +416,7 @@ static int reset_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const 
 static int check_ready(ExoHandle* h, const char* who) {
     if (!h) return fail(EXO_ERR_ARG, "%s: null handle", who);
     if (!h->seeded) return fail(EXO_ERR_STATE, "%s: call exo_load_motions, exo_set_env_types and exo_seed first", who);
+    if (h->cfg.motor_model == EXO_MOTOR_FULL && !h->have_dyn) return fail(EXO_ERR_STATE, "%s: EXO_MOTOR_FULL needs exo_set_motor_model", who);
     CK(cudaSetDevice(h->device));
     return 0;
 }
@@ -325,6 +449,10 @@ extern "C" int exo_reset(ExoHandle* h, const uint8_t* mask_dev, float* obs_dev, 
                                        : reset_t(h, h->Ad, h->Cd, mask_dev, obs_dev, -1, 0, s);
 }
 
+template <typename R> static const DynConst<R>& dyn_const(const ExoHandle* h);
+template <> const DynConst<float>& dyn_const<float>(const ExoHandle* h) { return h->Df; }
+template <> const DynConst<double>& dyn_const<double>(const ExoHandle* h) { return h->Dd; }
+
 template <typename R>
 static int step_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const float* actions, float* obs, void* reward,
                   uint8_t* done, const ExoInfo* info, cudaStream_t s, int env0 = 0, int env1 = -1) {
@@ -339,8 +467,14 @@ static int step_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const f
         ip.tremor_torque_val = (R*)info->tremor_torque_val; ip.tremor_ampl_val = (R*)info->tremor_ampl_val;
         ip.reward_parts = (R*)info->reward_parts; ip.amp_metric = (R*)info->amp_metric;
     }
-    launch_step<R>(A, C, K, h->nax, want_info, actions, obs, (R*)reward, done, ip, s);
-    h->launches += 1;
+    if (K.motor_full) {
+        launch_step_full<R>(A, C, K, h->nax, want_info, actions, obs, (R*)reward, done, ip, s);
+        launch_motor<R>(A, C, dyn_const<R>(h), K.lag, K.env0, K.env1, s);
+        h->launches += 2;
+    } else {
+        launch_step<R>(A, C, K, h->nax, want_info, actions, obs, (R*)reward, done, ip, s);
+        h->launches += 1;
+    }
     CK(cudaGetLastError());
     if (h->cfg.auto_reset) return reset_t(h, A, C, nullptr, obs, K.parity, 0, s);
     return 0;
@@ -426,8 +560,8 @@ extern "C" int exo_reset_host(ExoHandle* h, const uint8_t* mask_host, float* obs
 
 // elements per env and dtype of each EXO_FIELD_*
 static int field_shape(const ExoHandle* h, int field, int* k, int* dtype) {
-    static const int K0[EXO_N_FIELDS] = {5, 5, 21, 3, 7, 7, 2, 42, 49, 147, 0, 1, 1, 1, 625, 1};
-    static const int D0[EXO_N_FIELDS] = {0, 0, 0, 0, 0, 0, 0, 0, 0, EXO_DT_F64, 0, EXO_DT_F64, EXO_DT_I32, EXO_DT_I32, EXO_DT_U32, 0};
+    static const int K0[EXO_N_FIELDS] = {5, 5, 21, 3, 7, 7, 2, 42, 49, 147, 0, 1, 1, 1, 625, 1, EXO_NDOF, EXO_NPRIS, EXO_NPRIS};
+    static const int D0[EXO_N_FIELDS] = {0, 0, 0, 0, 0, 0, 0, 0, 0, EXO_DT_F64, 0, EXO_DT_F64, EXO_DT_I32, EXO_DT_I32, EXO_DT_U32, 0, 0, 0, 0};
     if (field < 0 || field >= EXO_N_FIELDS) return -1;
     *k = K0[field]; *dtype = D0[field];
     if (field == EXO_FIELD_TREMOR_TABLE) *k = (h->cfg.precision == EXO_F32 ? h->Af.table_len : h->Ad.table_len) * h->nax;
@@ -448,6 +582,8 @@ static int field_io(ExoHandle* h, int32_t field, void* buf, int set, void* strea
     if (!h->have_types) return fail(EXO_ERR_STATE, "%s: env types not set yet", who);
     int k, dt;
     if (field_shape(h, field, &k, &dt)) return fail(EXO_ERR_ARG, "%s: unknown field %d", who, field);
+    if (field >= EXO_FIELD_QD && field <= EXO_FIELD_Q_PRIS_LAG && h->cfg.motor_model != EXO_MOTOR_FULL)
+        return fail(EXO_ERR_STATE, "%s: field %d exists only with EXO_MOTOR_FULL", who, field);
     CK(cudaSetDevice(h->device));
     cudaStream_t s = (cudaStream_t)stream;
     const int naxv = (h->nax + 3) / 4;

@@ -7,6 +7,13 @@ namespace exo {
 template <typename R>
 void launch_step(const EnvArrays<R>& A, const ChainConst<R>& C, const StepConst<R>& K, int nax, bool info_on,
                  const float* actions, float* obs, R* reward, uint8_t* done, const InfoPtrs<R>& ip, cudaStream_t s);
+// EXO_MOTOR_FULL: the same step with the FULL template flag (targets handed to the motor kernel), then the general
+// multibody step itself (exo_motor.cuh)
+template <typename R>
+void launch_step_full(const EnvArrays<R>& A, const ChainConst<R>& C, const StepConst<R>& K, int nax, bool info_on,
+                      const float* actions, float* obs, R* reward, uint8_t* done, const InfoPtrs<R>& ip, cudaStream_t s);
+template <typename R>
+void launch_motor(const EnvArrays<R>& A, const ChainConst<R>& C, const DynConst<R>& D, int lag, int env0, int env1, cudaStream_t s);
 // One kernel: draws, tremor table, parameters, first observation and propagator. K.list_parity >= 0 resets the envs
 // of that finished-list (auto-reset), otherwise the envs selected by mask (NULL: all). Returns a cudaError_t.
 template <typename R>

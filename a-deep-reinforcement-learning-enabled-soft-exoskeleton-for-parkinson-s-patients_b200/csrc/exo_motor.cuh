@@ -1,0 +1,376 @@
+// exo_motor.cuh — the general Bullet multibody step for the exo_v3.urdf tree, one thread per environment
+// (ExoConfig.motor_model = EXO_MOTOR_FULL). Replaces `client.stepSimulation()` (Exoskeleton_env.py:433) after
+// `setJointMotorControlArray(POSITION_CONTROL)` (Exoskeleton_sim_pybullet.py:109-117) WITHOUT assuming that the
+// constraint solver converges: forward dynamics of the tree (gravity, Bullet's per-link velocity damping, Coriolis /
+// centrifugal / gyroscopic terms), one motor row per joint with Bullet's impulse caps, joint-limit rows while a bound
+// is violated, `iterations` sweeps of projected Gauss-Seidel in Bullet's row order with its early-exit test, then
+// semi-implicit Euler. The algorithm is restated in oracle/multibody.py (fp64 numpy; its header lists what each stage
+// follows in Bullet); tests/test_gpu_parity.py compares the two. The default, EXO_MOTOR_IDEAL, is the fixed point of
+// this iteration (q+ = q + kp (target - q)), evaluated inside the step kernel.
+//
+// Degrees of freedom: 5 revolute arm joints + 9 prismatic dummies carried by the humerus (7) and forearm (2). The 5
+// dummies on the fixed base are decoupled 1-DoF systems (M row = 1 kg on the diagonal): their default velocity motor
+// cancels the gravity impulse (0.245 N s < the 1 N s cap) exactly in its first sweep, so they never move and are not
+// simulated. Everything is evaluated in the world frame.
+//
+// Cost: ~12 kflop + up to 50 x 14 x 15 FMA per env-step, fp32 or fp64 like the rest of the handle; the 14 x 14
+// inverse mass matrix lives in local memory (L1-resident). Compute-bound, unlike the HBM-bound default step.
+#pragma once
+#include "exo_step.cuh"
+
+namespace exo {
+
+template <typename R> __device__ __forceinline__ void cross3(const R* a, const R* b, R* o) {
+    o[0] = a[1] * b[2] - a[2] * b[1]; o[1] = a[2] * b[0] - a[0] * b[2]; o[2] = a[0] * b[1] - a[1] * b[0];
+}
+template <typename R> __device__ __forceinline__ R dot3(const R* a, const R* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+template <typename R> __device__ __forceinline__ void matvec3(const R* M, const R* v, R* o) {
+#pragma unroll
+    for (int i = 0; i < 3; i++) o[i] = M[i * 3] * v[0] + M[i * 3 + 1] * v[1] + M[i * 3 + 2] * v[2];
+}
+// world inertia tensor Rm * I6 * Rm^T (I6 = xx,xy,xz,yy,yz,zz in the body frame) -> full 3x3
+template <typename R> __device__ __forceinline__ void rotate_inertia(const R* Rm, const R* I6, R* out) {
+    const R I[9] = {I6[0], I6[1], I6[2], I6[1], I6[3], I6[4], I6[2], I6[4], I6[5]};
+    R T[9];
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) T[i * 3 + j] = Rm[i * 3] * I[j] + Rm[i * 3 + 1] * I[3 + j] + Rm[i * 3 + 2] * I[6 + j];
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) out[i * 3 + j] = T[i * 3] * Rm[j * 3] + T[i * 3 + 1] * Rm[j * 3 + 1] + T[i * 3 + 2] * Rm[j * 3 + 2];
+}
+
+template <typename R>
+__global__ void __launch_bounds__(64)
+exo_motor_kernel(EnvArrays<R> S, ChainConst<R> C, DynConst<R> D, int lag, int env0, int env1) {
+    const int e = env0 + blockIdx.x * blockDim.x + threadIdx.x;
+    const int st = S.stride;
+    int sweeps_done = 0, did = 0;
+    if (e < env1) {
+        R tg[8];
+        ld4(S.tgt + e, tg); ld4(S.tgt + (size_t)st + e, tg + 4);
+        if (tg[5] != R(0)) {
+            did = 1;
+            R q[5], dy[4 * NV_DYN];
+#pragma unroll
+            for (int j = 0; j < 5; j++) q[j] = *exo_word(S.state, W_Q + j, e, st);
+#pragma unroll
+            for (int v = 0; v < NV_DYN; v++) ld4(S.dyn + (size_t)v * st + e, dy + 4 * v);
+            R* qd = dy + W_QD;
+            R* qp = dy + W_QP;
+            // ---- 1. kinematics of the 5 revolute links
+            R Rl[5][9], pl[5][3], ax[5][3];
+            {
+                const R eye[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+                R sn, cs;
+                sincos_r(q[0], &sn, &cs);
+                mul_origin_rz(eye, C.Rorg[0], sn, cs, Rl[0]);
+                pl[0][0] = C.p0[0]; pl[0][1] = C.p0[1]; pl[0][2] = C.p0[2];
+#pragma unroll
+                for (int i = 1; i < 5; i++) {
+                    sincos_r(q[i], &sn, &cs);
+                    affine(Rl[i - 1], pl[i - 1], C.porg[i], pl[i]);
+                    mul_origin_rz(Rl[i - 1], C.Rorg[i], sn, cs, Rl[i]);
+                }
+#pragma unroll
+                for (int i = 0; i < 5; i++) { ax[i][0] = Rl[i][2]; ax[i][1] = Rl[i][5]; ax[i][2] = Rl[i][8]; }   // joint axis = local z
+            }
+            // ---- 2. velocities / zero-qdd accelerations of the links (recursive Newton-Euler, forward pass)
+            R w[5][3], al[5][3], vo[5][3], ao[5][3];
+            {
+                R pw[3] = {0, 0, 0}, pal[3] = {0, 0, 0}, pv[3] = {0, 0, 0}, pa[3] = {0, 0, 0};
+#pragma unroll
+                for (int i = 0; i < 5; i++) {
+                    R r[3] = {0, 0, 0};
+                    if (i > 0) { r[0] = pl[i][0] - pl[i - 1][0]; r[1] = pl[i][1] - pl[i - 1][1]; r[2] = pl[i][2] - pl[i - 1][2]; }
+                    R wr[3], wwr[3], ar[3], wa[3];
+                    cross3(pw, r, wr); cross3(pw, wr, wwr); cross3(pal, r, ar); cross3(pw, ax[i], wa);
+#pragma unroll
+                    for (int k = 0; k < 3; k++) {
+                        vo[i][k] = pv[k] + wr[k];
+                        ao[i][k] = pa[k] + ar[k] + wwr[k];
+                        w[i][k] = pw[k] + ax[i][k] * qd[i];
+                        al[i][k] = pal[k] + wa[k] * qd[i];
+                    }
+#pragma unroll
+                    for (int k = 0; k < 3; k++) { pw[k] = w[i][k]; pal[k] = al[i][k]; pv[k] = vo[i][k]; pa[k] = ao[i][k]; }
+                }
+            }
+            // ---- 3. per body: inertial force/torque (gravity, damping, gyroscopic) and the composite inertias of M
+            R fl[5][3], nl[5][3];                       // force / moment about the link origin, accumulated over the subtree
+            R cm[5], ch[5][3], cI[5][6];                // composite mass, first moment, inertia about the world origin (per link, own bodies)
+            R bias[EXO_NDOF];
+            R B[5][EXO_NPRIS];                          // M[rev k][dummy d]
+#pragma unroll
+            for (int i = 0; i < 5; i++) {
+#pragma unroll
+                for (int k = 0; k < 3; k++) { fl[i][k] = 0; nl[i][k] = 0; ch[i][k] = 0; }
+#pragma unroll
+                for (int k = 0; k < 6; k++) cI[i][k] = 0;
+                cm[i] = 0;
+            }
+            auto body = [&](int carrier, R m, const R* c, const R* Iw, const R* vc, const R* ac, R* F, R* N) {
+                // Newton-Euler of one rigid body riding on `carrier` (angular state of the carrier)
+                R Iwv[3], Ial[3], gy[3];
+                matvec3(Iw, w[carrier], Iwv); matvec3(Iw, al[carrier], Ial); cross3(w[carrier], Iwv, gy);
+                const R nv = sqrt_r(dot3(vc, vc)), nw = sqrt_r(dot3(w[carrier], w[carrier]));
+#pragma unroll
+                for (int k = 0; k < 3; k++) {
+                    F[k] = m * (ac[k] - D.g[k]) + m * vc[k] * (D.k_lin + D.k_lin * nv);
+                    N[k] = Ial[k] + gy[k] + Iwv[k] * (D.k_ang + D.k_ang * nw);
+                }
+                // composite inertia of the carrier's own bodies about the carrier's joint origin (no large offsets: fp32-safe)
+                const R rr[3] = {c[0] - pl[carrier][0], c[1] - pl[carrier][1], c[2] - pl[carrier][2]};
+                const R r2 = dot3(rr, rr);
+                cm[carrier] += m;
+#pragma unroll
+                for (int k = 0; k < 3; k++) ch[carrier][k] += m * rr[k];
+                cI[carrier][0] += Iw[0] + m * (r2 - rr[0] * rr[0]); cI[carrier][1] += Iw[1] - m * rr[0] * rr[1];
+                cI[carrier][2] += Iw[2] - m * rr[0] * rr[2];        cI[carrier][3] += Iw[4] + m * (r2 - rr[1] * rr[1]);
+                cI[carrier][4] += Iw[5] - m * rr[1] * rr[2];        cI[carrier][5] += Iw[8] + m * (r2 - rr[2] * rr[2]);
+            };
+#pragma unroll
+            for (int i = 0; i < 5; i++) {               // the links themselves
+                R rc[3], c[3], Iw[9], t1[3], t2[3], t3[3], vc[3], ac[3], F[3], N[3], rxF[3];
+                matvec3(Rl[i], D.com_link[i], rc);
+#pragma unroll
+                for (int k = 0; k < 3; k++) c[k] = pl[i][k] + rc[k];
+                rotate_inertia(Rl[i], D.I_link[i], Iw);
+                cross3(w[i], rc, t1); cross3(w[i], t1, t2); cross3(al[i], rc, t3);
+#pragma unroll
+                for (int k = 0; k < 3; k++) { vc[k] = vo[i][k] + t1[k]; ac[k] = ao[i][k] + t3[k] + t2[k]; }
+                body(i, D.m_link[i], c, Iw, vc, ac, F, N);
+                cross3(rc, F, rxF);
+#pragma unroll
+                for (int k = 0; k < 3; k++) { fl[i][k] += F[k]; nl[i][k] += N[k] + rxF[k]; }
+            }
+            R ud[EXO_NPRIS][3], cd[EXO_NPRIS][3];
+#pragma unroll
+            for (int d = 0; d < EXO_NPRIS; d++) {        // the dummies: prismatic leaves on link 2 (humerus) or 4 (forearm)
+                const int cr = d < 7 ? 2 : 4;
+                const R* off = d < 7 ? C.off_hum[d] : C.off_alk[d - 7];
+                const R* pax = d < 7 ? C.pax_hum[d] : C.pax_alk[d - 7];
+                R loc[3], r[3], Iw[9], t1[3], t2[3], t3[3], t4[3], vc[3], ac[3], F[3], N[3], rxF[3];
+#pragma unroll
+                for (int k = 0; k < 3; k++) loc[k] = off[k] + pax[k] * qp[d];
+                matvec3(Rl[cr], loc, r); matvec3(Rl[cr], pax, ud[d]);
+#pragma unroll
+                for (int k = 0; k < 3; k++) cd[d][k] = pl[cr][k] + r[k];
+                rotate_inertia(Rl[cr], D.I_d[d], Iw);
+                cross3(w[cr], r, t1); cross3(w[cr], t1, t2); cross3(al[cr], r, t3); cross3(w[cr], ud[d], t4);
+#pragma unroll
+                for (int k = 0; k < 3; k++) {
+                    vc[k] = vo[cr][k] + t1[k] + ud[d][k] * qd[5 + d];
+                    ac[k] = ao[cr][k] + t3[k] + t2[k] + R(2) * t4[k] * qd[5 + d];
+                }
+                body(cr, D.m_d[d], cd[d], Iw, vc, ac, F, N);
+                bias[5 + d] = dot3(ud[d], F);
+                cross3(r, F, rxF);
+#pragma unroll
+                for (int k = 0; k < 3; k++) { fl[cr][k] += F[k]; nl[cr][k] += N[k] + rxF[k]; }
+#pragma unroll
+                for (int k = 0; k < 5; k++) {
+                    R rel[3] = {cd[d][0] - pl[k][0], cd[d][1] - pl[k][1], cd[d][2] - pl[k][2]}, x[3];
+                    cross3(rel, ud[d], x);
+                    B[k][d] = (k <= cr) ? D.m_d[d] * dot3(ax[k], x) : R(0);
+                }
+            }
+            // backward passes: joint torques of the bias, composite inertias -> revolute block of M
+            R Mrr[5][5];
+#pragma unroll
+            for (int i = 4; i >= 0; i--) {
+                bias[i] = dot3(ax[i], nl[i]);
+                if (i > 0) {
+                    R r[3] = {pl[i][0] - pl[i - 1][0], pl[i][1] - pl[i - 1][1], pl[i][2] - pl[i - 1][2]}, rxf[3];
+                    cross3(r, fl[i], rxf);
+#pragma unroll
+                    for (int k = 0; k < 3; k++) { fl[i - 1][k] += fl[i][k]; nl[i - 1][k] += nl[i][k] + rxf[k]; }
+                }
+                // unit velocity of joint i moves its subtree (composite about p_i): momentum P, angular momentum about p_i
+                R P[3];
+                cross3(ax[i], ch[i], P);
+                const R Lp[3] = {cI[i][0] * ax[i][0] + cI[i][1] * ax[i][1] + cI[i][2] * ax[i][2],
+                                 cI[i][1] * ax[i][0] + cI[i][3] * ax[i][1] + cI[i][4] * ax[i][2],
+                                 cI[i][2] * ax[i][0] + cI[i][4] * ax[i][1] + cI[i][5] * ax[i][2]};
+#pragma unroll
+                for (int k = 0; k <= i; k++) {
+                    const R rel[3] = {pl[i][0] - pl[k][0], pl[i][1] - pl[k][1], pl[i][2] - pl[k][2]};
+                    R rxP[3];
+                    cross3(rel, P, rxP);
+                    const R v = ax[k][0] * (Lp[0] + rxP[0]) + ax[k][1] * (Lp[1] + rxP[1]) + ax[k][2] * (Lp[2] + rxP[2]);
+                    Mrr[k][i] = v; Mrr[i][k] = v;
+                }
+                if (i > 0) {                            // shift the composite of link i to the origin of link i-1 and add it there
+                    const R r[3] = {pl[i][0] - pl[i - 1][0], pl[i][1] - pl[i - 1][1], pl[i][2] - pl[i - 1][2]};
+                    const R* h = ch[i];
+                    const R r2 = dot3(r, r), hr = dot3(h, r), mi = cm[i];
+                    cI[i - 1][0] += cI[i][0] + mi * (r2 - r[0] * r[0]) + R(2) * hr - R(2) * h[0] * r[0];
+                    cI[i - 1][1] += cI[i][1] - mi * r[0] * r[1] - h[0] * r[1] - r[0] * h[1];
+                    cI[i - 1][2] += cI[i][2] - mi * r[0] * r[2] - h[0] * r[2] - r[0] * h[2];
+                    cI[i - 1][3] += cI[i][3] + mi * (r2 - r[1] * r[1]) + R(2) * hr - R(2) * h[1] * r[1];
+                    cI[i - 1][4] += cI[i][4] - mi * r[1] * r[2] - h[1] * r[2] - r[1] * h[2];
+                    cI[i - 1][5] += cI[i][5] + mi * (r2 - r[2] * r[2]) + R(2) * hr - R(2) * h[2] * r[2];
+#pragma unroll
+                    for (int k = 0; k < 3; k++) ch[i - 1][k] += h[k] + mi * r[k];
+                    cm[i - 1] += mi;
+                }
+            }
+            // ---- 4. M^-1 through the Schur complement of the (diagonal) dummy block
+            R Sc[5][5];
+#pragma unroll
+            for (int k = 0; k < 5; k++)
+#pragma unroll
+                for (int l = 0; l < 5; l++) {
+                    R acc = Mrr[k][l];
+#pragma unroll
+                    for (int d = 0; d < EXO_NPRIS; d++) acc -= B[k][d] * B[l][d] / D.m_d[d];
+                    Sc[k][l] = acc;
+                }
+            R Lc[5][5], Li[5][5], Sinv[5][5];          // Cholesky S = L L^T, L^-1, S^-1 = L^-T L^-1
+#pragma unroll
+            for (int i = 0; i < 5; i++)
+#pragma unroll
+                for (int j = 0; j < 5; j++) { Lc[i][j] = 0; Li[i][j] = 0; }
+#pragma unroll
+            for (int j = 0; j < 5; j++) {
+                R dsum = Sc[j][j];
+#pragma unroll
+                for (int k = 0; k < j; k++) dsum -= Lc[j][k] * Lc[j][k];
+                Lc[j][j] = sqrt_r(dsum);
+#pragma unroll
+                for (int i = j + 1; i < 5; i++) {
+                    R acc = Sc[i][j];
+#pragma unroll
+                    for (int k = 0; k < j; k++) acc -= Lc[i][k] * Lc[j][k];
+                    Lc[i][j] = acc / Lc[j][j];
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 5; j++) {
+                Li[j][j] = R(1) / Lc[j][j];
+#pragma unroll
+                for (int i = j + 1; i < 5; i++) {
+                    R acc = 0;
+#pragma unroll
+                    for (int k = j; k < i; k++) acc -= Lc[i][k] * Li[k][j];
+                    Li[i][j] = acc / Lc[i][i];
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 5; i++)
+#pragma unroll
+                for (int j = 0; j < 5; j++) {
+                    R acc = 0;
+#pragma unroll
+                    for (int k = 0; k < 5; k++) if (k >= i && k >= j) acc += Li[k][i] * Li[k][j];
+                    Sinv[i][j] = acc;
+                }
+            R Minv[EXO_NDOF][EXO_NDOF];
+            {
+                R W[5][EXO_NPRIS];
+#pragma unroll
+                for (int k = 0; k < 5; k++)
+#pragma unroll
+                    for (int d = 0; d < EXO_NPRIS; d++) {
+                        R acc = 0;
+#pragma unroll
+                        for (int l = 0; l < 5; l++) acc += Sinv[k][l] * B[l][d];
+                        W[k][d] = acc / D.m_d[d];
+                    }
+#pragma unroll
+                for (int k = 0; k < 5; k++) {
+#pragma unroll
+                    for (int l = 0; l < 5; l++) Minv[k][l] = Sinv[k][l];
+#pragma unroll
+                    for (int d = 0; d < EXO_NPRIS; d++) { Minv[k][5 + d] = -W[k][d]; Minv[5 + d][k] = -W[k][d]; }
+                }
+#pragma unroll
+                for (int d = 0; d < EXO_NPRIS; d++)
+#pragma unroll
+                    for (int d2 = 0; d2 < EXO_NPRIS; d2++) {
+                        R acc = (d == d2) ? R(1) / D.m_d[d] : R(0);
+#pragma unroll
+                        for (int k = 0; k < 5; k++) acc += (B[k][d] / D.m_d[d]) * W[k][d2];
+                        Minv[5 + d][5 + d2] = acc;
+                    }
+            }
+            // ---- 5. unconstrained velocities, constraint rows in Bullet's order
+            R qdu[EXO_NDOF];
+            for (int i = 0; i < EXO_NDOF; i++) {
+                R acc = 0;
+                for (int j = 0; j < EXO_NDOF; j++) acc -= Minv[i][j] * bias[j];
+                qdu[i] = qd[i] + D.dt * acc;
+            }
+            int rj[EXO_MAX_ROWS];
+            R rsg[EXO_MAX_ROWS], rrhs[EXO_MAX_ROWS], rdinv[EXO_MAX_ROWS], rlo[EXO_MAX_ROWS], rhi[EXO_MAX_ROWS], lam[EXO_MAX_ROWS];
+            int m = 0;
+            for (int ci = 0; ci < D.n_cons; ci++) {
+                const int cc = D.cons[ci];
+                if (cc >= 0) {                          // motor row
+                    const int j = cc;
+                    R desired, cap;
+                    if (j < 5) { desired = D.kp * (tg[j] - q[j]) / D.dt + qdu[j] + D.kd * (R(0) - qdu[j]); cap = D.cap_pos; }
+                    else { desired = qdu[j] + R(1) * (R(0) - qdu[j]); cap = D.cap_vel; }
+                    rj[m] = j; rsg[m] = R(1); rdinv[m] = R(1) / Minv[j][j]; rrhs[m] = (desired - qdu[j]) * rdinv[m];
+                    rlo[m] = -cap; rhi[m] = cap; lam[m] = 0; m++;
+                } else {                                // joint-limit constraint of a revolute joint: rows only while violated
+                    const int j = -cc - 1;
+                    const R pen_lo = q[j] - C.lower[j], pen_hi = C.upper[j] - q[j];
+#pragma unroll
+                    for (int sgi = 0; sgi < 2; sgi++) {
+                        const R pen = sgi ? pen_hi : pen_lo, sg = sgi ? R(-1) : R(1);
+                        if (pen > R(0)) continue;
+                        rj[m] = j; rsg[m] = sg; rdinv[m] = R(1) / Minv[j][j];
+                        rrhs[m] = (-pen * D.erp / D.dt - sg * qdu[j]) * rdinv[m];
+                        rlo[m] = 0; rhi[m] = D.limit_cap; lam[m] = 0; m++;
+                    }
+                }
+            }
+            // ---- 6. projected Gauss-Seidel (sweep direction alternates, early exit on the largest squared row error)
+            R dv[EXO_NDOF];
+            for (int i = 0; i < EXO_NDOF; i++) dv[i] = 0;
+            for (int it = 0; it < D.iterations; it++) {
+                R worst = 0;
+                for (int k = 0; k < m; k++) {
+                    const int idx = (it & 1) ? k : m - 1 - k;
+                    const int j = rj[idx];
+                    R dl = rrhs[idx] - rsg[idx] * dv[j] * rdinv[idx];
+                    const R sum = lam[idx] + dl;
+                    if (sum < rlo[idx]) { dl = rlo[idx] - lam[idx]; lam[idx] = rlo[idx]; }
+                    else if (sum > rhi[idx]) { dl = rhi[idx] - lam[idx]; lam[idx] = rhi[idx]; }
+                    else lam[idx] = sum;
+                    const R imp = rsg[idx] * dl;
+                    for (int i = 0; i < EXO_NDOF; i++) dv[i] += Minv[i][j] * imp;
+                    const R res = dl / rdinv[idx];
+                    worst = fmax(worst, res * res);
+                }
+                sweeps_done++;
+                if (worst <= D.threshold) break;
+            }
+            // ---- 7. integrate, write back
+            if (lag) {
+#pragma unroll
+                for (int d = 0; d < EXO_NPRIS; d++) dy[W_QPLAG + d] = qp[d];
+            }
+            for (int i = 0; i < EXO_NDOF; i++) qd[i] = qdu[i] + dv[i];
+#pragma unroll
+            for (int j = 0; j < 5; j++) *exo_word(S.state, W_Q + j, e, st) = q[j] + D.dt * qd[j];
+#pragma unroll
+            for (int d = 0; d < EXO_NPRIS; d++) qp[d] += D.dt * qd[5 + d];
+            if (!lag) {
+#pragma unroll
+                for (int d = 0; d < EXO_NPRIS; d++) dy[W_QPLAG + d] = qp[d];
+            }
+#pragma unroll
+            for (int v = 0; v < NV_DYN; v++) st4(S.dyn + (size_t)v * st + e, dy + 4 * v);
+        }
+    }
+    // solver statistics: slots 14 (sweeps) and 15 (env-steps through this kernel)
+    const unsigned full = 0xffffffffu;
+    const int t_sw = __reduce_add_sync(full, sweeps_done), t_n = __reduce_add_sync(full, did);
+    if ((threadIdx.x & 31) == 0 && t_n) { atomicAdd(S.stats + 14, (double)t_sw); atomicAdd(S.stats + 15, (double)t_n); }
+}
+
+}  // namespace exo

@@ -525,9 +525,16 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
             __syncwarp();
             if (lane < 7) {                                                           // one actuator per lane
                 const int i = lane;
-                R a2[3];
-                if (i < 2) affine(P.R4, P.p4, C.off_alk[i], a2);
-                else affine(P.R2, P.p2, C.off_hum[i], a2);
+                R a2[3], off[3];
+#pragma unroll
+                for (int k = 0; k < 3; k++) off[k] = i < 2 ? C.off_alk[i][k] : C.off_hum[i][k];
+                if (K.motor_full) {            // EXO_MOTOR_FULL: the insertion-end dummy may have drifted along its prismatic axis
+                    const R qp = *exo_word(S.dyn, (K.lag ? W_QPLAG : W_QP) + (i < 2 ? 7 + i : i), e, st);
+#pragma unroll
+                    for (int k = 0; k < 3; k++) off[k] += (i < 2 ? C.pax_alk[i][k] : C.pax_hum[i][k]) * qp;
+                }
+                if (i < 2) affine(P.R4, P.p4, off, a2);
+                else affine(P.R2, P.p2, off, a2);
 #pragma unroll
                 for (int k = 0; k < 3; k++) {
                     a2[k] += (R)sml[16 + (2 * i + 1) * 3 + k];

@@ -31,7 +31,7 @@ static int launch_reset_nax(const EnvArrays<R>& A, const ChainConst<R>& C, const
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr; cfg.numAttrs = K.list_parity >= 0 ? 1 : 0;
+    cfg.attrs = attr; cfg.numAttrs = (K.list_parity >= 0 && !K.motor_full) ? 1 : 0;   // FULL: the motor kernel sits between
     return (int)cudaLaunchKernelEx(&cfg, exo_reset_kernel<R, NAX>, A, C, K, mask, obs);
 }
 template <typename R>

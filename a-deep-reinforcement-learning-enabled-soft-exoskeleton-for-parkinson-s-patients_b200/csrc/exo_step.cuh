@@ -167,8 +167,10 @@ __device__ __forceinline__ void dh_end_effector(const R* th, R L1, R L2, R* p) {
     }
 }
 
-template <typename R, bool INFO, int NAX>
-__global__ void __launch_bounds__(EXO_STEP_THREADS, (sizeof(R) == 4 && !INFO) ? EXO_STEP_MIN_BLOCKS : 4)
+// FULL: ExoConfig.motor_model = EXO_MOTOR_FULL - the position targets go to exo_motor_kernel (exo_motor.cuh) instead of the
+// closed-form tracker, and the actuator end points follow their prismatic dummies (which the general step lets drift).
+template <typename R, bool INFO, int NAX, bool FULL = false>
+__global__ void __launch_bounds__(EXO_STEP_THREADS, (sizeof(R) == 4 && !INFO && !FULL) ? EXO_STEP_MIN_BLOCKS : 4)
 exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __restrict__ actions,
                 float* __restrict__ obs, R* __restrict__ reward, uint8_t* __restrict__ done, InfoPtrs<R> info) {
     constexpr int WARPS = EXO_STEP_THREADS / 32;
@@ -256,7 +258,10 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
     R v_ret = 0, v_amp = 0;
     int v_cge = 0, v_clt = 0, v_ntr = 0, v_nam = 0;      // training-script suppression metrics (INFO mode only)
     R v_str = 0, v_sam = 0;
-    if (valid && !live) { done[e] = 1; reward[e] = R(0); }
+    if (valid && !live) {
+        done[e] = 1; reward[e] = R(0);
+        if (FULL) { const R z[4] = {0, 0, 0, 0}; st4(S.tgt + (size_t)st + e, z); }     // live flag off: the motor kernel skips this env
+    }
     const unsigned full = 0xffffffffu;
     const unsigned live_mask = __ballot_sync(full, live);
     if (live) {
@@ -310,6 +315,12 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
         R el_old[3];
 #pragma unroll
         for (int k = 0; k < 3; k++) el_old[k] = s[W_ELREF + k];
+        R qpl[12];                                                    // FULL: prismatic positions behind the link-state cache
+        if (FULL) {
+            const int w0 = K.lag ? W_QPLAG : W_QP;                    // words w0 .. w0+8 of the dyn record
+#pragma unroll
+            for (int d = 0; d < EXO_NPRIS; d++) qpl[d] = *exo_word(S.dyn, w0 + d, e, st);
+        }
         // new pos_vec -> obs[47:68]
         // ---- per actuator: endpoints, force direction, pos_vec, torque (sim:207-336, env:177-187)
         R at0 = 0, at1 = 0, at2 = 0, ty0 = 0, ty1 = 0;
@@ -320,11 +331,24 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
             const int i = order[oi];
             R a1[3], a2[3];
             if (i < 2) {
-                affine(P.R2, P.p2, C.off_hum[i], a1);                   // act11 / act21 ride on the humerus
-                affine(P.R4, P.p4, C.off_alk[i], a2);                   // act12 / act22 ride on the forearm
+                if (FULL) {
+                    R oh[3], oa[3];
+#pragma unroll
+                    for (int k = 0; k < 3; k++) { oh[k] = C.off_hum[i][k] + C.pax_hum[i][k] * qpl[i]; oa[k] = C.off_alk[i][k] + C.pax_alk[i][k] * qpl[7 + i]; }
+                    affine(P.R2, P.p2, oh, a1);
+                    affine(P.R4, P.p4, oa, a2);
+                } else {
+                    affine(P.R2, P.p2, C.off_hum[i], a1);               // act11 / act21 ride on the humerus
+                    affine(P.R4, P.p4, C.off_alk[i], a2);               // act12 / act22 ride on the forearm
+                }
             } else {
                 a1[0] = C.fixed[fix_of[i]][0]; a1[1] = C.fixed[fix_of[i]][1]; a1[2] = C.fixed[fix_of[i]][2];
-                affine(P.R2, P.p2, C.off_hum[i], a2);
+                if (FULL) {
+                    R oh[3];
+#pragma unroll
+                    for (int k = 0; k < 3; k++) oh[k] = C.off_hum[i][k] + C.pax_hum[i][k] * qpl[i];
+                    affine(P.R2, P.p2, oh, a2);
+                } else affine(P.R2, P.p2, C.off_hum[i], a2);
             }
             {   // dummy_shift_coordinates of this actuator's two ends: words 6i..6i+5 of the staged record = two vectors
                 constexpr int W0 = W_SHIFT;
@@ -393,8 +417,13 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
         const R tgt[5] = {(mrow[4] + qa[2]) * d2r, (mrow[3] + qa[0]) * d2r, (mrow[2] + qa[1]) * d2r, (mrow[0] + qa[3]) * d2r,
                           mrow[1] * d2r};
         int crossed = 0;
+        if (FULL) {                                   // hand the targets to exo_motor_kernel; q itself is its output
+            const R t0[4] = {tgt[0], tgt[1], tgt[2], tgt[3]}, t1[4] = {tgt[4], R(1), R(0), R(0)};
+            st4(S.tgt + e, t0); st4(S.tgt + (size_t)st + e, t1);
+        }
 #pragma unroll
         for (int j = 0; j < 5; j++) {
+            if (FULL) { if (K.lag) s[W_QLAG + j] = qb[j]; continue; }
             R qn = qb[j] + R(0.025) * div_r(R(0.1) * (tgt[j] - qb[j]), R(0.025));   // q + dt*v*, v* = kp*(target-q)/dt
             if (qn < C.lower[j] || qn > C.upper[j]) {
                 crossed++;
@@ -617,6 +646,9 @@ __global__ void exo_field_kernel(EnvArrays<R> S, int field, int k, int naxv, T* 
         case F_META: a = (T*)(S.meta + e); break;
         case F_MT_STATE: a = (T*)(S.mt + (size_t)e * EXO_MT_PITCH + i); break;
         case F_EP_RETURN: a = (T*)(S.ret + e); break;
+        case F_QD: if (!S.dyn) return; a = (T*)exo_word(S.dyn, W_QD + i, e, st); break;
+        case F_Q_PRIS: if (!S.dyn) return; a = (T*)exo_word(S.dyn, W_QP + i, e, st); break;
+        case F_Q_PRIS_LAG: if (!S.dyn) return; a = (T*)exo_word(S.dyn, W_QPLAG + i, e, st); break;
         default: return;
     }
     if (SET) *a = buf[idx]; else buf[idx] = *a;

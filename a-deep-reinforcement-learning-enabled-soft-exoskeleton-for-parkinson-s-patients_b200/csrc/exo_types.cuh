@@ -36,6 +36,19 @@
 #define NV_EP 11
 // propagator G (7x7) reordered so that the 4x4 block the plain step needs is vectors 0..3
 #define NV_G 13
+// general multibody step (ExoConfig.motor_model = EXO_MOTOR_FULL): 14 coupled degrees of freedom = 5 revolute arm joints
+// + the 7 prismatic dummies riding on the humerus + the 2 on the forearm (the 5 dummies on the fixed base are decoupled
+// 1-DoF systems their velocity motors hold at exactly 0). Per env: qd[14] | qp[9] prismatic positions | qplag[9] the
+// positions behind the link-state cache = 32 words = 8 vectors; the step kernel hands the position targets over in
+// 2 more vectors: tgt[5], live flag.
+#define EXO_NDOF 14
+#define EXO_NPRIS 9
+#define W_QD 0
+#define W_QP 14
+#define W_QPLAG 23
+#define NV_DYN 8
+#define NV_TGT 2
+#define EXO_MAX_ROWS 24          // 14 motor rows + 2 limit rows for each of the 5 revolute joints
 #define EXO_MT_PITCH 640         // words per env in the MT19937 array: 624 key + position (+pad to 128 B multiple)
 #define EXO_IDS_PITCH 148        // doubles per env: I, D, S (3 x 49) + pad
 
@@ -68,6 +81,8 @@ struct EnvArrays {
     const R* motion;         // [n_motions][5][max_len] degrees
     const int* motion_len;   // [n_motions]
     int max_len, n_motions, table_len;
+    V4<R>* dyn;              // [NV_DYN][stride]  EXO_MOTOR_FULL only: qd, qp, qplag
+    V4<R>* tgt;              // [NV_TGT][stride]  EXO_MOTOR_FULL only: this step's position targets + live flag
     double* stats;           // [EXO_N_STATS]
     int* fin_count;          // [2]          envs that finished in the step of parity p (auto-reset work list)
     int* fin_list;           // [2][stride]
@@ -85,6 +100,20 @@ struct ChainConst {
     R fixed[5][3];    // act31, act41, act51, act61, act71 world positions (base-fixed)
     R sh_ref[3];      // shoulder reference (link-0 COM) world position
     R lower[5], upper[5];
+    R pax_hum[7][3];  // prismatic axis of each humerus dummy in the humerus frame (EXO_MOTOR_FULL: endpoint += axis * qp)
+    R pax_alk[2][3];  // same for the two forearm dummies
+};
+
+// Inertial data and solver settings of the general multibody step (exo_motor.cuh), flattened on the host from the
+// URDF link data (exo_api.cu: build_dynamics). DoF order: revolute 0..4, humerus dummies in off_hum order, forearm dummies.
+template <typename R>
+struct DynConst {
+    R m_link[5], com_link[5][3], I_link[5][6];     // link frame: mass, COM, inertia tensor (xx,xy,xz,yy,yz,zz)
+    R m_d[EXO_NPRIS], I_d[EXO_NPRIS][6];           // dummy mass, inertia tensor in the carrier frame
+    R kp, kd, cap_pos, cap_vel;                    // position motors (joints 0-4) / default velocity motors (dummies)
+    R k_lin, k_ang, g[3], dt, erp, limit_cap, threshold;
+    int iterations, n_cons;
+    signed char cons[EXO_MAX_ROWS];                // solver order: dof (motor row) or -(dof+1) (joint-limit constraint)
 };
 
 template <typename R>
@@ -92,7 +121,7 @@ struct StepConst {
     R fmax_sh0, fmax_el0;          // un-randomised maxima (obs normalisation, Exoskeleton_env.py:488-501)
     R inv_fmax_sh0, inv_fmax_el0;
     R L1, L2;                      // humerus / forearm length for the amplitude metric
-    int lag, limits, auto_reset, metrics;
+    int lag, limits, auto_reset, metrics, motor_full;
     int parity;                    // which finished-list this step appends to (the other counter is cleared)
     int env0, env1;                // env range [env0, env1) of this launch (env0 a multiple of 32): exo_step_host pipelines
                                    // chunks of the population against their PCIe copies
@@ -104,6 +133,7 @@ struct ResetConst {
     double fmax_sh0, fmax_el0;
     double dt;
     int lag;
+    int motor_full;    // EXO_MOTOR_FULL: the actuator end points follow their prismatic dummies
     int ctor_skip;     // 32-bit outputs consumed before the episode draws (2 for the constructor's rand(), env:70)
     int list_parity;   // >= 0: reset the envs of fin_list[parity]; < 0: reset by mask
 };
@@ -116,5 +146,5 @@ struct InfoPtrs {
 // field ids of exo_get_field / exo_set_field (include/exo_env.h EXO_FIELD_*)
 enum {
     F_Q = 0, F_Q_LAG, F_POS_VEC, F_ELBOW_REF, F_PREV_ACTION, F_PREV_ACTION2, F_FORCE_MAX, F_SHIFT, F_G, F_IDS,
-    F_TREMOR_TABLE, F_TREMOR_MAG, F_COUNTS, F_META, F_MT_STATE, F_EP_RETURN, F_N_FIELDS
+    F_TREMOR_TABLE, F_TREMOR_MAG, F_COUNTS, F_META, F_MT_STATE, F_EP_RETURN, F_QD, F_Q_PRIS, F_Q_PRIS_LAG, F_N_FIELDS
 };

@@ -38,7 +38,11 @@ class BatchedExoskeletonEnv(object):
                  second_harmonics_interval, max_force_shoulder, max_force_elbow, dr_actuator_end_pos_shift=0.02,
                  dr_actuator_range=0.1, matrix_noise_fraction=0.1, device="cuda:0", precision="fp32", auto_reset=False,
                  reference_ctor=True, link_state_lag=1, joint_limits="off", metrics=False, motions=None, urdf=None,
-                 humerus_length=0.4, forearm_length=0.4, hand_length=0.05):
+                 humerus_length=0.4, forearm_length=0.4, hand_length=0.05, motor_model="ideal", motor_options=None):
+        """motor_model: "ideal" - the fixed point of Bullet's motor solve, q+ = q + kp (target - q) (default);
+        "full" - the general multibody step (forward dynamics + 50-sweep projected Gauss-Seidel, csrc/exo_motor.cuh);
+        motor_options: dict of ExoMotorModel fields overriding pybullet's defaults (inertia_from_file, iterations,
+        row_order, residual_threshold, kp, kd, max_force, default_motor_impulse, linear_damping, angular_damping, ...)."""
         self.lib = _capi.load()
         if not torch.cuda.is_available():
             raise _capi.ExoError("no CUDA device: the batched env runs on a B200 only (there is no CPU fallback)")
@@ -78,6 +82,8 @@ class BatchedExoskeletonEnv(object):
         cfg.auto_reset = int(self.auto_reset)
         cfg.reference_ctor = int(bool(reference_ctor))
         cfg.metrics = int(bool(metrics))
+        cfg.motor_model = {"ideal": _capi.MOTOR_IDEAL, "full": _capi.MOTOR_FULL}[motor_model]
+        self.motor_model = motor_model
         self.cfg = cfg
         self.max_force_shoulder, self.max_force_elbow = float(max_force_shoulder), float(max_force_elbow)
 
@@ -94,6 +100,16 @@ class BatchedExoskeletonEnv(object):
         self.h = C.c_void_p()
         with torch.cuda.device(dev_index):
             _capi.check(self.lib.exo_create(C.byref(cfg), C.byref(geo), self.n, dev_index, C.byref(self.h)))
+            if motor_model == "full":
+                mm = _capi.ExoMotorModel()
+                self.lib.exo_default_motor_model(C.byref(mm))
+                for k, v in (motor_options or {}).items():
+                    if k == "gravity":
+                        mm.gravity[:] = [float(x) for x in v]
+                    else:
+                        setattr(mm, k, v)
+                links = _urdf.to_dynamics_struct(self.geometry)
+                _capi.check(self.lib.exo_set_motor_model(self.h, C.byref(links), C.byref(mm)))
             _capi.check(self.lib.exo_load_motions(self.h, tables.ctypes.data_as(C.POINTER(C.c_double)),
                                                   lengths.ctypes.data_as(C.POINTER(C.c_int32)), len(self.motions),
                                                   tables.shape[2]))
@@ -293,6 +309,7 @@ class ExoskeletonEnv_train(object):
         high = np.concatenate([np.repeat(1.5, 14), np.repeat(15.0, 12), np.repeat(2.0, 54)])
         self.observation_space = _Box(low, high)
         self.state = None
+        self._out = None
 
     def reset(self):
         obs = self.batch.reset()
@@ -300,17 +317,49 @@ class ExoskeletonEnv_train(object):
         self.state = obs[0].cpu().numpy()
         return self.state, self.counts
 
+    def _blob(self):
+        """All outputs of one step in ONE device buffer (and one pinned host mirror), so a step costs one H2D copy of the
+        action and one D2H copy instead of a synchronising copy per output: obs | reward | done | info[5x7] | reward parts[5] |
+        amplitude metric, each 16-byte aligned."""
+        if self._out is None:
+            b = self.batch
+            rb = 8 if b.real == torch.float64 else 4
+            offs, o = {}, 0
+            for name, nbytes in (("obs", 320), ("reward", rb), ("done", 1), ("act", 28)) + tuple((k, 7 * rb) for k in INFO_KEYS) + \
+                    (("reward_parts", 5 * rb), ("amp_metric", rb)):
+                offs[name] = (o, nbytes)
+                o += (nbytes + 15) & ~15
+            dev = torch.zeros(o, dtype=torch.uint8, device=b.device)
+            host = torch.zeros(o, dtype=torch.uint8).pin_memory()
+            info = _capi.ExoInfo()
+            for k in INFO_KEYS + ("reward_parts", "amp_metric"):
+                setattr(info, k, dev.data_ptr() + offs[k][0])
+            hv = host.numpy()
+            views = {k: hv[a:a + nb].view(np.float32 if k in ("obs", "act") else (np.uint8 if k == "done" else
+                                                                                  (np.float64 if rb == 8 else np.float32)))
+                     for k, (a, nb) in offs.items()}
+            self._out = (dev, host, offs, info, views)
+        return self._out
+
     def step(self, action):
-        a = torch.as_tensor(np.asarray(action, dtype=np.float32).reshape(1, 7))
-        obs, reward, done, info = self.batch.step(a.to(self.batch.device), with_info=True)
+        dev, host, offs, info, v = self._blob()
+        b = self.batch
+        v["act"][:] = np.asarray(action, dtype=np.float32).reshape(7)
+        a0, an = offs["act"]
+        dev[a0:a0 + an].copy_(host[a0:a0 + an], non_blocking=True)                     # the one H2D copy
+        base = dev.data_ptr()
+        _capi.check(b.lib.exo_step(b.h, C.c_void_p(base + a0), C.c_void_p(base + offs["obs"][0]),
+                                   C.c_void_p(base + offs["reward"][0]), C.c_void_p(base + offs["done"][0]), C.byref(info),
+                                   b._stream()))
+        host.copy_(dev, non_blocking=True)                                              # the one D2H copy
+        torch.cuda.current_stream(b.device).synchronize()
         self.counts += 1
-        host = {k: info[k][0].cpu().numpy().astype(np.float64) for k in INFO_KEYS}
-        parts = info["reward_parts"][0].cpu().numpy().astype(np.float64)
-        for k, v in zip(REWARD_KEYS, parts):
-            host[k] = float(v)
-        host["amp_metric"] = float(info["amp_metric"][0].item())
-        self.state = obs[0].cpu().numpy()
-        return self.state, float(reward[0].item()), bool(done[0].item()), False, host
+        out = {k: v[k].astype(np.float64) for k in INFO_KEYS}
+        for k, x in zip(REWARD_KEYS, v["reward_parts"]):
+            out[k] = float(x)
+        out["amp_metric"] = float(v["amp_metric"][0])
+        self.state = v["obs"].copy()
+        return self.state, float(v["reward"][0]), bool(v["done"][0]), False, out
 
     def return_generated_tremor_data(self):
         tt = self.batch.get_field("tremor_table")[0]          # [L, axes]

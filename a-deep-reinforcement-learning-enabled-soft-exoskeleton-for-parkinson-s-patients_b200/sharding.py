@@ -13,16 +13,18 @@ def shard_range(n_total, rank, world):
     return lo, lo + base + (1 if rank < extra else 0)
 
 
+MOTION_BLOCK = 1024      # envs per contiguous same-motion block (a multiple of the 32-env warp and of the 64-env step block)
+
+
 def benchmark_population(n_total, rank=0, world=1, n_motions=8):
-    """BASELINE configs 3/4 population for this rank's shard: inside a shard envs are grouped in contiguous
-    blocks per reference motion (so a warp shares its motion row and episode phase), tremor type = the 15 non-zero
-    [a,b,c,d] patterns round-robin over the GLOBAL env id, seed = global env id (results do not depend on `world`
-    for the RNG-derived parameters)."""
+    """BASELINE configs 3/4 population for this rank's shard. Everything is a function of the GLOBAL env id g, so global
+    env g is the same env (motion, tremor type, seed -> every RNG-derived episode parameter, every trajectory) whatever the
+    world size: motion = (g // 1024) mod 8 (contiguous 1024-env blocks per reference motion, so a warp shares its motion row
+    and episode phase and every shard holds an even mix of episode lengths), tremor type = the 15 non-zero [a,b,c,d]
+    patterns round-robin over g, seed = g."""
     lo, hi = shard_range(n_total, rank, world)
-    n = hi - lo
-    local = np.arange(n)
-    gid = lo + local
-    motion = (local * n_motions // max(n, 1)).astype(np.int32)
+    gid = np.arange(lo, hi)
+    motion = ((gid // MOTION_BLOCK) % n_motions).astype(np.int32)
     seqs = np.asarray(TYPES15, dtype=np.uint8)[gid % 15]
     return motion, seqs, gid.astype(np.uint32)
 

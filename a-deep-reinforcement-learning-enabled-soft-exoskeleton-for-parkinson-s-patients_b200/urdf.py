@@ -41,11 +41,36 @@ def parse_urdf(path, base_position=(0.0, 0.0, 0.1)):
     """Returns a plain dict (JSON-serialisable) describing the tree in Bullet link order."""
     doc = minidom.parse(path)
     robot = doc.documentElement
-    com = {}
+    com, dyn = {}, {}
     for ln in robot.getElementsByTagName("link"):
         inertial = _child(ln, "inertial")
         org = _child(inertial, "origin") if inertial is not None else None
         com[ln.getAttribute("name")] = _floats(org.getAttribute("xyz")) if org is not None else [0.0, 0.0, 0.0]
+        # inertial data for the general multibody step (EXO_MOTOR_FULL): mass, principal inertias, inertial-frame rotation,
+        # and the collision box pybullet derives its default inertia from
+        rec = dict(mass=0.0, inertia_diag=[0.0] * 3, inertial_R=_rotation_from_rpy(0.0, 0.0, 0.0),
+                   box_size=[0.0] * 3, box_xyz=[0.0] * 3, box_R=_rotation_from_rpy(0.0, 0.0, 0.0))
+        if inertial is not None:
+            ms, it = _child(inertial, "mass"), _child(inertial, "inertia")
+            rec["mass"] = float(ms.getAttribute("value")) if ms is not None else 0.0
+        if inertial is not None and _child(inertial, "inertia") is not None:
+            it = _child(inertial, "inertia")
+            if any(float(it.getAttribute(k) or 0.0) != 0.0 for k in ("ixy", "ixz", "iyz")):
+                raise ValueError("link %s: products of inertia are not supported" % ln.getAttribute("name"))
+            rec["inertia_diag"] = [float(it.getAttribute(k)) for k in ("ixx", "iyy", "izz")]
+            if org is not None and org.hasAttribute("rpy"):
+                rec["inertial_R"] = _rotation_from_rpy(*_floats(org.getAttribute("rpy")))
+        col = _child(ln, "collision")
+        if col is not None:
+            geom = _child(col, "geometry")
+            box = _child(geom, "box") if geom is not None else None
+            corg = _child(col, "origin")
+            if box is not None:
+                rec["box_size"] = _floats(box.getAttribute("size"))
+            if corg is not None:
+                rec["box_xyz"] = _floats(corg.getAttribute("xyz"))
+                rec["box_R"] = _rotation_from_rpy(*_floats(corg.getAttribute("rpy")))
+        dyn[ln.getAttribute("name")] = rec
     by_parent, children = {}, set()
     for jn in robot.getElementsByTagName("joint"):
         parent = _child(jn, "parent").getAttribute("link")
@@ -77,7 +102,7 @@ def parse_urdf(path, base_position=(0.0, 0.0, 0.1)):
             raise ValueError("joint %s: type %s is not supported" % (rec["name"], rec["kind"]))
         links.append(dict(name=rec["child"], joint=rec["name"], parent=parent_idx, joint_type=kinds[rec["kind"]],
                           origin_xyz=rec["xyz"], origin_R=_rotation_from_rpy(*rec["rpy"]), axis=rec["axis"],
-                          com_xyz=com[rec["child"]], lower=rec["lower"], upper=rec["upper"]))
+                          com_xyz=com[rec["child"]], lower=rec["lower"], upper=rec["upper"], **dyn[rec["child"]]))
     base_com = com[roots[0]]
     return dict(base=roots[0], base_pos=[base_position[i] - base_com[i] for i in range(3)], links=links,
                 act_link=list(ACT_LINKS), shoulder_link=SHOULDER_LINK, elbow_link=ELBOW_LINK)
@@ -103,6 +128,23 @@ def to_struct(tree):
         g.act_link[a] = tree["act_link"][a]
     g.shoulder_link, g.elbow_link = tree["shoulder_link"], tree["elbow_link"]
     return g
+
+
+def to_dynamics_struct(tree):
+    """ExoLinkDynamics (include/exo_env.h) for exo_set_motor_model."""
+    d = _capi.ExoLinkDynamics()
+    for i, ln in enumerate(tree["links"]):
+        if "mass" not in ln:
+            raise ValueError("geometry table has no inertial data (regenerate it with tools/extract_reference_data.py)")
+        d.mass[i] = ln["mass"]
+        for k in range(3):
+            d.inertia_diag[i][k] = ln["inertia_diag"][k]
+            d.box_size[i][k] = ln["box_size"][k]
+            d.box_xyz[i][k] = ln["box_xyz"][k]
+        for k in range(9):
+            d.inertial_R[i][k] = ln["inertial_R"][k]
+            d.box_R[i][k] = ln["box_R"][k]
+    return d
 
 
 BUNDLED = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "exo_v3_geometry.json")

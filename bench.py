@@ -9,6 +9,11 @@ Workload (config.workload): BASELINE config 3 per GPU — 65 536 envs/GPU, train
 types round-robin, auto-reset on, U(-1,1)^7 actions generated on the device before timing. Envs shard over
 ranks with no data-path collective (weak scaling); NCCL only all-reduces the episode-statistics vector.
 
+Steady state: before anything is timed the population is DE-PHASED (untimed set-up, `dephase`): 347 pre-roll steps in
+which env e is reset at pre-roll step e mod 347, so that every later window of steps - however short - contains its share
+of episode ends (n / ~280 per step) instead of none for 229 steps and then 8192-env bursts. The line asserts
+episodes_finished > 0. The CPU arms de-phase their sample the same way.
+
 Timing: every step sits between its own pair of CUDA events on the launching stream; between steps a 512 MiB
 buffer is overwritten to flush the 126 MB L2 (the per-step working set of 65 536 envs would otherwise stay L2
 resident). The timed region is bracketed by barrier + synchronize; the reported time is the max over ranks of the
@@ -36,9 +41,29 @@ UNIT = "env-steps/s"
 # Compulsory HBM traffic of one env-step of exo_step_kernel<float,false,4> (DESIGN.md "Algorithmic bytes"):
 # reads 520 B + writes 525 B.
 ALGO_BYTES_PER_ENV_STEP = 1045
-# dram__bytes_read.sum + dram__bytes_write.sum of one exo_step_kernel<float,false,4> launch over 65 536 envs
-# (profiles/r01g_ncu_full_step.txt): 34.130944 MB + 0.103424 MB
+# dram__bytes_read.sum + dram__bytes_write.sum of one exo_step_kernel<float,false,4> launch over 65 536 envs, from the
+# ncu --set full capture named in TRAFFIC_SOURCE (refreshed per round from the final code)
 STEP_KERNEL_DRAM_BYTES_65536 = 34234368
+TRAFFIC_SOURCE = "profiles/r01g_ncu_full_step.txt"
+DEPHASE_PERIOD = 347          # longest reference motion: every env is reset once during the pre-roll
+MEAN_EPISODE_STEPS = float(np.mean([l - 3 for l in (232, 316, 282, 295, 270, 347, 266, 273)]))
+
+
+def reset_bytes(table_len_mean=MEAN_EPISODE_STEPS + 3, nax=4, real=4):
+    """Compulsory HBM bytes of one env reset: MT19937 key read + written back (2 x 2500), the tremor table
+    written (L rows x 4 axes), I/D/S (147 fp64), shifts + force maxima (44 words), G (49 words), first observation (320),
+    carried state touched (~48 words)."""
+    return 2 * 2500 + table_len_mean * nax * real + 147 * 8 + 44 * real + 49 * real + 320 + 48 * real
+
+
+def dephase(env, actions, period=DEPHASE_PERIOD):
+    """Untimed set-up: spread the envs over their episodes. env e is reset at pre-roll step e mod period; all envs step."""
+    import torch
+    n = env.n
+    phase = torch.arange(n, device=env.device) % period
+    for t in range(period):
+        env.reset((phase == t).to(torch.uint8))
+        env.step(actions[t % actions.shape[0]], keep_idle_obs=False)
 
 
 def population(n_per_gpu, rank, world):
@@ -105,6 +130,7 @@ def cpu_baseline(sample_envs, steps, threads=0, seed0=0):
     rs = np.random.RandomState(1)
     acts = rs.uniform(-1, 1, (4, sample_envs, 7))
     nthreads = O.lib().orc_max_threads() if threads <= 0 else threads
+    batch.dephase(DEPHASE_PERIOD, threads=nthreads)           # same steady state as the GPU arm: episode ends in every window
     batch.step(acts[0], auto_reset=True, threads=nthreads)
     t0 = time.perf_counter()
     for t in range(steps):
@@ -163,17 +189,31 @@ def bench_lap(exo_b200, env, actions, dev, flush):
 POLICY_FLOP_PER_OBS = 2 * (80 * 300 * 2 + 300 * 300 * 3 + 600 * 300 + 300 * 7)
 
 
-def bench_policy(exo_b200, env, dev, flush, peaks):
+def synthetic_policy_state_dict(seed=0):
+    """Random-init weights of the reference's Actor + Encoder.zs architecture (TD7_multi_agent_Pink_noise.py:59-105:
+    zs1 80->300, zs2, zs3 300->300, l0 80->300, l1 600->300, l2 300->300, l3 300->7), torch.nn.Linear's default init."""
+    rs = np.random.RandomState(seed)
+    sd = {}
+    for name, (o, i) in dict(zs1=(300, 80), zs2=(300, 300), zs3=(300, 300), l0=(300, 80), l1=(300, 600), l2=(300, 300), l3=(7, 300)).items():
+        b = 1.0 / np.sqrt(i)
+        sd[name + ".weight"] = rs.uniform(-b, b, (o, i)).astype(np.float32)
+        sd[name + ".bias"] = rs.uniform(-b, b, o).astype(np.float32)
+    return sd
+
+
+def bench_policy(exo_b200, env, dev, flush, peaks, weights=None):
     """Next row N2: select_action's networks (encoder.zs + actor, TD7_multi_agent_Pink_noise.py:66-105)
     as one tcgen05 kernel reading the env's obs tensor. Weights: the shipped [1,1,1,1] checkpoint (tests/golden/ref_policy.npz).
     Reports the forward pass alone (CUDA events, L2 flushed) against the tensor-core roofline - kind::tf32 issues at half
     the bf16 MMA rate, so peak = MEASURED_PEAKS bf16_tflops / 2 - and the closed loop obs -> policy -> env.step."""
     import torch
     n = env.n
-    g = np.load(os.path.join(REPO, "tests", "golden", "ref_policy.npz"))
-    sd = {k: g[k] for k in g.files if "." in k}
     pol = exo_b200.DevicePolicy(dev)
-    pol.set_networks(sd, sd, "checkpoint")
+    if weights:                                # a reference checkpoint prefix, e.g. .../AGENT_NNS/[1,1,1,1]/[1,1,1,1]
+        pol.load(weights)
+    else:
+        sd = synthetic_policy_state_dict()
+        pol.set_networks(sd, sd, "checkpoint")
     obs = env.reset().clone()
     act = torch.empty(n, 7, device=dev)
     for _ in range(3):
@@ -240,7 +280,8 @@ def bench_policy(exo_b200, env, dev, flush, peaks):
            "closed_loop_env_steps_per_s": n / (loop_ms * 1e-3), "closed_loop_ms_per_step": loop_ms,
            "acting_loop_env_steps_per_s": n / (act_ms * 1e-3), "acting_loop_ms_per_step": act_ms,
            "acting_loop": "policy.forward -> env.step -> LAP.add_batch per step, device resident, no host copy",
-           "launches": pol.launch_count(), "weights": "shipped [1,1,1,1] checkpoint actor + encoder"}
+           "launches": pol.launch_count(),
+           "weights": ("checkpoint " + weights) if weights else "synthetic: random-init Actor + Encoder of the reference's architecture"}
     pol.close()
     return out
 
@@ -320,6 +361,140 @@ def bench_large_population(exo_b200, dev, flush, peak, precision, n_large=524288
             "note": "same kernel at config 4's per-GPU population (1M envs over 2 GPUs); 65 536 envs are one wave of 14 warps per SM"}
 
 
+def bench_reset(env, dev, flush, peak):
+    """The reset kernel by itself (the second kernel of the timed step): (a) latency of resetting one step's steady-state
+    share of the population (n / mean episode length envs, random positions, masked launch, L2 flushed) - what a step waits
+    for when the reset is on its critical path; (b) throughput of resetting every env -> HBM roofline entry."""
+    import torch
+    n = env.n
+    k = max(1, int(round(n / MEAN_EPISODE_STEPS)))
+    g = torch.Generator(device="cpu").manual_seed(0)
+    was = env.auto_reset
+    env.set_auto_reset(False)
+
+    def timed(mask, reps):
+        ts = []
+        for _ in range(reps):
+            if flush is not None:
+                flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            env.reset(mask)
+            b.record()
+            ts.append((a, b))
+        torch.cuda.synchronize(dev)
+        return float(np.median([a.elapsed_time(b) for a, b in ts[2:]]))
+    m = torch.zeros(n, dtype=torch.uint8)
+    m[torch.randperm(n, generator=g)[:k]] = 1
+    share_ms = timed(m.to(dev), 16)
+    empty_ms = timed(torch.zeros(n, dtype=torch.uint8, device=dev), 10)
+    all_ms = timed(None, 6)
+    env.set_auto_reset(was)
+    by = reset_bytes()
+    achieved = by * n / (all_ms * 1e-3) / 1e9
+    return {"kernel": "exo_reset_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": None, "algorithmic_bytes_per_reset": by, "all_envs_ms": all_ms, "ns_per_reset": all_ms * 1e6 / n,
+            "resets_per_step_steady_state": k, "steady_state_share_ms": share_ms, "empty_launch_ms": empty_ms,
+            "note": "issue/latency-bound (one warp walks an env's draw chain), not bandwidth-bound; the frac is reported against HBM "
+                    "because its compulsory work is byte movement"}
+
+
+def bench_cfg4(exo_b200, args, rank, world, dev, flush, peak, barrier):
+    """BASELINE config 4 in the driver's own run: 1 048 576 envs split over the ranks (N > 1), de-phased, same timing rules;
+    the statistics all-reduce (the path's only collective, every 344 steps - it never fires inside a 20-step window) is timed
+    explicitly once."""
+    import torch
+    import torch.distributed as dist
+    total = 1 << 20
+    n4 = total // world
+    motion, seqs, seeds = population(n4, rank, world)
+    env = exo_b200.BatchedExoskeletonEnv(motion, seqs, seeds, device=dev, precision=args.precision, auto_reset=True, **TRAIN)
+    gen = torch.Generator(device=dev).manual_seed(77 + rank)
+    acts = torch.rand(2, n4, 7, device=dev, generator=gen) * 2 - 1
+    env.reset()
+    dephase(env, acts)
+    steps = max(5, min(args.steps, 100))
+    for t in range(3):
+        env.step(acts[t % 2], keep_idle_obs=False)
+    env.stats(reset=True)
+    barrier()
+    ev = []
+    for t in range(steps):
+        if flush is not None:
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        env.step(acts[t % 2], keep_idle_obs=False)
+        b.record()
+        ev.append((a, b))
+    barrier()
+    tot = torch.tensor([sum(a.elapsed_time(b) for a, b in ev)], dtype=torch.float64, device=dev)
+    dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+    st = env.stats(reset=True).clone()
+    exo_b200.sharding.reduce_stats(st)                      # warm the communicator
+    barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    exo_b200.sharding.reduce_stats(st)
+    b.record()
+    torch.cuda.synchronize(dev)
+    ar = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
+    dist.all_reduce(ar, op=dist.ReduceOp.MAX)
+    env.set_auto_reset(False)
+    env.reset()
+    kev = []
+    for t in range(20):
+        if flush is not None:
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        env.step(acts[t % 2], keep_idle_obs=False)
+        b.record()
+        kev.append((a, b))
+    torch.cuda.synchronize(dev)
+    kms = float(np.mean([a.elapsed_time(b) for a, b in kev[2:]]))
+    env.close()
+    ms = float(tot.item()) / steps
+    achieved = ALGO_BYTES_PER_ENV_STEP * n4 / (kms * 1e-3) / 1e9
+    return {"workload": "BASELINE cfg4: 1 048 576 envs over %d GPUs, de-phased, auto-reset" % world, "total_envs": total,
+            "envs_per_gpu": n4, "steps": steps, "value": total * steps / (float(tot.item()) * 1e-3), "unit": UNIT, "ms_per_step": ms,
+            "episodes_finished": float(st[0].item()), "step_kernel_ms": kms, "step_kernel_frac_of_hbm": achieved / peak,
+            "stats_allreduce_ms": float(ar.item()), "stats_allreduce": "one sum all-reduce of the 16-double statistics vector (NCCL), "
+            "issued every 344 steps in production: %.4f of a step when amortised" % (float(ar.item()) / 344.0 / ms)}
+
+
+def bench_motor_full(exo_b200, args, dev, flush):
+    """The same workload with ExoConfig.motor_model = EXO_MOTOR_FULL: the general Bullet multibody step (forward dynamics +
+    50-sweep projected Gauss-Seidel, csrc/exo_motor.cuh) instead of its closed-form fixed point. Compute-bound."""
+    import torch
+    n = args.envs_per_gpu
+    motion, seqs, seeds = population(n, 0, 1)
+    env = exo_b200.BatchedExoskeletonEnv(motion, seqs, seeds, device=dev, precision=args.precision, auto_reset=True,
+                                         motor_model="full", **TRAIN)
+    gen = torch.Generator(device=dev).manual_seed(5)
+    acts = torch.rand(2, n, 7, device=dev, generator=gen) * 2 - 1
+    env.reset()
+    dephase(env, acts)
+    env.stats(reset=True)
+    steps = 20
+    ev = []
+    for t in range(steps):
+        if flush is not None:
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        env.step(acts[t % 2], keep_idle_obs=False)
+        b.record()
+        ev.append((a, b))
+    torch.cuda.synchronize(dev)
+    ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    st = env.stats().cpu().numpy()
+    env.close()
+    return {"motor_model": "EXO_MOTOR_FULL (pybullet default solver settings: 50 iterations, residual threshold 1e-7, inertia from "
+                           "collision boxes)", "envs": n, "ms_per_step": ms, "value": n / (ms * 1e-3), "unit": UNIT,
+            "solver_sweeps_per_env_step": float(st[14] / max(st[15], 1.0)), "kernel": "exo_motor_kernel + exo_step_kernel<FULL>"}
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU algorithm (oracle port; the Python reference cannot travel to the GPU box
     and needs pybullet) on all host threads, rank 0 only."""
@@ -359,6 +534,10 @@ def main():
     ap.add_argument("--no-lap", action="store_true", help="skip the replay-buffer (next row N1) measurement")
     ap.add_argument("--no-large", action="store_true", help="skip the 524 288-env roofline measurement of the step kernel")
     ap.add_argument("--no-policy", action="store_true", help="skip the policy forward pass (next row N2) measurement")
+    ap.add_argument("--policy-weights", default=None, help="reference checkpoint prefix for the policy leg (default: synthetic weights)")
+    ap.add_argument("--no-dephase", action="store_true", help="skip the pre-roll (lock-step population: no episode ends for 229 steps)")
+    ap.add_argument("--no-cfg4", action="store_true", help="skip the BASELINE config 4 sub-record (1M envs over the ranks, N > 1 only)")
+    ap.add_argument("--no-motor-full", action="store_true", help="skip the EXO_MOTOR_FULL (general multibody step) sub-record")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -392,6 +571,8 @@ def main():
         torch.cuda.synchronize(dev)
 
     env.reset()
+    if not args.no_dephase:
+        dephase(env, actions)
     for t in range(args.warmup):
         env.step(actions[t % n_act])
     env.stats(reset=True)
@@ -473,10 +654,17 @@ def main():
         pass
     policy_line = None
     if rank == 0 and not args.no_policy:
-        policy_line = bench_policy(exo_b200, env, dev, flush, peaks)
+        policy_line = bench_policy(exo_b200, env, dev, flush, peaks, args.policy_weights)
         policy_line["td7_update"] = bench_td7(exo_b200, dev)
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    cfg4 = None
+    if world > 1 and not args.no_cfg4:
+        cfg4 = bench_cfg4(exo_b200, args, rank, world, dev, flush, peak, barrier)
     if rank == 0:
-        peak = float(peaks.get("hbm_gbs", 6650.0))
+        reset_line = bench_reset(env, dev, flush, peak)
+        motor_line = None
+        if world == 1 and not args.no_motor_full:
+            motor_line = bench_motor_full(exo_b200, args, dev, flush)
         achieved = ALGO_BYTES_PER_ENV_STEP * n / (kms * 1e-3) / 1e9
         cpu_v, cpu_cores, cpu_secs = cpu_baseline(args.cpu_sample, args.cpu_steps)
         large = None
@@ -487,7 +675,9 @@ def main():
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32" if args.precision == "fp32" else "f64", "data": "synthetic",
             "config": {"workload": "BASELINE cfg3 per GPU: %d envs/GPU, training DR (0.02/0.03/0.1), 8 reference motions x 15 tremor "
-                                   "types, auto-reset, U(-1,1)^7 device actions" % n,
+                                   "types, auto-reset, U(-1,1)^7 device actions, population de-phased by a %d-step untimed pre-roll"
+                                   % (n, 0 if args.no_dephase else DEPHASE_PERIOD),
+                       "expected_episode_ends_per_step": n / MEAN_EPISODE_STEPS,
                        "envs_per_gpu": n, "total_envs": world * n, "l2": "flushed between steps (512 MiB overwrite, untimed)"
                        if flush is not None else "not flushed", "episodes_finished": stats_sum[0].item(),
                        "mean_return": (stats_sum[1] / stats_sum[0]).item() if stats_sum[0].item() > 0 else None,
@@ -495,7 +685,7 @@ def main():
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": STEP_KERNEL_DRAM_BYTES_65536 if (n == 65536 and args.precision == "fp32") else None,
                          "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of one launch, "
-                                           "profiles/r01g_ncu_full_step.txt (writes stay in L2 inside the launch)",
+                                           + TRAFFIC_SOURCE + " (writes stay in L2 inside the launch)",
                          "kernel": "exo_step_kernel", "kernel_ms": kms,
                          "algorithmic_bytes_per_env_step": ALGO_BYTES_PER_ENV_STEP,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)"},
@@ -507,6 +697,13 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
         }
+        line["roofline_reset"] = reset_line
+        if motor_line is not None:
+            line["motor_full"] = motor_line
+        if cfg4 is not None:
+            line["cfg4"] = cfg4
+        if not args.no_dephase and not (stats_sum[0].item() > 0):
+            raise SystemExit("bench.py: no episode ended inside the timed region - the steady-state assumption is broken")
         if large is not None:
             line["roofline"]["large_population"] = large
         if lap_line is not None:

@@ -34,6 +34,14 @@ typedef enum {
 
 enum { EXO_F32 = 0, EXO_F64 = 1 };
 enum { EXO_ODE_PROPAGATOR = 0, EXO_ODE_RK45 = 1 };
+/* What stands in for pybullet's stepSimulation (Exoskeleton_env.py:433) behind the POSITION_CONTROL motors
+ * (Exoskeleton_sim_pybullet.py:109-117):
+ *   EXO_MOTOR_IDEAL  the fixed point of Bullet's constraint solve, q+ = q + kp (target - q), inside the step kernel (default);
+ *   EXO_MOTOR_FULL   the general multibody step: forward dynamics of the URDF tree (gravity, link damping, Coriolis),
+ *                    motor + joint-limit rows, numSolverIterations sweeps of projected Gauss-Seidel in Bullet's row order
+ *                    with its early exit, semi-implicit Euler (csrc/exo_motor.cuh, oracle/multibody.py). Needs
+ *                    exo_set_motor_model before exo_seed. */
+enum { EXO_MOTOR_IDEAL = 0, EXO_MOTOR_FULL = 1 };
 
 /* Constructor arguments of ExoskeletonEnv_train (Exoskeleton_env.py:38-48), shared by all envs of a handle,
  * plus the knobs of the restated pybullet boundary (oracle/minibullet.py) and kernel options. */
@@ -52,7 +60,7 @@ typedef struct {
     int32_t reference_ctor;   /* 1: exo_seed also performs the constructor's draws: one rand() (Exoskeleton_env.py:70)
                                  and one initialize_movement (:172), so streams line up with the reference */
     int32_t metrics;          /* 1: accumulate the training script's per-step suppression metrics on device */
-    int32_t reserved;
+    int32_t motor_model;      /* EXO_MOTOR_IDEAL (default) | EXO_MOTOR_FULL */
 } ExoConfig;
 
 /* Kinematic tree of the URDF in Bullet numbering (pre-order DFS over child joints in file order, base = -1). */
@@ -68,6 +76,32 @@ typedef struct {
     int32_t act_link[14];                 /* link handles act11,act12,act21,...,act72 (Exoskeleton_sim_pybullet.py:48-61) */
     int32_t shoulder_link, elbow_link;    /* Exoskeleton_sim_pybullet.py:62-63 */
 } ExoGeometry;
+
+/* Inertial data of the URDF links, Bullet numbering (Simulation/exo_v3.urdf <inertial> / <collision> elements). pybullet
+ * recomputes link inertias from the collision shape unless URDF_USE_INERTIA_FROM_FILE is passed (the reference passes no
+ * flags, Exoskeleton_sim_pybullet.py:18), so both descriptions travel. */
+typedef struct {
+    double mass[EXO_NLINKS];
+    double inertia_diag[EXO_NLINKS][3];   /* ixx, iyy, izz of <inertia> (products of inertia are zero in this URDF) */
+    double inertial_R[EXO_NLINKS][9];     /* rotation of the inertial frame in the link frame (<inertial><origin rpy>) */
+    double box_size[EXO_NLINKS][3];       /* the link's <collision> box */
+    double box_xyz[EXO_NLINKS][3];
+    double box_R[EXO_NLINKS][9];
+} ExoLinkDynamics;
+
+/* Settings of the general multibody step; the values in comments are pybullet 3.2.5's defaults as the reference uses it. */
+typedef struct {
+    int32_t inertia_from_file;     /* 0: inertia of the collision box's AABB in the inertial frame (pybullet default), 1: <inertia> */
+    int32_t iterations;            /* numSolverIterations: 50 */
+    int32_t row_order;             /* 0: order left by Bullet's quickSort of the world's constraints by island id, 1: world order */
+    int32_t reserved;
+    double  residual_threshold;    /* leastSquaresResidualThreshold on the largest squared row velocity error of a sweep: 1e-7 */
+    double  kp, kd, max_force;     /* setJointMotorControlArray defaults: 0.1, 1.0, 1e5 N (impulse cap = max_force * dt) */
+    double  default_motor_impulse; /* the velocity motors createJointMotors puts on every joint: 1.0 N s */
+    double  linear_damping, angular_damping;   /* btMultiBody per-link damping: 0.04, 0.04 */
+    double  gravity[3];            /* Exoskeleton_env.py:116: 0, 0, -9.81 */
+    double  erp, limit_max_impulse;            /* joint-limit rows: 0.2, 100 */
+} ExoMotorModel;
 
 /* Optional per-step outputs = the reference's `info` dict (Exoskeleton_env.py:464-469). Any pointer may be NULL. */
 typedef struct {
@@ -100,6 +134,10 @@ typedef enum {
     EXO_FIELD_META,           /* i32  [1]   bits 0-6 tremor_sequence, bits 8-15 motion id, bits 16-31 max_count */
     EXO_FIELD_MT_STATE,       /* u32  [625] numpy legacy MT19937 key + position */
     EXO_FIELD_EP_RETURN,      /* real [1]   running episode return */
+    EXO_FIELD_QD,             /* real [14]  EXO_MOTOR_FULL: joint velocities: 5 arm joints, 7 humerus dummies (act11, act21, act32,
+                                            act42, act52, act62, act72), 2 forearm dummies (act12, act22) */
+    EXO_FIELD_Q_PRIS,         /* real [9]   EXO_MOTOR_FULL: prismatic positions of those 9 dummies (m) */
+    EXO_FIELD_Q_PRIS_LAG,     /* real [9]   EXO_MOTOR_FULL: the prismatic positions behind the link-state cache */
     EXO_N_FIELDS
 } ExoField;
 enum { EXO_DT_REAL = 0, EXO_DT_F64 = 1, EXO_DT_I32 = 2, EXO_DT_U32 = 3 };
@@ -117,6 +155,12 @@ int exo_destroy(ExoHandle* h);
 /* read_env_texts result (Utilities/read_txt_env.py:73-170), columns 0-4 only:
  * tables[m][r][k], r = elbow_y, elbow_z, shoulder_x, shoulder_y, shoulder_z in degrees, padded to max_len. Host pointers. */
 int exo_load_motions(ExoHandle* h, const double* tables, const int32_t* lengths, int32_t n_motions, int32_t max_len);
+
+/* EXO_MOTOR_FULL only: link inertial data + solver settings (model == NULL: pybullet's defaults). Host pointers.
+ * Call after exo_create, before exo_seed. */
+int exo_set_motor_model(ExoHandle* h, const ExoLinkDynamics* links, const ExoMotorModel* model);
+/* pybullet's defaults, for callers that want to change one knob */
+void exo_default_motor_model(ExoMotorModel* out);
 
 /* Per-env constructor arguments: tremor_sequence[7] (0/1) and reference_motion_file_num. Host pointers. */
 int exo_set_env_types(ExoHandle* h, const uint8_t* tremor_sequence /*[n,7]*/, const int32_t* motion_id /*[n]*/);
@@ -153,7 +197,8 @@ int exo_set_field(ExoHandle* h, int32_t field, const void* in_dev, void* stream)
  * 7 count of those steps; with `info` requested also the training script's suppression metrics
  * (Simulation/Exoskeleton_agent_train.py:150-193): 8 / 9 arm-axis samples with torque reduction >= 0 / < 0 (tremor_when_reduction),
  * 10 / 11 sum and count of negative torque-reduction percentages over the 7 axes, 12 / 13 the same for the amplitude
- * reduction (positive values dropped as by the script's `disregard`), 14.. reserved.
+ * reduction (positive values dropped as by the script's `disregard`); EXO_MOTOR_FULL: 14 constraint-solver sweeps,
+ * 15 env-steps through the general multibody step (14 / 15 = sweeps per step).
  * This vector is what ranks all-reduce over NCCL. */
 int exo_stats(ExoHandle* h, double* out_dev, int32_t reset, void* stream);
 

@@ -25,6 +25,9 @@ Families
   B  BASELINE config 2: 15 tremor types x 8 motions, no domain randomisation, 30 steps.
   C  BASELINE config 3 settings (training DR, Exoskeleton_agent_train.py:30-35,43-44),
      one env per motion: a full episode, reset, 20 more steps (state carried across reset).
+  F  the same env on minibullet's motor_model="full" (the general Bullet multibody step, oracle/multibody.py, pybullet's
+     default solver settings): config 1 for 300 steps (one reset) and config 3 on motions 1 and 5. Written to
+     ref_full_motor.npz; what the product's EXO_MOTOR_FULL path is held to.
 """
 import argparse
 import contextlib
@@ -59,7 +62,7 @@ class Recorder(object):
     def __init__(self, env):
         self.env = env
         self.ep = dict(tt=[], I=[], D=[], S=[], shift=[], fmax=[], mag=[], obs0=[], at_step=[])
-        self.st = dict(action=[], obs=[], reward=[], done=[], qb=[], rew_parts=[])
+        self.st = dict(action=[], obs=[], reward=[], done=[], qb=[], rew_parts=[], q19=[], qd19=[])
         for k in INFO_KEYS:
             self.st[k] = []
 
@@ -83,14 +86,18 @@ class Recorder(object):
         self.st["reward"].append(float(reward))
         self.st["done"].append(bool(done))
         self.st["qb"].append(np.array(self.env.client._world.bodies[0].q[:5]))
+        self.st["q19"].append(np.array(self.env.client._world.bodies[0].q))
+        self.st["qd19"].append(np.array(self.env.client._world.bodies[0].qd))
         self.st["rew_parts"].append(np.array([float(info[k]) for k in REW_KEYS]))
         for k in INFO_KEYS:
             self.st[k].append(np.array(info[k], dtype=np.float64))
 
-    def pack(self, prefix, out, meta):
+    def pack(self, prefix, out, meta, keep_q19=False):
         for k, v in self.ep.items():
             out[f"{prefix}/ep_{k}"] = np.array(v)
         for k, v in self.st.items():
+            if k in ("q19", "qd19") and not keep_q19:
+                continue
             out[f"{prefix}/{k}"] = np.array(v)
         for k, v in meta.items():
             out[f"{prefix}/meta_{k}"] = np.array(v)
@@ -164,7 +171,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default=os.path.join(REPO, "tests", "golden"))
     ap.add_argument("--lag", type=int, default=1)
-    ap.add_argument("--families", default="DABC")
+    ap.add_argument("--families", default="DABCF")
     args = ap.parse_args()
     out_dir = os.path.abspath(args.out)
     Env = _import_reference(dict(link_state_lag=args.lag))
@@ -258,6 +265,25 @@ def main():
             n += meta["limit_crossings"]
         np.savez_compressed(os.path.join(out_dir, "ref_cfg3_dr_episodes.npz"), **out)
         print("C: 8 cases, limit crossings", n)
+
+
+    if "F" in args.families:
+        import pybullet_utils.bullet_client as bc
+        bc.DEFAULT_KNOBS.update(dict(motor_model="full"))
+        out = {}
+        rec, meta = run_case(Env, 0, 0, [1, 1, 1, 1, 0, 0, 0], EVAL_SETTINGS, 300, trained_actor_policy())
+        rec.pack("F0", out, meta, keep_q19=True)
+        sweeps = [rec.env.client._world.full[0].stats["sweeps"] / 300.0]
+        for k, m in enumerate((1, 5)):
+            seq = TYPES15[(5 * m + 14) % 15]
+            rs = np.random.RandomState(60_000 + m)
+            L = [232, 316, 282, 295, 270, 347, 266, 273][m]
+            rec, meta = run_case(Env, 900 + m, m, seq, TRAIN_SETTINGS, (L - 3) + 20, lambda o, t: f32_actions(rs))
+            rec.pack(f"F{k + 1}", out, meta, keep_q19=True)
+            sweeps.append(rec.env.client._world.full[0].stats["sweeps"] / float((L - 3) + 20))
+        bc.DEFAULT_KNOBS.pop("motor_model")
+        np.savez_compressed(os.path.join(out_dir, "ref_full_motor.npz"), **out)
+        print("F: 3 cases on the general multibody step, sweeps/step", sweeps)
 
 
 if __name__ == "__main__":

@@ -231,6 +231,20 @@ class OracleBatch(object):
             self.obs[i] = e.reset()[0]
         return self.obs
 
+    def dephase(self, period, threads=0, seed=7):
+        """Spread the envs over their episodes (bench.py does the same on the GPU): env i takes (i mod period) extra steps
+        with random actions and auto-reset, so a timed window holds its steady-state share of episode ends."""
+        rs = np.random.RandomState(seed)
+        phase = np.arange(self.n) % period
+        obs, rew, done = np.zeros((self.n, 80), np.float32), np.zeros(self.n), np.zeros(self.n, np.int32)
+        for t in range(period):
+            idx = np.nonzero(phase > t)[0]
+            if idx.size == 0:
+                break
+            hs = (C.c_void_p * idx.size)(*[self.envs[i].h for i in idx])
+            a = np.ascontiguousarray(rs.uniform(-1, 1, (idx.size, 7)))
+            lib().orc_step_many(hs, int(idx.size), _dp(a), _fp(obs), _dp(rew), done.ctypes.data_as(C.POINTER(C.c_int)), 1, int(threads))
+
     def step(self, actions, auto_reset=True, threads=0):
         a = np.ascontiguousarray(actions, dtype=np.float64)
         lib().orc_step_many(self.handles, self.n, _dp(a), _fp(self.obs), _dp(self.reward),

@@ -178,6 +178,31 @@ def _replay_golden_episodes(exo, g, cases, precision, settings_case):
     return worst_obs, worst_q, worst_r
 
 
+def test_two_shards_reproduce_the_one_handle_run_bit_for_bit(exo):
+    """World-size independence (BASELINE config 4): two handles holding the two halves of a population - what
+    ranks 0 and 1 of a 2-GPU job build - give, bit for bit, the observations / rewards / done flags of the one-handle run,
+    over 360 steps with auto-reset (every env crosses at least one episode boundary)."""
+    from exo_b200 import sharding
+    n, steps = 8192, 360
+    whole = exo.BatchedExoskeletonEnv(*sharding.benchmark_population(n, 0, 1), auto_reset=True, **TRAIN)
+    halves = [exo.BatchedExoskeletonEnv(*sharding.benchmark_population(n, r, 2), auto_reset=True, **TRAIN) for r in range(2)]
+    spans = [sharding.shard_range(n, r, 2) for r in range(2)]
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(3)
+    acts = torch.rand(6, n, 7, device="cuda", generator=gen) * 2 - 1
+    o = whole.reset()
+    for (lo, hi), hv in zip(spans, halves):
+        assert torch.equal(o[lo:hi], hv.reset())
+    for t in range(steps):
+        ob, rw, dn = whole.step(acts[t % 6])
+        for (lo, hi), hv in zip(spans, halves):
+            hob, hrw, hdn = hv.step(acts[t % 6][lo:hi].contiguous())
+            assert torch.equal(ob[lo:hi], hob) and torch.equal(rw[lo:hi], hrw) and torch.equal(dn[lo:hi], hdn), t
+    assert float(whole.stats()[0]) == sum(float(hv.stats()[0]) for hv in halves) >= n
+    for e in [whole] + halves:
+        e.close()
+
+
 @pytest.mark.parametrize("precision", ["fp64", "fp32"])
 def test_against_reference_goldens_cfg3_full_episodes_with_auto_reset(exo, precision):
     """Training DR, one full episode per motion, reset, 20 more steps: state carried over the reset
@@ -339,7 +364,7 @@ def test_full_size_properties_65536_envs(exo):
     n, steps = 65536, 400
     motion, seqs, seeds = sharding.benchmark_population(n)
     env = exo.BatchedExoskeletonEnv(motion, seqs, seeds, auto_reset=True, **TRAIN)
-    sl = slice(8192 * 3 - 2048, 8192 * 3 + 2048)                   # straddles a motion boundary
+    sl = slice(1024 * 3 - 2048, 1024 * 3 + 2048)                   # straddles motion-block boundaries
     sub = exo.BatchedExoskeletonEnv(motion[sl], seqs[sl], seeds[sl], auto_reset=True, **TRAIN)
     gen = torch.Generator(device="cuda")
     gen.manual_seed(0)

@@ -135,9 +135,18 @@ def test_shard_ranges_partition_the_population(exo):
         spans = [sh.shard_range(n, r, w) for r in range(w)]
         assert spans[0][0] == 0 and spans[-1][1] == n and all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
     m, s, seeds = sh.benchmark_population(65_536, 0, 1)
-    assert np.array_equal(np.bincount(m), np.full(8, 8192)) and np.all(np.diff(m) >= 0)     # cfg 3: 8192 envs per motion, contiguous
+    assert np.array_equal(np.bincount(m), np.full(8, 8192))                                   # cfg 3: 8192 envs per motion
+    assert all(len(set(m[b:b + 1024])) == 1 for b in range(0, 65_536, 1024))                   # in contiguous 1024-env blocks
     assert len({tuple(x) for x in s}) == 15 and s[:, :4].sum(1).min() >= 1 and s[:, 4:].sum() == 0
     # global ids/seeds do not depend on the number of ranks
     parts = [sh.benchmark_population(4096, r, 4) for r in range(4)]
     assert np.array_equal(np.concatenate([p[2] for p in parts]), np.arange(4096))
     assert np.array_equal(np.concatenate([p[1] for p in parts]), sh.benchmark_population(4096, 0, 1)[1])
+    # ... nor does anything else about global env g: motion, tremor type and seed of the concatenated shards are those of
+    # the one-rank population for every world size (BASELINE config 4: 1M envs over 2/4/8 GPUs)
+    for n in (1_048_576, 65_536, 5000):
+        one = sh.benchmark_population(n, 0, 1)
+        for w in (2, 4, 8):
+            parts = [sh.benchmark_population(n, r, w) for r in range(w)]
+            for k in range(3):
+                assert np.array_equal(np.concatenate([p[k] for p in parts]), one[k]), (n, w, k)
