@@ -71,6 +71,7 @@ class ExoInfo(C.Structure):
 FIELDS = {name: i for i, name in enumerate(
     ("q", "q_lag", "pos_vec", "elbow_ref", "prev_action", "prev_action2", "force_max", "shift", "G", "IDS", "tremor_table",
      "tremor_mag", "counts", "meta", "mt_state", "ep_return", "qd", "q_pris", "q_pris_lag"))}
+FIELD_NEXT = 0x100        # EXO_FIELD_NEXT: the prefetched copy (next episode's parameters) of a per-episode field
 DT_REAL, DT_F64, DT_I32, DT_U32 = 0, 1, 2, 3
 
 
@@ -93,6 +94,8 @@ SIGNATURES = {
     "exo_get_field": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     "exo_set_field": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     "exo_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
+    "exo_wait_prefetch": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "exo_debug_timeline": (C.c_int, [C.c_void_p, C.c_void_p]),
     "exo_set_auto_reset": (C.c_int, [C.c_void_p, C.c_int32]),
     "exo_launch_count": (C.c_int64, [C.c_void_p]),
     "exo_forward_kinematics": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_void_p]),

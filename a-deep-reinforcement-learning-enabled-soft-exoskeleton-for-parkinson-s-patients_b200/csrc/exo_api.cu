@@ -39,10 +39,21 @@ int exo_set_error(int code, const char* fmt, ...) {
 extern "C" const char* exo_last_error(void) { return g_err; }
 extern "C" int exo_abi_version(void) { return 1; }
 
+#define EXO_GEN_STREAMS 4
+
 struct ExoHandle {
     ExoConfig cfg;
     ExoGeometry geo;
-    int n, stride, device, nax, max_len, n_motions, n_sm, parity;
+    int n, stride, device, nax, max_len, n_motions, n_sm;
+    // episode prefetch: generation passes run on s_gen, one work list of the ring per exo_step / exo_reset call
+    int64_t tick;                // calls so far; ring slot = tick % EXO_RING
+    int last_gen[EXO_GEN_STREAMS];   // per side stream: ring slot of its newest generation pass (-1: none)
+    bool gen_ready;              // s_gen / events created
+    bool ev_gen_used[EXO_RING];
+    int n_gen_streams;
+    cudaStream_t s_gen[EXO_GEN_STREAMS];   // passes of consecutive calls touch disjoint envs: they round-robin over these streams and
+                                           // overlap, so a pass's ~50 us chain latency does not pace the steps (one in-order stream would)
+    cudaEvent_t ev_gen[EXO_RING], ev_main[EXO_RING];
     bool have_motions, have_types, seeded;
     int64_t launches;
     std::vector<void*> allocs;
@@ -50,6 +61,7 @@ struct ExoHandle {
     EnvArrays<double> Ad;
     ChainConst<float> Cf;
     ChainConst<double> Cd;
+    long long* timeline;         // debug: exo_debug_timeline
     DynConst<float> Df;          // EXO_MOTOR_FULL: inertial data + solver settings (exo_set_motor_model)
     DynConst<double> Dd;
     bool have_dyn;
@@ -259,10 +271,11 @@ static int alloc_arrays(ExoHandle* h, EnvArrays<R>& A) {
     memset(&A, 0, sizeof(A));
     A.n = h->n; A.stride = h->stride;
 #define AL(field, T, count) if (int rc = dev_alloc(h, (void**)&A.field, sizeof(T) * (size_t)(count))) return rc
-    AL(state, V4<R>, NV_STATE * st); AL(ep, V4<R>, NV_EP * st); AL(G, V4<R>, NV_G * st);
-    AL(ret, R, st); AL(counts, int, st); AL(meta, int, st); AL(mag, double, st);
-    AL(IDS, double, n * EXO_IDS_PITCH); AL(mt, uint32_t, n * EXO_MT_PITCH);
-    AL(stats, double, EXO_N_STATS); AL(fin_count, int, 2); AL(fin_list, int, 2 * st);
+    AL(state, V4<R>, NV_STATE * st); AL(ep, V4<R>, 2 * NV_EP * st); AL(G, V4<R>, 2 * NV_G * st);
+    A.ep_slot = NV_EP * st; A.G_slot = NV_G * st;
+    AL(ret, R, st); AL(counts, int, st); AL(meta, int, st); AL(mag, double, 2 * st);
+    AL(IDS, double, 2 * n * EXO_IDS_PITCH); AL(mt, uint32_t, n * EXO_MT_PITCH);
+    AL(stats, double, EXO_N_STATS); AL(fin_count, int, EXO_RING); AL(fin_list, int, (size_t)EXO_RING * st);
     if (h->cfg.motor_model == EXO_MOTOR_FULL) { AL(dyn, V4<R>, NV_DYN * st); AL(tgt, V4<R>, NV_TGT * st); }
 #undef AL
     return 0;
@@ -283,7 +296,12 @@ extern "C" int exo_create(const ExoConfig* cfg, const ExoGeometry* geo, int32_t 
     ExoHandle* h = new ExoHandle();
     h->cfg = *cfg; h->geo = *geo; h->n = n_envs; h->stride = (n_envs + 31) & ~31; h->device = device;
     h->nax = 4; h->max_len = 0; h->n_motions = 0; h->have_motions = h->have_types = h->seeded = false; h->launches = 0;
-    h->n_sm = prop.multiProcessorCount; h->parity = 0; h->pipe_ready = false; h->have_dyn = false;
+    h->n_sm = prop.multiProcessorCount; h->pipe_ready = false; h->have_dyn = false;
+    h->timeline = nullptr;
+    h->tick = 0; h->gen_ready = false; h->n_gen_streams = EXO_GEN_STREAMS;
+    if (const char* e = getenv("EXO_GEN_STREAMS")) { const int k = atoi(e); if (k >= 1 && k <= EXO_GEN_STREAMS) h->n_gen_streams = k; }
+    for (int i = 0; i < EXO_GEN_STREAMS; i++) h->last_gen[i] = -1;
+    for (int i = 0; i < EXO_RING; i++) h->ev_gen_used[i] = false;
     h->d_act = nullptr; h->d_obs = nullptr; h->d_rew = nullptr; h->d_done = nullptr; h->d_mask = nullptr; h->d_seeds = nullptr;
     if (int rc = build_chain(h)) { delete h; return rc; }
     int rc = (cfg->precision == EXO_F32) ? alloc_arrays(h, h->Af) : alloc_arrays(h, h->Ad);
@@ -302,6 +320,10 @@ extern "C" int exo_destroy(ExoHandle* h) {
     if (!h) return 0;
     cudaSetDevice(h->device);
     for (void* p : h->allocs) cudaFree(p);
+    if (h->gen_ready) {
+        for (int i = 0; i < EXO_GEN_STREAMS; i++) { cudaStreamSynchronize(h->s_gen[i]); cudaStreamDestroy(h->s_gen[i]); }
+        for (int i = 0; i < EXO_RING; i++) { cudaEventDestroy(h->ev_gen[i]); cudaEventDestroy(h->ev_main[i]); }
+    }
     if (h->pipe_ready) {
         cudaStreamDestroy(h->s_in); cudaStreamDestroy(h->s_out);
         cudaEventDestroy(h->ev_start); cudaEventDestroy(h->ev_done);
@@ -344,7 +366,8 @@ static int alloc_tables(ExoHandle* h, EnvArrays<R>& A) {
     for (int l : h->motion_len) tl = l > tl ? l : tl;
     A.table_len = tl;
     const size_t naxv = (h->nax + 3) / 4;
-    return dev_alloc(h, (void**)&A.tt, sizeof(V4<R>) * (size_t)tl * h->stride * naxv);
+    A.tt_slot = (size_t)tl * h->stride * naxv;
+    return dev_alloc(h, (void**)&A.tt, sizeof(V4<R>) * 2 * A.tt_slot);
 }
 
 extern "C" int exo_set_env_types(ExoHandle* h, const uint8_t* seq, const int32_t* motion_id) {
@@ -378,7 +401,14 @@ static StepConst<R> step_const(const ExoHandle* h) {
     StepConst<R> K;
     K.fmax_sh0 = (R)h->cfg.max_force_shoulder; K.fmax_el0 = (R)h->cfg.max_force_elbow;
     K.inv_fmax_sh0 = R(1) / K.fmax_sh0; K.inv_fmax_el0 = R(1) / K.fmax_el0;
-    K.parity = h->parity;
+    K.list = 0; K.fused_begin = 0;
+    // staggered load issue (exo_step.cuh): one dispatch layer's share of the launch's HBM burst takes ~0.75 us at the measured
+    // 6.5 TB/s (34 MB / 7 layers) = ~1470 SM cycles; only single-wave launches (<= 8 blocks per SM) are staggered - in a
+    // multi-wave launch successive waves overlap their phases by themselves. EXO_STEP_STAGGER overrides (0 = off).
+    static const int stagger = getenv("EXO_STEP_STAGGER") ? atoi(getenv("EXO_STEP_STAGGER")) : 1470;
+    const int blocks = (h->n + EXO_STEP_THREADS - 1) / EXO_STEP_THREADS;
+    K.stagger_cycles = (blocks > 2 * h->n_sm && blocks <= 8 * h->n_sm) ? stagger : 0; K.n_sm = h->n_sm;
+    K.timeline = h->timeline;
     K.L1 = (R)h->cfg.humerus_length; K.L2 = (R)h->cfg.forearm_length;
     K.lag = h->cfg.link_state_lag; K.limits = h->cfg.joint_limits; K.auto_reset = h->cfg.auto_reset; K.metrics = h->cfg.metrics;
     K.motor_full = h->cfg.motor_model == EXO_MOTOR_FULL;
@@ -396,21 +426,64 @@ static ResetConst reset_const(const ExoHandle* h) {
     K.dt = 1.0 / 40.0;                       // Exoskeleton_env.py:59
     K.lag = h->cfg.link_state_lag;
     K.motor_full = h->cfg.motor_model == EXO_MOTOR_FULL;
-    K.ctor_skip = 0; K.list_parity = -1;
+    K.ctor_skip = 0; K.list = -1; K.append = -1;
     return K;
 }
 
-// list_parity >= 0: the envs the step of that parity appended to the finished-list; otherwise by mask (NULL: all)
+static int gen_setup(ExoHandle* h) {
+    if (h->gen_ready) return 0;
+    // lowest priority: when blocks of a step kernel and of a generation pass are both waiting for an SM, the step goes first
+    int prio_lo = 0, prio_hi = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    if (getenv("EXO_GEN_NOPRIO")) prio_lo = 0;
+    for (int i = 0; i < EXO_GEN_STREAMS; i++) CK(cudaStreamCreateWithPriority(&h->s_gen[i], cudaStreamNonBlocking, prio_lo));
+    for (int i = 0; i < EXO_RING; i++) {
+        CK(cudaEventCreateWithFlags(&h->ev_gen[i], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&h->ev_main[i], cudaEventDisableTiming));
+    }
+    h->gen_ready = true;
+    return 0;
+}
+
+// `s` waits for every generation pass launched so far (they run in order on s_gen)
+static int wait_all_gen(ExoHandle* h, cudaStream_t s) {
+    if (h->gen_ready)
+        for (int i = 0; i < EXO_GEN_STREAMS; i++)
+            if (h->last_gen[i] >= 0) CK(cudaStreamWaitEvent(s, h->ev_gen[h->last_gen[i]], 0));
+    return 0;
+}
+
+// generation pass for work list `list` (filled by kernels already queued on `s`), on the side stream
 template <typename R>
-static int reset_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const uint8_t* mask, float* obs, int list_parity,
-                   int ctor_skip, cudaStream_t s) {
+static int gen_list_async(ExoHandle* h, EnvArrays<R>& A, int list, cudaStream_t s) {
+    if (int rc = gen_setup(h)) return rc;
+    const int si = list % h->n_gen_streams;
+    cudaStream_t g = h->s_gen[si];
+    CK(cudaEventRecord(h->ev_main[list], s));
+    CK(cudaStreamWaitEvent(g, h->ev_main[list], 0));
     ResetConst K = reset_const(h);
-    K.list_parity = list_parity; K.ctor_skip = ctor_skip;
-    if (int e = launch_reset<R>(A, C, K, h->nax, h->n_sm, mask, obs, s))
-        return fail(EXO_ERR_CUDA, "exo_reset_kernel setup: %s", cudaGetErrorString((cudaError_t)e));
+    K.list = list;
+    if (int e = launch_gen<R>(A, K, h->nax, h->n_sm, nullptr, g))
+        return fail(EXO_ERR_CUDA, "exo_gen_kernel: %s", cudaGetErrorString((cudaError_t)e));
+    h->launches += 1;
+    CK(cudaEventRecord(h->ev_gen[list], g));
+    h->ev_gen_used[list] = true;
+    h->last_gen[si] = list;
+    return 0;
+}
+
+// env.reset() for the masked envs: start their prefetched episode (exo_begin_kernel) on `s`, refill the spare slot on s_gen
+template <typename R>
+static int reset_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const uint8_t* mask, float* obs, cudaStream_t s) {
+    if (int rc = wait_all_gen(h, s)) return rc;        // an env reset here may still have its spare slot in flight
+    const int list = (int)(h->tick++ % EXO_RING);
+    CK(cudaMemsetAsync(A.fin_count + list, 0, sizeof(int), s));
+    ResetConst K = reset_const(h);
+    K.append = list;
+    launch_begin<R>(A, C, K, h->nax, mask, obs, s);
     h->launches += 1;
     CK(cudaGetLastError());
-    return 0;
+    return gen_list_async<R>(h, A, list, s);
 }
 
 static int check_ready(ExoHandle* h, const char* who) {
@@ -418,6 +491,28 @@ static int check_ready(ExoHandle* h, const char* who) {
     if (!h->seeded) return fail(EXO_ERR_STATE, "%s: call exo_load_motions, exo_set_env_types and exo_seed first", who);
     if (h->cfg.motor_model == EXO_MOTOR_FULL && !h->have_dyn) return fail(EXO_ERR_STATE, "%s: EXO_MOTOR_FULL needs exo_set_motor_model", who);
     CK(cudaSetDevice(h->device));
+    return 0;
+}
+
+// After np.random.seed: every env gets the parameters of its first episode into the spare slot (the invariant the step
+// kernel's auto-reset and exo_reset rely on). With reference_ctor the constructor's draws come first: one rand()
+// (Exoskeleton_env.py:70) and a whole initialize_movement (:172), which also leaves its position vectors in the state.
+template <typename R>
+static int seed_prime(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, cudaStream_t s) {
+    if (h->gen_ready) { for (int i = 0; i < EXO_GEN_STREAMS; i++) CK(cudaStreamSynchronize(h->s_gen[i])); }
+    for (int i = 0; i < EXO_GEN_STREAMS; i++) h->last_gen[i] = -1;
+    CK(cudaMemsetAsync(A.counts, 0, sizeof(int) * h->stride, s));
+    ResetConst K = reset_const(h);
+    if (h->cfg.reference_ctor) {
+        K.ctor_skip = 2;
+        if (int e = launch_gen<R>(A, K, h->nax, h->n_sm, nullptr, s)) return fail(EXO_ERR_CUDA, "exo_gen_kernel: %s", cudaGetErrorString((cudaError_t)e));
+        K.ctor_skip = 0;
+        launch_begin<R>(A, C, K, h->nax, nullptr, nullptr, s);
+        h->launches += 2;
+    }
+    if (int e = launch_gen<R>(A, K, h->nax, h->n_sm, nullptr, s)) return fail(EXO_ERR_CUDA, "exo_gen_kernel: %s", cudaGetErrorString((cudaError_t)e));
+    h->launches += 1;
+    CK(cudaGetLastError());
     return 0;
 }
 
@@ -432,11 +527,8 @@ extern "C" int exo_seed(ExoHandle* h, const uint32_t* seeds, void* stream) {
     h->launches += 1;
     CK(cudaGetLastError());
     h->seeded = true;
-    if (h->cfg.reference_ctor) {             // the constructor's rand() (Exoskeleton_env.py:70) and its own initialize_movement (:172)
-        int rc = h->cfg.precision == EXO_F32 ? reset_t(h, h->Af, h->Cf, nullptr, nullptr, -1, 2, s)
-                                             : reset_t(h, h->Ad, h->Cd, nullptr, nullptr, -1, 2, s);
-        if (rc) return rc;
-    }
+    int rc = h->cfg.precision == EXO_F32 ? seed_prime(h, h->Af, h->Cf, s) : seed_prime(h, h->Ad, h->Cd, s);
+    if (rc) return rc;
     CK(cudaStreamSynchronize(s));            // seeds is a host buffer the caller may free
     return 0;
 }
@@ -445,8 +537,8 @@ extern "C" int exo_reset(ExoHandle* h, const uint8_t* mask_dev, float* obs_dev, 
     if (int rc = check_ready(h, "exo_reset")) return rc;
     if (!obs_dev) return fail(EXO_ERR_ARG, "exo_reset: obs_dev is null");
     cudaStream_t s = (cudaStream_t)stream;
-    return h->cfg.precision == EXO_F32 ? reset_t(h, h->Af, h->Cf, mask_dev, obs_dev, -1, 0, s)
-                                       : reset_t(h, h->Ad, h->Cd, mask_dev, obs_dev, -1, 0, s);
+    return h->cfg.precision == EXO_F32 ? reset_t(h, h->Af, h->Cf, mask_dev, obs_dev, s)
+                                       : reset_t(h, h->Ad, h->Cd, mask_dev, obs_dev, s);
 }
 
 template <typename R> static const DynConst<R>& dyn_const(const ExoHandle* h);
@@ -456,9 +548,16 @@ template <> const DynConst<double>& dyn_const<double>(const ExoHandle* h) { retu
 template <typename R>
 static int step_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const float* actions, float* obs, void* reward,
                   uint8_t* done, const ExoInfo* info, cudaStream_t s, int env0 = 0, int env1 = -1) {
-    h->parity ^= 1;
+    const int list = (int)(h->tick++ % EXO_RING);
     StepConst<R> K = step_const<R>(h);
+    K.list = list;
+    K.fused_begin = K.auto_reset && !(K.motor_full && !K.lag);      // (general step without link-state lag: the first observation
+                                                                    //  needs the joint angles the motor kernel is about to produce)
+    static const bool dbg_no_fused = getenv("EXO_DEBUG_NO_FUSED") != nullptr, dbg_no_gen = getenv("EXO_DEBUG_NO_GEN") != nullptr;
+    if (dbg_no_fused) K.fused_begin = 0;                            // timing experiments only
     if (env1 >= 0) { K.env0 = env0; K.env1 = env1; }
+    // this launch clears the counter of ring slot list+1: the generation pass that last consumed it must have finished
+    if (h->gen_ready && h->ev_gen_used[(list + 1) % EXO_RING]) CK(cudaStreamWaitEvent(s, h->ev_gen[(list + 1) % EXO_RING], 0));
     InfoPtrs<R> ip;
     memset(&ip, 0, sizeof(ip));
     const bool want_info = info != nullptr || h->cfg.metrics;
@@ -476,7 +575,17 @@ static int step_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const f
         h->launches += 1;
     }
     CK(cudaGetLastError());
-    if (h->cfg.auto_reset) return reset_t(h, A, C, nullptr, obs, K.parity, 0, s);
+    if (K.auto_reset) {
+        if (!K.fused_begin) {                      // start the finished envs' next episode after the motor kernel
+            ResetConst RK = reset_const(h);
+            RK.list = list;
+            launch_begin<R>(A, C, RK, h->nax, nullptr, obs, s);
+            h->launches += 1;
+            CK(cudaGetLastError());
+        }
+        if (dbg_no_gen) return 0;                  // timing experiments only: the spare slots go stale
+        return gen_list_async<R>(h, A, list, s);   // refill the vacated slots, off the critical path
+    }
     return 0;
 }
 
@@ -572,7 +681,7 @@ extern "C" int exo_field_info(ExoHandle* h, int32_t field, int32_t* k, int32_t* 
     if (!h || !k || !dtype) return fail(EXO_ERR_ARG, "exo_field_info: bad arguments");
     if (!h->have_types) return fail(EXO_ERR_STATE, "exo_field_info: env types not set yet");
     int kk, dd;
-    if (field_shape(h, field, &kk, &dd)) return fail(EXO_ERR_ARG, "exo_field_info: unknown field %d", field);
+    if (field_shape(h, field & ~EXO_FIELD_NEXT, &kk, &dd)) return fail(EXO_ERR_ARG, "exo_field_info: unknown field %d", field);
     *k = kk; *dtype = dd;
     return 0;
 }
@@ -581,14 +690,17 @@ static int field_io(ExoHandle* h, int32_t field, void* buf, int set, void* strea
     if (!h || !buf) return fail(EXO_ERR_ARG, "%s: bad arguments", who);
     if (!h->have_types) return fail(EXO_ERR_STATE, "%s: env types not set yet", who);
     int k, dt;
+    const int next = (field & EXO_FIELD_NEXT) ? 1 : 0;
+    field &= ~EXO_FIELD_NEXT;
     if (field_shape(h, field, &k, &dt)) return fail(EXO_ERR_ARG, "%s: unknown field %d", who, field);
     if (field >= EXO_FIELD_QD && field <= EXO_FIELD_Q_PRIS_LAG && h->cfg.motor_model != EXO_MOTOR_FULL)
         return fail(EXO_ERR_STATE, "%s: field %d exists only with EXO_MOTOR_FULL", who, field);
     CK(cudaSetDevice(h->device));
     cudaStream_t s = (cudaStream_t)stream;
     const int naxv = (h->nax + 3) / 4;
-    if (h->cfg.precision == EXO_F32) launch_field<float>(h->Af, field, k, dt, naxv, buf, set, s);
-    else launch_field<double>(h->Ad, field, k, dt, naxv, buf, set, s);
+    if (int rc = wait_all_gen(h, s)) return rc;          // the spare slots / MT keys may still be being written on the side stream
+    if (h->cfg.precision == EXO_F32) launch_field<float>(h->Af, field, k, dt, naxv, next, buf, set, s);
+    else launch_field<double>(h->Ad, field, k, dt, naxv, next, buf, set, s);
     h->launches += 1;
     CK(cudaGetLastError());
     return 0;
@@ -609,6 +721,20 @@ extern "C" int exo_stats(ExoHandle* h, double* out_dev, int32_t reset, void* str
     CK(cudaMemcpyAsync(out_dev, st, sizeof(double) * EXO_N_STATS, cudaMemcpyDeviceToDevice, s));
     if (reset) CK(cudaMemsetAsync(st, 0, sizeof(double) * EXO_N_STATS, s));
     return 0;
+}
+
+// Debug: per-warp phase timestamps of the next exo_step launches into buf_dev ([ceil(n/32)][8] int64; NULL: off).
+// Word 0 globaltimer (ns) at entry, 1 SM id, 2..7 clock64 at: entry, all loads issued, staged data landed, kinematics +
+// actuators done, reward done, observation rows written.
+extern "C" int exo_debug_timeline(ExoHandle* h, void* buf_dev) {
+    if (!h) return fail(EXO_ERR_ARG, "exo_debug_timeline: null handle");
+    h->timeline = (long long*)buf_dev;
+    return 0;
+}
+
+extern "C" int exo_wait_prefetch(ExoHandle* h, void* stream) {
+    if (int rc = check_ready(h, "exo_wait_prefetch")) return rc;
+    return wait_all_gen(h, (cudaStream_t)stream);
 }
 
 extern "C" int exo_set_auto_reset(ExoHandle* h, int32_t on) {

@@ -1,6 +1,7 @@
 #define REAL double
 // Instantiates the general multibody step (exo_motor.cuh) and the FULL variant of the step kernel for one arithmetic type.
 #include "exo_launch.h"
+#include "exo_reset.cuh"       // begin_episode
 #include "exo_motor.cuh"
 
 namespace exo {

@@ -365,9 +365,13 @@ __host__ __device__ inline size_t reset_smem_per_warp(int table_len) {
 }
 
 
+// ---------------------------------------------------------------------------------------------------------
+// exo_gen_kernel: episode parameters of the NEXT episode of each env of the work list, into the env's spare slot
+// (the slot bit of `counts` names the slot in use). Runs one episode ahead of its consumer, on a side stream.
+// ---------------------------------------------------------------------------------------------------------
 template <typename R, int NAX>
 __global__ void __launch_bounds__(RST_WARPS * 32)
-exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* __restrict__ mask, float* __restrict__ obs) {
+exo_gen_kernel(EnvArrays<R> S, ResetConst K, const uint8_t* __restrict__ mask) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int NAXV = (NAX + 3) / 4;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -381,24 +385,25 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
     uint32_t* key = reinterpret_cast<uint32_t*>(wav);                      // [624] MT key: dead before wav is written
     double* ids = reinterpret_cast<double*>(wsm + reset_region_a(S.table_len));   // [148]
     double* sml = ids + 148;                                               // [160] small per-env scratch
-    // sml layout: 0..13 a1[7],a2[7] | 16..57 shift[42] | 58,59 fmax | 64..75 first three table rows [3][4] | 80..159 obs row (as float)
-    float* s_ob = reinterpret_cast<float*>(sml + 80);
+    // sml layout: 0..13 a1[7],a2[7] | 16..57 shift[42] | 58,59 fmax
 
-    const int total_warps = gridDim.x * RST_WARPS;
-    const int gw = blockIdx.x * RST_WARPS + wid;
+    const int nwarps = blockDim.x >> 5;                                    // 1 .. RST_WARPS warps per block (launcher's choice)
+    const int total_warps = gridDim.x * nwarps;
+    const int gw = blockIdx.x * nwarps + wid;
     const int* list = nullptr;
     int work = S.n;
-    // launched as a programmatic dependent of the step kernel (auto-reset): everything above overlapped its tail;
-    // from here on its writes (work list, state) are visible. A no-op for an ordinary launch.
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-    if (K.list_parity >= 0) { work = S.fin_count[K.list_parity]; list = S.fin_list + (size_t)K.list_parity * st; }
+    if (K.list >= 0) { work = S.fin_count[K.list]; list = S.fin_list + (size_t)K.list * st; }
 
     for (int wi = gw; wi < work; wi += total_warps) {
         const int e = list ? list[wi] : wi;
         if (!list && mask != nullptr && mask[e] == 0) continue;
         const int meta = S.meta[e];
-        const int mid = (meta >> 8) & 0xff;
         const int L = meta >> 16;
+        const int slot = ((S.counts[e] >> EXO_SLOT_SHIFT) & 1) ^ 1;        // the spare slot
+        V4<R>* tt = S.tt + (size_t)slot * S.tt_slot;
+        V4<R>* ep = S.ep + (size_t)slot * S.ep_slot;
+        V4<R>* Gs = S.G + (size_t)slot * S.G_slot;
+        double* IDS = S.IDS + ((size_t)slot * S.n + e) * EXO_IDS_PITCH;
         // ---- 1. MT19937: key -> shared, generate the episode's outputs into the stream
         uint32_t* gkey = S.mt + (size_t)e * EXO_MT_PITCH;
         for (int i = lane; i < MT_N; i += 32) key[i] = gkey[i];
@@ -449,7 +454,7 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
             const double sij = __ddiv_rn(__dadd_rn(nij, nji), 2.0);
             const double v = __dadd_rn(M0[ij], __dmul_rn(sij, M0[ij]));
             ids[idx] = v;
-            S.IDS[(size_t)e * EXO_IDS_PITCH + idx] = v;
+            IDS[idx] = v;
         }
         // ---- actuator end shifts (sim:98-107) and force range scale (:216-217)
         for (int i = lane; i < 42; i += 32) sml[16 + i] = rs_uniform(strm, o_shift + 2 * i, -K.shift_range, K.shift_range);
@@ -496,71 +501,16 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
                 row[j] = (R)v;
             }
 #pragma unroll
-            for (int h = 0; h < NAXV; h++) st4(S.tt + ((size_t)k * st + e) * NAXV + h, row + 4 * h);
-            if (k < 3) {
-#pragma unroll
-                for (int j = 0; j < 4; j++) sml[64 + k * 4 + j] = (double)row[j];
-            }
+            for (int h = 0; h < NAXV; h++) st4(tt + ((size_t)k * st + e) * NAXV + h, row + 4 * h);
         }
         // ---- per-episode parameter record: 42 shifts + 2 force maxima, one 16-byte vector per lane
         if (lane < NV_EP) {
             R pv[4];
 #pragma unroll
             for (int c4 = 0; c4 < 4; c4++) { const int w = lane * 4 + c4; pv[c4] = (R)(w < 42 ? sml[16 + w] : sml[58 + (w - 42)]); }
-            st4(S.ep + (size_t)lane * st + e, pv);
+            st4(ep + (size_t)lane * st + e, pv);
         }
-        if (lane == 0) { S.mag[e] = mag; S.counts[e] = 2; S.ret[e] = R(0); }     // counts = 2 (:220)
-        __syncwarp();
-        // ---- two position reads of the unchanged link-state cache (:230-250) and the first observation (:252);
-        //      every lane evaluates the (identical) chain, lane 0 stores
-        {
-            R qs[5];
-#pragma unroll
-            for (int j = 0; j < 5; j++) qs[j] = *exo_word(S.state, (K.lag ? W_QLAG : W_Q) + j, e, st);
-            ChainPose<R> P;
-            chain_fk(C, qs, P);
-            R el_old[3];
-#pragma unroll
-            for (int k = 0; k < 3; k++) el_old[k] = *exo_word(S.state, W_ELREF + k, e, st);
-            __syncwarp();
-            if (lane < 7) {                                                           // one actuator per lane
-                const int i = lane;
-                R a2[3], off[3];
-#pragma unroll
-                for (int k = 0; k < 3; k++) off[k] = i < 2 ? C.off_alk[i][k] : C.off_hum[i][k];
-                if (K.motor_full) {            // EXO_MOTOR_FULL: the insertion-end dummy may have drifted along its prismatic axis
-                    const R qp = *exo_word(S.dyn, (K.lag ? W_QPLAG : W_QP) + (i < 2 ? 7 + i : i), e, st);
-#pragma unroll
-                    for (int k = 0; k < 3; k++) off[k] += (i < 2 ? C.pax_alk[i][k] : C.pax_hum[i][k]) * qp;
-                }
-                if (i < 2) affine(P.R4, P.p4, off, a2);
-                else affine(P.R2, P.p2, off, a2);
-#pragma unroll
-                for (int k = 0; k < 3; k++) {
-                    a2[k] += (R)sml[16 + (2 * i + 1) * 3 + k];
-                    const R prev = a2[k] - (i < 2 ? el_old[k] : C.sh_ref[k]);      // stale elbow ref on the first read (:237)
-                    const R cur = a2[k] - (i < 2 ? P.elref[k] : C.sh_ref[k]);      // refreshed before the second (:238,249)
-                    *exo_word(S.state, W_POSVEC + i * 3 + k, e, st) = cur;
-                    s_ob[26 + i * 3 + k] = (float)prev; s_ob[47 + i * 3 + k] = (float)cur;
-                }
-            }
-            if (lane < 14) s_ob[lane] = 0.0f;                                         // force history zeroed (:195)
-            if (lane == 0) {
-#pragma unroll
-                for (int k = 0; k < 3; k++) *exo_word(S.state, W_ELREF + k, e, st) = P.elref[k];
-                for (int k = 0; k < 3; k++) {
-                    s_ob[68 + k] = (float)C.sh_ref[k]; s_ob[71 + k] = (float)P.elref[k];
-                    s_ob[74 + k] = (float)C.sh_ref[k]; s_ob[77 + k] = (float)P.elref[k];
-                }
-            }
-            if (lane >= 16 && lane < 28) {                                            // tremor rows 0..2 (:502-513)
-                const int idx = lane - 16;
-                s_ob[14 + idx] = (float)((R)sml[64 + idx] / ((idx & 3) == 3 ? R(5) : R(10)));
-            }
-            __syncwarp();
-            if (obs != nullptr && lane < 20)
-                reinterpret_cast<float4*>(obs + (size_t)e * 80)[lane] = reinterpret_cast<const float4*>(s_ob)[lane];
-        }
+        if (lane == 0) S.mag[(size_t)slot * st + e] = mag;
         __syncwarp();
         // ---- 3. propagator from this episode's I, D, S on the fp64 tensor cores; scratch aliases region A (dead by now)
         {
@@ -568,11 +518,125 @@ exo_reset_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* _
             warp_propagator(ids, scratch, K.dt, lane, f);
             const int row = lane >> 2, col = (lane & 3) * 2;               // rows 0..6 of F are in the first row tile
             if (row < 7) {
-                *exo_word(S.G, exo_g_word(row, col), e, st) = (R)f[0];
-                if (col + 1 < 7) *exo_word(S.G, exo_g_word(row, col + 1), e, st) = (R)f[1];
+                *exo_word(Gs, exo_g_word(row, col), e, st) = (R)f[0];
+                if (col + 1 < 7) *exo_word(Gs, exo_g_word(row, col + 1), e, st) = (R)f[1];
             }
         }
         __syncwarp();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Beginning of an episode on already generated parameters (Exoskeleton_env.py:220-252): flip to the spare slot,
+// counts = 2, the two position reads of the unchanged link-state cache (:230-250) and the first observation (:252).
+// One thread per env; shared by exo_begin_kernel (explicit reset()) and the step kernel's auto-reset path, which
+// passes the joint vector / elbow reference it already holds and a staging tile for the observation.
+//   qs[5]   joint vector behind the link-state cache at this moment;  el_old  act_elbow_reference_positions as last read
+//   qpl     EXO_MOTOR_FULL: prismatic positions behind the cache (else nullptr)
+//   obA/obB the 80-float observation as 20 float4 chunks: chunks 0..10 -> obA[0..10], chunks 11..19 -> obB[0..8]
+// ---------------------------------------------------------------------------------------------------------
+template <typename R, int NAX>
+__device__ __forceinline__ void begin_episode(const EnvArrays<R>& S, const ChainConst<R>& C, int e, int new_slot,
+                                           const R* qs, const R* el_old, const R* qpl, float4* obA, float4* obB) {
+    constexpr int NAXV = (NAX + 3) / 4;
+    const int st = S.stride;
+    const V4<R>* ep = S.ep + (size_t)new_slot * S.ep_slot;
+    const V4<R>* tt = S.tt + (size_t)new_slot * S.tt_slot;
+    // every global load of this path is issued before the first use (the 11 parameter vectors and the three tremor rows
+    // fly while the chain is evaluated), and every store comes after the last load: with loads interleaved between the
+    // stores the 21 shift reads were 21 exposed memory latencies (~10 us on the step's critical path, r02g)
+    R sh[4 * NV_EP], rows[3][4];
+#pragma unroll
+    for (int v = 0; v < NV_EP; v++) ld4_ord(ep + (size_t)v * st + e, sh + 4 * v);
+#pragma unroll
+    for (int k = 0; k < 3; k++) ld4_ord(tt + ((size_t)k * st + e) * NAXV, rows[k]);
+    float ob[80];
+    ChainPose<R> P;
+    chain_fk(C, qs, P);
+#pragma unroll
+    for (int i = 0; i < 14; i++) ob[i] = 0.0f;                                        // force history zeroed (:195)
+#pragma unroll
+    for (int k = 0; k < 3; k++)                                                       // tremor rows 0..2 (:502-513)
+#pragma unroll
+        for (int j = 0; j < 4; j++) ob[14 + k * 4 + j] = (float)(rows[k][j] / (j == 3 ? R(5) : R(10)));
+    R pv[21];
+#pragma unroll
+    for (int i = 0; i < 7; i++) {
+        R a2[3], off[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) off[k] = i < 2 ? C.off_alk[i][k] : C.off_hum[i][k];
+        if (qpl != nullptr) {                  // EXO_MOTOR_FULL: the insertion-end dummy may have drifted along its prismatic axis
+            const R qp = qpl[i < 2 ? 7 + i : i];
+#pragma unroll
+            for (int k = 0; k < 3; k++) off[k] += (i < 2 ? C.pax_alk[i][k] : C.pax_hum[i][k]) * qp;
+        }
+        if (i < 2) affine(P.R4, P.p4, off, a2);
+        else affine(P.R2, P.p2, off, a2);
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            a2[k] += sh[W_SHIFT + (2 * i + 1) * 3 + k];
+            const R prev = a2[k] - (i < 2 ? el_old[k] : C.sh_ref[k]);      // stale elbow ref on the first read (:237)
+            const R cur = a2[k] - (i < 2 ? P.elref[k] : C.sh_ref[k]);      // refreshed before the second (:238,249)
+            pv[i * 3 + k] = cur;
+            ob[26 + i * 3 + k] = (float)prev; ob[47 + i * 3 + k] = (float)cur;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        ob[68 + k] = (float)C.sh_ref[k]; ob[71 + k] = (float)P.elref[k];
+        ob[74 + k] = (float)C.sh_ref[k]; ob[77 + k] = (float)P.elref[k];
+    }
+#pragma unroll
+    for (int w = 0; w < 21; w++) *exo_word(S.state, W_POSVEC + w, e, st) = pv[w];
+#pragma unroll
+    for (int k = 0; k < 3; k++) *exo_word(S.state, W_ELREF + k, e, st) = P.elref[k];
+    S.counts[e] = 2 | (new_slot << EXO_SLOT_SHIFT);                                   // counts = 2 (:220)
+    S.ret[e] = R(0);
+#pragma unroll
+    for (int ch = 0; ch < 11; ch++) obA[ch] = make_float4(ob[4 * ch], ob[4 * ch + 1], ob[4 * ch + 2], ob[4 * ch + 3]);
+#pragma unroll
+    for (int ch = 11; ch < 20; ch++) obB[ch - 11] = make_float4(ob[4 * ch], ob[4 * ch + 1], ob[4 * ch + 2], ob[4 * ch + 3]);
+}
+
+// explicit env.reset() (mask / all), or the envs of a work list (auto-reset when the flip cannot be fused into the step)
+template <typename R, int NAX>
+__global__ void __launch_bounds__(64)
+exo_begin_kernel(EnvArrays<R> S, ChainConst<R> C, ResetConst K, const uint8_t* __restrict__ mask, float* __restrict__ obs) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x, st = S.stride;
+    const int lane = threadIdx.x & 31;
+    int e = idx;
+    bool act;
+    if (K.list >= 0) { act = idx < S.fin_count[K.list]; if (act) e = S.fin_list[(size_t)K.list * st + idx]; }
+    else act = idx < S.n && (mask == nullptr || mask[idx] != 0);
+    if (act) {
+        const int new_slot = ((S.counts[e] >> EXO_SLOT_SHIFT) & 1) ^ 1;
+        R qs[5], el_old[3], qpl[EXO_NPRIS];
+#pragma unroll
+        for (int j = 0; j < 5; j++) qs[j] = *exo_word(S.state, (K.lag ? W_QLAG : W_Q) + j, e, st);
+#pragma unroll
+        for (int k = 0; k < 3; k++) el_old[k] = *exo_word(S.state, W_ELREF + k, e, st);
+        if (K.motor_full) {
+#pragma unroll
+            for (int d = 0; d < EXO_NPRIS; d++) qpl[d] = *exo_word(S.dyn, (K.lag ? W_QPLAG : W_QP) + d, e, st);
+        }
+        float4 oa[11], obb[9];
+        begin_episode<R, NAX>(S, C, e, new_slot, qs, el_old, K.motor_full ? qpl : nullptr, oa, obb);
+        if (obs != nullptr) {
+            float4* dst = reinterpret_cast<float4*>(obs + (size_t)e * 80);
+#pragma unroll
+            for (int ch = 0; ch < 11; ch++) dst[ch] = oa[ch];
+#pragma unroll
+            for (int ch = 0; ch < 9; ch++) dst[11 + ch] = obb[ch];
+        }
+    }
+    if (K.append >= 0) {                       // the envs started here need their (new) spare slot refilled
+        const unsigned m = __ballot_sync(0xffffffffu, act);
+        if (m) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(S.fin_count + K.append, __popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (act) S.fin_list[(size_t)K.append * st + base + __popc(m & ((1u << lane) - 1u))] = e;
+        }
     }
 }
 

@@ -1,46 +1,53 @@
 #define REAL float
 #define EXO_WITH_SEED 1
 // Instantiates the reset kernel for one arithmetic type (see exo_reset.cuh).
+#include <stdlib.h>
 #include "exo_launch.h"
 #include "exo_reset.cuh"
 
 namespace exo {
 template <typename R, int NAX>
-static int launch_reset_nax(const EnvArrays<R>& A, const ChainConst<R>& C, const ResetConst& K, int n_sm,
-                            const uint8_t* mask, float* obs, cudaStream_t s) {
+static int launch_gen_nax(const EnvArrays<R>& A, const ResetConst& K, int n_sm, const uint8_t* mask, cudaStream_t s) {
     const size_t smem = RST_WARPS * reset_smem_per_warp(A.table_len);
     static size_t configured[64] = {0};           // per device: the attribute belongs to the device's copy of the kernel
     int dev = 0;
     cudaGetDevice(&dev);
     if (smem > configured[dev & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(exo_reset_kernel<R, NAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(exo_gen_kernel<R, NAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return (int)e;
         configured[dev & 63] = smem;
     }
-    // persistent-style grid: as many blocks as fit (shared memory bound), each warp strides over the work list
+    // persistent-style grid: as many blocks as fit (shared memory bound), each warp strides over the work list.
+    // Work-list passes run BESIDE the step kernel (side stream): one-warp blocks (4 k registers, 12.5 KB of shared memory)
+    // slot into the space the step kernel's 7 blocks per SM leave free, so the step stays a single wave; a four-warp block
+    // would take the place of one step block on its SM and push that block into a second wave.
+    int warps = K.list >= 0 ? 1 : RST_WARPS;
+    if (const char* e = getenv("EXO_GEN_WARPS")) { const int w = atoi(e); if (w >= 1 && w <= RST_WARPS) warps = w; }
     int per_sm = (int)((227 * 1024) / (smem + 1024));
     if (per_sm < 1) per_sm = 1;
     if (per_sm > 4) per_sm = 4;
-    int grid = n_sm * per_sm;
-    if (K.list_parity < 0) { const int need = (A.n + RST_WARPS - 1) / RST_WARPS; if (need < grid) grid = need; }
-    // Auto-reset launches follow the step kernel in the same stream: programmatic dependent launch lets this grid be
-    // scheduled while the step kernel drains (it signals at its start); the kernel waits with griddepcontrol.wait
-    // before it touches the work list, so an empty list costs almost nothing on the device timeline.
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(RST_WARPS * 32); cfg.dynamicSmemBytes = smem; cfg.stream = s;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr; cfg.numAttrs = (K.list_parity >= 0 && !K.motor_full) ? 1 : 0;   // FULL: the motor kernel sits between
-    return (int)cudaLaunchKernelEx(&cfg, exo_reset_kernel<R, NAX>, A, C, K, mask, obs);
+    int grid = n_sm * per_sm * (RST_WARPS / warps);
+    if (K.list < 0) { const int need = (A.n + warps - 1) / warps; if (need < grid) grid = need; }
+    else {
+        grid = n_sm * 2;                          // a work list holds ~n / 280 envs at steady state; two one-warp blocks per SM walk it
+        if (const char* e = getenv("EXO_GEN_GRID")) { const int g = atoi(e); if (g >= 1) grid = g; }
+    }
+    exo_gen_kernel<R, NAX><<<grid, warps * 32, (size_t)warps * reset_smem_per_warp(A.table_len), s>>>(A, K, mask);
+    return (int)cudaGetLastError();
 }
 template <typename R>
-int launch_reset(const EnvArrays<R>& A, const ChainConst<R>& C, const ResetConst& K, int nax, int n_sm,
-                 const uint8_t* mask, float* obs, cudaStream_t s) {
-    return nax == 4 ? launch_reset_nax<R, 4>(A, C, K, n_sm, mask, obs, s) : launch_reset_nax<R, 7>(A, C, K, n_sm, mask, obs, s);
+int launch_gen(const EnvArrays<R>& A, const ResetConst& K, int nax, int n_sm, const uint8_t* mask, cudaStream_t s) {
+    return nax == 4 ? launch_gen_nax<R, 4>(A, K, n_sm, mask, s) : launch_gen_nax<R, 7>(A, K, n_sm, mask, s);
 }
-template int launch_reset<REAL>(const EnvArrays<REAL>&, const ChainConst<REAL>&, const ResetConst&, int, int, const uint8_t*,
-                                float*, cudaStream_t);
+template <typename R>
+void launch_begin(const EnvArrays<R>& A, const ChainConst<R>& C, const ResetConst& K, int nax, const uint8_t* mask, float* obs,
+                  cudaStream_t s) {
+    const int grid = (A.n + 63) / 64;             // list mode: threads past the list length idle
+    if (nax == 4) exo_begin_kernel<R, 4><<<grid, 64, 0, s>>>(A, C, K, mask, obs);
+    else exo_begin_kernel<R, 7><<<grid, 64, 0, s>>>(A, C, K, mask, obs);
+}
+template int launch_gen<REAL>(const EnvArrays<REAL>&, const ResetConst&, int, int, const uint8_t*, cudaStream_t);
+template void launch_begin<REAL>(const EnvArrays<REAL>&, const ChainConst<REAL>&, const ResetConst&, int, const uint8_t*, float*, cudaStream_t);
 #ifdef EXO_WITH_SEED
 void launch_seed(uint32_t* mt, int n, const uint32_t* seeds, cudaStream_t s) {
     exo_seed_kernel<<<(n + 31) / 32, 32, 0, s>>>(mt, n, seeds);

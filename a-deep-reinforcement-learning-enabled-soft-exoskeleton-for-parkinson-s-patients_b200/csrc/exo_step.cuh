@@ -15,11 +15,34 @@
 // shared memory (no block barrier: STS.128 into a 21-chunk pitch, LDS.128 + STG.128 out), and the fp32 build
 // uses MUFU-based reciprocal / rsqrt / exp where the stated tolerances allow.
 #pragma once
+#include <type_traits>
 #include "exo_types.cuh"
 
 namespace exo {
 
-__device__ __forceinline__ void sincos_r(float x, float* s, float* c) { sincosf(x, s, c); }
+// sin and cos of a joint angle, fp32. Joint angles live inside the URDF limits (|q| < 2.9 rad), so the argument reduction is
+// three Cody-Waite steps by pi/2 (exact for |k| < 2^7) and the kernels are the degree-7 / degree-8 minimax polynomials on
+// [-pi/4, pi/4] (< 1 ulp each): ~28 instructions for the pair against ~78 for sincosf, whose generality (Payne-Hanek path,
+// local-memory table) the 5 evaluations per env-step paid for - 20 % of the step kernel's instructions in the r02e profile.
+// Larger arguments (a diverging env) take the library path.
+__device__ __forceinline__ void sincos_r(float x, float* s, float* c) {
+    if (fabsf(x) > 100.0f) { sincosf(x, s, c); return; }
+    const float k = rintf(x * 0.63661977236758134308f);
+    float r = fmaf(-k, 1.5707962512969970703125f, x);               // pi/2 split in three: 24 + 24 + 24 bits
+    r = fmaf(-k, 7.5497894158615963533520698547e-8f, r);
+    r = fmaf(-k, 5.3903029534742383e-15f, r);
+    const float r2 = r * r;
+    float ps = fmaf(r2, -1.9515295891e-4f, 8.3321608736e-3f);
+    ps = fmaf(ps, r2, -1.6666654611e-1f);
+    const float sn = fmaf(ps * r2, r, r);
+    float pc = fmaf(r2, 2.443315711809948e-5f, -1.388731625493765e-3f);
+    pc = fmaf(pc, r2, 4.166664568298827e-2f);
+    const float cs = fmaf(pc * r2, r2, fmaf(-0.5f, r2, 1.0f));
+    const int q = (int)k;
+    const float a = (q & 1) ? cs : sn, b = (q & 1) ? sn : cs;
+    *s = (q & 2) ? -a : a;
+    *c = ((q + 1) & 2) ? -b : b;
+}
 __device__ __forceinline__ void sincos_r(double x, double* s, double* c) { sincos(x, s, c); }
 __device__ __forceinline__ float exp_r(float x) { return __expf(x); }
 __device__ __forceinline__ double exp_r(double x) { return exp(x); }
@@ -167,6 +190,11 @@ __device__ __forceinline__ void dh_end_effector(const R* th, R L1, R L2, R* p) {
     }
 }
 
+// defined in exo_reset.cuh: start the prefetched episode of env e (slot flip, counts = 2, position reads, first observation)
+template <typename R, int NAX>
+__device__ __forceinline__ void begin_episode(const EnvArrays<R>& S, const ChainConst<R>& C, int e, int new_slot,
+                                           const R* qs, const R* el_old, const R* qpl, float4* obA, float4* obB);
+
 // FULL: ExoConfig.motor_model = EXO_MOTOR_FULL - the position targets go to exo_motor_kernel (exo_motor.cuh) instead of the
 // closed-form tracker, and the actuator end points follow their prismatic dummies (which the general step lets drift).
 template <typename R, bool INFO, int NAX, bool FULL = false>
@@ -186,27 +214,43 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
     const int wbase = K.env0 + blockIdx.x * EXO_STEP_THREADS + wid * 32;     // first env of this warp
     const int e = wbase + lane;
     const int n = K.env1, st = S.stride;                            // this launch covers envs [K.env0, K.env1)
-    asm volatile("griddepcontrol.launch_dependents;");               // the auto-reset kernel may be scheduled behind this grid
-    if (blockIdx.x == 0 && tid == 0) S.fin_count[K.parity ^ 1] = 0;  // consumed by the previous step's reset
+    if (blockIdx.x == 0 && tid == 0) S.fin_count[(K.list + 1) % EXO_RING] = 0;   // the next call's list (its last
+                                                                     // consumer finished: the host waited for that generation pass)
     if (wbase >= n) return;                                          // whole warp past the end
+    long long* tl = nullptr;
+    if (K.timeline != nullptr) {
+        tl = K.timeline + (size_t)((wbase - K.env0) >> 5) * 8;
+        if (lane == 0) {
+            unsigned long long gt; unsigned smid;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            tl[0] = (long long)gt; tl[1] = smid; tl[2] = clock64();
+        }
+    }
+#define EXO_MARK(k) do { if (tl != nullptr && lane == 0) tl[k] = clock64(); } while (0)
+    if (K.stagger_cycles > 0) {
+        // The launch is one wave whose warps would all issue their ~30 vector loads at once; the memory system then serves
+        // them roughly first-come first-served ACROSS warps, so every warp's last vector arrives when the whole 34 MB burst
+        // has been served (~5 us at the HBM rate) and no warp computes before that. Starting the blocks of later dispatch
+        // layers a little later gives the early layers their data first: they compute while the rest of the burst streams.
+        const int layer = blockIdx.x / K.n_sm;
+        if (layer > 0) {
+            const long long t0 = clock64(), wait = (long long)layer * K.stagger_cycles;
+            while (clock64() - t0 < wait) __nanosleep(64);
+        }
+    }
 
     // ---- every global access of the step is issued up front, in this order and unconditionally (a lane past the end
     //      or an idle env re-reads a valid record and discards it): counts/meta first (the second-level addresses
-    //      depend on them), then the per-episode parameters and the action rows as asynchronous global->shared copies
-    //      (no registers), then state and G as 128-bit register loads, then - one memory latency later - the three
-    //      tremor rows and the motion row addressed by counts.
+    //      depend on them: counts carries the step index AND which of the two parameter slots holds the running
+    //      episode), the action rows as asynchronous global->shared copies, the carried state as 128-bit register
+    //      loads, then - one memory latency later - the per-episode parameters (async copies), G, the three tremor rows
+    //      and the motion row.
     const bool valid = e < n;
     const int ec = valid ? e : n - 1;
-    const int c_raw = ld_int_ord(S.counts + ec);
+    const int c_word = ld_int_ord(S.counts + ec);
     const int meta = ld_int_ord(S.meta + ec);
     V4<R>* sp = reinterpret_cast<V4<R>*>(&s_epB[wid][0]);            // [NV_EP][32]
-#pragma unroll
-    for (int v = 0; v < NV_EP; v++) {
-        const char* src = reinterpret_cast<const char*>(S.ep + (size_t)v * st + ec);
-        char* dst = reinterpret_cast<char*>(sp + v * 32 + lane);
-#pragma unroll
-        for (int h = 0; h < (int)sizeof(V4<R>) / 16; h++) cp_async16(dst + 16 * h, src + 16 * h);
-    }
     const int rows_here = min(32, n - wbase);
     const float* asrc = actions + (size_t)wbase * 7;
     const bool act_async = rows_here == 32 && (reinterpret_cast<size_t>(asrc) & 15) == 0;   // warp-uniform
@@ -222,21 +266,39 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
     R s[4 * NV_STATE];
 #pragma unroll
     for (int v = 0; v < NV_STATE; v++) ld4_ord(S.state + (size_t)v * st + ec, s + 4 * v);
-    constexpr int NGV = (INFO || NAX > 4) ? NV_G : 4;
-    R g[4 * NGV];
-#pragma unroll
-    for (int v = 0; v < NGV; v++) ld4_ro_ord(S.G + (size_t)v * st + ec, g + 4 * v);
     const R ret0 = S.ret[ec];
     // second level (clamped so the addresses are always inside the tables; a live env has 2 <= counts <= L - 2, so
     // the clamp never changes what a live env reads)
+    const int c_raw = c_word & EXO_COUNT_MASK, slot = (c_word >> EXO_SLOT_SHIFT) & 1;
     const int mid = (meta >> 8) & 0xff, L = meta >> 16;
     const int c = min(max(c_raw, 1), S.table_len - 2);
-    R tm[4 * NAXV], tc[4 * NAXV], tp[4 * NAXV];                       // tremor rows c-1, c, c+1
+    {
+        const V4<R>* eps = S.ep + (size_t)slot * S.ep_slot;
 #pragma unroll
-    for (int h = 0; h < NAXV; h++) {
-        ld4_ro_ord(S.tt + ((size_t)(c - 1) * st + ec) * NAXV + h, tm + 4 * h);
-        ld4_ro_ord(S.tt + ((size_t)c * st + ec) * NAXV + h, tc + 4 * h);
-        ld4_ro_ord(S.tt + ((size_t)(c + 1) * st + ec) * NAXV + h, tp + 4 * h);
+        for (int v = 0; v < NV_EP; v++) {
+            const char* src = reinterpret_cast<const char*>(eps + (size_t)v * st + ec);
+            char* dst = reinterpret_cast<char*>(sp + v * 32 + lane);
+#pragma unroll
+            for (int h = 0; h < (int)sizeof(V4<R>) / 16; h++) cp_async16(dst + 16 * h, src + 16 * h);
+        }
+        cp_async_commit();
+    }
+    constexpr int NGV = (INFO || NAX > 4) ? NV_G : 4;
+    R g[4 * NGV];
+    {
+        const V4<R>* Gs = S.G + (size_t)slot * S.G_slot;
+#pragma unroll
+        for (int v = 0; v < NGV; v++) ld4_ro_ord(Gs + (size_t)v * st + ec, g + 4 * v);
+    }
+    R tm[4 * NAXV], tc[4 * NAXV], tp[4 * NAXV];                       // tremor rows c-1, c, c+1
+    {
+        const V4<R>* tts = S.tt + (size_t)slot * S.tt_slot;
+#pragma unroll
+        for (int h = 0; h < NAXV; h++) {
+            ld4_ro_ord(tts + ((size_t)(c - 1) * st + ec) * NAXV + h, tm + 4 * h);
+            ld4_ro_ord(tts + ((size_t)c * st + ec) * NAXV + h, tc + 4 * h);
+            ld4_ro_ord(tts + ((size_t)(c + 1) * st + ec) * NAXV + h, tp + 4 * h);
+        }
     }
     const R* mo = S.motion + (size_t)mid * 5 * S.max_len;
     R mrow[5], mnext[5];
@@ -245,15 +307,18 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
         mrow[r] = ld_ro_ord(mo + r * S.max_len + c);
         mnext[r] = INFO ? ld_ro_ord(mo + r * S.max_len + c + 1) : R(0);
     }
+    EXO_MARK(3);                                                     // every load issued, counts arrived
     if (!act_async) {
 #pragma unroll
         for (int k = 0; k < 7; k++) s_act[wid][lane + 32 * k] = araw[k];
     }
     cp_async_wait_all();
     __syncwarp();
+    EXO_MARK(4);                                                     // staged parameters + actions landed
 
     const bool live = valid && c_raw < L - 1;   // an env that already reported done idles (Exoskeleton_agent_train.py:139)
     bool fin = false;
+    R b_qs[5], b_el[3];                         // auto-reset: joint vector behind the link-state cache / elbow reference after this step
     int v_cross = 0, v_red = 0, v_len = 0;
     R v_ret = 0, v_amp = 0;
     int v_cge = 0, v_clt = 0, v_ntr = 0, v_nam = 0;      // training-script suppression metrics (INFO mode only)
@@ -324,11 +389,12 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
         // new pos_vec -> obs[47:68]
         // ---- per actuator: endpoints, force direction, pos_vec, torque (sim:207-336, env:177-187)
         R at0 = 0, at1 = 0, at2 = 0, ty0 = 0, ty1 = 0;
-        const int order[7] = {0, 1, 2, 3, 4, 6, 5};          // summation order of :395-397 (3,4,5,7,6)
-        const int fix_of[7] = {-1, -1, 0, 1, 2, 3, 4};       // fixed slot of act_i1 for the shoulder actuators
-#pragma unroll
-        for (int oi = 0; oi < 7; oi++) {
-            const int i = order[oi];
+        // one instantiation per actuator (compile-time index: every array subscript below is static - the loop over a
+        // run-time order[] table left the shift selects as local-memory accesses), called in the summation order of
+        // :395-397 (3,4,5,7,6)
+        auto actuator = [&](auto IC) {
+            constexpr int i = decltype(IC)::value;
+            constexpr int fix_slot = i - 2;                  // fixed slot of act_i1 for the shoulder actuators
             R a1[3], a2[3];
             if (i < 2) {
                 if (FULL) {
@@ -342,7 +408,7 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
                     affine(P.R4, P.p4, C.off_alk[i], a2);               // act12 / act22 ride on the forearm
                 }
             } else {
-                a1[0] = C.fixed[fix_of[i]][0]; a1[1] = C.fixed[fix_of[i]][1]; a1[2] = C.fixed[fix_of[i]][2];
+                a1[0] = C.fixed[fix_slot < 0 ? 0 : fix_slot][0]; a1[1] = C.fixed[fix_slot < 0 ? 0 : fix_slot][1]; a1[2] = C.fixed[fix_slot < 0 ? 0 : fix_slot][2];
                 if (FULL) {
                     R oh[3];
 #pragma unroll
@@ -352,7 +418,7 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
             }
             {   // dummy_shift_coordinates of this actuator's two ends: words 6i..6i+5 of the staged record = two vectors
                 constexpr int W0 = W_SHIFT;
-                const int w = W0 + 6 * i, va = w >> 2;
+                constexpr int w = W0 + 6 * i, va = w >> 2;
                 R pa[4], pb[4];
                 ld4(sp + va * 32 + lane, pa);
                 ld4(sp + (va + 1) * 32 + lane, pb);
@@ -386,8 +452,13 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
             if (i == 0) ty0 = ty;
             else if (i == 1) ty1 = ty;
             else { at0 += ty; at1 += tx; at2 += tz; }
-        }
+        };
+        actuator(std::integral_constant<int, 0>{}); actuator(std::integral_constant<int, 1>{});
+        actuator(std::integral_constant<int, 2>{}); actuator(std::integral_constant<int, 3>{});
+        actuator(std::integral_constant<int, 4>{}); actuator(std::integral_constant<int, 6>{});
+        actuator(std::integral_constant<int, 5>{});
         const R at[4] = {at0, at1, at2, abs_r(ty0) - abs_r(ty1)};      // :394-400
+        EXO_MARK(5);                                                   // kinematics + actuators done
         // ---- tremor lookup (:403-406) and the rows the observation needs (:502-513)
         R ttc[7], tv[7];
 #pragma unroll
@@ -433,7 +504,9 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
             if (K.lag) s[W_QLAG + j] = qb[j];
         }
 #pragma unroll
-        for (int k = 0; k < 3; k++) s[W_ELREF + k] = P.elref[k];
+        for (int k = 0; k < 3; k++) { s[W_ELREF + k] = P.elref[k]; b_el[k] = P.elref[k]; }
+#pragma unroll
+        for (int j = 0; j < 5; j++) b_qs[j] = K.lag ? qb[j] : s[W_Q + j];
         // ---- reward (:268-366)
         const R eps = R(1e-10);
         const R m = fm_el + fm_sh;
@@ -470,12 +543,13 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
         const R max_reward = nf * R(0.5) + R(0.9) + R(0.05) + R(0.05) + R(0.5);
         const R rew = div_r(r_axis + r_tor + r_smo + r_ctl + r_unw, max_reward);
         reward[e] = rew;
+        EXO_MARK(6);                                                   // reward done
         // ---- write the carried state back
 #pragma unroll
         for (int v = 0; v < NV_STATE; v++) st4(S.state + (size_t)v * st + e, s + 4 * v);
         // ---- counts, observation head, done (:448-457)
         const int k1 = c + 1;
-        S.counts[e] = k1;
+        S.counts[e] = k1 | (slot << EXO_SLOT_SHIFT);
 #pragma unroll
         for (int k = 0; k < 3; k++) {
             ob[68 + k] = (float)C.sh_ref[k]; ob[71 + k] = (float)el_old[k];     // ref_prev (:383)
@@ -538,6 +612,19 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
         if (dn) { v_len = k1 - 2; v_ret = ret; }
         if (INFO && amp < R(0)) v_amp = amp;
     }
+    // ---- auto-reset: an env whose episode just ended starts its next one HERE - the parameters were generated one episode
+    //      ahead into its spare slot (exo_gen_kernel on the side stream), so this is a slot flip, counts = 2, the position
+    //      reads of Exoskeleton_env.py:230-250 and the first observation (:252), which replaces the env's row in the staging
+    //      tiles. Nothing on the step's critical path waits for a random draw.
+    if (K.fused_begin && fin) {
+        R qplb[EXO_NPRIS];
+        if (FULL) {
+#pragma unroll
+            for (int d = 0; d < EXO_NPRIS; d++) qplb[d] = *exo_word(S.dyn, W_QP + d, e, st);
+        }
+        begin_episode<R, NAX>(S, C, e, slot ^ 1, b_qs, b_el, FULL ? qplb : nullptr, &s_obsA[wid][lane * 11],
+                              reinterpret_cast<float4*>(&s_epB[wid][0]) + lane * 9);
+    }
     // ---- warp-level epilogue: every lane of the warp arrives here
     const unsigned fin_mask = __ballot_sync(full, fin);
     if (live_mask == 0) return;
@@ -561,13 +648,14 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
             if ((live_mask >> row) & 1u) dst[row * 20 + 11 + ch] = srcB[v];
         }
     }
-    // finished envs -> the auto-reset work list (one atomic per warp that has any)
+    // finished envs -> this call's work list (one atomic per warp that has any): their vacated slot gets the episode after next
     if (K.auto_reset && fin_mask) {
         int base = 0;
-        if (lane == 0) base = atomicAdd(S.fin_count + K.parity, __popc(fin_mask));
+        if (lane == 0) base = atomicAdd(S.fin_count + K.list, __popc(fin_mask));
         base = __shfl_sync(full, base, 0);
-        if (fin) S.fin_list[(size_t)K.parity * st + base + __popc(fin_mask & ((1u << lane) - 1u))] = e;
+        if (fin) S.fin_list[(size_t)K.list * st + base + __popc(fin_mask & ((1u << lane) - 1u))] = e;
     }
+    EXO_MARK(7);                                                     // observation rows written
     // statistics: integer counters by warp-reduce, the real-valued ones only in warps where an episode ended
     {
         const int n_live = __popc(live_mask);
@@ -619,11 +707,13 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
 // ---------------------------------------------------------------------------------------------------------
 // exo_get_field / exo_set_field: gather/scatter between the resident layout and env-major [n, k] buffers.
 // ---------------------------------------------------------------------------------------------------------
+// `next` != 0 addresses the prefetched (spare) slot of the per-episode fields instead of the one in use.
 template <typename R, typename T, bool SET>
-__global__ void exo_field_kernel(EnvArrays<R> S, int field, int k, int naxv, T* __restrict__ buf) {
+__global__ void exo_field_kernel(EnvArrays<R> S, int field, int k, int naxv, int next, T* __restrict__ buf) {
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (size_t)S.n * k) return;
     const int e = (int)(idx / k), i = (int)(idx - (size_t)e * k), st = S.stride;
+    const int slot = ((S.counts[e] >> EXO_SLOT_SHIFT) & 1) ^ (next ? 1 : 0);
     T* a = nullptr;
     switch (field) {
         case F_Q: a = (T*)exo_word(S.state, W_Q + i, e, st); break;
@@ -632,17 +722,20 @@ __global__ void exo_field_kernel(EnvArrays<R> S, int field, int k, int naxv, T* 
         case F_ELBOW_REF: a = (T*)exo_word(S.state, W_ELREF + i, e, st); break;
         case F_PREV_ACTION: a = (T*)exo_word(S.state, W_FPREV + i, e, st); break;
         case F_PREV_ACTION2: a = (T*)exo_word(S.state, W_FPREV2 + i, e, st); break;
-        case F_FORCE_MAX: a = (T*)exo_word(S.ep, W_FMAX + i, e, st); break;
-        case F_SHIFT: a = (T*)exo_word(S.ep, W_SHIFT + i, e, st); break;
-        case F_G: a = (T*)exo_word(S.G, exo_g_word(i / 7, i % 7), e, st); break;
-        case F_IDS: a = (T*)(S.IDS + (size_t)e * EXO_IDS_PITCH + i); break;
+        case F_FORCE_MAX: a = (T*)exo_word(S.ep + (size_t)slot * S.ep_slot, W_FMAX + i, e, st); break;
+        case F_SHIFT: a = (T*)exo_word(S.ep + (size_t)slot * S.ep_slot, W_SHIFT + i, e, st); break;
+        case F_G: a = (T*)exo_word(S.G + (size_t)slot * S.G_slot, exo_g_word(i / 7, i % 7), e, st); break;
+        case F_IDS: a = (T*)(S.IDS + ((size_t)slot * S.n + e) * EXO_IDS_PITCH + i); break;
         case F_TREMOR_TABLE: {
             const int nax = k / S.table_len, row = i / nax, j = i - row * nax;
-            a = (T*)&S.tt[((size_t)row * st + e) * naxv + (j >> 2)].v[j & 3];
+            a = (T*)&(S.tt + (size_t)slot * S.tt_slot)[((size_t)row * st + e) * naxv + (j >> 2)].v[j & 3];
             break;
         }
-        case F_TREMOR_MAG: a = (T*)(S.mag + e); break;
-        case F_COUNTS: a = (T*)(S.counts + e); break;
+        case F_TREMOR_MAG: a = (T*)(S.mag + (size_t)slot * st + e); break;
+        case F_COUNTS:                                                  // the slot bit is private: masked on get, kept on set
+            if (SET) S.counts[e] = ((int)buf[idx] & EXO_COUNT_MASK) | (S.counts[e] & ~EXO_COUNT_MASK);
+            else buf[idx] = (T)(S.counts[e] & EXO_COUNT_MASK);
+            return;
         case F_META: a = (T*)(S.meta + e); break;
         case F_MT_STATE: a = (T*)(S.mt + (size_t)e * EXO_MT_PITCH + i); break;
         case F_EP_RETURN: a = (T*)(S.ret + e); break;

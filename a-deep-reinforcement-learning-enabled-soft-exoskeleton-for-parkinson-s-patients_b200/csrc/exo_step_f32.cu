@@ -1,7 +1,7 @@
 #define REAL float
 // Instantiates the step kernel for one arithmetic type (see exo_step.cuh).
 #include "exo_launch.h"
-#include "exo_step.cuh"
+#include "exo_reset.cuh"       // begin_episode (the auto-reset path of the step kernel) + exo_step.cuh
 
 namespace exo {
 template <typename R>
@@ -32,13 +32,13 @@ void launch_fk(const R* theta, R* p, int n, R L1, R L2, cudaStream_t s) {
     exo_fk_kernel<R><<<(n + 127) / 128, 128, 0, s>>>(theta, p, n, L1, L2);
 }
 template <typename R>
-void launch_field(const EnvArrays<R>& A, int field, int k, int dtype, int naxv, void* buf, int set, cudaStream_t s) {
+void launch_field(const EnvArrays<R>& A, int field, int k, int dtype, int naxv, int next, void* buf, int set, cudaStream_t s) {
     const size_t total = (size_t)A.n * k;
     const int grid = (int)((total + 255) / 256);
 #define EXO_FIELD_GO(T)                                                                                  \
     do {                                                                                                 \
-        if (set) exo_field_kernel<R, T, true><<<grid, 256, 0, s>>>(A, field, k, naxv, (T*)buf);          \
-        else exo_field_kernel<R, T, false><<<grid, 256, 0, s>>>(A, field, k, naxv, (T*)buf);             \
+        if (set) exo_field_kernel<R, T, true><<<grid, 256, 0, s>>>(A, field, k, naxv, next, (T*)buf);          \
+        else exo_field_kernel<R, T, false><<<grid, 256, 0, s>>>(A, field, k, naxv, next, (T*)buf);             \
     } while (0)
     if (dtype == 0) EXO_FIELD_GO(R);
     else if (dtype == 1) EXO_FIELD_GO(double);
@@ -49,5 +49,5 @@ void launch_field(const EnvArrays<R>& A, int field, int k, int dtype, int naxv, 
 template void launch_step<REAL>(const EnvArrays<REAL>&, const ChainConst<REAL>&, const StepConst<REAL>&, int, bool, const float*,
                                 float*, REAL*, uint8_t*, const InfoPtrs<REAL>&, cudaStream_t);
 template void launch_fk<REAL>(const REAL*, REAL*, int, REAL, REAL, cudaStream_t);
-template void launch_field<REAL>(const EnvArrays<REAL>&, int, int, int, int, void*, int, cudaStream_t);
+template void launch_field<REAL>(const EnvArrays<REAL>&, int, int, int, int, int, void*, int, cudaStream_t);
 }  // namespace exo

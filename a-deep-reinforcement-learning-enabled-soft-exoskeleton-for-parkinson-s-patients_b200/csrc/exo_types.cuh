@@ -49,6 +49,13 @@
 #define NV_DYN 8
 #define NV_TGT 2
 #define EXO_MAX_ROWS 24          // 14 motor rows + 2 limit rows for each of the 5 revolute joints
+// Per-episode parameters are DOUBLE-BUFFERED: while an env plays the episode held in slot s, the parameters of its next
+// episode are generated into slot s^1 on a side stream (exo_gen_kernel), one episode ahead, so the end of an episode is a
+// slot flip + first observation inside the step kernel and nothing waits for the ~50 us generation chain. The slot lives
+// in bit 16 of `counts` (no extra load). A ring of EXO_RING work lists carries the envs whose spare slot needs refilling.
+#define EXO_SLOT_SHIFT 16
+#define EXO_COUNT_MASK 0xffff
+#define EXO_RING 32
 #define EXO_MT_PITCH 640         // words per env in the MT19937 array: 624 key + position (+pad to 128 B multiple)
 #define EXO_IDS_PITCH 148        // doubles per env: I, D, S (3 x 49) + pad
 
@@ -69,14 +76,15 @@ template <typename R>
 struct EnvArrays {
     int n, stride;
     V4<R>* state;    // [NV_STATE][stride]
-    V4<R>* ep;       // [NV_EP][stride]
-    V4<R>* G;        // [NV_G][stride]
-    V4<R>* tt;       // [table_len][stride][NAXP/4]  tremor table, time-major: one step reads rows c-1, c, c+1
+    V4<R>* ep;       // [2][NV_EP][stride]                  slot-major: slot s at + s * ep_slot
+    V4<R>* G;        // [2][NV_G][stride]
+    V4<R>* tt;       // [2][table_len][stride][NAXP/4]      tremor table, time-major: one step reads rows c-1, c, c+1
+    size_t ep_slot, G_slot, tt_slot;                        // slot strides, in V4 units
     R* ret;          // [stride] running episode return
-    int* counts;     // [stride] self.counts
+    int* counts;     // [stride] self.counts | slot << 16
     int* meta;       // [stride] bits 0-6 tremor_sequence, bits 8-15 motion id, bits 16-31 motion length (max_count)
-    double* IDS;     // [n][EXO_IDS_PITCH]  I_current, D_current, S_current (fp64, env-major)
-    double* mag;     // [stride] tremor_magnitude
+    double* IDS;     // [2][n][EXO_IDS_PITCH]  I_current, D_current, S_current (fp64, env-major), slot s at + s * n * EXO_IDS_PITCH
+    double* mag;     // [2][stride] tremor_magnitude
     uint32_t* mt;    // [n][EXO_MT_PITCH]   numpy legacy MT19937 key + position (env-major)
     const R* motion;         // [n_motions][5][max_len] degrees
     const int* motion_len;   // [n_motions]
@@ -84,8 +92,8 @@ struct EnvArrays {
     V4<R>* dyn;              // [NV_DYN][stride]  EXO_MOTOR_FULL only: qd, qp, qplag
     V4<R>* tgt;              // [NV_TGT][stride]  EXO_MOTOR_FULL only: this step's position targets + live flag
     double* stats;           // [EXO_N_STATS]
-    int* fin_count;          // [2]          envs that finished in the step of parity p (auto-reset work list)
-    int* fin_list;           // [2][stride]
+    int* fin_count;          // [EXO_RING]          envs whose episode began in call t (ring slot t mod EXO_RING): their spare
+    int* fin_list;           // [EXO_RING][stride]  slot is refilled by exo_gen_kernel on the side stream
 };
 
 // Geometry of the 5-revolute chain, flattened on the host from the URDF tree (exo_api.cu: build_chain).
@@ -122,7 +130,10 @@ struct StepConst {
     R inv_fmax_sh0, inv_fmax_el0;
     R L1, L2;                      // humerus / forearm length for the amplitude metric
     int lag, limits, auto_reset, metrics, motor_full;
-    int parity;                    // which finished-list this step appends to (the other counter is cleared)
+    long long* timeline;           // debug (EXO_STEP_TIMELINE): per warp 8 words: globaltimer at entry, smid, clock64 at 6 phase marks
+    int stagger_cycles, n_sm;      // blocks of dispatch layer l = blockIdx / n_sm start their loads l * stagger_cycles late
+    int list;                      // ring slot of the work list this step appends to (it clears the next one)
+    int fused_begin;               // auto-reset: finished envs flip to their prefetched episode inside this kernel
     int env0, env1;                // env range [env0, env1) of this launch (env0 a multiple of 32): exo_step_host pipelines
                                    // chunks of the population against their PCIe copies
 };
@@ -135,7 +146,8 @@ struct ResetConst {
     int lag;
     int motor_full;    // EXO_MOTOR_FULL: the actuator end points follow their prismatic dummies
     int ctor_skip;     // 32-bit outputs consumed before the episode draws (2 for the constructor's rand(), env:70)
-    int list_parity;   // >= 0: reset the envs of fin_list[parity]; < 0: reset by mask
+    int list;          // >= 0: the envs of work list `list` of the ring; < 0: by mask (NULL: all)
+    int append;        // exo_begin_kernel, mask mode: append the envs it started to work list `append` (>= 0)
 };
 
 template <typename R>

@@ -141,6 +141,10 @@ class BatchedExoskeletonEnv(object):
         except Exception:
             pass
 
+    def wait_prefetch(self):
+        """The current stream waits for the episode-parameter generation passes queued so far (side stream); for timing."""
+        _capi.check(self.lib.exo_wait_prefetch(self.h, self._stream()))
+
     def set_auto_reset(self, on):
         _capi.check(self.lib.exo_set_auto_reset(self.h, int(bool(on))))
         self.auto_reset = bool(on)
@@ -231,33 +235,48 @@ class BatchedExoskeletonEnv(object):
         dtype = {_capi.DT_REAL: self.real, _capi.DT_F64: torch.float64, _capi.DT_I32: torch.int32, _capi.DT_U32: torch.int32}[dt.value]
         return k.value, dtype
 
-    def get_field(self, name):
+    PER_EPISODE_FIELDS = ("force_max", "shift", "G", "IDS", "tremor_mag", "tremor_table")
+
+    def get_field(self, name, next=False):
         """Copy of one state field as an env-major tensor [N, k] (tremor_table: [N, table_len, axes]); the layout
-        inside the handle is private (exo_get_field gathers it on the device)."""
+        inside the handle is private (exo_get_field gathers it on the device). Episode parameters are generated one episode
+        ahead: next=True reads the prefetched copy (what the env's NEXT episode will use) of a PER_EPISODE_FIELDS entry."""
         k, dtype = self._field_info(name)
         out = torch.empty(self.n, k, dtype=dtype, device=self.device)
-        _capi.check(self.lib.exo_get_field(self.h, _capi.FIELDS[name], _ptr(out), self._stream()))
+        fid = _capi.FIELDS[name] | (_capi.FIELD_NEXT if next else 0)
+        _capi.check(self.lib.exo_get_field(self.h, fid, _ptr(out), self._stream()))
         if name == "tremor_table":
             axes = 7 if int(self.tremor_sequences[:, 4:].max(initial=0)) else 4
             return out.reshape(self.n, k // axes, axes)
         return out
 
-    def set_field(self, name, value):
+    def set_field(self, name, value, next=False):
         k, dtype = self._field_info(name)
         val = torch.as_tensor(value, device=self.device).to(dtype).reshape(self.n, k).contiguous()
-        _capi.check(self.lib.exo_set_field(self.h, _capi.FIELDS[name], _ptr(val), self._stream()))
+        fid = _capi.FIELDS[name] | (_capi.FIELD_NEXT if next else 0)
+        _capi.check(self.lib.exo_set_field(self.h, fid, _ptr(val), self._stream()))
         torch.cuda.current_stream(self.device).synchronize()      # `val` may be a temporary
 
     CHECKPOINT_FIELDS = ("q", "q_lag", "pos_vec", "elbow_ref", "prev_action", "prev_action2", "force_max", "shift", "G",
                          "ep_return", "IDS", "tremor_mag", "counts", "tremor_table", "mt_state")
 
     def state_dict(self):
-        """Everything needed to resume: a handful of SoA tensors."""
-        return {k: self.get_field(k) for k in self.CHECKPOINT_FIELDS}
+        """Everything needed to resume: a handful of SoA tensors - the carried state, the running episode's parameters, the
+        prefetched parameters of the next episode ("next/<field>") and the RNG stream position behind them."""
+        sd = {k: self.get_field(k) for k in self.CHECKPOINT_FIELDS}
+        sd.update({"next/" + k: self.get_field(k, next=True) for k in self.PER_EPISODE_FIELDS})
+        if self.motor_model == "full":
+            sd.update({k: self.get_field(k) for k in ("qd", "q_pris", "q_pris_lag")})
+        return sd
 
     def load_state_dict(self, sd):
         for k in self.CHECKPOINT_FIELDS:
             self.set_field(k, sd[k])
+        for k in self.PER_EPISODE_FIELDS:
+            self.set_field(k, sd["next/" + k], next=True)
+        if self.motor_model == "full":
+            for k in ("qd", "q_pris", "q_pris_lag"):
+                self.set_field(k, sd[k])
 
 
 class _Box(object):

@@ -362,9 +362,11 @@ def bench_large_population(exo_b200, dev, flush, peak, precision, n_large=524288
 
 
 def bench_reset(env, dev, flush, peak):
-    """The reset kernel by itself (the second kernel of the timed step): (a) latency of resetting one step's steady-state
-    share of the population (n / mean episode length envs, random positions, masked launch, L2 flushed) - what a step waits
-    for when the reset is on its critical path; (b) throughput of resetting every env -> HBM roofline entry."""
+    """Episode (re)initialisation by itself: exo_begin_kernel (slot flip + first observation, on the caller's stream) and
+    exo_gen_kernel (the next episode's parameters: draws, tremor table, I/D/S noise, propagator - on the side stream, one
+    episode ahead, OFF the step's critical path; the timed region here waits for it explicitly). (a) one step's steady-state
+    share of the population (n / mean episode length envs, random positions, L2 flushed); (b) every env -> throughput and
+    the HBM roofline entry."""
     import torch
     n = env.n
     k = max(1, int(round(n / MEAN_EPISODE_STEPS)))
@@ -380,6 +382,7 @@ def bench_reset(env, dev, flush, peak):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             env.reset(mask)
+            env.wait_prefetch()
             b.record()
             ts.append((a, b))
         torch.cuda.synchronize(dev)
@@ -392,11 +395,12 @@ def bench_reset(env, dev, flush, peak):
     env.set_auto_reset(was)
     by = reset_bytes()
     achieved = by * n / (all_ms * 1e-3) / 1e9
-    return {"kernel": "exo_reset_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+    return {"kernel": "exo_gen_kernel (+ exo_begin_kernel)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "traffic": None, "algorithmic_bytes_per_reset": by, "all_envs_ms": all_ms, "ns_per_reset": all_ms * 1e6 / n,
             "resets_per_step_steady_state": k, "steady_state_share_ms": share_ms, "empty_launch_ms": empty_ms,
             "note": "issue/latency-bound (one warp walks an env's draw chain), not bandwidth-bound; the frac is reported against HBM "
-                    "because its compulsory work is byte movement"}
+                    "because its compulsory work is byte movement. In the timed step this work runs one episode ahead on a side "
+                    "stream, overlapped with the step kernels"}
 
 
 def bench_cfg4(exo_b200, args, rank, world, dev, flush, peak, barrier):

@@ -11,9 +11,12 @@
  *    entry points never synchronise, host-buffer entry points synchronise that stream before returning.
  *  - `real` below is float when ExoConfig.precision == EXO_F32 and double when EXO_F64.
  *  - env arrays are row-major [n_envs, k] at this boundary; inside the handle state is structure-of-arrays.
- *  - with auto_reset, exo_step appends the envs that finished to a device-side work list and the reset kernel
- *    consumes it in the same call: no host synchronisation, and a step in which nothing finished pays one
- *    empty launch.
+ *  - episode parameters (tremor table, I/D/S, propagator, shifts, force maxima) are double-buffered per env and generated
+ *    one episode ahead: exo_seed fills the spare slot of every env; starting an episode (exo_reset, or - with auto_reset -
+ *    inside exo_step's kernel when an episode ends) flips the env to its spare slot and queues the env on a device-side
+ *    work list, from which a generation pass on an internal side stream refills the vacated slot while later steps run.
+ *    The draws each env makes from its private numpy-legacy MT19937 stream, and their order, are those of the reference
+ *    (reset after reset); only WHEN they are computed moves. No host synchronisation anywhere.
  */
 #ifndef EXO_ENV_H
 #define EXO_ENV_H
@@ -141,6 +144,11 @@ typedef enum {
     EXO_N_FIELDS
 } ExoField;
 enum { EXO_DT_REAL = 0, EXO_DT_F64 = 1, EXO_DT_I32 = 2, EXO_DT_U32 = 3 };
+/* Episode parameters are generated ONE EPISODE AHEAD (see the conventions above). OR this flag into a field id to address
+ * the prefetched copy - the parameters the env's NEXT episode will use - of FORCE_MAX, SHIFT, G, IDS, TREMOR_TABLE and
+ * TREMOR_MAG. EXO_FIELD_MT_STATE is the stream position AFTER the prefetched episode's draws. A checkpoint is every field
+ * plus the EXO_FIELD_NEXT copies. */
+#define EXO_FIELD_NEXT 0x100
 
 typedef struct ExoHandle ExoHandle;
 
@@ -201,6 +209,16 @@ int exo_set_field(ExoHandle* h, int32_t field, const void* in_dev, void* stream)
  * 15 env-steps through the general multibody step (14 / 15 = sweeps per step).
  * This vector is what ranks all-reduce over NCCL. */
 int exo_stats(ExoHandle* h, double* out_dev, int32_t reset, void* stream);
+
+/* Make `stream` wait (device side, no host sync) for every episode-parameter generation pass queued so far on the
+ * handle's side stream. Not needed for correctness of exo_step / exo_reset / exo_get_field (they order themselves);
+ * for timing the generation work and for callers that read handle memory by other means. */
+int exo_wait_prefetch(ExoHandle* h, void* stream);
+
+/* Debug/profiling: per-warp phase timestamps of the following exo_step launches are written to buf_dev, int64
+ * [ceil(n_envs/32)][8] (NULL switches it off): globaltimer ns at entry, SM id, then clock64 at entry / all loads issued /
+ * staged data landed / kinematics + actuators done / reward done / observation rows written. tools/step_timeline.py. */
+int exo_debug_timeline(ExoHandle* h, void* buf_dev);
 
 /* Toggle ExoConfig.auto_reset after creation (e.g. to time the step kernel alone). */
 int exo_set_auto_reset(ExoHandle* h, int32_t on);

@@ -39,6 +39,7 @@ def main():
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             env.reset(mask)
+            env.wait_prefetch()          # the generation pass runs on the handle's side stream
             b.record()
             ts.append((a, b))
         torch.cuda.synchronize()
