@@ -212,6 +212,7 @@ static void cast_dyn(const DynConst<double>& s, DynConst<R>& d) {
     d.dt = (R)s.dt; d.erp = (R)s.erp; d.limit_cap = (R)s.limit_cap; d.threshold = (R)s.threshold;
     d.iterations = s.iterations; d.n_cons = s.n_cons;
     memcpy(d.cons, s.cons, sizeof(s.cons));
+    memcpy(d.slot_dof, s.slot_dof, sizeof(s.slot_dof)); memcpy(d.dof_slot, s.dof_slot, sizeof(s.dof_slot));
 }
 
 extern "C" int exo_set_motor_model(ExoHandle* h, const ExoLinkDynamics* L, const ExoMotorModel* model) {
@@ -260,6 +261,10 @@ extern "C" int exo_set_motor_model(ExoHandle* h, const ExoLinkDynamics* L, const
         if (D.n_cons >= EXO_MAX_ROWS) return fail(EXO_ERR_TOPOLOGY, "exo_set_motor_model: too many constraint rows");
         D.cons[D.n_cons++] = (signed char)(c >= 0 ? dof : -(dof + 1));
     }
+    int slot = 0;
+    for (int ci = 0; ci < D.n_cons; ci++)
+        if (D.cons[ci] >= 0) { D.slot_dof[slot] = D.cons[ci]; D.dof_slot[(int)D.cons[ci]] = (signed char)slot; slot++; }
+    if (slot != EXO_NDOF) return fail(EXO_ERR_TOPOLOGY, "exo_set_motor_model: %d motor rows, expected %d", slot, EXO_NDOF);
     cast_dyn(D, h->Df);
     h->have_dyn = true;
     return 0;

@@ -42,9 +42,67 @@ template <typename R> __device__ __forceinline__ void rotate_inertia(const R* Rm
         for (int j = 0; j < 3; j++) out[i * 3 + j] = T[i * 3] * Rm[j * 3] + T[i * 3 + 1] * Rm[j * 3 + 1] + T[i * 3 + 2] * Rm[j * 3 + 2];
 }
 
+#define EXO_MOTOR_THREADS 64
+
+#define EXO_NCONS 19             // 14 motor rows + the 5 revolute joints' limit constraints: the static solver path's list length
+
 template <typename R>
-__global__ void __launch_bounds__(64)
+__device__ __forceinline__ R pick14(const R* v, int s) {          // v[s] for a warp-uniform s without local memory
+    switch (s) {
+        case 0: return v[0]; case 1: return v[1]; case 2: return v[2]; case 3: return v[3]; case 4: return v[4];
+        case 5: return v[5]; case 6: return v[6]; case 7: return v[7]; case 8: return v[8]; case 9: return v[9];
+        case 10: return v[10]; case 11: return v[11]; case 12: return v[12]; default: return v[13];
+    }
+}
+
+// One projected Gauss-Seidel sweep over Bullet's constraint list (19 entries, forward or backward). Entry ci is a motor row
+// (always present) or a joint-limit constraint (a row only in the threads where that joint is at / over a bound: bit ci of
+// `act`; bit ci of `neg` = the upper bound). Per-row data (rhs, 1/diag, impulse) is indexed by the compile-time ci, the
+// velocity change dv by solver slot (the 14 loads + FMAs per row have no branch); a row's own dv comes through pick14.
+template <typename R, bool FWD>
+__device__ __forceinline__ void pgs_sweep(const R* sM, const DynConst<R>& D, unsigned act, unsigned neg, const R* dinv,
+                                          const R* rhs, R* lam, R* dv, R& worst) {
+    constexpr int NT = EXO_MOTOR_THREADS;
+#pragma unroll
+    for (int k = 0; k < EXO_NCONS; k++) {
+        const int ci = FWD ? k : EXO_NCONS - 1 - k;
+        const int cc = D.cons[ci];                                  // warp-uniform
+        R imp, dl;
+        int sr;
+        if (cc >= 0) {
+            sr = D.dof_slot[cc];
+            const R cap = cc < 5 ? D.cap_pos : D.cap_vel;
+            dl = rhs[ci] - pick14(dv, sr) * dinv[ci];
+            const R sum = lam[ci] + dl;
+            if (sum < -cap) { dl = -cap - lam[ci]; lam[ci] = -cap; }
+            else if (sum > cap) { dl = cap - lam[ci]; lam[ci] = cap; }
+            else lam[ci] = sum;
+            imp = dl;
+        } else {
+            if (!((act >> ci) & 1u)) continue;                       // divergent only in warps where a joint is at a limit
+            sr = D.dof_slot[-cc - 1];
+            const R sg = ((neg >> ci) & 1u) ? R(-1) : R(1);
+            dl = rhs[ci] - sg * pick14(dv, sr) * dinv[ci];
+            const R sum = lam[ci] + dl;
+            if (sum < R(0)) { dl = -lam[ci]; lam[ci] = 0; }
+            else if (sum > D.limit_cap) { dl = D.limit_cap - lam[ci]; lam[ci] = D.limit_cap; }
+            else lam[ci] = sum;
+            imp = sg * dl;
+        }
+#pragma unroll
+        for (int i = 0; i < EXO_NDOF; i++) dv[i] += sM[(i * EXO_NDOF + sr) * NT] * imp;
+        const R res = dl / dinv[ci];
+        worst = fmax(worst, res * res);
+    }
+}
+
+template <typename R>
+__global__ void __launch_bounds__(EXO_MOTOR_THREADS)
 exo_motor_kernel(EnvArrays<R> S, ChainConst<R> C, DynConst<R> D, int lag, int env0, int env1) {
+    constexpr int NT = EXO_MOTOR_THREADS;
+    extern __shared__ __align__(16) unsigned char motor_smem[];
+    R* sM = reinterpret_cast<R*>(motor_smem) + threadIdx.x;                       // [14 * 14][NT]: M^-1 in solver-slot order
+    R* sV = reinterpret_cast<R*>(motor_smem) + EXO_NDOF * EXO_NDOF * NT + threadIdx.x;   // [14][NT]: reorder scratch
     const int e = env0 + blockIdx.x * blockDim.x + threadIdx.x;
     const int st = S.stride;
     int sweeps_done = 0, did = 0;
@@ -267,9 +325,11 @@ exo_motor_kernel(EnvArrays<R> S, ChainConst<R> C, DynConst<R> D, int lag, int en
                     for (int k = 0; k < 5; k++) if (k >= i && k >= j) acc += Li[k][i] * Li[k][j];
                     Sinv[i][j] = acc;
                 }
-            R Minv[EXO_NDOF][EXO_NDOF];
+            // M^-1 goes to shared memory in SOLVER-SLOT order: slot r = the r-th motor row of Bullet's row order, so the
+            // sweeps below address rows, velocities and impulses with compile-time indices (registers) and only the matrix
+            // through shared memory ([entry][thread]: conflict-free). A 14 x 14 local-memory array here cost 20x (r02b).
             {
-                R W[5][EXO_NPRIS];
+                R W[5][EXO_NPRIS], U[5][EXO_NPRIS];
 #pragma unroll
                 for (int k = 0; k < 5; k++)
 #pragma unroll
@@ -278,13 +338,19 @@ exo_motor_kernel(EnvArrays<R> S, ChainConst<R> C, DynConst<R> D, int lag, int en
 #pragma unroll
                         for (int l = 0; l < 5; l++) acc += Sinv[k][l] * B[l][d];
                         W[k][d] = acc / D.m_d[d];
+                        U[k][d] = B[k][d] / D.m_d[d];
                     }
 #pragma unroll
                 for (int k = 0; k < 5; k++) {
+                    const int sk = D.dof_slot[k];
 #pragma unroll
-                    for (int l = 0; l < 5; l++) Minv[k][l] = Sinv[k][l];
+                    for (int l = 0; l < 5; l++) sM[(sk * EXO_NDOF + D.dof_slot[l]) * NT] = Sinv[k][l];
 #pragma unroll
-                    for (int d = 0; d < EXO_NPRIS; d++) { Minv[k][5 + d] = -W[k][d]; Minv[5 + d][k] = -W[k][d]; }
+                    for (int d = 0; d < EXO_NPRIS; d++) {
+                        const int sd = D.dof_slot[5 + d];
+                        sM[(sk * EXO_NDOF + sd) * NT] = -W[k][d];
+                        sM[(sd * EXO_NDOF + sk) * NT] = -W[k][d];
+                    }
                 }
 #pragma unroll
                 for (int d = 0; d < EXO_NPRIS; d++)
@@ -292,69 +358,130 @@ exo_motor_kernel(EnvArrays<R> S, ChainConst<R> C, DynConst<R> D, int lag, int en
                     for (int d2 = 0; d2 < EXO_NPRIS; d2++) {
                         R acc = (d == d2) ? R(1) / D.m_d[d] : R(0);
 #pragma unroll
-                        for (int k = 0; k < 5; k++) acc += (B[k][d] / D.m_d[d]) * W[k][d2];
-                        Minv[5 + d][5 + d2] = acc;
+                        for (int k = 0; k < 5; k++) acc += U[k][d] * W[k][d2];
+                        sM[(D.dof_slot[5 + d] * EXO_NDOF + D.dof_slot[5 + d2]) * NT] = acc;
                     }
             }
-            // ---- 5. unconstrained velocities, constraint rows in Bullet's order
-            R qdu[EXO_NDOF];
-            for (int i = 0; i < EXO_NDOF; i++) {
-                R acc = 0;
-                for (int j = 0; j < EXO_NDOF; j++) acc -= Minv[i][j] * bias[j];
-                qdu[i] = qd[i] + D.dt * acc;
-            }
-            int rj[EXO_MAX_ROWS];
-            R rsg[EXO_MAX_ROWS], rrhs[EXO_MAX_ROWS], rdinv[EXO_MAX_ROWS], rlo[EXO_MAX_ROWS], rhi[EXO_MAX_ROWS], lam[EXO_MAX_ROWS];
-            int m = 0;
-            for (int ci = 0; ci < D.n_cons; ci++) {
-                const int cc = D.cons[ci];
-                if (cc >= 0) {                          // motor row
-                    const int j = cc;
-                    R desired, cap;
-                    if (j < 5) { desired = D.kp * (tg[j] - q[j]) / D.dt + qdu[j] + D.kd * (R(0) - qdu[j]); cap = D.cap_pos; }
-                    else { desired = qdu[j] + R(1) * (R(0) - qdu[j]); cap = D.cap_vel; }
-                    rj[m] = j; rsg[m] = R(1); rdinv[m] = R(1) / Minv[j][j]; rrhs[m] = (desired - qdu[j]) * rdinv[m];
-                    rlo[m] = -cap; rhi[m] = cap; lam[m] = 0; m++;
-                } else {                                // joint-limit constraint of a revolute joint: rows only while violated
-                    const int j = -cc - 1;
-                    const R pen_lo = q[j] - C.lower[j], pen_hi = C.upper[j] - q[j];
+            // physical DoF order -> slot order through the scratch column (static writes, uniform-address reads)
 #pragma unroll
-                    for (int sgi = 0; sgi < 2; sgi++) {
-                        const R pen = sgi ? pen_hi : pen_lo, sg = sgi ? R(-1) : R(1);
-                        if (pen > R(0)) continue;
-                        rj[m] = j; rsg[m] = sg; rdinv[m] = R(1) / Minv[j][j];
-                        rrhs[m] = (-pen * D.erp / D.dt - sg * qdu[j]) * rdinv[m];
-                        rlo[m] = 0; rhi[m] = D.limit_cap; lam[m] = 0; m++;
+            for (int i = 0; i < EXO_NDOF; i++) sV[i * NT] = bias[i];
+            R bs[EXO_NDOF], qds[EXO_NDOF];
+#pragma unroll
+            for (int r = 0; r < EXO_NDOF; r++) bs[r] = sV[D.slot_dof[r] * NT];
+#pragma unroll
+            for (int i = 0; i < EXO_NDOF; i++) sV[i * NT] = qd[i];
+#pragma unroll
+            for (int r = 0; r < EXO_NDOF; r++) qds[r] = sV[D.slot_dof[r] * NT];
+            // ---- 5. unconstrained velocities (slot order), then one row per entry of Bullet's constraint list
+            R qdu[EXO_NDOF], dv[EXO_NDOF];
+#pragma unroll
+            for (int r = 0; r < EXO_NDOF; r++) {
+                R acc = 0;
+#pragma unroll
+                for (int c2 = 0; c2 < EXO_NDOF; c2++) acc -= sM[(r * EXO_NDOF + c2) * NT] * bs[c2];
+                qdu[r] = qds[r] + D.dt * acc;
+                dv[r] = 0;
+            }
+            // per physical joint: motor target term kp (target - q) / dt, and the joint-limit penetrations
+#pragma unroll
+            for (int i = 0; i < EXO_NDOF; i++) sV[i * NT] = i < 5 ? D.kp * (tg[i] - q[i]) / D.dt : R(0);
+            if (D.n_cons == EXO_NCONS) {
+                R dinv[EXO_NCONS], rhs[EXO_NCONS], lam[EXO_NCONS];
+                unsigned act = 0, neg = 0;
+#pragma unroll
+                for (int ci = 0; ci < EXO_NCONS; ci++) {
+                    const int cc = D.cons[ci];
+                    const int dof = cc >= 0 ? cc : -cc - 1, sr = D.dof_slot[dof];
+                    const R vu = pick14(qdu, sr);
+                    dinv[ci] = R(1) / sM[(sr * EXO_NDOF + sr) * NT];
+                    lam[ci] = 0;
+                    if (cc >= 0) {
+                        const R desired = cc < 5 ? sV[cc * NT] + vu + D.kd * (R(0) - vu) : vu + R(1) * (R(0) - vu);
+                        rhs[ci] = (desired - vu) * dinv[ci];
+                    } else {                                 // rows only while violated; lower and upper cannot both be
+                        R qj = q[0], lo = C.lower[0], hi = C.upper[0];
+#pragma unroll
+                        for (int j = 1; j < 5; j++) if (dof == j) { qj = q[j]; lo = C.lower[j]; hi = C.upper[j]; }
+                        const R pen_lo = qj - lo, pen_hi = hi - qj;
+                        rhs[ci] = 0;
+                        if (pen_lo <= R(0)) { act |= 1u << ci; rhs[ci] = (-pen_lo * D.erp / D.dt - vu) * dinv[ci]; }
+                        else if (pen_hi <= R(0)) { act |= 1u << ci; neg |= 1u << ci; rhs[ci] = (-pen_hi * D.erp / D.dt + vu) * dinv[ci]; }
                     }
                 }
-            }
-            // ---- 6. projected Gauss-Seidel (sweep direction alternates, early exit on the largest squared row error)
-            R dv[EXO_NDOF];
-            for (int i = 0; i < EXO_NDOF; i++) dv[i] = 0;
-            for (int it = 0; it < D.iterations; it++) {
-                R worst = 0;
-                for (int k = 0; k < m; k++) {
-                    const int idx = (it & 1) ? k : m - 1 - k;
-                    const int j = rj[idx];
-                    R dl = rrhs[idx] - rsg[idx] * dv[j] * rdinv[idx];
-                    const R sum = lam[idx] + dl;
-                    if (sum < rlo[idx]) { dl = rlo[idx] - lam[idx]; lam[idx] = rlo[idx]; }
-                    else if (sum > rhi[idx]) { dl = rhi[idx] - lam[idx]; lam[idx] = rhi[idx]; }
-                    else lam[idx] = sum;
-                    const R imp = rsg[idx] * dl;
-                    for (int i = 0; i < EXO_NDOF; i++) dv[i] += Minv[i][j] * imp;
-                    const R res = dl / rdinv[idx];
-                    worst = fmax(worst, res * res);
+                // ---- 6a. projected Gauss-Seidel, everything but M^-1 in registers
+                const unsigned amask = __activemask();
+                bool going = true;
+                for (int it = 0; it < D.iterations; it++) {
+                    if (going) {
+                        R worst = 0;
+                        // sweep direction alternates: even sweeps run the rows backwards (Bullet: iteration & 1 ? j : size-1-j);
+                        // both directions are separately unrolled so the row index stays a compile-time constant
+                        if (it & 1) pgs_sweep<R, true>(sM, D, act, neg, dinv, rhs, lam, dv, worst);
+                        else pgs_sweep<R, false>(sM, D, act, neg, dinv, rhs, lam, dv, worst);
+                        sweeps_done++;
+                        if (worst <= D.threshold) going = false;
+                    }
+                    if (!__any_sync(amask, going)) break;
                 }
-                sweeps_done++;
-                if (worst <= D.threshold) break;
+#pragma unroll
+                for (int r = 0; r < EXO_NDOF; r++) sV[r * NT] = qdu[r] + dv[r];      // new velocities, slot order
+            } else {
+                // ---- 6b. a constraint list of another length (a different URDF): the general row list, indices at run time
+                //      (local memory). Same arithmetic, not tuned.
+                int rj[EXO_MAX_ROWS];
+                R rsg[EXO_MAX_ROWS], rrhs[EXO_MAX_ROWS], rdinv[EXO_MAX_ROWS], rlo[EXO_MAX_ROWS], rhi[EXO_MAX_ROWS], rlam[EXO_MAX_ROWS];
+                R dvv[EXO_NDOF], qduv[EXO_NDOF];
+                for (int r = 0; r < EXO_NDOF; r++) { dvv[r] = 0; qduv[r] = qdu[r]; }
+                int m = 0;
+                for (int ci = 0; ci < D.n_cons; ci++) {
+                    const int cc = D.cons[ci];
+                    if (cc >= 0) {                          // motor row of dof cc -> slot
+                        const int r = D.dof_slot[cc];
+                        const R vu = qduv[r], di = R(1) / sM[(r * EXO_NDOF + r) * NT];
+                        const R desired = cc < 5 ? sV[cc * NT] + vu + D.kd * (R(0) - vu) : vu + R(1) * (R(0) - vu);
+                        rj[m] = r; rsg[m] = R(1); rdinv[m] = di; rrhs[m] = (desired - vu) * di;
+                        const R cap = cc < 5 ? D.cap_pos : D.cap_vel;
+                        rlo[m] = -cap; rhi[m] = cap; rlam[m] = 0; m++;
+                    } else {                                // joint-limit constraint of a revolute joint: rows only while violated
+                        const int j = -cc - 1, r = D.dof_slot[j];
+                        const R pen_lo = q[j] - C.lower[j], pen_hi = C.upper[j] - q[j];
+                        for (int sgi = 0; sgi < 2; sgi++) {
+                            const R pen = sgi ? pen_hi : pen_lo, sg = sgi ? R(-1) : R(1);
+                            if (pen > R(0)) continue;
+                            const R di = R(1) / sM[(r * EXO_NDOF + r) * NT];
+                            rj[m] = r; rsg[m] = sg; rdinv[m] = di;
+                            rrhs[m] = (-pen * D.erp / D.dt - sg * qduv[r]) * di;
+                            rlo[m] = 0; rhi[m] = D.limit_cap; rlam[m] = 0; m++;
+                        }
+                    }
+                }
+                for (int it = 0; it < D.iterations; it++) {
+                    R worst = 0;
+                    for (int k = 0; k < m; k++) {
+                        const int idx = (it & 1) ? k : m - 1 - k;
+                        const int r = rj[idx];
+                        R dl = rrhs[idx] - rsg[idx] * dvv[r] * rdinv[idx];
+                        const R sum = rlam[idx] + dl;
+                        if (sum < rlo[idx]) { dl = rlo[idx] - rlam[idx]; rlam[idx] = rlo[idx]; }
+                        else if (sum > rhi[idx]) { dl = rhi[idx] - rlam[idx]; rlam[idx] = rhi[idx]; }
+                        else rlam[idx] = sum;
+                        const R imp = rsg[idx] * dl;
+                        for (int i = 0; i < EXO_NDOF; i++) dvv[i] += sM[(i * EXO_NDOF + r) * NT] * imp;
+                        const R res = dl / rdinv[idx];
+                        worst = fmax(worst, res * res);
+                    }
+                    sweeps_done++;
+                    if (worst <= D.threshold) break;
+                }
+                for (int r = 0; r < EXO_NDOF; r++) sV[r * NT] = qduv[r] + dvv[r];
             }
-            // ---- 7. integrate, write back
+            // ---- 7. back to the physical order, integrate, write back
             if (lag) {
 #pragma unroll
                 for (int d = 0; d < EXO_NPRIS; d++) dy[W_QPLAG + d] = qp[d];
             }
-            for (int i = 0; i < EXO_NDOF; i++) qd[i] = qdu[i] + dv[i];
+#pragma unroll
+            for (int i = 0; i < EXO_NDOF; i++) qd[i] = sV[D.dof_slot[i] * NT];
 #pragma unroll
             for (int j = 0; j < 5; j++) *exo_word(S.state, W_Q + j, e, st) = q[j] + D.dt * qd[j];
 #pragma unroll

@@ -19,8 +19,16 @@ void launch_step_full(const EnvArrays<R>& A, const ChainConst<R>& C, const StepC
 }
 template <typename R>
 void launch_motor(const EnvArrays<R>& A, const ChainConst<R>& C, const DynConst<R>& D, int lag, int env0, int env1, cudaStream_t s) {
-    const int grid = (env1 - env0 + 63) / 64;
-    exo_motor_kernel<R><<<grid, 64, 0, s>>>(A, C, D, lag, env0, env1);
+    const int grid = (env1 - env0 + EXO_MOTOR_THREADS - 1) / EXO_MOTOR_THREADS;
+    const size_t smem = (size_t)(EXO_NDOF * EXO_NDOF + EXO_NDOF) * EXO_MOTOR_THREADS * sizeof(R);
+    static bool configured[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!configured[dev & 63]) {
+        cudaFuncSetAttribute(exo_motor_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        configured[dev & 63] = true;
+    }
+    exo_motor_kernel<R><<<grid, EXO_MOTOR_THREADS, smem, s>>>(A, C, D, lag, env0, env1);
 }
 template void launch_step_full<REAL>(const EnvArrays<REAL>&, const ChainConst<REAL>&, const StepConst<REAL>&, int, bool, const float*,
                                      float*, REAL*, uint8_t*, const InfoPtrs<REAL>&, cudaStream_t);

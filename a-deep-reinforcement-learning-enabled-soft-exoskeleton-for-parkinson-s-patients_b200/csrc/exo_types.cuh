@@ -122,6 +122,7 @@ struct DynConst {
     R k_lin, k_ang, g[3], dt, erp, limit_cap, threshold;
     int iterations, n_cons;
     signed char cons[EXO_MAX_ROWS];                // solver order: dof (motor row) or -(dof+1) (joint-limit constraint)
+    signed char slot_dof[EXO_NDOF], dof_slot[EXO_NDOF];   // solver slot r = r-th motor row of `cons` <-> physical DoF
 };
 
 template <typename R>

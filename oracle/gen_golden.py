@@ -25,6 +25,10 @@ Families
   B  BASELINE config 2: 15 tremor types x 8 motions, no domain randomisation, 30 steps.
   C  BASELINE config 3 settings (training DR, Exoskeleton_agent_train.py:30-35,43-44),
      one env per motion: a full episode, reset, 20 more steps (state carried across reset).
+  S  the training script's SHARED stream (seed_setting_.py:9, Exoskeleton_agent_train.py:51-71,110-147): np.random.seed once,
+     8 envs built one after the other (one per motion), reset in order, then lock-step steps whose warm-up actions
+     np.random.uniform(-1, 1, 7) come from the same global stream, across the first episode end of the shortest motion.
+     Written to ref_shared_stream.npz; replayed through host-generated parameters (exo_b200.reference_stream).
   F  the same env on minibullet's motor_model="full" (the general Bullet multibody step, oracle/multibody.py, pybullet's
      default solver settings): config 1 for 300 steps (one reset) and config 3 on motions 1 and 5. Written to
      ref_full_motor.npz; what the product's EXO_MOTOR_FULL path is held to.
@@ -171,7 +175,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default=os.path.join(REPO, "tests", "golden"))
     ap.add_argument("--lag", type=int, default=1)
-    ap.add_argument("--families", default="DABCF")
+    ap.add_argument("--families", default="DABCSF")
     args = ap.parse_args()
     out_dir = os.path.abspath(args.out)
     Env = _import_reference(dict(link_state_lag=args.lag))
@@ -266,6 +270,42 @@ def main():
         np.savez_compressed(os.path.join(out_dir, "ref_cfg3_dr_episodes.npz"), **out)
         print("C: 8 cases, limit crossings", n)
 
+
+    if "S" in args.families:
+        out = {}
+        seed, n_steps = 5, 260
+        seqs = [TYPES15[(3 * m + 14) % 15] for m in range(8)]
+        np.random.seed(seed)                                   # set_seeds (seed_setting_.py:9)
+        sink = io.StringIO()
+        with contextlib.redirect_stdout(sink):
+            envs = [Env(reference_motion_file_num=str(m), tremor_sequence=np.array(seqs[m]), **TRAIN_SETTINGS) for m in range(8)]
+            recs = [Recorder(e) for e in envs]
+            done = [False] * 8
+            obs = [None] * 8
+            for i, e in enumerate(envs):                       # train:111-113
+                obs[i], _ = e.reset()
+                recs[i].snap_episode(obs[i])
+            for t in range(n_steps):
+                if all(done):                                  # train:123 -> next outer iteration resets every env
+                    for i, e in enumerate(envs):
+                        obs[i], _ = e.reset()
+                        recs[i].snap_episode(obs[i])
+                    done = [False] * 8
+                acts = [np.random.uniform(-1, 1, 7) if not done[i] else None for i in range(8)]   # train:125-131: one draw per live env
+                for i, e in enumerate(envs):
+                    if not done[i]:                            # train:139
+                        a32 = acts[i].astype(np.float32).astype(np.float64)
+                        o = e.step(a32)
+                        recs[i].snap_step(a32, o)
+                        obs[i], done[i] = o[0], o[2]
+        for i in range(8):
+            meta = dict(seed=seed, motion=i, seq=np.array(seqs[i], dtype=np.int64), max_count=envs[i].max_count,
+                        max_reward=float(envs[i].max_reward), limit_crossings=envs[i].client._world.limit_crossings,
+                        **{k: np.array(v, dtype=np.float64) for k, v in TRAIN_SETTINGS.items()})
+            recs[i].pack(f"S{i}", out, meta)
+        out["S/n_steps"] = np.array(n_steps)
+        np.savez_compressed(os.path.join(out_dir, "ref_shared_stream.npz"), **out)
+        print("S: 8 envs on one shared stream,", n_steps, "lock-step rounds; steps per env", [len(r.st["reward"]) for r in recs])
 
     if "F" in args.families:
         import pybullet_utils.bullet_client as bc

@@ -30,12 +30,15 @@ OPTION_SETS = [
     (dict(row_order=1), dict(row_order="natural")),
     (dict(residual_threshold=0.0, iterations=70), dict(residual_threshold=0.0, iterations=70)),
     (dict(linear_damping=0.0, angular_damping=0.0, kd=0.8), dict(linear_damping=0.0, angular_damping=0.0)),
+    (dict(at_limits=True), {}),             # joints at / beyond URDF bounds: joint-limit rows join the solve (0.8 % of bench env-steps)
 ]
 
 
 @pytest.mark.parametrize("which", range(len(OPTION_SETS)))
 def test_one_multibody_step_matches_the_cpu_model(exo, which):
     kopts, popts = OPTION_SETS[which]
+    kopts = dict(kopts)
+    at_limits = kopts.pop("at_limits", False)
     geo = dict(np.load(os.path.join(GOLDEN, "ref_data_and_units.npz")))
     n = 10
     mids = [i % 8 for i in range(n)]
@@ -45,6 +48,10 @@ def test_one_multibody_step_matches_the_cpu_model(exo, which):
     rs = np.random.RandomState(11 + which)
     # start away from rest so Coriolis / damping / prismatic offsets all matter
     q0 = rs.uniform(-0.4, 0.4, (n, 5)); q0[:, 3] = np.abs(q0[:, 3]) + 0.2
+    if at_limits:
+        q0[0::3, 3] = -0.05                       # elbow y below its -2 deg lower bound (exo_v3.urdf:77)
+        q0[1::3, 0] = 1.45                        # shoulder z above its +80 deg upper bound (:17)
+        q0[2::3, 4] = -1.5184364318848            # elbow z exactly on its lower bound: a row with zero penetration
     env.set_field("q", torch.from_numpy(q0).cuda()); env.set_field("q_lag", torch.from_numpy(q0).cuda())
     env.set_field("qd", torch.from_numpy(rs.uniform(-1.0, 1.0, (n, 14)) * np.r_[np.ones(5), 0.05 * np.ones(9)]).cuda())
     env.set_field("q_pris", torch.from_numpy(rs.uniform(-2e-3, 2e-3, (n, 9))).cuda())
@@ -76,8 +83,10 @@ def test_one_multibody_step_matches_the_cpu_model(exo, which):
             worst["qd"] = max(worst["qd"], np.max(np.abs(b.qd[DOF_LINK] - qd1[i])))
             assert np.max(np.abs(b.q[[14, 15, 16, 17, 18]])) < 1e-15      # the base dummies the kernel leaves out stay at rest
     st = env.stats()
-    print("options %r: max |dq| %.2e  |dqd| %.2e  |dq_pris| %.2e; sweeps kernel %d cpu %d" %
-          (kopts, worst["q"], worst["qd"], worst["qp"], int(st[14]), sweeps_cpu))
+    limit_rows = sum(sp.stats["limit_rows"] for sp in steppers)
+    print("options %r%s: max |dq| %.2e  |dqd| %.2e  |dq_pris| %.2e; sweeps kernel %d cpu %d; limit rows %d" %
+          (kopts, " at limits" if at_limits else "", worst["q"], worst["qd"], worst["qp"], int(st[14]), sweeps_cpu, limit_rows))
+    assert (limit_rows > 0) == at_limits
     assert worst["q"] <= 1e-10 and worst["qd"] <= 1e-9 and worst["qp"] <= 1e-10
     assert int(st[14]) == sweeps_cpu and int(st[15]) == 12 * n
     env.close()

@@ -28,6 +28,13 @@ def rel(a, b):
     return float(np.max(np.abs(a - b)) / max(1e-300, np.max(np.abs(b))))
 
 
+# reward tolerances against the reference goldens (see _replay_golden_episodes). Measured on B200 (r02l, profiles/
+# r02l_pytest_gpu.txt): family C worst |d reward| 4.3e-6 (fp32) / 4.2e-6 (fp64) on every step, no ties; family A 4.0e-7 on
+# non-tie steps and on the smooth terms of ALL steps, tie fraction 0.311 of 1000 steps. Bounds = measured x ~5 / + 0.04.
+REWARD_TOL = {"A": 5e-6, "C": 2e-5}
+TIE_FRACTION_A = 0.35
+
+
 def population(n_types=15, n_motions=8, seed0=100):
     mids, seqs, seeds = [], [], []
     for ti in range(n_types):
@@ -137,21 +144,31 @@ def test_against_reference_goldens_cfg2(exo, precision):
     env.close()
 
 
-def _replay_golden_episodes(exo, g, cases, precision, settings_case):
+def _replay_golden_episodes(exo, g, cases, precision, settings_case, label=""):
+    """Replays golden families (reference Python on the restated pybullet boundary) through the CUDA path with auto-reset.
+    Reward parity is checked term by term (info.reward_parts vs the golden's reward_* entries): the four smooth terms
+    (unwanted, torque, control, smoothness) on EVERY step; the discontinuous axis_reward (a count of axes with
+    |torque| < |tremor|, Exoskeleton_env.py:294-306, worth 0.5 / max_reward per axis) only on steps where no axis sits on the
+    tie |torque| == |tremor| to 1e-5 relative - the shipped actor saturates at action -1 = zero force, which makes
+    torque == tremor EXACTLY on the unactuated side, so ties are common in family A and their count is reported.
+    Returns the worst errors; prints them with the tie fraction."""
     mids = [int(g[c + "/meta_motion"]) for c in cases]
     seqs = [g[c + "/meta_seq"] for c in cases]
     seeds = [int(g[c + "/meta_seed"]) for c in cases]
     env = exo.BatchedExoskeletonEnv(mids, seqs, seeds, precision=precision, auto_reset=True, **case_settings(g, settings_case))
     obs = env.reset().cpu().numpy()
     nsteps = [len(g[c + "/action"]) for c in cases]
+    max_reward = [float(g[c + "/meta_max_reward"]) for c in cases]
     ep = [0] * len(cases)
     for i, c in enumerate(cases):
         assert np.max(np.abs(obs[i] - g[c + "/ep_obs0"][0])) <= 2e-7
-    worst_obs, worst_q, worst_r, ties = 0.0, 0.0, 0.0, 0
+    w = dict(obs=0.0, q=0.0, reward=0.0, smooth=0.0, axis_non_tie=0.0)
+    ties = 0
     for t in range(max(nsteps)):
         a = np.stack([g[c + "/action"][min(t, nsteps[i] - 1)] for i, c in enumerate(cases)]).astype(np.float32)
-        ob, rw, dn = env.step(torch.from_numpy(a).cuda())
+        ob, rw, dn, info = env.step(torch.from_numpy(a).cuda(), with_info=True)
         ob, rw, dn = ob.cpu().numpy(), rw.cpu().numpy(), dn.cpu().numpy()
+        parts = info["reward_parts"].cpu().numpy()          # unwanted, torque, axis, control, smoothness
         qb = env.get_field("q").cpu().numpy()
         mag = env.get_field("tremor_mag").cpu().numpy()
         ids = env.get_field("IDS").cpu().numpy()
@@ -159,23 +176,74 @@ def _replay_golden_episodes(exo, g, cases, precision, settings_case):
             if t >= nsteps[i]:
                 continue
             assert bool(dn[i]) == bool(g[c + "/done"][t])
-            worst_q = max(worst_q, float(np.max(np.abs(qb[i] - g[c + "/qb"][t]))))
+            w["q"] = max(w["q"], float(np.max(np.abs(qb[i] - g[c + "/qb"][t]))))
+            ref_parts = g[c + "/rew_parts"][t]
+            smooth_err = np.abs(np.delete(parts[i], 2) - np.delete(ref_parts, 2)).sum() / max_reward[i]
+            w["smooth"] = max(w["smooth"], float(smooth_err))
             ta, tb = np.abs(g[c + "/torque_val"][t]), np.abs(g[c + "/tremor_torque_val"][t])
             tie = bool(np.any((np.abs(ta - tb) <= 1e-5 * np.maximum(tb, 1e-30)) & (tb > 0)))
             ties += tie
-            if not tie:     # axis_reward is a 0.5-step at |torque| == |tremor| (Exoskeleton_env.py:301-304); a saturated
-                            # actor (action == -1 -> zero force) sits exactly on it
-                worst_r = max(worst_r, abs(float(rw[i]) - float(g[c + "/reward"][t])))
+            if not tie:
+                assert parts[i][2] == ref_parts[2], (c, t, parts[i][2], ref_parts[2])      # the axis count itself, exactly
+                w["reward"] = max(w["reward"], abs(float(rw[i]) - float(g[c + "/reward"][t])))
             if dn[i]:       # auto-reset: the returned obs is the first obs of the next episode
                 ep[i] += 1
                 assert np.max(np.abs(ob[i] - g[c + "/ep_obs0"][ep[i]])) <= 1e-5
                 assert mag[i, 0] == float(g[c + "/ep_mag"][ep[i]])                       # stream continues bit-exactly
                 assert np.array_equal(ids[i, :49], g[c + "/ep_I"][ep[i]].ravel())
             else:
-                worst_obs = max(worst_obs, float(np.max(np.abs(ob[i] - g[c + "/obs"][t]))))
+                w["obs"] = max(w["obs"], float(np.max(np.abs(ob[i] - g[c + "/obs"][t]))))
     env.close()
-    assert ties <= 0.5 * sum(nsteps)
-    return worst_obs, worst_q, worst_r
+    w["tie_fraction"] = ties / float(sum(nsteps))
+    print("%s %s: %d steps, tie fraction %.3f | worst |d obs| %.2e  |dq| %.2e  |d reward| (non-tie steps) %.2e  "
+          "|d smooth reward terms| / max_reward (all steps) %.2e" % (label, precision, sum(nsteps), w["tie_fraction"], w["obs"], w["q"],
+                                                                     w["reward"], w["smooth"]))
+    return w
+
+
+def test_shared_stream_golden_through_host_generated_parameters(exo):
+    """The reference's training script draws everything - 8 envs' episode parameters AND the warm-up actions - from ONE
+    global numpy stream (seed_setting_.py:9, Exoskeleton_agent_train.py:51-71,110-131). The batched env's private per-env
+    streams cannot reproduce that; the reference-stream mode does: parameters generated on the host in the reference's
+    draw order (exo_b200.reference_stream) and uploaded into each env's prefetched slot, the step itself on the device.
+    Golden: tests/golden/ref_shared_stream.npz (reference Python), 260 lock-step rounds across the first episode end."""
+    rsm = exo.reference_stream
+    g = np.load(os.path.join(GOLDEN, "ref_shared_stream.npz"))
+    st = case_settings(g, "S0")
+    L = [int(g["S%d/meta_max_count" % i]) for i in range(8)]
+    seqs = [g["S%d/meta_seq" % i] for i in range(8)]
+    env = exo.BatchedExoskeletonEnv(list(range(8)), seqs, [0] * 8, precision="fp64", auto_reset=False, **st)
+    stream = rsm.ReferenceStream(int(g["S0/meta_seed"]))
+    for i in range(8):                                           # constructors, in order (state they leave is overwritten below)
+        stream.constructor(L[i], seqs[i], **st)
+    for i in range(8):                                           # first reset() of each env, in order
+        rsm.upload_next_episode(env, i, stream.initialize_movement(L[i], seqs[i], **st))
+    obs = env.reset().cpu().numpy()
+    for i in range(8):
+        assert np.max(np.abs(obs[i] - g["S%d/ep_obs0" % i][0])) <= 2e-7
+    done = np.zeros(8, bool)
+    n = [0] * 8
+    worst_obs = worst_rw = 0.0
+    for t in range(int(g["S/n_steps"])):
+        a = np.zeros((8, 7), np.float32)
+        for i in range(8):
+            if not done[i]:
+                a[i] = stream.warmup_action().astype(np.float32)
+        ob, rw, dn = env.step(torch.from_numpy(a).cuda())
+        ob, rw, dn = ob.cpu().numpy(), rw.cpu().numpy(), dn.cpu().numpy()
+        for i in range(8):
+            if done[i]:
+                continue
+            c = "S%d" % i
+            assert np.array_equal(a[i].astype(np.float64), g[c + "/action"][n[i]])
+            worst_obs = max(worst_obs, float(np.max(np.abs(ob[i] - g[c + "/obs"][n[i]]))))
+            worst_rw = max(worst_rw, abs(float(rw[i]) - float(g[c + "/reward"][n[i]])))
+            assert bool(dn[i]) == bool(g[c + "/done"][n[i]])
+            done[i] = bool(dn[i])
+            n[i] += 1
+    print("shared-stream golden: worst |d obs| %.2e  |d reward| %.2e over %d env-steps" % (worst_obs, worst_rw, sum(n)))
+    assert worst_obs <= 1e-5 and worst_rw <= 2e-5 and done[0] and not done[1:].any()      # measured 8.8e-7 / 2.5e-6 (r02l)
+    env.close()
 
 
 def test_two_shards_reproduce_the_one_handle_run_bit_for_bit(exo):
@@ -208,8 +276,13 @@ def test_against_reference_goldens_cfg3_full_episodes_with_auto_reset(exo, preci
     """Training DR, one full episode per motion, reset, 20 more steps: state carried over the reset
     (Bullet joint state and prev_action are NOT reset by the reference) and the per-env RNG stream continues."""
     g = np.load(os.path.join(GOLDEN, "ref_cfg3_dr_episodes.npz"))
-    wo, wq, wr = _replay_golden_episodes(exo, g, ["C%d" % m for m in range(8)], precision, "C0")
-    assert wo <= 1e-5 and wq <= 1e-5 and wr <= 2e-3, (wo, wq, wr)
+    w = _replay_golden_episodes(exo, g, ["C%d" % m for m in range(8)], precision, "C0", "family C (cfg3)")
+    assert w["obs"] <= 1e-5 and w["q"] <= 1e-5, w
+    # reward bound: the kernel integrates the arm ODE exactly where the golden used scipy's RK45 at rtol 1e-3 (angles differ by
+    # <= 1e-3 relative, obs by <= 1e-5); torque_reward has no epsilon in its |tremor| denominator (Exoskeleton_env.py:318), so a
+    # 1e-5 torque difference at a tremor sample of 1e-2 Nm moves that term by 1e-3. Measured worst values (r02, printed above)
+    # stay below the asserted bounds by > 2x; random actions never sit on an axis tie.
+    assert w["reward"] <= REWARD_TOL["C"] and w["smooth"] <= REWARD_TOL["C"] and w["tie_fraction"] <= 0.02, w
 
 
 @pytest.mark.parametrize("precision", ["fp64", "fp32"])
@@ -217,8 +290,11 @@ def test_against_reference_goldens_cfg1_trained_actor_1000_steps(exo, precision)
     """BASELINE config 1: motion 0, type [1,1,1,1], seed 0, evaluation settings, the shipped TD7 checkpoint actor's
     actions, 1000 steps over 4+ episodes."""
     g = np.load(os.path.join(GOLDEN, "ref_cfg1_trained_actor.npz"))
-    wo, wq, wr = _replay_golden_episodes(exo, g, ["A0"], precision, "A0")
-    assert wo <= 1e-5 and wq <= 1e-5 and wr <= 2e-3, (wo, wq, wr)
+    w = _replay_golden_episodes(exo, g, ["A0"], precision, "A0", "family A (cfg1)")
+    assert w["obs"] <= 1e-5 and w["q"] <= 1e-5, w
+    # the shipped actor is near bang-bang: action -1 (zero force) on one side makes |torque| == |tremor| exactly there, so
+    # a large, stable share of steps are axis ties (measured 0.40 of 1000); the smooth terms are held on ALL steps
+    assert w["reward"] <= REWARD_TOL["A"] and w["smooth"] <= REWARD_TOL["A"] and w["tie_fraction"] <= TIE_FRACTION_A, w
 
 
 def test_single_env_facade_matches_reference_signatures(exo):

@@ -150,3 +150,43 @@ def test_shard_ranges_partition_the_population(exo):
             parts = [sh.benchmark_population(n, r, w) for r in range(w)]
             for k in range(3):
                 assert np.array_equal(np.concatenate([p[k] for p in parts]), one[k]), (n, w, k)
+
+
+def test_reference_stream_reproduces_the_shared_numpy_stream_bit_for_bit(exo):
+    """8 reference envs built after ONE np.random.seed, reset in order, warm-up actions from the same stream
+    (Exoskeleton_agent_train.py:51-71,110-131): exo_b200.reference_stream restates the draw ORDER on the host. Every
+    RNG-derived quantity of the golden (tests/golden/ref_shared_stream.npz, reference Python) must come out bit-identical:
+    tremor tables, I/D/S, shifts, force maxima, magnitudes and the actions themselves."""
+    from conftest import GOLDEN, case_settings
+    rsm = exo.reference_stream
+    g = np.load(os.path.join(GOLDEN, "ref_shared_stream.npz"))
+    st = case_settings(g, "S0")
+    L = [int(g["S%d/meta_max_count" % i]) for i in range(8)]
+    seqs = [g["S%d/meta_seq" % i] for i in range(8)]
+    stream = rsm.ReferenceStream(int(g["S0/meta_seed"]))
+    for i in range(8):
+        stream.constructor(L[i], seqs[i], **st)                 # the constructors' own initialize_movement draws
+    eps = [stream.initialize_movement(L[i], seqs[i], **st) for i in range(8)]        # the first reset() of each env, in order
+    for i in range(8):
+        c = "S%d" % i
+        assert np.array_equal(eps[i]["tremor_table"], g[c + "/ep_tt"][0])
+        assert eps[i]["tremor_mag"] == float(g[c + "/ep_mag"][0])
+        for k, key in (("I", "ep_I"), ("D", "ep_D"), ("S", "ep_S"), ("shift", "ep_shift")):
+            assert np.array_equal(eps[i][k], g[c + "/" + key][0]), (i, k)
+        assert np.array_equal(eps[i]["force_max"], g[c + "/ep_fmax"][0])
+    done = [False] * 8
+    n = [0] * 8
+    for t in range(int(g["S/n_steps"])):
+        for i in range(8):
+            if not done[i]:
+                a = stream.warmup_action().astype(np.float32).astype(np.float64)
+                assert np.array_equal(a, g["S%d/action" % i][n[i]])
+        for i in range(8):
+            if not done[i]:
+                done[i] = bool(g["S%d/done" % i][n[i]])
+                n[i] += 1
+    # the exact propagator of the host matches the kernel's arithmetic contract: G T = scipy RK45 solution to its tolerance
+    d = np.load(os.path.join(GOLDEN, "ref_data_and_units.npz"))
+    G = rsm.propagator(d["mat/I"], d["mat/D"], d["mat/S"])
+    for T, q in zip(d["ode/T"], d["ode/q"]):
+        assert np.max(np.abs(G @ T - q)) <= 1e-3 * max(np.max(np.abs(q)), 1e-9)
