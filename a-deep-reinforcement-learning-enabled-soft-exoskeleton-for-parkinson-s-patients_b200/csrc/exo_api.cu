@@ -460,7 +460,7 @@ static int wait_all_gen(ExoHandle* h, cudaStream_t s) {
 
 // generation pass for work list `list` (filled by kernels already queued on `s`), on the side stream
 template <typename R>
-static int gen_list_async(ExoHandle* h, EnvArrays<R>& A, int list, cudaStream_t s) {
+static int gen_list_async(ExoHandle* h, EnvArrays<R>& A, int list, cudaStream_t s, int expect) {
     if (int rc = gen_setup(h)) return rc;
     const int si = list % h->n_gen_streams;
     cudaStream_t g = h->s_gen[si];
@@ -468,7 +468,7 @@ static int gen_list_async(ExoHandle* h, EnvArrays<R>& A, int list, cudaStream_t 
     CK(cudaStreamWaitEvent(g, h->ev_main[list], 0));
     ResetConst K = reset_const(h);
     K.list = list;
-    if (int e = launch_gen<R>(A, K, h->nax, h->n_sm, nullptr, g))
+    if (int e = launch_gen<R>(A, K, h->nax, h->n_sm, nullptr, expect, g))
         return fail(EXO_ERR_CUDA, "exo_gen_kernel: %s", cudaGetErrorString((cudaError_t)e));
     h->launches += 1;
     CK(cudaEventRecord(h->ev_gen[list], g));
@@ -488,7 +488,7 @@ static int reset_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const 
     launch_begin<R>(A, C, K, h->nax, mask, obs, s);
     h->launches += 1;
     CK(cudaGetLastError());
-    return gen_list_async<R>(h, A, list, s);
+    return gen_list_async<R>(h, A, list, s, mask == nullptr ? h->n : 0);
 }
 
 static int check_ready(ExoHandle* h, const char* who) {
@@ -510,12 +510,12 @@ static int seed_prime(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, cud
     ResetConst K = reset_const(h);
     if (h->cfg.reference_ctor) {
         K.ctor_skip = 2;
-        if (int e = launch_gen<R>(A, K, h->nax, h->n_sm, nullptr, s)) return fail(EXO_ERR_CUDA, "exo_gen_kernel: %s", cudaGetErrorString((cudaError_t)e));
+        if (int e = launch_gen<R>(A, K, h->nax, h->n_sm, nullptr, h->n, s)) return fail(EXO_ERR_CUDA, "exo_gen_kernel: %s", cudaGetErrorString((cudaError_t)e));
         K.ctor_skip = 0;
         launch_begin<R>(A, C, K, h->nax, nullptr, nullptr, s);
         h->launches += 2;
     }
-    if (int e = launch_gen<R>(A, K, h->nax, h->n_sm, nullptr, s)) return fail(EXO_ERR_CUDA, "exo_gen_kernel: %s", cudaGetErrorString((cudaError_t)e));
+    if (int e = launch_gen<R>(A, K, h->nax, h->n_sm, nullptr, h->n, s)) return fail(EXO_ERR_CUDA, "exo_gen_kernel: %s", cudaGetErrorString((cudaError_t)e));
     h->launches += 1;
     CK(cudaGetLastError());
     return 0;
@@ -589,7 +589,7 @@ static int step_t(ExoHandle* h, EnvArrays<R>& A, const ChainConst<R>& C, const f
             CK(cudaGetLastError());
         }
         if (dbg_no_gen) return 0;                  // timing experiments only: the spare slots go stale
-        return gen_list_async<R>(h, A, list, s);   // refill the vacated slots, off the critical path
+        return gen_list_async<R>(h, A, list, s, 0);   // refill the vacated slots, off the critical path
     }
     return 0;
 }

@@ -17,7 +17,7 @@ void launch_motor(const EnvArrays<R>& A, const ChainConst<R>& C, const DynConst<
 // exo_gen_kernel: draws, tremor table, parameters and propagator of the NEXT episode into the spare slot of the envs of
 // work list K.list (>= 0) or selected by mask (NULL: all). Returns a cudaError_t.
 template <typename R>
-int launch_gen(const EnvArrays<R>& A, const ResetConst& K, int nax, int n_sm, const uint8_t* mask, cudaStream_t s);
+int launch_gen(const EnvArrays<R>& A, const ResetConst& K, int nax, int n_sm, const uint8_t* mask, int expect, cudaStream_t s);
 // exo_begin_kernel: start the prefetched episode (slot flip, counts = 2, first observation) of the envs of work list
 // K.list (>= 0; `count_hint` bounds the grid) or selected by mask (NULL: all), appending them to work list K.append.
 template <typename R>

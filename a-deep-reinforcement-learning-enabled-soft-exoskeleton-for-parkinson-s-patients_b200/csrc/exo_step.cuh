@@ -204,7 +204,9 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
     constexpr int WARPS = EXO_STEP_THREADS / 32;
     constexpr int NAXV = (NAX + 3) / 4;                               // vectors per tremor-table row
     // Per-warp staging (no block barrier anywhere): obs chunks 0..10 | per-episode parameter vectors, later reused for
-    // obs chunks 11..19 | the warp's 32 action rows. Pitches of 11 and 9 sixteen-byte chunks are odd: conflict-free.
+    // obs chunks 11..19 | the warp's 32 action rows. Pitches of 11 and 9 sixteen-byte chunks are odd: the STS.128 / LDS.128 of
+    // these two tiles are conflict-free (ncu still counts ~28 conflicting wavefronts per warp in the kernel, 10.9 % of its
+    // shared-memory wavefronts, in the LDGSTS copies).
     constexpr int EPB_BYTES = (NV_EP * 32 * (int)sizeof(V4<R>) > 32 * 9 * 16) ? NV_EP * 32 * (int)sizeof(V4<R>) : 32 * 9 * 16;
     __shared__ __align__(16) float4 s_obsA[WARPS][32 * 11];
     __shared__ __align__(16) unsigned char s_epB[WARPS][EPB_BYTES];
@@ -299,6 +301,16 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
             ld4_ro_ord(tts + ((size_t)c * st + ec) * NAXV + h, tc + 4 * h);
             ld4_ro_ord(tts + ((size_t)(c + 1) * st + ec) * NAXV + h, tp + 4 * h);
         }
+    }
+    if (K.fused_begin && valid && c_raw + 2 >= L) {
+        // this env's episode ends in this step: pull the first rows of its NEXT episode's parameters (spare slot) towards L2
+        // now, so the episode-start path at the end of the kernel does not wait for DRAM
+        const V4<R>* epn = S.ep + (size_t)(slot ^ 1) * S.ep_slot;
+        const V4<R>* ttn = S.tt + (size_t)(slot ^ 1) * S.tt_slot;
+#pragma unroll
+        for (int v = 0; v < NV_EP; v++) asm volatile("prefetch.global.L2 [%0];" :: "l"(epn + (size_t)v * st + ec));
+#pragma unroll
+        for (int k = 0; k < 3; k++) asm volatile("prefetch.global.L2 [%0];" :: "l"(ttn + ((size_t)k * st + ec) * NAXV));
     }
     const R* mo = S.motion + (size_t)mid * 5 * S.max_len;
     R mrow[5], mnext[5];

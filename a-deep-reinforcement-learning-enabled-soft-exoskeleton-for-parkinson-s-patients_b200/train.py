@@ -78,6 +78,11 @@ def train_device(n_steps, tremor_sequence=(0, 1, 0, 1, 0, 0, 0), replicas=1, num
     tremor_num = torch.from_numpy(motion).to(dev)
     ep_length = int(env.motion_lengths.max())
     exploration = float(hp.exploration_noise)
+    # the reference lowers the exploration noise once per select_action call = once per LIVE env per step (select_action,
+    # TD7_multi_agent_Pink_noise.py:208-228, is called per env, Exoskeleton_agent_train.py:125-129); episode t of motion m is live
+    # for steps t < L_m - 3, which the host knows without a device sync
+    ep_steps = (env.motion_lengths[motion].astype(np.int64) - 3)
+    live_per_step = np.array([int((ep_steps > t).sum()) for t in range(int(env.motion_lengths.max()))], dtype=np.int64)
     steps_count, allow_train = 0, False
     out = dict(episode_return=[], episode_len=[], train_iterations=0, env_steps=0)
     t0 = time.perf_counter()
@@ -93,7 +98,7 @@ def train_device(n_steps, tremor_sequence=(0, 1, 0, 1, 0, 0, 0), replicas=1, num
         for t in range(ep_length):
             if allow_train:
                 act = (policy.forward(obs, use_checkpoint=False) + noise[:, :, t]).clamp_(-1.0, 1.0)
-                exploration -= agent.action_noise_decrease
+                exploration -= agent.action_noise_decrease * int(live_per_step[t])
             else:
                 act = torch.rand(n, 7, device=dev, generator=gen) * 2.0 - 1.0
             nxt, rew, done = env.step(act)

@@ -43,8 +43,8 @@ UNIT = "env-steps/s"
 ALGO_BYTES_PER_ENV_STEP = 1045
 # dram__bytes_read.sum + dram__bytes_write.sum of one exo_step_kernel<float,false,4> launch over 65 536 envs, from the
 # ncu --set full capture named in TRAFFIC_SOURCE (refreshed per round from the final code)
-STEP_KERNEL_DRAM_BYTES_65536 = 34234368
-TRAFFIC_SOURCE = "profiles/r01g_ncu_full_step.txt"
+STEP_KERNEL_DRAM_BYTES_65536 = 34154496 + 321792       # r02e: 34.15 MB read (= 521 B/env) + 0.32 MB written (the rest stays in L2)
+TRAFFIC_SOURCE = "profiles/r02e_ncu_full_step.txt"
 DEPHASE_PERIOD = 347          # longest reference motion: every env is reset once during the pre-roll
 MEAN_EPISODE_STEPS = float(np.mean([l - 3 for l in (232, 316, 282, 295, 270, 347, 266, 273)]))
 
@@ -56,6 +56,14 @@ def reset_bytes(table_len_mean=MEAN_EPISODE_STEPS + 3, nax=4, real=4):
     return 2 * 2500 + table_len_mean * nax * real + 147 * 8 + 44 * real + 49 * real + 320 + 48 * real
 
 
+def settle(env):
+    """env.reset() queues a generation pass for every env on the handle's side streams (~2 ms at 65 536 envs): let it
+    finish before a timed section, which would otherwise run beside it."""
+    import torch
+    env.wait_prefetch()
+    torch.cuda.synchronize(env.device)
+
+
 def dephase(env, actions, period=DEPHASE_PERIOD):
     """Untimed set-up: spread the envs over their episodes. env e is reset at pre-roll step e mod period; all envs step."""
     import torch
@@ -64,6 +72,7 @@ def dephase(env, actions, period=DEPHASE_PERIOD):
     for t in range(period):
         env.reset((phase == t).to(torch.uint8))
         env.step(actions[t % actions.shape[0]], keep_idle_obs=False)
+    settle(env)
 
 
 def population(n_per_gpu, rank, world):
@@ -149,6 +158,7 @@ def bench_lap(exo_b200, env, actions, dev, flush):
     E, MAX, B = 8, 250000, 128
     buf = exo_b200.LAP(80, 7, dev, E, max_size=MAX, batch_size=B)
     obs = env.reset().clone()
+    settle(env)
     evs = []
     steps = 40
     for t in range(steps):
@@ -215,6 +225,7 @@ def bench_policy(exo_b200, env, dev, flush, peaks, weights=None):
         sd = synthetic_policy_state_dict()
         pol.set_networks(sd, sd, "checkpoint")
     obs = env.reset().clone()
+    settle(env)
     act = torch.empty(n, 7, device=dev)
     for _ in range(3):
         pol.forward(obs, use_checkpoint=True, out=act)
@@ -339,6 +350,7 @@ def bench_large_population(exo_b200, dev, flush, peak, precision, n_large=524288
     gen = torch.Generator(device=dev).manual_seed(99)
     acts = [torch.rand(n_large, 7, device=dev, generator=gen) * 2 - 1 for _ in range(2)]
     env.reset()
+    settle(env)
     for t in range(5):
         env.step(acts[t % 2], keep_idle_obs=False)
     ev = []
@@ -446,6 +458,7 @@ def bench_cfg4(exo_b200, args, rank, world, dev, flush, peak, barrier):
     dist.all_reduce(ar, op=dist.ReduceOp.MAX)
     env.set_auto_reset(False)
     env.reset()
+    settle(env)
     kev = []
     for t in range(20):
         if flush is not None:
@@ -554,6 +567,7 @@ def main():
     import exo_b200
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    host_pin = exo_b200.hostpin.pin_to_gpu(local_rank)     # before any pinned allocation: the host buffers land next to the GPU
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
@@ -609,6 +623,7 @@ def main():
     # ---- dominant kernel alone (exo_step_kernel): auto-reset off, all envs live, flush between launches
     env.set_auto_reset(False)
     env.reset()
+    settle(env)
     ksteps = min(args.kernel_steps, 200)
     for t in range(3):
         env.step(actions[t % n_act], keep_idle_obs=False)
@@ -625,9 +640,27 @@ def main():
     kms = float(np.mean([a.elapsed_time(b) for a, b in zip(k0, k1)]))
     clocks = sampler.stop()
 
-    # ---- end to end through the host-buffer C-ABI call (exo_step_host): pinned H2D + kernels + D2H + sync per step
+    # ---- end to end through the host-buffer C-ABI call (exo_step_host): pinned H2D + kernels + D2H + sync per step.
+    #      First the ceiling: the bare pinned device->host copy of one step's observations from every rank at once.
     env.set_auto_reset(True)
     env.reset()
+    settle(env)
+    obs_h = torch.zeros(n, 80).pin_memory()
+    obs_d = torch.zeros(n, 80, device=dev)
+    for _ in range(3):
+        obs_h.copy_(obs_d, non_blocking=True)
+    barrier()
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0.record()
+    for _ in range(20):
+        obs_h.copy_(obs_d, non_blocking=True)
+    c1.record()
+    barrier()
+    d2h_ms = torch.tensor([c0.elapsed_time(c1) / 20.0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(d2h_ms, op=dist.ReduceOp.MAX)
+    d2h_ms = float(d2h_ms.item())
+    del obs_h, obs_d
     host_actions = [(torch.rand(n, 7) * 2 - 1).pin_memory() for _ in range(4)]
     for t in range(3):
         env.step_host(host_actions[t % 4])
@@ -697,7 +730,11 @@ def main():
                              "sample": "%d envs x %d steps (%.1f s) of the same population, oracle/exo_oracle.c fp64 with scipy-RK45 "
                                        "restated, %d pthreads" % (args.cpu_sample, args.cpu_steps, cpu_secs, cpu_cores)},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 7 * 4, "d2h_bytes_per_step": n * (80 * 4 + rbytes + 1),
-                    "steps": args.e2e_steps, "call": "exo_step_host (pinned host buffers)"},
+                    "steps": args.e2e_steps, "call": "exo_step_host (pinned host buffers)",
+                    "d2h_ceiling": {"what": "bare concurrent pinned D2H of one step's observations (%.1f MB) from all %d ranks" % (n * 320 / 1e6, world),
+                                    "gbs_per_rank": n * 320 / (d2h_ms * 1e-3) / 1e9, "env_steps_per_s": world * n / (d2h_ms * 1e-3),
+                                    "e2e_fraction_of_ceiling": e2e_value / (world * n / (d2h_ms * 1e-3))},
+                    "host_placement": host_pin},
             "gpu_launches": int(launches),
             "clocks": clocks,
         }

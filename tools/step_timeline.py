@@ -19,7 +19,7 @@ import exo_b200  # noqa: E402
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
 motion, seqs, seeds = bench.population(n, 0, 1)
 env = exo_b200.BatchedExoskeletonEnv(motion, seqs, seeds, device="cuda:0", auto_reset=True, **bench.TRAIN)
-env.reset()
+env.reset(); env.wait_prefetch(); torch.cuda.synchronize()
 g = torch.Generator(device="cuda").manual_seed(0)
 acts = torch.rand(4, n, 7, device="cuda", generator=g) * 2 - 1
 flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
