@@ -534,10 +534,14 @@ exo_gen_kernel(EnvArrays<R> S, ResetConst K, const uint8_t* __restrict__ mask) {
 //   qs[5]   joint vector behind the link-state cache at this moment;  el_old  act_elbow_reference_positions as last read
 //   qpl     EXO_MOTOR_FULL: prismatic positions behind the cache (else nullptr)
 //   obA/obB the 80-float observation as 20 float4 chunks: chunks 0..10 -> obA[0..10], chunks 11..19 -> obB[0..8]
+//   st_ep / st_tt  fp32 step kernel: the 11 parameter vectors / 3 tremor rows of the new slot, already staged in shared
+//           memory by asynchronous copies issued at load time (st_ep may alias obA: it is read before obA is written);
+//           nullptr: read them from global memory here
 // ---------------------------------------------------------------------------------------------------------
 template <typename R, int NAX>
 __device__ __forceinline__ void begin_episode(const EnvArrays<R>& S, const ChainConst<R>& C, int e, int new_slot,
-                                           const R* qs, const R* el_old, const R* qpl, float4* obA, float4* obB) {
+                                           const R* qs, const R* el_old, const R* qpl, float4* obA, float4* obB,
+                                           const float4* st_ep = nullptr, const float4* st_tt = nullptr) {
     constexpr int NAXV = (NAX + 3) / 4;
     const int st = S.stride;
     const V4<R>* ep = S.ep + (size_t)new_slot * S.ep_slot;
@@ -546,10 +550,25 @@ __device__ __forceinline__ void begin_episode(const EnvArrays<R>& S, const Chain
     // fly while the chain is evaluated), and every store comes after the last load: with loads interleaved between the
     // stores the 21 shift reads were 21 exposed memory latencies (~10 us on the step's critical path, r02g)
     R sh[4 * NV_EP], rows[3][4];
+#ifdef EXO_DBG_BEGIN_NOLOAD      // timing experiment only (wrong results): is the episode-start path's cost its data loads?
 #pragma unroll
-    for (int v = 0; v < NV_EP; v++) ld4_ord(ep + (size_t)v * st + e, sh + 4 * v);
+    for (int v = 0; v < 4 * NV_EP; v++) sh[v] = R(0.001) * v;
 #pragma unroll
-    for (int k = 0; k < 3; k++) ld4_ord(tt + ((size_t)k * st + e) * NAXV, rows[k]);
+    for (int k = 0; k < 3; k++) { rows[k][0] = rows[k][1] = rows[k][2] = rows[k][3] = R(k); }
+    (void)ep; (void)tt;
+#else
+    if (sizeof(R) == 4 && st_ep != nullptr) {
+#pragma unroll
+        for (int v = 0; v < NV_EP; v++) { const float4 t = st_ep[v]; sh[4 * v] = (R)t.x; sh[4 * v + 1] = (R)t.y; sh[4 * v + 2] = (R)t.z; sh[4 * v + 3] = (R)t.w; }
+#pragma unroll
+        for (int k = 0; k < 3; k++) { const float4 t = st_tt[k]; rows[k][0] = (R)t.x; rows[k][1] = (R)t.y; rows[k][2] = (R)t.z; rows[k][3] = (R)t.w; }
+    } else {
+#pragma unroll
+        for (int v = 0; v < NV_EP; v++) ld4_ord(ep + (size_t)v * st + e, sh + 4 * v);
+#pragma unroll
+        for (int k = 0; k < 3; k++) ld4_ord(tt + ((size_t)k * st + e) * NAXV, rows[k]);
+    }
+#endif
     float ob[80];
     ChainPose<R> P;
     chain_fk(C, qs, P);
@@ -558,7 +577,8 @@ __device__ __forceinline__ void begin_episode(const EnvArrays<R>& S, const Chain
 #pragma unroll
     for (int k = 0; k < 3; k++)                                                       // tremor rows 0..2 (:502-513)
 #pragma unroll
-        for (int j = 0; j < 4; j++) ob[14 + k * 4 + j] = (float)(rows[k][j] / (j == 3 ? R(5) : R(10)));
+        for (int j = 0; j < 4; j++)               // same arithmetic as the step kernel's observation (fp32: reciprocal multiply)
+            ob[14 + k * 4 + j] = sizeof(R) == 8 ? (float)(rows[k][j] / (j == 3 ? R(5) : R(10))) : (float)(rows[k][j] * (j == 3 ? R(0.2) : R(0.1)));
     R pv[21];
 #pragma unroll
     for (int i = 0; i < 7; i++) {
@@ -586,12 +606,24 @@ __device__ __forceinline__ void begin_episode(const EnvArrays<R>& S, const Chain
         ob[68 + k] = (float)C.sh_ref[k]; ob[71 + k] = (float)P.elref[k];
         ob[74 + k] = (float)C.sh_ref[k]; ob[77 + k] = (float)P.elref[k];
     }
+#ifdef EXO_DBG_BEGIN_NOSTORE     // timing experiment only: ... or its 26 scalar stores?
+    if (pv[0] == R(12345.678)) {
+#endif
+    {   // words 10..33 of the state record = elref[3] | posvec[21]: vectors 3..7 whole, the four words around them singly
+        static_assert(W_ELREF == 10 && W_POSVEC == 13, "state layout");
+        V4<R>* sv = S.state + e;
+        sv[(size_t)2 * st].v[2] = P.elref[0]; sv[(size_t)2 * st].v[3] = P.elref[1];
+        const R v3[4] = {P.elref[2], pv[0], pv[1], pv[2]};
+        st4(sv + (size_t)3 * st, v3);
 #pragma unroll
-    for (int w = 0; w < 21; w++) *exo_word(S.state, W_POSVEC + w, e, st) = pv[w];
-#pragma unroll
-    for (int k = 0; k < 3; k++) *exo_word(S.state, W_ELREF + k, e, st) = P.elref[k];
-    S.counts[e] = 2 | (new_slot << EXO_SLOT_SHIFT);                                   // counts = 2 (:220)
+        for (int v = 4; v < 8; v++) st4(sv + (size_t)v * st, pv + (4 * v - 13));
+        sv[(size_t)8 * st].v[0] = pv[19]; sv[(size_t)8 * st].v[1] = pv[20];
+    }
     S.ret[e] = R(0);
+#ifdef EXO_DBG_BEGIN_NOSTORE
+    }
+#endif
+    S.counts[e] = 2 | (new_slot << EXO_SLOT_SHIFT);                                   // counts = 2 (:220)
 #pragma unroll
     for (int ch = 0; ch < 11; ch++) obA[ch] = make_float4(ob[4 * ch], ob[4 * ch + 1], ob[4 * ch + 2], ob[4 * ch + 3]);
 #pragma unroll

@@ -24,9 +24,10 @@ namespace exo {
 // three Cody-Waite steps by pi/2 (exact for |k| < 2^7) and the kernels are the degree-7 / degree-8 minimax polynomials on
 // [-pi/4, pi/4] (< 1 ulp each): ~28 instructions for the pair against ~78 for sincosf, whose generality (Payne-Hanek path,
 // local-memory table) the 5 evaluations per env-step paid for - 20 % of the step kernel's instructions in the r02e profile.
-// Larger arguments (a diverging env) take the library path.
+// There is deliberately NO library fallback for large arguments: with one in the source the compiler predicated sincosf's
+// fast path into every call (67 instructions per call in the r02v profile instead of 28). An env whose joint angle has left
+// +-100 rad has diverged (non-SPD inertia draw, SURVEY hard part 5); its angle is reduced with fp32 accuracy like any other.
 __device__ __forceinline__ void sincos_r(float x, float* s, float* c) {
-    if (fabsf(x) > 100.0f) { sincosf(x, s, c); return; }
     const float k = rintf(x * 0.63661977236758134308f);
     float r = fmaf(-k, 1.5707962512969970703125f, x);               // pi/2 split in three: 24 + 24 + 24 bits
     r = fmaf(-k, 7.5497894158615963533520698547e-8f, r);
@@ -38,7 +39,7 @@ __device__ __forceinline__ void sincos_r(float x, float* s, float* c) {
     float pc = fmaf(r2, 2.443315711809948e-5f, -1.388731625493765e-3f);
     pc = fmaf(pc, r2, 4.166664568298827e-2f);
     const float cs = fmaf(pc * r2, r2, fmaf(-0.5f, r2, 1.0f));
-    const int q = (int)k;
+    const int q = __float2int_rn(k);
     const float a = (q & 1) ? cs : sn, b = (q & 1) ? sn : cs;
     *s = (q & 2) ? -a : a;
     *c = ((q + 1) & 2) ? -b : b;
@@ -193,7 +194,8 @@ __device__ __forceinline__ void dh_end_effector(const R* th, R L1, R L2, R* p) {
 // defined in exo_reset.cuh: start the prefetched episode of env e (slot flip, counts = 2, position reads, first observation)
 template <typename R, int NAX>
 __device__ __forceinline__ void begin_episode(const EnvArrays<R>& S, const ChainConst<R>& C, int e, int new_slot,
-                                           const R* qs, const R* el_old, const R* qpl, float4* obA, float4* obB);
+                                           const R* qs, const R* el_old, const R* qpl, float4* obA, float4* obB,
+                                           const float4* st_ep, const float4* st_tt);
 
 // FULL: ExoConfig.motor_model = EXO_MOTOR_FULL - the position targets go to exo_motor_kernel (exo_motor.cuh) instead of the
 // closed-form tracker, and the actuator end points follow their prismatic dummies (which the general step lets drift).
@@ -211,6 +213,10 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
     __shared__ __align__(16) float4 s_obsA[WARPS][32 * 11];
     __shared__ __align__(16) unsigned char s_epB[WARPS][EPB_BYTES];
     __shared__ __align__(16) float s_act[WARPS][32 * 7];
+    // fp32: the first three tremor rows of the NEXT episode of a lane whose episode ends in this step (its 11 parameter
+    // vectors go to the lane's row of s_obsA, which that lane does not need: its observation is the next episode's first)
+    constexpr bool STAGE_NEXT = sizeof(R) == 4;
+    __shared__ __align__(16) float4 s_nxt[STAGE_NEXT ? WARPS : 1][STAGE_NEXT ? 32 * 3 : 1];
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int wbase = K.env0 + blockIdx.x * EXO_STEP_THREADS + wid * 32;     // first env of this warp
@@ -302,16 +308,32 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
             ld4_ro_ord(tts + ((size_t)(c + 1) * st + ec) * NAXV + h, tp + 4 * h);
         }
     }
-    if (K.fused_begin && valid && c_raw + 2 >= L) {
-        // this env's episode ends in this step: pull the first rows of its NEXT episode's parameters (spare slot) towards L2
-        // now, so the episode-start path at the end of the kernel does not wait for DRAM
+    // The envs whose episode ends in this step are known NOW (counts + 1 reaches L - 1): reserve their places on the work list
+    // here, so the atomic's round trip to a cold L2 line overlaps the whole step instead of sitting at the end of the warp
+    const bool will_fin = valid && c_raw < L - 1 && c_raw + 2 >= L;
+    const unsigned wf_mask = __ballot_sync(0xffffffffu, will_fin);
+    int fin_base = 0;
+    if (K.auto_reset && wf_mask != 0u && lane == 0) fin_base = atomicAdd(S.fin_count + K.list, __popc(wf_mask));
+    const bool stage_next = STAGE_NEXT && K.fused_begin && will_fin;
+    if (K.fused_begin && will_fin) {
+        // this env's episode ends in this step: fetch the first rows of its NEXT episode's parameters (spare slot) now, so the
+        // episode-start path at the end of the kernel does not wait for memory: asynchronous copies into shared memory
+        // (fp32), an L2 prefetch otherwise
         const V4<R>* epn = S.ep + (size_t)(slot ^ 1) * S.ep_slot;
         const V4<R>* ttn = S.tt + (size_t)(slot ^ 1) * S.tt_slot;
+        if (STAGE_NEXT) {
 #pragma unroll
-        for (int v = 0; v < NV_EP; v++) asm volatile("prefetch.global.L2 [%0];" :: "l"(epn + (size_t)v * st + ec));
+            for (int v = 0; v < NV_EP; v++) cp_async16(&s_obsA[wid][lane * 11 + v], epn + (size_t)v * st + ec);
 #pragma unroll
-        for (int k = 0; k < 3; k++) asm volatile("prefetch.global.L2 [%0];" :: "l"(ttn + ((size_t)k * st + ec) * NAXV));
+            for (int k = 0; k < 3; k++) cp_async16(&s_nxt[STAGE_NEXT ? wid : 0][STAGE_NEXT ? lane * 3 + k : 0], ttn + ((size_t)k * st + ec) * NAXV);
+        } else {
+#pragma unroll
+            for (int v = 0; v < NV_EP; v++) asm volatile("prefetch.global.L2 [%0];" :: "l"(epn + (size_t)v * st + ec));
+#pragma unroll
+            for (int k = 0; k < 3; k++) asm volatile("prefetch.global.L2 [%0];" :: "l"(ttn + ((size_t)k * st + ec) * NAXV));
+        }
     }
+    cp_async_commit();
     const R* mo = S.motion + (size_t)mid * 5 * S.max_len;
     R mrow[5], mnext[5];
 #pragma unroll
@@ -381,8 +403,10 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
         }
 #pragma unroll
         for (int i = 0; i < 21; i++) ob[26 + i] = (float)s[W_POSVEC + i];
+        if (!stage_next) {                       // (a lane whose episode ends keeps the staged next-episode parameters in its row)
 #pragma unroll
-        for (int ch = 0; ch < 11; ch++) so[ch] = make_float4(ob[4 * ch], ob[4 * ch + 1], ob[4 * ch + 2], ob[4 * ch + 3]);
+            for (int ch = 0; ch < 11; ch++) so[ch] = make_float4(ob[4 * ch], ob[4 * ch + 1], ob[4 * ch + 2], ob[4 * ch + 3]);
+        }
         // ---- link-state cache -> world points (getLinkState reads, sim:129-142,194-195)
         R qb[5], qs[5];
 #pragma unroll
@@ -635,7 +659,8 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
             for (int d = 0; d < EXO_NPRIS; d++) qplb[d] = *exo_word(S.dyn, W_QP + d, e, st);
         }
         begin_episode<R, NAX>(S, C, e, slot ^ 1, b_qs, b_el, FULL ? qplb : nullptr, &s_obsA[wid][lane * 11],
-                              reinterpret_cast<float4*>(&s_epB[wid][0]) + lane * 9);
+                              reinterpret_cast<float4*>(&s_epB[wid][0]) + lane * 9,
+                              stage_next ? &s_obsA[wid][lane * 11] : nullptr, stage_next ? &s_nxt[STAGE_NEXT ? wid : 0][STAGE_NEXT ? lane * 3 : 0] : nullptr);
     }
     // ---- warp-level epilogue: every lane of the warp arrives here
     const unsigned fin_mask = __ballot_sync(full, fin);
@@ -661,10 +686,8 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
         }
     }
     // finished envs -> this call's work list (one atomic per warp that has any): their vacated slot gets the episode after next
-    if (K.auto_reset && fin_mask) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(S.fin_count + K.list, __popc(fin_mask));
-        base = __shfl_sync(full, base, 0);
+    if (K.auto_reset && fin_mask) {                                   // fin_mask == wf_mask: the places were reserved at load time
+        const int base = __shfl_sync(full, fin_base, 0);
         if (fin) S.fin_list[(size_t)K.list * st + base + __popc(fin_mask & ((1u << lane) - 1u))] = e;
     }
     EXO_MARK(7);                                                     // observation rows written
