@@ -190,3 +190,57 @@ def test_reference_stream_reproduces_the_shared_numpy_stream_bit_for_bit(exo):
     G = rsm.propagator(d["mat/I"], d["mat/D"], d["mat/S"])
     for T, q in zip(d["ode/T"], d["ode/q"]):
         assert np.max(np.abs(G @ T - q)) <= 1e-3 * max(np.max(np.abs(q)), 1e-9)
+
+
+def test_episode_suppression_log_matches_the_training_scripts_numpy_statistics(exo):
+    """Per-env medians / standard deviations / means of the training script (Simulation/Exoskeleton_agent_train.py:150-205
+    per step, :239-265 per episode; VERDICT r01 'missing' 7): exo_b200.metrics.EpisodeSuppressionLog against a literal numpy
+    restatement of the script's loop on the same synthetic info."""
+    import torch
+    rs = np.random.RandomState(4)
+    n, T = 5, 37
+    lens = [37, 30, 37, 12, 25]
+    log = exo.metrics.EpisodeSuppressionLog(n, T, "cpu", disregard=True)
+    red_full, ampl_full, tot_full = [], [], []
+    when, when_ampl = np.zeros((n, 2)), np.zeros((n, 2))
+    for t in range(T):
+        info = {k: rs.uniform(-2, 2, (n, 7)) for k in ("torque_val", "tremor_torque_val", "ampl_val", "tremor_ampl_val")}
+        info["tremor_torque_val"][:, 4:] = 0.0                        # axes without tremor: 0/0 -> nan -> 0
+        info["torque_val"][:, 4:] = 0.0
+        info["amp_metric"] = rs.uniform(-50, 50, n)
+        live = np.array([t < l - 3 for l in lens])
+        log.add({k: torch.from_numpy(v) for k, v in info.items()}, torch.from_numpy(live))
+        red_ep, ampl_ep, tot_ep = np.zeros((n, 7)), np.zeros((n, 7)), np.zeros(n)
+        for i in range(n):                                            # the script, line by line
+            if not live[i]:
+                continue
+            with np.errstate(all="ignore"):
+                tr = (abs(info["torque_val"][i]) - abs(info["tremor_torque_val"][i])) / abs(info["tremor_torque_val"][i]) * 100
+                ta = (abs(info["ampl_val"][i]) - abs(info["tremor_ampl_val"][i])) / abs(info["tremor_ampl_val"][i]) * 100
+            tr = np.nan_to_num(tr, nan=0, posinf=0, neginf=0)
+            ta = np.nan_to_num(ta, nan=0, posinf=0, neginf=0)
+            tot = info["amp_metric"][i]
+            when[i, 0] += np.sum(tr[:4] >= 0); when[i, 1] += np.sum(tr[:4] < 0)
+            if tot < 0:
+                when_ampl[i, 1] += 1; tot_ep[i] = tot
+            else:
+                when_ampl[i, 0] += 1
+            tr[tr > 0] = 0; ta[ta > 0] = 0
+            if len(np.nonzero(tr)[0]) > 0:
+                red_ep[i] = tr
+            if len(np.nonzero(ta)[0]) > 0:
+                ampl_ep[i] = ta
+        red_full.append(red_ep); ampl_full.append(ampl_ep); tot_full.append(tot_ep)
+    red_np, ampl_np, tot_np = np.array(red_full), np.array(ampl_full), np.array(tot_full)
+    s = {k: v.numpy() for k, v in log.summary(lens).items()}
+    for i in range(n):
+        a, b = red_np[:lens[i], i], ampl_np[:lens[i], i]
+        assert np.allclose(s["tremor_avg"][i], a.mean(0), atol=1e-12) and np.allclose(s["tremor_median"][i], np.median(a, 0), atol=1e-12)
+        assert np.allclose(s["tremor_std"][i], a.std(0), atol=1e-12)
+        assert np.allclose(s["tremor_ampl_avg"][i], b.mean(0), atol=1e-12) and np.allclose(s["tremor_ampl_median"][i], np.median(b, 0), atol=1e-12)
+        assert np.allclose(s["tremor_ampl_std"][i], b.std(0), atol=1e-12)
+        assert abs(s["tremor_sup_avg"][i] - a[a != 0].mean()) < 1e-12 and abs(s["tremor_sup_median"][i] - np.median(a[a != 0])) < 1e-12
+        assert abs(s["tremor_ampl_sup_avg"][i] - b[b != 0].mean()) < 1e-12
+        assert abs(s["tremor_ampl_total_avg"][i] - tot_np[:lens[i], i].mean()) < 1e-12
+        assert abs(s["tremor_occurrence_pct"][i] - when[i, 1] / when[i].sum() * 100) < 1e-12
+        assert abs(s["tremor_ampl_occurrence_pct"][i] - when_ampl[i, 1] / when_ampl[i].sum() * 100) < 1e-12
