@@ -7,7 +7,7 @@ LIB_PATH = os.environ.get("EXO_LIB", os.path.join(HERE, "libexo_env.so"))   # EX
 
 OBS_DIM, ACT_DIM, NLINKS, N_STATS = 80, 7, 19, 16
 F32, F64 = 0, 1
-ODE_PROPAGATOR = 0
+ODE_PROPAGATOR, ODE_RK45 = 0, 1
 MOTOR_IDEAL, MOTOR_FULL = 0, 1
 
 

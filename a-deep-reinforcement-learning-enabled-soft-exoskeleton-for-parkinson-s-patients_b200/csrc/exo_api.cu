@@ -289,7 +289,8 @@ static int alloc_arrays(ExoHandle* h, EnvArrays<R>& A) {
 extern "C" int exo_create(const ExoConfig* cfg, const ExoGeometry* geo, int32_t n_envs, int32_t device, ExoHandle** out) {
     if (!cfg || !geo || !out || n_envs <= 0) return fail(EXO_ERR_ARG, "exo_create: bad arguments");
     if (cfg->precision != EXO_F32 && cfg->precision != EXO_F64) return fail(EXO_ERR_ARG, "precision must be EXO_F32 or EXO_F64");
-    if (cfg->ode != EXO_ODE_PROPAGATOR) return fail(EXO_ERR_ARG, "ode mode %d is not built in this version", cfg->ode);
+    if (cfg->ode != EXO_ODE_PROPAGATOR && cfg->ode != EXO_ODE_RK45) return fail(EXO_ERR_ARG, "ode must be EXO_ODE_PROPAGATOR or EXO_ODE_RK45");
+    if (cfg->ode == EXO_ODE_RK45 && cfg->precision != EXO_F64) return fail(EXO_ERR_ARG, "EXO_ODE_RK45 is an fp64 verification mode: precision must be EXO_F64");
     if (cfg->motor_model != EXO_MOTOR_IDEAL && cfg->motor_model != EXO_MOTOR_FULL) return fail(EXO_ERR_ARG, "motor_model must be EXO_MOTOR_IDEAL or EXO_MOTOR_FULL");
     int ndev = 0;
     CK(cudaGetDeviceCount(&ndev));
@@ -417,6 +418,7 @@ static StepConst<R> step_const(const ExoHandle* h) {
     K.L1 = (R)h->cfg.humerus_length; K.L2 = (R)h->cfg.forearm_length;
     K.lag = h->cfg.link_state_lag; K.limits = h->cfg.joint_limits; K.auto_reset = h->cfg.auto_reset; K.metrics = h->cfg.metrics;
     K.motor_full = h->cfg.motor_model == EXO_MOTOR_FULL;
+    K.ode_rk45 = h->cfg.ode == EXO_ODE_RK45;
     K.env0 = 0; K.env1 = h->n;
     return K;
 }

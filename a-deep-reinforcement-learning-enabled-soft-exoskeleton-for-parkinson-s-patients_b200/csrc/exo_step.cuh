@@ -17,6 +17,7 @@
 #pragma once
 #include <type_traits>
 #include "exo_types.cuh"
+#include "exo_rk45.cuh"
 
 namespace exo {
 
@@ -506,19 +507,43 @@ exo_step_kernel(EnvArrays<R> S, ChainConst<R> C, StepConst<R> K, const float* __
         const R r2d = R(57.29577951308232087679815481410517), d2r = R(0.017453292519943295769236907684886);
         R qa[7], qt[7];
         constexpr int ROWS = INFO ? 7 : 4;
+        bool ode_done = false;
+        if constexpr (sizeof(R) == 8) {
+            if (K.ode_rk45) {
+                // verification mode (fp64 handles): the reference's own integrator, scipy's RK45 restated (exo_rk45.cuh), on
+                // this episode's I, D, S - twice per step as in Exoskeleton_env.py:409-414
+                const double* ids = S.IDS + ((size_t)slot * S.n + e) * EXO_IDS_PITCH;
+                double Tv[7], q7[7];
 #pragma unroll
-        for (int i = 0; i < ROWS; i++) {
-            R acc = 0, acc2 = 0;
+                for (int j = 0; j < 7; j++) Tv[j] = tv[j];
+                rk45_solve(ids, Tv, 1.0 / 40.0, q7);
 #pragma unroll
-            for (int j = 0; j < 7; j++) {
-                if (j < 4 || j < NAX) {
-                    const R gij = g[exo_g_word(i, j)];
-                    acc += gij * tv[j];
-                    if (INFO) acc2 += gij * ttc[j];
+                for (int i = 0; i < ROWS; i++) qa[i] = q7[i] * r2d;
+                if (INFO) {
+#pragma unroll
+                    for (int j = 0; j < 7; j++) Tv[j] = ttc[j];
+                    rk45_solve(ids, Tv, 1.0 / 40.0, q7);
+#pragma unroll
+                    for (int i = 0; i < 7; i++) qt[i] = q7[i] * r2d;
                 }
+                ode_done = true;
             }
-            qa[i] = acc * r2d;
-            if (INFO) qt[i] = acc2 * r2d;
+        }
+        if (!ode_done) {
+#pragma unroll
+            for (int i = 0; i < ROWS; i++) {
+                R acc = 0, acc2 = 0;
+#pragma unroll
+                for (int j = 0; j < 7; j++) {
+                    if (j < 4 || j < NAX) {
+                        const R gij = g[exo_g_word(i, j)];
+                        acc += gij * tv[j];
+                        if (INFO) acc2 += gij * ttc[j];
+                    }
+                }
+                qa[i] = acc * r2d;
+                if (INFO) qt[i] = acc2 * r2d;
+            }
         }
         // ---- angle composition + position motors + one Bullet step (:421-433, oracle/minibullet.py)
         const R tgt[5] = {(mrow[4] + qa[2]) * d2r, (mrow[3] + qa[0]) * d2r, (mrow[2] + qa[1]) * d2r, (mrow[0] + qa[3]) * d2r,

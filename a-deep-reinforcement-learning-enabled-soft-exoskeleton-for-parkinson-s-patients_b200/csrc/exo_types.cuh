@@ -130,7 +130,7 @@ struct StepConst {
     R fmax_sh0, fmax_el0;          // un-randomised maxima (obs normalisation, Exoskeleton_env.py:488-501)
     R inv_fmax_sh0, inv_fmax_el0;
     R L1, L2;                      // humerus / forearm length for the amplitude metric
-    int lag, limits, auto_reset, metrics, motor_full;
+    int lag, limits, auto_reset, metrics, motor_full, ode_rk45;
     long long* timeline;           // debug (EXO_STEP_TIMELINE): per warp 8 words: globaltimer at entry, smid, clock64 at 6 phase marks
     int stagger_cycles, n_sm;      // blocks of dispatch layer l = blockIdx / n_sm start their loads l * stagger_cycles late
     int list;                      // ring slot of the work list this step appends to (it clears the next one)

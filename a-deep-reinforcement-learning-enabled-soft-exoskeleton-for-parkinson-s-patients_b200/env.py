@@ -38,7 +38,8 @@ class BatchedExoskeletonEnv(object):
                  second_harmonics_interval, max_force_shoulder, max_force_elbow, dr_actuator_end_pos_shift=0.02,
                  dr_actuator_range=0.1, matrix_noise_fraction=0.1, device="cuda:0", precision="fp32", auto_reset=False,
                  reference_ctor=True, link_state_lag=1, joint_limits="off", metrics=False, motions=None, urdf=None,
-                 humerus_length=0.4, forearm_length=0.4, hand_length=0.05, motor_model="ideal", motor_options=None):
+                 humerus_length=0.4, forearm_length=0.4, hand_length=0.05, motor_model="ideal", motor_options=None,
+                 ode="propagator"):
         """motor_model: "ideal" - the fixed point of Bullet's motor solve, q+ = q + kp (target - q) (default);
         "full" - the general multibody step (forward dynamics + 50-sweep projected Gauss-Seidel, csrc/exo_motor.cuh);
         motor_options: dict of ExoMotorModel fields overriding pybullet's defaults (inertia_from_file, iterations,
@@ -78,7 +79,7 @@ class BatchedExoskeletonEnv(object):
         cfg.link_state_lag = int(link_state_lag)
         cfg.joint_limits = {"off": 0, "clamp": 1}[joint_limits]
         cfg.precision = self.precision
-        cfg.ode = _capi.ODE_PROPAGATOR
+        cfg.ode = {"propagator": _capi.ODE_PROPAGATOR, "rk45": _capi.ODE_RK45}[ode]     # "rk45": fp64 verification mode (exo_rk45.cuh)
         cfg.auto_reset = int(self.auto_reset)
         cfg.reference_ctor = int(bool(reference_ctor))
         cfg.metrics = int(bool(metrics))

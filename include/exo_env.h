@@ -36,7 +36,12 @@ typedef enum {
 } ExoStatus;
 
 enum { EXO_F32 = 0, EXO_F64 = 1 };
-enum { EXO_ODE_PROPAGATOR = 0 };   /* the only ODE mode: exact solution q(dt) = G T (scipy's RK45 lives in the oracle, ode_mode 0) */
+/* How the arm ODE of Utilities/calculate_joint_angles.py:5-22 is integrated over one dt from rest:
+ *   EXO_ODE_PROPAGATOR  exact solution q(dt) = G T, G built per episode in fp64 (default; the product path);
+ *   EXO_ODE_RK45        the reference's own integrator, scipy's RK45 at its default tolerances restated on the device
+ *                       (csrc/exo_rk45.cuh), fp64 handles only: a verification mode that removes RK45's own 1e-3 truncation
+ *                       error from comparisons with reference goldens. ~100x slower than the default. */
+enum { EXO_ODE_PROPAGATOR = 0, EXO_ODE_RK45 = 1 };
 /* What stands in for pybullet's stepSimulation (Exoskeleton_env.py:433) behind the POSITION_CONTROL motors
  * (Exoskeleton_sim_pybullet.py:109-117):
  *   EXO_MOTOR_IDEAL  the fixed point of Bullet's constraint solve, q+ = q + kp (target - q), inside the step kernel (default);
@@ -58,7 +63,7 @@ typedef struct {
     int32_t link_state_lag;   /* 1: getLinkState lags the joint state by one stepSimulation (default), 0: no lag */
     int32_t joint_limits;     /* 0: motor row wins (default), 1: clamp to the URDF limits */
     int32_t precision;        /* EXO_F32 | EXO_F64 */
-    int32_t ode;              /* EXO_ODE_PROPAGATOR: the linear ODE's exact solution from rest, q(dt) = G T, G built per episode in fp64 */
+    int32_t ode;              /* EXO_ODE_PROPAGATOR (default) | EXO_ODE_RK45 (fp64 verification mode) */
     int32_t auto_reset;       /* 1: exo_step re-initialises finished envs in the same call (obs = first obs of next episode) */
     int32_t reference_ctor;   /* 1: exo_seed also performs the constructor's draws: one rand() (Exoskeleton_env.py:70)
                                  and one initialize_movement (:172), so streams line up with the reference */

@@ -144,7 +144,39 @@ def test_against_reference_goldens_cfg2(exo, precision):
     env.close()
 
 
-def _replay_golden_episodes(exo, g, cases, precision, settings_case, label=""):
+def test_rk45_mode_reproduces_the_reference_goldens_without_the_integrator_gap(exo):
+    """ExoConfig.ode = EXO_ODE_RK45 (fp64): scipy's RK45 restated in the step kernel (csrc/exo_rk45.cuh), so the CUDA path
+    and the reference's Python (goldens: numpy RNG + scipy solve_ivp + the restated pybullet boundary) run the SAME
+    integrator. The default path's 1e-3 relative gap on ampl_val (RK45's own truncation error) disappears: angles to 1e-10
+    relative, torques 1e-11, observations equal as float32 up to the last bit, rewards 1e-9 - over all 15 tremor types x 8
+    motions, 30 steps (config 2)."""
+    g = np.load(os.path.join(GOLDEN, "ref_cfg2_types_x_motions.npz"))
+    cases = ["B%d" % i for i in range(120)]
+    env = exo.BatchedExoskeletonEnv([int(g[c + "/meta_motion"]) for c in cases], [g[c + "/meta_seq"] for c in cases],
+                                    [int(g[c + "/meta_seed"]) for c in cases], precision="fp64", ode="rk45", **case_settings(g, "B0"))
+    env.reset()
+    w = dict(ampl=0.0, tampl=0.0, torque=0.0, obs=0.0, reward=0.0, q=0.0)
+    for t in range(30):
+        a = np.stack([g[c + "/action"][t] for c in cases]).astype(np.float32)
+        ob, rw, dn, info = env.step(torch.from_numpy(a).cuda(), with_info=True)
+        ob, rw = ob.cpu().numpy(), rw.cpu().numpy()
+        inf = {k: v.cpu().numpy() for k, v in info.items()}
+        qb = env.get_field("q").cpu().numpy()
+        for i, c in enumerate(cases):
+            w["ampl"] = max(w["ampl"], rel(inf["ampl_val"][i], g[c + "/ampl_val"][t]))
+            w["tampl"] = max(w["tampl"], rel(inf["tremor_ampl_val"][i], g[c + "/tremor_ampl_val"][t]))
+            w["torque"] = max(w["torque"], rel(inf["torque_val"][i], g[c + "/torque_val"][t]))
+            w["obs"] = max(w["obs"], float(np.max(np.abs(ob[i] - g[c + "/obs"][t]))))
+            w["q"] = max(w["q"], float(np.max(np.abs(qb[i] - g[c + "/qb"][t]))))
+            w["reward"] = max(w["reward"], abs(float(rw[i]) - float(g[c + "/reward"][t])))
+    env.close()
+    print("RK45 mode vs reference goldens (cfg 2, 3600 env-steps): ampl_val rel %.2e  tremor_ampl_val rel %.2e  torque rel %.2e  "
+          "|d obs| %.2e  |dq| %.2e  |d reward| %.2e" % (w["ampl"], w["tampl"], w["torque"], w["obs"], w["q"], w["reward"]))
+    assert w["ampl"] <= 1e-10 and w["tampl"] <= 1e-10 and w["torque"] <= 1e-10 and w["q"] <= 1e-12
+    assert w["obs"] <= 2.4e-7 and w["reward"] <= 1e-9
+
+
+def _replay_golden_episodes(exo, g, cases, precision, settings_case, label="", ode="propagator"):
     """Replays golden families (reference Python on the restated pybullet boundary) through the CUDA path with auto-reset.
     Reward parity is checked term by term (info.reward_parts vs the golden's reward_* entries): the four smooth terms
     (unwanted, torque, control, smoothness) on EVERY step; the discontinuous axis_reward (a count of axes with
@@ -155,7 +187,7 @@ def _replay_golden_episodes(exo, g, cases, precision, settings_case, label=""):
     mids = [int(g[c + "/meta_motion"]) for c in cases]
     seqs = [g[c + "/meta_seq"] for c in cases]
     seeds = [int(g[c + "/meta_seed"]) for c in cases]
-    env = exo.BatchedExoskeletonEnv(mids, seqs, seeds, precision=precision, auto_reset=True, **case_settings(g, settings_case))
+    env = exo.BatchedExoskeletonEnv(mids, seqs, seeds, precision=precision, auto_reset=True, ode=ode, **case_settings(g, settings_case))
     obs = env.reset().cpu().numpy()
     nsteps = [len(g[c + "/action"]) for c in cases]
     max_reward = [float(g[c + "/meta_max_reward"]) for c in cases]
@@ -295,6 +327,21 @@ def test_against_reference_goldens_cfg1_trained_actor_1000_steps(exo, precision)
     # the shipped actor is near bang-bang: action -1 (zero force) on one side makes |torque| == |tremor| exactly there, so
     # a large, stable share of steps are axis ties (measured 0.40 of 1000); the smooth terms are held on ALL steps
     assert w["reward"] <= REWARD_TOL["A"] and w["smooth"] <= REWARD_TOL["A"] and w["tie_fraction"] <= TIE_FRACTION_A, w
+
+
+@pytest.mark.parametrize("family", ["A", "C"])
+def test_rk45_mode_full_episodes_with_auto_reset_against_reference_goldens(exo, family):
+    """The same replays as above with the reference's own integrator in the kernel (fp64, ode="rk45"): config 1 (shipped actor,
+    1000 steps over 4 resets) and config 3 (training DR, 8 full episodes + reset). With the integrator gap gone the CUDA
+    path follows the reference's Python run to float32 resolution in the observations and 1e-9 in the rewards, across
+    episode boundaries (auto-reset, per-env RNG stream continuing bit-exactly)."""
+    if family == "A":
+        g = np.load(os.path.join(GOLDEN, "ref_cfg1_trained_actor.npz"))
+        w = _replay_golden_episodes(exo, g, ["A0"], "fp64", "A0", "family A (cfg1), RK45 mode", ode="rk45")
+    else:
+        g = np.load(os.path.join(GOLDEN, "ref_cfg3_dr_episodes.npz"))
+        w = _replay_golden_episodes(exo, g, ["C%d" % m for m in range(8)], "fp64", "C0", "family C (cfg3), RK45 mode", ode="rk45")
+    assert w["obs"] <= 2.4e-7 and w["q"] <= 1e-10 and w["reward"] <= 1e-9 and w["smooth"] <= 1e-9, w
 
 
 def test_single_env_facade_matches_reference_signatures(exo):
