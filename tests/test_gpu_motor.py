@@ -92,11 +92,11 @@ def test_one_multibody_step_matches_the_cpu_model(exo, which):
     env.close()
 
 
-def _replay(exo, g, cases, precision, settings_case):
+def _replay(exo, g, cases, precision, settings_case, ode="propagator"):
     mids = [int(g[c + "/meta_motion"]) for c in cases]
     seqs = [g[c + "/meta_seq"] for c in cases]
     seeds = [int(g[c + "/meta_seed"]) for c in cases]
-    env = exo.BatchedExoskeletonEnv(mids, seqs, seeds, precision=precision, auto_reset=True, motor_model="full",
+    env = exo.BatchedExoskeletonEnv(mids, seqs, seeds, precision=precision, auto_reset=True, motor_model="full", ode=ode,
                                     **case_settings(g, settings_case))
     obs = env.reset().cpu().numpy()
     nsteps = [len(g[c + "/action"]) for c in cases]
@@ -137,6 +137,18 @@ def test_closed_loop_against_reference_env_on_the_general_step(exo, precision):
         print("%s %s: max |d obs| %.2e (first obs after reset %.2e)  |dq| %.2e  |dqd| %.2e  |dq_pris| %.2e  %.1f sweeps/step"
               % (precision, cases, w["obs"], w["obs0"], w["q"], w["qd"], w["qp"], sweeps))
         assert w["obs"] <= tol and w["obs0"] <= tol and w["q"] <= tol and w["qp"] <= tol, w
+
+
+def test_closed_loop_general_step_with_the_reference_integrator(exo):
+    """EXO_MOTOR_FULL + EXO_ODE_RK45 (fp64): both the integrator and the multibody step are now the ones the golden's
+    reference env ran on, so the closed loop must follow it far below the 1e-4 of the test above: the whole state - arm and
+    dummy joint positions and velocities of the general step included - to 1e-9, observations to float32 resolution."""
+    g = np.load(os.path.join(GOLDEN, "ref_full_motor.npz"))
+    for cases, sc in ((["F0"], "F0"), (["F1", "F2"], "F1")):
+        w, sweeps = _replay(exo, g, cases, "fp64", sc, ode="rk45")
+        print("fp64 rk45 %s: max |d obs| %.2e (first obs after reset %.2e)  |dq| %.2e  |dqd| %.2e  |dq_pris| %.2e  %.1f sweeps/step"
+              % (cases, w["obs"], w["obs0"], w["q"], w["qd"], w["qp"], sweeps))
+        assert w["obs"] <= 2.4e-7 and w["obs0"] <= 2.4e-7 and w["q"] <= 1e-9 and w["qd"] <= 1e-8 and w["qp"] <= 1e-9, w
 
 
 def test_general_step_converges_to_the_default_closed_form(exo):

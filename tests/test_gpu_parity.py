@@ -522,7 +522,10 @@ def test_training_script_suppression_metrics_on_device(exo, precision):
     """Next row N3: the per-step suppression metrics of Simulation/Exoskeleton_agent_train.py:150-193,
     accumulated by the step kernel, against the script's own numpy arithmetic applied to the kernel's info outputs
     (nan_to_num(nan=0, posinf=0, neginf=0), tremor_when_reduction counters, `disregard` masking). Counts are exact;
-    sums agree to the accumulation order (fp64 atomics) - 1e-9 relative in fp64, 1e-5 in fp32."""
+    sums agree to the accumulation order (fp64 atomics) - 1e-9 relative in fp64, 1e-5 in fp32.
+    Scope: this checks the REDUCTION (the script's arithmetic) on the kernel's own info tensors; that those info tensors are
+    the reference's is what test_info_outputs_and_amplitude_metric_vs_oracle (vs the oracle) and the golden replays - in
+    RK45 mode to 1e-12 against the reference's Python - establish."""
     n, steps = 960, 40
     env = exo.BatchedExoskeletonEnv([i % 8 for i in range(n)], [TYPES15[i % 15] for i in range(n)], list(range(n)),
                                     precision=precision, auto_reset=True, **TRAIN)
