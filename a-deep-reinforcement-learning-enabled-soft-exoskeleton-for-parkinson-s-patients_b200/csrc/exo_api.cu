@@ -213,6 +213,7 @@ static void cast_dyn(const DynConst<double>& s, DynConst<R>& d) {
     d.iterations = s.iterations; d.n_cons = s.n_cons;
     memcpy(d.cons, s.cons, sizeof(s.cons));
     memcpy(d.slot_dof, s.slot_dof, sizeof(s.slot_dof)); memcpy(d.dof_slot, s.dof_slot, sizeof(s.dof_slot));
+    memcpy(d.tri, s.tri, sizeof(s.tri)); memcpy(d.etri, s.etri, sizeof(s.etri));
 }
 
 extern "C" int exo_set_motor_model(ExoHandle* h, const ExoLinkDynamics* L, const ExoMotorModel* model) {
@@ -265,6 +266,14 @@ extern "C" int exo_set_motor_model(ExoHandle* h, const ExoLinkDynamics* L, const
     for (int ci = 0; ci < D.n_cons; ci++)
         if (D.cons[ci] >= 0) { D.slot_dof[slot] = D.cons[ci]; D.dof_slot[(int)D.cons[ci]] = (signed char)slot; slot++; }
     if (slot != EXO_NDOF) return fail(EXO_ERR_TOPOLOGY, "exo_set_motor_model: %d motor rows, expected %d", slot, EXO_NDOF);
+    for (int a = 0; a < EXO_NDOF; a++)
+        for (int b = 0; b < EXO_NDOF; b++) D.tri[a][b] = (unsigned char)(a >= b ? a * (a + 1) / 2 + b : b * (b + 1) / 2 + a);
+    memset(D.etri, 0, sizeof(D.etri));
+    for (int a = 0; a < D.n_cons && a < 19; a++)
+        for (int b = 0; b < D.n_cons && b < 19; b++) {
+            const int da = D.cons[a] >= 0 ? D.cons[a] : -D.cons[a] - 1, db = D.cons[b] >= 0 ? D.cons[b] : -D.cons[b] - 1;
+            D.etri[a][b] = D.tri[(int)D.dof_slot[da]][(int)D.dof_slot[db]];
+        }
     cast_dyn(D, h->Df);
     h->have_dyn = true;
     return 0;

@@ -43,36 +43,59 @@ template <typename R> __device__ __forceinline__ void rotate_inertia(const R* Rm
 }
 
 #define EXO_MOTOR_THREADS 64
+#ifndef EXO_MOTOR_BLOCKS
+#define EXO_MOTOR_BLOCKS 6      // resident 64-thread blocks per SM the fp32 instantiation is compiled for (<= 170 registers)
+#endif
 
+#define EXO_NTRI (EXO_NDOF * (EXO_NDOF + 1) / 2)
 #define EXO_NCONS 19             // 14 motor rows + the 5 revolute joints' limit constraints: the static solver path's list length
 
-template <typename R>
-__device__ __forceinline__ R pick14(const R* v, int s) {          // v[s] for a warp-uniform s without local memory
-    switch (s) {
-        case 0: return v[0]; case 1: return v[1]; case 2: return v[2]; case 3: return v[3]; case 4: return v[4];
-        case 5: return v[5]; case 6: return v[6]; case 7: return v[7]; case 8: return v[8]; case 9: return v[9];
-        case 10: return v[10]; case 11: return v[11]; case 12: return v[12]; default: return v[13];
+// The common case - no joint of any env of the warp at a bound (84 % of warps in the bench population) - leaves only the 14
+// motor rows, whose order is the solver-slot order by construction: every index below is a compile-time constant, the
+// velocity change is kept per slot, and a row costs 14 loads + FMAs. `big` collects "some row moved more than the exit
+// threshold": |dl| / dinv > sqrt(threshold), tested as |dl| > lim[r] = sqrt(threshold) * dinv[r] (fp32 handles; the fp64
+// instantiation keeps the CPU model's exact form res * res > threshold so that sweep counts agree bit for bit).
+__host__ __device__ constexpr int tri_c(int a, int b) { return a >= b ? a * (a + 1) / 2 + b : b * (b + 1) / 2 + a; }   // == DynConst::tri
+
+template <typename R, bool FWD>
+__device__ __forceinline__ void pgs_sweep_motors(const R* sM, const DynConst<R>& D, const R* dinv, const R* rhs, const R* lim,
+                                                 R* lam, R* dv, R& worst, bool& big) {
+    constexpr int NT = EXO_MOTOR_THREADS;
+#pragma unroll
+    for (int k = 0; k < EXO_NDOF; k++) {
+        const int r = FWD ? k : EXO_NDOF - 1 - k;
+        const R cap = D.slot_dof[r] < 5 ? D.cap_pos : D.cap_vel;
+        R dl = rhs[r] - dv[r] * dinv[r];
+        const R sum = lam[r] + dl;
+        if (sum < -cap) { dl = -cap - lam[r]; lam[r] = -cap; }
+        else if (sum > cap) { dl = cap - lam[r]; lam[r] = cap; }
+        else lam[r] = sum;
+#pragma unroll
+        for (int i = 0; i < EXO_NDOF; i++) dv[i] += sM[tri_c(i, r) * NT] * dl;       // compile-time offsets: LDS + FFMA per element
+        if (sizeof(R) == 8) { const R res = dl / dinv[r]; worst = fmax(worst, res * res); }
+        else big |= abs_r(dl) > lim[r];
     }
 }
 
 // One projected Gauss-Seidel sweep over Bullet's constraint list (19 entries, forward or backward). Entry ci is a motor row
 // (always present) or a joint-limit constraint (a row only in the threads where that joint is at / over a bound: bit ci of
-// `act`; bit ci of `neg` = the upper bound). Per-row data (rhs, 1/diag, impulse) is indexed by the compile-time ci, the
-// velocity change dv by solver slot (the 14 loads + FMAs per row have no branch); a row's own dv comes through pick14.
+// `act`; bit ci of `neg` = the upper bound). EVERYTHING is indexed by the compile-time entry index ci: rhs, 1/diag, impulse and
+// dvc[ci] = the velocity change so far of the joint entry ci acts on (a limit entry shares its joint with a motor entry and
+// carries its own copy). A row's impulse updates all 19 copies through D.etri[c2][ci] = the M^-1 entry (joint of c2, joint
+// of ci) - 19 loads + FMAs with constant-bank offsets, no run-time register index. (The first version kept dv per joint and
+// fetched a row's own dv through a 14-way switch: 28 % of the kernel's instructions, r02B.)
 template <typename R, bool FWD>
 __device__ __forceinline__ void pgs_sweep(const R* sM, const DynConst<R>& D, unsigned act, unsigned neg, const R* dinv,
-                                          const R* rhs, R* lam, R* dv, R& worst) {
+                                          const R* rhs, R* lam, R* dvc, R& worst) {
     constexpr int NT = EXO_MOTOR_THREADS;
 #pragma unroll
     for (int k = 0; k < EXO_NCONS; k++) {
         const int ci = FWD ? k : EXO_NCONS - 1 - k;
         const int cc = D.cons[ci];                                  // warp-uniform
         R imp, dl;
-        int sr;
         if (cc >= 0) {
-            sr = D.dof_slot[cc];
             const R cap = cc < 5 ? D.cap_pos : D.cap_vel;
-            dl = rhs[ci] - pick14(dv, sr) * dinv[ci];
+            dl = rhs[ci] - dvc[ci] * dinv[ci];
             const R sum = lam[ci] + dl;
             if (sum < -cap) { dl = -cap - lam[ci]; lam[ci] = -cap; }
             else if (sum > cap) { dl = cap - lam[ci]; lam[ci] = cap; }
@@ -80,9 +103,8 @@ __device__ __forceinline__ void pgs_sweep(const R* sM, const DynConst<R>& D, uns
             imp = dl;
         } else {
             if (!((act >> ci) & 1u)) continue;                       // divergent only in warps where a joint is at a limit
-            sr = D.dof_slot[-cc - 1];
             const R sg = ((neg >> ci) & 1u) ? R(-1) : R(1);
-            dl = rhs[ci] - sg * pick14(dv, sr) * dinv[ci];
+            dl = rhs[ci] - sg * dvc[ci] * dinv[ci];
             const R sum = lam[ci] + dl;
             if (sum < R(0)) { dl = -lam[ci]; lam[ci] = 0; }
             else if (sum > D.limit_cap) { dl = D.limit_cap - lam[ci]; lam[ci] = D.limit_cap; }
@@ -90,19 +112,22 @@ __device__ __forceinline__ void pgs_sweep(const R* sM, const DynConst<R>& D, uns
             imp = sg * dl;
         }
 #pragma unroll
-        for (int i = 0; i < EXO_NDOF; i++) dv[i] += sM[(i * EXO_NDOF + sr) * NT] * imp;
-        const R res = dl / dinv[ci];
+        for (int c2 = 0; c2 < EXO_NCONS; c2++) dvc[c2] += sM[D.etri[c2][ci] * NT] * imp;
+        const R res = div_r(dl, dinv[ci]);                        // fp64: IEEE division as in the CPU model; fp32: fast division
         worst = fmax(worst, res * res);
     }
 }
 
 template <typename R>
-__global__ void __launch_bounds__(EXO_MOTOR_THREADS)
+__global__ void __launch_bounds__(EXO_MOTOR_THREADS, sizeof(R) == 4 ? EXO_MOTOR_BLOCKS : 2)
 exo_motor_kernel(EnvArrays<R> S, ChainConst<R> C, DynConst<R> D, int lag, int env0, int env1) {
     constexpr int NT = EXO_MOTOR_THREADS;
     extern __shared__ __align__(16) unsigned char motor_smem[];
-    R* sM = reinterpret_cast<R*>(motor_smem) + threadIdx.x;                       // [14 * 14][NT]: M^-1 in solver-slot order
-    R* sV = reinterpret_cast<R*>(motor_smem) + EXO_NDOF * EXO_NDOF * NT + threadIdx.x;   // [14][NT]: reorder scratch
+    // M^-1 is symmetric: its 105 distinct entries in solver-slot order, entry D.tri[a][b] of thread t at [entry][t]. (The
+    // full 14 x 14 image, 54 KB per 64-thread block, held an SM to 8 warps; 30 KB lets all 14 warps of a 65 536-env launch be
+    // resident at once, and the solver is a dependent chain that only other warps can hide.)
+    R* sM = reinterpret_cast<R*>(motor_smem) + threadIdx.x;                       // [105][NT]
+    R* sV = reinterpret_cast<R*>(motor_smem) + EXO_NTRI * NT + threadIdx.x;        // [14][NT]: reorder scratch
     const int e = env0 + blockIdx.x * blockDim.x + threadIdx.x;
     const int st = S.stride;
     int sweeps_done = 0, did = 0;
@@ -344,12 +369,12 @@ exo_motor_kernel(EnvArrays<R> S, ChainConst<R> C, DynConst<R> D, int lag, int en
                 for (int k = 0; k < 5; k++) {
                     const int sk = D.dof_slot[k];
 #pragma unroll
-                    for (int l = 0; l < 5; l++) sM[(sk * EXO_NDOF + D.dof_slot[l]) * NT] = Sinv[k][l];
+                    for (int l = 0; l < 5; l++) sM[D.tri[sk][D.dof_slot[l]] * NT] = Sinv[k][l];
 #pragma unroll
                     for (int d = 0; d < EXO_NPRIS; d++) {
                         const int sd = D.dof_slot[5 + d];
-                        sM[(sk * EXO_NDOF + sd) * NT] = -W[k][d];
-                        sM[(sd * EXO_NDOF + sk) * NT] = -W[k][d];
+                        sM[D.tri[sk][sd] * NT] = -W[k][d];
+                        sM[D.tri[sd][sk] * NT] = -W[k][d];
                     }
                 }
 #pragma unroll
@@ -359,7 +384,7 @@ exo_motor_kernel(EnvArrays<R> S, ChainConst<R> C, DynConst<R> D, int lag, int en
                         R acc = (d == d2) ? R(1) / D.m_d[d] : R(0);
 #pragma unroll
                         for (int k = 0; k < 5; k++) acc += U[k][d] * W[k][d2];
-                        sM[(D.dof_slot[5 + d] * EXO_NDOF + D.dof_slot[5 + d2]) * NT] = acc;
+                        sM[D.tri[D.dof_slot[5 + d]][D.dof_slot[5 + d2]] * NT] = acc;
                     }
             }
             // physical DoF order -> slot order through the scratch column (static writes, uniform-address reads)
@@ -373,36 +398,76 @@ exo_motor_kernel(EnvArrays<R> S, ChainConst<R> C, DynConst<R> D, int lag, int en
 #pragma unroll
             for (int r = 0; r < EXO_NDOF; r++) qds[r] = sV[D.slot_dof[r] * NT];
             // ---- 5. unconstrained velocities (slot order), then one row per entry of Bullet's constraint list
-            R qdu[EXO_NDOF], dv[EXO_NDOF];
+            R qdu[EXO_NDOF];
 #pragma unroll
             for (int r = 0; r < EXO_NDOF; r++) {
                 R acc = 0;
 #pragma unroll
-                for (int c2 = 0; c2 < EXO_NDOF; c2++) acc -= sM[(r * EXO_NDOF + c2) * NT] * bs[c2];
+                for (int c2 = 0; c2 < EXO_NDOF; c2++) acc -= sM[tri_c(r, c2) * NT] * bs[c2];
                 qdu[r] = qds[r] + D.dt * acc;
-                dv[r] = 0;
             }
-            // per physical joint: motor target term kp (target - q) / dt, and the joint-limit penetrations
+            bool has_limit = false;
 #pragma unroll
-            for (int i = 0; i < EXO_NDOF; i++) sV[i * NT] = i < 5 ? D.kp * (tg[i] - q[i]) / D.dt : R(0);
+            for (int j = 0; j < 5; j++) has_limit |= (q[j] - C.lower[j] <= R(0)) || (C.upper[j] - q[j] <= R(0));
+            const unsigned amask0 = __activemask();
+            if (!__any_sync(amask0, has_limit)) {
+                // ---- 6m. motor rows only, slot order, all indices static
+#pragma unroll
+                for (int j = 0; j < 5; j++) sV[(5 + j) * NT] = D.kp * (tg[j] - q[j]) / D.dt;
+                R dinv[EXO_NDOF], rhs[EXO_NDOF], lam[EXO_NDOF], dv[EXO_NDOF], lim[EXO_NDOF];
+                const R sthr = sqrt_r(D.threshold);
+#pragma unroll
+                for (int r = 0; r < EXO_NDOF; r++) {
+                    const int dof = D.slot_dof[r];
+                    const R vu = qdu[r];
+                    const R desired = dof < 5 ? sV[(5 + dof) * NT] + vu + D.kd * (R(0) - vu) : vu + R(1) * (R(0) - vu);
+                    dinv[r] = R(1) / sM[tri_c(r, r) * NT];
+                    rhs[r] = (desired - vu) * dinv[r];
+                    lim[r] = sthr * dinv[r];
+                    lam[r] = 0; dv[r] = 0;
+                }
+                bool going = true;
+                for (int it = 0; it < D.iterations; it++) {
+                    if (going) {
+                        R worst = 0;
+                        bool big = false;
+                        if (it & 1) pgs_sweep_motors<R, true>(sM, D, dinv, rhs, lim, lam, dv, worst, big);
+                        else pgs_sweep_motors<R, false>(sM, D, dinv, rhs, lim, lam, dv, worst, big);
+                        sweeps_done++;
+                        if (sizeof(R) == 8 ? (worst <= D.threshold) : !big) going = false;
+                    }
+                    if (!__any_sync(amask0, going)) break;
+                }
+#pragma unroll
+                for (int r = 0; r < EXO_NDOF; r++) sV[r * NT] = qdu[r] + dv[r];      // new velocities, slot order
+            } else
             if (D.n_cons == EXO_NCONS) {
-                R dinv[EXO_NCONS], rhs[EXO_NCONS], lam[EXO_NCONS];
+                // per-entry data through the scratch column (static writes, warp-uniform-address reads; no register is
+                // indexed at run time): first q and kp (target - q) / dt of the five arm joints, then the unconstrained velocities
+#pragma unroll
+                for (int j = 0; j < 5; j++) { sV[j * NT] = q[j]; sV[(5 + j) * NT] = D.kp * (tg[j] - q[j]) / D.dt; }
+                R aux[EXO_NCONS];                                    // motor entry of an arm joint: its target term; limit entry: its joint angle
+#pragma unroll
+                for (int ci = 0; ci < EXO_NCONS; ci++) {
+                    const int cc = D.cons[ci];
+                    aux[ci] = cc >= 0 ? (cc < 5 ? sV[(5 + cc) * NT] : R(0)) : sV[(-cc - 1) * NT];
+                }
+#pragma unroll
+                for (int r = 0; r < EXO_NDOF; r++) sV[r * NT] = qdu[r];
+                R dinv[EXO_NCONS], rhs[EXO_NCONS], lam[EXO_NCONS], dvc[EXO_NCONS];
                 unsigned act = 0, neg = 0;
 #pragma unroll
                 for (int ci = 0; ci < EXO_NCONS; ci++) {
                     const int cc = D.cons[ci];
                     const int dof = cc >= 0 ? cc : -cc - 1, sr = D.dof_slot[dof];
-                    const R vu = pick14(qdu, sr);
-                    dinv[ci] = R(1) / sM[(sr * EXO_NDOF + sr) * NT];
-                    lam[ci] = 0;
+                    const R vu = sV[sr * NT];
+                    dinv[ci] = R(1) / sM[D.tri[sr][sr] * NT];
+                    lam[ci] = 0; dvc[ci] = 0;
                     if (cc >= 0) {
-                        const R desired = cc < 5 ? sV[cc * NT] + vu + D.kd * (R(0) - vu) : vu + R(1) * (R(0) - vu);
+                        const R desired = cc < 5 ? aux[ci] + vu + D.kd * (R(0) - vu) : vu + R(1) * (R(0) - vu);
                         rhs[ci] = (desired - vu) * dinv[ci];
                     } else {                                 // rows only while violated; lower and upper cannot both be
-                        R qj = q[0], lo = C.lower[0], hi = C.upper[0];
-#pragma unroll
-                        for (int j = 1; j < 5; j++) if (dof == j) { qj = q[j]; lo = C.lower[j]; hi = C.upper[j]; }
-                        const R pen_lo = qj - lo, pen_hi = hi - qj;
+                        const R pen_lo = aux[ci] - C.lower[dof], pen_hi = C.upper[dof] - aux[ci];
                         rhs[ci] = 0;
                         if (pen_lo <= R(0)) { act |= 1u << ci; rhs[ci] = (-pen_lo * D.erp / D.dt - vu) * dinv[ci]; }
                         else if (pen_hi <= R(0)) { act |= 1u << ci; neg |= 1u << ci; rhs[ci] = (-pen_hi * D.erp / D.dt + vu) * dinv[ci]; }
@@ -416,18 +481,21 @@ exo_motor_kernel(EnvArrays<R> S, ChainConst<R> C, DynConst<R> D, int lag, int en
                         R worst = 0;
                         // sweep direction alternates: even sweeps run the rows backwards (Bullet: iteration & 1 ? j : size-1-j);
                         // both directions are separately unrolled so the row index stays a compile-time constant
-                        if (it & 1) pgs_sweep<R, true>(sM, D, act, neg, dinv, rhs, lam, dv, worst);
-                        else pgs_sweep<R, false>(sM, D, act, neg, dinv, rhs, lam, dv, worst);
+                        if (it & 1) pgs_sweep<R, true>(sM, D, act, neg, dinv, rhs, lam, dvc, worst);
+                        else pgs_sweep<R, false>(sM, D, act, neg, dinv, rhs, lam, dvc, worst);
                         sweeps_done++;
                         if (worst <= D.threshold) going = false;
                     }
                     if (!__any_sync(amask, going)) break;
                 }
 #pragma unroll
-                for (int r = 0; r < EXO_NDOF; r++) sV[r * NT] = qdu[r] + dv[r];      // new velocities, slot order
+                for (int ci = 0; ci < EXO_NCONS; ci++)               // new velocities, slot order: the scratch column still holds the
+                    if (D.cons[ci] >= 0) sV[D.dof_slot[(int)D.cons[ci]] * NT] += dvc[ci];   // unconstrained ones; motor entries cover every joint once
             } else {
                 // ---- 6b. a constraint list of another length (a different URDF): the general row list, indices at run time
                 //      (local memory). Same arithmetic, not tuned.
+#pragma unroll
+                for (int i = 0; i < EXO_NDOF; i++) sV[i * NT] = i < 5 ? D.kp * (tg[i] - q[i]) / D.dt : R(0);
                 int rj[EXO_MAX_ROWS];
                 R rsg[EXO_MAX_ROWS], rrhs[EXO_MAX_ROWS], rdinv[EXO_MAX_ROWS], rlo[EXO_MAX_ROWS], rhi[EXO_MAX_ROWS], rlam[EXO_MAX_ROWS];
                 R dvv[EXO_NDOF], qduv[EXO_NDOF];
@@ -437,7 +505,7 @@ exo_motor_kernel(EnvArrays<R> S, ChainConst<R> C, DynConst<R> D, int lag, int en
                     const int cc = D.cons[ci];
                     if (cc >= 0) {                          // motor row of dof cc -> slot
                         const int r = D.dof_slot[cc];
-                        const R vu = qduv[r], di = R(1) / sM[(r * EXO_NDOF + r) * NT];
+                        const R vu = qduv[r], di = R(1) / sM[D.tri[r][r] * NT];
                         const R desired = cc < 5 ? sV[cc * NT] + vu + D.kd * (R(0) - vu) : vu + R(1) * (R(0) - vu);
                         rj[m] = r; rsg[m] = R(1); rdinv[m] = di; rrhs[m] = (desired - vu) * di;
                         const R cap = cc < 5 ? D.cap_pos : D.cap_vel;
@@ -448,7 +516,7 @@ exo_motor_kernel(EnvArrays<R> S, ChainConst<R> C, DynConst<R> D, int lag, int en
                         for (int sgi = 0; sgi < 2; sgi++) {
                             const R pen = sgi ? pen_hi : pen_lo, sg = sgi ? R(-1) : R(1);
                             if (pen > R(0)) continue;
-                            const R di = R(1) / sM[(r * EXO_NDOF + r) * NT];
+                            const R di = R(1) / sM[D.tri[r][r] * NT];
                             rj[m] = r; rsg[m] = sg; rdinv[m] = di;
                             rrhs[m] = (-pen * D.erp / D.dt - sg * qduv[r]) * di;
                             rlo[m] = 0; rhi[m] = D.limit_cap; rlam[m] = 0; m++;
@@ -466,7 +534,7 @@ exo_motor_kernel(EnvArrays<R> S, ChainConst<R> C, DynConst<R> D, int lag, int en
                         else if (sum > rhi[idx]) { dl = rhi[idx] - rlam[idx]; rlam[idx] = rhi[idx]; }
                         else rlam[idx] = sum;
                         const R imp = rsg[idx] * dl;
-                        for (int i = 0; i < EXO_NDOF; i++) dvv[i] += sM[(i * EXO_NDOF + r) * NT] * imp;
+                        for (int i = 0; i < EXO_NDOF; i++) dvv[i] += sM[D.tri[i][r] * NT] * imp;
                         const R res = dl / rdinv[idx];
                         worst = fmax(worst, res * res);
                     }

@@ -20,7 +20,7 @@ void launch_step_full(const EnvArrays<R>& A, const ChainConst<R>& C, const StepC
 template <typename R>
 void launch_motor(const EnvArrays<R>& A, const ChainConst<R>& C, const DynConst<R>& D, int lag, int env0, int env1, cudaStream_t s) {
     const int grid = (env1 - env0 + EXO_MOTOR_THREADS - 1) / EXO_MOTOR_THREADS;
-    const size_t smem = (size_t)(EXO_NDOF * EXO_NDOF + EXO_NDOF) * EXO_MOTOR_THREADS * sizeof(R);
+    const size_t smem = (size_t)(EXO_NTRI + EXO_NDOF) * EXO_MOTOR_THREADS * sizeof(R);
     static bool configured[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);

@@ -123,6 +123,8 @@ struct DynConst {
     int iterations, n_cons;
     signed char cons[EXO_MAX_ROWS];                // solver order: dof (motor row) or -(dof+1) (joint-limit constraint)
     signed char slot_dof[EXO_NDOF], dof_slot[EXO_NDOF];   // solver slot r = r-th motor row of `cons` <-> physical DoF
+    unsigned char tri[EXO_NDOF][EXO_NDOF];         // index of (a, b) = (b, a) among the 105 stored entries of the symmetric M^-1
+    unsigned char etri[19][19];                    // tri[slot of the joint of entry a][slot of the joint of entry b], entries of `cons`
 };
 
 template <typename R>

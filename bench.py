@@ -64,6 +64,29 @@ def settle(env):
     torch.cuda.synchronize(env.device)
 
 
+def in_kernel_span_ms(env, actions, flush, reps=6):
+    """First warp entry -> last warp exit of exo_step_kernel from the kernel's own timestamps (exo_debug_timeline: per-warp
+    globaltimer at entry + clock64 marks), L2 flushed: what the launch costs once the first instruction runs, i.e. the
+    CUDA-event figure minus launch latency, completion and event-pair overhead. Informative only; `roofline` uses events."""
+    import ctypes as C
+    import torch
+    nw = (env.n + 31) // 32
+    buf = torch.zeros(nw, 8, dtype=torch.int64, device=env.device)
+    spans = []
+    for rep in range(reps):
+        if flush is not None:
+            flush.zero_()
+        env.lib.exo_debug_timeline(env.h, C.c_void_p(buf.data_ptr()))
+        env.step(actions[rep % actions.shape[0]], keep_idle_obs=False)
+        torch.cuda.synchronize(env.device)
+        env.lib.exo_debug_timeline(env.h, None)
+        tl = buf.cpu().numpy()
+        t_entry = (tl[:, 0] - tl[:, 0].min()) * 1e-6                      # ms
+        life = (tl[:, 7] - tl[:, 2]) / 1.965e6                             # ms at the 1965 MHz the bench runs at
+        spans.append(float((t_entry + life).max()))
+    return float(np.median(spans[1:]))
+
+
 def dephase(env, actions, period=DEPHASE_PERIOD):
     """Untimed set-up: spread the envs over their episodes. env e is reset at pre-roll step e mod period; all envs step."""
     import torch
@@ -638,6 +661,7 @@ def main():
         k1[t].record()
     torch.cuda.synchronize(dev)
     kms = float(np.mean([a.elapsed_time(b) for a, b in zip(k0, k1)]))
+    span_ms = in_kernel_span_ms(env, actions, flush) if rank == 0 else None
     clocks = sampler.stop()
 
     # ---- end to end through the host-buffer C-ABI call (exo_step_host): pinned H2D + kernels + D2H + sync per step.
@@ -724,6 +748,11 @@ def main():
                          "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of one launch, "
                                            + TRAFFIC_SOURCE + " (writes stay in L2 inside the launch)",
                          "kernel": "exo_step_kernel", "kernel_ms": kms,
+                         "in_kernel_span_ms": span_ms,
+                         "in_kernel_span_note": "first warp entry -> last warp exit from the kernel's own clocks (exo_debug_timeline), "
+                                                "instrumented launches: the event figure above minus launch / completion / event-pair "
+                                                "overhead; 1045 B x envs / span = %.0f GB/s = %.2f of peak. Not used for `frac`."
+                                                % (ALGO_BYTES_PER_ENV_STEP * n / (span_ms * 1e-3) / 1e9, ALGO_BYTES_PER_ENV_STEP * n / (span_ms * 1e-3) / 1e9 / peak),
                          "algorithmic_bytes_per_env_step": ALGO_BYTES_PER_ENV_STEP,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)"},
             "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cpu_cores, "kind": "port",
