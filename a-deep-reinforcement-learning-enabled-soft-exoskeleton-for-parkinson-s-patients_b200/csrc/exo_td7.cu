@@ -88,6 +88,8 @@ __device__ __forceinline__ void gemm_store(const GemmArgs& g, int m, int n, floa
     else atomicAdd(c, v);
 }
 
+#include "exo_td7_tc5.cuh"      // gemm_tc5_kernel: the same GEMM on tcgen05 + tensor memory (EXO_TD7_GEMM=tc5)
+
 // C tile 64 x TN per CTA (TN = 64 or 80), 256 threads, k in steps of 16 through a 4-stage cp.async ring (4-byte copies:
 // any alignment, either operand transposed, zero fill outside the matrix). The host picks TN so that the tiles fill one
 // wave of SMs: 1920 x 300 is 30 x 5 = 150 tiles of 64 x 64 - two more than a B200 has SMs, i.e. two waves - but
@@ -470,6 +472,7 @@ struct ExoTD7 {
     ExoTD7GradHook hook = nullptr;
     void* hook_user = nullptr;
     bool ffma = false;                      // EXO_TD7_FFMA=1: the FP32-pipe GEMM instead of the 3xTF32 tensor-core one
+    bool tc5 = false;                       // EXO_TD7_GEMM=tc5: 3xTF32 on tcgen05 / tensor memory (exo_td7_tc5.cuh) instead of mma.sync
     ExoTD7Config c;
     int64_t launches = 0, steps = 0;
     double sigma = 0;                       // hp.target_policy_noise, decays by policy_noise_decrease per iteration
@@ -516,6 +519,22 @@ struct Ctx {
 
     void gemm(bool ta, bool tb, GemmArgs g, int splits) {
         if (g.M <= 0 || g.N <= 0 || g.K <= 0) return;
+        if (t->tc5 && !t->ffma) {
+            // 128-row tiles: a 1920-row batch is 15 of them, so narrow operands are split along k to fill the SMs
+            const int mt5 = (g.M + tc5::TM5 - 1) / tc5::TM5;
+            auto ctas = [&](int tn) { return mt5 * ((g.N + tn - 1) / tn); };
+            const int tn5 = (g.N <= 64 || ctas(64) <= t->n_sm) && (g.N % 80 != 0 || g.N <= 64) ? 64 : 80;
+            int sp = splits;
+            if (sp <= 1 && g.out == OUT_ATOMIC) sp = 1;
+            g.kchunk = sp <= 1 ? g.K : (((g.K + sp - 1) / sp + tc5::KA - 1) / tc5::KA) * tc5::KA;
+            const int ks5 = (g.K + g.kchunk - 1) / g.kchunk;
+            dim3 grid5((g.N + tn5 - 1) / tn5, mt5, ks5);
+            if (!ta && tb) tc5::launch<false, true>(g, tn5, grid5, s);
+            else if (!ta && !tb) tc5::launch<false, false>(g, tn5, grid5, s);
+            else tc5::launch<true, false>(g, tn5, grid5, s);
+            t->launches++;
+            return;
+        }
         g.kchunk = splits <= 1 ? g.K : (((g.K + splits - 1) / splits + TK - 1) / TK) * TK;
         const int ks = (g.K + g.kchunk - 1) / g.kchunk, mt = (g.M + TM - 1) / TM;
         // tile width: the one with the shorter critical path = waves of CTAs x columns per tile
@@ -930,6 +949,8 @@ extern "C" int exo_td7_create(int32_t device, const ExoTD7Config* cfg, ExoTD7** 
     t->device = device; t->n_sm = prop.multiProcessorCount; t->c = c; t->sigma = c.target_policy_noise;
     const char* fm = getenv("EXO_TD7_FFMA");
     t->ffma = fm && fm[0] != '0';
+    const char* gemm_mode = getenv("EXO_TD7_GEMM");
+    t->tc5 = gemm_mode && !strcmp(gemm_mode, "tc5");
     const int B = c.batch_rows, S = c.state_dim, A = c.action_dim, Z = c.zs_dim, H = c.enc_hdim, C = c.critic_hdim, Ha = c.actor_hdim;
     t->def[0] = make_def({{Ha, S}, {Ha, Z + Ha}, {Ha, Ha}, {A, Ha}});
     t->def[1] = make_def({{C, S + A}, {C, 2 * Z + C}, {C, C}, {1, C}, {C, S + A}, {C, 2 * Z + C}, {C, C}, {1, C}});
