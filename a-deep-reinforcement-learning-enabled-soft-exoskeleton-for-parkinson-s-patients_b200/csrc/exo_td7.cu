@@ -472,6 +472,7 @@ struct ExoTD7 {
     ExoTD7GradHook hook = nullptr;
     void* hook_user = nullptr;
     bool ffma = false;                      // EXO_TD7_FFMA=1: the FP32-pipe GEMM instead of the 3xTF32 tensor-core one
+    int tc5_stages = 2;
     bool tc5 = false;                       // EXO_TD7_GEMM=tc5: 3xTF32 on tcgen05 / tensor memory (exo_td7_tc5.cuh) instead of mma.sync
     ExoTD7Config c;
     int64_t launches = 0, steps = 0;
@@ -529,9 +530,9 @@ struct Ctx {
             g.kchunk = sp <= 1 ? g.K : (((g.K + sp - 1) / sp + tc5::KA - 1) / tc5::KA) * tc5::KA;
             const int ks5 = (g.K + g.kchunk - 1) / g.kchunk;
             dim3 grid5((g.N + tn5 - 1) / tn5, mt5, ks5);
-            if (!ta && tb) tc5::launch<false, true>(g, tn5, grid5, s);
-            else if (!ta && !tb) tc5::launch<false, false>(g, tn5, grid5, s);
-            else tc5::launch<true, false>(g, tn5, grid5, s);
+            if (!ta && tb) tc5::launch<false, true>(g, tn5, t->tc5_stages, grid5, s);
+            else if (!ta && !tb) tc5::launch<false, false>(g, tn5, t->tc5_stages, grid5, s);
+            else tc5::launch<true, false>(g, tn5, t->tc5_stages, grid5, s);
             t->launches++;
             return;
         }

@@ -84,32 +84,87 @@ __device__ __forceinline__ void split_store(unsigned char* hi, unsigned char* lo
     *reinterpret_cast<float*>(lo + off) = x - h;
 }
 
-constexpr int TM5 = 128, KA = 32;                   // tile rows, k per atom (one 128-byte swizzle row)
+#ifdef TC5_TIMELINE
+__device__ long long tc5_marks[64];
+#define TC5_MARK(i) do { if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (i) < 64) tc5_marks[i] = clock64(); } while (0)
+#else
+#define TC5_MARK(i) do { } while (0)
+#endif
 
-template <int TN>
+constexpr int TM5 = 128, KA = 32;                   // tile rows, k per atom (one 128-byte swizzle row)
+constexpr int PACK_WARPS = 8, THREADS5 = (PACK_WARPS + 1) * 32;   // 8 packing / epilogue warps + the MMA-issuing warp
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t* r) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr));
+}
+
+template <int TN, int NS>
 struct Smem5 {
     static constexpr int A_BYTES = TM5 * 128, B_BYTES = TN * 128;             // one atom of A / B (hi or lo)
     static constexpr int STAGE = 2 * A_BYTES + 2 * B_BYTES;                   // A_hi | A_lo | B_hi | B_lo
     static constexpr int EPI_PITCH = TN + 1;
-    static constexpr int BYTES = 2 * STAGE + 1024 /* alignment slack */ + 64 /* barriers, tmem slot */;
-    static_assert(2 * STAGE >= TM5 * EPI_PITCH * 4, "the epilogue tile reuses the operand stages");
+    static constexpr int BYTES = NS * STAGE + 1024 /* alignment slack */ + 128 /* barriers, tmem slot */;
+    static_assert(NS * STAGE >= TM5 * EPI_PITCH * 4, "the epilogue tile reuses the operand stages");
 };
 
-template <bool TA, bool TB, int TN>
-__global__ void __launch_bounds__(128) gemm_tc5_kernel(GemmArgs g) {
-    using S = Smem5<TN>;
+template <bool TA, bool TB, int TN, int NS>
+__global__ void __launch_bounds__(THREADS5, NS == 2 ? 2 : 1) gemm_tc5_kernel(GemmArgs g) {
+    using S = Smem5<TN, NS>;
     extern __shared__ unsigned char smem_raw5[];
     unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw5) + 1023) & ~(uintptr_t)1023);   // 1024-aligned atoms
-    uint64_t* bars = reinterpret_cast<uint64_t*>(base + 2 * S::STAGE);        // [0,1] stage free, [2] accumulator done
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(base + NS * S::STAGE);       // full[NS] | free[NS] | accumulator done
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NS + 1);
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int m0 = blockIdx.y * TM5, n0 = blockIdx.x * TN;
     const int kbeg = blockIdx.z * g.kchunk, kend = min(g.K, kbeg + g.kchunk);
+    const int n_atoms = (kend - kbeg + KA - 1) / KA;
+    if (n_atoms <= 0) return;
+    const uint32_t bar0 = smem_u32(bars);
+    auto bar_full = [&](int s) { return bar0 + 8u * s; };
+    auto bar_free = [&](int s) { return bar0 + 8u * (NS + s); };
+    const uint32_t bar_done = bar0 + 8u * (2 * NS);
+    TC5_MARK(0);
+
+    // Thread -> element map of one atom for the 8 packing warps: 16 A elements and TN / 8 B elements per thread, rows
+    // row0 + 8 u (u = 0 .. 15 / TN/8 - 1) at one k of the atom, so that a thread's shared-memory offsets are op_off(row0, kk)
+    // + 1024 u (one 8-row group per u) and its global addresses one pointer + u * stride. Chosen so that a warp's loads cover
+    // whole 32-byte sectors AND its stores fall on 32 different banks of the swizzled image:
+    //   operand contiguous along k: the warp takes row (warp + 8 u), lanes = the 32 k      (bank = ((k / 4) ^ row) * 4 + k % 4)
+    //   operand contiguous along m / n: the warp takes k-group `warp` (4 k) of rows 8 u .. 8 u + 7, lane = (row % 8, k % 4)
+    constexpr int NA = TM5 / 8, NB = TN / 8;
+    const int ml = lane & 7, kl = lane >> 3;
+    const int a_row0 = TA ? ml : warp, a_kk = TA ? warp * 4 + kl : lane;
+    const int b_row0 = TB ? warp : ml, b_kk = TB ? lane : warp * 4 + kl;
+    const uint32_t a_off = op_off(a_row0, a_kk), b_off = op_off(b_row0, b_kk);
+    const float* pa = TA ? g.A + (size_t)(kbeg + a_kk) * g.lda + (m0 + a_row0) : g.A + (size_t)(m0 + a_row0) * g.lda + (kbeg + a_kk);
+    const float* pb = TB ? g.B + (size_t)(n0 + b_row0) * g.ldb + (kbeg + b_kk) : g.B + (size_t)(kbeg + b_kk) * g.ldb + (n0 + b_row0);
+    const int a_stride = TA ? 8 : 8 * g.lda, b_stride = TB ? 8 * g.ldb : 8;
+    const size_t a_step = TA ? (size_t)KA * g.lda : (size_t)KA, b_step = TB ? (size_t)KA : (size_t)KA * g.ldb;
+    const int a_ulim = max(g.M - m0 - a_row0 + 7, 0) >> 3, b_ulim = max(g.N - n0 - b_row0 + 7, 0) >> 3;   // rows row0 + 8 u inside the matrix
+    float ra[NA], rb[NB];
+    auto load_atom = [&](int atom) {
+        const int k0 = kbeg + atom * KA;
+        const int au = k0 + a_kk < kend ? a_ulim : 0, bu = k0 + b_kk < kend ? b_ulim : 0;
+#pragma unroll
+        for (int u = 0; u < NA; ++u) ra[u] = u < au ? __ldg(pa + u * a_stride) : 0.f;
+#pragma unroll
+        for (int u = 0; u < NB; ++u) rb[u] = u < bu ? __ldg(pb + u * b_stride) : 0.f;
+        pa += a_step; pb += b_step;
+    };
+
+    if (warp < PACK_WARPS) load_atom(0);              // in flight across the set-up below
     if (t == 0) {
-        mbar_init(smem_u32(&bars[0]), 1); mbar_init(smem_u32(&bars[1]), 1); mbar_init(smem_u32(&bars[2]), 1);
+#pragma unroll
+        for (int s = 0; s < NS; ++s) { mbar_init(bar_full(s), PACK_WARPS * 32); mbar_init(bar_free(s), 1); }
+        mbar_init(bar_done, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 0) {
+    if (warp == PACK_WARPS) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(128u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -118,101 +173,136 @@ __global__ void __launch_bounds__(128) gemm_tc5_kernel(GemmArgs g) {
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     constexpr uint32_t IDESC = idesc_tf32(TN, TM5);
+    TC5_MARK(1);
 
-    const int n_atoms = (kend - kbeg + KA - 1) / KA;
-    for (int atom = 0; atom < n_atoms; ++atom) {
-        const int stage = atom & 1, k0 = kbeg + atom * KA;
-        unsigned char* sAh = base + stage * S::STAGE;
-        unsigned char* sAl = sAh + S::A_BYTES;
-        unsigned char* sBh = sAl + S::A_BYTES;
-        unsigned char* sBl = sBh + S::B_BYTES;
-        if (atom >= 2) mbar_wait(smem_u32(&bars[stage]), ((atom >> 1) - 1) & 1);      // the MMAs that read this stage two atoms ago
-        // ---- pack A: 128 rows x 32 k
-        if (!TA) {                                   // A[m * lda + k]: lanes along k, a warp walks 32 rows
-#pragma unroll 4
-            for (int rr = 0; rr < 32; ++rr) {
-                const int r = warp * 32 + rr, gm = m0 + r, gk = k0 + lane;
-                const float x = (gm < g.M && gk < kend) ? g.A[(size_t)gm * g.lda + gk] : 0.f;
-                split_store(sAh, sAl, op_off(r, lane), x);
-            }
-        } else {                                     // A[k * lda + m]: lanes along m, a warp walks the 32 k of its 32 rows
-            const int r = warp * 32 + lane, gm = m0 + r;
-#pragma unroll 4
-            for (int kk = 0; kk < 32; ++kk) {
-                const int gk = k0 + kk;
-                const float x = (gm < g.M && gk < kend) ? g.A[(size_t)gk * g.lda + gm] : 0.f;
-                split_store(sAh, sAl, op_off(r, kk), x);
-            }
-        }
-        // ---- pack B: TN rows (n) x 32 k
-        if (TB) {                                    // B[n * ldb + k]: lanes along k
-            for (int r = warp; r < TN; r += 4) {
-                const int gn = n0 + r, gk = k0 + lane;
-                const float x = (gn < g.N && gk < kend) ? g.B[(size_t)gn * g.ldb + gk] : 0.f;
-                split_store(sBh, sBl, op_off(r, lane), x);
-            }
-        } else {                                     // B[k * ldb + n]: lanes along n
-            for (int e = t; e < TN * 32; e += 128) {
-                const int r = e % TN, kk = e / TN;
-                const int gn = n0 + r, gk = k0 + kk;
-                const float x = (gn < g.N && gk < kend) ? g.B[(size_t)gk * g.ldb + gn] : 0.f;
-                split_store(sBh, sBl, op_off(r, kk), x);
-            }
-        }
-        fence_proxy_async_smem();                    // generic-proxy writes -> visible to the tensor core's async proxy
-        __syncthreads();
-        if (t == 0) {
+    if (warp == PACK_WARPS) {
+        // ---- the MMA warp: per atom 4 k-steps x 3 products into the one accumulator, small terms first
+        int stage = 0, phase = 0;
+        for (int atom = 0; atom < n_atoms; ++atom) {
+            mbar_wait(bar_full(stage), phase);
             tc_fence_after();
-            const uint32_t ah = smem_u32(sAh), al = smem_u32(sAl), bh = smem_u32(sBh), bl = smem_u32(sBl);
+            if (lane == 0) {
+                const uint32_t ah = smem_u32(base + stage * S::STAGE), al = ah + S::A_BYTES, bh = al + S::A_BYTES, bl = bh + S::B_BYTES;
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) {         // 8 k per MMA = 32 bytes along the swizzled row
-                const uint32_t o = ks * 32;
-                tc_mma_tf32(tmem, smem_desc(al + o), smem_desc(bh + o), IDESC, (atom | ks) != 0);
-                tc_mma_tf32(tmem, smem_desc(ah + o), smem_desc(bl + o), IDESC, 1);
-                tc_mma_tf32(tmem, smem_desc(ah + o), smem_desc(bh + o), IDESC, 1);
+                for (int ks = 0; ks < 4; ++ks) {     // 8 k per MMA = 32 bytes along the swizzled row
+                    const uint32_t o = ks * 32;
+                    tc_mma_tf32(tmem, smem_desc(al + o), smem_desc(bh + o), IDESC, (atom | ks) != 0);
+                    tc_mma_tf32(tmem, smem_desc(ah + o), smem_desc(bl + o), IDESC, 1);
+                    tc_mma_tf32(tmem, smem_desc(ah + o), smem_desc(bh + o), IDESC, 1);
+                }
+                tc_commit(bar_free(stage));          // arrives when these MMAs have read the stage
+                if (atom == n_atoms - 1) tc_commit(bar_done);
             }
-            tc_commit(smem_u32(&bars[stage]));       // arrives when these MMAs have read the stage
-            if (atom == n_atoms - 1) tc_commit(smem_u32(&bars[2]));
+            __syncwarp();
+            if (++stage == NS) { stage = 0; phase ^= 1; }
+        }
+    } else {
+        // ---- the packing warps
+        int stage = 0, phase = 1;                    // parity of the stage's PREVIOUS use; first NS atoms do not wait
+        for (int atom = 0; atom < n_atoms; ++atom) {
+            if (atom >= NS) mbar_wait(bar_free(stage), phase);
+            TC5_MARK(8 + atom * 4);
+            float* dah = reinterpret_cast<float*>(base + stage * S::STAGE + a_off);
+            float* dbh = reinterpret_cast<float*>(base + stage * S::STAGE + 2 * S::A_BYTES + b_off);
+#pragma unroll
+            for (int u = 0; u < NA; ++u) {
+                const float x = ra[u], h = __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+                dah[u * 256] = h; dah[u * 256 + S::A_BYTES / 4] = x - h;
+            }
+#pragma unroll
+            for (int u = 0; u < NB; ++u) {
+                const float x = rb[u], h = __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+                dbh[u * 256] = h; dbh[u * 256 + S::B_BYTES / 4] = x - h;
+            }
+            fence_proxy_async_smem();                // generic-proxy writes -> visible to the tensor core's async proxy
+            mbar_arrive(bar_full(stage));
+            TC5_MARK(9 + atom * 4);
+            if (atom + 1 < n_atoms) load_atom(atom + 1);
+            TC5_MARK(10 + atom * 4);
+            if (++stage == NS) { stage = 0; phase ^= 1; }
         }
     }
-    // ---- epilogue: TMEM -> registers -> shared (row-major tile) -> gemm_store with the lanes along n
-    mbar_wait(smem_u32(&bars[2]), 0);
+
+    // ---- epilogue: TMEM -> registers -> shared (row-major tile), then rows with the lanes along n (coalesced), loads batched
+    mbar_wait(bar_done, 0);
     tc_fence_after();
+    TC5_MARK(3);
     float* tile = reinterpret_cast<float*>(base);    // [128][TN + 1]; every MMA has finished reading the stages
-    {
-        const int r = warp * 32 + lane;
+    if (warp < PACK_WARPS) {
+        const int q = warp & 3, half = warp >> 2, r = q * 32 + lane;       // TMEM lane quarter of this warp, column half
+        constexpr int HC = TN / 2;                    // 32 or 40 columns
 #pragma unroll
-        for (int c0 = 0; c0 < TN; c0 += 16) {
-            uint32_t v[16];
-            tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+        for (int c0 = 0; c0 < HC; c0 += 8) {
+            uint32_t v[8];
+            tmem_ld8(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * HC + c0), v);
             tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 16; ++j) tile[r * S::EPI_PITCH + c0 + j] = __uint_as_float(v[j]);
+            for (int j = 0; j < 8; ++j) tile[r * S::EPI_PITCH + half * HC + c0 + j] = __uint_as_float(v[j]);
         }
     }
     tc_fence_before();
     __syncthreads();
-    for (int e = t; e < TM5 * TN; e += 128) {
-        const int r = e / TN, c = e - r * TN;
-        gemm_store(g, m0 + r, n0 + c, tile[r * S::EPI_PITCH + c]);
-    }
-    __syncthreads();
-    if (warp == 0) {
+    TC5_MARK(4);
+    if (warp == PACK_WARPS) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(128u) : "memory");
+        return;
     }
+    constexpr int NJ = (TN + 31) / 32, RB = 4;        // columns per lane, rows per batch
+    float bj[NJ];
+    bool cv[NJ];
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+        const int c = lane + 32 * j;
+        cv[j] = c < TN && n0 + c < g.N;
+        bj[j] = (g.bias && cv[j]) ? __ldg(g.bias + n0 + c) : 0.f;
+    }
+    const int act = g.act, dact = g.dact, out = g.out;
+    for (int r0 = warp * (TM5 / PACK_WARPS); r0 < (warp + 1) * (TM5 / PACK_WARPS); r0 += RB) {
+        float d[RB][NJ], old[RB][NJ];
+#pragma unroll
+        for (int i = 0; i < RB; ++i)
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) {
+                const int m = m0 + r0 + i, n = n0 + lane + 32 * j;
+                const bool ok = cv[j] && m < g.M;
+                d[i][j] = (g.D && ok) ? __ldg(g.D + (size_t)m * g.ldd + n) : 0.f;
+                old[i][j] = (out == OUT_ADD && ok) ? g.C[(size_t)m * g.ldc + n] : 0.f;
+            }
+#pragma unroll
+        for (int i = 0; i < RB; ++i)
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) {
+                const int m = m0 + r0 + i, c = lane + 32 * j;
+                if (!(cv[j] && m < g.M)) continue;
+                float v = act_fwd(tile[(r0 + i) * S::EPI_PITCH + c] + bj[j], act);
+                if (g.D) v *= act_bwd(d[i][j], dact);
+                float* cp = g.C + (size_t)m * g.ldc + n0 + c;
+                if (out == OUT_STORE) *cp = v;
+                else if (out == OUT_ADD) *cp = old[i][j] + v;
+                else atomicAdd(cp, v);
+            }
+    }
+    TC5_MARK(5);
 }
 
 template <bool TA, bool TB>
-inline cudaError_t launch(const GemmArgs& g, int tn, dim3 grid, cudaStream_t s) {
+inline cudaError_t launch(const GemmArgs& g, int tn, int ns, dim3 grid, cudaStream_t s) {
     static bool configured = false;
     if (!configured) {
-        cudaFuncSetAttribute(gemm_tc5_kernel<TA, TB, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem5<64>::BYTES);
-        cudaFuncSetAttribute(gemm_tc5_kernel<TA, TB, 80>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem5<80>::BYTES);
+        cudaFuncSetAttribute(gemm_tc5_kernel<TA, TB, 64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem5<64, 2>::BYTES);
+        cudaFuncSetAttribute(gemm_tc5_kernel<TA, TB, 80, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem5<80, 2>::BYTES);
+        cudaFuncSetAttribute(gemm_tc5_kernel<TA, TB, 64, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem5<64, 3>::BYTES);
+        cudaFuncSetAttribute(gemm_tc5_kernel<TA, TB, 80, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem5<80, 3>::BYTES);
         configured = true;
     }
-    if (tn == 64) gemm_tc5_kernel<TA, TB, 64><<<grid, 128, Smem5<64>::BYTES, s>>>(g);
-    else gemm_tc5_kernel<TA, TB, 80><<<grid, 128, Smem5<80>::BYTES, s>>>(g);
+    if (ns == 2) {
+        if (tn == 64) gemm_tc5_kernel<TA, TB, 64, 2><<<grid, THREADS5, Smem5<64, 2>::BYTES, s>>>(g);
+        else gemm_tc5_kernel<TA, TB, 80, 2><<<grid, THREADS5, Smem5<80, 2>::BYTES, s>>>(g);
+    } else {
+        if (tn == 64) gemm_tc5_kernel<TA, TB, 64, 3><<<grid, THREADS5, Smem5<64, 3>::BYTES, s>>>(g);
+        else gemm_tc5_kernel<TA, TB, 80, 3><<<grid, THREADS5, Smem5<80, 3>::BYTES, s>>>(g);
+    }
     return cudaGetLastError();
 }
 
