@@ -472,8 +472,8 @@ struct ExoTD7 {
     ExoTD7GradHook hook = nullptr;
     void* hook_user = nullptr;
     bool ffma = false;                      // EXO_TD7_FFMA=1: the FP32-pipe GEMM instead of the 3xTF32 tensor-core one
-    int tc5_stages = 2;
-    bool tc5 = false;                       // EXO_TD7_GEMM=tc5: 3xTF32 on tcgen05 / tensor memory (exo_td7_tc5.cuh) instead of mma.sync
+    int tc5_cluster = 1;                    // EXO_TD7_TC5_CLUSTER: largest split-k cluster the tcgen05 GEMM may use (1, 2, 4)
+    bool tc5 = true;                        // 3xTF32 on tcgen05 / tensor memory (exo_td7_tc5.cuh); EXO_TD7_GEMM=mma: the mma.sync kernel
     ExoTD7Config c;
     int64_t launches = 0, steps = 0;
     double sigma = 0;                       // hp.target_policy_noise, decays by policy_noise_decrease per iteration
@@ -521,18 +521,27 @@ struct Ctx {
     void gemm(bool ta, bool tb, GemmArgs g, int splits) {
         if (g.M <= 0 || g.N <= 0 || g.K <= 0) return;
         if (t->tc5 && !t->ffma) {
-            // 128-row tiles: a 1920-row batch is 15 of them, so narrow operands are split along k to fill the SMs
+            // 128-row tiles: a 1920-row batch is 15 of them. Atomic outputs (weight gradients) split k over blockIdx.z as
+            // before; store / add outputs split k over a cluster of 2 (4 for single-column-tile layers) CTAs that sum
+            // their partial tiles through distributed shared memory, while the tile count leaves SMs idle.
             const int mt5 = (g.M + tc5::TM5 - 1) / tc5::TM5;
             auto ctas = [&](int tn) { return mt5 * ((g.N + tn - 1) / tn); };
             const int tn5 = (g.N <= 64 || ctas(64) <= t->n_sm) && (g.N % 80 != 0 || g.N <= 64) ? 64 : 80;
-            int sp = splits;
-            if (sp <= 1 && g.out == OUT_ATOMIC) sp = 1;
-            g.kchunk = sp <= 1 ? g.K : (((g.K + sp - 1) / sp + tc5::KA - 1) / tc5::KA) * tc5::KA;
-            const int ks5 = (g.K + g.kchunk - 1) / g.kchunk;
-            dim3 grid5((g.N + tn5 - 1) / tn5, mt5, ks5);
-            if (!ta && tb) tc5::launch<false, true>(g, tn5, t->tc5_stages, grid5, s);
-            else if (!ta && !tb) tc5::launch<false, false>(g, tn5, t->tc5_stages, grid5, s);
-            else tc5::launch<true, false>(g, tn5, t->tc5_stages, grid5, s);
+            const int atoms = (g.K + tc5::KA - 1) / tc5::KA;
+            int ck = 1, ks5 = 1;
+            if (g.out == OUT_ATOMIC) {
+                g.kchunk = splits <= 1 ? g.K : (((g.K + splits - 1) / splits + tc5::KA - 1) / tc5::KA) * tc5::KA;
+                ks5 = (g.K + g.kchunk - 1) / g.kchunk;
+            } else {
+                g.kchunk = g.K;
+                auto fits = [&](int c) { const int per = (atoms + c - 1) / c; return atoms - per * (c - 1) >= 1 && per >= 2; };
+                if (t->tc5_cluster >= 2 && ctas(tn5) * 2 <= t->n_sm + 12 && fits(2)) ck = 2;
+                if (t->tc5_cluster >= 4 && ctas(tn5) * 4 <= t->n_sm / 2 && fits(4)) ck = 4;
+            }
+            dim3 grid5((g.N + tn5 - 1) / tn5, mt5, ck > 1 ? ck : ks5);
+            if (!ta && tb) tc5::launch<false, true>(g, tn5, ck, grid5, s);          // (errors surface in cudaGetLastError, as for gemm_kernel)
+            else if (!ta && !tb) tc5::launch<false, false>(g, tn5, ck, grid5, s);
+            else tc5::launch<true, false>(g, tn5, ck, grid5, s);
             t->launches++;
             return;
         }
@@ -951,7 +960,8 @@ extern "C" int exo_td7_create(int32_t device, const ExoTD7Config* cfg, ExoTD7** 
     const char* fm = getenv("EXO_TD7_FFMA");
     t->ffma = fm && fm[0] != '0';
     const char* gemm_mode = getenv("EXO_TD7_GEMM");
-    t->tc5 = gemm_mode && !strcmp(gemm_mode, "tc5");
+    t->tc5 = !(gemm_mode && !strcmp(gemm_mode, "mma"));       // default: tcgen05; EXO_TD7_GEMM=mma keeps the mma.sync kernel
+    if (const char* ck = getenv("EXO_TD7_TC5_CLUSTER")) t->tc5_cluster = atoi(ck);
     const int B = c.batch_rows, S = c.state_dim, A = c.action_dim, Z = c.zs_dim, H = c.enc_hdim, C = c.critic_hdim, Ha = c.actor_hdim;
     t->def[0] = make_def({{Ha, S}, {Ha, Z + Ha}, {Ha, Ha}, {A, Ha}});
     t->def[1] = make_def({{C, S + A}, {C, 2 * Z + C}, {C, C}, {1, C}, {C, S + A}, {C, 2 * Z + C}, {C, C}, {1, C}});

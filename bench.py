@@ -354,9 +354,11 @@ def bench_td7(exo_b200, dev):
     torch.cuda.synchronize(dev)
     ms_upd = a.elapsed_time(b) / iters
     sc = t.scalars()
-    out = {"kernel": "gemm_kernel<.,.,TC> (csrc/exo_td7.cu)", "rows": envs * bs, "train_ms": ms, "train_iterations_per_s": 1e3 / ms,
+    gemm = "gemm_kernel<.,.,TC> (mma.sync, csrc/exo_td7.cu)" if os.environ.get("EXO_TD7_GEMM") == "mma" else \
+        "tc5::gemm_tc5_kernel (tcgen05.mma kind::tf32 x3, accumulator in tensor memory, csrc/exo_td7_tc5.cuh)"
+    out = {"kernel": gemm, "rows": envs * bs, "train_ms": ms, "train_iterations_per_s": 1e3 / ms,
            "update_only_ms": ms_upd, "transitions_per_s": envs * bs / (ms * 1e-3),
-           "dtype": "f32 storage and sums, 3xTF32 tensor-core products (fp32-class; EXO_TD7_FFMA=1 = FP32-pipe products)",
+           "dtype": "f32 storage and sums, 3xTF32 tensor-core products (fp32-class; EXO_TD7_GEMM=mma = the mma.sync kernel, EXO_TD7_FFMA=1 = FP32-pipe products)",
            "launches_per_iteration": (t.launch_count() - l0) / (2.0 * iters),
            "what": "LAP.sample + encoder/critic/(actor every 2nd) update + Adam + update_priority per iteration, device resident",
            "losses": {k: sc[k] for k in ("encoder_loss", "critic_loss", "actor_loss")}}

@@ -50,14 +50,15 @@ __device__ __forceinline__ void gemm_store(const GemmArgs& g, int m, int n, floa
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("%s: %s\n", #x, cudaGetErrorString(e_)); exit(1); } } while (0)
 
 struct Case { const char* name; bool ta, tb; int M, N, K, lda, ldb, tn, splits; bool bias; int act; bool deriv; int out; };
-static int g_ns = 2;
+static int g_ck = 1;
 
 int main(int argc, char** argv) {
-    if (argc > 1) g_ns = atoi(argv[1]);
-    printf("stages %d\n", g_ns);
+    if (argc > 1) g_ck = atoi(argv[1]);
+    printf("cluster split-k %d (store outputs)\n", g_ck);
     const int rows = 1920;
     std::vector<Case> cases = {
         {"fwd 1920x300x300 elu tn80", false, true, rows, 300, 300, 300, 300, 80, 1, true, ACT_ELU, false, OUT_STORE},
+        {"fwd 1920x300x300 none tn80", false, true, rows, 300, 300, 300, 300, 80, 1, false, ACT_NONE, false, OUT_STORE},
         {"fwd 1920x300x300 elu tn64", false, true, rows, 300, 300, 300, 300, 64, 1, true, ACT_ELU, false, OUT_STORE},
         {"fwd 1920x320x920 elu tn80", false, true, rows, 320, 920, 920, 920, 80, 1, true, ACT_ELU, false, OUT_STORE},
         {"fwd 1920x7x300 tanh tn64", false, true, rows, 7, 300, 300, 300, 64, 1, true, ACT_TANH, false, OUT_STORE},
@@ -77,11 +78,12 @@ int main(int argc, char** argv) {
         g.A = A; g.lda = c.lda; g.B = B; g.ldb = c.ldb; g.C = C; g.ldc = c.N; g.M = c.M; g.N = c.N; g.K = c.K;
         g.bias = c.bias ? bias : nullptr; g.act = c.act; g.D = c.deriv ? D : nullptr; g.ldd = c.N; g.dact = ACT_ELU; g.out = c.out;
         g.kchunk = c.splits <= 1 ? c.K : (((c.K + c.splits - 1) / c.splits + tc5::KA - 1) / tc5::KA) * tc5::KA;
-        dim3 grid((c.N + c.tn - 1) / c.tn, (c.M + 127) / 128, (c.K + g.kchunk - 1) / g.kchunk);
+        const int ck = c.out == OUT_ATOMIC ? 1 : g_ck;
+        dim3 grid((c.N + c.tn - 1) / c.tn, (c.M + 127) / 128, ck > 1 ? ck : (c.K + g.kchunk - 1) / g.kchunk);
         auto go = [&]() {
-            if (!c.ta && c.tb) CK((tc5::launch<false, true>(g, c.tn, g_ns, grid, 0)));
-            else if (!c.ta && !c.tb) CK((tc5::launch<false, false>(g, c.tn, g_ns, grid, 0)));
-            else CK((tc5::launch<true, false>(g, c.tn, g_ns, grid, 0)));
+            if (!c.ta && c.tb) CK((tc5::launch<false, true>(g, c.tn, ck, grid, 0)));
+            else if (!c.ta && !c.tb) CK((tc5::launch<false, false>(g, c.tn, ck, grid, 0)));
+            else CK((tc5::launch<true, false>(g, c.tn, ck, grid, 0)));
         };
         // sampled check against a float64 product on the host
         CK(cudaMemset(C, 0, big * 4));
@@ -118,9 +120,9 @@ int main(int argc, char** argv) {
 #ifdef TC5_TIMELINE
         long long mk[64];
         CK(cudaMemcpyFromSymbol(mk, tc5::tc5_marks, sizeof(mk)));
-        const int na = (g.kchunk + 31) / 32;
-        printf("   cycles from kernel entry (warp 0): set-up done %lld | accumulator done %lld, tile in smem %lld, stored %lld\n",
-               mk[1] - mk[0], mk[3] - mk[0], mk[4] - mk[0], mk[5] - mk[0]);
+        const int na = ((g.kchunk + 31) / 32 + ck - 1) / ck;
+        printf("   cycles from kernel entry (warp 0): set-up done %lld | accumulator done %lld, tile in smem %lld, bias loaded %lld, first 4 rows %lld, stored %lld\n",
+               mk[1] - mk[0], mk[3] - mk[0], mk[4] - mk[0], mk[6] - mk[0], mk[7] - mk[0], mk[5] - mk[0]);
         for (int a = 0; a < na && 11 + a * 4 < 64; a++)
             printf("   atom %2d: stage free @%lld, packed + arrived +%lld, next loads issued +%lld\n", a, mk[8 + a * 4] - mk[0],
                    mk[9 + a * 4] - mk[8 + a * 4], mk[10 + a * 4] - mk[9 + a * 4]);
