@@ -119,6 +119,7 @@ SIGNATURES = {
     "exo_policy_set_weights": (C.c_int, [C.c_void_p, C.POINTER(ExoPolicyWeights), C.c_int32, C.c_int32, C.c_int32]),
     "exo_policy_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
     "exo_policy_forward_fp32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "exo_policy_forward_fp32_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
     "exo_policy_profile": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(C.c_int64), C.c_void_p]),
     "exo_policy_launch_count": (C.c_int64, [C.c_void_p]),
     # include/exo_td7.h

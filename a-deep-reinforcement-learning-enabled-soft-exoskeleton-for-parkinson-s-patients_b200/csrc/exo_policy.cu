@@ -894,6 +894,18 @@ extern "C" int exo_policy_forward_fp32(ExoPolicy* p, const float* obs_dev, int64
     return EXO_OK;
 }
 
+// No allocation on this path: argument checks, one kernel launch (exo_policy_fp32.cu, scratch in a static __device__ array).
+extern "C" int exo_policy_forward_fp32_noalloc(ExoPolicy* p, const float* obs_dev, int64_t n, float max_action, float* actions_dev,
+                                               float* zs_dev, void* stream) {
+    if (!p || !obs_dev || !actions_dev || n < 0) return exo_set_error(EXO_ERR_ARG, "exo_policy_forward_fp32_noalloc: bad arguments");
+    if (!p->loaded) return exo_set_error(EXO_ERR_STATE, "exo_policy_forward_fp32_noalloc: no weights (exo_policy_set_weights first)");
+    if (((uintptr_t)obs_dev & 15) != 0) return exo_set_error(EXO_ERR_ARG, "exo_policy_forward_fp32_noalloc: obs must be 16-byte aligned");
+    if (n == 0) return EXO_OK;
+    if (int rc = exo_policy_f32_forward_noalloc(p->f32, obs_dev, n, max_action, actions_dev, zs_dev, stream)) return rc;
+    p->launches += 1;
+    return EXO_OK;
+}
+
 extern "C" int exo_policy_profile(ExoPolicy* p, const float* obs_dev, int64_t n, float* actions_dev, int64_t* clocks_host, void* stream) {
     if (!p || !clocks_host) return exo_set_error(EXO_ERR_ARG, "exo_policy_profile: bad arguments");
     long long* d = nullptr;

@@ -13,6 +13,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string.h>
+#include <mutex>
 #include <vector>
 
 #include "../../include/exo_env.h"
@@ -232,18 +233,47 @@ void transpose_into(float* dst, const float* W, int n_rows, int ld, int col0, in
 
 }  // namespace
 
+// Scratch of exo_policy_forward_fp32_noalloc: one BUF_FLOATS slice (64 rows x 304 floats = 77 824 B) per CTA for
+// EXO_POLICY_NOALLOC_MAX_OBS / 64 = 64 CTAs, 4.75 MiB, resident on every GPU that loads the library until the process
+// exits. In HOST code this name is a host-side stand-in, not a device address: noalloc_scratch_ptr() asks the runtime for
+// the address (cudaGetSymbolAddress, once per device, with that device current) and the launch passes that.
+constexpr int NOALLOC_MAX_CTAS = EXO_POLICY_NOALLOC_MAX_OBS / TM;
+static_assert(EXO_POLICY_NOALLOC_MAX_OBS % TM == 0, "whole tiles");
+static __device__ __align__(256) float g_noalloc_scratch[(size_t)NOALLOC_MAX_CTAS * BUF_FLOATS];
+
 struct ExoPolicyF32 {
     int device, n_sm;
     float *wt, *bias, *scratch;
+    float* scratch_static;       // device address of g_noalloc_scratch on `device`
 };
+
+namespace {
+constexpr int MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+float* g_noalloc_ptr[MAX_DEVICES] = {};
+// device address of g_noalloc_scratch on the CURRENT device (= `device`); resolved once per device
+cudaError_t noalloc_scratch_ptr(int device, float** out) {
+    if (device < 0 || device >= MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_ptr[device] == nullptr) {
+        float* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        g_noalloc_ptr[device] = ptr;
+    }
+    *out = g_noalloc_ptr[device];
+    return cudaSuccess;
+}
+}  // namespace
 
 int exo_policy_f32_create(int device, int n_sm, ExoPolicyF32** out) {
     ExoPolicyF32* p = new ExoPolicyF32();
-    p->device = device; p->n_sm = n_sm; p->wt = p->bias = p->scratch = nullptr;
+    p->device = device; p->n_sm = n_sm; p->wt = p->bias = p->scratch = nullptr; p->scratch_static = nullptr;
     cudaError_t e = cudaMalloc((void**)&p->wt, WT_FLOATS * sizeof(float));
     if (e == cudaSuccess) e = cudaMalloc((void**)&p->bias, BIAS_FLOATS * sizeof(float));
     if (e == cudaSuccess) e = cudaMalloc((void**)&p->scratch, (size_t)n_sm * BUF_FLOATS * sizeof(float));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(exo_policy_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e == cudaSuccess) e = noalloc_scratch_ptr(device, &p->scratch_static);      // (exo_policy_create made `device` current)
     if (e != cudaSuccess) {
         exo_policy_f32_destroy(p);
         return exo_set_error(EXO_ERR_CUDA, "exo_policy (fp32 path): %s", cudaGetErrorString(e));
@@ -288,5 +318,25 @@ int exo_policy_f32_forward(ExoPolicyF32* p, const float* obs_dev, long long n, f
     exo_policy_fp32_kernel<<<grid, NT, SMEM_BYTES, (cudaStream_t)stream>>>(a);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return exo_set_error(EXO_ERR_CUDA, "exo_policy_forward (fp32 path): %s", cudaGetErrorString(e));
+    return EXO_OK;
+}
+
+// exo_policy_forward_fp32_noalloc: the same kernel, one CTA per 64-row tile, its scratch slices in g_noalloc_scratch. Nothing
+// is allocated or freed here (one kernel launch + cudaGetLastError). The kernel writes every word of a CTA's slice (a0 for all
+// 64 rows x 304 columns) before it reads it back, so the array's contents from the previous call need no clearing; two calls
+// that overlap on the GPU (different streams, or different handles on one device) would share the slices and race.
+int exo_policy_f32_forward_noalloc(ExoPolicyF32* p, const float* obs_dev, long long n, float max_action, float* actions_dev, float* zs_dev,
+                                   void* stream) {
+    if (n > EXO_POLICY_NOALLOC_MAX_OBS)
+        return exo_set_error(EXO_ERR_ARG, "exo_policy_forward_fp32_noalloc: %lld observations exceed the static scratch's maximum of %d "
+                             "(EXO_POLICY_NOALLOC_MAX_OBS); split the batch or use exo_policy_forward_fp32", n, EXO_POLICY_NOALLOC_MAX_OBS);
+    if (p->scratch_static == nullptr) return exo_set_error(EXO_ERR_STATE, "exo_policy_forward_fp32_noalloc: static scratch not resolved");
+    F32Args a;
+    a.obs = obs_dev; a.wt = p->wt; a.bias = p->bias; a.scratch = p->scratch_static; a.actions = actions_dev; a.zs = zs_dev;
+    a.n = n; a.max_action = max_action;
+    a.n_tiles = (int)((n + TM - 1) / TM);            // <= NOALLOC_MAX_CTAS
+    exo_policy_fp32_kernel<<<a.n_tiles, NT, SMEM_BYTES, (cudaStream_t)stream>>>(a);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return exo_set_error(EXO_ERR_CUDA, "exo_policy_forward_fp32_noalloc: %s", cudaGetErrorString(e));
     return EXO_OK;
 }

@@ -8,4 +8,5 @@ int exo_policy_f32_create(int device, int n_sm, ExoPolicyF32** out);
 void exo_policy_f32_destroy(ExoPolicyF32* p);
 int exo_policy_f32_set_weights(ExoPolicyF32* p, const ExoPolicyWeights* w);
 int exo_policy_f32_forward(ExoPolicyF32* p, const float* obs_dev, long long n, float max_action, float* actions_dev, float* zs_dev, void* stream);
+int exo_policy_f32_forward_noalloc(ExoPolicyF32* p, const float* obs_dev, long long n, float max_action, float* actions_dev, float* zs_dev, void* stream);
 #endif

@@ -65,6 +65,22 @@ int exo_policy_forward(ExoPolicy* p, const float* obs_dev, int64_t n, float max_
 int exo_policy_forward_fp32(ExoPolicy* p, const float* obs_dev, int64_t n, float max_action, float* actions_dev, float* zs_dev,
                             void* stream);
 
+/* exo_policy_forward_fp32 for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE.
+ * Same kernel, arguments and results (bit-identical) as exo_policy_forward_fp32, but the kernel's per-CTA scratch lives in a
+ * file-scope `static __device__` array in csrc/exo_policy_fp32.cu - 64 CTAs x 77 824 B = 4.75 MiB that every GPU which loads
+ * the library holds until exit - and the call performs no cudaMalloc / cudaFree / allocating library call: it checks its
+ * arguments and launches one kernel on `stream`. (The handle - weights, the array's device address - is made beforehand by
+ * exo_policy_create / exo_policy_set_weights, which do allocate.)
+ *   limit   n <= EXO_POLICY_NOALLOC_MAX_OBS observations per call; larger n fails with EXO_ERR_ARG and a message naming the
+ *           limit (nothing is launched).
+ *   sharing every call on a device uses the same array, which keeps the previous call's contents. Nothing needs clearing
+ *           (the kernel overwrites a CTA's slice before reading it), but calls that OVERLAP on the GPU - two streams, or
+ *           two handles on one device - race on it: serialise them (one stream, or events). */
+#define EXO_POLICY_NOALLOC_MAX_OBS 4096
+int exo_policy_forward_fp32_noalloc(ExoPolicy* p, const float* obs_dev, int64_t n, float max_action, float* actions_dev,
+                                    float* zs_dev, void* stream);
+
 /* One forward pass (max_action 1) that also records the SM clock (clock64) of CTA 0's first tile; synchronises.
  * clocks_host[32]: [2*g], [2*g+1] = MMA issuer starts / has issued GEMM phase g (0..7: l0, zs1, zs2, zs3, l1-zs half,
  * l1-a0 half, l2, l3); [16+2*k], [17+2*k] = epilogue k (0 = observation load, 1..7 after each accumulator) begins /
