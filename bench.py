@@ -43,8 +43,14 @@ UNIT = "env-steps/s"
 ALGO_BYTES_PER_ENV_STEP = 1045
 # dram__bytes_read.sum + dram__bytes_write.sum of one exo_step_kernel<float,false,4> launch over 65 536 envs, from the
 # ncu --set full capture named in TRAFFIC_SOURCE (refreshed per round from the final code)
-STEP_KERNEL_DRAM_BYTES_65536 = 34154496 + 321792       # r02e: 34.15 MB read (= 521 B/env) + 0.32 MB written (the rest stays in L2)
-TRAFFIC_SOURCE = "profiles/r02e_ncu_full_step.txt"
+# Under the bench's own flush (zeroing 512 MiB leaves L2 full of DIRTY lines) every line the step kernel allocates pushes a
+# dirty flush line out to DRAM: r02O, `ncu --cache-control none` with the flush in front of every launch, 12 launches:
+# 34.09 MB read (= 520 B/env) + 38.29 MB written = 72.4 MB per launch. With a cold but CLEAN L2 (the flush followed by a read
+# pass; also ncu's default cache control, r02e) the same launch reads 34.1 MB and writes 0.1-0.3 MB: its own 34 MB of
+# results are still in L2 when it ends. Either way DRAM moves what the algorithm needs (1045 B/env = 68.5 MB) or less.
+STEP_KERNEL_DRAM_BYTES_65536 = 34090000 + 38290000
+STEP_KERNEL_DRAM_BYTES_65536_CLEAN_L2 = 34120000 + 127000
+TRAFFIC_SOURCE = "profiles/r02O_ncu_step_dirty_l2.csv"
 DEPHASE_PERIOD = 347          # longest reference motion: every env is reset once during the pre-roll
 MEAN_EPISODE_STEPS = float(np.mean([l - 3 for l in (232, 316, 282, 295, 270, 347, 266, 273)]))
 
@@ -663,6 +669,17 @@ def main():
         k1[t].record()
     torch.cuda.synchronize(dev)
     kms = float(np.mean([a.elapsed_time(b) for a, b in zip(k0, k1)]))
+    # the same with a cold but clean L2: the flush's dirty lines are drained by a read pass before the launch
+    kms_clean = kms
+    if flush is not None:
+        for t in range(ksteps):
+            flush.zero_()
+            flush.view(torch.int32).sum()
+            k0[t].record()
+            env.step(actions[t % n_act], keep_idle_obs=False)
+            k1[t].record()
+        torch.cuda.synchronize(dev)
+        kms_clean = float(np.mean([a.elapsed_time(b) for a, b in zip(k0, k1)]))
     span_ms = in_kernel_span_ms(env, actions, flush) if rank == 0 else None
     clocks = sampler.stop()
 
@@ -748,7 +765,15 @@ def main():
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": STEP_KERNEL_DRAM_BYTES_65536 if (n == 65536 and args.precision == "fp32") else None,
                          "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of one launch, "
-                                           + TRAFFIC_SOURCE + " (writes stay in L2 inside the launch)",
+                                           + TRAFFIC_SOURCE + " (--cache-control none, the bench's flush before every launch: 34.1 MB "
+                                           "read + 38.3 MB of the flush's dirty lines written back; with a clean cold L2 the launch "
+                                           "reads 34.1 MB and writes 0.1 MB, profiles/r02O_ncu_step_clean_l2.csv)",
+                         "traffic_clean_l2": STEP_KERNEL_DRAM_BYTES_65536_CLEAN_L2 if (n == 65536 and args.precision == "fp32") else None,
+                         "kernel_ms_clean_l2": kms_clean,
+                         "clean_l2_note": "same launches with the flush followed by a read pass over the flush buffer (L2 cold, no dirty "
+                                          "lines to write back): 1045 B x envs / kernel_ms_clean_l2 = %.0f GB/s = %.2f of peak. Informative; "
+                                          "`frac` uses the write-flushed launches." % (
+                                              ALGO_BYTES_PER_ENV_STEP * n / (kms_clean * 1e-3) / 1e9, ALGO_BYTES_PER_ENV_STEP * n / (kms_clean * 1e-3) / 1e9 / peak),
                          "kernel": "exo_step_kernel", "kernel_ms": kms,
                          "in_kernel_span_ms": span_ms,
                          "in_kernel_span_note": "first warp entry -> last warp exit from the kernel's own clocks (exo_debug_timeline), "
