@@ -550,13 +550,6 @@ __device__ __forceinline__ void begin_episode(const EnvArrays<R>& S, const Chain
     // fly while the chain is evaluated), and every store comes after the last load: with loads interleaved between the
     // stores the 21 shift reads were 21 exposed memory latencies (~10 us on the step's critical path, r02g)
     R sh[4 * NV_EP], rows[3][4];
-#ifdef EXO_DBG_BEGIN_NOLOAD      // timing experiment only (wrong results): is the episode-start path's cost its data loads?
-#pragma unroll
-    for (int v = 0; v < 4 * NV_EP; v++) sh[v] = R(0.001) * v;
-#pragma unroll
-    for (int k = 0; k < 3; k++) { rows[k][0] = rows[k][1] = rows[k][2] = rows[k][3] = R(k); }
-    (void)ep; (void)tt;
-#else
     if (sizeof(R) == 4 && st_ep != nullptr) {
 #pragma unroll
         for (int v = 0; v < NV_EP; v++) { const float4 t = st_ep[v]; sh[4 * v] = (R)t.x; sh[4 * v + 1] = (R)t.y; sh[4 * v + 2] = (R)t.z; sh[4 * v + 3] = (R)t.w; }
@@ -568,7 +561,6 @@ __device__ __forceinline__ void begin_episode(const EnvArrays<R>& S, const Chain
 #pragma unroll
         for (int k = 0; k < 3; k++) ld4_ord(tt + ((size_t)k * st + e) * NAXV, rows[k]);
     }
-#endif
     float ob[80];
     ChainPose<R> P;
     chain_fk(C, qs, P);
@@ -606,9 +598,6 @@ __device__ __forceinline__ void begin_episode(const EnvArrays<R>& S, const Chain
         ob[68 + k] = (float)C.sh_ref[k]; ob[71 + k] = (float)P.elref[k];
         ob[74 + k] = (float)C.sh_ref[k]; ob[77 + k] = (float)P.elref[k];
     }
-#ifdef EXO_DBG_BEGIN_NOSTORE     // timing experiment only: ... or its 26 scalar stores?
-    if (pv[0] == R(12345.678)) {
-#endif
     {   // words 10..33 of the state record = elref[3] | posvec[21]: vectors 3..7 whole, the four words around them singly
         static_assert(W_ELREF == 10 && W_POSVEC == 13, "state layout");
         V4<R>* sv = S.state + e;
@@ -620,9 +609,6 @@ __device__ __forceinline__ void begin_episode(const EnvArrays<R>& S, const Chain
         sv[(size_t)8 * st].v[0] = pv[19]; sv[(size_t)8 * st].v[1] = pv[20];
     }
     S.ret[e] = R(0);
-#ifdef EXO_DBG_BEGIN_NOSTORE
-    }
-#endif
     S.counts[e] = 2 | (new_slot << EXO_SLOT_SHIFT);                                   // counts = 2 (:220)
 #pragma unroll
     for (int ch = 0; ch < 11; ch++) obA[ch] = make_float4(ob[4 * ch], ob[4 * ch + 1], ob[4 * ch + 2], ob[4 * ch + 3]);
