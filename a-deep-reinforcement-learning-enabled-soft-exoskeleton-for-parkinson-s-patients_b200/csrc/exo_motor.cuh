@@ -13,8 +13,9 @@
 // cancels the gravity impulse (0.245 N s < the 1 N s cap) exactly in its first sweep, so they never move and are not
 // simulated. Everything is evaluated in the world frame.
 //
-// Cost: ~12 kflop + up to 50 x 14 x 15 FMA per env-step, fp32 or fp64 like the rest of the handle; the 14 x 14
-// inverse mass matrix lives in local memory (L1-resident). Compute-bound, unlike the HBM-bound default step.
+// Cost: ~12 kflop + up to 50 x 14 x 15 FMA per env-step, fp32 or fp64 like the rest of the handle; the symmetric 14 x 14
+// inverse mass matrix lives in shared memory ([entry][thread], 105 entries, compile-time offsets). Compute-bound, unlike
+// the HBM-bound default step.
 #pragma once
 #include "exo_step.cuh"
 

@@ -2,6 +2,8 @@
 // :230-312) with every network, gradient and Adam state resident in HBM.
 //
 // Building blocks:
+//   tc5::gemm_tc5_kernel  (exo_td7_tc5.cuh, the DEFAULT) the GEMM contract below on tcgen05: 128 x TN tiles, 3xTF32 products
+//                         with the accumulator in tensor memory. EXO_TD7_GEMM=mma selects gemm_kernel instead.
 //   gemm_kernel<TA,TB,TC,TN>  C = op(A) op(B) on 64 x TN x 16 tiles (TN = 64 | 80, picked per launch so the tiles fill one
 //                         wave of SMs), 256 threads, a 4-stage cp.async ring. TC: the products run on the tensor cores as
 //                         3xTF32 (split operands, mma.sync m16n8k8, fp32 accumulation; fp32-class accuracy); !TC
