@@ -619,6 +619,10 @@ def main():
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    # nvidia-smi is started ahead of the untimed set-up: its start-up (a process spawn + NVML initialisation per rank) would
+    # otherwise compete with the host thread that launches the first timed steps; it keeps sampling through the timed region
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     env.reset()
     if not args.no_dephase:
         dephase(env, actions)
@@ -626,8 +630,6 @@ def main():
         env.step(actions[t % n_act])
     env.stats(reset=True)
     barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
     ev0 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     ev1 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     launches0 = env.launch_count
